@@ -1,0 +1,165 @@
+/*
+ * voxelnet_b200.h - C ABI of libvoxelnet_b200.so: the VoxelNet front-end hot path
+ * (voxelize -> stacked VFE -> sparse-to-dense scatter -> Conv3d middle layers) as hand-written
+ * sm_100a CUDA kernels.
+ *
+ * The reference (johanngerberding/voxelnet-pytorch) is pure Python and has no FFI; the interfaces
+ * these entry points replace are Python call sites, cited per function as `file:line` relative to
+ * the reference root.  The Python host side that mirrors those call sites lives in
+ * voxelnet-pytorch_b200/{utils,dataset,model}.py and binds this header with ctypes
+ * (voxelnet-pytorch_b200/_cabi.py); INTEGRATION.md shows the stub a reference maintainer adds.
+ *
+ * Conventions
+ *   - Every pointer is a DEVICE pointer unless its name ends in `_host`.  The caller allocates all
+ *     buffers including workspaces; the library owns no device memory.
+ *   - `stream` is a cudaStream_t passed as void*.  Calls only enqueue work: no hidden host
+ *     synchronisation, no host callbacks.  (The one exception is documented at vn_voxelize_counts_host.)
+ *   - Return value: 0 = ok, < 0 = bad argument (VN_ERR_*), > 0 = cudaError_t.  vn_last_error()
+ *     returns a thread-local message for the last non-zero return.
+ *   - There is no CPU fallback: without a CUDA device every compute entry point fails.
+ */
+#ifndef VOXELNET_B200_H
+#define VOXELNET_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define VN_ABI_VERSION 1
+
+#define VN_OK 0
+#define VN_ERR_BAD_ARG (-1)
+#define VN_ERR_WORKSPACE (-2)
+#define VN_ERR_UNSUPPORTED (-3)
+#define VN_ERR_DRIVER (-4)
+
+typedef void* vn_stream_t; /* cudaStream_t */
+
+/* Per-class grid constants: voxelnet/utils.py:24-33 (voxelizer) and voxelnet/config.py:38-50,61-73
+ * (model side).  Axis naming follows the reference: D = z cells, H = y cells, W = x cells. */
+typedef struct vn_grid {
+  int32_t D, H, W;       /* grid_size (z, y, x): Car 10x400x352, Ped/Cyc 10x200x240          */
+  int32_t T;             /* max points per voxel: 35 / 45                                     */
+  float off_x, off_y, off_z; /* lidar_coord added to (x, y, z): (0, 40, 3) / (0, 20, 3)       */
+  float vs_x, vs_y, vs_z;    /* voxel size along (x, y, z): (0.2, 0.2, 0.4), as float32       */
+} vn_grid_t;
+
+int vn_abi_version(void);
+const char* vn_last_error(void);
+
+/* utils.py:24-33: target == "Car" selects the Car grid, any other string Pedestrian/Cyclist. */
+int vn_grid_for_target(const char* target, vn_grid_t* grid_out);
+
+/* ------------------------------------------------------------------------------------------
+ * Voxelizer - replaces pcl_to_voxels (voxelnet/utils.py:10-100) and prepare_voxel's batch column
+ * (voxelnet/dataset.py:101-119) for a whole batch of frames in one call sequence.
+ *
+ * Frames are concatenated: points[frame_offsets[f] .. frame_offsets[f+1]) belong to frame f,
+ * each point 4 x float32 (x, y, z, reflectance) as in dataset.py:51.  Point ORDER is the
+ * caller's (the reference's shuffle, utils.py:35, is the caller's business - see DESIGN.md).
+ *
+ * Phase 1 (vn_voxelize_index): range crop + voxel index with IEEE fp32 add/divide/floor
+ *   (utils.py:37-61), per-frame occupancy bitmap, sorted-unique rank of every occupied cell
+ *   (== np.unique(axis=0) order, utils.py:63), per-voxel point counts and per-point arrival
+ *   slots.  Writes voxel_offsets[0..n_frames] = exclusive prefix of voxels per frame
+ *   (voxel_offsets[n_frames] = total K).
+ * Phase 2 (vn_voxelize_fill): first-T-points-in-array-order selection (utils.py:78-84), 7-d
+ *   features with fp64 centroid arithmetic (utils.py:87-88), int64 coordinates [b, z, y, x],
+ *   int64 counts.  Rows >= max_voxels are dropped (the caller sized the outputs from
+ *   voxel_offsets, or passed a capacity).
+ * ------------------------------------------------------------------------------------------ */
+size_t vn_voxelize_workspace_bytes(const vn_grid_t* grid, int32_t n_frames, int64_t n_points_total);
+
+int vn_voxelize_index(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                      int32_t n_frames, int64_t n_points_total, int32_t max_points_per_frame,
+                      int32_t* voxel_offsets /* [n_frames + 1] */, void* workspace,
+                      size_t workspace_bytes, vn_stream_t stream);
+
+int vn_voxelize_fill(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                     int32_t n_frames, int64_t n_points_total, int32_t max_points_per_frame,
+                     const int32_t* voxel_offsets, int64_t max_voxels,
+                     float* feature_buffer /* [max_voxels, T, 7]  utils.py:71     */,
+                     int64_t* coordinate_buffer /* [max_voxels, 4] b,z,y,x  dataset.py:110-117 */,
+                     int64_t* number_buffer /* [max_voxels]        utils.py:69     */,
+                     void* workspace, size_t workspace_bytes, vn_stream_t stream);
+
+/* Convenience for the NumPy-returning wrapper: synchronises `stream` and copies
+ * voxel_offsets[0..n_frames] to the host.  This is the only entry point that blocks. */
+int vn_voxelize_counts_host(const int32_t* voxel_offsets, int32_t n_frames,
+                            int32_t* voxel_offsets_host, vn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Stacked VFE - replaces VFELayer.forward (voxelnet/model.py:74-82) and the VFE part of
+ * FeatureLearningNet.forward (model.py:95-100).  Eval-mode BatchNorm1d is passed folded as a
+ * post-ReLU affine: y = relu(W x + b) * bn_scale + bn_shift (Linear -> ReLU -> BN, model.py:68-76).
+ * ------------------------------------------------------------------------------------------ */
+
+/* One VFE layer, drop-in shapes: inputs [K, T, cin] f32, mask [K, T] u8 (bool) ->
+ * out [K, T, 2*units] f32 = concat(pointwise, max over all T rows) * mask.
+ * Supported (cin, units): (7, 16) and (32, 64) - the two instances at model.py:88-89. */
+int vn_vfe_layer_fwd(const float* inputs, const uint8_t* mask, int64_t K, int32_t T, int32_t cin,
+                     int32_t units, const float* weight /* [units, cin] */,
+                     const float* bias /* [units] */, const float* bn_scale, const float* bn_shift,
+                     float* out, vn_stream_t stream);
+
+/* model.py:95-96: mask[k, t] = (max_j feature[k, t, j] != 0). */
+int vn_feature_mask(const float* feature, int64_t K, int32_t T, int32_t cin, uint8_t* mask,
+                    vn_stream_t stream);
+
+/* Fused VFE-1 -> VFE-2 -> voxel-wise max (model.py:95-100): feature [K, T, 7] f32 ->
+ * voxelwise [K, 128] f32.  The mask is derived from the features exactly as the reference does.
+ * `n_voxels_dev` (optional, may be NULL) points at a device int32 holding the live K (<= K);
+ * it lets a pipeline run without a host read of K. */
+int vn_svfe_fused_fwd(const float* feature, int64_t K, int32_t T, const int32_t* n_voxels_dev,
+                      const float* w1 /* [16,7] */, const float* b1, const float* s1, const float* t1,
+                      const float* w2 /* [64,32] */, const float* b2, const float* s2,
+                      const float* t2, float* voxelwise /* [K,128] */, vn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Sparse -> dense - replaces torch.sparse.FloatTensor(coords.t(), voxelwise, [B,D,H,W,128])
+ * .to_dense() (voxelnet/model.py:102-106).  Layout of `dense`: [B, D, H, W, C] contiguous.
+ * ------------------------------------------------------------------------------------------ */
+int vn_fill_zero(void* ptr, size_t bytes, vn_stream_t stream);
+
+/* fp32 drop-in: dense must be zero-filled by the caller; duplicates are summed (COO coalesce). */
+int vn_scatter_dense_f32(const float* voxelwise, const int64_t* coords /* [K,4] b,z,y,x */, int64_t K,
+                         const int32_t* n_voxels_dev, int32_t C, int32_t B, int32_t D, int32_t H,
+                         int32_t W, float* dense, vn_stream_t stream);
+
+/* bf16 fast path: writes (or, with clear != 0, re-zeroes) the K occupied rows of a bf16 grid that
+ * is kept resident and zero between frames, so the 360 MB/frame zero-fill is paid once. */
+int vn_scatter_dense_bf16(const float* voxelwise, const int64_t* coords, int64_t K,
+                          const int32_t* n_voxels_dev, int32_t C, int32_t B, int32_t D, int32_t H,
+                          int32_t W, void* dense_bf16, int32_t clear, vn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Conv3d middle layers - replaces ConvMD(3, ...).forward = Conv3d(k=3) -> BatchNorm3d -> ReLU
+ * (voxelnet/model.py:158-167; the three instances at :207-209) and the reshape at :262.
+ * bf16 implicit GEMM on tcgen05/TMEM, TMA-fed; fp32 accumulate; eval-mode BN + conv bias folded
+ * into a per-channel fp32 (scale, shift) applied in the epilogue before ReLU.
+ * ------------------------------------------------------------------------------------------ */
+
+/* Repack torch-layout fp32 weights [64, cin, 3, 3, 3] into the kernel's bf16 tap-major,
+ * 128B-swizzled tile layout.  packed holds 27 * cin * 64 bf16. */
+size_t vn_conv3d_packed_weight_bytes(int32_t cin);
+int vn_conv3d_pack_weights(const float* weight, int32_t cin, void* packed, vn_stream_t stream);
+
+/* x: [B, Din, H, W, cin] bf16 (NDHWC).  cin in {64, 128}, cout = 64, kernel 3x3x3, H/W stride 1 and
+ * padding 1; depth stride/padding (stride_d, pad_d) in {(2,1), (1,0)}.
+ * out_mode 0: y [B, Dout, H, W, 64] bf16 (NDHWC) - feeds the next layer.
+ * out_mode 1: y [B, 64*Dout, H, W] f32 with channel = c*Dout + d - the reshape of model.py:262. */
+int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin,
+                          int32_t stride_d, int32_t pad_d, const void* packed_weight,
+                          const float* scale /* [64] */, const float* shift /* [64] */,
+                          int32_t out_mode, void* y, vn_stream_t stream);
+
+/* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
+int64_t vn_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VOXELNET_B200_H */

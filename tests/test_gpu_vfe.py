@@ -1,0 +1,90 @@
+"""GPU parity: fused SVFE and per-layer VFE kernels vs the CPU fp32 oracle (rel 1e-4)."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_torch as OM
+from oracle import voxelize_np as OV
+from tests.helpers import load_state, synth_frames
+
+pytestmark = pytest.mark.gpu
+
+RTOL = 1e-4  # north_star: "VFE outputs must be within 1e-4 relative in fp32"
+
+
+def _close(got, want, what):
+    got, want = got.double().cpu(), want.double()
+    err = (got - want).abs()
+    tol = RTOL * want.abs() + RTOL * float(want.abs().max()) * 1e-2
+    assert bool((err <= tol).all()), "%s: max err %.3e (max |ref| %.3e)" % (what, float(err.max()), float(want.abs().max()))
+
+
+@pytest.mark.parametrize("target", ["Car", "Pedestrian"])
+def test_svfe_fused_matches_oracle(cuda_device, target):
+    import voxelnet_pytorch_b200 as vn
+
+    sd = OM.random_state_dict(1)
+    feat = torch.from_numpy(OV.pcl_to_voxels_fast(synth_frames(1, 2)[0], target)["feature_buffer"])
+    want = OM.svfe_voxelwise(feat, sd)
+    net = vn.FeatureLearningNet(target).eval()
+    load_state(net, sd, "")
+    net = net.to(cuda_device)
+    got = net.voxelwise(feat.to(cuda_device))
+    _close(got, want, "svfe voxelwise")
+
+
+def test_svfe_handles_arbitrary_rows(cuda_device):
+    """No assumption about pad rows: random features incl. all-zero rows, rows whose max is 0
+    (mask off although non-zero), fully populated voxels and voxels made of one repeated row."""
+    import voxelnet_pytorch_b200 as vn
+
+    g = torch.Generator().manual_seed(0)
+    K, T = 300, 35
+    feat = torch.randn((K, T, 7), generator=g)
+    feat[:40, 5:] = 0.0                       # zero tails
+    feat[40:80] = -feat[40:80].abs()          # all negative -> max < 0 -> mask on
+    feat[80:120, :, :] = torch.minimum(feat[80:120], torch.zeros(()))  # max may be exactly 0 -> mask off
+    feat[80:120, ::2, 3] = 0.0
+    feat[120:160] = feat[120:160, :1].expand(-1, T, -1)  # one repeated row
+    feat[160:170] = 0.0                       # completely empty voxel
+    sd = OM.random_state_dict(2)
+    want = OM.svfe_voxelwise(feat, sd)
+    net = vn.FeatureLearningNet().eval()
+    load_state(net, sd, "")
+    got = net.to(cuda_device).voxelwise(feat.to(cuda_device))
+    _close(got, want, "svfe voxelwise (arbitrary rows)")
+
+
+@pytest.mark.parametrize("layer,cin,cout", [("vfe_1.", 7, 32), ("vfe_2.", 32, 128)])
+def test_vfe_layer_dropin(cuda_device, layer, cin, cout):
+    import voxelnet_pytorch_b200 as vn
+
+    g = torch.Generator().manual_seed(3)
+    K, T = 257, 35
+    x = torch.randn((K, T, cin), generator=g)
+    x[:, 20:] *= (torch.rand((K, 15, 1), generator=g) > 0.5)
+    mask = torch.rand((K, T, 1), generator=g) > 0.3
+    sd = OM.random_state_dict(4)
+    want = OM.vfe_layer(x, mask, sd, layer)
+    m = vn.VFELayer(cin, cout).eval()
+    load_state(m, sd, layer)
+    got = m.to(cuda_device)(x.to(cuda_device), mask.to(cuda_device))
+    assert got.shape == (K, T, cout)
+    _close(got, want, "vfe layer " + layer)
+
+
+def test_feature_mask(cuda_device):
+    from voxelnet_pytorch_b200 import ops
+
+    feat = torch.from_numpy(OV.pcl_to_voxels_fast(synth_frames(1, 4)[0], "Car")["feature_buffer"])
+    want = OM.feature_mask(feat)
+    got = ops.feature_mask(feat.to(cuda_device))
+    assert got.dtype == torch.bool and torch.equal(got.cpu(), want)
+
+
+def test_train_mode_raises(cuda_device):
+    import voxelnet_pytorch_b200 as vn
+
+    net = vn.FeatureLearningNet().to(cuda_device).train()
+    with pytest.raises(NotImplementedError):
+        net.voxelwise(torch.zeros((1, 35, 7), device=cuda_device))

@@ -1,0 +1,87 @@
+"""Build libvoxelnet_b200.so in-tree with nvcc for sm_100a (no GPU needed: nvcc cross-compiles).
+
+    python voxelnet-pytorch_b200/build.py [--force] [--verbose]
+
+The shared library is written next to the sources' parent (`voxelnet-pytorch_b200/lib/`), is
+git-ignored, and travels to the GPU box inside the repo snapshot.  Objects are rebuilt only when a
+source or header is newer than the object.
+"""
+from __future__ import annotations
+
+import os
+import shutil
+import subprocess
+import sys
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+CSRC = os.path.join(HERE, "csrc")
+INCLUDE = os.path.join(ROOT, "include")
+OBJ_DIR = os.path.join(HERE, "build")
+LIB_DIR = os.path.join(HERE, "lib")
+LIB_PATH = os.path.join(LIB_DIR, "libvoxelnet_b200.so")
+
+SOURCES = ["vn_api.cu", "vn_voxelize.cu", "vn_vfe.cu", "vn_scatter.cu", "vn_conv3d.cu"]
+
+NVCC_FLAGS = [
+    "-gencode", "arch=compute_100a,code=sm_100a",
+    "-O3", "-std=c++17", "-lineinfo",
+    "-Xcompiler", "-fPIC,-O3,-Wall,-Wno-unused-function",
+    "-Xptxas", "-v",
+    "-I", INCLUDE, "-I", CSRC,
+]
+
+
+def _nvcc() -> str:
+    cand = shutil.which("nvcc") or "/usr/local/cuda/bin/nvcc"
+    if not os.path.exists(cand):
+        raise RuntimeError("nvcc not found; libvoxelnet_b200.so cannot be built")
+    return cand
+
+
+def _newer(path: str, deps: list) -> bool:
+    if not os.path.exists(path):
+        return True
+    t = os.path.getmtime(path)
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    """Compile every .cu to an object and link the shared library.  Returns the library path."""
+    os.makedirs(OBJ_DIR, exist_ok=True)
+    os.makedirs(LIB_DIR, exist_ok=True)
+    nvcc = _nvcc()
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    headers.append(os.path.join(INCLUDE, "voxelnet_b200.h"))
+    objs, log = [], []
+    procs = []
+    for src in SOURCES:
+        s = os.path.join(CSRC, src)
+        o = os.path.join(OBJ_DIR, src.replace(".cu", ".o"))
+        objs.append(o)
+        if force or _newer(o, [s] + headers):
+            cmd = [nvcc] + NVCC_FLAGS + ["-c", s, "-o", o]
+            procs.append((src, cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    for src, cmd, p in procs:
+        out, _ = p.communicate()
+        log.append("$ " + " ".join(cmd) + "\n" + out)
+        if p.returncode != 0:
+            sys.stderr.write(log[-1])
+            raise RuntimeError("nvcc failed on %s" % src)
+    if procs or force or _newer(LIB_PATH, objs):
+        cmd = [nvcc, "-shared", "-gencode", "arch=compute_100a,code=sm_100a", "-o", LIB_PATH] + objs
+        r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        log.append("$ " + " ".join(cmd) + "\n" + r.stdout)
+        if r.returncode != 0:
+            sys.stderr.write(log[-1])
+            raise RuntimeError("link failed")
+    with open(os.path.join(OBJ_DIR, "build.log"), "a") as f:
+        f.write("\n".join(log))
+    if verbose:
+        print("\n".join(log))
+    return LIB_PATH
+
+
+if __name__ == "__main__":
+    path = build(force="--force" in sys.argv, verbose="--verbose" in sys.argv or "-v" in sys.argv)
+    print(path)

@@ -1,0 +1,371 @@
+// Conv3d(k=3) + BatchNorm3d(eval) + ReLU as a bf16 implicit GEMM on tcgen05 / TMEM, TMA-fed.
+// Replaces ConvMD(3, ...).forward (reference voxelnet/model.py:158-167) for the three middle layers
+// instantiated at model.py:207-209, and (out_mode 1) the reshape at model.py:262.
+//
+// GEMM view: M = output positions, N = 64 output channels, K = 27 taps x Cin.
+//
+// Tiling (DESIGN.md "Conv3d"): one CTA owns a 16 (h) x 8 (w) spatial tile for ALL output depths of
+// one frame: Dout accumulators of 128 x 64 fp32 live side by side in TMEM (64 columns each).  The
+// K loop walks the INPUT planes in ascending order; an input plane p feeds output depth
+// d' = (p + pad_d - kd) / stride_d for every valid kd, so each A tile fetched from L2 is used for up
+// to three depth taps, and accumulators complete one after the other - the epilogue drains
+// accumulator d' while the tensor core is already working on d'+1 (and on the next tile).
+//
+//   A operand: per (plane, 64-channel chunk, kw) ONE TMA box of 64 ch x 8 w x 18 h (an h-halo'd
+//              tile, 128-byte rows, SWIZZLE_128B).  The three kh taps read it at +kh*1024 B: one
+//              image row of the tile is exactly one 8-row swizzle atom, so every tap start stays
+//              atom-aligned.  Out-of-range h / w / (skipped) d are the convolution's zero padding,
+//              supplied by TMA's out-of-bounds zero fill.
+//   B operand: weights pre-packed per (kd, chunk, kw) as three [64 n x 64 k] K-major tiles (kh = 0..2)
+//              already in the swizzled shared-memory image, fetched with one 24 KB bulk copy.
+//   Warp roles: warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer (one lane),
+//              warps 2..5 = epilogue (TMEM -> registers -> scale/shift/ReLU -> global).
+#include <cuda.h>
+#include <cuda_bf16.h>
+
+#include "vn_common.cuh"
+
+namespace vn {
+namespace {
+
+constexpr int kTileH = 16, kTileW = 8;             // 128 output positions per accumulator
+constexpr int kHaloH = kTileH + 2;
+constexpr uint32_t kABytes = kHaloH * kTileW * 128;  // 18432: 144 rows of 64 bf16
+constexpr uint32_t kBTapBytes = 64 * 128;            // 8192: [64 n][64 k] bf16
+constexpr uint32_t kBBytes = 3 * kBTapBytes;         // kh = 0..2
+constexpr int kNA = 4, kNB = 5;                      // ring depths
+constexpr int kMaxDout = 8;                          // 8 x 64 = 512 TMEM columns
+constexpr int kThreads = 6 * 32;
+constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBBytes;  // 196608
+constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + 1024 /*barriers, params*/;
+
+struct ConvParams {
+  int B, Din, Dout, H, W;
+  int nchunk;      // Cin / 64
+  int stride_d, pad_d;
+  int tiles_h, tiles_w, n_tiles;
+  int out_mode;    // 0: bf16 NDHWC, 1: f32 [B, 64*Dout, H, W] with channel = c*Dout + d
+  const uint8_t* wpack;
+  const float* scale;
+  const float* shift;
+  void* out;
+};
+
+struct Barriers {
+  uint64_t full_a[kNA], empty_a[kNA];
+  uint64_t full_b[kNB], empty_b[kNB];
+  uint64_t acc_full[kMaxDout], acc_empty[kMaxDout];
+  uint32_t tmem_base;
+  uint32_t pad;
+  float scale[64], shift[64];
+};
+static_assert(sizeof(Barriers) <= 1024, "barrier block too large");
+
+__device__ __forceinline__ bool tap_target(int p, int kd, const ConvParams& P, int& dout) {
+  const int num = p + P.pad_d - kd;
+  if (num < 0 || num % P.stride_d != 0) return false;
+  dout = num / P.stride_d;
+  return dout < P.Dout;
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+    k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const ConvParams P) {
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B operands need 1024-byte aligned tiles
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  uint8_t* smem_a = smem;
+  uint8_t* smem_b = smem + kNA * kABytes;
+  Barriers* bar = reinterpret_cast<Barriers*>(smem + kSmemData);
+
+  const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t tmem_cols = P.Dout * 64 <= 32 ? 32 : (P.Dout * 64 <= 64 ? 64 : (P.Dout * 64 <= 128 ? 128 : (P.Dout * 64 <= 256 ? 256 : 512)));
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < kNA; ++i) { mbar_init(&bar->full_a[i], 1); mbar_init(&bar->empty_a[i], 1); }
+    for (int i = 0; i < kNB; ++i) { mbar_init(&bar->full_b[i], 1); mbar_init(&bar->empty_b[i], 1); }
+    for (int i = 0; i < kMaxDout; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], 4); }
+    mbar_fence_init();
+    fence_proxy_async_smem();
+    tma_prefetch_desc(&tmap_x);
+  }
+  if (threadIdx.x >= 64 && threadIdx.x < 128) {
+    bar->scale[threadIdx.x - 64] = P.scale[threadIdx.x - 64];
+    bar->shift[threadIdx.x - 64] = P.shift[threadIdx.x - 64];
+  }
+  if (warp == 1) {
+    tmem_alloc(&bar->tmem_base, tmem_cols);
+    tmem_relinquish();
+  }
+  tc_fence_before_sync();
+  __syncthreads();
+  tc_fence_after_sync();
+  const uint32_t tmem_base = bar->tmem_base;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (lane == 0) {
+      uint32_t a_it = 0, b_it = 0;
+      for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+        const int tw = tile % P.tiles_w;
+        const int th = (tile / P.tiles_w) % P.tiles_h;
+        const int b = tile / (P.tiles_w * P.tiles_h);
+        const int h0 = th * kTileH, w0 = tw * kTileW;
+        for (int p = 0; p < P.Din; ++p) {
+          int dd;
+          const bool v0 = tap_target(p, 0, P, dd), v1 = tap_target(p, 1, P, dd), v2 = tap_target(p, 2, P, dd);
+          if (!(v0 | v1 | v2)) continue;
+          for (int c = 0; c < P.nchunk; ++c) {
+            for (int kw = 0; kw < 3; ++kw) {
+              const uint32_t sa = a_it % kNA;
+              mbar_wait(&bar->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+              mbar_arrive_expect_tx(&bar->full_a[sa], kABytes);
+              tma_load_5d(smem_a + sa * kABytes, &tmap_x, &bar->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
+              ++a_it;
+              for (int kd = 0; kd < 3; ++kd) {
+                if (!(kd == 0 ? v0 : (kd == 1 ? v1 : v2))) continue;
+                const uint32_t sb = b_it % kNB;
+                mbar_wait(&bar->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
+                mbar_arrive_expect_tx(&bar->full_b[sb], kBBytes);
+                const uint8_t* src = P.wpack + (size_t)(((kd * P.nchunk + c) * 3 + kw) * 3) * kBTapBytes;
+                bulk_load_1d(smem_b + sb * kBBytes, src, kBBytes, &bar->full_b[sb]);
+                ++b_it;
+              }
+            }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
+      uint32_t a_it = 0, b_it = 0, tile_it = 0;
+      for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tile_it) {
+        uint32_t started = 0;
+        for (int p = 0; p < P.Din; ++p) {
+          int d0, d1, d2;
+          const bool v0 = tap_target(p, 0, P, d0), v1 = tap_target(p, 1, P, d1), v2 = tap_target(p, 2, P, d2);
+          if (!(v0 | v1 | v2)) continue;
+          for (int c = 0; c < P.nchunk; ++c) {
+            for (int kw = 0; kw < 3; ++kw) {
+              const uint32_t sa = a_it % kNA;
+              mbar_wait(&bar->full_a[sa], (a_it / kNA) & 1);
+              tc_fence_after_sync();
+              const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
+              for (int kd = 0; kd < 3; ++kd) {
+                if (!(kd == 0 ? v0 : (kd == 1 ? v1 : v2))) continue;
+                const int dout = kd == 0 ? d0 : (kd == 1 ? d1 : d2);
+                if (!((started >> dout) & 1)) {
+                  // first touch of this accumulator in this tile: the epilogue must have drained it
+                  mbar_wait(&bar->acc_empty[dout], (tile_it & 1) ^ 1);
+                  tc_fence_after_sync();
+                }
+                const uint32_t sb = b_it % kNB;
+                mbar_wait(&bar->full_b[sb], (b_it / kNB) & 1);
+                tc_fence_after_sync();
+                const uint32_t b_addr = smem_u32(smem_b + sb * kBBytes);
+                const uint32_t d_tmem = tmem_base + (uint32_t)dout * 64;
+#pragma unroll
+                for (int kh = 0; kh < 3; ++kh) {
+#pragma unroll
+                  for (int k4 = 0; k4 < 4; ++k4) {
+                    const uint64_t da = umma_desc_sw128(a_addr + kh * (kTileW * 128) + k4 * 32, 1024);
+                    const uint64_t db = umma_desc_sw128(b_addr + kh * kBTapBytes + k4 * 32, 1024);
+                    const uint32_t acc = (((started >> dout) & 1) | (uint32_t)(kh | k4)) != 0;
+                    umma_bf16_ss(d_tmem, da, db, idesc, acc);
+                  }
+                }
+                started |= 1u << dout;
+                umma_commit(&bar->empty_b[sb]);
+                ++b_it;
+                // last contribution to this accumulator?
+                int plast = dout * P.stride_d - P.pad_d + 2;
+                if (plast > P.Din - 1) plast = P.Din - 1;
+                if (p == plast && c == P.nchunk - 1 && kw == 2) umma_commit(&bar->acc_full[dout]);
+              }
+              umma_commit(&bar->empty_a[sa]);
+              ++a_it;
+            }
+          }
+        }
+      }
+    }
+  } else {
+    // ===================== epilogue (warps 2..5) =====================
+    const uint32_t quad = warp & 3;                // TMEM lane quadrant this warp may read
+    const uint32_t m = quad * 32 + lane;           // accumulator row = output position in the tile
+    const int hl = m / kTileW, wl = m % kTileW;
+    uint32_t tile_it = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tile_it) {
+      const int tw = tile % P.tiles_w;
+      const int th = (tile / P.tiles_w) % P.tiles_h;
+      const int b = tile / (P.tiles_w * P.tiles_h);
+      const int h = th * kTileH + hl, w = tw * kTileW + wl;
+      const bool inside = h < P.H && w < P.W;
+      for (int dout = 0; dout < P.Dout; ++dout) {
+        mbar_wait(&bar->acc_full[dout], tile_it & 1);
+        tc_fence_after_sync();
+        const uint32_t taddr = tmem_base + ((quad * 32) << 16) + (uint32_t)dout * 64;
+#pragma unroll
+        for (int half = 0; half < 2; ++half) {
+          uint32_t r[32];
+          tmem_ld_32x32b_x32(taddr + half * 32, r);
+          tmem_ld_wait();
+          if (half == 1) {
+            // accumulator fully read: hand it back to the MMA issuer before the global stores
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&bar->acc_empty[dout]);
+          }
+          if (inside) {
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              const int c = half * 32 + j;
+              v[j] = fmaxf(fmaf(__uint_as_float(r[j]), bar->scale[c], bar->shift[c]), 0.0f);
+            }
+            if (P.out_mode == 0) {
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
+                                   ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32;
+#pragma unroll
+              for (int q = 0; q < 4; ++q) {
+                uint32_t pk[4];
+#pragma unroll
+                for (int e = 0; e < 4; ++e) {
+                  const __nv_bfloat162 t2 = __floats2bfloat162_rn(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1]);
+                  pk[e] = *reinterpret_cast<const uint32_t*>(&t2);
+                }
+                *reinterpret_cast<uint4*>(dst + q * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+              }
+            } else {
+              const size_t plane = (size_t)P.H * P.W;
+              float* dst = reinterpret_cast<float*>(P.out) +
+                           ((size_t)b * 64 * P.Dout + (size_t)(half * 32) * P.Dout + dout) * plane + (size_t)h * P.W + w;
+#pragma unroll
+              for (int j = 0; j < 32; ++j) dst[(size_t)j * P.Dout * plane] = v[j];
+            }
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem_base, tmem_cols);
+  }
+}
+
+// torch [64][cin][3][3][3] fp32 -> bf16 tiles [kd][chunk][kw][kh][n=64][k=64], 128B-swizzled rows.
+__global__ void __launch_bounds__(256) k_pack_weights(const float* __restrict__ w, int cin, uint8_t* __restrict__ packed) {
+  const int nchunk = cin / 64;
+  const int total = 27 * cin * 64;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    int r = i;
+    const int k = r % 64; r /= 64;
+    const int n = r % 64; r /= 64;
+    const int kh = r % 3; r /= 3;
+    const int kw = r % 3; r /= 3;
+    const int c = r % nchunk; r /= nchunk;
+    const int kd = r;
+    const float v = w[((((size_t)n * cin + (c * 64 + k)) * 3 + kd) * 3 + kh) * 3 + kw];
+    const size_t tile = (size_t)(((kd * nchunk + c) * 3 + kw) * 3 + kh) * kBTapBytes;
+    const size_t off = tile + (size_t)n * 128 + ((((k >> 3) ^ (n & 7)) << 4) | ((k & 7) << 1));
+    *reinterpret_cast<__nv_bfloat16*>(packed + off) = __float2bfloat16_rn(v);
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+}  // namespace
+}  // namespace vn
+
+using namespace vn;
+
+extern "C" {
+
+size_t vn_conv3d_packed_weight_bytes(int32_t cin) {
+  if (cin != 64 && cin != 128) return 0;
+  return (size_t)27 * cin * 64 * 2;
+}
+
+int vn_conv3d_pack_weights(const float* weight, int32_t cin, void* packed, vn_stream_t stream) {
+  VN_REQUIRE(cin == 64 || cin == 128, "conv3d_pack_weights: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(weight != nullptr && packed != nullptr, "conv3d_pack_weights: null pointer");
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0, "conv3d_pack_weights: packed must be 16-byte aligned");
+  k_pack_weights<<<sm_count() * 4, 256, 0, as_stream(stream)>>>(weight, cin, reinterpret_cast<uint8_t*>(packed));
+  VN_LAUNCH_CHECK("k_pack_weights");
+  return VN_OK;
+}
+
+int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
+                          int32_t pad_d, const void* packed_weight, const float* scale, const float* shift,
+                          int32_t out_mode, void* y, vn_stream_t stream) {
+  VN_REQUIRE(x && packed_weight && scale && shift && y, "conv3d: null pointer");
+  VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
+  VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d: stride_d=%d pad_d=%d unsupported",
+             stride_d, pad_d);
+  VN_REQUIRE(out_mode == 0 || out_mode == 1, "conv3d: out_mode=%d", out_mode);
+  VN_REQUIRE(W % kTileW == 0, "conv3d: W=%d must be a multiple of %d", W, kTileW);
+  const int Dout = (Din + 2 * pad_d - 3) / stride_d + 1;
+  VN_REQUIRE(Din + 2 * pad_d >= 3 && Dout >= 1 && Dout <= kMaxDout, "conv3d: Dout=%d outside [1,%d]", Dout, kMaxDout);
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(packed_weight) & 15) == 0 &&
+                 (reinterpret_cast<uintptr_t>(y) & 15) == 0,
+             "conv3d: buffers must be 16-byte aligned");
+
+  EncodeTiledFn encode = encode_tiled_fn();
+  if (encode == nullptr) {
+    set_error("conv3d: cuTensorMapEncodeTiled not available from the driver");
+    return VN_ERR_DRIVER;
+  }
+  CUtensorMap tmap;
+  const cuuint64_t gdim[5] = {(cuuint64_t)cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Din, (cuuint64_t)B};
+  const cuuint64_t gstr[4] = {(cuuint64_t)cin * 2, (cuuint64_t)W * cin * 2, (cuuint64_t)H * W * cin * 2,
+                              (cuuint64_t)Din * H * W * cin * 2};
+  const cuuint32_t box[5] = {64, (cuuint32_t)kTileW, (cuuint32_t)kHaloH, 1, 1};
+  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(x), gdim, gstr, box, estr,
+                             CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                             CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (cr != CUDA_SUCCESS) {
+    set_error("conv3d: cuTensorMapEncodeTiled failed with CUresult %d", (int)cr);
+    return VN_ERR_DRIVER;
+  }
+
+  ConvParams P{};
+  P.B = B; P.Din = Din; P.Dout = Dout; P.H = H; P.W = W;
+  P.nchunk = cin / 64;
+  P.stride_d = stride_d; P.pad_d = pad_d;
+  P.tiles_h = (H + kTileH - 1) / kTileH;
+  P.tiles_w = W / kTileW;
+  P.n_tiles = B * P.tiles_h * P.tiles_w;
+  P.out_mode = out_mode;
+  P.wpack = reinterpret_cast<const uint8_t*>(packed_weight);
+  P.scale = scale; P.shift = shift;
+  P.out = y;
+
+  VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+  const int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
+  k_conv3d_bn_relu<<<grid, kThreads, kSmemBytes, as_stream(stream)>>>(tmap, P);
+  VN_LAUNCH_CHECK("k_conv3d_bn_relu");
+  return VN_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,310 @@
+// Stacked voxel feature encoder kernels: the replacement for VFELayer.forward (reference
+// voxelnet/model.py:74-82) and for the VFE part of FeatureLearningNet.forward (model.py:95-100).
+//
+// Semantics restated from the reference:
+//   pointwise = BN1d(ReLU(Linear(x)))           Linear -> ReLU -> BN, eval-mode BN folded into
+//                                               y = relu(Wx + b) * s + t
+//   agg       = max over ALL T rows of pointwise (pad rows included, no mask)
+//   out       = concat(pointwise, agg) * mask    mask[k,t] = (max_j feature[k,t,j] != 0)
+//   voxelwise = max over t of the masked VFE-2 output
+//
+// k_svfe_fused keeps one voxel per warp entirely on chip: the [T,7] block is staged in shared
+// memory, VFE-1 is evaluated with one row per lane, VFE-2 with two output units per lane and its
+// 64x32 weights held in registers, and only the 128 voxel-wise maxima are written.  Rows at the
+// tail of a voxel that are bit-identical to its last row (the reference's pad rows are all
+// [0,0,0,0,-cx,-cy,-cz]) are evaluated once: max() ignores multiplicity, so this is exact.
+#include "vn_common.cuh"
+
+namespace vn {
+namespace {
+
+constexpr int kMaxT = 64;
+constexpr int kWarps = 8;
+
+struct Vfe1Params {  // small enough to travel as a kernel argument (constant bank, uniform reads)
+  float w[16][7];
+  float b[16], s[16], t[16];
+};
+
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, d));
+  return v;
+}
+
+__global__ void __launch_bounds__(kWarps * 32)
+    k_svfe_fused(const float* __restrict__ feature, int64_t K, int T, const int32_t* __restrict__ n_voxels_dev,
+                 const float* __restrict__ w1, const float* __restrict__ b1, const float* __restrict__ s1,
+                 const float* __restrict__ t1, const float* __restrict__ w2, const float* __restrict__ b2,
+                 const float* __restrict__ s2, const float* __restrict__ t2, float* __restrict__ voxelwise) {
+  // dynamic shared memory: [kWarps][T+1][32] x1 rows (row T = agg1) | [kWarps][in_ld] staged inputs
+  extern __shared__ __align__(16) float dyn_smem[];
+  __shared__ Vfe1Params p1;
+  const int in_ld = (T * 7 + 3) & ~3;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < 16 * 7; i += blockDim.x) p1.w[i / 7][i % 7] = w1[i];
+  if (threadIdx.x < 16) {
+    p1.b[threadIdx.x] = b1[threadIdx.x];
+    p1.s[threadIdx.x] = s1[threadIdx.x];
+    p1.t[threadIdx.x] = t1[threadIdx.x];
+  }
+
+  // VFE-2 weights for this lane's two units (lane, lane + 32): 64 registers.
+  float wa[32], wb[32];
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    wa[k] = w2[lane * 32 + k];
+    wb[k] = w2[(lane + 32) * 32 + k];
+  }
+  const float ba = b2[lane], bb = b2[lane + 32];
+  const float sa = s2[lane], sb = s2[lane + 32];
+  const float ta = t2[lane], tb = t2[lane + 32];
+  __syncthreads();
+
+  int64_t total = K;
+  if (n_voxels_dev != nullptr) {
+    const int64_t live = *n_voxels_dev;
+    if (live < total) total = live;
+  }
+  float(*x1)[32] = reinterpret_cast<float(*)[32]>(dyn_smem + (size_t)warp * (T + 1) * 32);
+  float* in = dyn_smem + (size_t)kWarps * (T + 1) * 32 + (size_t)warp * in_ld;
+  const int64_t nwarps = (int64_t)gridDim.x * kWarps;
+  for (int64_t v = (int64_t)blockIdx.x * kWarps + warp; v < total; v += nwarps) {
+    const float* src = feature + v * (int64_t)(T * 7);
+    for (int e = lane; e < T * 7; e += 32) in[e] = src[e];
+    __syncwarp();
+
+    // Unique-row analysis: rows [nu, T) are bit-identical to row T-1.
+    int nu = 0;  // 1 + index of the last row that differs from row T-1
+    for (int t0 = 0; t0 < T; t0 += 32) {
+      const int t = t0 + lane;
+      bool differs = false;
+      if (t < T) {
+#pragma unroll
+        for (int j = 0; j < 7; ++j)
+          differs |= __float_as_uint(in[t * 7 + j]) != __float_as_uint(in[(T - 1) * 7 + j]);
+      }
+      const uint32_t b = __ballot_sync(0xffffffffu, differs);
+      if (b) nu = t0 + 32 - __clz(b);
+    }
+    const int R = nu < T ? nu + 1 : T;  // rows to evaluate: 0..nu-1 and (if any) the tail row T-1
+
+    // ---- VFE-1: lane <-> row.  x1[r][0:16] = pointwise, mask kept in a register bit set ----
+    uint64_t on_bits = 0;  // bit r set <=> evaluated row r has mask == 1
+    for (int r0 = 0; r0 < R; r0 += 32) {
+      const int r = r0 + lane;
+      bool on = false;
+      if (r < R) {
+        const int t = r < nu ? r : T - 1;
+        float f[7];
+#pragma unroll
+        for (int j = 0; j < 7; ++j) f[j] = in[t * 7 + j];
+        float mx = f[0];
+#pragma unroll
+        for (int j = 1; j < 7; ++j) mx = fmaxf(mx, f[j]);
+        on = mx != 0.0f;
+#pragma unroll
+        for (int u = 0; u < 16; ++u) {
+          float a = p1.b[u];
+#pragma unroll
+          for (int j = 0; j < 7; ++j) a = fmaf(p1.w[u][j], f[j], a);
+          x1[r][u] = fmaxf(a, 0.0f) * p1.s[u] + p1.t[u];
+        }
+      }
+      const uint32_t b = __ballot_sync(0xffffffffu, on);
+      on_bits |= (uint64_t)b << r0;
+    }
+    __syncwarp();
+    // agg1[u] = max over evaluated rows (== max over all T rows); lanes 0..15 own unit u.
+    if (lane < 16) {
+      float a = x1[0][lane];
+      for (int r = 1; r < R; ++r) a = fmaxf(a, x1[r][lane]);
+      x1[T][lane] = a;
+    }
+    __syncwarp();
+    // concat + mask: rows with mask 0 become all-zero inputs of VFE-2
+    for (int e = lane; e < R * 32; e += 32) {
+      const int r = e >> 5, c = e & 31;
+      const bool on = (on_bits >> r) & 1;
+      const float val = c < 16 ? x1[r][c] : x1[T][c - 16];
+      x1[r][c] = on ? val : 0.0f;
+    }
+    __syncwarp();
+
+    // ---- VFE-2: lane <-> units (lane, lane+32); rows broadcast from shared memory ----
+    float all_a = -INFINITY, all_b = -INFINITY;  // max over all rows (the reference's `agg`)
+    float on_a = -INFINITY, on_b = -INFINITY;    // max over rows with mask 1 of the pointwise part
+    for (int r = 0; r < R; ++r) {
+      float a = ba, b = bb;
+      const float4* xr = reinterpret_cast<const float4*>(x1[r]);
+#pragma unroll
+      for (int q = 0; q < 8; ++q) {
+        const float4 x = xr[q];
+        a = fmaf(wa[4 * q + 0], x.x, a);
+        b = fmaf(wb[4 * q + 0], x.x, b);
+        a = fmaf(wa[4 * q + 1], x.y, a);
+        b = fmaf(wb[4 * q + 1], x.y, b);
+        a = fmaf(wa[4 * q + 2], x.z, a);
+        b = fmaf(wb[4 * q + 2], x.z, b);
+        a = fmaf(wa[4 * q + 3], x.w, a);
+        b = fmaf(wb[4 * q + 3], x.w, b);
+      }
+      a = fmaxf(a, 0.0f) * sa + ta;
+      b = fmaxf(b, 0.0f) * sb + tb;
+      all_a = fmaxf(all_a, a);
+      all_b = fmaxf(all_b, b);
+      if ((on_bits >> r) & 1) {
+        on_a = fmaxf(on_a, a);
+        on_b = fmaxf(on_b, b);
+      }
+    }
+    // voxelwise[c] = max_t(mask_t * out2[t][c]): rows with mask 0 contribute exactly 0.
+    const uint64_t evaluated = R >= 64 ? ~0ull : ((1ull << R) - 1ull);
+    const bool any_on = on_bits != 0;
+    const bool any_off = (on_bits & evaluated) != evaluated;
+    const float floor0 = any_off ? 0.0f : -INFINITY;
+    float* dst = voxelwise + v * 128;
+    dst[lane] = fmaxf(any_on ? on_a : -INFINITY, floor0);
+    dst[lane + 32] = fmaxf(any_on ? on_b : -INFINITY, floor0);
+    dst[lane + 64] = fmaxf(any_on ? all_a : -INFINITY, floor0);
+    dst[lane + 96] = fmaxf(any_on ? all_b : -INFINITY, floor0);
+    __syncwarp();
+  }
+}
+
+// Drop-in single layer: inputs [K,T,CIN], mask [K,T] -> out [K,T,2*UNITS].  One warp per voxel;
+// the voxel's rows and the layer's weights sit in shared memory (row stride CIN+1 to spread banks).
+template <int CIN, int UNITS>
+__global__ void __launch_bounds__(kWarps * 32)
+    k_vfe_layer(const float* __restrict__ inputs, const uint8_t* __restrict__ mask, int64_t K, int T,
+                const float* __restrict__ weight, const float* __restrict__ bias,
+                const float* __restrict__ bn_scale, const float* __restrict__ bn_shift, float* __restrict__ out) {
+  constexpr int LD = CIN + 1;
+  extern __shared__ float smem[];
+  float* s_w = smem;                        // [UNITS][LD]
+  float* s_b = s_w + UNITS * LD;            // [UNITS]
+  float* s_s = s_b + UNITS;                 // [UNITS]
+  float* s_t = s_s + UNITS;                 // [UNITS]
+  float* s_rows = s_t + UNITS;              // [kWarps][kMaxT][LD]
+  float* s_agg = s_rows + kWarps * kMaxT * LD;  // [kWarps][UNITS]
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < UNITS * CIN; i += blockDim.x) s_w[(i / CIN) * LD + i % CIN] = weight[i];
+  for (int i = threadIdx.x; i < UNITS; i += blockDim.x) {
+    s_b[i] = bias[i];
+    s_s[i] = bn_scale[i];
+    s_t[i] = bn_shift[i];
+  }
+  __syncthreads();
+  float* rows = s_rows + warp * kMaxT * LD;
+  float* agg = s_agg + warp * UNITS;
+  const int64_t nwarps = (int64_t)gridDim.x * kWarps;
+  for (int64_t v = (int64_t)blockIdx.x * kWarps + warp; v < K; v += nwarps) {
+    const float* src = inputs + v * (int64_t)T * CIN;
+    for (int e = lane; e < T * CIN; e += 32) rows[(e / CIN) * LD + e % CIN] = src[e];
+    __syncwarp();
+    float* dst = out + v * (int64_t)T * (2 * UNITS);
+    const uint8_t* mk = mask + v * (int64_t)T;
+    // pointwise part, kept unmasked in registers' place: written masked, max taken unmasked
+    for (int u0 = 0; u0 < UNITS; u0 += 32) {
+      const int u = u0 + (lane % (UNITS < 32 ? UNITS : 32));
+      // with UNITS == 16 the two half-warps split the rows
+      const int tstep = UNITS < 32 ? 32 / UNITS : 1;
+      const int tfirst = UNITS < 32 ? lane / UNITS : 0;
+      float mx = -INFINITY;
+      for (int t = tfirst; t < T; t += tstep) {
+        float a = s_b[u];
+#pragma unroll
+        for (int k = 0; k < CIN; ++k) a = fmaf(s_w[u * LD + k], rows[t * LD + k], a);
+        a = fmaxf(a, 0.0f) * s_s[u] + s_t[u];
+        mx = fmaxf(mx, a);
+        dst[(int64_t)t * (2 * UNITS) + u] = mk[t] ? a : 0.0f;
+      }
+      if (UNITS < 32) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, 16));
+      if (UNITS >= 32 || lane < UNITS) agg[u] = mx;
+    }
+    __syncwarp();
+    for (int e = lane; e < T * UNITS; e += 32) {
+      const int t = e / UNITS, u = e % UNITS;
+      dst[(int64_t)t * (2 * UNITS) + UNITS + u] = mk[t] ? agg[u] : 0.0f;
+    }
+    __syncwarp();
+  }
+}
+
+__global__ void __launch_bounds__(256)
+    k_feature_mask(const float* __restrict__ feature, int64_t rows, int cin, uint8_t* __restrict__ mask) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; r < rows; r += stride) {
+    const float* f = feature + r * cin;
+    float mx = f[0];
+    for (int j = 1; j < cin; ++j) mx = fmaxf(mx, f[j]);
+    mask[r] = mx != 0.0f ? 1 : 0;
+  }
+}
+
+template <int CIN, int UNITS>
+int launch_vfe_layer(const float* inputs, const uint8_t* mask, int64_t K, int T, const float* weight,
+                     const float* bias, const float* bn_scale, const float* bn_shift, float* out, cudaStream_t st) {
+  constexpr int LD = CIN + 1;
+  const size_t smem = sizeof(float) * (UNITS * LD + 3 * UNITS + kWarps * kMaxT * LD + kWarps * UNITS);
+  VN_CUDA(cudaFuncSetAttribute(k_vfe_layer<CIN, UNITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t want = (K + kWarps - 1) / kWarps;
+  const int64_t cap = (int64_t)sm_count() * 4;
+  k_vfe_layer<CIN, UNITS><<<(unsigned)(want < cap ? want : cap), kWarps * 32, smem, st>>>(
+      inputs, mask, K, T, weight, bias, bn_scale, bn_shift, out);
+  VN_LAUNCH_CHECK("k_vfe_layer");
+  return VN_OK;
+}
+
+}  // namespace
+}  // namespace vn
+
+using namespace vn;
+
+extern "C" {
+
+int vn_vfe_layer_fwd(const float* inputs, const uint8_t* mask, int64_t K, int32_t T, int32_t cin, int32_t units,
+                     const float* weight, const float* bias, const float* bn_scale, const float* bn_shift,
+                     float* out, vn_stream_t stream) {
+  VN_REQUIRE(K >= 0, "vfe_layer: K < 0");
+  VN_REQUIRE(T >= 1 && T <= kMaxT, "vfe_layer: T=%d outside [1,%d]", T, kMaxT);
+  if (K == 0) return VN_OK;
+  VN_REQUIRE(inputs && mask && weight && bias && bn_scale && bn_shift && out, "vfe_layer: null pointer");
+  cudaStream_t st = as_stream(stream);
+  if (cin == 7 && units == 16) return launch_vfe_layer<7, 16>(inputs, mask, K, T, weight, bias, bn_scale, bn_shift, out, st);
+  if (cin == 32 && units == 64) return launch_vfe_layer<32, 64>(inputs, mask, K, T, weight, bias, bn_scale, bn_shift, out, st);
+  set_error("vfe_layer: unsupported (cin=%d, units=%d); the reference instantiates (7,16) and (32,64)", cin, units);
+  return VN_ERR_UNSUPPORTED;
+}
+
+int vn_feature_mask(const float* feature, int64_t K, int32_t T, int32_t cin, uint8_t* mask, vn_stream_t stream) {
+  VN_REQUIRE(K >= 0 && T >= 1 && cin >= 1, "feature_mask: bad shape");
+  if (K == 0) return VN_OK;
+  VN_REQUIRE(feature && mask, "feature_mask: null pointer");
+  const int64_t rows = K * T;
+  const int64_t want = (rows + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  k_feature_mask<<<(unsigned)(want < cap ? want : cap), 256, 0, as_stream(stream)>>>(feature, rows, cin, mask);
+  VN_LAUNCH_CHECK("k_feature_mask");
+  return VN_OK;
+}
+
+int vn_svfe_fused_fwd(const float* feature, int64_t K, int32_t T, const int32_t* n_voxels_dev, const float* w1,
+                      const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
+                      const float* s2, const float* t2, float* voxelwise, vn_stream_t stream) {
+  VN_REQUIRE(K >= 0, "svfe_fused: K < 0");
+  VN_REQUIRE(T >= 1 && T <= kMaxT, "svfe_fused: T=%d outside [1,%d]", T, kMaxT);
+  if (K == 0) return VN_OK;
+  VN_REQUIRE(feature && w1 && b1 && s1 && t1 && w2 && b2 && s2 && t2 && voxelwise, "svfe_fused: null pointer");
+  cudaStream_t st = as_stream(stream);
+  const size_t smem = sizeof(float) * ((size_t)kWarps * (T + 1) * 32 + (size_t)kWarps * ((T * 7 + 3) & ~3));
+  VN_CUDA(cudaFuncSetAttribute(k_svfe_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t want = (K + kWarps - 1) / kWarps;
+  const int64_t cap = (int64_t)sm_count() * 2;
+  k_svfe_fused<<<(unsigned)(want < cap ? want : cap), kWarps * 32, smem, st>>>(feature, K, T, n_voxels_dev, w1, b1, s1,
+                                                                              t1, w2, b2, s2, t2, voxelwise);
+  VN_LAUNCH_CHECK("k_svfe_fused");
+  return VN_OK;
+}
+
+}  // extern "C"

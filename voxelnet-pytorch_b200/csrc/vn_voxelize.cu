@@ -1,0 +1,481 @@
+// Batched GPU voxelizer: the replacement for pcl_to_voxels (reference voxelnet/utils.py:10-100)
+// plus the batch column of prepare_voxel (voxelnet/dataset.py:101-119).
+//
+// Design (see DESIGN.md "Voxelizer"): the grid is small and dense (1.4 M cells for Car), so the
+// sorted-unique step (np.unique(axis=0), utils.py:63) is done WITHOUT a sort: an occupancy bitmap per
+// frame (176 KB, L2 resident) plus a prefix sum of its popcounts gives every occupied cell its
+// rank in ascending (z, y, x) order - exactly np.unique's lexicographic order.  The first-T-points
+// rule (utils.py:78-84) needs a deterministic order that plain atomics cannot give, so points
+// are first bucketed per voxel in arrival order (warp-aggregated atomics) and each voxel's short
+// list is then ordered by original point index when its feature rows are written.
+//
+//   P0 zero            bitmap + per-voxel counters
+//   P1 mark            float4 point load, IEEE add/div/floor, range crop, cell key, bitmap bit
+//   P2 scan words      per frame: exclusive prefix of popcounts  -> K per frame
+//   P3 frame offsets   exclusive prefix of K over frames         -> voxel_offsets
+//   P4 count           key -> voxel row; arrival slot via warp-aggregated atomicAdd
+//   P5 segment scan    per frame: exclusive prefix of counts     -> CSR segment starts
+//   P6 place           point index -> its voxel's segment
+//   P7 features        per voxel (one warp): T smallest indices ascending, gather, fp32 sequential
+//                      sum, fp64 centroid, write [T,7] row block, coords, count
+#include "vn_common.cuh"
+
+namespace vn {
+namespace {
+
+constexpr uint32_t kInvalidKey = 0xFFFFFFFFu;
+constexpr int kMaxT = 64;  // smem staging rows per warp (T is 35 or 45)
+
+struct VoxWorkspace {
+  uint32_t* bitmap;      // [n_frames * words]   occupancy bits, cell = (z*H + y)*W + x
+  uint32_t* wordprefix;  // [n_frames * words]   exclusive popcount prefix within the frame
+  int32_t* frame_k;      // [n_frames]           voxels per frame
+  int32_t* cnt;          // [n_points]           points per voxel row (uncapped)
+  int32_t* keyrow;       // [n_points]           P1: cell key; P4 onwards: voxel row (-1 = cropped)
+  int32_t* arrival;      // [n_points]           arrival slot inside the voxel
+  int32_t* seg;          // [n_points]           segment start of each voxel row in pidx
+  int32_t* pidx;         // [n_points]           point indices bucketed per voxel
+  size_t words;          // bitmap words per frame
+  size_t zero_bytes;     // bitmap..cnt are contiguous: one fill
+  size_t total_bytes;
+};
+
+__host__ VoxWorkspace carve(const vn_grid_t& g, int n_frames, int64_t n_points, void* base) {
+  VoxWorkspace w{};
+  const size_t cells = (size_t)g.D * g.H * g.W;
+  w.words = align_up((cells + 31) / 32, 32);
+  const size_t np = align_up((size_t)(n_points > 0 ? n_points : 1), 64);
+  char* p = static_cast<char*>(base);
+  size_t off = 0;
+  auto take = [&](size_t bytes) {
+    char* r = p ? p + off : nullptr;
+    off += align_up(bytes, 256);
+    return r;
+  };
+  w.bitmap = reinterpret_cast<uint32_t*>(take((size_t)n_frames * w.words * 4));
+  w.cnt = reinterpret_cast<int32_t*>(take(np * 4));
+  w.zero_bytes = off;
+  w.wordprefix = reinterpret_cast<uint32_t*>(take((size_t)n_frames * w.words * 4));
+  w.frame_k = reinterpret_cast<int32_t*>(take((size_t)n_frames * 4));
+  w.keyrow = reinterpret_cast<int32_t*>(take(np * 4));
+  w.arrival = reinterpret_cast<int32_t*>(take(np * 4));
+  w.seg = reinterpret_cast<int32_t*>(take(np * 4));
+  w.pidx = reinterpret_cast<int32_t*>(take(np * 4));
+  w.total_bytes = off;
+  return w;
+}
+
+// utils.py:37-57.  shifted = p + lidar_coord (fp32), idx = floor(shifted / voxel_size) with a true
+// IEEE fp32 division (a reciprocal multiply moves ~1e-3 of the points to a neighbouring cell,
+// SURVEY F2).  The bounds test is done on the floored float, which equals the reference's test on
+// the int64 cast for every finite value and rejects NaN/inf like the cast's INT64_MIN does.
+__device__ __forceinline__ bool point_cell(const float4& p, const vn_grid_t& g, int& z, int& y, int& x) {
+  const float fx = floorf(__fdiv_rn(__fadd_rn(p.x, g.off_x), g.vs_x));
+  const float fy = floorf(__fdiv_rn(__fadd_rn(p.y, g.off_y), g.vs_y));
+  const float fz = floorf(__fdiv_rn(__fadd_rn(p.z, g.off_z), g.vs_z));
+  const bool ok = (fx >= 0.0f) & (fx < (float)g.W) & (fy >= 0.0f) & (fy < (float)g.H) & (fz >= 0.0f) &
+                  (fz < (float)g.D);
+  x = (int)fx;
+  y = (int)fy;
+  z = (int)fz;
+  return ok;
+}
+
+__global__ void k_fill_zero16(uint4* __restrict__ p, size_t n16) {
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n16; i += stride)
+    p[i] = make_uint4(0, 0, 0, 0);
+}
+
+// P1: one thread per point; blockIdx.y = frame.
+__global__ void __launch_bounds__(256) k_vox_mark(const vn_grid_t g, const float4* __restrict__ points,
+                                                   const int32_t* __restrict__ frame_offsets,
+                                                   uint32_t* __restrict__ bitmap, size_t words,
+                                                   int32_t* __restrict__ keyrow) {
+  const int f = blockIdx.y;
+  const int beg = frame_offsets[f], end = frame_offsets[f + 1];
+  uint32_t* bm = bitmap + (size_t)f * words;
+  for (int i = beg + blockIdx.x * blockDim.x + threadIdx.x; i < end; i += gridDim.x * blockDim.x) {
+    const float4 p = ld_stream_f4(points + i);
+    int z, y, x;
+    uint32_t key = kInvalidKey;
+    if (point_cell(p, g, z, y, x)) {
+      key = (uint32_t)((z * g.H + y) * g.W + x);
+      const uint32_t bit = 1u << (key & 31);
+      uint32_t* wptr = bm + (key >> 5);
+      // most points land in a voxel whose bit is already set: test before paying for the atomic
+      if ((*reinterpret_cast<volatile uint32_t*>(wptr) & bit) == 0) atomicOr(wptr, bit);
+    }
+    keyrow[i] = (int32_t)key;
+  }
+}
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const uint32_t n = __shfl_up_sync(0xffffffffu, v, d);
+    if (lane >= (uint32_t)d) v += n;
+  }
+  return v;
+}
+
+// P2: one 1024-thread block per frame.  Each warp owns a contiguous, 32-word-aligned range.
+__global__ void __launch_bounds__(1024) k_vox_scan_words(const uint32_t* __restrict__ bitmap,
+                                                          uint32_t* __restrict__ wordprefix, size_t words,
+                                                          int32_t* __restrict__ frame_k) {
+  __shared__ uint32_t warp_total[32];
+  const int f = blockIdx.x;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const uint32_t* bm = bitmap + (size_t)f * words;
+  uint32_t* wp = wordprefix + (size_t)f * words;
+  const size_t per_warp = align_up((words + 31) / 32, 32);
+  const size_t w0 = (size_t)warp * per_warp;
+  const size_t w1 = w0 + per_warp < words ? w0 + per_warp : words;
+
+  uint32_t sum = 0;
+  for (size_t w = w0 + lane; w < w1; w += 32) sum += __popc(bm[w]);
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  if (lane == 0) warp_total[warp] = sum;
+  __syncthreads();
+  if (warp == 0) {
+    const uint32_t t = warp_total[lane];
+    const uint32_t incl = warp_incl_scan(t, lane);
+    warp_total[lane] = incl - t;
+    if (lane == 31) frame_k[f] = (int32_t)incl;
+  }
+  __syncthreads();
+  uint32_t run = warp_total[warp];
+  for (size_t w = w0; w < w1; w += 32) {  // w1 - w0 is a multiple of 32 except possibly at the very end
+    const size_t i = w + lane;
+    const uint32_t c = i < w1 ? __popc(bm[i]) : 0;
+    const uint32_t incl = warp_incl_scan(c, lane);
+    if (i < w1) wp[i] = run + incl - c;
+    run += __shfl_sync(0xffffffffu, incl, 31);
+  }
+}
+
+// P3: exclusive prefix over frames (one warp).
+__global__ void k_vox_frame_offsets(const int32_t* __restrict__ frame_k, int n_frames,
+                                    int32_t* __restrict__ voxel_offsets) {
+  const uint32_t lane = threadIdx.x;
+  uint32_t run = 0;
+  for (int f0 = 0; f0 < n_frames; f0 += 32) {
+    const int f = f0 + lane;
+    const uint32_t k = f < n_frames ? (uint32_t)frame_k[f] : 0;
+    const uint32_t incl = warp_incl_scan(k, lane);
+    if (f < n_frames) voxel_offsets[f] = (int32_t)(run + incl - k);
+    run += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  if (lane == 0) voxel_offsets[n_frames] = (int32_t)run;
+}
+
+// P4: key -> voxel row, arrival slot.  Lanes of a warp that hit the same voxel share one atomic.
+__global__ void __launch_bounds__(256) k_vox_count(const int32_t* __restrict__ frame_offsets,
+                                                    const uint32_t* __restrict__ bitmap,
+                                                    const uint32_t* __restrict__ wordprefix, size_t words,
+                                                    const int32_t* __restrict__ voxel_offsets,
+                                                    int32_t* __restrict__ keyrow, int32_t* __restrict__ arrival,
+                                                    int32_t* __restrict__ cnt) {
+  const int f = blockIdx.y;
+  const int beg = frame_offsets[f], end = frame_offsets[f + 1];
+  const uint32_t* bm = bitmap + (size_t)f * words;
+  const uint32_t* wp = wordprefix + (size_t)f * words;
+  const int row0 = voxel_offsets[f];
+  const uint32_t lane = threadIdx.x & 31;
+  const int span = gridDim.x * blockDim.x;
+  // warp-uniform trip count so that __match_any_sync sees whole warps
+  for (int base = beg + blockIdx.x * blockDim.x + (threadIdx.x & ~31); base < end; base += span) {
+    const int i = base + lane;
+    int row = -1;
+    if (i < end) {
+      const uint32_t key = (uint32_t)keyrow[i];
+      if (key != kInvalidKey) {
+        const uint32_t w = key >> 5, b = key & 31;
+        row = row0 + (int)(wp[w] + __popc(bm[w] & ((1u << b) - 1u)));
+      }
+    }
+    const uint32_t peers = __match_any_sync(0xffffffffu, row);
+    if (row >= 0) {
+      const int leader = __ffs(peers) - 1;
+      int slot0 = 0;
+      if ((int)lane == leader) slot0 = atomicAdd(cnt + row, __popc(peers));
+      slot0 = __shfl_sync(peers, slot0, leader);
+      arrival[i] = slot0 + __popc(peers & ((1u << lane) - 1u));
+    }
+    if (i < end) keyrow[i] = row;
+  }
+}
+
+// P5: one 1024-thread block per frame; seg[row] = frame's first point + exclusive prefix of cnt.
+__global__ void __launch_bounds__(1024) k_vox_segment_scan(const int32_t* __restrict__ frame_offsets,
+                                                            const int32_t* __restrict__ voxel_offsets,
+                                                            const int32_t* __restrict__ cnt,
+                                                            int32_t* __restrict__ seg) {
+  __shared__ uint32_t warp_total[32];
+  __shared__ uint32_t carry;
+  const int f = blockIdx.x;
+  const int r0 = voxel_offsets[f], r1 = voxel_offsets[f + 1];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) carry = (uint32_t)frame_offsets[f];
+  __syncthreads();
+  for (int base = r0; base < r1; base += 1024) {
+    const int r = base + threadIdx.x;
+    const uint32_t c = r < r1 ? (uint32_t)cnt[r] : 0;
+    const uint32_t incl = warp_incl_scan(c, lane);
+    if (lane == 31) warp_total[warp] = incl;
+    __syncthreads();
+    const uint32_t start = carry;
+    if (warp == 0) {
+      const uint32_t t = warp_total[lane];
+      const uint32_t ti = warp_incl_scan(t, lane);
+      warp_total[lane] = ti - t;
+      if (lane == 31) carry = start + ti;
+    }
+    __syncthreads();
+    if (r < r1) seg[r] = (int32_t)(start + warp_total[warp] + incl - c);
+    __syncthreads();
+  }
+}
+
+// P6
+__global__ void __launch_bounds__(256) k_vox_place(int64_t n_points, const int32_t* __restrict__ keyrow,
+                                                    const int32_t* __restrict__ arrival,
+                                                    const int32_t* __restrict__ seg, int32_t* __restrict__ pidx) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_points; i += stride) {
+    const int row = keyrow[i];
+    if (row >= 0) pidx[seg[row] + arrival[i]] = (int32_t)i;
+  }
+}
+
+__device__ __forceinline__ int warp_min_i32(int v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v = min(v, __shfl_xor_sync(0xffffffffu, v, d));
+  return v;
+}
+
+__device__ __forceinline__ float f4_comp(const float4& v, int j) {
+  return j == 0 ? v.x : (j == 1 ? v.y : (j == 2 ? v.z : v.w));
+}
+
+// P7: one warp per voxel row.
+constexpr int kFeatWarps = 8;
+__global__ void __launch_bounds__(kFeatWarps * 32) k_vox_features(
+    const vn_grid_t g, const float4* __restrict__ points, int n_frames,
+    const int32_t* __restrict__ voxel_offsets, int64_t max_voxels, const int32_t* __restrict__ cnt,
+    const int32_t* __restrict__ seg, const int32_t* __restrict__ pidx, float* __restrict__ feature,
+    long long* __restrict__ coords, long long* __restrict__ counts) {
+  __shared__ float4 stage[kFeatWarps][kMaxT];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  float4* pts = stage[warp];
+  const int T = g.T;
+  int64_t total = voxel_offsets[n_frames];
+  if (total > max_voxels) total = max_voxels;
+  const int64_t nwarps = (int64_t)gridDim.x * kFeatWarps;
+  for (int64_t row = (int64_t)blockIdx.x * kFeatWarps + warp; row < total; row += nwarps) {
+    const int n = cnt[row];
+    const int s0 = seg[row];
+    const int m = n < T ? n : T;
+    if (n <= 32) {
+      // rank of every index among the voxel's indices == its slot (n <= 32 <= T: all are kept)
+      const int idx = (int)lane < n ? pidx[s0 + lane] : 0x7fffffff;
+      int rank = 0;
+      for (int j = 0; j < n; ++j) rank += (__shfl_sync(0xffffffffu, idx, j) < idx) ? 1 : 0;
+      if ((int)lane < n) pts[rank] = points[idx];
+    } else {
+      // rare: more than a warp's worth of points.  Select the m smallest indices in ascending
+      // order by repeated min-above-threshold over the segment.
+      int last = -1, mine0 = -1, mine1 = -1;
+      for (int s = 0; s < m; ++s) {
+        int cand = 0x7fffffff;
+        for (int j = lane; j < n; j += 32) {
+          const int v = pidx[s0 + j];
+          if (v > last && v < cand) cand = v;
+        }
+        cand = warp_min_i32(cand);
+        last = cand;
+        if ((int)lane == (s & 31)) {
+          if (s < 32) mine0 = cand; else mine1 = cand;
+        }
+      }
+      if (mine0 >= 0) pts[lane] = points[mine0];
+      if (mine1 >= 0) pts[32 + lane] = points[mine1];
+    }
+    __syncwarp();
+
+    // utils.py:87-88: fp32 sum over ALL T slots in slot order (numpy reduces axis 1
+    // sequentially), the zero pads included - they only matter for the sign of a -0.0 sum.
+    double mean = 0.0;
+    if (lane < 3) {
+      float s = f4_comp(pts[0], lane);
+      for (int t = 1; t < m; ++t) s = __fadd_rn(s, f4_comp(pts[t], lane));
+      if (m < T) s = __fadd_rn(s, 0.0f);
+      mean = (double)s / (double)m;  // float32 / int64 promotes to float64 in numpy
+    }
+    const double mx = __shfl_sync(0xffffffffu, mean, 0);
+    const double my = __shfl_sync(0xffffffffu, mean, 1);
+    const double mz = __shfl_sync(0xffffffffu, mean, 2);
+
+    float* out = feature + row * (int64_t)(T * 7);
+    for (int e = lane; e < T * 7; e += 32) {
+      const int t = e / 7, j = e - t * 7;
+      float v;
+      if (j < 4) {
+        v = t < m ? f4_comp(pts[t], j) : 0.0f;
+      } else {
+        const float b = t < m ? f4_comp(pts[t], j - 4) : 0.0f;
+        const double c = j == 4 ? mx : (j == 5 ? my : mz);
+        v = __double2float_rn((double)b - c);  // float64 subtraction, rounded on store
+      }
+      out[e] = v;
+    }
+    if (lane == 0) {
+      int z, y, x;
+      point_cell(pts[0], g, z, y, x);
+      int lo = 0, hi = n_frames;  // frame of this row: last f with voxel_offsets[f] <= row
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if ((int64_t)voxel_offsets[mid] <= row) lo = mid; else hi = mid;
+      }
+      long long* c = coords + row * 4;
+      c[0] = lo;
+      c[1] = z;
+      c[2] = y;
+      c[3] = x;
+      counts[row] = m;
+    }
+    __syncwarp();
+  }
+}
+
+int check_common(const vn_grid_t* grid, const void* points, const int32_t* frame_offsets, int32_t n_frames,
+                 int64_t n_points_total, const void* workspace, size_t workspace_bytes) {
+  VN_REQUIRE(grid != nullptr, "voxelize: grid is null");
+  VN_REQUIRE(grid->D > 0 && grid->H > 0 && grid->W > 0, "voxelize: empty grid");
+  VN_REQUIRE((int64_t)grid->D * grid->H * grid->W < (int64_t)0x7fffffff, "voxelize: grid too large");
+  VN_REQUIRE(grid->T >= 1 && grid->T <= kMaxT, "voxelize: T=%d outside [1,%d]", grid->T, kMaxT);
+  VN_REQUIRE(n_frames >= 1, "voxelize: n_frames=%d", n_frames);
+  VN_REQUIRE(n_points_total >= 0 && n_points_total < (int64_t)0x7fffffff, "voxelize: bad point count");
+  VN_REQUIRE(frame_offsets != nullptr, "voxelize: frame_offsets is null");
+  VN_REQUIRE(points != nullptr || n_points_total == 0, "voxelize: points is null");
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(points) & 15) == 0, "voxelize: points must be 16-byte aligned");
+  VN_REQUIRE(workspace != nullptr, "voxelize: workspace is null");
+  const size_t need = carve(*grid, n_frames, n_points_total, nullptr).total_bytes;
+  if (workspace_bytes < need) {
+    set_error("voxelize: workspace %zu < %zu bytes", workspace_bytes, need);
+    return VN_ERR_WORKSPACE;
+  }
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "voxelize: workspace must be 256-byte aligned");
+  return VN_OK;
+}
+
+}  // namespace
+}  // namespace vn
+
+using namespace vn;
+
+extern "C" {
+
+size_t vn_voxelize_workspace_bytes(const vn_grid_t* grid, int32_t n_frames, int64_t n_points_total) {
+  if (grid == nullptr || n_frames < 1 || n_points_total < 0) return 0;
+  return carve(*grid, n_frames, n_points_total, nullptr).total_bytes;
+}
+
+int vn_voxelize_index(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                      int32_t n_frames, int64_t n_points_total, int32_t max_points_per_frame,
+                      int32_t* voxel_offsets, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  int rc = check_common(grid, points, frame_offsets, n_frames, n_points_total, workspace, workspace_bytes);
+  if (rc != VN_OK) return rc;
+  VN_REQUIRE(voxel_offsets != nullptr, "voxelize_index: voxel_offsets is null");
+  VN_REQUIRE(max_points_per_frame >= 0, "voxelize_index: max_points_per_frame < 0");
+  cudaStream_t st = as_stream(stream);
+  const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
+  const int sms = sm_count();
+
+  {
+    const size_t n16 = w.zero_bytes / 16;
+    const int blocks = (int)((n16 + 255) / 256 < (size_t)sms * 8 ? (n16 + 255) / 256 : (size_t)sms * 8);
+    k_fill_zero16<<<blocks, 256, 0, st>>>(reinterpret_cast<uint4*>(workspace), n16);
+    VN_LAUNCH_CHECK("k_fill_zero16");
+  }
+  const int bx = max_points_per_frame > 0 ? (max_points_per_frame + 255) / 256 : 1;
+  if (n_points_total > 0) {
+    k_vox_mark<<<dim3(bx, n_frames), 256, 0, st>>>(*grid, reinterpret_cast<const float4*>(points),
+                                                   frame_offsets, w.bitmap, w.words, w.keyrow);
+    VN_LAUNCH_CHECK("k_vox_mark");
+  }
+  k_vox_scan_words<<<n_frames, 1024, 0, st>>>(w.bitmap, w.wordprefix, w.words, w.frame_k);
+  VN_LAUNCH_CHECK("k_vox_scan_words");
+  k_vox_frame_offsets<<<1, 32, 0, st>>>(w.frame_k, n_frames, voxel_offsets);
+  VN_LAUNCH_CHECK("k_vox_frame_offsets");
+  if (n_points_total > 0) {
+    k_vox_count<<<dim3(bx, n_frames), 256, 0, st>>>(frame_offsets, w.bitmap, w.wordprefix, w.words,
+                                                    voxel_offsets, w.keyrow, w.arrival, w.cnt);
+    VN_LAUNCH_CHECK("k_vox_count");
+  }
+  return VN_OK;
+}
+
+int vn_voxelize_fill(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                     int32_t n_frames, int64_t n_points_total, int32_t max_points_per_frame,
+                     const int32_t* voxel_offsets, int64_t max_voxels, float* feature_buffer,
+                     int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace,
+                     size_t workspace_bytes, vn_stream_t stream) {
+  int rc = check_common(grid, points, frame_offsets, n_frames, n_points_total, workspace, workspace_bytes);
+  if (rc != VN_OK) return rc;
+  (void)max_points_per_frame;
+  VN_REQUIRE(voxel_offsets != nullptr, "voxelize_fill: voxel_offsets is null");
+  VN_REQUIRE(max_voxels >= 0, "voxelize_fill: max_voxels < 0");
+  if (max_voxels == 0 || n_points_total == 0) return VN_OK;
+  VN_REQUIRE(feature_buffer && coordinate_buffer && number_buffer, "voxelize_fill: null output");
+  cudaStream_t st = as_stream(stream);
+  const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
+  const int sms = sm_count();
+
+  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg);
+  VN_LAUNCH_CHECK("k_vox_segment_scan");
+  {
+    const int64_t want = (n_points_total + 255) / 256;
+    const int blocks = (int)(want < (int64_t)sms * 16 ? want : (int64_t)sms * 16);
+    k_vox_place<<<blocks, 256, 0, st>>>(n_points_total, w.keyrow, w.arrival, w.seg, w.pidx);
+    VN_LAUNCH_CHECK("k_vox_place");
+  }
+  {
+    // persistent warps: 8 resident blocks of 8 warps per SM
+    const int64_t want = (max_voxels + kFeatWarps - 1) / kFeatWarps;
+    const int blocks = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
+    k_vox_features<<<blocks, kFeatWarps * 32, 0, st>>>(
+        *grid, reinterpret_cast<const float4*>(points), n_frames, voxel_offsets, max_voxels, w.cnt, w.seg,
+        w.pidx, feature_buffer, reinterpret_cast<long long*>(coordinate_buffer),
+        reinterpret_cast<long long*>(number_buffer));
+    VN_LAUNCH_CHECK("k_vox_features");
+  }
+  return VN_OK;
+}
+
+int vn_voxelize_counts_host(const int32_t* voxel_offsets, int32_t n_frames, int32_t* voxel_offsets_host,
+                            vn_stream_t stream) {
+  VN_REQUIRE(voxel_offsets && voxel_offsets_host && n_frames >= 1, "voxelize_counts_host: bad argument");
+  cudaStream_t st = as_stream(stream);
+  VN_CUDA(cudaMemcpyAsync(voxel_offsets_host, voxel_offsets, sizeof(int32_t) * (size_t)(n_frames + 1),
+                          cudaMemcpyDeviceToHost, st));
+  VN_CUDA(cudaStreamSynchronize(st));
+  return VN_OK;
+}
+
+int vn_fill_zero(void* ptr, size_t bytes, vn_stream_t stream) {
+  VN_REQUIRE(ptr != nullptr || bytes == 0, "fill_zero: null pointer");
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(ptr) & 15) == 0 && (bytes & 15) == 0,
+             "fill_zero: pointer and size must be multiples of 16");
+  if (bytes == 0) return VN_OK;
+  const size_t n16 = bytes / 16;
+  const size_t want = (n16 + 255) / 256;
+  const size_t cap = (size_t)sm_count() * 16;
+  k_fill_zero16<<<(unsigned)(want < cap ? want : cap), 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<uint4*>(ptr), n16);
+  VN_LAUNCH_CHECK("k_fill_zero16");
+  return VN_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,158 @@
+"""The reference's front-end modules, re-implemented on libvoxelnet_b200 kernels.
+
+Mirrors (same class names, constructor arguments, forward signatures, parameter names):
+
+* `VFELayer`            voxelnet/model.py:60-82
+* `FeatureLearningNet`  voxelnet/model.py:85-108
+* `ConvMD` (3-D only)   voxelnet/model.py:111-167
+* `MiddleConvNet`       voxelnet/model.py:202-262, up to and including the reshape at :262
+                        (the RPN blocks after it stay on stock PyTorch in the reference and are
+                        out of scope here; `MiddleConvNet.forward` returns the (B,128,H,W) tensor
+                        the RPN consumes).
+
+Parameters live in ordinary nn.Linear / nn.BatchNorm1d / nn.Conv3d / nn.BatchNorm3d containers so
+that a reference `state_dict()` loads by name (`vfe_1.fcn.0.weight`, `vfe_1.bn.running_mean`,
+`middle_layer.0.conv.weight`, `middle_layer.0.batch_norm.weight`, ...), but their forward is never
+called: every forward here launches kernels from the C ABI.  Only eval-mode BatchNorm (running
+statistics) is implemented; calling a module in training mode raises.
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as nn
+
+from . import ops
+from .config import MIDDLE_LAYERS, grid_config
+
+
+def _fold_bn(bn: nn.modules.batchnorm._BatchNorm):
+    """Eval-mode BN as y = x * scale + shift (fp32, computed in fp64 then rounded)."""
+    var = bn.running_var.detach().double()
+    scale = bn.weight.detach().double() / torch.sqrt(var + bn.eps)
+    shift = bn.bias.detach().double() - bn.running_mean.detach().double() * scale
+    return scale.float().contiguous(), shift.float().contiguous()
+
+
+def _require_eval(module: nn.Module) -> None:
+    if module.training:
+        raise NotImplementedError(
+            "%s: only eval-mode BatchNorm is implemented on the B200 path (training statistics are "
+            "listed as 'next' in DESIGN.md); call .eval() first" % type(module).__name__
+        )
+
+
+class VFELayer(nn.Module):
+    """model.py:60-82.  forward(inputs (K,T,cin) f32, mask (K,T,1) bool) -> (K,T,cout) f32."""
+
+    def __init__(self, cin: int, cout: int):
+        super().__init__()
+        self.in_channels = cin
+        self.out_channels = cout
+        self.local_agg_features = cout // 2
+        self.fcn = nn.Sequential(nn.Linear(self.in_channels, self.local_agg_features), nn.ReLU())
+        self.bn = nn.BatchNorm1d(self.local_agg_features)
+
+    def folded(self):
+        """(weight, bias, bn_scale, bn_shift): Linear -> ReLU -> BN as relu(Wx+b)*scale+shift."""
+        scale, shift = _fold_bn(self.bn)
+        lin = self.fcn[0]
+        return lin.weight.detach().contiguous(), lin.bias.detach().contiguous(), scale, shift
+
+    def forward(self, inputs, mask):
+        _require_eval(self)
+        return ops.vfe_layer_fwd(inputs.contiguous(), mask, *self.folded())
+
+
+class FeatureLearningNet(nn.Module):
+    """model.py:85-108.  forward(feature: list[(K_i,T,7) f32], coordinate: list[(K_i,4) i64])
+    -> dense (B, D, H, W, 128) f32, B = len(feature)."""
+
+    def __init__(self, target: str = "Car"):
+        super().__init__()
+        self.target = target
+        self.vfe_1 = VFELayer(7, 32)
+        self.vfe_2 = VFELayer(32, 128)
+
+    def voxelwise(self, feature: torch.Tensor, out=None, n_voxels_dev=None) -> torch.Tensor:
+        """model.py:95-100 as one fused kernel: (K,T,7) -> (K,128)."""
+        _require_eval(self)
+        return ops.svfe_fused_fwd(feature, self.vfe_1.folded(), self.vfe_2.folded(), out=out, n_voxels_dev=n_voxels_dev)
+
+    def forward(self, feature: list, coordinate: list):
+        bs = len(feature)
+        feature = torch.cat(feature, dim=0).contiguous()
+        coordinate = torch.cat(coordinate, dim=0).contiguous()
+        vw = self.voxelwise(feature)
+        g = grid_config(self.target)
+        dense = torch.empty((bs, g.depth, g.height, g.width, 128), dtype=torch.float32, device=vw.device)
+        ops.fill_zero(dense)
+        ops.scatter_dense_f32(vw, coordinate, dense)
+        return dense
+
+
+class ConvMD(nn.Module):
+    """model.py:111-167, 3-D case: Conv3d(k=3) -> BatchNorm3d -> ReLU.
+
+    forward(x) takes the logical NCDHW fp32 tensor the reference passes (model.py:259 hands it a
+    channels-last view) and returns logical NCDHW fp32.  Internally: bf16 NDHWC in, tcgen05
+    implicit GEMM with fp32 accumulation, BN/bias/ReLU in the epilogue.  `forward_ndhwc` is the
+    chaining form without layout or dtype round trips.
+    """
+
+    def __init__(self, input_dim: int, cin: int, cout: int, kernel_size: int, stride, padding, bn: bool = True,
+                 activation: bool = True):
+        super().__init__()
+        if input_dim != 3:
+            raise ValueError("the B200 path implements the 3-D middle layers; 2-D ConvMD (the RPN) stays on stock PyTorch")
+        if kernel_size != 3 or cout != 64 or cin not in (64, 128) or not bn or not activation:
+            raise ValueError("unsupported ConvMD configuration for the B200 kernel (model.py:207-209 shapes only)")
+        stride, padding = tuple(stride), tuple(padding)
+        if stride[1:] != (1, 1) or padding[1:] != (1, 1) or (stride[0], padding[0]) not in ((2, 1), (1, 0)):
+            raise ValueError("unsupported stride/padding %s/%s" % (stride, padding))
+        self.input_dim, self.cin, self.cout = input_dim, cin, cout
+        self.kernel_size, self.stride, self.padding = kernel_size, stride, padding
+        self.bn, self.activation = bn, activation
+        self.conv = nn.Conv3d(cin, cout, kernel_size, stride, padding)
+        self.batch_norm = nn.BatchNorm3d(cout)
+        self._packed = None
+        self._packed_key = None
+
+    def folded(self):
+        """(packed bf16 weights, scale, shift): BN(conv(x)+b) = conv(x)*scale + shift."""
+        w = self.conv.weight
+        key = (w.data_ptr(), w._version, w.device)
+        if self._packed is None or self._packed_key != key:
+            self._packed = ops.conv3d_pack_weights(w)
+            self._packed_key = key
+        scale, bn_shift = _fold_bn(self.batch_norm)
+        shift = (self.conv.bias.detach().double() * scale.double() + bn_shift.double()).float().contiguous()
+        return self._packed, scale, shift
+
+    def forward_ndhwc(self, x_bf16, final: bool = False, out=None):
+        _require_eval(self)
+        packed, scale, shift = self.folded()
+        return ops.conv3d_bn_relu_fwd(x_bf16, packed, scale, shift, self.stride[0], self.padding[0], final=final, out=out)
+
+    def forward(self, x):
+        x_ndhwc = x.permute(0, 2, 3, 4, 1).contiguous().to(torch.bfloat16)
+        y = self.forward_ndhwc(x_ndhwc)
+        return y.permute(0, 4, 1, 2, 3).float()
+
+
+class MiddleConvNet(nn.Module):
+    """model.py:202-262 up to the reshape: forward(x (B,D,H,W,128) f32 or bf16) -> (B,128,H,W) f32."""
+
+    def __init__(self):
+        super().__init__()
+        self.middle_layer = nn.Sequential(
+            *[ConvMD(3, l["cin"], l["cout"], 3, l["stride"], l["padding"]) for l in MIDDLE_LAYERS]
+        )
+
+    def forward(self, x, out=None):
+        if x.dtype != torch.bfloat16:
+            x = x.to(torch.bfloat16)
+        x = x.contiguous()
+        x = self.middle_layer[0].forward_ndhwc(x)
+        x = self.middle_layer[1].forward_ndhwc(x)
+        # the last layer writes fp32 straight into the (B, c*2+d, H, W) layout of model.py:262
+        return self.middle_layer[2].forward_ndhwc(x, final=True, out=out)

@@ -1,0 +1,223 @@
+"""Thin torch-tensor wrappers over the C ABI (include/voxelnet_b200.h).
+
+torch is used here for device memory and the current stream only; every arithmetic step is a
+kernel of libvoxelnet_b200.so.  All functions require CUDA tensors and raise otherwise - there is
+no CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _cabi
+from ._cabi import check
+
+
+def _require_cuda(*tensors) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError(
+                "voxelnet_pytorch_b200 runs on CUDA only (sm_100a kernels, no CPU fallback); got a %s tensor" % t.device
+            )
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def _contig(t, dtype):
+    if t.dtype != dtype or not t.is_contiguous():
+        raise RuntimeError("expected a contiguous %s tensor, got %s contiguous=%s" % (dtype, t.dtype, t.is_contiguous()))
+    return t
+
+
+# ---------------------------------------------------------------------------------------------
+# voxelizer
+# ---------------------------------------------------------------------------------------------
+def voxelize_workspace_bytes(grid, n_frames: int, n_points: int) -> int:
+    return int(_cabi.lib().vn_voxelize_workspace_bytes(C.byref(grid), n_frames, n_points))
+
+
+def voxelize_index(grid, points, frame_offsets, max_points_per_frame: int, voxel_offsets, workspace) -> None:
+    """Phase 1 (see header).  points (N,4) f32, frame_offsets (B+1) i32, voxel_offsets (B+1) i32 out."""
+    _require_cuda(points, frame_offsets, voxel_offsets, workspace)
+    _contig(points, torch.float32), _contig(frame_offsets, torch.int32), _contig(voxel_offsets, torch.int32)
+    n_frames = frame_offsets.numel() - 1
+    with torch.cuda.device(points.device):
+        check(
+            _cabi.lib().vn_voxelize_index(
+                C.byref(grid), _ptr(points), _ptr(frame_offsets), n_frames, points.shape[0], max_points_per_frame,
+                _ptr(voxel_offsets), _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+            ),
+            "vn_voxelize_index",
+        )
+
+
+def voxelize_fill(grid, points, frame_offsets, max_points_per_frame, voxel_offsets, feature, coords, counts, workspace) -> None:
+    """Phase 2.  feature (cap,T,7) f32, coords (cap,4) i64, counts (cap,) i64 out."""
+    _require_cuda(points, frame_offsets, voxel_offsets, feature, coords, counts, workspace)
+    _contig(feature, torch.float32), _contig(coords, torch.int64), _contig(counts, torch.int64)
+    n_frames = frame_offsets.numel() - 1
+    with torch.cuda.device(points.device):
+        check(
+            _cabi.lib().vn_voxelize_fill(
+                C.byref(grid), _ptr(points), _ptr(frame_offsets), n_frames, points.shape[0], max_points_per_frame,
+                _ptr(voxel_offsets), feature.shape[0], _ptr(feature), _ptr(coords), _ptr(counts), _ptr(workspace),
+                workspace.numel() * workspace.element_size(), _stream(),
+            ),
+            "vn_voxelize_fill",
+        )
+
+
+def voxel_offsets_to_host(voxel_offsets) -> list:
+    """Blocking read of the (B+1) voxel prefix (the only synchronising entry point)."""
+    _require_cuda(voxel_offsets)
+    n = voxel_offsets.numel()
+    host = (C.c_int32 * n)()
+    with torch.cuda.device(voxel_offsets.device):
+        check(_cabi.lib().vn_voxelize_counts_host(_ptr(voxel_offsets), n - 1, host, _stream()), "vn_voxelize_counts_host")
+    return list(host)
+
+
+# ---------------------------------------------------------------------------------------------
+# VFE
+# ---------------------------------------------------------------------------------------------
+def feature_mask(feature) -> torch.Tensor:
+    """model.py:95-96 -> (K,T,1) bool."""
+    _require_cuda(feature)
+    _contig(feature, torch.float32)
+    K, T, cin = feature.shape
+    mask = torch.empty((K, T, 1), dtype=torch.bool, device=feature.device)
+    with torch.cuda.device(feature.device):
+        check(_cabi.lib().vn_feature_mask(_ptr(feature), K, T, cin, _ptr(mask), _stream()), "vn_feature_mask")
+    return mask
+
+
+def vfe_layer_fwd(inputs, mask, weight, bias, bn_scale, bn_shift) -> torch.Tensor:
+    """model.py:74-82 with eval BN folded.  inputs (K,T,cin) f32, mask (K,T,1) bool -> (K,T,2*units)."""
+    _require_cuda(inputs, mask, weight, bias, bn_scale, bn_shift)
+    _contig(inputs, torch.float32)
+    K, T, cin = inputs.shape
+    units = weight.shape[0]
+    if mask.dtype != torch.bool or mask.numel() != K * T:
+        raise RuntimeError("mask must be a bool tensor with K*T elements")
+    mask = mask.contiguous()
+    out = torch.empty((K, T, 2 * units), dtype=torch.float32, device=inputs.device)
+    with torch.cuda.device(inputs.device):
+        check(
+            _cabi.lib().vn_vfe_layer_fwd(
+                _ptr(inputs), _ptr(mask), K, T, cin, units, _ptr(_contig(weight, torch.float32)),
+                _ptr(_contig(bias, torch.float32)), _ptr(_contig(bn_scale, torch.float32)),
+                _ptr(_contig(bn_shift, torch.float32)), _ptr(out), _stream(),
+            ),
+            "vn_vfe_layer_fwd",
+        )
+    return out
+
+
+def svfe_fused_fwd(feature, p1, p2, out=None, n_voxels_dev=None) -> torch.Tensor:
+    """model.py:95-100 fused.  p1/p2 = (weight, bias, bn_scale, bn_shift) of VFE-1 / VFE-2."""
+    _require_cuda(feature, *p1, *p2)
+    _contig(feature, torch.float32)
+    K, T, cin = feature.shape
+    if cin != 7:
+        raise RuntimeError("svfe_fused_fwd expects 7 input features per point")
+    if out is None:
+        out = torch.empty((K, 128), dtype=torch.float32, device=feature.device)
+    with torch.cuda.device(feature.device):
+        check(
+            _cabi.lib().vn_svfe_fused_fwd(
+                _ptr(feature), K, T, _ptr(n_voxels_dev), *[_ptr(_contig(t, torch.float32)) for t in p1],
+                *[_ptr(_contig(t, torch.float32)) for t in p2], _ptr(out), _stream(),
+            ),
+            "vn_svfe_fused_fwd",
+        )
+    return out
+
+
+# ---------------------------------------------------------------------------------------------
+# sparse -> dense
+# ---------------------------------------------------------------------------------------------
+def fill_zero(t) -> None:
+    _require_cuda(t)
+    with torch.cuda.device(t.device):
+        check(_cabi.lib().vn_fill_zero(_ptr(t), t.numel() * t.element_size(), _stream()), "vn_fill_zero")
+
+
+def scatter_dense_f32(voxelwise, coords, dense, n_voxels_dev=None) -> None:
+    """model.py:102-106.  dense (B,D,H,W,C) f32, already zero."""
+    _require_cuda(voxelwise, coords, dense)
+    _contig(voxelwise, torch.float32), _contig(coords, torch.int64), _contig(dense, torch.float32)
+    B, D, H, W, Cc = dense.shape
+    with torch.cuda.device(dense.device):
+        check(
+            _cabi.lib().vn_scatter_dense_f32(
+                _ptr(voxelwise), _ptr(coords), voxelwise.shape[0], _ptr(n_voxels_dev), Cc, B, D, H, W, _ptr(dense), _stream()
+            ),
+            "vn_scatter_dense_f32",
+        )
+
+
+def scatter_dense_bf16(voxelwise, coords, dense, clear: bool = False, n_voxels_dev=None) -> None:
+    _require_cuda(voxelwise, coords, dense)
+    _contig(coords, torch.int64), _contig(dense, torch.bfloat16)
+    B, D, H, W, Cc = dense.shape
+    with torch.cuda.device(dense.device):
+        check(
+            _cabi.lib().vn_scatter_dense_bf16(
+                _ptr(voxelwise), _ptr(coords), coords.shape[0], _ptr(n_voxels_dev), Cc, B, D, H, W, _ptr(dense),
+                1 if clear else 0, _stream(),
+            ),
+            "vn_scatter_dense_bf16",
+        )
+
+
+# ---------------------------------------------------------------------------------------------
+# Conv3d middle
+# ---------------------------------------------------------------------------------------------
+def conv3d_pack_weights(weight) -> torch.Tensor:
+    """torch (64,cin,3,3,3) f32 -> packed bf16 tile image (see vn_conv3d.cu)."""
+    _require_cuda(weight)
+    w = _contig(weight.detach(), torch.float32)
+    cout, cin = w.shape[0], w.shape[1]
+    if cout != 64 or tuple(w.shape[2:]) != (3, 3, 3):
+        raise RuntimeError("conv3d kernel supports cout=64, 3x3x3 filters (model.py:207-209); got %s" % (tuple(w.shape),))
+    nbytes = int(_cabi.lib().vn_conv3d_packed_weight_bytes(cin))
+    if nbytes == 0:
+        raise RuntimeError("conv3d kernel supports cin in {64,128}; got %d" % cin)
+    packed = torch.empty(nbytes // 2, dtype=torch.bfloat16, device=w.device)
+    with torch.cuda.device(w.device):
+        check(_cabi.lib().vn_conv3d_pack_weights(_ptr(w), cin, _ptr(packed), _stream()), "vn_conv3d_pack_weights")
+    return packed
+
+
+def conv3d_out_depth(din: int, stride_d: int, pad_d: int) -> int:
+    return (din + 2 * pad_d - 3) // stride_d + 1
+
+
+def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int, final: bool = False, out=None):
+    """x (B,Din,H,W,cin) bf16 NDHWC -> (B,Dout,H,W,64) bf16, or with final=True the reference's
+    reshaped (B, 64*Dout, H, W) f32 (model.py:262)."""
+    _require_cuda(x, packed_weight, scale, shift)
+    _contig(x, torch.bfloat16)
+    B, Din, H, W, cin = x.shape
+    Dout = conv3d_out_depth(Din, stride_d, pad_d)
+    if out is None:
+        if final:
+            out = torch.empty((B, 64 * Dout, H, W), dtype=torch.float32, device=x.device)
+        else:
+            out = torch.empty((B, Dout, H, W, 64), dtype=torch.bfloat16, device=x.device)
+    with torch.cuda.device(x.device):
+        check(
+            _cabi.lib().vn_conv3d_bn_relu_fwd(
+                _ptr(x), B, Din, H, W, cin, stride_d, pad_d, _ptr(packed_weight), _ptr(_contig(scale, torch.float32)),
+                _ptr(_contig(shift, torch.float32)), 1 if final else 0, _ptr(out), _stream(),
+            ),
+            "vn_conv3d_bn_relu_fwd",
+        )
+    return out
