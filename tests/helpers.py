@@ -35,7 +35,8 @@ def assert_voxels_equal(got: dict, want: dict):
 
 def load_state(module, sd, prefix):
     """Load the oracle-style flat state dict entries under `prefix` into a module."""
-    sub = {k[len(prefix):]: v for k, v in sd.items() if k.startswith(prefix)}
+    own = set(module.state_dict().keys())
+    sub = {k[len(prefix):]: v for k, v in sd.items() if k.startswith(prefix) and k[len(prefix):] in own}
     missing, unexpected = module.load_state_dict(sub, strict=False)
     assert not unexpected, unexpected
     assert not missing, missing
