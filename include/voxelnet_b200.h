@@ -143,9 +143,11 @@ int vn_scatter_dense_bf16(const float* voxelwise, const int64_t* coords, int64_t
  * ------------------------------------------------------------------------------------------ */
 
 /* Repack torch-layout fp32 weights [64, cin, 3, 3, 3] into the kernel's bf16 tap-major,
- * 128B-swizzled tile layout.  packed holds 27 * cin * 64 bf16. */
+ * 128B-swizzled tile layout.  packed holds 27 * cin * 64 bf16.  The image depends on the depth
+ * stride of the layer it will be used with (depth taps that share an input plane sit side by side). */
 size_t vn_conv3d_packed_weight_bytes(int32_t cin);
-int vn_conv3d_pack_weights(const float* weight, int32_t cin, void* packed, vn_stream_t stream);
+int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, void* packed,
+                           vn_stream_t stream);
 
 /* x: [B, Din, H, W, cin] bf16 (NDHWC).  cin in {64, 128}, cout = 64, kernel 3x3x3, H/W stride 1 and
  * padding 1; depth stride/padding (stride_d, pad_d) in {(2,1), (1,0)}.

@@ -1,0 +1,148 @@
+"""CPU: the C-ABI library loads and exports every symbol include/voxelnet_b200.h declares; host-side
+logic (config, batch packer, argument validation, no-GPU failure mode)."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _header_symbols():
+    text = open(os.path.join(ROOT, "include", "voxelnet_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(vn_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_library_exports_every_declared_symbol():
+    from voxelnet_pytorch_b200 import _cabi
+
+    lib = _cabi.lib()
+    names = _header_symbols()
+    assert len(names) >= 17
+    for n in names:
+        assert hasattr(lib, n), "libvoxelnet_b200.so lacks %s" % n
+    assert sorted(_cabi.PROTOTYPES) == names, "ctypes prototypes out of sync with the header"
+    assert lib.vn_abi_version() == _cabi.VN_ABI_VERSION
+
+
+def test_grid_constants_match_reference_values():
+    from voxelnet_pytorch_b200 import _cabi, grid_config
+
+    car, ped = _cabi.grid_for_target("Car"), _cabi.grid_for_target("Cyclist")
+    assert (car.D, car.H, car.W, car.T) == (10, 400, 352, 35)
+    assert (ped.D, ped.H, ped.W, ped.T) == (10, 200, 240, 45)
+    assert (car.off_x, car.off_y, car.off_z) == (0.0, 40.0, 3.0) and ped.off_y == 20.0
+    assert np.float32(car.vs_x) == np.float32(0.2) and np.float32(car.vs_z) == np.float32(0.4)
+    for t, g in (("Car", car), ("Pedestrian", ped)):
+        c = grid_config(t)
+        assert (c.depth, c.height, c.width, c.points_per_voxel) == (g.D, g.H, g.W, g.T)
+        # config.py:46-48: cells = range / voxel size
+        assert c.width == int(round((c.x_range[1] - c.x_range[0]) / 0.2)) and c.height == int(round((c.y_range[1] - c.y_range[0]) / 0.2))
+
+
+def test_bad_arguments_are_rejected_without_a_gpu():
+    from voxelnet_pytorch_b200 import _cabi
+
+    lib = _cabi.lib()
+    g = _cabi.grid_for_target("Car")
+    assert lib.vn_voxelize_workspace_bytes(ctypes.byref(g), 16, 2_000_000) > 0
+    assert lib.vn_voxelize_workspace_bytes(ctypes.byref(g), 0, 10) == 0
+    rc = lib.vn_voxelize_index(ctypes.byref(g), None, None, 1, 10, 10, None, None, 0, None)
+    assert rc == -1 and b"null" in lib.vn_last_error()
+    rc = lib.vn_vfe_layer_fwd(None, None, 5, 35, 9, 16, None, None, None, None, None, None)
+    assert rc < 0
+    rc = lib.vn_conv3d_bn_relu_fwd(ctypes.c_void_p(16), 1, 10, 16, 12, 128, 2, 1, ctypes.c_void_p(16), ctypes.c_void_p(16),
+                                  ctypes.c_void_p(16), 0, ctypes.c_void_p(16), None)
+    assert rc == -1 and b"multiple of 8" in lib.vn_last_error()
+    assert lib.vn_conv3d_packed_weight_bytes(128) == 27 * 128 * 64 * 2 and lib.vn_conv3d_packed_weight_bytes(32) == 0
+    with pytest.raises(_cabi.VnError):
+        _cabi.check(rc, "probe")
+
+
+def test_product_path_fails_loudly_without_cuda():
+    import voxelnet_pytorch_b200 as vn
+
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    with pytest.raises(RuntimeError, match="CUDA"):
+        vn.pcl_to_voxels(np.zeros((10, 4), np.float32), "Car")
+    net = vn.FeatureLearningNet().eval()
+    with pytest.raises(RuntimeError, match="CUDA"):
+        net.voxelwise(torch.zeros((3, 35, 7)))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        vn.MiddleConvNet().eval()(torch.zeros((1, 10, 16, 8, 128)))
+
+
+def test_product_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "voxelnet-pytorch_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh")):
+                text = open(os.path.join(dirpath, f)).read()
+                assert "oracle" not in text.replace("# oracle", ""), "%s mentions the oracle" % f
+
+
+def test_prepare_voxel_and_collate():
+    import voxelnet_pytorch_b200 as vn
+    from oracle import voxelize_np as OV
+    from tests import golden_util as G
+
+    pts = G.kitti_sub_points()
+    d = [OV.pcl_to_voxels_fast(pts[:4000], "Car"), OV.pcl_to_voxels_fast(pts[4000:9000], "Car"), OV.pcl_to_voxels_fast(pts[:0], "Car")]
+    f, n, c = vn.prepare_voxel(d)
+    f0, n0, c0 = OV.prepare_voxel(d)
+    for a, b in zip(c, c0):
+        assert a.dtype == np.int64 and np.array_equal(a, b)
+    assert f[1] is d[1]["feature_buffer"] and c[2].shape == (0, 4)
+    parts = [("t%d" % i, None, pts[:10], [], d[i]) for i in range(3)]
+    out = vn.collate_fn(parts)
+    assert len(out) == 7 and out[2][0].dtype == torch.float32 and out[4][1].dtype == torch.int64
+    assert torch.equal(out[4][1], torch.from_numpy(c0[1]))
+
+
+def test_modules_keep_reference_parameter_names_and_shapes():
+    import voxelnet_pytorch_b200 as vn
+    from oracle import model_torch as OM
+
+    sd = OM.random_state_dict(0)
+    f, m = vn.FeatureLearningNet(), vn.MiddleConvNet()
+    f.load_state_dict({k: v for k, v in sd.items() if k.startswith("vfe_")})
+    m.load_state_dict({k: v for k, v in sd.items() if k.startswith("middle_layer.")})
+    assert f.vfe_1.fcn[0].weight.shape == (16, 7) and f.vfe_2.fcn[0].weight.shape == (64, 32)
+    assert m.middle_layer[0].conv.weight.shape == (64, 128, 3, 3, 3)
+    assert m.middle_layer[1].conv.stride == (1, 1, 1) and m.middle_layer[1].conv.padding == (0, 1, 1)
+    with pytest.raises(ValueError):
+        vn.ConvMD(2, 128, 128, 3, (1, 1), (1, 1))
+    with pytest.raises(NotImplementedError):
+        vn.VFELayer(7, 32).train()(torch.zeros(1, 35, 7), torch.ones(1, 35, 1, dtype=torch.bool))
+
+
+def test_bn_folding_is_the_eval_affine():
+    import voxelnet_pytorch_b200 as vn
+    from oracle import model_torch as OM
+
+    sd = OM.random_state_dict(4)
+    l = vn.VFELayer(7, 32).eval()
+    l.load_state_dict({k[len("vfe_1."):]: v for k, v in sd.items() if k.startswith("vfe_1.")})
+    w, b, s, t = l.folded()
+    x = torch.randn(50, 7)
+    want = torch.nn.functional.batch_norm(torch.relu(x @ w.T + b), sd["vfe_1.bn.running_mean"], sd["vfe_1.bn.running_var"],
+                                          sd["vfe_1.bn.weight"], sd["vfe_1.bn.bias"], False, 0.0, 1e-5)
+    assert torch.allclose(torch.relu(x @ w.T + b) * s + t, want, rtol=1e-5, atol=1e-6)
+
+
+def test_synthetic_frames_are_kitti_shaped():
+    from oracle import voxelize_np as OV
+    from voxelnet_pytorch_b200 import synth
+
+    p = synth.lidar_frame(0)
+    assert p.dtype == np.float32 and p.shape[1] == 4 and 100_000 < len(p) < 135_000
+    assert np.array_equal(p, synth.lidar_frame(0))  # seeded
+    v = OV.pcl_to_voxels_fast(p, "Car")
+    K = len(v["number_buffer"])
+    assert 9_000 < K < 16_000, K  # KITTI-typical 12-14k
+    assert 3.5 < v["number_buffer"].mean() < 6.5

@@ -1,0 +1,82 @@
+"""CPU: the oracle against the golden vectors frozen from the unmodified reference."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_torch as OM
+from oracle import voxelize_np as OV
+from tests import golden_util as G
+
+
+@pytest.mark.parametrize("case", range(5))
+def test_voxelizer_oracle_fast_matches_reference_golden(case):
+    name, target, pts = G.voxel_cases()[case]
+    G.check_voxel_dict_against_golden(OV.pcl_to_voxels_fast(pts, target), name)
+
+
+def test_voxelizer_oracle_loop_matches_reference_golden():
+    name, target, pts = G.voxel_cases()[0]
+    G.check_voxel_dict_against_golden(OV.pcl_to_voxels_loop(pts, target), name)
+
+
+def test_loop_and_fast_agree_on_edge_cases():
+    rng = np.random.default_rng(0)
+    pts = np.concatenate([
+        np.tile(np.array([[10.05, 0.05, -1.0, 0.5]], np.float32), (80, 1)) + rng.uniform(0, 0.09, (80, 4)).astype(np.float32),
+        np.array([[0.0, -40.0, -3.0, 0.1], [70.4, 0, 0, 0.2], [-0.0, 0.0, -0.0, 0.0], [0, 0, 0, 0], [-1e-9, 0, 0, 0.5]], np.float32),
+    ])
+    for target in ("Car", "Cyclist"):
+        a, b = OV.pcl_to_voxels_loop(pts, target), OV.pcl_to_voxels_fast(pts, target)
+        for k in a:
+            assert a[k].dtype == b[k].dtype and np.array_equal(a[k].view(np.uint8), b[k].view(np.uint8)), (target, k)
+    e = OV.pcl_to_voxels_fast(np.zeros((0, 4), np.float32), "Car")
+    assert e["feature_buffer"].shape == (0, 35, 7) and e["coordinate_buffer"].shape == (0, 3)
+
+
+def test_prepare_voxel_batch_column():
+    pts = G.kitti_sub_points()
+    d = [OV.pcl_to_voxels_fast(pts[:5000], "Car"), OV.pcl_to_voxels_fast(pts[5000:9000], "Car")]
+    f, n, c = OV.prepare_voxel(d)
+    assert c[1].shape[1] == 4 and c[1].dtype == np.int64 and (c[1][:, 0] == 1).all() and (c[0][:, 0] == 0).all()
+    assert np.array_equal(c[1][:, 1:], d[1]["coordinate_buffer"])
+
+
+def _model_inputs():
+    g = G.load("model_ref_outputs.npz")
+    sd = OM.random_state_dict(int(g["state_seed"]))
+    K = int(g["K"])
+    vox = OV.pcl_to_voxels_fast(G.kitti_sub_points(), "Car")
+    feat = torch.from_numpy(vox["feature_buffer"][:K].copy())
+    coord = torch.from_numpy(np.pad(vox["coordinate_buffer"][:K], ((0, 0), (1, 0)), constant_values=0))
+    return g, sd, feat, coord
+
+
+def test_svfe_oracle_matches_reference_golden():
+    g, sd, feat, coord = _model_inputs()
+    with torch.no_grad():
+        vw = OM.svfe_voxelwise(feat, sd)
+        assert torch.allclose(vw, torch.from_numpy(g["voxelwise"]), rtol=1e-6, atol=1e-6)
+        mask = OM.feature_mask(feat)
+        v1 = OM.vfe_layer(feat, mask, sd, "vfe_1.")
+        assert torch.allclose(v1, torch.from_numpy(g["vfe1_out"]), rtol=1e-6, atol=1e-6)
+        gen = torch.Generator().manual_seed(int(g["vfe2_seed"]))
+        x2 = torch.randn((64, 35, 32), generator=gen)
+        m2 = torch.rand((64, 35, 1), generator=gen) > 0.3
+        v2 = OM.vfe_layer(x2, m2, sd, "vfe_2.")
+        assert torch.allclose(v2, torch.from_numpy(g["vfe2_out"]), rtol=1e-6, atol=1e-6)
+        dense = OM.feature_learning_net([feat], [coord], sd, "Car")
+        assert dense.shape == (1, 10, 400, 352, 128)
+        assert int((dense.abs().sum(-1) != 0).sum()) == int(g["dense_nonzero_rows"])
+
+
+def test_middle_oracle_matches_reference_golden():
+    g = G.load("model_ref_outputs.npz")
+    sd = OM.random_state_dict(int(g["state_seed"]))
+    B, D, H, W = (int(v) for v in g["middle_shape"])
+    gen = torch.Generator().manual_seed(int(g["middle_seed"]))
+    xd = torch.randn((B, D, H, W, 128), generator=gen) * (torch.rand((B, D, H, W, 1), generator=gen) > 0.8)
+    with torch.no_grad():
+        y = OM.middle_layers(xd, sd)
+        y1 = OM.middle_layers(xd, sd, upto=1)
+    assert torch.allclose(y1, torch.from_numpy(g["middle_layer0_out"]), rtol=1e-5, atol=1e-5)
+    assert torch.allclose(y, torch.from_numpy(g["middle_out"]), rtol=1e-5, atol=1e-5)

@@ -1,0 +1,84 @@
+"""CPU, container only: the oracle against the LIVE unmodified reference imported from
+/root/reference (skipped where the reference is absent, e.g. on the GPU box)."""
+import warnings
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import model_torch as OM
+from oracle import ref_import as R
+from oracle import voxelize_np as OV
+
+pytestmark = [
+    pytest.mark.reference,
+    pytest.mark.skipif(not R.reference_available(), reason="/root/reference not present"),
+    pytest.mark.filterwarnings("ignore"),
+]
+
+
+@pytest.mark.parametrize("frame,target", [(0, "Car"), (57, "Car"), (107, "Pedestrian")])
+def test_voxelizer_on_real_kitti_frames(frame, target):
+    pcl = np.fromfile(R.kitti_frame_path(frame), dtype=np.float32).reshape(-1, 4)
+    want = R.ref_pcl_to_voxels(pcl, target)
+    got = OV.pcl_to_voxels_fast(pcl, target)
+    for k in want:
+        assert got[k].dtype == want[k].dtype and got[k].shape == want[k].shape, k
+        assert np.array_equal(got[k].view(np.uint8), want[k].view(np.uint8)), k
+
+
+def test_voxelizer_with_reference_shuffle_seeded():
+    """With the real in-place shuffle on both sides and the same numpy seed."""
+    ref = R.load_reference()
+    pcl = np.fromfile(R.kitti_frame_path(3), dtype=np.float32).reshape(-1, 4)[::3].copy()
+    a = pcl.copy()
+    np.random.seed(7)
+    want = ref.utils.pcl_to_voxels(a, "Car", False)
+    b = pcl.copy()
+    np.random.seed(7)
+    np.random.shuffle(b)
+    assert np.array_equal(a, b)
+    got = OV.pcl_to_voxels_loop(b, "Car")
+    for k in want:
+        assert np.array_equal(got[k].view(np.uint8), want[k].view(np.uint8)), k
+
+
+def test_prepare_voxel_matches_reference():
+    ref = R.load_reference()
+    pcl = np.fromfile(R.kitti_frame_path(1), dtype=np.float32).reshape(-1, 4)[::5]
+    d = [OV.pcl_to_voxels_fast(pcl, "Car"), OV.pcl_to_voxels_fast(pcl[::2], "Car")]
+    f0, n0, c0 = ref.dataset.prepare_voxel(d)
+    f1, n1, c1 = OV.prepare_voxel(d)
+    for a, b in zip(c0, c1):
+        assert a.dtype == b.dtype and np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("target", ["Car", "Pedestrian"])
+def test_model_oracle_matches_reference_modules(target):
+    sd = OM.random_state_dict(31)
+    pcl = np.fromfile(R.kitti_frame_path(2), dtype=np.float32).reshape(-1, 4)[::8]
+    vox = OV.pcl_to_voxels_fast(pcl, target)
+    feat = torch.from_numpy(vox["feature_buffer"][:200].copy())
+    coord = torch.from_numpy(np.pad(vox["coordinate_buffer"][:200], ((0, 0), (1, 0)), constant_values=0))
+    with R.ref_model_cfg(target) as ref, torch.no_grad():
+        fnet = ref.model.FeatureLearningNet().eval()
+        fnet.load_state_dict({k: v for k, v in sd.items() if k.startswith("vfe_")})
+        want = fnet([feat], [coord])
+        got = OM.feature_learning_net([feat], [coord], sd, target)
+        assert got.shape == want.shape and torch.allclose(got, want, rtol=1e-6, atol=1e-6)
+        mid = ref.model.MiddleConvNet().eval()
+        mid.load_state_dict({k: v for k, v in sd.items() if k.startswith("middle_layer.")}, strict=False)
+        x = torch.randn((1, 10, 16, 24, 128), generator=torch.Generator().manual_seed(1))
+        want_mid = mid.middle_layer(x.permute(0, 4, 1, 2, 3)).reshape((1, -1, 16, 24))
+        assert torch.allclose(OM.middle_layers(x, sd), want_mid, rtol=1e-5, atol=1e-5)
+
+
+def test_state_dict_names_match_reference():
+    ref = R.load_reference()
+    import voxelnet_pytorch_b200 as vn
+
+    rf = set(ref.model.FeatureLearningNet().state_dict().keys())
+    assert rf == set(vn.FeatureLearningNet().state_dict().keys())
+    rm = {k for k in ref.model.MiddleConvNet().state_dict().keys() if k.startswith("middle_layer.")}
+    assert rm == set(vn.MiddleConvNet().state_dict().keys())
+    assert rf | rm == set(OM.random_state_dict(0).keys())

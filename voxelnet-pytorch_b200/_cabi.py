@@ -47,7 +47,7 @@ PROTOTYPES = {
     "vn_scatter_dense_f32": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p]),
     "vn_scatter_dense_bf16": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p]),
     "vn_conv3d_packed_weight_bytes": (_sz, [_i32]),
-    "vn_conv3d_pack_weights": (C.c_int, [_p, _i32, _p, _p]),
+    "vn_conv3d_pack_weights": (C.c_int, [_p, _i32, _i32, _p, _p]),
     "vn_conv3d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p]),
     "vn_launch_count": (_i64, []),
 }

@@ -79,6 +79,18 @@ __device__ __forceinline__ void st_stream_u4(void* p, uint4 v) {
                : "memory");
 }
 
+// One elected lane of a fully converged warp (warp-uniform control flow around single-thread
+// instructions keeps their operands in uniform registers - no per-lane waterfall loops).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred = 0;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.b32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // ---- mbarrier ---------------------------------------------------------------------------------
 __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");

@@ -5,21 +5,27 @@
 // GEMM view: M = output positions, N = 64 output channels, K = 27 taps x Cin.
 //
 // Tiling (DESIGN.md "Conv3d"): one CTA owns a 16 (h) x 8 (w) spatial tile for ALL output depths of
-// one frame: Dout accumulators of 128 x 64 fp32 live side by side in TMEM (64 columns each).  The
-// K loop walks the INPUT planes in ascending order; an input plane p feeds output depth
-// d' = (p + pad_d - kd) / stride_d for every valid kd, so each A tile fetched from L2 is used for up
-// to three depth taps, and accumulators complete one after the other - the epilogue drains
-// accumulator d' while the tensor core is already working on d'+1 (and on the next tile).
+// one frame: Dout accumulators of 128 x 64 fp32 live side by side in TMEM (64 columns each, depth
+// ascending).  The K loop walks the INPUT planes in ascending order.  An input plane p feeds
+// output depth d' = (p + pad_d - kd) / stride_d for every valid kd; those d' are consecutive, so
+// the depth taps of one plane are fused along N: ONE tcgen05.mma of shape 128 x (64*nkd) x 16
+// multiplies the A tile with the nkd weight tiles laid side by side and lands in nkd adjacent
+// accumulators.  This reads the A operand from shared memory once instead of nkd times (N = 64
+// alone is shared-memory-bandwidth bound: 6 KB of operands per 32 tensor cycles), and accumulators
+// complete in ascending order, so the epilogue drains d' while the tensor core works on d'+1 and on
+// the next tile.
 //
 //   A operand: per (plane, 64-channel chunk, kw) ONE TMA box of 64 ch x 8 w x 18 h (an h-halo'd
 //              tile, 128-byte rows, SWIZZLE_128B).  The three kh taps read it at +kh*1024 B: one
 //              image row of the tile is exactly one 8-row swizzle atom, so every tap start stays
 //              atom-aligned.  Out-of-range h / w / (skipped) d are the convolution's zero padding,
 //              supplied by TMA's out-of-bounds zero fill.
-//   B operand: weights pre-packed per (kd, chunk, kw) as three [64 n x 64 k] K-major tiles (kh = 0..2)
-//              already in the swizzled shared-memory image, fetched with one 24 KB bulk copy.
-//   Warp roles: warp 0 = TMA producer (one lane), warp 1 = TMEM allocator + MMA issuer (one lane),
-//              warps 2..5 = epilogue (TMEM -> registers -> scale/shift/ReLU -> global).
+//   B operand: weights pre-packed per (kd class, chunk, kw, kh) as nkd [64 n x 64 k] K-major tiles,
+//              kd descending (= d' ascending), already in the swizzled shared-memory image; one
+//              bulk copy of nkd * 8 KB per (chunk, kw, kh).
+//   Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (both run warp-uniform
+//              control flow and elect one lane for the asynchronous instructions), warps 2..5 =
+//              epilogue (TMEM -> registers -> scale/shift/ReLU -> global).
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -32,23 +38,34 @@ constexpr int kTileH = 16, kTileW = 8;             // 128 output positions per a
 constexpr int kHaloH = kTileH + 2;
 constexpr uint32_t kABytes = kHaloH * kTileW * 128;  // 18432: 144 rows of 64 bf16
 constexpr uint32_t kBTapBytes = 64 * 128;            // 8192: [64 n][64 k] bf16
-constexpr uint32_t kBBytes = 3 * kBTapBytes;         // kh = 0..2
-constexpr int kNA = 4, kNB = 5;                      // ring depths
+constexpr uint32_t kBSlotBytes = 3 * kBTapBytes;     // up to three depth taps side by side
+constexpr int kNA = 3, kNB = 6;                      // ring depths
 constexpr int kMaxDout = 8;                          // 8 x 64 = 512 TMEM columns
+constexpr int kMaxPlanes = 16;
 constexpr int kThreads = 6 * 32;
-constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBBytes;  // 196608
+constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBSlotBytes;  // 202752
 constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + 1024 /*barriers, params*/;
+
+// What one input plane contributes (host-computed; see plan_planes()).
+struct PlaneInfo {
+  int32_t nkd;        // number of valid depth taps (0: plane unused)
+  int32_t dmin;       // first output depth fed; tap j feeds dmin + j
+  int32_t new_acc;    // output depth whose FIRST contribution comes from this plane, or -1
+  uint32_t woff;      // byte offset of this plane's first weight tile inside its kd class
+  uint32_t wstride;   // bytes between consecutive (chunk, kw, kh) tile groups of the class
+  int32_t done_mask;  // bit d set: accumulator d is complete after this plane
+};
 
 struct ConvParams {
   int B, Din, Dout, H, W;
   int nchunk;      // Cin / 64
-  int stride_d, pad_d;
   int tiles_h, tiles_w, n_tiles;
   int out_mode;    // 0: bf16 NDHWC, 1: f32 [B, 64*Dout, H, W] with channel = c*Dout + d
   const uint8_t* wpack;
   const float* scale;
   const float* shift;
   void* out;
+  PlaneInfo plane[kMaxPlanes];
 };
 
 struct Barriers {
@@ -61,15 +78,8 @@ struct Barriers {
 };
 static_assert(sizeof(Barriers) <= 1024, "barrier block too large");
 
-__device__ __forceinline__ bool tap_target(int p, int kd, const ConvParams& P, int& dout) {
-  const int num = p + P.pad_d - kd;
-  if (num < 0 || num % P.stride_d != 0) return false;
-  dout = num / P.stride_d;
-  return dout < P.Dout;
-}
-
 __global__ void __launch_bounds__(kThreads, 1)
-    k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const ConvParams P) {
+    k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ ConvParams P) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte aligned tiles
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -78,7 +88,8 @@ __global__ void __launch_bounds__(kThreads, 1)
   Barriers* bar = reinterpret_cast<Barriers*>(smem + kSmemData);
 
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t tmem_cols = P.Dout * 64 <= 32 ? 32 : (P.Dout * 64 <= 64 ? 64 : (P.Dout * 64 <= 128 ? 128 : (P.Dout * 64 <= 256 ? 256 : 512)));
+  const uint32_t acc_cols = (uint32_t)P.Dout * 64;
+  const uint32_t tmem_cols = acc_cols <= 32 ? 32 : (acc_cols <= 64 ? 64 : (acc_cols <= 128 ? 128 : (acc_cols <= 256 ? 256 : 512)));
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < kNA; ++i) { mbar_init(&bar->full_a[i], 1); mbar_init(&bar->empty_a[i], 1); }
@@ -102,92 +113,104 @@ __global__ void __launch_bounds__(kThreads, 1)
   const uint32_t tmem_base = bar->tmem_base;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (lane == 0) {
-      uint32_t a_it = 0, b_it = 0;
-      for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-        const int tw = tile % P.tiles_w;
-        const int th = (tile / P.tiles_w) % P.tiles_h;
-        const int b = tile / (P.tiles_w * P.tiles_h);
-        const int h0 = th * kTileH, w0 = tw * kTileW;
-        for (int p = 0; p < P.Din; ++p) {
-          int dd;
-          const bool v0 = tap_target(p, 0, P, dd), v1 = tap_target(p, 1, P, dd), v2 = tap_target(p, 2, P, dd);
-          if (!(v0 | v1 | v2)) continue;
-          for (int c = 0; c < P.nchunk; ++c) {
-            for (int kw = 0; kw < 3; ++kw) {
-              const uint32_t sa = a_it % kNA;
-              mbar_wait(&bar->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+    // ===================== TMA producer (warp-uniform; one elected lane issues) =====================
+    uint32_t a_it = 0, b_it = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      const int tw = tile % P.tiles_w;
+      const int th = (tile / P.tiles_w) % P.tiles_h;
+      const int b = tile / (P.tiles_w * P.tiles_h);
+      const int h0 = th * kTileH, w0 = tw * kTileW;
+      for (int p = 0; p < P.Din; ++p) {
+        const PlaneInfo& pi = P.plane[p];
+        if (pi.nkd == 0) continue;
+        const uint32_t b_bytes = (uint32_t)pi.nkd * kBTapBytes;
+        for (int c = 0; c < P.nchunk; ++c) {
+          for (int kw = 0; kw < 3; ++kw) {
+            const uint32_t sa = a_it % kNA;
+            mbar_wait(&bar->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+            if (elect_one()) {
               mbar_arrive_expect_tx(&bar->full_a[sa], kABytes);
               tma_load_5d(smem_a + sa * kABytes, &tmap_x, &bar->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
-              ++a_it;
-              for (int kd = 0; kd < 3; ++kd) {
-                if (!(kd == 0 ? v0 : (kd == 1 ? v1 : v2))) continue;
-                const uint32_t sb = b_it % kNB;
-                mbar_wait(&bar->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
-                mbar_arrive_expect_tx(&bar->full_b[sb], kBBytes);
-                const uint8_t* src = P.wpack + (size_t)(((kd * P.nchunk + c) * 3 + kw) * 3) * kBTapBytes;
-                bulk_load_1d(smem_b + sb * kBBytes, src, kBBytes, &bar->full_b[sb]);
-                ++b_it;
+            }
+            __syncwarp();
+            ++a_it;
+            for (int kh = 0; kh < 3; ++kh) {
+              const uint32_t sb = b_it % kNB;
+              mbar_wait(&bar->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
+              if (elect_one()) {
+                mbar_arrive_expect_tx(&bar->full_b[sb], b_bytes);
+                const uint8_t* src = P.wpack + pi.woff + (size_t)((c * 3 + kw) * 3 + kh) * pi.wstride;
+                bulk_load_1d(smem_b + sb * kBSlotBytes, src, b_bytes, &bar->full_b[sb]);
               }
+              __syncwarp();
+              ++b_it;
             }
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (lane == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(128, 64);
-      uint32_t a_it = 0, b_it = 0, tile_it = 0;
-      for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tile_it) {
-        uint32_t started = 0;
-        for (int p = 0; p < P.Din; ++p) {
-          int d0, d1, d2;
-          const bool v0 = tap_target(p, 0, P, d0), v1 = tap_target(p, 1, P, d1), v2 = tap_target(p, 2, P, d2);
-          if (!(v0 | v1 | v2)) continue;
-          for (int c = 0; c < P.nchunk; ++c) {
-            for (int kw = 0; kw < 3; ++kw) {
-              const uint32_t sa = a_it % kNA;
-              mbar_wait(&bar->full_a[sa], (a_it / kNA) & 1);
+    // ===================== MMA issuer (warp-uniform; one elected lane issues) =====================
+    uint32_t a_it = 0, b_it = 0, tile_it = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tile_it) {
+      for (int p = 0; p < P.Din; ++p) {
+        const PlaneInfo& pi = P.plane[p];
+        if (pi.nkd == 0) continue;
+        const int nkd = pi.nkd;
+        const uint32_t d_tmem = tmem_base + (uint32_t)pi.dmin * 64;
+        // Accumulators first touched by this plane must have been drained by the epilogue.
+        // (With an N-fused MMA the started accumulators need accumulate=1 and the new one 0, so
+        // the very first k-step of the plane is split into two instructions.)
+        const int jnew = pi.new_acc >= 0 ? pi.new_acc - pi.dmin : -1;  // tap index of the new accumulator
+        if (pi.new_acc >= 0) {
+          mbar_wait(&bar->acc_empty[pi.new_acc], (tile_it & 1) ^ 1);
+          tc_fence_after_sync();
+        }
+        const uint32_t idesc_all = umma_idesc_bf16(128, 64 * nkd);
+        bool first_step = true;
+        for (int c = 0; c < P.nchunk; ++c) {
+          for (int kw = 0; kw < 3; ++kw) {
+            const uint32_t sa = a_it % kNA;
+            mbar_wait(&bar->full_a[sa], (a_it / kNA) & 1);
+            tc_fence_after_sync();
+            const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
+            for (int kh = 0; kh < 3; ++kh) {
+              const uint32_t sb = b_it % kNB;
+              mbar_wait(&bar->full_b[sb], (b_it / kNB) & 1);
               tc_fence_after_sync();
-              const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
-              for (int kd = 0; kd < 3; ++kd) {
-                if (!(kd == 0 ? v0 : (kd == 1 ? v1 : v2))) continue;
-                const int dout = kd == 0 ? d0 : (kd == 1 ? d1 : d2);
-                if (!((started >> dout) & 1)) {
-                  // first touch of this accumulator in this tile: the epilogue must have drained it
-                  mbar_wait(&bar->acc_empty[dout], (tile_it & 1) ^ 1);
-                  tc_fence_after_sync();
+              const uint32_t b_addr = smem_u32(smem_b + sb * kBSlotBytes);
+              if (elect_one()) {
+                const uint64_t da0 = umma_desc_sw128(a_addr + kh * (kTileW * 128), 1024);
+                const uint64_t db0 = umma_desc_sw128(b_addr, 1024);
+                int k4 = 0;
+                if (first_step && jnew >= 0) {
+                  // split k-step: started accumulators (taps [0, jnew)) accumulate, the new one (tap jnew,
+                  // always the last tap of the plane) is overwritten
+                  if (jnew > 0) umma_bf16_ss(d_tmem, da0, db0, umma_idesc_bf16(128, 64 * jnew), 1);
+                  umma_bf16_ss(d_tmem + jnew * 64, da0, db0 + (uint64_t)((jnew * kBTapBytes) >> 4),
+                               umma_idesc_bf16(128, 64), 0);
+                  k4 = 1;
                 }
-                const uint32_t sb = b_it % kNB;
-                mbar_wait(&bar->full_b[sb], (b_it / kNB) & 1);
-                tc_fence_after_sync();
-                const uint32_t b_addr = smem_u32(smem_b + sb * kBBytes);
-                const uint32_t d_tmem = tmem_base + (uint32_t)dout * 64;
 #pragma unroll
-                for (int kh = 0; kh < 3; ++kh) {
-#pragma unroll
-                  for (int k4 = 0; k4 < 4; ++k4) {
-                    const uint64_t da = umma_desc_sw128(a_addr + kh * (kTileW * 128) + k4 * 32, 1024);
-                    const uint64_t db = umma_desc_sw128(b_addr + kh * kBTapBytes + k4 * 32, 1024);
-                    const uint32_t acc = (((started >> dout) & 1) | (uint32_t)(kh | k4)) != 0;
-                    umma_bf16_ss(d_tmem, da, db, idesc, acc);
-                  }
+                for (int k = 0; k < 4; ++k) {
+                  if (k >= k4) umma_bf16_ss(d_tmem, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc_all, 1);
                 }
-                started |= 1u << dout;
                 umma_commit(&bar->empty_b[sb]);
-                ++b_it;
-                // last contribution to this accumulator?
-                int plast = dout * P.stride_d - P.pad_d + 2;
-                if (plast > P.Din - 1) plast = P.Din - 1;
-                if (p == plast && c == P.nchunk - 1 && kw == 2) umma_commit(&bar->acc_full[dout]);
               }
-              umma_commit(&bar->empty_a[sa]);
-              ++a_it;
+              __syncwarp();
+              first_step = false;
+              ++b_it;
             }
+            if (elect_one()) umma_commit(&bar->empty_a[sa]);
+            __syncwarp();
+            ++a_it;
           }
         }
+        if (pi.done_mask != 0 && elect_one()) {
+          for (int d = 0; d < P.Dout; ++d)
+            if ((pi.done_mask >> d) & 1) umma_commit(&bar->acc_full[d]);
+        }
+        __syncwarp();
       }
     }
   } else {
@@ -258,9 +281,38 @@ __global__ void __launch_bounds__(kThreads, 1)
   }
 }
 
-// torch [64][cin][3][3][3] fp32 -> bf16 tiles [kd][chunk][kw][kh][n=64][k=64], 128B-swizzled rows.
-__global__ void __launch_bounds__(256) k_pack_weights(const float* __restrict__ w, int cin, uint8_t* __restrict__ packed) {
+// Weight image.  Depth taps are grouped into "kd classes" that can be valid for the same input plane:
+//   stride_d 1: one class {2,1,0};  stride_d 2: class 0 = {2,0} (planes with p+pad even), class 1 = {1}.
+// Layout: [class][chunk][kw][kh][j: kd descending][n = 64][k = 64] bf16, rows 128B-swizzled.
+struct KdClasses {
+  int n_classes;
+  int nkd[2];
+  int kd[2][3];
+  uint32_t base[2];  // byte offset of the class
+};
+
+__host__ __device__ inline KdClasses kd_classes(int stride_d, int cin) {
+  KdClasses k{};
+  const uint32_t per_tap = (uint32_t)(cin / 64) * 9 * kBTapBytes;
+  if (stride_d == 1) {
+    k.n_classes = 1;
+    k.nkd[0] = 3; k.kd[0][0] = 2; k.kd[0][1] = 1; k.kd[0][2] = 0;
+    k.base[0] = 0;
+  } else {
+    k.n_classes = 2;
+    k.nkd[0] = 2; k.kd[0][0] = 2; k.kd[0][1] = 0;
+    k.nkd[1] = 1; k.kd[1][0] = 1;
+    k.base[0] = 0;
+    k.base[1] = 2 * per_tap;
+  }
+  return k;
+}
+
+// torch [64][cin][3][3][3] fp32 -> the image above.
+__global__ void __launch_bounds__(256)
+    k_pack_weights(const float* __restrict__ w, int cin, int stride_d, uint8_t* __restrict__ packed) {
   const int nchunk = cin / 64;
+  const KdClasses kc = kd_classes(stride_d, cin);
   const int total = 27 * cin * 64;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     int r = i;
@@ -270,11 +322,54 @@ __global__ void __launch_bounds__(256) k_pack_weights(const float* __restrict__ 
     const int kw = r % 3; r /= 3;
     const int c = r % nchunk; r /= nchunk;
     const int kd = r;
+    int cls = 0, j = 0;
+    for (int a = 0; a < kc.n_classes; ++a)
+      for (int q = 0; q < kc.nkd[a]; ++q)
+        if (kc.kd[a][q] == kd) { cls = a; j = q; }
     const float v = w[((((size_t)n * cin + (c * 64 + k)) * 3 + kd) * 3 + kh) * 3 + kw];
-    const size_t tile = (size_t)(((kd * nchunk + c) * 3 + kw) * 3 + kh) * kBTapBytes;
+    const size_t tile = kc.base[cls] + ((size_t)(((c * 3 + kw) * 3 + kh) * kc.nkd[cls] + j)) * kBTapBytes;
     const size_t off = tile + (size_t)n * 128 + ((((k >> 3) ^ (n & 7)) << 4) | ((k & 7) << 1));
     *reinterpret_cast<__nv_bfloat16*>(packed + off) = __float2bfloat16_rn(v);
   }
+}
+
+// Per-plane schedule: which taps are valid, where their weights sit, which accumulators start/finish.
+int plan_planes(ConvParams& P, int cin, int stride_d, int pad_d) {
+  const KdClasses kc = kd_classes(stride_d, cin);
+  int first_plane[kMaxDout], last_plane[kMaxDout];
+  for (int d = 0; d < P.Dout; ++d) { first_plane[d] = -1; last_plane[d] = -1; }
+  for (int p = 0; p < P.Din; ++p) {
+    PlaneInfo& pi = P.plane[p];
+    pi = PlaneInfo{0, 0, -1, 0, 0, 0};
+    const int cls = stride_d == 1 ? 0 : (((p + pad_d) % 2 == 0) ? 0 : 1);
+    int jfirst = -1, jlast = -1, dmin = 0;
+    for (int j = 0; j < kc.nkd[cls]; ++j) {  // kd descending -> d ascending
+      const int num = p + pad_d - kc.kd[cls][j];
+      if (num < 0 || num % stride_d != 0) continue;
+      const int d = num / stride_d;
+      if (d >= P.Dout) continue;
+      if (jfirst < 0) { jfirst = j; dmin = d; }
+      if (jlast >= 0 && j != jlast + 1) return -1;  // taps must be contiguous
+      jlast = j;
+      if (d != dmin + (j - jfirst)) return -1;      // and feed consecutive depths
+      if (first_plane[d] < 0) first_plane[d] = p;
+      last_plane[d] = p;
+    }
+    if (jfirst < 0) continue;
+    pi.nkd = jlast - jfirst + 1;
+    pi.dmin = dmin;
+    pi.woff = kc.base[cls] + (uint32_t)jfirst * kBTapBytes;
+    pi.wstride = (uint32_t)kc.nkd[cls] * kBTapBytes;
+  }
+  for (int d = 0; d < P.Dout; ++d) {
+    if (first_plane[d] < 0) return -1;
+    PlaneInfo& pf = P.plane[first_plane[d]];
+    if (pf.new_acc >= 0) return -1;                      // at most one new accumulator per plane
+    if (d != pf.dmin + pf.nkd - 1) return -1;            // and it is the plane's last tap
+    pf.new_acc = d;
+    P.plane[last_plane[d]].done_mask |= 1 << d;
+  }
+  return 0;
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
@@ -305,11 +400,12 @@ size_t vn_conv3d_packed_weight_bytes(int32_t cin) {
   return (size_t)27 * cin * 64 * 2;
 }
 
-int vn_conv3d_pack_weights(const float* weight, int32_t cin, void* packed, vn_stream_t stream) {
+int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, void* packed, vn_stream_t stream) {
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d_pack_weights: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(stride_d == 1 || stride_d == 2, "conv3d_pack_weights: stride_d=%d (supported: 1, 2)", stride_d);
   VN_REQUIRE(weight != nullptr && packed != nullptr, "conv3d_pack_weights: null pointer");
   VN_REQUIRE((reinterpret_cast<uintptr_t>(packed) & 15) == 0, "conv3d_pack_weights: packed must be 16-byte aligned");
-  k_pack_weights<<<sm_count() * 4, 256, 0, as_stream(stream)>>>(weight, cin, reinterpret_cast<uint8_t*>(packed));
+  k_pack_weights<<<sm_count() * 4, 256, 0, as_stream(stream)>>>(weight, cin, stride_d, reinterpret_cast<uint8_t*>(packed));
   VN_LAUNCH_CHECK("k_pack_weights");
   return VN_OK;
 }
@@ -324,6 +420,7 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
              stride_d, pad_d);
   VN_REQUIRE(out_mode == 0 || out_mode == 1, "conv3d: out_mode=%d", out_mode);
   VN_REQUIRE(W % kTileW == 0, "conv3d: W=%d must be a multiple of %d", W, kTileW);
+  VN_REQUIRE(Din <= kMaxPlanes, "conv3d: Din=%d exceeds %d", Din, kMaxPlanes);
   const int Dout = (Din + 2 * pad_d - 3) / stride_d + 1;
   VN_REQUIRE(Din + 2 * pad_d >= 3 && Dout >= 1 && Dout <= kMaxDout, "conv3d: Dout=%d outside [1,%d]", Dout, kMaxDout);
   VN_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(packed_weight) & 15) == 0 &&
@@ -352,7 +449,6 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
   ConvParams P{};
   P.B = B; P.Din = Din; P.Dout = Dout; P.H = H; P.W = W;
   P.nchunk = cin / 64;
-  P.stride_d = stride_d; P.pad_d = pad_d;
   P.tiles_h = (H + kTileH - 1) / kTileH;
   P.tiles_w = W / kTileW;
   P.n_tiles = B * P.tiles_h * P.tiles_w;
@@ -360,6 +456,10 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
   P.wpack = reinterpret_cast<const uint8_t*>(packed_weight);
   P.scale = scale; P.shift = shift;
   P.out = y;
+  if (plan_planes(P, cin, stride_d, pad_d) != 0) {
+    set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
+    return VN_ERR_UNSUPPORTED;
+  }
 
   VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
   const int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();

@@ -122,7 +122,7 @@ class ConvMD(nn.Module):
         w = self.conv.weight
         key = (w.data_ptr(), w._version, w.device)
         if self._packed is None or self._packed_key != key:
-            self._packed = ops.conv3d_pack_weights(w)
+            self._packed = ops.conv3d_pack_weights(w, self.stride[0])
             self._packed_key = key
         scale, bn_shift = _fold_bn(self.batch_norm)
         shift = (self.conv.bias.detach().double() * scale.double() + bn_shift.double()).float().contiguous()

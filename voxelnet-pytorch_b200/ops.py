@@ -180,8 +180,9 @@ def scatter_dense_bf16(voxelwise, coords, dense, clear: bool = False, n_voxels_d
 # ---------------------------------------------------------------------------------------------
 # Conv3d middle
 # ---------------------------------------------------------------------------------------------
-def conv3d_pack_weights(weight) -> torch.Tensor:
-    """torch (64,cin,3,3,3) f32 -> packed bf16 tile image (see vn_conv3d.cu)."""
+def conv3d_pack_weights(weight, stride_d: int) -> torch.Tensor:
+    """torch (64,cin,3,3,3) f32 -> packed bf16 tile image for a layer with depth stride `stride_d`
+    (see vn_conv3d.cu)."""
     _require_cuda(weight)
     w = _contig(weight.detach(), torch.float32)
     cout, cin = w.shape[0], w.shape[1]
@@ -192,7 +193,7 @@ def conv3d_pack_weights(weight) -> torch.Tensor:
         raise RuntimeError("conv3d kernel supports cin in {64,128}; got %d" % cin)
     packed = torch.empty(nbytes // 2, dtype=torch.bfloat16, device=w.device)
     with torch.cuda.device(w.device):
-        check(_cabi.lib().vn_conv3d_pack_weights(_ptr(w), cin, _ptr(packed), _stream()), "vn_conv3d_pack_weights")
+        check(_cabi.lib().vn_conv3d_pack_weights(_ptr(w), cin, stride_d, _ptr(packed), _stream()), "vn_conv3d_pack_weights")
     return packed
 
 

@@ -19,6 +19,50 @@ from .model import FeatureLearningNet, MiddleConvNet
 from .utils import VoxelBatch, pack_frames
 
 
+class StageTimer:
+    """CUDA-event stopwatch around the stages of `forward_points` (events are recorded on the
+    launching stream; reading them is deferred to `summary()`, after a synchronize)."""
+
+    def __init__(self):
+        self.records = []  # (stage, start_event, end_event)
+
+    def span(self, stage: str):
+        return _Span(self, stage)
+
+    def summary(self) -> dict:
+        """stage -> (mean ms per recorded span, spans)."""
+        acc = {}
+        for stage, e0, e1 in self.records:
+            t, n = acc.get(stage, (0.0, 0))
+            acc[stage] = (t + e0.elapsed_time(e1), n + 1)
+        return {k: (t / n, n) for k, (t, n) in acc.items()}
+
+
+class _Span:
+    def __init__(self, timer, stage):
+        self.timer, self.stage = timer, stage
+
+    def __enter__(self):
+        self.e0 = torch.cuda.Event(enable_timing=True)
+        self.e1 = torch.cuda.Event(enable_timing=True)
+        self.e0.record()
+
+    def __exit__(self, *exc):
+        self.e1.record()
+        self.timer.records.append((self.stage, self.e0, self.e1))
+
+
+class _NoSpan:
+    def __enter__(self):
+        return None
+
+    def __exit__(self, *exc):
+        return False
+
+
+_NO_SPAN = _NoSpan()
+
+
 class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
                  voxels_per_frame_capacity: int = 32768):
@@ -66,23 +110,32 @@ class VoxelNetFrontEnd:
         self.capacity = cap
         self._shape = shape
 
-    def forward_points(self, points: torch.Tensor, frame_offsets: torch.Tensor, max_points_per_frame: int) -> torch.Tensor:
+    def forward_points(self, points: torch.Tensor, frame_offsets: torch.Tensor, max_points_per_frame: int,
+                       timer: StageTimer = None) -> torch.Tensor:
         """points (N,4) f32 cuda (frames concatenated), frame_offsets (B+1,) i32 cuda ->
         (B,128,H,W) f32.  The returned tensor is an internal buffer reused by the next call."""
         n_frames = frame_offsets.numel() - 1
         self._ensure_buffers(n_frames, points.shape[0], points.device)
         vb = self.voxels
-        ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
-        ops.voxelize_fill(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, vb.feature,
-                          vb.coordinate, vb.number, self.workspace)
+        span = timer.span if timer is not None else (lambda stage: _NO_SPAN)
+        with span("voxelize"):
+            ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
+            ops.voxelize_fill(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, vb.feature,
+                              vb.coordinate, vb.number, self.workspace)
         k_dev = vb.n_voxels_dev
-        ops.svfe_fused_fwd(vb.feature, self._p1, self._p2, out=self.voxelwise, n_voxels_dev=k_dev)
-        ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
+        with span("svfe"):
+            ops.svfe_fused_fwd(vb.feature, self._p1, self._p2, out=self.voxelwise, n_voxels_dev=k_dev)
+        with span("scatter"):
+            ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
-        ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1)
-        ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
-        ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2)
-        ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out)
+        with span("conv1"):
+            ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1)
+        with span("unscatter"):
+            ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+        with span("conv2"):
+            ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2)
+        with span("conv3"):
+            ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out)
         return self.out
 
     # kernels enqueued by one forward_points call (for bench.py's gpu_launches)
