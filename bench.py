@@ -61,7 +61,7 @@ def load_peaks():
 class ClockSampler:
     """nvidia-smi clock / throttle sampler running during the timed region."""
 
-    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    Q = "timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index: int):
         self.index, self.proc, self.lines = index, None, []
@@ -69,7 +69,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "50"],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
@@ -80,40 +80,52 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.lines.append(line.strip())
 
-    def stop(self) -> dict:
+    @staticmethod
+    def _epoch(ts: str):
+        import datetime
+
+        try:
+            return datetime.datetime.strptime(ts.strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+        except ValueError:
+            return None
+
+    def stop(self, t0: float = None, t1: float = None) -> dict:
+        """Summary of the samples taken in the wall-clock window [t0, t1] (all samples if the
+        window is empty or timestamps are unparseable)."""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
-        time.sleep(0.15)
+        time.sleep(0.1)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=2)
         except Exception:
             self.proc.kill()
-        sm, mx, pw, reasons = [], [], [], set()
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        rows = []
         for ln in self.lines:
             parts = [p.strip() for p in ln.split(",")]
-            if len(parts) < 7:
+            if len(parts) < 8:
                 continue
             try:
-                sm.append(float(parts[0])); mx.append(float(parts[1])); pw.append(float(parts[2]))
+                rows.append((self._epoch(parts[0]), float(parts[1]), float(parts[2]), float(parts[3]),
+                             [n for n, v in zip(names, parts[4:8]) if v.lower().startswith("active")]))
             except ValueError:
                 continue
-            for n, v in zip(names, parts[3:7]):
-                if v.lower().startswith("active"):
-                    reasons.add(n)
-        if not sm:
+        inside = [r for r in rows if t0 is not None and r[0] is not None and t0 <= r[0] <= t1]
+        use = inside if inside else rows
+        if not use:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
-        # samples under load = upper half of the observed clocks' power draw
-        return {"sm_mhz": statistics.median(sm), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm),
-                "reasons": sorted(reasons)}
+        reasons = sorted({n for r in use for n in r[4]})
+        return {"sm_mhz": statistics.median(r[1] for r in use), "sm_max_mhz": max(r[2] for r in use),
+                "power_w_max": max(r[3] for r in use), "samples": len(use), "window": "timed region" if inside else "whole run",
+                "reasons": reasons}
 
 
-def make_frames(cfg_name, rank, batch):
+def make_frames(cfg_name, rank, batch, seed=None):
     from voxelnet_pytorch_b200 import synth
 
     _, _, kw, _ = CONFIGS[cfg_name]
-    return synth.lidar_batch(batch, seed0=1000 * rank, **kw)
+    return synth.lidar_batch(batch, seed0=1000 * rank if seed is None else seed, **kw)
 
 
 def cpu_reference_sample(target, frames, sd, seconds_budget=20.0, max_frames=None):
@@ -174,7 +186,7 @@ def run_reference(args, rank, world):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=50)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--config", default="car16", choices=sorted(CONFIGS))
@@ -207,8 +219,15 @@ def main():
     from voxelnet_pytorch_b200.pipeline import StageTimer
 
     target, batch_cfg, _, desc = CONFIGS[args.config]
-    batch = batch_cfg if args.config != "stress64" else max(64 // world, 1)
-    frames = make_frames(args.config, rank, batch)
+    if args.config == "stress64":  # strong-scaling stress: 64 frames in total, frame i -> rank i mod world
+        from voxelnet_pytorch_b200 import sharding as _sh
+
+        mine = _sh.shard_frames(64, rank, world)
+        batch = len(mine)
+        frames = [make_frames(args.config, 0, 1, seed=1000 + i)[0] for i in mine]
+    else:
+        batch = batch_cfg
+        frames = make_frames(args.config, rank, batch)
 
     torch.manual_seed(0)
     fnet = vn.FeatureLearningNet(target).eval()
@@ -247,9 +266,12 @@ def main():
     torch.cuda.synchronize()
     counts = fe.voxel_counts()  # also checks the voxel capacity
     sampler = ClockSampler(local_rank)
+    sampler.start()
+    for _ in range(2):  # keep the GPU busy while nvidia-smi spins up
+        fe.forward_points(points, offsets, max_n)
     timer = StageTimer()
     barrier()
-    sampler.start()
+    wall0 = time.time()
     launches0 = _cabi.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
@@ -257,8 +279,9 @@ def main():
         fe.forward_points(points, offsets, max_n, timer=timer)
     e1.record()
     barrier()
+    wall1 = time.time()
     launches = _cabi.launch_count() - launches0
-    clocks = sampler.stop()
+    clocks = sampler.stop(wall0, wall1)
     ms_total = e0.elapsed_time(e1)
 
     # ---- end to end: host buffers in, voxel counts out ---------------------------------------------
@@ -283,10 +306,10 @@ def main():
     barrier()
     ms_e2e = f0.elapsed_time(f1)
 
-    if world > 1:
-        t = torch.tensor([ms_total, ms_e2e], dtype=torch.float64, device=dev)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_total, ms_e2e = float(t[0]), float(t[1])
+    from voxelnet_pytorch_b200 import sharding
+
+    ms_total, ms_e2e = sharding.reduce_max([ms_total, ms_e2e])  # device time, max over ranks
+    frames_total = sum(sharding.gather_ints(batch))
 
     stages = {k: v[0] for k, v in timer.summary().items()}
 
@@ -295,7 +318,6 @@ def main():
         c = fe.cfg
         flops = conv_flops_per_frame(c.depth, c.height, c.width)
         ms_step = ms_total / args.steps
-        frames_total = batch * world
         value = frames_total / (ms_step * 1e-3)
         conv1_ms = stages.get("conv1", float("nan"))
         achieved = flops[0] * batch / (conv1_ms * 1e-3) / 1e12
@@ -315,7 +337,7 @@ def main():
             v["frac"] = v["achieved"] / v["peak"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.config == "stress64" else "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": desc, "name": args.config, "batch_per_gpu": batch, "points_per_batch": N_total,
                        "voxels_per_batch": K_total, "l2_policy": "working set (%.1f GB dense grid + activations) exceeds L2" % (fe.dense.numel() * 2 / 1e9),
