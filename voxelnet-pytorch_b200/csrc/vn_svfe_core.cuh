@@ -1,0 +1,131 @@
+// Per-warp evaluation of the stacked VFE for ONE voxel whose rows sit in shared memory.
+// Shared by k_svfe_fused (rows staged from a materialised [K,T,7] feature buffer) and by
+// k_vox_svfe_fused (rows built straight from the voxelizer's point buckets), so both paths run
+// the same instruction sequence and produce identical bits.
+//
+// Reference semantics (voxelnet/model.py:74-82, 95-100):
+//   pointwise = relu(W x + b) * s + t          Linear -> ReLU -> eval BatchNorm folded
+//   agg       = max over ALL T rows (pad rows included, no mask)
+//   out       = concat(pointwise, agg) * mask   mask = (max_j x_j != 0)
+//   voxelwise = max over t of the masked VFE-2 output
+// Rows that are bit-identical (the reference's pad rows) are passed once: max() ignores multiplicity.
+#pragma once
+
+#include "vn_common.cuh"
+
+namespace vn {
+
+struct Vfe1Params {
+  float w[16 * 7];
+  float b[16], s[16], t[16];
+};
+
+struct Vfe2Lane {  // VFE-2 parameters of the two output units (lane, lane + 32) owned by one lane
+  float wa[32], wb[32];
+  float ba, bb, sa, sb, ta, tb;
+};
+
+__device__ __forceinline__ void load_vfe1_params(Vfe1Params& p1, const float* w1, const float* b1, const float* s1,
+                                                 const float* t1) {
+  for (int i = threadIdx.x; i < 16 * 7; i += blockDim.x) p1.w[i] = w1[i];
+  if (threadIdx.x < 16) {
+    p1.b[threadIdx.x] = b1[threadIdx.x];
+    p1.s[threadIdx.x] = s1[threadIdx.x];
+    p1.t[threadIdx.x] = t1[threadIdx.x];
+  }
+}
+
+__device__ __forceinline__ void load_vfe2_lane(Vfe2Lane& q, const float* w2, const float* b2, const float* s2,
+                                               const float* t2, uint32_t lane) {
+#pragma unroll
+  for (int k = 0; k < 32; ++k) {
+    q.wa[k] = w2[lane * 32 + k];
+    q.wb[k] = w2[(lane + 32) * 32 + k];
+  }
+  q.ba = b2[lane];  q.bb = b2[lane + 32];
+  q.sa = s2[lane];  q.sb = s2[lane + 32];
+  q.ta = t2[lane];  q.tb = t2[lane + 32];
+}
+
+// rows: shared memory, 7 floats per row.  Evaluated row r (0 <= r < R) is source row
+// (r < nu ? r : tlast).  x1: shared scratch of (R + 1) x 32 floats; row `aggrow` holds agg1.
+// dst: 128 floats in global memory.
+__device__ __forceinline__ void svfe_eval_voxel(const float* rows, int nu, int R, int tlast, float (*x1)[32], int aggrow,
+                                                const Vfe1Params& p1, const Vfe2Lane& q, float* dst, uint32_t lane) {
+  // ---- mask bits: bit r set <=> evaluated row r has max_j != 0 --------------------------------
+  uint64_t on_bits = 0;
+  for (int r0 = 0; r0 < R; r0 += 32) {
+    const int r = r0 + lane;
+    bool on = false;
+    if (r < R) {
+      const float* f = rows + (r < nu ? r : tlast) * 7;
+      float mx = f[0];
+#pragma unroll
+      for (int j = 1; j < 7; ++j) mx = fmaxf(mx, f[j]);
+      on = mx != 0.0f;
+    }
+    on_bits |= (uint64_t)__ballot_sync(0xffffffffu, on) << r0;
+  }
+  // ---- VFE-1: (row, unit) pairs spread over the lanes ----------------------------------------
+  for (int e = lane; e < R * 16; e += 32) {
+    const int r = e >> 4, u = e & 15;
+    const float* f = rows + (r < nu ? r : tlast) * 7;
+    float a = p1.b[u];
+#pragma unroll
+    for (int j = 0; j < 7; ++j) a = fmaf(p1.w[u * 7 + j], f[j], a);
+    x1[r][u] = fmaxf(a, 0.0f) * p1.s[u] + p1.t[u];
+  }
+  __syncwarp();
+  if (lane < 16) {  // agg1[u] = max over evaluated rows (== max over all T rows)
+    float a = x1[0][lane];
+    for (int r = 1; r < R; ++r) a = fmaxf(a, x1[r][lane]);
+    x1[aggrow][lane] = a;
+  }
+  __syncwarp();
+  // concat + mask: rows with mask 0 become all-zero inputs of VFE-2
+  for (int e = lane; e < R * 32; e += 32) {
+    const int r = e >> 5, c = e & 31;
+    const bool on = (on_bits >> r) & 1;
+    const float val = c < 16 ? x1[r][c] : x1[aggrow][c - 16];
+    x1[r][c] = on ? val : 0.0f;
+  }
+  __syncwarp();
+  // ---- VFE-2: lane <-> units (lane, lane + 32); rows broadcast from shared memory -----------------
+  float all_a = -INFINITY, all_b = -INFINITY;  // max over all rows (the reference's `agg`)
+  float on_a = -INFINITY, on_b = -INFINITY;    // max over rows with mask 1 of the pointwise part
+  for (int r = 0; r < R; ++r) {
+    float a = q.ba, b = q.bb;
+    const float4* xr = reinterpret_cast<const float4*>(x1[r]);
+#pragma unroll
+    for (int k4 = 0; k4 < 8; ++k4) {
+      const float4 x = xr[k4];
+      a = fmaf(q.wa[4 * k4 + 0], x.x, a);
+      b = fmaf(q.wb[4 * k4 + 0], x.x, b);
+      a = fmaf(q.wa[4 * k4 + 1], x.y, a);
+      b = fmaf(q.wb[4 * k4 + 1], x.y, b);
+      a = fmaf(q.wa[4 * k4 + 2], x.z, a);
+      b = fmaf(q.wb[4 * k4 + 2], x.z, b);
+      a = fmaf(q.wa[4 * k4 + 3], x.w, a);
+      b = fmaf(q.wb[4 * k4 + 3], x.w, b);
+    }
+    a = fmaxf(a, 0.0f) * q.sa + q.ta;
+    b = fmaxf(b, 0.0f) * q.sb + q.tb;
+    all_a = fmaxf(all_a, a);
+    all_b = fmaxf(all_b, b);
+    if ((on_bits >> r) & 1) {
+      on_a = fmaxf(on_a, a);
+      on_b = fmaxf(on_b, b);
+    }
+  }
+  // voxelwise[c] = max_t(mask_t * out2[t][c]): rows with mask 0 contribute exactly 0
+  const uint64_t evaluated = R >= 64 ? ~0ull : ((1ull << R) - 1ull);
+  const bool any_on = on_bits != 0;
+  const bool any_off = (on_bits & evaluated) != evaluated;
+  const float floor0 = any_off ? 0.0f : -INFINITY;
+  dst[lane] = fmaxf(any_on ? on_a : -INFINITY, floor0);
+  dst[lane + 32] = fmaxf(any_on ? on_b : -INFINITY, floor0);
+  dst[lane + 64] = fmaxf(any_on ? all_a : -INFINITY, floor0);
+  dst[lane + 96] = fmaxf(any_on ? all_b : -INFINITY, floor0);
+}
+
+}  // namespace vn

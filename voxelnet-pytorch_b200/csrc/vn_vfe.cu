@@ -1,19 +1,12 @@
 // Stacked voxel feature encoder kernels: the replacement for VFELayer.forward (reference
 // voxelnet/model.py:74-82) and for the VFE part of FeatureLearningNet.forward (model.py:95-100).
 //
-// Semantics restated from the reference:
-//   pointwise = BN1d(ReLU(Linear(x)))           Linear -> ReLU -> BN, eval-mode BN folded into
-//                                               y = relu(Wx + b) * s + t
-//   agg       = max over ALL T rows of pointwise (pad rows included, no mask)
-//   out       = concat(pointwise, agg) * mask    mask[k,t] = (max_j feature[k,t,j] != 0)
-//   voxelwise = max over t of the masked VFE-2 output
-//
 // k_svfe_fused keeps one voxel per warp entirely on chip: the [T,7] block is staged in shared
-// memory, VFE-1 is evaluated with one row per lane, VFE-2 with two output units per lane and its
-// 64x32 weights held in registers, and only the 128 voxel-wise maxima are written.  Rows at the
-// tail of a voxel that are bit-identical to its last row (the reference's pad rows are all
-// [0,0,0,0,-cx,-cy,-cz]) are evaluated once: max() ignores multiplicity, so this is exact.
-#include "vn_common.cuh"
+// memory, rows at the tail of a voxel that are bit-identical to its last row (the reference's pad
+// rows are all [0,0,0,0,-cx,-cy,-cz]) are evaluated once (exact: max() ignores multiplicity), and
+// the per-voxel arithmetic is the shared svfe_eval_voxel() of vn_svfe_core.cuh.  Only the 128
+// voxel-wise maxima are written.  k_vfe_layer is the drop-in per-layer kernel.
+#include "vn_svfe_core.cuh"
 
 namespace vn {
 namespace {
@@ -21,18 +14,8 @@ namespace {
 constexpr int kMaxT = 64;
 constexpr int kWarps = 8;
 
-struct Vfe1Params {  // small enough to travel as a kernel argument (constant bank, uniform reads)
-  float w[16][7];
-  float b[16], s[16], t[16];
-};
-
-__device__ __forceinline__ float warp_max(float v) {
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, d));
-  return v;
-}
-
-__global__ void __launch_bounds__(kWarps * 32)
+// 2 blocks of 8 warps per SM: the 64 VFE-2 weights per lane live in registers (<= 128 regs/thread).
+__global__ void __launch_bounds__(kWarps * 32, 2)
     k_svfe_fused(const float* __restrict__ feature, int64_t K, int T, const int32_t* __restrict__ n_voxels_dev,
                  const float* __restrict__ w1, const float* __restrict__ b1, const float* __restrict__ s1,
                  const float* __restrict__ t1, const float* __restrict__ w2, const float* __restrict__ b2,
@@ -42,23 +25,9 @@ __global__ void __launch_bounds__(kWarps * 32)
   __shared__ Vfe1Params p1;
   const int in_ld = (T * 7 + 3) & ~3;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  for (int i = threadIdx.x; i < 16 * 7; i += blockDim.x) p1.w[i / 7][i % 7] = w1[i];
-  if (threadIdx.x < 16) {
-    p1.b[threadIdx.x] = b1[threadIdx.x];
-    p1.s[threadIdx.x] = s1[threadIdx.x];
-    p1.t[threadIdx.x] = t1[threadIdx.x];
-  }
-
-  // VFE-2 weights for this lane's two units (lane, lane + 32): 64 registers.
-  float wa[32], wb[32];
-#pragma unroll
-  for (int k = 0; k < 32; ++k) {
-    wa[k] = w2[lane * 32 + k];
-    wb[k] = w2[(lane + 32) * 32 + k];
-  }
-  const float ba = b2[lane], bb = b2[lane + 32];
-  const float sa = s2[lane], sb = s2[lane + 32];
-  const float ta = t2[lane], tb = t2[lane + 32];
+  load_vfe1_params(p1, w1, b1, s1, t1);
+  Vfe2Lane q;
+  load_vfe2_lane(q, w2, b2, s2, t2, lane);
   __syncthreads();
 
   int64_t total = K;
@@ -73,7 +42,6 @@ __global__ void __launch_bounds__(kWarps * 32)
     const float* src = feature + v * (int64_t)(T * 7);
     for (int e = lane; e < T * 7; e += 32) in[e] = src[e];
     __syncwarp();
-
     // Unique-row analysis: rows [nu, T) are bit-identical to row T-1.
     int nu = 0;  // 1 + index of the last row that differs from row T-1
     for (int t0 = 0; t0 < T; t0 += 32) {
@@ -88,86 +56,7 @@ __global__ void __launch_bounds__(kWarps * 32)
       if (b) nu = t0 + 32 - __clz(b);
     }
     const int R = nu < T ? nu + 1 : T;  // rows to evaluate: 0..nu-1 and (if any) the tail row T-1
-
-    // ---- VFE-1: lane <-> row.  x1[r][0:16] = pointwise, mask kept in a register bit set ----
-    uint64_t on_bits = 0;  // bit r set <=> evaluated row r has mask == 1
-    for (int r0 = 0; r0 < R; r0 += 32) {
-      const int r = r0 + lane;
-      bool on = false;
-      if (r < R) {
-        const int t = r < nu ? r : T - 1;
-        float f[7];
-#pragma unroll
-        for (int j = 0; j < 7; ++j) f[j] = in[t * 7 + j];
-        float mx = f[0];
-#pragma unroll
-        for (int j = 1; j < 7; ++j) mx = fmaxf(mx, f[j]);
-        on = mx != 0.0f;
-#pragma unroll
-        for (int u = 0; u < 16; ++u) {
-          float a = p1.b[u];
-#pragma unroll
-          for (int j = 0; j < 7; ++j) a = fmaf(p1.w[u][j], f[j], a);
-          x1[r][u] = fmaxf(a, 0.0f) * p1.s[u] + p1.t[u];
-        }
-      }
-      const uint32_t b = __ballot_sync(0xffffffffu, on);
-      on_bits |= (uint64_t)b << r0;
-    }
-    __syncwarp();
-    // agg1[u] = max over evaluated rows (== max over all T rows); lanes 0..15 own unit u.
-    if (lane < 16) {
-      float a = x1[0][lane];
-      for (int r = 1; r < R; ++r) a = fmaxf(a, x1[r][lane]);
-      x1[T][lane] = a;
-    }
-    __syncwarp();
-    // concat + mask: rows with mask 0 become all-zero inputs of VFE-2
-    for (int e = lane; e < R * 32; e += 32) {
-      const int r = e >> 5, c = e & 31;
-      const bool on = (on_bits >> r) & 1;
-      const float val = c < 16 ? x1[r][c] : x1[T][c - 16];
-      x1[r][c] = on ? val : 0.0f;
-    }
-    __syncwarp();
-
-    // ---- VFE-2: lane <-> units (lane, lane+32); rows broadcast from shared memory ----
-    float all_a = -INFINITY, all_b = -INFINITY;  // max over all rows (the reference's `agg`)
-    float on_a = -INFINITY, on_b = -INFINITY;    // max over rows with mask 1 of the pointwise part
-    for (int r = 0; r < R; ++r) {
-      float a = ba, b = bb;
-      const float4* xr = reinterpret_cast<const float4*>(x1[r]);
-#pragma unroll
-      for (int q = 0; q < 8; ++q) {
-        const float4 x = xr[q];
-        a = fmaf(wa[4 * q + 0], x.x, a);
-        b = fmaf(wb[4 * q + 0], x.x, b);
-        a = fmaf(wa[4 * q + 1], x.y, a);
-        b = fmaf(wb[4 * q + 1], x.y, b);
-        a = fmaf(wa[4 * q + 2], x.z, a);
-        b = fmaf(wb[4 * q + 2], x.z, b);
-        a = fmaf(wa[4 * q + 3], x.w, a);
-        b = fmaf(wb[4 * q + 3], x.w, b);
-      }
-      a = fmaxf(a, 0.0f) * sa + ta;
-      b = fmaxf(b, 0.0f) * sb + tb;
-      all_a = fmaxf(all_a, a);
-      all_b = fmaxf(all_b, b);
-      if ((on_bits >> r) & 1) {
-        on_a = fmaxf(on_a, a);
-        on_b = fmaxf(on_b, b);
-      }
-    }
-    // voxelwise[c] = max_t(mask_t * out2[t][c]): rows with mask 0 contribute exactly 0.
-    const uint64_t evaluated = R >= 64 ? ~0ull : ((1ull << R) - 1ull);
-    const bool any_on = on_bits != 0;
-    const bool any_off = (on_bits & evaluated) != evaluated;
-    const float floor0 = any_off ? 0.0f : -INFINITY;
-    float* dst = voxelwise + v * 128;
-    dst[lane] = fmaxf(any_on ? on_a : -INFINITY, floor0);
-    dst[lane + 32] = fmaxf(any_on ? on_b : -INFINITY, floor0);
-    dst[lane + 64] = fmaxf(any_on ? all_a : -INFINITY, floor0);
-    dst[lane + 96] = fmaxf(any_on ? all_b : -INFINITY, floor0);
+    svfe_eval_voxel(in, nu, R, T - 1, x1, T, p1, q, voxelwise + v * 128, lane);
     __syncwarp();
   }
 }
