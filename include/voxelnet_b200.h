@@ -118,6 +118,20 @@ int vn_svfe_fused_fwd(const float* feature, int64_t K, int32_t T, const int32_t*
                       const float* w2 /* [64,32] */, const float* b2, const float* s2,
                       const float* t2, float* voxelwise /* [K,128] */, vn_stream_t stream);
 
+/* Fully fused fast path: phase 2 of the voxelizer and the stacked VFE in one kernel.  After
+ * vn_voxelize_index, builds each voxel's distinct feature rows on chip (first-T selection, fp64
+ * centroid - utils.py:78-88) and evaluates VFE-1 -> VFE-2 -> voxel-wise max on them (model.py:95-100),
+ * writing voxelwise [max_voxels,128] f32 and coordinate_buffer [max_voxels,4] i64 (number_buffer may
+ * be NULL).  The [K,T,7] feature buffer is never materialised; results are bit-identical to
+ * vn_voxelize_fill followed by vn_svfe_fused_fwd. */
+int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                           int32_t n_frames, int64_t n_points_total, const int32_t* voxel_offsets,
+                           int64_t max_voxels, const float* w1, const float* b1, const float* s1,
+                           const float* t1, const float* w2, const float* b2, const float* s2,
+                           const float* t2, float* voxelwise, int64_t* coordinate_buffer,
+                           int64_t* number_buffer, void* workspace, size_t workspace_bytes,
+                           vn_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * Sparse -> dense - replaces torch.sparse.FloatTensor(coords.t(), voxelwise, [B,D,H,W,128])
  * .to_dense() (voxelnet/model.py:102-106).  Layout of `dense`: [B, D, H, W, C] contiguous.

@@ -9,14 +9,14 @@ from tests.helpers import load_state, oracle_batch, rel_max_err, synth_frames
 pytestmark = pytest.mark.gpu
 
 
-def _build(cuda_device, target, sd):
+def _build(cuda_device, target, sd, **kw):
     import voxelnet_pytorch_b200 as vn
 
     fnet = vn.FeatureLearningNet(target).eval()
     mnet = vn.MiddleConvNet().eval()
     load_state(fnet, sd, "")
     load_state(mnet, sd, "")
-    return vn.VoxelNetFrontEnd(fnet.to(cuda_device), mnet.to(cuda_device), target)
+    return vn.VoxelNetFrontEnd(fnet.to(cuda_device), mnet.to(cuda_device), target, **kw)
 
 
 def test_front_end_matches_oracle_ped(cuda_device):
@@ -51,3 +51,48 @@ def test_front_end_car_shapes_and_determinism(cuda_device):
     assert a.shape == (2, 128, 400, 352)
     assert torch.equal(a, b)
     assert bool(torch.isfinite(a).all())
+
+
+@pytest.mark.parametrize("target", ["Car", "Pedestrian"])
+def test_fused_voxel_svfe_is_bit_identical_to_materialised_path(cuda_device, target):
+    """vn_voxelize_svfe_fused (no feature buffer) == vn_voxelize_fill + vn_svfe_fused_fwd, bit for bit,
+    and both match the oracle; coordinates / counts identical."""
+    import voxelnet_pytorch_b200 as vn
+    from voxelnet_pytorch_b200 import _cabi, ops
+
+    sd = OM.random_state_dict(13)
+    frames = synth_frames(3, 60)
+    frames[1] = frames[1][:5000]
+    # a voxel with > T points and one with > 32 points exercises both selection paths
+    rng = np.random.default_rng(0)
+    blob = np.stack([rng.uniform(20.0, 20.19, 300), rng.uniform(1.0, 1.19, 300), rng.uniform(-1.0, -0.61, 300), rng.random(300)], 1)
+    frames[2] = np.concatenate([frames[2], blob.astype(np.float32)])
+    fnet = vn.FeatureLearningNet(target).eval()
+    load_state(fnet, sd, "")
+    fnet = fnet.to(cuda_device)
+    points, offsets, max_n = vn.pack_frames(frames)
+    vb = vn.voxelize_batch(points, offsets, max_n, target)
+    want = fnet.voxelwise(vb.feature)
+    grid = _cabi.grid_for_target(target)
+    ws = torch.empty(ops.voxelize_workspace_bytes(grid, 3, points.shape[0]), dtype=torch.uint8, device=cuda_device)
+    vo = torch.empty(4, dtype=torch.int32, device=cuda_device)
+    ops.voxelize_index(grid, points, offsets, max_n, vo, ws)
+    K = vb.feature.shape[0]
+    vw = torch.empty((K, 128), dtype=torch.float32, device=cuda_device)
+    co = torch.empty((K, 4), dtype=torch.int64, device=cuda_device)
+    nu = torch.empty((K,), dtype=torch.int64, device=cuda_device)
+    ops.voxelize_svfe_fused(grid, points, offsets, vo, fnet.vfe_1.folded(), fnet.vfe_2.folded(), vw, co, nu, ws)
+    assert torch.equal(vo.cpu(), vb.voxel_offsets.cpu())
+    assert torch.equal(co, vb.coordinate) and torch.equal(nu, vb.number)
+    assert torch.equal(vw.view(torch.int32), want.view(torch.int32))
+    _, feats, _, _ = oracle_batch(frames, target)
+    ref = OM.svfe_voxelwise(torch.from_numpy(np.concatenate(feats)), sd)
+    assert torch.allclose(vw.cpu(), ref, rtol=1e-4, atol=1e-5)
+
+
+def test_front_end_fused_and_unfused_agree(cuda_device):
+    sd = OM.random_state_dict(14)
+    frames = synth_frames(2, 70)
+    a = _build(cuda_device, "Pedestrian", sd, fuse_voxel_features=True).forward_frames(frames).clone()
+    b = _build(cuda_device, "Pedestrian", sd, fuse_voxel_features=False).forward_frames(frames)
+    assert torch.equal(a, b)

@@ -43,6 +43,7 @@ PROTOTYPES = {
     "vn_vfe_layer_fwd": (C.c_int, [_p, _p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vn_feature_mask": (C.c_int, [_p, _i64, _i32, _i32, _p, _p]),
     "vn_svfe_fused_fwd": (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "vn_voxelize_svfe_fused": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vn_fill_zero": (C.c_int, [_p, _sz, _p]),
     "vn_scatter_dense_f32": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p]),
     "vn_scatter_dense_bf16": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p]),

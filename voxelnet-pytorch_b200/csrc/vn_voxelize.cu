@@ -18,7 +18,7 @@
 //   P6 place           point index -> its voxel's segment
 //   P7 features        per voxel (one warp): T smallest indices ascending, gather, fp32 sequential
 //                      sum, fp64 centroid, write [T,7] row block, coords, count
-#include "vn_common.cuh"
+#include "vn_svfe_core.cuh"
 
 namespace vn {
 namespace {
@@ -259,7 +259,84 @@ __device__ __forceinline__ float f4_comp(const float4& v, int j) {
   return j == 0 ? v.x : (j == 1 ? v.y : (j == 2 ? v.z : v.w));
 }
 
-// P7: one warp per voxel row.
+// ---- per-voxel point selection, shared by P7 and the fused voxel->SVFE kernel -----------------
+// Loads the voxel's bucket, orders it by original point index and leaves the first m = min(n, T)
+// points in pts[0..m) (shared memory, one float4 per slot).  Returns m.
+__device__ __forceinline__ int warp_select_points(const float4* __restrict__ points, const int32_t* __restrict__ pidx,
+                                                  int n, int s0, int T, float4* pts, uint32_t lane) {
+  const int m = n < T ? n : T;
+  if (n <= 32) {
+    // rank of every index among the voxel's indices == its slot
+    const int idx = (int)lane < n ? pidx[s0 + lane] : 0x7fffffff;
+    int rank = 0;
+    for (int j = 0; j < n; ++j) rank += (__shfl_sync(0xffffffffu, idx, j) < idx) ? 1 : 0;
+    if ((int)lane < n && rank < m) pts[rank] = points[idx];
+  } else {
+    // rare: more than a warp's worth of points.  Select the m smallest indices in ascending
+    // order by repeated min-above-threshold over the segment.
+    int last = -1, mine0 = -1, mine1 = -1;
+    for (int s = 0; s < m; ++s) {
+      int cand = 0x7fffffff;
+      for (int j = lane; j < n; j += 32) {
+        const int v = pidx[s0 + j];
+        if (v > last && v < cand) cand = v;
+      }
+      cand = warp_min_i32(cand);
+      last = cand;
+      if ((int)lane == (s & 31)) {
+        if (s < 32) mine0 = cand; else mine1 = cand;
+      }
+    }
+    if (mine0 >= 0) pts[lane] = points[mine0];
+    if (mine1 >= 0) pts[32 + lane] = points[mine1];
+  }
+  __syncwarp();
+  return m;
+}
+
+// utils.py:87-88: fp32 sum over ALL T slots in slot order (numpy reduces axis 1 sequentially), the
+// zero pads included - they only matter for the sign of a -0.0 sum; float32 / int64 promotes to
+// float64.  Every lane returns the three means.
+__device__ __forceinline__ void warp_centroid(const float4* pts, int m, int T, uint32_t lane, double& mx, double& my,
+                                              double& mz) {
+  double mean = 0.0;
+  if (lane < 3) {
+    float s = f4_comp(pts[0], lane);
+    for (int t = 1; t < m; ++t) s = __fadd_rn(s, f4_comp(pts[t], lane));
+    if (m < T) s = __fadd_rn(s, 0.0f);
+    mean = (double)s / (double)m;
+  }
+  mx = __shfl_sync(0xffffffffu, mean, 0);
+  my = __shfl_sync(0xffffffffu, mean, 1);
+  mz = __shfl_sync(0xffffffffu, mean, 2);
+}
+
+// feature_buffer[row, t, j] for t < m (real point) or a pad slot (utils.py:71, 87-88).
+__device__ __forceinline__ float feature_value(const float4* pts, int m, int t, int j, double mx, double my, double mz) {
+  if (j < 4) return t < m ? f4_comp(pts[t], j) : 0.0f;
+  const float b = t < m ? f4_comp(pts[t], j - 4) : 0.0f;
+  const double c = j == 4 ? mx : (j == 5 ? my : mz);
+  return __double2float_rn((double)b - c);  // float64 subtraction, rounded on store
+}
+
+__device__ __forceinline__ void write_coords(const vn_grid_t& g, const float4& p0, int n_frames,
+                                             const int32_t* __restrict__ voxel_offsets, int64_t row,
+                                             long long* __restrict__ coords) {
+  int z, y, x;
+  point_cell(p0, g, z, y, x);
+  int lo = 0, hi = n_frames;  // frame of this row: last f with voxel_offsets[f] <= row
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if ((int64_t)voxel_offsets[mid] <= row) lo = mid; else hi = mid;
+  }
+  long long* c = coords + row * 4;
+  c[0] = lo;
+  c[1] = z;
+  c[2] = y;
+  c[3] = x;
+}
+
+// P7: one warp per voxel row -> materialised [T,7] feature rows (the reference's voxel dict).
 constexpr int kFeatWarps = 8;
 __global__ void __launch_bounds__(kFeatWarps * 32) k_vox_features(
     const vn_grid_t g, const float4* __restrict__ points, int n_frames,
@@ -274,76 +351,67 @@ __global__ void __launch_bounds__(kFeatWarps * 32) k_vox_features(
   if (total > max_voxels) total = max_voxels;
   const int64_t nwarps = (int64_t)gridDim.x * kFeatWarps;
   for (int64_t row = (int64_t)blockIdx.x * kFeatWarps + warp; row < total; row += nwarps) {
-    const int n = cnt[row];
-    const int s0 = seg[row];
-    const int m = n < T ? n : T;
-    if (n <= 32) {
-      // rank of every index among the voxel's indices == its slot (n <= 32 <= T: all are kept)
-      const int idx = (int)lane < n ? pidx[s0 + lane] : 0x7fffffff;
-      int rank = 0;
-      for (int j = 0; j < n; ++j) rank += (__shfl_sync(0xffffffffu, idx, j) < idx) ? 1 : 0;
-      if ((int)lane < n) pts[rank] = points[idx];
-    } else {
-      // rare: more than a warp's worth of points.  Select the m smallest indices in ascending
-      // order by repeated min-above-threshold over the segment.
-      int last = -1, mine0 = -1, mine1 = -1;
-      for (int s = 0; s < m; ++s) {
-        int cand = 0x7fffffff;
-        for (int j = lane; j < n; j += 32) {
-          const int v = pidx[s0 + j];
-          if (v > last && v < cand) cand = v;
-        }
-        cand = warp_min_i32(cand);
-        last = cand;
-        if ((int)lane == (s & 31)) {
-          if (s < 32) mine0 = cand; else mine1 = cand;
-        }
-      }
-      if (mine0 >= 0) pts[lane] = points[mine0];
-      if (mine1 >= 0) pts[32 + lane] = points[mine1];
-    }
-    __syncwarp();
-
-    // utils.py:87-88: fp32 sum over ALL T slots in slot order (numpy reduces axis 1
-    // sequentially), the zero pads included - they only matter for the sign of a -0.0 sum.
-    double mean = 0.0;
-    if (lane < 3) {
-      float s = f4_comp(pts[0], lane);
-      for (int t = 1; t < m; ++t) s = __fadd_rn(s, f4_comp(pts[t], lane));
-      if (m < T) s = __fadd_rn(s, 0.0f);
-      mean = (double)s / (double)m;  // float32 / int64 promotes to float64 in numpy
-    }
-    const double mx = __shfl_sync(0xffffffffu, mean, 0);
-    const double my = __shfl_sync(0xffffffffu, mean, 1);
-    const double mz = __shfl_sync(0xffffffffu, mean, 2);
-
+    const int m = warp_select_points(points, pidx, cnt[row], seg[row], T, pts, lane);
+    double mx, my, mz;
+    warp_centroid(pts, m, T, lane, mx, my, mz);
     float* out = feature + row * (int64_t)(T * 7);
     for (int e = lane; e < T * 7; e += 32) {
       const int t = e / 7, j = e - t * 7;
-      float v;
-      if (j < 4) {
-        v = t < m ? f4_comp(pts[t], j) : 0.0f;
-      } else {
-        const float b = t < m ? f4_comp(pts[t], j - 4) : 0.0f;
-        const double c = j == 4 ? mx : (j == 5 ? my : mz);
-        v = __double2float_rn((double)b - c);  // float64 subtraction, rounded on store
-      }
-      out[e] = v;
+      out[e] = feature_value(pts, m, t, j, mx, my, mz);
     }
     if (lane == 0) {
-      int z, y, x;
-      point_cell(pts[0], g, z, y, x);
-      int lo = 0, hi = n_frames;  // frame of this row: last f with voxel_offsets[f] <= row
-      while (hi - lo > 1) {
-        const int mid = (lo + hi) >> 1;
-        if ((int64_t)voxel_offsets[mid] <= row) lo = mid; else hi = mid;
-      }
-      long long* c = coords + row * 4;
-      c[0] = lo;
-      c[1] = z;
-      c[2] = y;
-      c[3] = x;
+      write_coords(g, pts[0], n_frames, voxel_offsets, row, coords);
       counts[row] = m;
+    }
+    __syncwarp();
+  }
+}
+
+// Fused P7 + stacked VFE: one warp per voxel builds the voxel's DISTINCT feature rows (its m real
+// points plus one representative pad row when m < T) in shared memory and evaluates VFE-1, VFE-2 and
+// the voxel-wise max on them - the [K,T,7] feature buffer is never written or read.  Bit-identical
+// to k_vox_features followed by k_svfe_fused (same row values, same instruction sequence).
+__global__ void __launch_bounds__(kFeatWarps * 32, 2) k_vox_svfe_fused(
+    const vn_grid_t g, const float4* __restrict__ points, int n_frames,
+    const int32_t* __restrict__ voxel_offsets, int64_t max_voxels, const int32_t* __restrict__ cnt,
+    const int32_t* __restrict__ seg, const int32_t* __restrict__ pidx, const float* __restrict__ w1,
+    const float* __restrict__ b1, const float* __restrict__ s1, const float* __restrict__ t1,
+    const float* __restrict__ w2, const float* __restrict__ b2, const float* __restrict__ s2,
+    const float* __restrict__ t2, float* __restrict__ voxelwise, long long* __restrict__ coords,
+    long long* __restrict__ counts) {
+  // dynamic smem per warp: float4 pts[T] | float rows[(T+1)*7 padded] | float x1[T+1][32]
+  extern __shared__ __align__(16) uint8_t dyn_smem[];
+  __shared__ Vfe1Params p1;
+  const int T = g.T;
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
+  const size_t per_warp = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128;
+  uint8_t* base = dyn_smem + warp * per_warp;
+  float4* pts = reinterpret_cast<float4*>(base);
+  float* rows = reinterpret_cast<float*>(base + (size_t)T * 16);
+  float(*x1)[32] = reinterpret_cast<float(*)[32]>(base + (size_t)T * 16 + rows_bytes);
+  load_vfe1_params(p1, w1, b1, s1, t1);
+  Vfe2Lane q;
+  load_vfe2_lane(q, w2, b2, s2, t2, lane);
+  __syncthreads();
+
+  int64_t total = voxel_offsets[n_frames];
+  if (total > max_voxels) total = max_voxels;
+  const int64_t nwarps = (int64_t)gridDim.x * kFeatWarps;
+  for (int64_t row = (int64_t)blockIdx.x * kFeatWarps + warp; row < total; row += nwarps) {
+    const int m = warp_select_points(points, pidx, cnt[row], seg[row], T, pts, lane);
+    double mx, my, mz;
+    warp_centroid(pts, m, T, lane, mx, my, mz);
+    const int R = m < T ? m + 1 : T;  // real rows 0..m-1, then one pad row at index m
+    for (int e = lane; e < R * 7; e += 32) {
+      const int t = e / 7, j = e - t * 7;
+      rows[e] = feature_value(pts, m, t, j, mx, my, mz);
+    }
+    __syncwarp();
+    svfe_eval_voxel(rows, m, R, m, x1, T, p1, q, voxelwise + row * 128, lane);
+    if (lane == 0) {
+      write_coords(g, pts[0], n_frames, voxel_offsets, row, coords);
+      if (counts != nullptr) counts[row] = m;
     }
     __syncwarp();
   }
@@ -367,6 +435,18 @@ int check_common(const vn_grid_t* grid, const void* points, const int32_t* frame
     return VN_ERR_WORKSPACE;
   }
   VN_REQUIRE((reinterpret_cast<uintptr_t>(workspace) & 255) == 0, "voxelize: workspace must be 256-byte aligned");
+  return VN_OK;
+}
+
+// P5 + P6: CSR segments per voxel and the bucketed point indices.
+int launch_bucket(const VoxWorkspace& w, const int32_t* frame_offsets, int n_frames, int64_t n_points_total,
+                  const int32_t* voxel_offsets, cudaStream_t st) {
+  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg);
+  VN_LAUNCH_CHECK("k_vox_segment_scan");
+  const int64_t want = (n_points_total + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 16;
+  k_vox_place<<<(unsigned)(want < cap ? want : cap), 256, 0, st>>>(n_points_total, w.keyrow, w.arrival, w.seg, w.pidx);
+  VN_LAUNCH_CHECK("k_vox_place");
   return VN_OK;
 }
 
@@ -432,15 +512,8 @@ int vn_voxelize_fill(const vn_grid_t* grid, const float* points, const int32_t* 
   cudaStream_t st = as_stream(stream);
   const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
   const int sms = sm_count();
-
-  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg);
-  VN_LAUNCH_CHECK("k_vox_segment_scan");
-  {
-    const int64_t want = (n_points_total + 255) / 256;
-    const int blocks = (int)(want < (int64_t)sms * 16 ? want : (int64_t)sms * 16);
-    k_vox_place<<<blocks, 256, 0, st>>>(n_points_total, w.keyrow, w.arrival, w.seg, w.pidx);
-    VN_LAUNCH_CHECK("k_vox_place");
-  }
+  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, st);
+  if (rc != VN_OK) return rc;
   {
     // persistent warps: 8 resident blocks of 8 warps per SM
     const int64_t want = (max_voxels + kFeatWarps - 1) / kFeatWarps;
@@ -451,6 +524,36 @@ int vn_voxelize_fill(const vn_grid_t* grid, const float* points, const int32_t* 
         reinterpret_cast<long long*>(number_buffer));
     VN_LAUNCH_CHECK("k_vox_features");
   }
+  return VN_OK;
+}
+
+int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
+                           int64_t n_points_total, const int32_t* voxel_offsets, int64_t max_voxels, const float* w1,
+                           const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
+                           const float* s2, const float* t2, float* voxelwise, int64_t* coordinate_buffer,
+                           int64_t* number_buffer, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  int rc = check_common(grid, points, frame_offsets, n_frames, n_points_total, workspace, workspace_bytes);
+  if (rc != VN_OK) return rc;
+  VN_REQUIRE(voxel_offsets != nullptr, "voxelize_svfe_fused: voxel_offsets is null");
+  VN_REQUIRE(max_voxels >= 0, "voxelize_svfe_fused: max_voxels < 0");
+  if (max_voxels == 0 || n_points_total == 0) return VN_OK;
+  VN_REQUIRE(w1 && b1 && s1 && t1 && w2 && b2 && s2 && t2, "voxelize_svfe_fused: null parameter pointer");
+  VN_REQUIRE(voxelwise && coordinate_buffer, "voxelize_svfe_fused: null output");
+  cudaStream_t st = as_stream(stream);
+  const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
+  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, st);
+  if (rc != VN_OK) return rc;
+  const int T = grid->T;
+  const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
+  const size_t smem = kFeatWarps * ((size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128);
+  VN_CUDA(cudaFuncSetAttribute(k_vox_svfe_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t want = (max_voxels + kFeatWarps - 1) / kFeatWarps;
+  const int64_t cap = (int64_t)sm_count() * 2;
+  k_vox_svfe_fused<<<(unsigned)(want < cap ? want : cap), kFeatWarps * 32, smem, st>>>(
+      *grid, reinterpret_cast<const float4*>(points), n_frames, voxel_offsets, max_voxels, w.cnt, w.seg, w.pidx, w1, b1,
+      s1, t1, w2, b2, s2, t2, voxelwise, reinterpret_cast<long long*>(coordinate_buffer),
+      reinterpret_cast<long long*>(number_buffer));
+  VN_LAUNCH_CHECK("k_vox_svfe_fused");
   return VN_OK;
 }
 

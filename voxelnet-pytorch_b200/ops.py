@@ -140,6 +140,24 @@ def svfe_fused_fwd(feature, p1, p2, out=None, n_voxels_dev=None) -> torch.Tensor
     return out
 
 
+def voxelize_svfe_fused(grid, points, frame_offsets, voxel_offsets, p1, p2, voxelwise, coords, counts, workspace) -> None:
+    """Voxelizer phase 2 fused with the stacked VFE: writes voxelwise (cap,128) f32 and coords
+    (cap,4) i64 (counts optional) without materialising the (K,T,7) feature buffer."""
+    _require_cuda(points, frame_offsets, voxel_offsets, voxelwise, coords, counts, workspace, *p1, *p2)
+    _contig(voxelwise, torch.float32), _contig(coords, torch.int64)
+    n_frames = frame_offsets.numel() - 1
+    with torch.cuda.device(points.device):
+        check(
+            _cabi.lib().vn_voxelize_svfe_fused(
+                C.byref(grid), _ptr(points), _ptr(frame_offsets), n_frames, points.shape[0], _ptr(voxel_offsets),
+                voxelwise.shape[0], *[_ptr(_contig(t, torch.float32)) for t in p1],
+                *[_ptr(_contig(t, torch.float32)) for t in p2], _ptr(voxelwise), _ptr(coords), _ptr(counts),
+                _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+            ),
+            "vn_voxelize_svfe_fused",
+        )
+
+
 # ---------------------------------------------------------------------------------------------
 # sparse -> dense
 # ---------------------------------------------------------------------------------------------

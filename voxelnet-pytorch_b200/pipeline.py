@@ -65,12 +65,15 @@ _NO_SPAN = _NoSpan()
 
 class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
-                 voxels_per_frame_capacity: int = 32768):
+                 voxels_per_frame_capacity: int = 32768, fuse_voxel_features: bool = True):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
         self.cfg = grid_config(target)
         self.grid = _cabi.grid_for_target(target)
         self.cap_per_frame = int(voxels_per_frame_capacity)
+        # True: the (K,T,7) feature buffer is never materialised (vn_voxelize_svfe_fused);
+        # False: voxel dict written then read back by the SVFE kernel (the reference's data flow)
+        self.fuse_voxel_features = bool(fuse_voxel_features)
         self._shape = None
         self.refresh_parameters()
 
@@ -95,7 +98,7 @@ class VoxelNetFrontEnd:
         d3 = ops.conv3d_out_depth(d2, 2, 1)
         self.workspace = torch.empty(ops.voxelize_workspace_bytes(self.grid, n_frames, n_points), dtype=torch.uint8, device=device)
         self.voxels = VoxelBatch(
-            torch.empty((cap, T, 7), dtype=torch.float32, device=device),
+            torch.empty((0 if self.fuse_voxel_features else cap, T, 7), dtype=torch.float32, device=device),
             torch.empty((cap, 4), dtype=torch.int64, device=device),
             torch.empty((cap,), dtype=torch.int64, device=device),
             torch.zeros(n_frames + 1, dtype=torch.int32, device=device),
@@ -118,13 +121,20 @@ class VoxelNetFrontEnd:
         self._ensure_buffers(n_frames, points.shape[0], points.device)
         vb = self.voxels
         span = timer.span if timer is not None else (lambda stage: _NO_SPAN)
-        with span("voxelize"):
-            ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
-            ops.voxelize_fill(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, vb.feature,
-                              vb.coordinate, vb.number, self.workspace)
         k_dev = vb.n_voxels_dev
-        with span("svfe"):
-            ops.svfe_fused_fwd(vb.feature, self._p1, self._p2, out=self.voxelwise, n_voxels_dev=k_dev)
+        if self.fuse_voxel_features:
+            with span("voxelize"):  # crop, cell keys, occupancy bitmap, ranks, per-voxel buckets
+                ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
+            with span("svfe"):      # bucket -> first-T selection -> 7-d rows on chip -> VFE-1/VFE-2/max
+                ops.voxelize_svfe_fused(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2,
+                                        self.voxelwise, vb.coordinate, vb.number, self.workspace)
+        else:
+            with span("voxelize"):
+                ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
+                ops.voxelize_fill(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, vb.feature,
+                                  vb.coordinate, vb.number, self.workspace)
+            with span("svfe"):
+                ops.svfe_fused_fwd(vb.feature, self._p1, self._p2, out=self.voxelwise, n_voxels_dev=k_dev)
         with span("scatter"):
             ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
