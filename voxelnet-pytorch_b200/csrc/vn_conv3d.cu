@@ -6,23 +6,26 @@
 //
 // Tiling (DESIGN.md "Conv3d"): one CTA owns a 16 (h) x 8 (w) spatial tile for ALL output depths of
 // one frame: Dout accumulators of 128 x 64 fp32 live side by side in TMEM (64 columns each, depth
-// ascending).  The K loop walks the INPUT planes in ascending order.  An input plane p feeds
-// output depth d' = (p + pad_d - kd) / stride_d for every valid kd; those d' are consecutive, so
-// the depth taps of one plane are fused along N: ONE tcgen05.mma of shape 128 x (64*nkd) x 16
-// multiplies the A tile with the nkd weight tiles laid side by side and lands in nkd adjacent
-// accumulators.  This reads the A operand from shared memory once instead of nkd times (N = 64
-// alone is shared-memory-bandwidth bound: 6 KB of operands per 32 tensor cycles), and accumulators
-// complete in ascending order, so the epilogue drains d' while the tensor core works on d'+1 and on
-// the next tile.
+// ascending).
+//
+// K loop: for each (64-channel chunk, kw) - 6 or 3 passes - the 72 KB of weights of that pass are
+// made resident in shared memory (one bulk copy, double buffered) and the INPUT planes are walked in
+// ascending order.  An input plane p feeds output depth d' = (p + pad_d - kd) / stride_d for every
+// valid kd; those d' are consecutive, so the depth taps of one plane are fused along N: ONE
+// tcgen05.mma of shape 128 x (64*nkd) x 16 multiplies the A tile with the nkd weight tiles laid side
+// by side and lands in nkd adjacent accumulators.  This reads the A operand from shared memory once
+// instead of nkd times (N = 64 alone is shared-memory-bandwidth bound: 6 KB of operands per 32
+// tensor cycles).  Per tile the kernel pulls 432/216 KB of weights (each exactly once) plus one A
+// box per (plane, chunk, kw) from L2.  In the last pass accumulators complete in ascending depth
+// order, so the epilogue drains d' while the tensor core finishes d'+1.. and starts the next tile.
 //
 //   A operand: per (plane, 64-channel chunk, kw) ONE TMA box of 64 ch x 8 w x 18 h (an h-halo'd
 //              tile, 128-byte rows, SWIZZLE_128B).  The three kh taps read it at +kh*1024 B: one
 //              image row of the tile is exactly one 8-row swizzle atom, so every tap start stays
 //              atom-aligned.  Out-of-range h / w / (skipped) d are the convolution's zero padding,
 //              supplied by TMA's out-of-bounds zero fill.
-//   B operand: weights pre-packed per (kd class, chunk, kw, kh) as nkd [64 n x 64 k] K-major tiles,
-//              kd descending (= d' ascending), already in the swizzled shared-memory image; one
-//              bulk copy of nkd * 8 KB per (chunk, kw, kh).
+//   B operand: weights pre-packed as [chunk][kw][kd class][kh][kd descending = d' ascending] K-major
+//              [64 n x 64 k] tiles already in the swizzled shared-memory image.
 //   Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (both run warp-uniform
 //              control flow and elect one lane for the asynchronous instructions), warps 2..5 =
 //              epilogue (TMEM -> registers -> scale/shift/ReLU -> global).
@@ -38,12 +41,12 @@ constexpr int kTileH = 16, kTileW = 8;             // 128 output positions per a
 constexpr int kHaloH = kTileH + 2;
 constexpr uint32_t kABytes = kHaloH * kTileW * 128;  // 18432: 144 rows of 64 bf16
 constexpr uint32_t kBTapBytes = 64 * 128;            // 8192: [64 n][64 k] bf16
-constexpr uint32_t kBSlotBytes = 3 * kBTapBytes;     // up to three depth taps side by side
-constexpr int kNA = 3, kNB = 6;                      // ring depths
+constexpr uint32_t kBSlotBytes = 9 * kBTapBytes;     // all weights of one (chunk, kw): 3 kh x 3 kd tiles = 72 KB
+constexpr int kNA = 4, kNB = 2;                      // ring depths
 constexpr int kMaxDout = 8;                          // 8 x 64 = 512 TMEM columns
 constexpr int kMaxPlanes = 16;
 constexpr int kThreads = 6 * 32;
-constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBSlotBytes;  // 202752
+constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBSlotBytes;  // 221184
 constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + 1024 /*barriers, params*/;
 
 // What one input plane contributes (host-computed; see plan_planes()).
@@ -51,8 +54,8 @@ struct PlaneInfo {
   int32_t nkd;        // number of valid depth taps (0: plane unused)
   int32_t dmin;       // first output depth fed; tap j feeds dmin + j
   int32_t new_acc;    // output depth whose FIRST contribution comes from this plane, or -1
-  uint32_t woff;      // byte offset of this plane's first weight tile inside its kd class
-  uint32_t wstride;   // bytes between consecutive (chunk, kw, kh) tile groups of the class
+  uint32_t woff;      // byte offset of this plane's first weight tile inside a (chunk, kw) weight group
+  uint32_t wstride;   // bytes between the kh = 0, 1, 2 tile rows of the plane's kd class
   int32_t done_mask;  // bit d set: accumulator d is complete after this plane
 };
 
@@ -120,12 +123,20 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int th = (tile / P.tiles_w) % P.tiles_h;
       const int b = tile / (P.tiles_w * P.tiles_h);
       const int h0 = th * kTileH, w0 = tw * kTileW;
-      for (int p = 0; p < P.Din; ++p) {
-        const PlaneInfo& pi = P.plane[p];
-        if (pi.nkd == 0) continue;
-        const uint32_t b_bytes = (uint32_t)pi.nkd * kBTapBytes;
-        for (int c = 0; c < P.nchunk; ++c) {
-          for (int kw = 0; kw < 3; ++kw) {
+      for (int c = 0; c < P.nchunk; ++c) {
+        for (int kw = 0; kw < 3; ++kw) {
+          // all weights of this (chunk, kw): resident while the K loop walks the input planes
+          const uint32_t sb = b_it % kNB;
+          mbar_wait(&bar->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
+          if (elect_one()) {
+            mbar_arrive_expect_tx(&bar->full_b[sb], kBSlotBytes);
+            bulk_load_1d(smem_b + sb * kBSlotBytes, P.wpack + (size_t)(c * 3 + kw) * kBSlotBytes, kBSlotBytes,
+                         &bar->full_b[sb]);
+          }
+          __syncwarp();
+          ++b_it;
+          for (int p = 0; p < P.Din; ++p) {
+            if (P.plane[p].nkd == 0) continue;
             const uint32_t sa = a_it % kNA;
             mbar_wait(&bar->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
             if (elect_one()) {
@@ -134,17 +145,6 @@ __global__ void __launch_bounds__(kThreads, 1)
             }
             __syncwarp();
             ++a_it;
-            for (int kh = 0; kh < 3; ++kh) {
-              const uint32_t sb = b_it % kNB;
-              mbar_wait(&bar->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
-              if (elect_one()) {
-                mbar_arrive_expect_tx(&bar->full_b[sb], b_bytes);
-                const uint8_t* src = P.wpack + pi.woff + (size_t)((c * 3 + kw) * 3 + kh) * pi.wstride;
-                bulk_load_1d(smem_b + sb * kBSlotBytes, src, b_bytes, &bar->full_b[sb]);
-              }
-              __syncwarp();
-              ++b_it;
-            }
           }
         }
       }
@@ -153,64 +153,61 @@ __global__ void __launch_bounds__(kThreads, 1)
     // ===================== MMA issuer (warp-uniform; one elected lane issues) =====================
     uint32_t a_it = 0, b_it = 0, tile_it = 0;
     for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tile_it) {
-      for (int p = 0; p < P.Din; ++p) {
-        const PlaneInfo& pi = P.plane[p];
-        if (pi.nkd == 0) continue;
-        const int nkd = pi.nkd;
-        const uint32_t d_tmem = tmem_base + (uint32_t)pi.dmin * 64;
-        // Accumulators first touched by this plane must have been drained by the epilogue.
-        // (With an N-fused MMA the started accumulators need accumulate=1 and the new one 0, so
-        // the very first k-step of the plane is split into two instructions.)
-        const int jnew = pi.new_acc >= 0 ? pi.new_acc - pi.dmin : -1;  // tap index of the new accumulator
-        if (pi.new_acc >= 0) {
-          mbar_wait(&bar->acc_empty[pi.new_acc], (tile_it & 1) ^ 1);
+      for (int c = 0; c < P.nchunk; ++c) {
+        for (int kw = 0; kw < 3; ++kw) {
+          const bool first_pass = (c == 0) & (kw == 0);
+          const bool last_pass = (c == P.nchunk - 1) & (kw == 2);
+          const uint32_t sb = b_it % kNB;
+          mbar_wait(&bar->full_b[sb], (b_it / kNB) & 1);
           tc_fence_after_sync();
-        }
-        const uint32_t idesc_all = umma_idesc_bf16(128, 64 * nkd);
-        bool first_step = true;
-        for (int c = 0; c < P.nchunk; ++c) {
-          for (int kw = 0; kw < 3; ++kw) {
+          const uint32_t b_addr = smem_u32(smem_b + sb * kBSlotBytes);
+          for (int p = 0; p < P.Din; ++p) {
+            const PlaneInfo& pi = P.plane[p];
+            if (pi.nkd == 0) continue;
+            const uint32_t d_tmem = tmem_base + (uint32_t)pi.dmin * 64;
+            // An accumulator first touched by this plane (first pass only) must have been drained by
+            // the epilogue, and needs accumulate=0 while its already-started neighbours need 1: the
+            // very first k-step of such a plane is split into two instructions.
+            const int jnew = (first_pass && pi.new_acc >= 0) ? pi.new_acc - pi.dmin : -1;
+            if (jnew >= 0) {
+              mbar_wait(&bar->acc_empty[pi.new_acc], (tile_it & 1) ^ 1);
+              tc_fence_after_sync();
+            }
+            const uint32_t idesc_all = umma_idesc_bf16(128, 64 * pi.nkd);
             const uint32_t sa = a_it % kNA;
             mbar_wait(&bar->full_a[sa], (a_it / kNA) & 1);
             tc_fence_after_sync();
             const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
-            for (int kh = 0; kh < 3; ++kh) {
-              const uint32_t sb = b_it % kNB;
-              mbar_wait(&bar->full_b[sb], (b_it / kNB) & 1);
-              tc_fence_after_sync();
-              const uint32_t b_addr = smem_u32(smem_b + sb * kBSlotBytes);
-              if (elect_one()) {
+            if (elect_one()) {
+#pragma unroll
+              for (int kh = 0; kh < 3; ++kh) {
                 const uint64_t da0 = umma_desc_sw128(a_addr + kh * (kTileW * 128), 1024);
-                const uint64_t db0 = umma_desc_sw128(b_addr, 1024);
-                int k4 = 0;
-                if (first_step && jnew >= 0) {
-                  // split k-step: started accumulators (taps [0, jnew)) accumulate, the new one (tap jnew,
-                  // always the last tap of the plane) is overwritten
+                const uint64_t db0 = umma_desc_sw128(b_addr + pi.woff + kh * pi.wstride, 1024);
+                int k0 = 0;
+                if (kh == 0 && jnew >= 0) {
                   if (jnew > 0) umma_bf16_ss(d_tmem, da0, db0, umma_idesc_bf16(128, 64 * jnew), 1);
                   umma_bf16_ss(d_tmem + jnew * 64, da0, db0 + (uint64_t)((jnew * kBTapBytes) >> 4),
                                umma_idesc_bf16(128, 64), 0);
-                  k4 = 1;
+                  k0 = 1;
                 }
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                  if (k >= k4) umma_bf16_ss(d_tmem, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc_all, 1);
+                  if (k >= k0) umma_bf16_ss(d_tmem, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc_all, 1);
                 }
-                umma_commit(&bar->empty_b[sb]);
               }
-              __syncwarp();
-              first_step = false;
-              ++b_it;
+              umma_commit(&bar->empty_a[sa]);
+              if (last_pass && pi.done_mask != 0) {
+                for (int d = 0; d < P.Dout; ++d)
+                  if ((pi.done_mask >> d) & 1) umma_commit(&bar->acc_full[d]);
+              }
             }
-            if (elect_one()) umma_commit(&bar->empty_a[sa]);
             __syncwarp();
             ++a_it;
           }
+          if (elect_one()) umma_commit(&bar->empty_b[sb]);
+          __syncwarp();
+          ++b_it;
         }
-        if (pi.done_mask != 0 && elect_one()) {
-          for (int d = 0; d < P.Dout; ++d)
-            if ((pi.done_mask >> d) & 1) umma_commit(&bar->acc_full[d]);
-        }
-        __syncwarp();
       }
     }
   } else {
@@ -283,17 +280,18 @@ __global__ void __launch_bounds__(kThreads, 1)
 
 // Weight image.  Depth taps are grouped into "kd classes" that can be valid for the same input plane:
 //   stride_d 1: one class {2,1,0};  stride_d 2: class 0 = {2,0} (planes with p+pad even), class 1 = {1}.
-// Layout: [class][chunk][kw][kh][j: kd descending][n = 64][k = 64] bf16, rows 128B-swizzled.
+// Layout: [chunk][kw][class][kh][j: kd descending][n = 64][k = 64] bf16, rows 128B-swizzled: the 72 KB
+// of one (chunk, kw) are contiguous (one bulk copy), and the taps valid for a plane sit side by side.
 struct KdClasses {
   int n_classes;
   int nkd[2];
   int kd[2][3];
-  uint32_t base[2];  // byte offset of the class
+  uint32_t base[2];  // byte offset of the class inside a (chunk, kw) group
 };
 
 __host__ __device__ inline KdClasses kd_classes(int stride_d, int cin) {
   KdClasses k{};
-  const uint32_t per_tap = (uint32_t)(cin / 64) * 9 * kBTapBytes;
+  (void)cin;
   if (stride_d == 1) {
     k.n_classes = 1;
     k.nkd[0] = 3; k.kd[0][0] = 2; k.kd[0][1] = 1; k.kd[0][2] = 0;
@@ -303,7 +301,7 @@ __host__ __device__ inline KdClasses kd_classes(int stride_d, int cin) {
     k.nkd[0] = 2; k.kd[0][0] = 2; k.kd[0][1] = 0;
     k.nkd[1] = 1; k.kd[1][0] = 1;
     k.base[0] = 0;
-    k.base[1] = 2 * per_tap;
+    k.base[1] = 3 * 2 * kBTapBytes;  // after class 0: 3 kh x 2 taps
   }
   return k;
 }
@@ -327,7 +325,7 @@ __global__ void __launch_bounds__(256)
       for (int q = 0; q < kc.nkd[a]; ++q)
         if (kc.kd[a][q] == kd) { cls = a; j = q; }
     const float v = w[((((size_t)n * cin + (c * 64 + k)) * 3 + kd) * 3 + kh) * 3 + kw];
-    const size_t tile = kc.base[cls] + ((size_t)(((c * 3 + kw) * 3 + kh) * kc.nkd[cls] + j)) * kBTapBytes;
+    const size_t tile = (size_t)(c * 3 + kw) * kBSlotBytes + kc.base[cls] + (size_t)(kh * kc.nkd[cls] + j) * kBTapBytes;
     const size_t off = tile + (size_t)n * 128 + ((((k >> 3) ^ (n & 7)) << 4) | ((k & 7) << 1));
     *reinterpret_cast<__nv_bfloat16*>(packed + off) = __float2bfloat16_rn(v);
   }
