@@ -145,9 +145,14 @@ int vn_scatter_dense_f32(const float* voxelwise, const int64_t* coords /* [K,4] 
 
 /* bf16 fast path: writes (or, with clear != 0, re-zeroes) the K occupied rows of a bf16 grid that
  * is kept resident and zero between frames, so the 360 MB/frame zero-fill is paid once. */
+/* `conv_box_flags` (optional, may be NULL): byte table [B][D][ceil(H/16)][W/8][3] of
+ * vn_conv3d_box_flags_bytes(B, D, H, W) bytes that the first Conv3d uses to skip all-zero input boxes.
+ * Writing a row sets (clear: resets) the flag of every 18x8 halo'd input box that contains the voxel;
+ * like the grid, the table is zero between frames. */
 int vn_scatter_dense_bf16(const float* voxelwise, const int64_t* coords, int64_t K,
                           const int32_t* n_voxels_dev, int32_t C, int32_t B, int32_t D, int32_t H,
-                          int32_t W, void* dense_bf16, int32_t clear, vn_stream_t stream);
+                          int32_t W, void* dense_bf16, uint8_t* conv_box_flags, int32_t clear,
+                          vn_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Conv3d middle layers - replaces ConvMD(3, ...).forward = Conv3d(k=3) -> BatchNorm3d -> ReLU
@@ -166,11 +171,15 @@ int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, v
 /* x: [B, Din, H, W, cin] bf16 (NDHWC).  cin in {64, 128}, cout = 64, kernel 3x3x3, H/W stride 1 and
  * padding 1; depth stride/padding (stride_d, pad_d) in {(2,1), (1,0)}.
  * out_mode 0: y [B, Dout, H, W, 64] bf16 (NDHWC) - feeds the next layer.
- * out_mode 1: y [B, 64*Dout, H, W] f32 with channel = c*Dout + d - the reshape of model.py:262. */
+ * out_mode 1: y [B, 64*Dout, H, W] f32 with channel = c*Dout + d - the reshape of model.py:262.
+ * box_flags (optional, may be NULL): [B][Din][ceil(H/16)][W/8][3] bytes; flag[b][p][th][tw][kw] == 0
+ * asserts that the input box x[b, p, 16*th-1 .. 16*th+16, 8*tw+kw-1 .. 8*tw+kw+6, :] is all zeros, and
+ * the kernel then skips its load and its MMAs (exact: zero operands contribute nothing). */
+size_t vn_conv3d_box_flags_bytes(int32_t B, int32_t Din, int32_t H, int32_t W);
 int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin,
                           int32_t stride_d, int32_t pad_d, const void* packed_weight,
                           const float* scale /* [64] */, const float* shift /* [64] */,
-                          int32_t out_mode, void* y, vn_stream_t stream);
+                          int32_t out_mode, void* y, const uint8_t* box_flags, vn_stream_t stream);
 
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);

@@ -22,7 +22,7 @@ def test_library_exports_every_declared_symbol():
 
     lib = _cabi.lib()
     names = _header_symbols()
-    assert len(names) >= 17
+    assert len(names) >= 19
     for n in names:
         assert hasattr(lib, n), "libvoxelnet_b200.so lacks %s" % n
     assert sorted(_cabi.PROTOTYPES) == names, "ctypes prototypes out of sync with the header"
@@ -56,7 +56,7 @@ def test_bad_arguments_are_rejected_without_a_gpu():
     rc = lib.vn_vfe_layer_fwd(None, None, 5, 35, 9, 16, None, None, None, None, None, None)
     assert rc < 0
     rc = lib.vn_conv3d_bn_relu_fwd(ctypes.c_void_p(16), 1, 10, 16, 12, 128, 2, 1, ctypes.c_void_p(16), ctypes.c_void_p(16),
-                                  ctypes.c_void_p(16), 0, ctypes.c_void_p(16), None)
+                                  ctypes.c_void_p(16), 0, ctypes.c_void_p(16), None, None)
     assert rc == -1 and b"multiple of 8" in lib.vn_last_error()
     assert lib.vn_conv3d_packed_weight_bytes(128) == 27 * 128 * 64 * 2 and lib.vn_conv3d_packed_weight_bytes(32) == 0
     with pytest.raises(_cabi.VnError):

@@ -111,3 +111,37 @@ def test_middle_net_end_to_end_small(cuda_device):
     assert rel_max_err(got, want) < BF16_TOL
     rel_l2 = float((got - want).norm() / want.norm())
     assert rel_l2 < 5e-3, rel_l2
+
+
+@pytest.mark.parametrize("density", [0.0, 0.002, 0.05])
+def test_conv1_with_box_flags_equals_dense_run(cuda_device, density):
+    """Skipping all-zero input boxes is exact: conv-1 with the occupancy table == conv-1 without it,
+    bit for bit, for an all-empty, a KITTI-sparse and a moderately dense grid (H, W not tile multiples
+    in H; several tiles; both batch entries different)."""
+    import voxelnet_pytorch_b200 as vn
+    from voxelnet_pytorch_b200 import ops
+
+    cin, cout, stride, padding = OM.MIDDLE_LAYERS[0]
+    g = torch.Generator().manual_seed(30)
+    sd = OM.random_state_dict(30)
+    B, D, H, W = 2, 10, 56, 40
+    occ = torch.rand((B, D, H, W), generator=g) < density
+    occ[1, :, :, :20] = False  # one frame half empty
+    idx = occ.nonzero().contiguous()
+    K = idx.shape[0]
+    vw = torch.randn((max(K, 1), 128), generator=g)[:K]
+    dense = torch.empty((B, D, H, W, 128), dtype=torch.bfloat16, device=cuda_device)
+    ops.fill_zero(dense)
+    flags = torch.zeros(ops.conv3d_box_flags_bytes(B, D, H, W), dtype=torch.uint8, device=cuda_device)
+    if K:
+        ops.scatter_dense_bf16(vw.to(cuda_device), idx.to(cuda_device), dense, box_flags=flags)
+    m = vn.ConvMD(3, cin, cout, 3, stride, padding).eval()
+    load_state(m, sd, "middle_layer.0.")
+    m = m.to(cuda_device)
+    packed, scale, shift = m.folded()
+    full = ops.conv3d_bn_relu_fwd(dense, packed, scale, shift, 2, 1)
+    skip = ops.conv3d_bn_relu_fwd(dense, packed, scale, shift, 2, 1, box_flags=flags)
+    assert torch.equal(full.view(torch.int16), skip.view(torch.int16))
+    want = OM.conv_md3(dense.float().cpu().permute(0, 4, 1, 2, 3), sd, "middle_layer.0.", stride, padding)
+    got = skip.float().permute(0, 4, 1, 2, 3).cpu()
+    assert rel_max_err(got, want) < BF16_TOL

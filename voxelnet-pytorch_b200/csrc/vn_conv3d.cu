@@ -65,6 +65,7 @@ struct ConvParams {
   int tiles_h, tiles_w, n_tiles;
   int out_mode;    // 0: bf16 NDHWC, 1: f32 [B, 64*Dout, H, W] with channel = c*Dout + d
   const uint8_t* wpack;
+  const uint8_t* box_flags;  // [B][Din][tiles_h][tiles_w][3] or nullptr
   const float* scale;
   const float* shift;
   void* out;
@@ -81,6 +82,36 @@ struct Barriers {
 };
 static_assert(sizeof(Barriers) <= 1024, "barrier block too large");
 
+// Which input boxes of a tile can hold non-zero data: bit (p*3 + kw).  Without a flag table every
+// box is live.  With one (written by vn_scatter_dense_bf16 from the voxel coordinates), a zero flag
+// guarantees the 18 x 8 box of plane p at w-shift kw is all zeros, so its TMA load and MMAs are
+// skipped - exact, since zero operands contribute nothing.  All 32 lanes must call this.
+template <bool kSkip>
+__device__ __forceinline__ uint64_t live_boxes(const ConvParams& P, int b, int th, int tw, uint32_t lane) {
+  if (!kSkip) return ~0ull;
+  uint64_t m = 0;
+  if ((int)lane < P.Din) {
+    const uint8_t* f = P.box_flags + ((((size_t)b * P.Din + lane) * P.tiles_h + th) * P.tiles_w + tw) * 3;
+    const uint32_t bits = (f[0] ? 1u : 0u) | (f[1] ? 2u : 0u) | (f[2] ? 4u : 0u);
+    m = (uint64_t)bits << (3 * lane);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) m |= __shfl_xor_sync(0xffffffffu, m, d);
+  return m;
+}
+
+// Accumulators (bit d) that receive at least one live box in this tile.
+__device__ __forceinline__ uint32_t touched_accumulators(const ConvParams& P, uint64_t live) {
+  uint32_t t = 0;
+  for (int p = 0; p < P.Din; ++p) {
+    const PlaneInfo& pi = P.plane[p];
+    if (pi.nkd != 0 && ((live >> (p * 3)) & 7)) t |= ((1u << pi.nkd) - 1u) << pi.dmin;
+  }
+  return t;
+}
+
+// kSkip = false compiles the occupancy logic away for dense inputs (conv-2, conv-3, drop-in calls).
+template <bool kSkip>
 __global__ void __launch_bounds__(kThreads, 1)
     k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ ConvParams P) {
   extern __shared__ uint8_t smem_raw[];
@@ -123,6 +154,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int th = (tile / P.tiles_w) % P.tiles_h;
       const int b = tile / (P.tiles_w * P.tiles_h);
       const int h0 = th * kTileH, w0 = tw * kTileW;
+      const uint64_t live = live_boxes<kSkip>(P, b, th, tw, lane);
       for (int c = 0; c < P.nchunk; ++c) {
         for (int kw = 0; kw < 3; ++kw) {
           // all weights of this (chunk, kw): resident while the K loop walks the input planes
@@ -136,7 +168,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           __syncwarp();
           ++b_it;
           for (int p = 0; p < P.Din; ++p) {
-            if (P.plane[p].nkd == 0) continue;
+            if (P.plane[p].nkd == 0 || !((live >> (p * 3 + kw)) & 1)) continue;
             const uint32_t sa = a_it % kNA;
             mbar_wait(&bar->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
             if (elect_one()) {
@@ -151,11 +183,17 @@ __global__ void __launch_bounds__(kThreads, 1)
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (warp-uniform; one elected lane issues) =====================
-    uint32_t a_it = 0, b_it = 0, tile_it = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tile_it) {
+    uint32_t a_it = 0, b_it = 0;
+    uint32_t acc_phase = 0;  // bit d: parity of the number of tiles that used accumulator d so far
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+      const int tw = tile % P.tiles_w;
+      const int th = (tile / P.tiles_w) % P.tiles_h;
+      const int b = tile / (P.tiles_w * P.tiles_h);
+      const uint64_t live = live_boxes<kSkip>(P, b, th, tw, lane);
+      const uint32_t touched = touched_accumulators(P, live);
+      uint32_t started = 0;  // accumulators that already hold a partial sum of this tile
       for (int c = 0; c < P.nchunk; ++c) {
         for (int kw = 0; kw < 3; ++kw) {
-          const bool first_pass = (c == 0) & (kw == 0);
           const bool last_pass = (c == P.nchunk - 1) & (kw == 2);
           const uint32_t sb = b_it % kNB;
           mbar_wait(&bar->full_b[sb], (b_it / kNB) & 1);
@@ -164,78 +202,97 @@ __global__ void __launch_bounds__(kThreads, 1)
           for (int p = 0; p < P.Din; ++p) {
             const PlaneInfo& pi = P.plane[p];
             if (pi.nkd == 0) continue;
-            const uint32_t d_tmem = tmem_base + (uint32_t)pi.dmin * 64;
-            // An accumulator first touched by this plane (first pass only) must have been drained by
-            // the epilogue, and needs accumulate=0 while its already-started neighbours need 1: the
-            // very first k-step of such a plane is split into two instructions.
-            const int jnew = (first_pass && pi.new_acc >= 0) ? pi.new_acc - pi.dmin : -1;
-            if (jnew >= 0) {
-              mbar_wait(&bar->acc_empty[pi.new_acc], (tile_it & 1) ^ 1);
+            if ((live >> (p * 3 + kw)) & 1) {
+              const uint32_t range = ((1u << pi.nkd) - 1u) << pi.dmin;
+              const uint32_t fresh = range & ~started;
+              // Accumulators first touched here must have been drained by the epilogue, and need
+              // accumulate=0 while already-started neighbours need 1: the first k-step is then issued
+              // per accumulator (N = 64) instead of fused along N.
+              if (fresh) {
+                for (int d = pi.dmin; d < pi.dmin + pi.nkd; ++d)
+                  if ((fresh >> d) & 1) mbar_wait(&bar->acc_empty[d], ((acc_phase >> d) & 1) ^ 1);
+                tc_fence_after_sync();
+              }
+              const uint32_t d_tmem = tmem_base + (uint32_t)pi.dmin * 64;
+              const uint32_t idesc_all = umma_idesc_bf16(128, 64 * pi.nkd);
+              const uint32_t sa = a_it % kNA;
+              mbar_wait(&bar->full_a[sa], (a_it / kNA) & 1);
               tc_fence_after_sync();
-            }
-            const uint32_t idesc_all = umma_idesc_bf16(128, 64 * pi.nkd);
-            const uint32_t sa = a_it % kNA;
-            mbar_wait(&bar->full_a[sa], (a_it / kNA) & 1);
-            tc_fence_after_sync();
-            const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
-            if (elect_one()) {
+              const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
+              if (elect_one()) {
 #pragma unroll
-              for (int kh = 0; kh < 3; ++kh) {
-                const uint64_t da0 = umma_desc_sw128(a_addr + kh * (kTileW * 128), 1024);
-                const uint64_t db0 = umma_desc_sw128(b_addr + pi.woff + kh * pi.wstride, 1024);
-                int k0 = 0;
-                if (kh == 0 && jnew >= 0) {
-                  if (jnew > 0) umma_bf16_ss(d_tmem, da0, db0, umma_idesc_bf16(128, 64 * jnew), 1);
-                  umma_bf16_ss(d_tmem + jnew * 64, da0, db0 + (uint64_t)((jnew * kBTapBytes) >> 4),
-                               umma_idesc_bf16(128, 64), 0);
-                  k0 = 1;
-                }
+                for (int kh = 0; kh < 3; ++kh) {
+                  const uint64_t da0 = umma_desc_sw128(a_addr + kh * (kTileW * 128), 1024);
+                  const uint64_t db0 = umma_desc_sw128(b_addr + pi.woff + kh * pi.wstride, 1024);
+                  int k0 = 0;
+                  if (kh == 0 && fresh) {
+                    for (int j = 0; j < pi.nkd; ++j)
+                      umma_bf16_ss(d_tmem + j * 64, da0, db0 + (uint64_t)((j * kBTapBytes) >> 4), umma_idesc_bf16(128, 64),
+                                   (started >> (pi.dmin + j)) & 1);
+                    k0 = 1;
+                  }
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                  if (k >= k0) umma_bf16_ss(d_tmem, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc_all, 1);
+                  for (int k = 0; k < 4; ++k) {
+                    if (k >= k0) umma_bf16_ss(d_tmem, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc_all, 1);
+                  }
                 }
+                umma_commit(&bar->empty_a[sa]);
               }
-              umma_commit(&bar->empty_a[sa]);
-              if (last_pass && pi.done_mask != 0) {
+              __syncwarp();
+              started |= range;
+              ++a_it;
+            }
+            // accumulators whose last possible contribution is this plane of the last pass
+            if (last_pass && (pi.done_mask & touched) != 0) {
+              if (elect_one()) {
                 for (int d = 0; d < P.Dout; ++d)
-                  if ((pi.done_mask >> d) & 1) umma_commit(&bar->acc_full[d]);
+                  if (((pi.done_mask & touched) >> d) & 1) umma_commit(&bar->acc_full[d]);
               }
+              __syncwarp();
             }
-            __syncwarp();
-            ++a_it;
           }
           if (elect_one()) umma_commit(&bar->empty_b[sb]);
           __syncwarp();
           ++b_it;
         }
       }
+      acc_phase ^= touched;
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const uint32_t quad = warp & 3;                // TMEM lane quadrant this warp may read
     const uint32_t m = quad * 32 + lane;           // accumulator row = output position in the tile
     const int hl = m / kTileW, wl = m % kTileW;
-    uint32_t tile_it = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, ++tile_it) {
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
       const int tw = tile % P.tiles_w;
       const int th = (tile / P.tiles_w) % P.tiles_h;
       const int b = tile / (P.tiles_w * P.tiles_h);
       const int h = th * kTileH + hl, w = tw * kTileW + wl;
       const bool inside = h < P.H && w < P.W;
+      const uint32_t touched = touched_accumulators(P, live_boxes<kSkip>(P, b, th, tw, lane));
       for (int dout = 0; dout < P.Dout; ++dout) {
-        mbar_wait(&bar->acc_full[dout], tile_it & 1);
-        tc_fence_after_sync();
+        const bool has_acc = (touched >> dout) & 1;  // else: no non-zero input reached this accumulator
+        if (has_acc) {
+          mbar_wait(&bar->acc_full[dout], (acc_phase >> dout) & 1);
+          tc_fence_after_sync();
+        }
         const uint32_t taddr = tmem_base + ((quad * 32) << 16) + (uint32_t)dout * 64;
 #pragma unroll
         for (int half = 0; half < 2; ++half) {
           uint32_t r[32];
-          tmem_ld_32x32b_x32(taddr + half * 32, r);
-          tmem_ld_wait();
-          if (half == 1) {
-            // accumulator fully read: hand it back to the MMA issuer before the global stores
-            tc_fence_before_sync();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&bar->acc_empty[dout]);
+          if (has_acc) {
+            tmem_ld_32x32b_x32(taddr + half * 32, r);
+            tmem_ld_wait();
+            if (half == 1) {
+              // accumulator fully read: hand it back to the MMA issuer before the global stores
+              tc_fence_before_sync();
+              __syncwarp();
+              if (lane == 0) mbar_arrive(&bar->acc_empty[dout]);
+            }
+          } else {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) r[j] = 0u;
           }
           if (inside) {
             float v[32];
@@ -267,6 +324,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           }
         }
       }
+      acc_phase ^= touched;
     }
   }
 
@@ -393,6 +451,11 @@ using namespace vn;
 
 extern "C" {
 
+size_t vn_conv3d_box_flags_bytes(int32_t B, int32_t Din, int32_t H, int32_t W) {
+  if (B < 1 || Din < 1 || H < 1 || W < 1 || W % kTileW != 0) return 0;
+  return (size_t)B * Din * ((H + kTileH - 1) / kTileH) * (W / kTileW) * 3;
+}
+
 size_t vn_conv3d_packed_weight_bytes(int32_t cin) {
   if (cin != 64 && cin != 128) return 0;
   return (size_t)27 * cin * 64 * 2;
@@ -410,7 +473,7 @@ int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, v
 
 int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
                           int32_t pad_d, const void* packed_weight, const float* scale, const float* shift,
-                          int32_t out_mode, void* y, vn_stream_t stream) {
+                          int32_t out_mode, void* y, const uint8_t* box_flags, vn_stream_t stream) {
   VN_REQUIRE(x && packed_weight && scale && shift && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
@@ -452,6 +515,7 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
   P.n_tiles = B * P.tiles_h * P.tiles_w;
   P.out_mode = out_mode;
   P.wpack = reinterpret_cast<const uint8_t*>(packed_weight);
+  P.box_flags = box_flags;
   P.scale = scale; P.shift = shift;
   P.out = y;
   if (plan_planes(P, cin, stride_d, pad_d) != 0) {
@@ -459,9 +523,14 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
     return VN_ERR_UNSUPPORTED;
   }
 
-  VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
   const int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
-  k_conv3d_bn_relu<<<grid, kThreads, kSmemBytes, as_stream(stream)>>>(tmap, P);
+  if (box_flags != nullptr) {
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<true><<<grid, kThreads, kSmemBytes, as_stream(stream)>>>(tmap, P);
+  } else {
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<false><<<grid, kThreads, kSmemBytes, as_stream(stream)>>>(tmap, P);
+  }
   VN_LAUNCH_CHECK("k_conv3d_bn_relu");
   return VN_OK;
 }

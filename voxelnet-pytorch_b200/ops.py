@@ -181,15 +181,17 @@ def scatter_dense_f32(voxelwise, coords, dense, n_voxels_dev=None) -> None:
         )
 
 
-def scatter_dense_bf16(voxelwise, coords, dense, clear: bool = False, n_voxels_dev=None) -> None:
-    _require_cuda(voxelwise, coords, dense)
+def scatter_dense_bf16(voxelwise, coords, dense, clear: bool = False, n_voxels_dev=None, box_flags=None) -> None:
+    """Write (clear=False) or re-zero (clear=True) the occupied rows of the resident bf16 grid; with
+    `box_flags` (uint8, conv3d_box_flags_bytes) also maintain the first conv's input-box occupancy table."""
+    _require_cuda(voxelwise, coords, dense, box_flags)
     _contig(coords, torch.int64), _contig(dense, torch.bfloat16)
     B, D, H, W, Cc = dense.shape
     with torch.cuda.device(dense.device):
         check(
             _cabi.lib().vn_scatter_dense_bf16(
                 _ptr(voxelwise), _ptr(coords), coords.shape[0], _ptr(n_voxels_dev), Cc, B, D, H, W, _ptr(dense),
-                1 if clear else 0, _stream(),
+                _ptr(box_flags), 1 if clear else 0, _stream(),
             ),
             "vn_scatter_dense_bf16",
         )
@@ -219,12 +221,19 @@ def conv3d_out_depth(din: int, stride_d: int, pad_d: int) -> int:
     return (din + 2 * pad_d - 3) // stride_d + 1
 
 
-def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int, final: bool = False, out=None):
+def conv3d_box_flags_bytes(B: int, Din: int, H: int, W: int) -> int:
+    return int(_cabi.lib().vn_conv3d_box_flags_bytes(B, Din, H, W))
+
+
+def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int, final: bool = False, out=None,
+                       box_flags=None):
     """x (B,Din,H,W,cin) bf16 NDHWC -> (B,Dout,H,W,64) bf16, or with final=True the reference's
     reshaped (B, 64*Dout, H, W) f32 (model.py:262)."""
-    _require_cuda(x, packed_weight, scale, shift)
+    _require_cuda(x, packed_weight, scale, shift, box_flags)
     _contig(x, torch.bfloat16)
     B, Din, H, W, cin = x.shape
+    if box_flags is not None and (box_flags.dtype != torch.uint8 or box_flags.numel() != conv3d_box_flags_bytes(B, Din, H, W)):
+        raise RuntimeError("box_flags must be a uint8 tensor of conv3d_box_flags_bytes(B, Din, H, W) elements")
     Dout = conv3d_out_depth(Din, stride_d, pad_d)
     if out is None:
         if final:
@@ -235,7 +244,7 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
         check(
             _cabi.lib().vn_conv3d_bn_relu_fwd(
                 _ptr(x), B, Din, H, W, cin, stride_d, pad_d, _ptr(packed_weight), _ptr(_contig(scale, torch.float32)),
-                _ptr(_contig(shift, torch.float32)), 1 if final else 0, _ptr(out), _stream(),
+                _ptr(_contig(shift, torch.float32)), 1 if final else 0, _ptr(out), _ptr(box_flags), _stream(),
             ),
             "vn_conv3d_bn_relu_fwd",
         )

@@ -65,7 +65,8 @@ _NO_SPAN = _NoSpan()
 
 class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
-                 voxels_per_frame_capacity: int = 32768, fuse_voxel_features: bool = True):
+                 voxels_per_frame_capacity: int = 32768, fuse_voxel_features: bool = True,
+                 skip_empty_boxes: bool = True):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
         self.cfg = grid_config(target)
@@ -74,6 +75,8 @@ class VoxelNetFrontEnd:
         # True: the (K,T,7) feature buffer is never materialised (vn_voxelize_svfe_fused);
         # False: voxel dict written then read back by the SVFE kernel (the reference's data flow)
         self.fuse_voxel_features = bool(fuse_voxel_features)
+        # True: conv-1 skips input boxes that hold no voxel (exact; the grid is ~99 % zeros)
+        self.skip_empty_boxes = bool(skip_empty_boxes)
         self._shape = None
         self.refresh_parameters()
 
@@ -107,6 +110,9 @@ class VoxelNetFrontEnd:
         self.voxelwise = torch.empty((cap, 128), dtype=torch.float32, device=device)
         self.dense = torch.empty((B, D, H, W, 128), dtype=torch.bfloat16, device=device)
         ops.fill_zero(self.dense)  # paid once: the step re-zeroes only the rows it wrote
+        # occupancy of the first conv's input boxes, maintained by the scatter/unscatter kernels
+        nflags = ops.conv3d_box_flags_bytes(B, D, H, W)
+        self.box_flags = torch.zeros((nflags + 15) // 16 * 16, dtype=torch.uint8, device=device)[:nflags] if self.skip_empty_boxes else None
         self.act1 = torch.empty((B, d1, H, W, 64), dtype=torch.bfloat16, device=device)
         self.act2 = torch.empty((B, d2, H, W, 64), dtype=torch.bfloat16, device=device)
         self.out = torch.empty((B, 64 * d3, H, W), dtype=torch.float32, device=device)
@@ -136,12 +142,13 @@ class VoxelNetFrontEnd:
             with span("svfe"):
                 ops.svfe_fused_fwd(vb.feature, self._p1, self._p2, out=self.voxelwise, n_voxels_dev=k_dev)
         with span("scatter"):
-            ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
+            ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev,
+                                   box_flags=self.box_flags)
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
         with span("conv1"):
-            ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1)
+            ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=self.box_flags)
         with span("unscatter"):
-            ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+            ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev, box_flags=self.box_flags)
         with span("conv2"):
             ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2)
         with span("conv3"):
