@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 1
+#define VN_ABI_VERSION 2
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -145,14 +145,9 @@ int vn_scatter_dense_f32(const float* voxelwise, const int64_t* coords /* [K,4] 
 
 /* bf16 fast path: writes (or, with clear != 0, re-zeroes) the K occupied rows of a bf16 grid that
  * is kept resident and zero between frames, so the 360 MB/frame zero-fill is paid once. */
-/* `conv_box_flags` (optional, may be NULL): byte table [B][D][ceil(H/16)][W/8][3] of
- * vn_conv3d_box_flags_bytes(B, D, H, W) bytes that the first Conv3d uses to skip all-zero input boxes.
- * Writing a row sets (clear: resets) the flag of every 18x8 halo'd input box that contains the voxel;
- * like the grid, the table is zero between frames. */
 int vn_scatter_dense_bf16(const float* voxelwise, const int64_t* coords, int64_t K,
                           const int32_t* n_voxels_dev, int32_t C, int32_t B, int32_t D, int32_t H,
-                          int32_t W, void* dense_bf16, uint8_t* conv_box_flags, int32_t clear,
-                          vn_stream_t stream);
+                          int32_t W, void* dense_bf16, int32_t clear, vn_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Conv3d middle layers - replaces ConvMD(3, ...).forward = Conv3d(k=3) -> BatchNorm3d -> ReLU
@@ -168,18 +163,61 @@ size_t vn_conv3d_packed_weight_bytes(int32_t cin);
 int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, void* packed,
                            vn_stream_t stream);
 
+/* Sizes of the two caller-allocated side buffers of the convolution:
+ *   box flags  [B][Din][ceil(H/16)][W/8][3] bytes, one per 18x8 halo'd input box (see below); must be
+ *              zero before the first vn_conv3d_mark_boxes;
+ *   workspace  the per-call work plan (tile masks, tile groups, work counter); contents are scratch. */
+size_t vn_conv3d_box_flags_bytes(int32_t B, int32_t Din, int32_t H, int32_t W);
+size_t vn_conv3d_workspace_bytes(int32_t B, int32_t H, int32_t W);
+
+#define VN_CONV_FLAGS_CONSUME 1     /* reset every flag that was read, leaving the table all-zero again */
+#define VN_CONV_FLAGS_BORDER_RING 2 /* also treat boxes that contain an H/W border position as live    */
+
 /* x: [B, Din, H, W, cin] bf16 (NDHWC).  cin in {64, 128}, cout = 64, kernel 3x3x3, H/W stride 1 and
- * padding 1; depth stride/padding (stride_d, pad_d) in {(2,1), (1,0)}.
+ * padding 1; depth stride/padding (stride_d, pad_d) in {(2,1), (1,0)}; Din <= 10, W % 8 == 0.
+ *
+ *   y = relu(conv(x) * scale[n] + shift) - sub
+ *
  * out_mode 0: y [B, Dout, H, W, 64] bf16 (NDHWC) - feeds the next layer.
  * out_mode 1: y [B, 64*Dout, H, W] f32 with channel = c*Dout + d - the reshape of model.py:262.
- * box_flags (optional, may be NULL): [B][Din][ceil(H/16)][W/8][3] bytes; flag[b][p][th][tw][kw] == 0
- * asserts that the input box x[b, p, 16*th-1 .. 16*th+16, 8*tw+kw-1 .. 8*tw+kw+6, :] is all zeros, and
- * the kernel then skips its load and its MMAs (exact: zero operands contribute nothing). */
-size_t vn_conv3d_box_flags_bytes(int32_t B, int32_t Din, int32_t H, int32_t W);
+ * shift_table / n_variants: n_variants 0: a plain [64] vector (BatchNorm shift with the conv bias
+ *   folded in) - the drop-in case.  n_variants 1: [Dout][64].  n_variants 9: [3][3][Dout][64] from
+ *   vn_conv3d_fold_background, indexed by (h class, w class) of the output position
+ *   (0 interior, 1 first row/column, 2 last row/column).
+ * sub (optional): [Dout][64] subtracted after the ReLU - the layer's own background, so that the
+ *   output is stored as a deviation that is exactly zero wherever the input was all background.
+ * box_flags (optional): flag[b][p][th][tw][kw] == 0 asserts that the input box
+ *   x[b, p, 16*th-1 .. 16*th+16, 8*tw+kw-1 .. 8*tw+kw+6, :] is all zeros; its load and its MMAs are
+ *   skipped (exact: zero operands contribute nothing).  NULL: every box is live.  flag_opts: VN_CONV_FLAGS_*.
+ * workspace: vn_conv3d_workspace_bytes(B, H, W) bytes, 16-byte aligned. */
 int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin,
                           int32_t stride_d, int32_t pad_d, const void* packed_weight,
-                          const float* scale /* [64] */, const float* shift /* [64] */,
-                          int32_t out_mode, void* y, const uint8_t* box_flags, vn_stream_t stream);
+                          const float* scale /* [64] */, const float* shift_table, int32_t n_variants,
+                          const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
+                          int32_t flag_opts, void* workspace, size_t workspace_bytes,
+                          vn_stream_t stream);
+
+/* Background folding for a layer whose INPUT is stored as a deviation from a per-(plane, channel)
+ * background bg_in [Din][cin] f32 (the previous layer's `sub`; NULL = zero background).  The
+ * reference zero-pads, so out-of-image taps see 0 rather than the background: the constant the
+ * background contributes depends on the output depth and on the border class of the output
+ * position.  Writes shift_table [3][3][Dout][64] (= bias*scale + shift, for n_variants 9) and, if
+ * bg_out is not NULL, the layer's own output background bg_out [Dout][64] = relu(interior row).
+ * weight is the torch-layout fp32 tensor; it is rounded to bf16 exactly as the packed image is. */
+int vn_conv3d_fold_background(const float* weight, int32_t cin, int32_t Din, int32_t stride_d,
+                              int32_t pad_d, const float* scale, const float* shift,
+                              const float* bg_in, float* shift_table, float* bg_out,
+                              vn_stream_t stream);
+
+/* Live-box flags for a chain of n_layers (<= 3) stacked middle layers from the voxel coordinates
+ * [K,4] (b,z,y,x) of the scattered grid: a voxel can disturb the input of layer l only at rows
+ * y-l..y+l, columns x-l..x+l and the planes its depth taps reach; every box containing such a
+ * position is flagged in flags[l] ([B][Din_l][ceil(H/16)][W/8][3], Din_0 = D).  `flags` is a HOST
+ * array of n_layers device pointers; stride_d / pad_d are host arrays of the layers' depth geometry. */
+int vn_conv3d_mark_boxes(const int64_t* coords, int64_t K, const int32_t* n_voxels_dev, int32_t B,
+                         int32_t D, int32_t H, int32_t W, int32_t n_layers,
+                         const int32_t* stride_d_host, const int32_t* pad_d_host,
+                         uint8_t* const* flags_host, vn_stream_t stream);
 
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);

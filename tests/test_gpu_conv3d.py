@@ -113,6 +113,61 @@ def test_middle_net_end_to_end_small(cuda_device):
     assert rel_l2 < 5e-3, rel_l2
 
 
+CHAIN = [(2, 1), (1, 0), (2, 1)]  # (stride_d, pad_d) of the three middle layers, model.py:207-209
+
+
+def _brute_force_flags(coords, B, D, H, W):
+    """Live-box tables of the 3-layer chain by brute force: dilate the set of disturbed positions
+    layer by layer (3x3 in h,w; depth taps), then test every 18x8 box window."""
+    TH, TW = (H + 15) // 16, W // 8
+    occ = torch.zeros((B, D, H, W), dtype=torch.bool)
+    occ[coords[:, 0], coords[:, 1], coords[:, 2], coords[:, 3]] = True
+    tables = []
+    for l, (s, p) in enumerate(CHAIN):
+        Din = occ.shape[1]
+        pad = torch.zeros((B, Din, TH * 16 + 2, W + 10), dtype=torch.bool)
+        pad[:, :, 1:H + 1, 1:W + 1] = occ  # +1: index -1 -> 0
+        want = torch.zeros((B, Din, TH, TW, 3), dtype=torch.bool)
+        for th in range(TH):
+            rows = pad[:, :, th * 16: th * 16 + 18].any(dim=2)
+            for tw in range(TW):
+                for kw in range(3):
+                    want[:, :, th, tw, kw] = rows[:, :, tw * 8 + kw: tw * 8 + kw + 8].any(dim=2)
+        tables.append(want)
+        Dout = (Din + 2 * p - 3) // s + 1
+        nxt = torch.zeros((B, Dout, H, W), dtype=torch.bool)
+        grown = torch.nn.functional.max_pool2d(occ.float(), 3, 1, 1).bool()  # rows/cols +-1
+        for d in range(Dout):
+            for kd in range(3):
+                q = d * s - p + kd
+                if 0 <= q < Din:
+                    nxt[:, d] |= grown[:, q]
+        occ = nxt
+    return tables
+
+
+def test_mark_boxes_matches_brute_force(cuda_device):
+    """vn_conv3d_mark_boxes == brute-force dilation for all three layers, incl. tile borders and grid corners."""
+    from voxelnet_pytorch_b200 import ops
+
+    g = torch.Generator().manual_seed(5)
+    B, D, H, W = 2, 10, 200, 240
+    K = 700
+    flat = torch.randperm(B * D * H * W, generator=g)[:K]
+    coords = torch.stack([flat // (D * H * W), (flat // (H * W)) % D, (flat // W) % H, flat % W], 1)
+    coords[:8, 2:] = torch.tensor([[0, 0], [H - 1, W - 1], [15, 7], [16, 8], [17, 9], [31, 239], [199, 0], [0, 239]])
+    coords[8:12, 1] = torch.tensor([0, 9, 0, 9])
+    coords = torch.unique(coords, dim=0)
+    dins = [10, 5, 3]
+    flags = [ops.conv3d_new_box_flags(B, d, H, W, cuda_device) for d in dins]
+    ops.conv3d_mark_boxes(coords.to(cuda_device), B, D, H, W, CHAIN, flags)
+    want = _brute_force_flags(coords, B, D, H, W)
+    TH, TW = (H + 15) // 16, W // 8
+    for l in range(3):
+        got = flags[l].cpu().view(B, dins[l], TH, TW, 3).bool()
+        assert torch.equal(got, want[l]), "layer %d: %d boxes differ" % (l, int((got != want[l]).sum()))
+
+
 @pytest.mark.parametrize("density", [0.0, 0.002, 0.05])
 def test_conv1_with_box_flags_equals_dense_run(cuda_device, density):
     """Skipping all-zero input boxes is exact: conv-1 with the occupancy table == conv-1 without it,
@@ -132,9 +187,10 @@ def test_conv1_with_box_flags_equals_dense_run(cuda_device, density):
     vw = torch.randn((max(K, 1), 128), generator=g)[:K]
     dense = torch.empty((B, D, H, W, 128), dtype=torch.bfloat16, device=cuda_device)
     ops.fill_zero(dense)
-    flags = torch.zeros(ops.conv3d_box_flags_bytes(B, D, H, W), dtype=torch.uint8, device=cuda_device)
+    flags = ops.conv3d_new_box_flags(B, D, H, W, cuda_device)
     if K:
-        ops.scatter_dense_bf16(vw.to(cuda_device), idx.to(cuda_device), dense, box_flags=flags)
+        ops.scatter_dense_bf16(vw.to(cuda_device), idx.to(cuda_device), dense)
+        ops.conv3d_mark_boxes(idx.to(cuda_device), B, D, H, W, CHAIN[:1], [flags])
     m = vn.ConvMD(3, cin, cout, 3, stride, padding).eval()
     load_state(m, sd, "middle_layer.0.")
     m = m.to(cuda_device)
@@ -142,6 +198,59 @@ def test_conv1_with_box_flags_equals_dense_run(cuda_device, density):
     full = ops.conv3d_bn_relu_fwd(dense, packed, scale, shift, 2, 1)
     skip = ops.conv3d_bn_relu_fwd(dense, packed, scale, shift, 2, 1, box_flags=flags)
     assert torch.equal(full.view(torch.int16), skip.view(torch.int16))
+    skip2 = ops.conv3d_bn_relu_fwd(dense, packed, scale, shift, 2, 1, box_flags=flags, consume_flags=True)
+    assert torch.equal(full.view(torch.int16), skip2.view(torch.int16))
+    assert int(flags.sum()) == 0  # consumed
     want = OM.conv_md3(dense.float().cpu().permute(0, 4, 1, 2, 3), sd, "middle_layer.0.", stride, padding)
     got = skip.float().permute(0, 4, 1, 2, 3).cpu()
     assert rel_max_err(got, want) < BF16_TOL
+
+
+@pytest.mark.parametrize("density,H,W", [(0.0, 40, 24), (0.003, 56, 40), (0.02, 40, 48), (0.3, 33, 16)])
+def test_background_delta_chain_matches_dense_chain(cuda_device, density, H, W):
+    """The sparse chain (live-box skipping in all three layers, activations stored as deviations from
+    the layer backgrounds, border-class shift tables) == the dense plain chain up to bf16 rounding of
+    the intermediate activations, and within the bf16 tolerance of the fp32 oracle.  Voxels are forced
+    onto the grid corners and edges so every border class is exercised; H is not a tile multiple."""
+    import voxelnet_pytorch_b200 as vn
+    from voxelnet_pytorch_b200 import ops
+
+    g = torch.Generator().manual_seed(40)
+    sd = OM.random_state_dict(41)
+    B, D = 2, 10
+    occ = torch.rand((B, D, H, W), generator=g) < density
+    if density > 0:
+        occ[0, 3, 0, 0] = occ[0, 0, H - 1, W - 1] = occ[0, 9, 0, W - 1] = occ[0, 5, H - 1, 0] = True
+        occ[1, 4, 0, W // 2] = occ[1, 4, H // 2, 0] = True
+        occ[1, :, :, : W // 2] &= torch.rand((D, H, W // 2), generator=g) < 0.2
+    idx = occ.nonzero().contiguous()
+    K = idx.shape[0]
+    vw = (torch.randn((max(K, 1), 128), generator=g)[:K]).abs()  # voxel-wise features are post-ReLU maxima
+    dense = torch.empty((B, D, H, W, 128), dtype=torch.bfloat16, device=cuda_device)
+    ops.fill_zero(dense)
+    dins = [10, 5, 3]
+    flags = [ops.conv3d_new_box_flags(B, d, H, W, cuda_device) for d in dins]
+    if K:
+        ops.scatter_dense_bf16(vw.to(cuda_device), idx.to(cuda_device), dense)
+        ops.conv3d_mark_boxes(idx.to(cuda_device), B, D, H, W, CHAIN, flags)
+    net = vn.MiddleConvNet().eval()
+    load_state(net, sd, "")
+    net = net.to(cuda_device)
+    plain = net(dense).cpu()
+
+    x, bg, din = dense, None, D
+    for i, layer in enumerate(net.middle_layer):
+        packed, scale, shift = layer.folded()
+        table, bg_out = ops.conv3d_fold_background(layer.conv.weight, din, layer.stride[0], layer.padding[0], scale, shift, bg)
+        last = i == 2
+        x = ops.conv3d_bn_relu_fwd(x, packed, scale, table if i else shift, layer.stride[0], layer.padding[0], final=last,
+                                   box_flags=flags[i], consume_flags=True, border_ring=last, sub=None if last else bg_out)
+        din, bg = bg_out.shape[0], bg_out
+    sparse = x.cpu()
+    assert all(int(f.sum()) == 0 for f in flags)
+    want = OM.middle_layers(dense.float().cpu(), sd)
+    assert sparse.shape == plain.shape == want.shape
+    assert rel_max_err(sparse, want) < BF16_TOL
+    assert rel_max_err(sparse, plain) < 6e-3  # both carry independent bf16 rounding of two activations
+    rel_l2 = float((sparse - want).norm() / want.norm())
+    assert rel_l2 < 5e-3, rel_l2

@@ -69,38 +69,3 @@ def test_feature_learning_net_forward(cuda_device):
     assert got.shape == want.shape == (2, 10, 200, 240, 128)
     assert torch.equal(got != 0, want != 0) or float((got - want).abs().max()) < 1e-4
     assert torch.allclose(got, want, rtol=1e-4, atol=1e-5)
-
-
-def test_box_flags_match_brute_force(cuda_device):
-    """The conv input-box occupancy table written by the scatter kernel == brute force over the grid."""
-    from voxelnet_pytorch_b200 import ops
-
-    g = torch.Generator().manual_seed(5)
-    B, D, H, W, C = 2, 10, 200, 240, 128
-    K = 900
-    flat = torch.randperm(B * D * H * W, generator=g)[:K]
-    # force voxels onto tile borders and grid corners
-    coords = torch.stack([flat // (D * H * W), (flat // (H * W)) % D, (flat // W) % H, flat % W], 1)
-    coords[:8, 2:] = torch.tensor([[0, 0], [H - 1, W - 1], [15, 7], [16, 8], [17, 9], [31, 239], [199, 0], [0, 239]])
-    coords = torch.unique(coords, dim=0)
-    K = coords.shape[0]
-    dense = torch.empty((B, D, H, W, C), dtype=torch.bfloat16, device=cuda_device)
-    ops.fill_zero(dense)
-    n = ops.conv3d_box_flags_bytes(B, D, H, W)
-    TH, TW = (H + 15) // 16, W // 8
-    assert n == B * D * TH * TW * 3
-    flags = torch.zeros(n, dtype=torch.uint8, device=cuda_device)
-    vw = torch.randn((K, C), generator=g)
-    ops.scatter_dense_bf16(vw.to(cuda_device), coords.to(cuda_device), dense, box_flags=flags)
-    got = flags.cpu().view(B, D, TH, TW, 3).bool()
-    occ = torch.zeros((B, D, TH * 16 + 2, W + 10), dtype=torch.bool)
-    occ[coords[:, 0], coords[:, 1], coords[:, 2] + 1, coords[:, 3] + 1] = True  # +1: index -1 -> 0
-    want = torch.zeros_like(got)
-    for th in range(TH):
-        rows = occ[:, :, th * 16: th * 16 + 18].any(dim=2)
-        for tw in range(TW):
-            for kw in range(3):
-                want[:, :, th, tw, kw] = rows[:, :, tw * 8 + kw: tw * 8 + kw + 8].any(dim=2)
-    assert torch.equal(got, want)
-    ops.scatter_dense_bf16(None, coords.to(cuda_device), dense, clear=True, box_flags=flags)
-    assert int(flags.sum()) == 0 and int(dense.view(torch.int16).ne(0).sum()) == 0

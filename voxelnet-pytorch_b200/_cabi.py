@@ -14,7 +14,9 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 1
+VN_ABI_VERSION = 2
+VN_CONV_FLAGS_CONSUME = 1
+VN_CONV_FLAGS_BORDER_RING = 2
 
 
 class VnGrid(C.Structure):
@@ -46,11 +48,14 @@ PROTOTYPES = {
     "vn_voxelize_svfe_fused": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vn_fill_zero": (C.c_int, [_p, _sz, _p]),
     "vn_scatter_dense_f32": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p]),
-    "vn_scatter_dense_bf16": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _i32, _p]),
+    "vn_scatter_dense_bf16": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p]),
     "vn_conv3d_packed_weight_bytes": (_sz, [_i32]),
     "vn_conv3d_pack_weights": (C.c_int, [_p, _i32, _i32, _p, _p]),
     "vn_conv3d_box_flags_bytes": (_sz, [_i32, _i32, _i32, _i32]),
-    "vn_conv3d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p, _p]),
+    "vn_conv3d_workspace_bytes": (_sz, [_i32, _i32, _i32]),
+    "vn_conv3d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _i32, _p, _p, _i32, _p, _sz, _p]),
+    "vn_conv3d_fold_background": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p]),
+    "vn_conv3d_mark_boxes": (C.c_int, [_p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "vn_launch_count": (_i64, []),
 }
 

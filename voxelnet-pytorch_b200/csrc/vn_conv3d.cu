@@ -4,31 +4,35 @@
 //
 // GEMM view: M = output positions, N = 64 output channels, K = 27 taps x Cin.
 //
-// Tiling (DESIGN.md "Conv3d"): one CTA owns a 16 (h) x 8 (w) spatial tile for ALL output depths of
-// one frame: Dout accumulators of 128 x 64 fp32 live side by side in TMEM (64 columns each, depth
-// ascending).
+// Units of work (DESIGN.md "Conv3d"):
+//   tile         16 (h) x 8 (w) output positions of one frame, all output depths: up to Dout
+//                accumulators of 128 x 64 fp32 in TMEM (64 columns each).
+//   input box    what one (tile, input plane p, kw) needs: 64 ch x 8 w x 18 h (h-halo'd, shifted by
+//                kw-1 in w) - ONE TMA box, 128-byte rows, SWIZZLE_128B.  The three kh taps read it at
+//                +kh*1024 B (one image row of the tile = one 8-row swizzle atom).  H / W borders are
+//                TMA out-of-bounds zero fill.
+//   live box     a box that may hold anything other than the input's background value (all-zero for
+//                the scattered voxel grid).  Dead boxes are never loaded or multiplied; what they
+//                would have contributed is a per-channel constant folded into the epilogue's shift
+//                table (see k_fold_background).  Without a flag table every box is live.
+//   group        consecutive tiles of one tile row whose *touched* accumulators (those fed by at
+//                least one live box) fit the 8 TMEM slots.  A group shares one pass over the weights:
+//                for each (64-channel chunk, kw) the 72 KB of weights of that pass are made resident
+//                in shared memory once and every live box of every tile in the group is multiplied
+//                against them.  k_conv3d_plan builds the groups on the device; the persistent CTAs
+//                pull them from an atomic counter (sparse scenes are badly balanced otherwise).
 //
-// K loop: for each (64-channel chunk, kw) - 6 or 3 passes - the 72 KB of weights of that pass are
-// made resident in shared memory (one bulk copy, double buffered) and the INPUT planes are walked in
-// ascending order.  An input plane p feeds output depth d' = (p + pad_d - kd) / stride_d for every
-// valid kd; those d' are consecutive, so the depth taps of one plane are fused along N: ONE
-// tcgen05.mma of shape 128 x (64*nkd) x 16 multiplies the A tile with the nkd weight tiles laid side
-// by side and lands in nkd adjacent accumulators.  This reads the A operand from shared memory once
-// instead of nkd times (N = 64 alone is shared-memory-bandwidth bound: 6 KB of operands per 32
-// tensor cycles).  Per tile the kernel pulls 432/216 KB of weights (each exactly once) plus one A
-// box per (plane, chunk, kw) from L2.  In the last pass accumulators complete in ascending depth
-// order, so the epilogue drains d' while the tensor core finishes d'+1.. and starts the next tile.
+// An input plane p feeds output depth d' = (p + pad_d - kd) / stride_d for every valid kd; those d'
+// are consecutive, so the depth taps of one plane are fused along N: ONE tcgen05.mma of shape
+// 128 x (64*nkd) x 16 multiplies the A tile with the nkd weight tiles laid side by side and lands in
+// nkd adjacent accumulators (A is read from shared memory once instead of nkd times; N = 64 alone is
+// shared-memory-bandwidth bound).
 //
-//   A operand: per (plane, 64-channel chunk, kw) ONE TMA box of 64 ch x 8 w x 18 h (an h-halo'd
-//              tile, 128-byte rows, SWIZZLE_128B).  The three kh taps read it at +kh*1024 B: one
-//              image row of the tile is exactly one 8-row swizzle atom, so every tap start stays
-//              atom-aligned.  Out-of-range h / w / (skipped) d are the convolution's zero padding,
-//              supplied by TMA's out-of-bounds zero fill.
 //   B operand: weights pre-packed as [chunk][kw][kd class][kh][kd descending = d' ascending] K-major
 //              [64 n x 64 k] tiles already in the swizzled shared-memory image.
-//   Warp roles: warp 0 = TMA producer, warp 1 = TMEM allocator + MMA issuer (both run warp-uniform
-//              control flow and elect one lane for the asynchronous instructions), warps 2..5 =
-//              epilogue (TMEM -> registers -> scale/shift/ReLU -> global).
+//   Warp roles: warp 0 = scheduler + TMA producer, warp 1 = TMEM allocator + MMA issuer (both run
+//              warp-uniform control flow and elect one lane for the asynchronous instructions),
+//              warps 2..5 = epilogue (TMEM -> registers -> scale/shift/ReLU -> global).
 #include <cuda.h>
 #include <cuda_bf16.h>
 
@@ -42,66 +46,92 @@ constexpr int kHaloH = kTileH + 2;
 constexpr uint32_t kABytes = kHaloH * kTileW * 128;  // 18432: 144 rows of 64 bf16
 constexpr uint32_t kBTapBytes = 64 * 128;            // 8192: [64 n][64 k] bf16
 constexpr uint32_t kBSlotBytes = 9 * kBTapBytes;     // all weights of one (chunk, kw): 3 kh x 3 kd tiles = 72 KB
-constexpr int kNA = 4, kNB = 2;                      // ring depths
-constexpr int kMaxDout = 8;                          // 8 x 64 = 512 TMEM columns
-constexpr int kMaxPlanes = 16;
+constexpr int kNA = 4, kNB = 2, kSched = 4;          // ring depths: A boxes, weight passes, group ids
+constexpr int kSlots = 8;                            // 8 x 64 = 512 TMEM columns
+constexpr int kMaxPlanes = 10;                       // live mask = 3 bits per plane in a uint32
+constexpr int kMaxGroupTiles = 8;
+constexpr int kMaxTilesW = 128;
+constexpr int kMaxTableRows = 27;                    // shift-table rows (variants x Dout) kept in smem
 constexpr int kThreads = 6 * 32;
 constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBSlotBytes;  // 221184
-constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + 1024 /*barriers, params*/;
 
 // What one input plane contributes (host-computed; see plan_planes()).
 struct PlaneInfo {
   int32_t nkd;        // number of valid depth taps (0: plane unused)
   int32_t dmin;       // first output depth fed; tap j feeds dmin + j
-  int32_t new_acc;    // output depth whose FIRST contribution comes from this plane, or -1
   uint32_t woff;      // byte offset of this plane's first weight tile inside a (chunk, kw) weight group
   uint32_t wstride;   // bytes between the kh = 0, 1, 2 tile rows of the plane's kd class
-  int32_t done_mask;  // bit d set: accumulator d is complete after this plane
 };
+
+// Work plan in the caller's workspace: header | groups[n_tiles] | tiles[n_tiles].
+struct PlanHeader {
+  int32_t n_groups;    // written by k_conv3d_plan (zeroed before it)
+  int32_t next_group;  // the conv kernel's work counter (zeroed before it)
+  int32_t pad[2];
+};
+struct GroupDesc {
+  int32_t tile0;   // first tile (global tile index = (b * tiles_h + th) * tiles_w + tw)
+  int32_t ntiles;  // consecutive tiles of the same tile row
+};
+struct TilePlan {
+  uint32_t live;    // bit p*3 + kw: input box (p, kw) of this tile is live
+  uint8_t touched;  // bit d: accumulator d receives at least one live box
+  uint8_t slot0;    // first TMEM slot of the tile inside its group; accumulator d sits at
+                    // slot0 + popcount(touched & ((1 << d) - 1))
+  uint8_t nslots;   // popcount(touched)
+  uint8_t pad;
+};
+static_assert(sizeof(TilePlan) == 8 && sizeof(GroupDesc) == 8 && sizeof(PlanHeader) == 16, "plan layout");
 
 struct ConvParams {
   int B, Din, Dout, H, W;
   int nchunk;      // Cin / 64
   int tiles_h, tiles_w, n_tiles;
   int out_mode;    // 0: bf16 NDHWC, 1: f32 [B, 64*Dout, H, W] with channel = c*Dout + d
+  int nvar;        // 1: shift rows [Dout][64]; 9: [3 h-classes][3 w-classes][Dout][64]
   const uint8_t* wpack;
-  const uint8_t* box_flags;  // [B][Din][tiles_h][tiles_w][3] or nullptr
-  const float* scale;
-  const float* shift;
+  const float* scale;   // [64]
+  const float* table;   // [nvar][Dout][64] (or [64] when table_plain)
+  int table_plain;      // table is a plain [64] shift vector used for every row
+  const float* sub;     // [Dout][64] subtracted after the ReLU, or nullptr
   void* out;
+  PlanHeader* hdr;
+  const GroupDesc* groups;
+  const TilePlan* tiles;
   PlaneInfo plane[kMaxPlanes];
 };
 
-struct Barriers {
+struct PlanParams {
+  int B, Din, Dout, H, W, tiles_h, tiles_w;
+  uint8_t* box_flags;  // [B][Din][tiles_h][tiles_w][3] or nullptr (every box live)
+  int consume;         // reset the flags that were read
+  int force_ring;      // boxes containing an H/W border position are live (input deviates there)
+  PlanHeader* hdr;
+  GroupDesc* groups;
+  TilePlan* tiles;
+  PlaneInfo plane[kMaxPlanes];
+};
+
+struct Control {
   uint64_t full_a[kNA], empty_a[kNA];
   uint64_t full_b[kNB], empty_b[kNB];
-  uint64_t acc_full[kMaxDout], acc_empty[kMaxDout];
+  uint64_t acc_full[kSlots], acc_empty[kSlots];
+  uint64_t sched_full[kSched], sched_empty[kSched];
+  int32_t sched[kSched];
   uint32_t tmem_base;
-  uint32_t pad;
-  float scale[64], shift[64];
+  uint32_t pad[3];
+  float scale[64];
+  float sub[kSlots * 64];
+  float table[kMaxTableRows * 64];
 };
-static_assert(sizeof(Barriers) <= 1024, "barrier block too large");
+constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + (uint32_t)sizeof(Control);
+static_assert(kSmemBytes <= 232448, "shared memory budget (227 KB)");
 
-// Which input boxes of a tile can hold non-zero data: bit (p*3 + kw).  Without a flag table every
-// box is live.  With one (written by vn_scatter_dense_bf16 from the voxel coordinates), a zero flag
-// guarantees the 18 x 8 box of plane p at w-shift kw is all zeros, so its TMA load and MMAs are
-// skipped - exact, since zero operands contribute nothing.  All 32 lanes must call this.
-template <bool kSkip>
-__device__ __forceinline__ uint64_t live_boxes(const ConvParams& P, int b, int th, int tw, uint32_t lane) {
-  if (!kSkip) return ~0ull;
-  uint64_t m = 0;
-  if ((int)lane < P.Din) {
-    const uint8_t* f = P.box_flags + ((((size_t)b * P.Din + lane) * P.tiles_h + th) * P.tiles_w + tw) * 3;
-    const uint32_t bits = (f[0] ? 1u : 0u) | (f[1] ? 2u : 0u) | (f[2] ? 4u : 0u);
-    m = (uint64_t)bits << (3 * lane);
-  }
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) m |= __shfl_xor_sync(0xffffffffu, m, d);
-  return m;
-}
+__host__ __device__ __forceinline__ uint32_t kw_bits(int kw) { return 0x09249249u << kw; }  // bits kw, kw+3, ...
 
-// Accumulators (bit d) that receive at least one live box in this tile.
-__device__ __forceinline__ uint32_t touched_accumulators(const ConvParams& P, uint64_t live) {
+// Accumulators (bit d) fed by at least one live box.
+template <typename Params>
+__device__ __forceinline__ uint32_t touched_accumulators(const Params& P, uint32_t live) {
   uint32_t t = 0;
   for (int p = 0; p < P.Din; ++p) {
     const PlaneInfo& pi = P.plane[p];
@@ -110,8 +140,79 @@ __device__ __forceinline__ uint32_t touched_accumulators(const ConvParams& P, ui
   return t;
 }
 
-// kSkip = false compiles the occupancy logic away for dense inputs (conv-2, conv-3, drop-in calls).
-template <bool kSkip>
+__device__ __forceinline__ uint32_t warp_or(uint32_t v) {
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) v |= __shfl_xor_sync(0xffffffffu, v, d);
+  return v;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Plan: one block per (frame, tile row).  Phase 1 turns the flag bytes into per-tile live masks,
+// phase 2 (one thread, <= 128 tiles) packs consecutive tiles into groups of <= 8 TMEM slots.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ PlanParams Q) {
+  __shared__ uint32_t s_live[kMaxTilesW];
+  __shared__ uint8_t s_touched[kMaxTilesW], s_slot0[kMaxTilesW];
+  const int b = blockIdx.x / Q.tiles_h, th = blockIdx.x % Q.tiles_h;
+  uint32_t valid = 0;
+  for (int p = 0; p < Q.Din; ++p)
+    if (Q.plane[p].nkd != 0) valid |= 7u << (p * 3);
+  // rows 16*th-1 .. 16*th+16 of this tile row's boxes
+  const bool ring_h = Q.force_ring && (th == 0 || (16 * th - 1 <= Q.H - 1 && Q.H - 1 <= 16 * th + 16));
+  for (int tw = threadIdx.x; tw < Q.tiles_w; tw += blockDim.x) {
+    uint32_t live = 0;
+    if (Q.box_flags != nullptr) {
+      for (int p = 0; p < Q.Din; ++p) {
+        uint8_t* f = Q.box_flags + ((((size_t)b * Q.Din + p) * Q.tiles_h + th) * Q.tiles_w + tw) * 3;
+        const uint32_t bits = (f[0] ? 1u : 0u) | (f[1] ? 2u : 0u) | (f[2] ? 4u : 0u);
+        live |= bits << (p * 3);
+        if (Q.consume && bits) { f[0] = 0; f[1] = 0; f[2] = 0; }
+      }
+      if (ring_h) live = ~0u;
+      if (Q.force_ring && tw == 0) live |= kw_bits(0) | kw_bits(1);                // columns -1..6, 0..7 hold column 0
+      if (Q.force_ring && tw == Q.tiles_w - 1) live |= kw_bits(1) | kw_bits(2);    // ... column W-1
+    } else {
+      live = ~0u;
+    }
+    live &= valid;
+    s_live[tw] = live;
+    s_touched[tw] = (uint8_t)touched_accumulators(Q, live);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int start = 0, cur_slots = 0, cur_n = 0;
+    const int tile_row0 = (b * Q.tiles_h + th) * Q.tiles_w;
+    for (int tw = 0; tw < Q.tiles_w; ++tw) {
+      const int n = __popc((uint32_t)s_touched[tw]);
+      if (cur_n > 0 && (cur_slots + n > kSlots || cur_n == kMaxGroupTiles)) {
+        const int g = atomicAdd(&Q.hdr->n_groups, 1);
+        Q.groups[g] = GroupDesc{tile_row0 + start, cur_n};
+        start = tw; cur_slots = 0; cur_n = 0;
+      }
+      s_slot0[tw] = (uint8_t)cur_slots;
+      cur_slots += n;
+      ++cur_n;
+    }
+    if (cur_n > 0) {
+      const int g = atomicAdd(&Q.hdr->n_groups, 1);
+      Q.groups[g] = GroupDesc{tile_row0 + start, cur_n};
+    }
+  }
+  __syncthreads();
+  for (int tw = threadIdx.x; tw < Q.tiles_w; tw += blockDim.x) {
+    TilePlan tp;
+    tp.live = s_live[tw];
+    tp.touched = s_touched[tw];
+    tp.slot0 = s_slot0[tw];
+    tp.nslots = (uint8_t)__popc((uint32_t)s_touched[tw]);
+    tp.pad = 0;
+    Q.tiles[(size_t)(b * Q.tiles_h + th) * Q.tiles_w + tw] = tp;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// The convolution.
+// ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(kThreads, 1)
     k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ ConvParams P) {
   extern __shared__ uint8_t smem_raw[];
@@ -119,104 +220,144 @@ __global__ void __launch_bounds__(kThreads, 1)
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kNA * kABytes;
-  Barriers* bar = reinterpret_cast<Barriers*>(smem + kSmemData);
+  Control* ctl = reinterpret_cast<Control*>(smem + kSmemData);
 
   const uint32_t warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t acc_cols = (uint32_t)P.Dout * 64;
-  const uint32_t tmem_cols = acc_cols <= 32 ? 32 : (acc_cols <= 64 ? 64 : (acc_cols <= 128 ? 128 : (acc_cols <= 256 ? 256 : 512)));
 
   if (threadIdx.x == 0) {
-    for (int i = 0; i < kNA; ++i) { mbar_init(&bar->full_a[i], 1); mbar_init(&bar->empty_a[i], 1); }
-    for (int i = 0; i < kNB; ++i) { mbar_init(&bar->full_b[i], 1); mbar_init(&bar->empty_b[i], 1); }
-    for (int i = 0; i < kMaxDout; ++i) { mbar_init(&bar->acc_full[i], 1); mbar_init(&bar->acc_empty[i], 4); }
+    for (int i = 0; i < kNA; ++i) { mbar_init(&ctl->full_a[i], 1); mbar_init(&ctl->empty_a[i], 1); }
+    for (int i = 0; i < kNB; ++i) { mbar_init(&ctl->full_b[i], 1); mbar_init(&ctl->empty_b[i], 1); }
+    for (int i = 0; i < kSlots; ++i) { mbar_init(&ctl->acc_full[i], 1); mbar_init(&ctl->acc_empty[i], 4); }
+    for (int i = 0; i < kSched; ++i) { mbar_init(&ctl->sched_full[i], 1); mbar_init(&ctl->sched_empty[i], 5); }
     mbar_fence_init();
     fence_proxy_async_smem();
     tma_prefetch_desc(&tmap_x);
   }
-  if (threadIdx.x >= 64 && threadIdx.x < 128) {
-    bar->scale[threadIdx.x - 64] = P.scale[threadIdx.x - 64];
-    bar->shift[threadIdx.x - 64] = P.shift[threadIdx.x - 64];
+  if (threadIdx.x >= 64) {
+    const int t = threadIdx.x - 64;  // 0..127
+    if (t < 64) ctl->scale[t] = P.scale[t];
+    const int nrow = P.nvar * P.Dout;
+    for (int i = t; i < nrow * 64; i += 128) ctl->table[i] = P.table_plain ? P.table[i & 63] : P.table[i];
+    for (int i = t; i < P.Dout * 64; i += 128) ctl->sub[i] = P.sub != nullptr ? P.sub[i] : 0.0f;
   }
   if (warp == 1) {
-    tmem_alloc(&bar->tmem_base, tmem_cols);
+    tmem_alloc(&ctl->tmem_base, kSlots * 64);
     tmem_relinquish();
   }
   tc_fence_before_sync();
   __syncthreads();
   tc_fence_after_sync();
-  const uint32_t tmem_base = bar->tmem_base;
+  const uint32_t tmem_base = ctl->tmem_base;
+  const int n_groups = P.hdr->n_groups;
 
   if (warp == 0) {
-    // ===================== TMA producer (warp-uniform; one elected lane issues) =====================
-    uint32_t a_it = 0, b_it = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      const int tw = tile % P.tiles_w;
-      const int th = (tile / P.tiles_w) % P.tiles_h;
-      const int b = tile / (P.tiles_w * P.tiles_h);
-      const int h0 = th * kTileH, w0 = tw * kTileW;
-      const uint64_t live = live_boxes<kSkip>(P, b, th, tw, lane);
+    // ============ scheduler + TMA producer (warp-uniform; one elected lane issues) ============
+    uint32_t a_it = 0, b_it = 0, s_it = 0;
+    for (;;) {
+      const uint32_t ss = s_it % kSched;
+      mbar_wait(&ctl->sched_empty[ss], ((s_it / kSched) & 1) ^ 1);
+      int g = 0;
+      if (lane == 0) {
+        g = atomicAdd(&P.hdr->next_group, 1);
+        if (g >= n_groups) g = -1;
+        ctl->sched[ss] = g;
+        mbar_arrive(&ctl->sched_full[ss]);
+      }
+      g = __shfl_sync(0xffffffffu, g, 0);
+      ++s_it;
+      if (g < 0) break;
+      const GroupDesc gd = P.groups[g];
+      const uint32_t mylive = (int)lane < gd.ntiles ? P.tiles[gd.tile0 + lane].live : 0u;
+      const uint32_t any = warp_or(mylive);
+      const int tw0 = gd.tile0 % P.tiles_w;
+      const int th = (gd.tile0 / P.tiles_w) % P.tiles_h;
+      const int b = gd.tile0 / (P.tiles_w * P.tiles_h);
+      const int h0 = th * kTileH;
       for (int c = 0; c < P.nchunk; ++c) {
         for (int kw = 0; kw < 3; ++kw) {
-          // all weights of this (chunk, kw): resident while the K loop walks the input planes
+          if (!(any & kw_bits(kw))) continue;  // no tile of the group has a live box at this w shift
+          // all weights of this (chunk, kw): resident while the group's live boxes stream through
           const uint32_t sb = b_it % kNB;
-          mbar_wait(&bar->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
+          mbar_wait(&ctl->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
           if (elect_one()) {
-            mbar_arrive_expect_tx(&bar->full_b[sb], kBSlotBytes);
+            mbar_arrive_expect_tx(&ctl->full_b[sb], kBSlotBytes);
             bulk_load_1d(smem_b + sb * kBSlotBytes, P.wpack + (size_t)(c * 3 + kw) * kBSlotBytes, kBSlotBytes,
-                         &bar->full_b[sb]);
+                         &ctl->full_b[sb]);
           }
           __syncwarp();
           ++b_it;
-          for (int p = 0; p < P.Din; ++p) {
-            if (P.plane[p].nkd == 0 || !((live >> (p * 3 + kw)) & 1)) continue;
-            const uint32_t sa = a_it % kNA;
-            mbar_wait(&bar->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
-            if (elect_one()) {
-              mbar_arrive_expect_tx(&bar->full_a[sa], kABytes);
-              tma_load_5d(smem_a + sa * kABytes, &tmap_x, &bar->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
+          for (int t = 0; t < gd.ntiles; ++t) {
+            uint32_t m = __shfl_sync(0xffffffffu, mylive, t) & kw_bits(kw);
+            const int w0 = (tw0 + t) * kTileW;
+            while (m) {
+              const int p = (__ffs(m) - 1) / 3;
+              m &= m - 1;
+              const uint32_t sa = a_it % kNA;
+              mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+              if (elect_one()) {
+                mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
+                tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
+              }
+              __syncwarp();
+              ++a_it;
             }
-            __syncwarp();
-            ++a_it;
           }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer (warp-uniform; one elected lane issues) =====================
-    uint32_t a_it = 0, b_it = 0;
-    uint32_t acc_phase = 0;  // bit d: parity of the number of tiles that used accumulator d so far
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      const int tw = tile % P.tiles_w;
-      const int th = (tile / P.tiles_w) % P.tiles_h;
-      const int b = tile / (P.tiles_w * P.tiles_h);
-      const uint64_t live = live_boxes<kSkip>(P, b, th, tw, lane);
-      const uint32_t touched = touched_accumulators(P, live);
-      uint32_t started = 0;  // accumulators that already hold a partial sum of this tile
+    uint32_t a_it = 0, b_it = 0, s_it = 0;
+    uint32_t acc_phase = 0;  // bit s: parity of the number of groups that used TMEM slot s so far
+    for (;;) {
+      const uint32_t ss = s_it % kSched;
+      mbar_wait(&ctl->sched_full[ss], (s_it / kSched) & 1);
+      const int g = ctl->sched[ss];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->sched_empty[ss]);
+      ++s_it;
+      if (g < 0) break;
+      const GroupDesc gd = P.groups[g];
+      TilePlan tp = TilePlan{0u, 0, 0, 0, 0};
+      if ((int)lane < gd.ntiles) tp = P.tiles[gd.tile0 + lane];
+      const uint32_t mylive = tp.live, mytouched = tp.touched, myslot0 = tp.slot0;
+      uint32_t mystarted = 0;  // lane t: accumulators of tile t that already hold a partial sum
+      const uint32_t any = warp_or(mylive);
+      const uint32_t used = warp_or(((1u << tp.nslots) - 1u) << tp.slot0);
+      const int last_kw = (any & kw_bits(2)) ? 2 : ((any & kw_bits(1)) ? 1 : 0);
       for (int c = 0; c < P.nchunk; ++c) {
         for (int kw = 0; kw < 3; ++kw) {
-          const bool last_pass = (c == P.nchunk - 1) & (kw == 2);
+          if (!(any & kw_bits(kw))) continue;
+          const bool last_pass = (c == P.nchunk - 1) & (kw == last_kw);
           const uint32_t sb = b_it % kNB;
-          mbar_wait(&bar->full_b[sb], (b_it / kNB) & 1);
+          mbar_wait(&ctl->full_b[sb], (b_it / kNB) & 1);
           tc_fence_after_sync();
           const uint32_t b_addr = smem_u32(smem_b + sb * kBSlotBytes);
-          for (int p = 0; p < P.Din; ++p) {
-            const PlaneInfo& pi = P.plane[p];
-            if (pi.nkd == 0) continue;
-            if ((live >> (p * 3 + kw)) & 1) {
+          for (int t = 0; t < gd.ntiles; ++t) {
+            uint32_t m = __shfl_sync(0xffffffffu, mylive, t) & kw_bits(kw);
+            const uint32_t touched = __shfl_sync(0xffffffffu, mytouched, t);
+            const uint32_t slot0 = __shfl_sync(0xffffffffu, myslot0, t);
+            uint32_t started = __shfl_sync(0xffffffffu, mystarted, t);
+            while (m) {
+              const int p = (__ffs(m) - 1) / 3;
+              m &= m - 1;
+              const PlaneInfo& pi = P.plane[p];
               const uint32_t range = ((1u << pi.nkd) - 1u) << pi.dmin;
               const uint32_t fresh = range & ~started;
+              const uint32_t slot_lo = slot0 + __popc(touched & ((1u << pi.dmin) - 1u));
               // Accumulators first touched here must have been drained by the epilogue, and need
               // accumulate=0 while already-started neighbours need 1: the first k-step is then issued
               // per accumulator (N = 64) instead of fused along N.
               if (fresh) {
-                for (int d = pi.dmin; d < pi.dmin + pi.nkd; ++d)
-                  if ((fresh >> d) & 1) mbar_wait(&bar->acc_empty[d], ((acc_phase >> d) & 1) ^ 1);
+                for (int j = 0; j < pi.nkd; ++j)
+                  if ((fresh >> (pi.dmin + j)) & 1)
+                    mbar_wait(&ctl->acc_empty[slot_lo + j], ((acc_phase >> (slot_lo + j)) & 1) ^ 1);
                 tc_fence_after_sync();
               }
-              const uint32_t d_tmem = tmem_base + (uint32_t)pi.dmin * 64;
+              const uint32_t d_tmem = tmem_base + slot_lo * 64;
               const uint32_t idesc_all = umma_idesc_bf16(128, 64 * pi.nkd);
               const uint32_t sa = a_it % kNA;
-              mbar_wait(&bar->full_a[sa], (a_it / kNA) & 1);
+              mbar_wait(&ctl->full_a[sa], (a_it / kNA) & 1);
               tc_fence_after_sync();
               const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
               if (elect_one()) {
@@ -236,95 +377,116 @@ __global__ void __launch_bounds__(kThreads, 1)
                     if (k >= k0) umma_bf16_ss(d_tmem, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc_all, 1);
                   }
                 }
-                umma_commit(&bar->empty_a[sa]);
+                umma_commit(&ctl->empty_a[sa]);
               }
               __syncwarp();
               started |= range;
               ++a_it;
             }
-            // accumulators whose last possible contribution is this plane of the last pass
-            if (last_pass && (pi.done_mask & touched) != 0) {
+            if ((int)lane == t) mystarted = started;
+            // last weight pass of the group: tile t has received everything it will get
+            if (last_pass && touched != 0) {
               if (elect_one()) {
-                for (int d = 0; d < P.Dout; ++d)
-                  if (((pi.done_mask & touched) >> d) & 1) umma_commit(&bar->acc_full[d]);
+                const int n = __popc(touched);
+                for (int j = 0; j < n; ++j) umma_commit(&ctl->acc_full[slot0 + j]);
               }
               __syncwarp();
             }
           }
-          if (elect_one()) umma_commit(&bar->empty_b[sb]);
+          if (elect_one()) umma_commit(&ctl->empty_b[sb]);
           __syncwarp();
           ++b_it;
         }
       }
-      acc_phase ^= touched;
+      acc_phase ^= used;
     }
   } else {
     // ===================== epilogue (warps 2..5) =====================
     const uint32_t quad = warp & 3;                // TMEM lane quadrant this warp may read
     const uint32_t m = quad * 32 + lane;           // accumulator row = output position in the tile
     const int hl = m / kTileW, wl = m % kTileW;
-    uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-      const int tw = tile % P.tiles_w;
-      const int th = (tile / P.tiles_w) % P.tiles_h;
-      const int b = tile / (P.tiles_w * P.tiles_h);
-      const int h = th * kTileH + hl, w = tw * kTileW + wl;
-      const bool inside = h < P.H && w < P.W;
-      const uint32_t touched = touched_accumulators(P, live_boxes<kSkip>(P, b, th, tw, lane));
-      for (int dout = 0; dout < P.Dout; ++dout) {
-        const bool has_acc = (touched >> dout) & 1;  // else: no non-zero input reached this accumulator
-        if (has_acc) {
-          mbar_wait(&bar->acc_full[dout], (acc_phase >> dout) & 1);
-          tc_fence_after_sync();
-        }
-        const uint32_t taddr = tmem_base + ((quad * 32) << 16) + (uint32_t)dout * 64;
-#pragma unroll
-        for (int half = 0; half < 2; ++half) {
-          uint32_t r[32];
+    uint32_t s_it = 0, acc_phase = 0;
+    for (;;) {
+      const uint32_t ss = s_it % kSched;
+      mbar_wait(&ctl->sched_full[ss], (s_it / kSched) & 1);
+      const int g = ctl->sched[ss];
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->sched_empty[ss]);
+      ++s_it;
+      if (g < 0) break;
+      const GroupDesc gd = P.groups[g];
+      const int tw0 = gd.tile0 % P.tiles_w;
+      const int th = (gd.tile0 / P.tiles_w) % P.tiles_h;
+      const int b = gd.tile0 / (P.tiles_w * P.tiles_h);
+      const int h = th * kTileH + hl;
+      const bool inside = h < P.H;
+      const int vh = h == 0 ? 1 : (h == P.H - 1 ? 2 : 0);
+      uint32_t used = 0;
+      for (int t = 0; t < gd.ntiles; ++t) {
+        const TilePlan tp = P.tiles[gd.tile0 + t];
+        const uint32_t touched = tp.touched;
+        used |= ((1u << tp.nslots) - 1u) << tp.slot0;
+        const int w = (tw0 + t) * kTileW + wl;
+        const int vw = w == 0 ? 1 : (w == P.W - 1 ? 2 : 0);
+        const int variant = P.nvar == 9 ? vh * 3 + vw : 0;
+        for (int dout = 0; dout < P.Dout; ++dout) {
+          const bool has_acc = (touched >> dout) & 1;  // else: no live box reached this accumulator
+          const uint32_t slot = tp.slot0 + __popc(touched & ((1u << dout) - 1u));
           if (has_acc) {
-            tmem_ld_32x32b_x32(taddr + half * 32, r);
-            tmem_ld_wait();
-            if (half == 1) {
-              // accumulator fully read: hand it back to the MMA issuer before the global stores
-              tc_fence_before_sync();
-              __syncwarp();
-              if (lane == 0) mbar_arrive(&bar->acc_empty[dout]);
-            }
-          } else {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) r[j] = 0u;
+            mbar_wait(&ctl->acc_full[slot], (acc_phase >> slot) & 1);
+            tc_fence_after_sync();
           }
-          if (inside) {
-            float v[32];
+          const uint32_t taddr = tmem_base + ((quad * 32) << 16) + slot * 64;
+          const float* shift_row = ctl->table + (variant * P.Dout + dout) * 64;
+          const float* sub_row = ctl->sub + dout * 64;
 #pragma unroll
-            for (int j = 0; j < 32; ++j) {
-              const int c = half * 32 + j;
-              v[j] = fmaxf(fmaf(__uint_as_float(r[j]), bar->scale[c], bar->shift[c]), 0.0f);
-            }
-            if (P.out_mode == 0) {
-              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
-                                   ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32;
-#pragma unroll
-              for (int q = 0; q < 4; ++q) {
-                uint32_t pk[4];
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const __nv_bfloat162 t2 = __floats2bfloat162_rn(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1]);
-                  pk[e] = *reinterpret_cast<const uint32_t*>(&t2);
-                }
-                *reinterpret_cast<uint4*>(dst + q * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+          for (int half = 0; half < 2; ++half) {
+            uint32_t r[32];
+            if (has_acc) {
+              tmem_ld_32x32b_x32(taddr + half * 32, r);
+              tmem_ld_wait();
+              if (half == 1) {
+                // accumulator fully read: hand it back to the MMA issuer before the global stores
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&ctl->acc_empty[slot]);
               }
             } else {
-              const size_t plane = (size_t)P.H * P.W;
-              float* dst = reinterpret_cast<float*>(P.out) +
-                           ((size_t)b * 64 * P.Dout + (size_t)(half * 32) * P.Dout + dout) * plane + (size_t)h * P.W + w;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) dst[(size_t)j * P.Dout * plane] = v[j];
+              for (int j = 0; j < 32; ++j) r[j] = 0u;
+            }
+            if (inside) {
+              float v[32];
+#pragma unroll
+              for (int j = 0; j < 32; ++j) {
+                const int c = half * 32 + j;
+                v[j] = fmaxf(fmaf(__uint_as_float(r[j]), ctl->scale[c], shift_row[c]), 0.0f) - sub_row[c];
+              }
+              if (P.out_mode == 0) {
+                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
+                                     ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32;
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                  uint32_t pk[4];
+#pragma unroll
+                  for (int e = 0; e < 4; ++e) {
+                    const __nv_bfloat162 t2 = __floats2bfloat162_rn(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1]);
+                    pk[e] = *reinterpret_cast<const uint32_t*>(&t2);
+                  }
+                  *reinterpret_cast<uint4*>(dst + q * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+                }
+              } else {
+                const size_t plane = (size_t)P.H * P.W;
+                float* dst = reinterpret_cast<float*>(P.out) +
+                             ((size_t)b * 64 * P.Dout + (size_t)(half * 32) * P.Dout + dout) * plane + (size_t)h * P.W + w;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) dst[(size_t)j * P.Dout * plane] = v[j];
+              }
             }
           }
         }
       }
-      acc_phase ^= touched;
+      acc_phase ^= used;
     }
   }
 
@@ -332,7 +494,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   __syncthreads();
   if (warp == 1) {
     tc_fence_after_sync();
-    tmem_dealloc(tmem_base, tmem_cols);
+    tmem_dealloc(tmem_base, kSlots * 64);
   }
 }
 
@@ -347,9 +509,8 @@ struct KdClasses {
   uint32_t base[2];  // byte offset of the class inside a (chunk, kw) group
 };
 
-__host__ __device__ inline KdClasses kd_classes(int stride_d, int cin) {
+__host__ __device__ inline KdClasses kd_classes(int stride_d) {
   KdClasses k{};
-  (void)cin;
   if (stride_d == 1) {
     k.n_classes = 1;
     k.nkd[0] = 3; k.kd[0][0] = 2; k.kd[0][1] = 1; k.kd[0][2] = 0;
@@ -368,7 +529,7 @@ __host__ __device__ inline KdClasses kd_classes(int stride_d, int cin) {
 __global__ void __launch_bounds__(256)
     k_pack_weights(const float* __restrict__ w, int cin, int stride_d, uint8_t* __restrict__ packed) {
   const int nchunk = cin / 64;
-  const KdClasses kc = kd_classes(stride_d, cin);
+  const KdClasses kc = kd_classes(stride_d);
   const int total = 27 * cin * 64;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     int r = i;
@@ -389,14 +550,113 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// Per-plane schedule: which taps are valid, where their weights sit, which accumulators start/finish.
-int plan_planes(ConvParams& P, int cin, int stride_d, int pad_d) {
-  const KdClasses kc = kd_classes(stride_d, cin);
-  int first_plane[kMaxDout], last_plane[kMaxDout];
-  for (int d = 0; d < P.Dout; ++d) { first_plane[d] = -1; last_plane[d] = -1; }
+// Background folding.  When the layer's input is stored as a deviation from a per-(plane, channel)
+// background bg_in (what the previous layer outputs wherever ITS input was all background), the
+// background's own contribution to every output is a constant that depends only on the output depth
+// and on which taps fall outside the image (the reference zero-pads, so out-of-image taps see 0, not
+// the background): 3 h-classes (interior, h = 0, h = H-1) x 3 w-classes.  This kernel evaluates
+//   bias[v][d'][n] = sum over in-image taps (kd, kh, kw), channels c of bf16(W[n][c][kd][kh][kw]) * bg_in[p][c]
+// and writes the epilogue's shift table  table[v][d'][n] = bias * scale[n] + shift[n]  plus the layer's
+// own output background  bg_out[d'][n] = relu(table[interior][d'][n]).
+// One block per (variant, d'), one thread per output channel.
+__global__ void __launch_bounds__(64)
+    k_fold_background(const float* __restrict__ w, int cin, int Din, int Dout, int stride_d, int pad_d,
+                      const float* __restrict__ scale, const float* __restrict__ shift,
+                      const float* __restrict__ bg_in, float* __restrict__ table, float* __restrict__ bg_out) {
+  const int v = blockIdx.x / Dout, d = blockIdx.x % Dout, n = threadIdx.x;
+  const int vh = v / 3, vw = v % 3;
+  double acc = 0.0;
+  if (bg_in != nullptr) {
+    for (int kd = 0; kd < 3; ++kd) {
+      const int p = d * stride_d - pad_d + kd;
+      if (p < 0 || p >= Din) continue;
+      for (int kh = 0; kh < 3; ++kh) {
+        if ((vh == 1 && kh == 0) || (vh == 2 && kh == 2)) continue;
+        for (int kw = 0; kw < 3; ++kw) {
+          if ((vw == 1 && kw == 0) || (vw == 2 && kw == 2)) continue;
+          for (int c = 0; c < cin; ++c) {
+            const float wv = __bfloat162float(__float2bfloat16_rn(w[((((size_t)n * cin + c) * 3 + kd) * 3 + kh) * 3 + kw]));
+            acc += (double)wv * (double)bg_in[p * cin + c];
+          }
+        }
+      }
+    }
+  }
+  const float t = (float)(acc * (double)scale[n] + (double)shift[n]);
+  table[((size_t)v * Dout + d) * 64 + n] = t;
+  if (v == 0 && bg_out != nullptr) bg_out[d * 64 + n] = fmaxf(t, 0.0f);
+}
+
+// Voxel coordinates -> live-box flags of a chain of up to three stacked 3x3x3 layers.  A voxel at
+// (z, y, x) makes the input of layer l deviate from its background at most at planes S_l (S_0 = {z},
+// S_{l+1} = output depths fed by S_l), rows y-l..y+l and columns x-l..x+l; every box (plane, th, tw, kw)
+// of layer l that contains such a position is flagged.  One warp per voxel.
+struct MarkParams {
+  int B, D, H, W, tiles_h, tiles_w, n_layers;
+  int Din[3], stride_d[3], pad_d[3];
+  uint8_t* flags[3];
+};
+
+__global__ void __launch_bounds__(256)
+    k_mark_boxes(const long long* __restrict__ coords, int64_t K, const int32_t* __restrict__ n_voxels_dev,
+                 const __grid_constant__ MarkParams Q) {
+  int64_t total = K;
+  if (n_voxels_dev != nullptr) {
+    const int64_t live = *n_voxels_dev;
+    if (live < total) total = live;
+  }
+  const uint32_t lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  for (int64_t r = warp; r < total; r += nwarps) {
+    const long long* c = coords + r * 4;
+    const long long cb = c[0], cz = c[1], cy = c[2], cx = c[3];
+    if (cb < 0 || cb >= Q.B || cz < 0 || cz >= Q.D || cy < 0 || cy >= Q.H || cx < 0 || cx >= Q.W) continue;
+    const int b = (int)cb, y = (int)cy, x = (int)cx;
+    uint32_t planes = 1u << (int)cz;
+    for (int l = 0; l < Q.n_layers; ++l) {
+      const int Din = Q.Din[l];
+      // rows [y-l, y+l] meet box rows [16 th - 1, 16 th + 16]
+      int th_lo = (y - l - 1) >> 4, th_hi = (y + l + 1) >> 4;
+      if (th_lo < 0) th_lo = 0;
+      if (th_hi > Q.tiles_h - 1) th_hi = Q.tiles_h - 1;
+      const int n_th = th_hi - th_lo + 1;
+      const int combos = __popc(planes) * n_th * 6;  // plane x th x kw x {first, second} tw candidate
+      for (int i = lane; i < combos; i += 32) {
+        const int cand = i % 2, kw = (i / 2) % 3, th = th_lo + (i / 6) % n_th;
+        const int p = (int)__fns(planes, 0, i / (6 * n_th) + 1);  // the n-th reachable plane
+        // columns [x-l, x+l] meet box columns [8 tw + kw - 1, 8 tw + kw + 6]
+        const int s_lo = x - l - 6 - kw, s_hi = x + l + 1 - kw;        // 8 tw in [s_lo, s_hi]
+        int tw = (s_lo + 7) >> 3;                                       // ceil(s_lo / 8)
+        if (tw < 0) tw = 0;
+        tw += cand;
+        if (tw * 8 > s_hi || tw > Q.tiles_w - 1) continue;
+        uint8_t* f = Q.flags[l] + ((((size_t)b * Din + p) * Q.tiles_h + th) * Q.tiles_w + tw) * 3 + kw;
+        if (*f == 0) *f = 1;
+      }
+      // planes of the next layer's input that this voxel can reach
+      if (l + 1 < Q.n_layers) {
+        const int Dn = Q.Din[l + 1];
+        uint32_t next = 0;
+        for (int d = 0; d < Dn; ++d)
+          for (int kd = 0; kd < 3; ++kd) {
+            const int p = d * Q.stride_d[l] - Q.pad_d[l] + kd;
+            if (p >= 0 && p < Din && ((planes >> p) & 1)) next |= 1u << d;
+          }
+        planes = next;
+      }
+    }
+  }
+}
+
+// Per-plane schedule: which taps are valid, where their weights sit.
+template <typename Params>
+int plan_planes(Params& P, int stride_d, int pad_d) {
+  const KdClasses kc = kd_classes(stride_d);
+  bool fed[kSlots] = {false, false, false, false, false, false, false, false};
   for (int p = 0; p < P.Din; ++p) {
     PlaneInfo& pi = P.plane[p];
-    pi = PlaneInfo{0, 0, -1, 0, 0, 0};
+    pi = PlaneInfo{0, 0, 0, 0};
     const int cls = stride_d == 1 ? 0 : (((p + pad_d) % 2 == 0) ? 0 : 1);
     int jfirst = -1, jlast = -1, dmin = 0;
     for (int j = 0; j < kc.nkd[cls]; ++j) {  // kd descending -> d ascending
@@ -408,8 +668,7 @@ int plan_planes(ConvParams& P, int cin, int stride_d, int pad_d) {
       if (jlast >= 0 && j != jlast + 1) return -1;  // taps must be contiguous
       jlast = j;
       if (d != dmin + (j - jfirst)) return -1;      // and feed consecutive depths
-      if (first_plane[d] < 0) first_plane[d] = p;
-      last_plane[d] = p;
+      fed[d] = true;
     }
     if (jfirst < 0) continue;
     pi.nkd = jlast - jfirst + 1;
@@ -417,14 +676,8 @@ int plan_planes(ConvParams& P, int cin, int stride_d, int pad_d) {
     pi.woff = kc.base[cls] + (uint32_t)jfirst * kBTapBytes;
     pi.wstride = (uint32_t)kc.nkd[cls] * kBTapBytes;
   }
-  for (int d = 0; d < P.Dout; ++d) {
-    if (first_plane[d] < 0) return -1;
-    PlaneInfo& pf = P.plane[first_plane[d]];
-    if (pf.new_acc >= 0) return -1;                      // at most one new accumulator per plane
-    if (d != pf.dmin + pf.nkd - 1) return -1;            // and it is the plane's last tap
-    pf.new_acc = d;
-    P.plane[last_plane[d]].done_mask |= 1 << d;
-  }
+  for (int d = 0; d < P.Dout; ++d)
+    if (!fed[d]) return -1;
   return 0;
 }
 
@@ -444,6 +697,19 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
+int out_depth(int Din, int stride_d, int pad_d) { return (Din + 2 * pad_d - 3) / stride_d + 1; }
+
+struct PlanLayout {
+  size_t groups_off, tiles_off, total;
+};
+PlanLayout plan_layout(int64_t n_tiles) {
+  PlanLayout L;
+  L.groups_off = sizeof(PlanHeader);
+  L.tiles_off = L.groups_off + (size_t)n_tiles * sizeof(GroupDesc);
+  L.total = L.tiles_off + (size_t)n_tiles * sizeof(TilePlan);
+  return L;
+}
+
 }  // namespace
 }  // namespace vn
 
@@ -454,6 +720,11 @@ extern "C" {
 size_t vn_conv3d_box_flags_bytes(int32_t B, int32_t Din, int32_t H, int32_t W) {
   if (B < 1 || Din < 1 || H < 1 || W < 1 || W % kTileW != 0) return 0;
   return (size_t)B * Din * ((H + kTileH - 1) / kTileH) * (W / kTileW) * 3;
+}
+
+size_t vn_conv3d_workspace_bytes(int32_t B, int32_t H, int32_t W) {
+  if (B < 1 || H < 1 || W < 1 || W % kTileW != 0) return 0;
+  return plan_layout((int64_t)B * ((H + kTileH - 1) / kTileH) * (W / kTileW)).total;
 }
 
 size_t vn_conv3d_packed_weight_bytes(int32_t cin) {
@@ -471,22 +742,88 @@ int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, v
   return VN_OK;
 }
 
+int vn_conv3d_fold_background(const float* weight, int32_t cin, int32_t Din, int32_t stride_d, int32_t pad_d,
+                              const float* scale, const float* shift, const float* bg_in, float* shift_table,
+                              float* bg_out, vn_stream_t stream) {
+  VN_REQUIRE(weight && scale && shift && shift_table, "conv3d_fold_background: null pointer");
+  VN_REQUIRE(cin == 64 || cin == 128, "conv3d_fold_background: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d_fold_background: stride_d=%d pad_d=%d",
+             stride_d, pad_d);
+  VN_REQUIRE(Din >= 1 && Din <= kMaxPlanes && Din + 2 * pad_d >= 3, "conv3d_fold_background: Din=%d", Din);
+  const int Dout = out_depth(Din, stride_d, pad_d);
+  VN_REQUIRE(Dout >= 1 && Dout <= kSlots, "conv3d_fold_background: Dout=%d outside [1,%d]", Dout, kSlots);
+  k_fold_background<<<9 * Dout, 64, 0, as_stream(stream)>>>(weight, cin, Din, Dout, stride_d, pad_d, scale, shift, bg_in,
+                                                            shift_table, bg_out);
+  VN_LAUNCH_CHECK("k_fold_background");
+  return VN_OK;
+}
+
+int vn_conv3d_mark_boxes(const int64_t* coords, int64_t K, const int32_t* n_voxels_dev, int32_t B, int32_t D, int32_t H,
+                         int32_t W, int32_t n_layers, const int32_t* stride_d, const int32_t* pad_d,
+                         uint8_t* const* flags, vn_stream_t stream) {
+  VN_REQUIRE(K >= 0, "conv3d_mark_boxes: K < 0");
+  VN_REQUIRE(n_layers >= 1 && n_layers <= 3 && stride_d && pad_d && flags, "conv3d_mark_boxes: n_layers=%d", n_layers);
+  VN_REQUIRE(B >= 1 && D >= 1 && D <= kMaxPlanes && H >= 1 && W >= 1 && W % kTileW == 0, "conv3d_mark_boxes: bad grid");
+  if (K == 0) return VN_OK;
+  VN_REQUIRE(coords != nullptr, "conv3d_mark_boxes: coords is null");
+  MarkParams Q{};
+  Q.B = B; Q.D = D; Q.H = H; Q.W = W;
+  Q.tiles_h = (H + kTileH - 1) / kTileH;
+  Q.tiles_w = W / kTileW;
+  Q.n_layers = n_layers;
+  int din = D;
+  for (int l = 0; l < n_layers; ++l) {
+    VN_REQUIRE((stride_d[l] == 1 || stride_d[l] == 2) && (pad_d[l] == 0 || pad_d[l] == 1) && din + 2 * pad_d[l] >= 3,
+               "conv3d_mark_boxes: layer %d geometry", l);
+    VN_REQUIRE(flags[l] != nullptr, "conv3d_mark_boxes: flags[%d] is null", l);
+    Q.Din[l] = din; Q.stride_d[l] = stride_d[l]; Q.pad_d[l] = pad_d[l]; Q.flags[l] = flags[l];
+    din = out_depth(din, stride_d[l], pad_d[l]);
+  }
+  const int64_t want = (K + 7) / 8;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  k_mark_boxes<<<(unsigned)(want < cap ? want : cap), 256, 0, as_stream(stream)>>>(
+      reinterpret_cast<const long long*>(coords), K, n_voxels_dev, Q);
+  VN_LAUNCH_CHECK("k_mark_boxes");
+  return VN_OK;
+}
+
 int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
-                          int32_t pad_d, const void* packed_weight, const float* scale, const float* shift,
-                          int32_t out_mode, void* y, const uint8_t* box_flags, vn_stream_t stream) {
-  VN_REQUIRE(x && packed_weight && scale && shift && y, "conv3d: null pointer");
+                          int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
+                          int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
+                          int32_t flag_opts, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(x && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
   VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d: stride_d=%d pad_d=%d unsupported",
              stride_d, pad_d);
   VN_REQUIRE(out_mode == 0 || out_mode == 1, "conv3d: out_mode=%d", out_mode);
-  VN_REQUIRE(W % kTileW == 0, "conv3d: W=%d must be a multiple of %d", W, kTileW);
+  VN_REQUIRE(W % kTileW == 0 && W / kTileW <= kMaxTilesW, "conv3d: W=%d must be a multiple of %d, at most %d", W, kTileW,
+             kTileW * kMaxTilesW);
   VN_REQUIRE(Din <= kMaxPlanes, "conv3d: Din=%d exceeds %d", Din, kMaxPlanes);
-  const int Dout = (Din + 2 * pad_d - 3) / stride_d + 1;
-  VN_REQUIRE(Din + 2 * pad_d >= 3 && Dout >= 1 && Dout <= kMaxDout, "conv3d: Dout=%d outside [1,%d]", Dout, kMaxDout);
+  const int Dout = out_depth(Din, stride_d, pad_d);
+  VN_REQUIRE(Din + 2 * pad_d >= 3 && Dout >= 1 && Dout <= kSlots, "conv3d: Dout=%d outside [1,%d]", Dout, kSlots);
+  VN_REQUIRE(n_variants == 0 || n_variants == 1 || n_variants == 9, "conv3d: n_variants=%d (0: plain [64] shift, 1, 9)",
+             n_variants);
+  const int nvar = n_variants == 9 ? 9 : 1;
+  VN_REQUIRE(nvar * Dout <= kMaxTableRows, "conv3d: shift table of %d x %d rows exceeds %d", nvar, Dout, kMaxTableRows);
+  VN_REQUIRE(nvar == 1 || H >= 2, "conv3d: border variants need H >= 2");
   VN_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(packed_weight) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(y) & 15) == 0,
              "conv3d: buffers must be 16-byte aligned");
+  VN_REQUIRE(workspace != nullptr && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "conv3d: workspace missing or misaligned");
+
+  const int tiles_h = (H + kTileH - 1) / kTileH, tiles_w = W / kTileW;
+  const int64_t n_tiles = (int64_t)B * tiles_h * tiles_w;
+  VN_REQUIRE(n_tiles < (int64_t)0x7fffffff, "conv3d: too many tiles");
+  const PlanLayout L = plan_layout(n_tiles);
+  if (workspace_bytes < L.total) {
+    set_error("conv3d: workspace %zu < %zu bytes", workspace_bytes, L.total);
+    return VN_ERR_WORKSPACE;
+  }
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  PlanHeader* hdr = reinterpret_cast<PlanHeader*>(ws);
+  GroupDesc* groups = reinterpret_cast<GroupDesc*>(ws + L.groups_off);
+  TilePlan* tiles = reinterpret_cast<TilePlan*>(ws + L.tiles_off);
 
   EncodeTiledFn encode = encode_tiled_fn();
   if (encode == nullptr) {
@@ -507,30 +844,39 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
     return VN_ERR_DRIVER;
   }
 
-  ConvParams P{};
-  P.B = B; P.Din = Din; P.Dout = Dout; P.H = H; P.W = W;
-  P.nchunk = cin / 64;
-  P.tiles_h = (H + kTileH - 1) / kTileH;
-  P.tiles_w = W / kTileW;
-  P.n_tiles = B * P.tiles_h * P.tiles_w;
-  P.out_mode = out_mode;
-  P.wpack = reinterpret_cast<const uint8_t*>(packed_weight);
-  P.box_flags = box_flags;
-  P.scale = scale; P.shift = shift;
-  P.out = y;
-  if (plan_planes(P, cin, stride_d, pad_d) != 0) {
+  cudaStream_t st = as_stream(stream);
+  PlanParams Q{};
+  Q.B = B; Q.Din = Din; Q.Dout = Dout; Q.H = H; Q.W = W; Q.tiles_h = tiles_h; Q.tiles_w = tiles_w;
+  Q.box_flags = box_flags;
+  Q.consume = (flag_opts & VN_CONV_FLAGS_CONSUME) ? 1 : 0;
+  Q.force_ring = (flag_opts & VN_CONV_FLAGS_BORDER_RING) ? 1 : 0;
+  Q.hdr = hdr; Q.groups = groups; Q.tiles = tiles;
+  if (plan_planes(Q, stride_d, pad_d) != 0) {
     set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
     return VN_ERR_UNSUPPORTED;
   }
+  VN_CUDA(cudaMemsetAsync(hdr, 0, sizeof(PlanHeader), st));
+  k_conv3d_plan<<<B * tiles_h, 64, 0, st>>>(Q);
+  VN_LAUNCH_CHECK("k_conv3d_plan");
 
-  const int grid = P.n_tiles < sm_count() ? P.n_tiles : sm_count();
-  if (box_flags != nullptr) {
-    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    k_conv3d_bn_relu<true><<<grid, kThreads, kSmemBytes, as_stream(stream)>>>(tmap, P);
-  } else {
-    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    k_conv3d_bn_relu<false><<<grid, kThreads, kSmemBytes, as_stream(stream)>>>(tmap, P);
-  }
+  ConvParams P{};
+  P.B = B; P.Din = Din; P.Dout = Dout; P.H = H; P.W = W;
+  P.nchunk = cin / 64;
+  P.tiles_h = tiles_h; P.tiles_w = tiles_w; P.n_tiles = (int)n_tiles;
+  P.out_mode = out_mode;
+  P.nvar = nvar;
+  P.wpack = reinterpret_cast<const uint8_t*>(packed_weight);
+  P.scale = scale;
+  P.table = shift_table;
+  P.table_plain = n_variants == 0 ? 1 : 0;
+  P.sub = sub;
+  P.out = y;
+  P.hdr = hdr; P.groups = groups; P.tiles = tiles;
+  for (int p = 0; p < kMaxPlanes; ++p) P.plane[p] = Q.plane[p];
+
+  const int grid = n_tiles < sm_count() ? (int)n_tiles : sm_count();
+  VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+  k_conv3d_bn_relu<<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   VN_LAUNCH_CHECK("k_conv3d_bn_relu");
   return VN_OK;
 }

@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(256)
 __global__ void __launch_bounds__(256)
     k_scatter_bf16(const float* __restrict__ voxelwise, const long long* __restrict__ coords, int64_t K,
                    const int32_t* __restrict__ n_voxels_dev, int C, int B, int D, int H, int W,
-                   __nv_bfloat16* __restrict__ dense, uint8_t* __restrict__ box_flags, int clear) {
+                   __nv_bfloat16* __restrict__ dense, int clear) {
   const int64_t total = live_rows(K, n_voxels_dev);
   const uint32_t lane = threadIdx.x & 31;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -60,19 +60,6 @@ __global__ void __launch_bounds__(256)
   for (int64_t r = warp; r < total; r += nwarps) {
     int64_t cell;
     if (!cell_offset(coords + r * 4, B, D, H, W, cell)) continue;
-    if (box_flags != nullptr && lane < 6) {
-      // Conv tile geometry (vn_conv3d.cu): 16 x 8 output tiles, input boxes = rows 16*th-1 .. 16*th+16,
-      // columns 8*tw+kw-1 .. 8*tw+kw+6.  A voxel lies in the boxes of <= 2 row tiles x 3 (tw, kw) pairs.
-      const long long* c = coords + r * 4;
-      const int y = (int)c[2], x = (int)c[3];
-      const int tiles_h = (H + 15) >> 4, tiles_w = W >> 3;
-      const int th_hi = (y + 1) >> 4, th_lo = y >= 1 ? (y - 1) >> 4 : 0;
-      const int kw = lane % 3;
-      const int th = lane < 3 ? th_lo : th_hi;
-      const int xs = x - kw + 1;
-      if ((lane < 3 || th_hi != th_lo) && th < tiles_h && xs >= 0 && (xs >> 3) < tiles_w)
-        box_flags[((((size_t)c[0] * D + c[1]) * tiles_h + th) * tiles_w + (xs >> 3)) * 3 + kw] = clear ? 0 : 1;
-    }
     uint2* dst = reinterpret_cast<uint2*>(dense + cell * C);
     if (clear) {
       for (int c4 = lane; c4 < C / 4; c4 += 32) dst[c4] = make_uint2(0u, 0u);
@@ -125,14 +112,13 @@ int vn_scatter_dense_f32(const float* voxelwise, const int64_t* coords, int64_t 
 }
 
 int vn_scatter_dense_bf16(const float* voxelwise, const int64_t* coords, int64_t K, const int32_t* n_voxels_dev,
-                          int32_t C, int32_t B, int32_t D, int32_t H, int32_t W, void* dense_bf16,
-                          uint8_t* conv_box_flags, int32_t clear, vn_stream_t stream) {
+                          int32_t C, int32_t B, int32_t D, int32_t H, int32_t W, void* dense_bf16, int32_t clear,
+                          vn_stream_t stream) {
   int rc = check(voxelwise, coords, K, C, B, D, H, W, dense_bf16, clear == 0);
   if (rc != VN_OK || K == 0) return rc;
-  VN_REQUIRE(conv_box_flags == nullptr || W % 8 == 0, "scatter: box flags need W to be a multiple of 8");
   k_scatter_bf16<<<grid_for_rows(K), 256, 0, as_stream(stream)>>>(
       voxelwise, reinterpret_cast<const long long*>(coords), K, n_voxels_dev, C, B, D, H, W,
-      reinterpret_cast<__nv_bfloat16*>(dense_bf16), conv_box_flags, clear);
+      reinterpret_cast<__nv_bfloat16*>(dense_bf16), clear);
   VN_LAUNCH_CHECK("k_scatter_bf16");
   return VN_OK;
 }

@@ -181,17 +181,16 @@ def scatter_dense_f32(voxelwise, coords, dense, n_voxels_dev=None) -> None:
         )
 
 
-def scatter_dense_bf16(voxelwise, coords, dense, clear: bool = False, n_voxels_dev=None, box_flags=None) -> None:
-    """Write (clear=False) or re-zero (clear=True) the occupied rows of the resident bf16 grid; with
-    `box_flags` (uint8, conv3d_box_flags_bytes) also maintain the first conv's input-box occupancy table."""
-    _require_cuda(voxelwise, coords, dense, box_flags)
+def scatter_dense_bf16(voxelwise, coords, dense, clear: bool = False, n_voxels_dev=None) -> None:
+    """Write (clear=False) or re-zero (clear=True) the occupied rows of the resident bf16 grid."""
+    _require_cuda(voxelwise, coords, dense)
     _contig(coords, torch.int64), _contig(dense, torch.bfloat16)
     B, D, H, W, Cc = dense.shape
     with torch.cuda.device(dense.device):
         check(
             _cabi.lib().vn_scatter_dense_bf16(
                 _ptr(voxelwise), _ptr(coords), coords.shape[0], _ptr(n_voxels_dev), Cc, B, D, H, W, _ptr(dense),
-                _ptr(box_flags), 1 if clear else 0, _stream(),
+                1 if clear else 0, _stream(),
             ),
             "vn_scatter_dense_bf16",
         )
@@ -225,26 +224,99 @@ def conv3d_box_flags_bytes(B: int, Din: int, H: int, W: int) -> int:
     return int(_cabi.lib().vn_conv3d_box_flags_bytes(B, Din, H, W))
 
 
+def conv3d_workspace_bytes(B: int, H: int, W: int) -> int:
+    return int(_cabi.lib().vn_conv3d_workspace_bytes(B, H, W))
+
+
+def conv3d_new_box_flags(B: int, Din: int, H: int, W: int, device) -> torch.Tensor:
+    """Zeroed live-box table for a layer with input (B, Din, H, W, .)."""
+    return torch.zeros(conv3d_box_flags_bytes(B, Din, H, W), dtype=torch.uint8, device=device)
+
+
+def conv3d_mark_boxes(coords, B: int, D: int, H: int, W: int, layers, flags, n_voxels_dev=None) -> None:
+    """Flag the live input boxes of a chain of stacked middle layers from voxel coordinates (K,4) i64.
+    layers: [(stride_d, pad_d), ...] (<= 3), flags: one uint8 table per layer (conv3d_new_box_flags)."""
+    _require_cuda(coords, *flags)
+    _contig(coords, torch.int64)
+    n = len(layers)
+    if n != len(flags) or not 1 <= n <= 3:
+        raise RuntimeError("conv3d_mark_boxes: need 1..3 layers with one flag table each")
+    din = D
+    for (s, p), f in zip(layers, flags):
+        if f.dtype != torch.uint8 or f.numel() != conv3d_box_flags_bytes(B, din, H, W):
+            raise RuntimeError("conv3d_mark_boxes: flag table size does not match the layer input (B,%d,%d,%d)" % (din, H, W))
+        din = conv3d_out_depth(din, s, p)
+    strides = (C.c_int32 * n)(*[int(s) for s, _ in layers])
+    pads = (C.c_int32 * n)(*[int(p) for _, p in layers])
+    ptrs = (C.c_void_p * n)(*[f.data_ptr() for f in flags])
+    with torch.cuda.device(coords.device):
+        check(
+            _cabi.lib().vn_conv3d_mark_boxes(_ptr(coords), coords.shape[0], _ptr(n_voxels_dev), B, D, H, W, n, strides, pads,
+                                             ptrs, _stream()),
+            "vn_conv3d_mark_boxes",
+        )
+
+
+def conv3d_fold_background(weight, din: int, stride_d: int, pad_d: int, scale, shift, bg_in=None):
+    """(shift_table (3,3,Dout,64) f32, bg_out (Dout,64) f32) for a layer whose input is stored as a
+    deviation from the background bg_in (Din,cin) f32 (None: zero) - see vn_conv3d_fold_background."""
+    _require_cuda(weight, scale, shift, bg_in)
+    w = _contig(weight.detach(), torch.float32)
+    cin = w.shape[1]
+    dout = conv3d_out_depth(din, stride_d, pad_d)
+    if bg_in is not None and (tuple(bg_in.shape) != (din, cin) or bg_in.dtype != torch.float32 or not bg_in.is_contiguous()):
+        raise RuntimeError("bg_in must be a contiguous (Din, cin) float32 tensor")
+    table = torch.empty((3, 3, dout, 64), dtype=torch.float32, device=w.device)
+    bg_out = torch.empty((dout, 64), dtype=torch.float32, device=w.device)
+    with torch.cuda.device(w.device):
+        check(
+            _cabi.lib().vn_conv3d_fold_background(_ptr(w), cin, din, stride_d, pad_d, _ptr(_contig(scale, torch.float32)),
+                                                  _ptr(_contig(shift, torch.float32)), _ptr(bg_in), _ptr(table), _ptr(bg_out),
+                                                  _stream()),
+            "vn_conv3d_fold_background",
+        )
+    return table, bg_out
+
+
 def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int, final: bool = False, out=None,
-                       box_flags=None):
+                       box_flags=None, consume_flags: bool = False, border_ring: bool = False, sub=None, workspace=None):
     """x (B,Din,H,W,cin) bf16 NDHWC -> (B,Dout,H,W,64) bf16, or with final=True the reference's
-    reshaped (B, 64*Dout, H, W) f32 (model.py:262)."""
-    _require_cuda(x, packed_weight, scale, shift, box_flags)
+    reshaped (B, 64*Dout, H, W) f32 (model.py:262).
+
+    shift: (64,) plain BatchNorm shift, (Dout,64), or the (3,3,Dout,64) table of conv3d_fold_background.
+    sub: optional (Dout,64) background subtracted after the ReLU.  box_flags: optional live-box table
+    (conv3d_mark_boxes); consume_flags resets it, border_ring forces boxes on the H/W border live."""
+    _require_cuda(x, packed_weight, scale, shift, box_flags, sub, workspace)
     _contig(x, torch.bfloat16)
     B, Din, H, W, cin = x.shape
     if box_flags is not None and (box_flags.dtype != torch.uint8 or box_flags.numel() != conv3d_box_flags_bytes(B, Din, H, W)):
         raise RuntimeError("box_flags must be a uint8 tensor of conv3d_box_flags_bytes(B, Din, H, W) elements")
     Dout = conv3d_out_depth(Din, stride_d, pad_d)
+    _contig(shift, torch.float32)
+    if tuple(shift.shape) == (64,):
+        n_variants = 0
+    elif tuple(shift.shape) == (Dout, 64):
+        n_variants = 1
+    elif tuple(shift.shape) == (3, 3, Dout, 64):
+        n_variants = 9
+    else:
+        raise RuntimeError("shift must have shape (64,), (Dout,64) or (3,3,Dout,64); got %s" % (tuple(shift.shape),))
+    if sub is not None and (tuple(sub.shape) != (Dout, 64) or sub.dtype != torch.float32 or not sub.is_contiguous()):
+        raise RuntimeError("sub must be a contiguous (Dout,64) float32 tensor")
     if out is None:
         if final:
             out = torch.empty((B, 64 * Dout, H, W), dtype=torch.float32, device=x.device)
         else:
             out = torch.empty((B, Dout, H, W, 64), dtype=torch.bfloat16, device=x.device)
+    if workspace is None:
+        workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
+    opts = (_cabi.VN_CONV_FLAGS_CONSUME if consume_flags else 0) | (_cabi.VN_CONV_FLAGS_BORDER_RING if border_ring else 0)
     with torch.cuda.device(x.device):
         check(
             _cabi.lib().vn_conv3d_bn_relu_fwd(
                 _ptr(x), B, Din, H, W, cin, stride_d, pad_d, _ptr(packed_weight), _ptr(_contig(scale, torch.float32)),
-                _ptr(_contig(shift, torch.float32)), 1 if final else 0, _ptr(out), _ptr(box_flags), _stream(),
+                _ptr(shift), n_variants, _ptr(sub), 1 if final else 0, _ptr(out), _ptr(box_flags), opts,
+                _ptr(workspace), workspace.numel(), _stream(),
             ),
             "vn_conv3d_bn_relu_fwd",
         )

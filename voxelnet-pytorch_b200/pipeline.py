@@ -75,9 +75,13 @@ class VoxelNetFrontEnd:
         # True: the (K,T,7) feature buffer is never materialised (vn_voxelize_svfe_fused);
         # False: voxel dict written then read back by the SVFE kernel (the reference's data flow)
         self.fuse_voxel_features = bool(fuse_voxel_features)
-        # True: conv-1 skips input boxes that hold no voxel (exact; the grid is ~99 % zeros)
+        # True: the middle layers skip input boxes that hold only background.  conv-1's input is the
+        # ~99 % empty voxel grid (exact skip); conv-2/3 then read their inputs as deviations from the
+        # constant the previous layer outputs over empty space, which are zero wherever no voxel is in
+        # reach (vn_conv3d_fold_background / vn_conv3d_mark_boxes).  False: dense, plain activations.
         self.skip_empty_boxes = bool(skip_empty_boxes)
         self._shape = None
+        self._layer_geometry = [(l.stride[0], l.padding[0]) for l in middle_net.middle_layer]
         self.refresh_parameters()
 
     def refresh_parameters(self) -> None:
@@ -87,6 +91,16 @@ class VoxelNetFrontEnd:
         self._p1 = self.feature_net.vfe_1.folded()
         self._p2 = self.feature_net.vfe_2.folded()
         self._conv = [layer.folded() for layer in self.middle_net.middle_layer]
+        # background chain: shift tables with the background's contribution folded in, and each
+        # layer's own output background (subtracted on store, so the stored deviation is sparse)
+        self._tables, self._bg = [], []
+        if self.skip_empty_boxes:
+            din, bg = self.cfg.depth, None
+            for layer, (_, scale, shift) in zip(self.middle_net.middle_layer, self._conv):
+                table, bg_out = ops.conv3d_fold_background(layer.conv.weight, din, layer.stride[0], layer.padding[0], scale, shift, bg)
+                self._tables.append(table)
+                self._bg.append(bg_out)
+                din, bg = bg_out.shape[0], bg_out
 
     def _ensure_buffers(self, n_frames: int, n_points: int, device) -> None:
         shape = (n_frames, n_points, str(device))
@@ -110,9 +124,10 @@ class VoxelNetFrontEnd:
         self.voxelwise = torch.empty((cap, 128), dtype=torch.float32, device=device)
         self.dense = torch.empty((B, D, H, W, 128), dtype=torch.bfloat16, device=device)
         ops.fill_zero(self.dense)  # paid once: the step re-zeroes only the rows it wrote
-        # occupancy of the first conv's input boxes, maintained by the scatter/unscatter kernels
-        nflags = ops.conv3d_box_flags_bytes(B, D, H, W)
-        self.box_flags = torch.zeros((nflags + 15) // 16 * 16, dtype=torch.uint8, device=device)[:nflags] if self.skip_empty_boxes else None
+        # live-box tables of the three layers: set by mark_boxes from the voxel coordinates, reset by
+        # the layer that consumes them
+        self.box_flags = [ops.conv3d_new_box_flags(B, d, H, W, device) for d in (D, d1, d2)] if self.skip_empty_boxes else None
+        self.conv_workspace = torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=device)
         self.act1 = torch.empty((B, d1, H, W, 64), dtype=torch.bfloat16, device=device)
         self.act2 = torch.empty((B, d2, H, W, 64), dtype=torch.bfloat16, device=device)
         self.out = torch.empty((B, 64 * d3, H, W), dtype=torch.float32, device=device)
@@ -142,21 +157,35 @@ class VoxelNetFrontEnd:
             with span("svfe"):
                 ops.svfe_fused_fwd(vb.feature, self._p1, self._p2, out=self.voxelwise, n_voxels_dev=k_dev)
         with span("scatter"):
-            ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev,
-                                   box_flags=self.box_flags)
+            ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
+            if self.skip_empty_boxes:
+                ops.conv3d_mark_boxes(vb.coordinate, n_frames, self.cfg.depth, self.cfg.height, self.cfg.width,
+                                      self._layer_geometry, self.box_flags, n_voxels_dev=k_dev)
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
-        with span("conv1"):
-            ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=self.box_flags)
-        with span("unscatter"):
-            ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev, box_flags=self.box_flags)
-        with span("conv2"):
-            ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2)
-        with span("conv3"):
-            ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out)
+        ws = self.conv_workspace
+        if self.skip_empty_boxes:
+            f0, f1, f2 = self.box_flags
+            with span("conv1"):  # zero background in, deviation from relu(shift) out
+                ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=f0, consume_flags=True,
+                                       sub=self._bg[0], workspace=ws)
+            with span("unscatter"):
+                ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+            with span("conv2"):
+                ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
+                                       consume_flags=True, sub=self._bg[1], workspace=ws)
+            with span("conv3"):  # conv-2's zero padding makes its output deviate along the H/W border
+                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
+                                       consume_flags=True, border_ring=True, workspace=ws)
+        else:
+            with span("conv1"):
+                ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, workspace=ws)
+            with span("unscatter"):
+                ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+            with span("conv2"):
+                ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2, workspace=ws)
+            with span("conv3"):
+                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out, workspace=ws)
         return self.out
-
-    # kernels enqueued by one forward_points call (for bench.py's gpu_launches)
-    LAUNCHES_PER_STEP = 5 + 3 + 1 + 1 + 1 + 1 + 1 + 1
 
     def forward_frames(self, frames: list) -> torch.Tensor:
         """Host frames [(N_i,4) f32 numpy] -> (B,128,H,W) f32 (includes the H2D copy)."""
