@@ -79,6 +79,13 @@ __device__ __forceinline__ void st_stream_u4(void* p, uint4 v) {
                : "memory");
 }
 
+// 256-bit store: one full 32-byte sector per lane (sm_100+).
+__device__ __forceinline__ void st_global_v8(void* p, const uint32_t (&v)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(v[0]), "r"(v[1]), "r"(v[2]),
+               "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+               : "memory");
+}
+
 // One elected lane of a fully converged warp (warp-uniform control flow around single-thread
 // instructions keeps their operands in uniform registers - no per-lane waterfall loops).
 __device__ __forceinline__ bool elect_one() {

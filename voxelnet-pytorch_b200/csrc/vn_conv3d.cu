@@ -52,7 +52,7 @@ constexpr int kMaxPlanes = 10;                       // live mask = 3 bits per p
 constexpr int kMaxGroupTiles = 8;
 constexpr int kMaxTilesW = 128;
 constexpr int kMaxTableRows = 27;                    // shift-table rows (variants x Dout) kept in smem
-constexpr int kThreads = 6 * 32;
+constexpr int kThreads = 10 * 32;            // producer, MMA issuer, 8 epilogue warps
 constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBSlotBytes;  // 221184
 
 // What one input plane contributes (host-computed; see plan_planes()).
@@ -120,12 +120,28 @@ struct Control {
   int32_t sched[kSched];
   uint32_t tmem_base;
   uint32_t pad[3];
+  uint32_t row_zero[kSlots];  // [dout]: relu(interior shift row) - sub == 0 for all channels
+  uint4 msg[kNA];  // one message per A stage, written by the producer before it arms full_a (see kMsg*)
   float scale[64];
   float sub[kSlots * 64];
   float table[kMaxTableRows * 64];
 };
 constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + (uint32_t)sizeof(Control);
 static_assert(kSmemBytes <= 232448, "shared memory budget (227 KB)");
+
+// Producer -> MMA issuer messages (Control::msg[stage]).  The producer does all the bookkeeping
+// (which accumulators a box feeds, whether they are fresh, when a tile is complete); the issuing warp
+// only interprets: x = flags, y = TMEM column of the first accumulator, z / w = (offset of the plane's
+// first weight tile, distance between its kh rows) >> 4.
+constexpr uint32_t kMsgNkdMask = 3;      // bits 0-1: depth taps fused along N (0: control message, no A box)
+constexpr uint32_t kMsgNewPass = 4;      // first box of a weight pass: release the previous slot, wait for the next
+constexpr uint32_t kMsgFreshShift = 4;   // bits 4-6: tap j starts its accumulator (accumulate = 0 on the first k-step)
+constexpr uint32_t kMsgEnd = 0x80;       // no more work
+constexpr uint32_t kMsgCommitShift = 8;  // bits 8-15: TMEM slots that are complete after this message
+constexpr uint32_t kMsgWaitShift = 16;   // bits 16-23: TMEM slots the epilogue must have drained before the MMAs
+constexpr uint32_t kDescHi = 0x40004040u;  // SW128 K-major descriptor, high word: SBO = 1024 B, version 1, layout 2
+
+__device__ __forceinline__ uint64_t desc_from_lo(uint32_t lo) { return ((uint64_t)kDescHi << 32) | lo; }
 
 __host__ __device__ __forceinline__ uint32_t kw_bits(int kw) { return 0x09249249u << kw; }  // bits kw, kw+3, ...
 
@@ -227,18 +243,28 @@ __global__ void __launch_bounds__(kThreads, 1)
   if (threadIdx.x == 0) {
     for (int i = 0; i < kNA; ++i) { mbar_init(&ctl->full_a[i], 1); mbar_init(&ctl->empty_a[i], 1); }
     for (int i = 0; i < kNB; ++i) { mbar_init(&ctl->full_b[i], 1); mbar_init(&ctl->empty_b[i], 1); }
-    for (int i = 0; i < kSlots; ++i) { mbar_init(&ctl->acc_full[i], 1); mbar_init(&ctl->acc_empty[i], 4); }
-    for (int i = 0; i < kSched; ++i) { mbar_init(&ctl->sched_full[i], 1); mbar_init(&ctl->sched_empty[i], 5); }
+    for (int i = 0; i < kSlots; ++i) { mbar_init(&ctl->acc_full[i], 1); mbar_init(&ctl->acc_empty[i], 8); }
+    for (int i = 0; i < kSched; ++i) { mbar_init(&ctl->sched_full[i], 1); mbar_init(&ctl->sched_empty[i], 8); }
     mbar_fence_init();
     fence_proxy_async_smem();
     tma_prefetch_desc(&tmap_x);
   }
   if (threadIdx.x >= 64) {
-    const int t = threadIdx.x - 64;  // 0..127
+    const int t = threadIdx.x - 64;  // 0..255
     if (t < 64) ctl->scale[t] = P.scale[t];
     const int nrow = P.nvar * P.Dout;
-    for (int i = t; i < nrow * 64; i += 128) ctl->table[i] = P.table_plain ? P.table[i & 63] : P.table[i];
-    for (int i = t; i < P.Dout * 64; i += 128) ctl->sub[i] = P.sub != nullptr ? P.sub[i] : 0.0f;
+    for (int i = t; i < nrow * 64; i += 256) ctl->table[i] = P.table_plain ? P.table[i & 63] : P.table[i];
+    for (int i = t; i < P.Dout * 64; i += 256) ctl->sub[i] = P.sub != nullptr ? P.sub[i] : 0.0f;
+    if (t < kSlots) {  // does the interior shift row of depth t cancel against `sub` exactly?
+      bool z = t < P.Dout;
+      if (z)
+        for (int c = 0; c < 64; ++c) {
+          const float sh = P.table_plain ? P.table[c] : P.table[t * 64 + c];
+          const float sb = P.sub != nullptr ? P.sub[t * 64 + c] : 0.0f;
+          z = z && (fmaxf(sh, 0.0f) - sb == 0.0f);
+        }
+      ctl->row_zero[t] = z ? 1u : 0u;
+    }
   }
   if (warp == 1) {
     tmem_alloc(&ctl->tmem_base, kSlots * 64);
@@ -251,7 +277,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   const int n_groups = P.hdr->n_groups;
 
   if (warp == 0) {
-    // ============ scheduler + TMA producer (warp-uniform; one elected lane issues) ============
+    // ====== scheduler + planner + TMA producer (warp-uniform; one elected lane issues) ======
     uint32_t a_it = 0, b_it = 0, s_it = 0;
     for (;;) {
       const uint32_t ss = s_it % kSched;
@@ -267,8 +293,12 @@ __global__ void __launch_bounds__(kThreads, 1)
       ++s_it;
       if (g < 0) break;
       const GroupDesc gd = P.groups[g];
-      const uint32_t mylive = (int)lane < gd.ntiles ? P.tiles[gd.tile0 + lane].live : 0u;
+      TilePlan tp = TilePlan{0u, 0, 0, 0, 0};
+      if ((int)lane < gd.ntiles) tp = P.tiles[gd.tile0 + lane];
+      const uint32_t mylive = tp.live, mytouched = tp.touched, myslot0 = tp.slot0;
+      uint32_t mystarted = 0;  // lane t: accumulators of tile t that already hold a partial sum
       const uint32_t any = warp_or(mylive);
+      const int last_kw = (any & kw_bits(2)) ? 2 : ((any & kw_bits(1)) ? 1 : 0);
       const int tw0 = gd.tile0 % P.tiles_w;
       const int th = (gd.tile0 / P.tiles_w) % P.tiles_h;
       const int b = gd.tile0 / (P.tiles_w * P.tiles_h);
@@ -276,6 +306,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       for (int c = 0; c < P.nchunk; ++c) {
         for (int kw = 0; kw < 3; ++kw) {
           if (!(any & kw_bits(kw))) continue;  // no tile of the group has a live box at this w shift
+          const bool last_pass = (c == P.nchunk - 1) & (kw == last_kw);
           // all weights of this (chunk, kw): resident while the group's live boxes stream through
           const uint32_t sb = b_it % kNB;
           mbar_wait(&ctl->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
@@ -286,125 +317,146 @@ __global__ void __launch_bounds__(kThreads, 1)
           }
           __syncwarp();
           ++b_it;
-          for (int t = 0; t < gd.ntiles; ++t) {
-            uint32_t m = __shfl_sync(0xffffffffu, mylive, t) & kw_bits(kw);
-            const int w0 = (tw0 + t) * kTileW;
-            while (m) {
-              const int p = (__ffs(m) - 1) / 3;
-              m &= m - 1;
-              const uint32_t sa = a_it % kNA;
-              mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
-              if (elect_one()) {
-                mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
-                tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
-              }
-              __syncwarp();
-              ++a_it;
-            }
-          }
-        }
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (warp-uniform; one elected lane issues) =====================
-    uint32_t a_it = 0, b_it = 0, s_it = 0;
-    uint32_t acc_phase = 0;  // bit s: parity of the number of groups that used TMEM slot s so far
-    for (;;) {
-      const uint32_t ss = s_it % kSched;
-      mbar_wait(&ctl->sched_full[ss], (s_it / kSched) & 1);
-      const int g = ctl->sched[ss];
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->sched_empty[ss]);
-      ++s_it;
-      if (g < 0) break;
-      const GroupDesc gd = P.groups[g];
-      TilePlan tp = TilePlan{0u, 0, 0, 0, 0};
-      if ((int)lane < gd.ntiles) tp = P.tiles[gd.tile0 + lane];
-      const uint32_t mylive = tp.live, mytouched = tp.touched, myslot0 = tp.slot0;
-      uint32_t mystarted = 0;  // lane t: accumulators of tile t that already hold a partial sum
-      const uint32_t any = warp_or(mylive);
-      const uint32_t used = warp_or(((1u << tp.nslots) - 1u) << tp.slot0);
-      const int last_kw = (any & kw_bits(2)) ? 2 : ((any & kw_bits(1)) ? 1 : 0);
-      for (int c = 0; c < P.nchunk; ++c) {
-        for (int kw = 0; kw < 3; ++kw) {
-          if (!(any & kw_bits(kw))) continue;
-          const bool last_pass = (c == P.nchunk - 1) & (kw == last_kw);
-          const uint32_t sb = b_it % kNB;
-          mbar_wait(&ctl->full_b[sb], (b_it / kNB) & 1);
-          tc_fence_after_sync();
-          const uint32_t b_addr = smem_u32(smem_b + sb * kBSlotBytes);
+          uint32_t new_pass = kMsgNewPass;
           for (int t = 0; t < gd.ntiles; ++t) {
             uint32_t m = __shfl_sync(0xffffffffu, mylive, t) & kw_bits(kw);
             const uint32_t touched = __shfl_sync(0xffffffffu, mytouched, t);
             const uint32_t slot0 = __shfl_sync(0xffffffffu, myslot0, t);
             uint32_t started = __shfl_sync(0xffffffffu, mystarted, t);
+            const int w0 = (tw0 + t) * kTileW;
             while (m) {
               const int p = (__ffs(m) - 1) / 3;
               m &= m - 1;
               const PlaneInfo& pi = P.plane[p];
               const uint32_t range = ((1u << pi.nkd) - 1u) << pi.dmin;
-              const uint32_t fresh = range & ~started;
+              const uint32_t fresh = (range & ~started) >> pi.dmin;  // bit j: tap j starts its accumulator
               const uint32_t slot_lo = slot0 + __popc(touched & ((1u << pi.dmin) - 1u));
-              // Accumulators first touched here must have been drained by the epilogue, and need
-              // accumulate=0 while already-started neighbours need 1: the first k-step is then issued
-              // per accumulator (N = 64) instead of fused along N.
-              if (fresh) {
-                for (int j = 0; j < pi.nkd; ++j)
-                  if ((fresh >> (pi.dmin + j)) & 1)
-                    mbar_wait(&ctl->acc_empty[slot_lo + j], ((acc_phase >> (slot_lo + j)) & 1) ^ 1);
-                tc_fence_after_sync();
-              }
-              const uint32_t d_tmem = tmem_base + slot_lo * 64;
-              const uint32_t idesc_all = umma_idesc_bf16(128, 64 * pi.nkd);
+              const uint32_t flags = (uint32_t)pi.nkd | new_pass | (fresh << kMsgFreshShift) |
+                                     ((fresh << slot_lo) << kMsgWaitShift);
               const uint32_t sa = a_it % kNA;
-              mbar_wait(&ctl->full_a[sa], (a_it / kNA) & 1);
-              tc_fence_after_sync();
-              const uint32_t a_addr = smem_u32(smem_a + sa * kABytes);
+              mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
               if (elect_one()) {
-#pragma unroll
-                for (int kh = 0; kh < 3; ++kh) {
-                  const uint64_t da0 = umma_desc_sw128(a_addr + kh * (kTileW * 128), 1024);
-                  const uint64_t db0 = umma_desc_sw128(b_addr + pi.woff + kh * pi.wstride, 1024);
-                  int k0 = 0;
-                  if (kh == 0 && fresh) {
-                    for (int j = 0; j < pi.nkd; ++j)
-                      umma_bf16_ss(d_tmem + j * 64, da0, db0 + (uint64_t)((j * kBTapBytes) >> 4), umma_idesc_bf16(128, 64),
-                                   (started >> (pi.dmin + j)) & 1);
-                    k0 = 1;
-                  }
-#pragma unroll
-                  for (int k = 0; k < 4; ++k) {
-                    if (k >= k0) umma_bf16_ss(d_tmem, da0 + (uint64_t)(k * 2), db0 + (uint64_t)(k * 2), idesc_all, 1);
-                  }
-                }
-                umma_commit(&ctl->empty_a[sa]);
+                ctl->msg[sa] = make_uint4(flags, slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
+                mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
+                tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
               }
               __syncwarp();
               started |= range;
+              new_pass = 0;
               ++a_it;
             }
             if ((int)lane == t) mystarted = started;
             // last weight pass of the group: tile t has received everything it will get
             if (last_pass && touched != 0) {
+              const uint32_t done = ((1u << __popc(touched)) - 1u) << slot0;
+              const uint32_t sa = a_it % kNA;
+              mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
               if (elect_one()) {
-                const int n = __popc(touched);
-                for (int j = 0; j < n; ++j) umma_commit(&ctl->acc_full[slot0 + j]);
+                ctl->msg[sa] = make_uint4(done << kMsgCommitShift, 0u, 0u, 0u);
+                mbar_arrive(&ctl->full_a[sa]);
               }
               __syncwarp();
+              ++a_it;
             }
           }
-          if (elect_one()) umma_commit(&ctl->empty_b[sb]);
-          __syncwarp();
-          ++b_it;
         }
       }
-      acc_phase ^= used;
+    }
+    {  // tell the issuing warp to stop
+      const uint32_t sa = a_it % kNA;
+      mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+      if (elect_one()) {
+        ctl->msg[sa] = make_uint4(kMsgEnd, 0u, 0u, 0u);
+        mbar_arrive(&ctl->full_a[sa]);
+      }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // ============ MMA issuer: interprets the producer's messages (warp-uniform) ============
+    uint32_t a_it = 0, b_it = 0;
+    uint32_t acc_phase = 0;  // bit s: parity of the number of times TMEM slot s has been (re)started
+    const uint32_t a_lo0 = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (1u << 16);
+    const uint32_t b_lo0 = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | (1u << 16);
+    uint32_t b_lo_pass = b_lo0;
+    for (;;) {
+      const uint32_t sa = a_it % kNA;
+      mbar_wait(&ctl->full_a[sa], (a_it / kNA) & 1);
+      const uint4 msg = ctl->msg[sa];
+      const uint32_t f = msg.x;
+      if (f & kMsgNewPass) {
+        if (b_it != 0) {  // the previous pass is fully issued: its weights may be overwritten once it completes
+          if (elect_one()) umma_commit(&ctl->empty_b[(b_it - 1) % kNB]);
+          __syncwarp();
+        }
+        mbar_wait(&ctl->full_b[b_it % kNB], (b_it / kNB) & 1);
+        b_lo_pass = b_lo0 + (b_it % kNB) * (kBSlotBytes >> 4);
+        ++b_it;
+      }
+      const uint32_t wait_mask = (f >> kMsgWaitShift) & 0xffu;
+      if (wait_mask) {  // accumulators started by this box must have been drained by the epilogue
+        uint32_t wm = wait_mask;
+        while (wm) {
+          const uint32_t s = __ffs(wm) - 1;
+          wm &= wm - 1;
+          mbar_wait(&ctl->acc_empty[s], ((acc_phase >> s) & 1) ^ 1);
+        }
+        acc_phase ^= wait_mask;
+      }
+      tc_fence_after_sync();
+      const uint32_t nkd = f & kMsgNkdMask;
+      if (nkd != 0) {
+        if (elect_one()) {
+          const uint32_t d_tmem = tmem_base + msg.y;
+          const uint32_t a_lo = a_lo0 + sa * (kABytes >> 4);
+          const uint32_t b_lo = b_lo_pass + msg.z;
+          const uint32_t idesc = umma_idesc_bf16(128, 64) + ((nkd - 1u) << 20);  // N = 64 * nkd
+          const uint32_t fresh = (f >> kMsgFreshShift) & 7u;
+          const bool split = fresh != 0 && fresh != (1u << nkd) - 1u;  // rare: neighbours in different states
+#pragma unroll
+          for (int kh = 0; kh < 3; ++kh) {
+            const uint32_t a = a_lo + kh * ((kTileW * 128) >> 4);
+            const uint32_t bq = b_lo + kh * msg.w;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+              if (kh == 0 && k == 0) {
+                if (split) {  // first k-step per accumulator (N = 64): accumulate only where a partial sum exists
+                  for (uint32_t j = 0; j < nkd; ++j)
+                    umma_bf16_ss(d_tmem + j * 64, desc_from_lo(a), desc_from_lo(bq + j * (kBTapBytes >> 4)),
+                                 umma_idesc_bf16(128, 64), ((fresh >> j) & 1) ^ 1);
+                } else {
+                  umma_bf16_ss(d_tmem, desc_from_lo(a), desc_from_lo(bq), idesc, fresh ? 0u : 1u);
+                }
+              } else {
+                umma_bf16_ss(d_tmem, desc_from_lo(a + k * 2), desc_from_lo(bq + k * 2), idesc, 1u);
+              }
+            }
+          }
+          umma_commit(&ctl->empty_a[sa]);
+        }
+      } else {
+        if (elect_one()) {
+          uint32_t cm = (f >> kMsgCommitShift) & 0xffu;
+          while (cm) {
+            const uint32_t s = __ffs(cm) - 1;
+            cm &= cm - 1;
+            umma_commit(&ctl->acc_full[s]);
+          }
+          mbar_arrive(&ctl->empty_a[sa]);
+        }
+      }
+      __syncwarp();
+      ++a_it;
+      if (f & kMsgEnd) break;
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const uint32_t quad = warp & 3;                // TMEM lane quadrant this warp may read
+    // ===================== epilogue (warps 2..9) =====================
+    // Two warps per TMEM lane quadrant (a warp may only read lanes 32*(warp%4)..+31): warps 2..5 take
+    // output channels 0..31 of their 32 positions, warps 6..9 channels 32..63.
+    const uint32_t quad = warp & 3;
+    const uint32_t half = (warp - 2) >> 2;
     const uint32_t m = quad * 32 + lane;           // accumulator row = output position in the tile
     const int hl = m / kTileW, wl = m % kTileW;
+    const float* scale_h = ctl->scale + half * 32;
     uint32_t s_it = 0, acc_phase = 0;
     for (;;) {
       const uint32_t ss = s_it % kSched;
@@ -421,67 +473,74 @@ __global__ void __launch_bounds__(kThreads, 1)
       const int h = th * kTileH + hl;
       const bool inside = h < P.H;
       const int vh = h == 0 ? 1 : (h == P.H - 1 ? 2 : 0);
+      // tile rows 1..H-2 only, all of them inside the image: every position is of the interior class
+      const bool rows_interior = th > 0 && (th + 1) * kTileH < P.H;
       uint32_t used = 0;
       for (int t = 0; t < gd.ntiles; ++t) {
         const TilePlan tp = P.tiles[gd.tile0 + t];
         const uint32_t touched = tp.touched;
         used |= ((1u << tp.nslots) - 1u) << tp.slot0;
-        const int w = (tw0 + t) * kTileW + wl;
+        const int tw = tw0 + t;
+        const int w = tw * kTileW + wl;
         const int vw = w == 0 ? 1 : (w == P.W - 1 ? 2 : 0);
         const int variant = P.nvar == 9 ? vh * 3 + vw : 0;
+        const bool tile_interior = P.nvar == 1 ? (th + 1) * kTileH <= P.H : (rows_interior && tw > 0 && tw < P.tiles_w - 1);
         for (int dout = 0; dout < P.Dout; ++dout) {
           const bool has_acc = (touched >> dout) & 1;  // else: no live box reached this accumulator
+          if (!has_acc && P.out_mode == 0 && tile_interior && ctl->row_zero[dout]) {
+            // nothing but background in reach and the layer stores deviations: the 16 KB block is zero.
+            // This warp clears tile rows 4*quad + 2*half, +1 (1 KB each, contiguous).
+            __nv_bfloat16* dst0 = reinterpret_cast<__nv_bfloat16*>(P.out) +
+                                  ((((size_t)b * P.Dout + dout) * P.H + th * kTileH + quad * 4 + half * 2) * P.W + tw * kTileW) * 64;
+#pragma unroll
+            for (int r = 0; r < 2; ++r) {
+              uint4* dst = reinterpret_cast<uint4*>(dst0 + (size_t)r * P.W * 64);
+              dst[lane] = make_uint4(0u, 0u, 0u, 0u);
+              dst[lane + 32] = make_uint4(0u, 0u, 0u, 0u);
+            }
+            continue;
+          }
           const uint32_t slot = tp.slot0 + __popc(touched & ((1u << dout) - 1u));
+          uint32_t r[32];
           if (has_acc) {
             mbar_wait(&ctl->acc_full[slot], (acc_phase >> slot) & 1);
             tc_fence_after_sync();
-          }
-          const uint32_t taddr = tmem_base + ((quad * 32) << 16) + slot * 64;
-          const float* shift_row = ctl->table + (variant * P.Dout + dout) * 64;
-          const float* sub_row = ctl->sub + dout * 64;
+            tmem_ld_32x32b_x32(tmem_base + ((quad * 32) << 16) + slot * 64 + half * 32, r);
+            tmem_ld_wait();
+            // accumulator read: hand it back to the MMA issuer before the global stores
+            tc_fence_before_sync();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&ctl->acc_empty[slot]);
+          } else {
 #pragma unroll
-          for (int half = 0; half < 2; ++half) {
-            uint32_t r[32];
-            if (has_acc) {
-              tmem_ld_32x32b_x32(taddr + half * 32, r);
-              tmem_ld_wait();
-              if (half == 1) {
-                // accumulator fully read: hand it back to the MMA issuer before the global stores
-                tc_fence_before_sync();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&ctl->acc_empty[slot]);
+            for (int j = 0; j < 32; ++j) r[j] = 0u;
+          }
+          if (inside) {
+            const float* shift_row = ctl->table + (variant * P.Dout + dout) * 64 + half * 32;
+            const float* sub_row = ctl->sub + dout * 64 + half * 32;
+            float v[32];
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              v[j] = fmaxf(fmaf(__uint_as_float(r[j]), scale_h[j], shift_row[j]), 0.0f) - sub_row[j];
+            if (P.out_mode == 0) {
+              __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
+                                   ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32;
+#pragma unroll
+              for (int q = 0; q < 2; ++q) {  // 2 x 32 B: one full sector per lane per store
+                uint32_t pk[8];
+#pragma unroll
+                for (int e = 0; e < 8; ++e) {
+                  const __nv_bfloat162 t2 = __floats2bfloat162_rn(v[q * 16 + 2 * e], v[q * 16 + 2 * e + 1]);
+                  pk[e] = *reinterpret_cast<const uint32_t*>(&t2);
+                }
+                st_global_v8(dst + q * 16, pk);
               }
             } else {
+              const size_t plane = (size_t)P.H * P.W;
+              float* dst = reinterpret_cast<float*>(P.out) +
+                           ((size_t)b * 64 * P.Dout + (size_t)(half * 32) * P.Dout + dout) * plane + (size_t)h * P.W + w;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) r[j] = 0u;
-            }
-            if (inside) {
-              float v[32];
-#pragma unroll
-              for (int j = 0; j < 32; ++j) {
-                const int c = half * 32 + j;
-                v[j] = fmaxf(fmaf(__uint_as_float(r[j]), ctl->scale[c], shift_row[c]), 0.0f) - sub_row[c];
-              }
-              if (P.out_mode == 0) {
-                __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
-                                     ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32;
-#pragma unroll
-                for (int q = 0; q < 4; ++q) {
-                  uint32_t pk[4];
-#pragma unroll
-                  for (int e = 0; e < 4; ++e) {
-                    const __nv_bfloat162 t2 = __floats2bfloat162_rn(v[q * 8 + 2 * e], v[q * 8 + 2 * e + 1]);
-                    pk[e] = *reinterpret_cast<const uint32_t*>(&t2);
-                  }
-                  *reinterpret_cast<uint4*>(dst + q * 8) = make_uint4(pk[0], pk[1], pk[2], pk[3]);
-                }
-              } else {
-                const size_t plane = (size_t)P.H * P.W;
-                float* dst = reinterpret_cast<float*>(P.out) +
-                             ((size_t)b * 64 * P.Dout + (size_t)(half * 32) * P.Dout + dout) * plane + (size_t)h * P.W + w;
-#pragma unroll
-                for (int j = 0; j < 32; ++j) dst[(size_t)j * P.Dout * plane] = v[j];
-              }
+              for (int j = 0; j < 32; ++j) dst[(size_t)j * P.Dout * plane] = v[j];
             }
           }
         }
@@ -590,10 +649,12 @@ __global__ void __launch_bounds__(64)
 // Voxel coordinates -> live-box flags of a chain of up to three stacked 3x3x3 layers.  A voxel at
 // (z, y, x) makes the input of layer l deviate from its background at most at planes S_l (S_0 = {z},
 // S_{l+1} = output depths fed by S_l), rows y-l..y+l and columns x-l..x+l; every box (plane, th, tw, kw)
-// of layer l that contains such a position is flagged.  One warp per voxel.
+// of layer l that contains such a position is flagged.  Half a warp per voxel: lane = (th candidate,
+// kw, tw candidate); the reachable planes (<= 3 per layer) are walked in a short loop.
 struct MarkParams {
   int B, D, H, W, tiles_h, tiles_w, n_layers;
-  int Din[3], stride_d[3], pad_d[3];
+  int Din[3];
+  uint16_t reach[3][kMaxPlanes];  // reach[l][p]: planes of layer l+1's input fed by plane p of layer l's
   uint8_t* flags[3];
 };
 
@@ -605,44 +666,43 @@ __global__ void __launch_bounds__(256)
     const int64_t live = *n_voxels_dev;
     if (live < total) total = live;
   }
-  const uint32_t lane = threadIdx.x & 31;
-  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t r = warp; r < total; r += nwarps) {
-    const long long* c = coords + r * 4;
-    const long long cb = c[0], cz = c[1], cy = c[2], cx = c[3];
-    if (cb < 0 || cb >= Q.B || cz < 0 || cz >= Q.D || cy < 0 || cy >= Q.H || cx < 0 || cx >= Q.W) continue;
+  const uint32_t l16 = threadIdx.x & 15;
+  const int th_sel = (l16 >> 3) & 1, kw = (l16 >> 1) & 3, cand = l16 & 1;
+  const int64_t first = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 4;
+  const int64_t step = ((int64_t)gridDim.x * blockDim.x) >> 4;
+  const int plane_stride = Q.tiles_h * Q.tiles_w * 3;
+  for (int64_t r = first; r < total; r += step) {
+    const longlong2 c01 = *reinterpret_cast<const longlong2*>(coords + r * 4);
+    const longlong2 c23 = *reinterpret_cast<const longlong2*>(coords + r * 4 + 2);
+    const long long cb = c01.x, cz = c01.y, cy = c23.x, cx = c23.y;
+    if (cb < 0 || cb >= Q.B || cz < 0 || cz >= Q.D || cy < 0 || cy >= Q.H || cx < 0 || cx >= Q.W || kw == 3) continue;
     const int b = (int)cb, y = (int)cy, x = (int)cx;
     uint32_t planes = 1u << (int)cz;
-    for (int l = 0; l < Q.n_layers; ++l) {
-      const int Din = Q.Din[l];
-      // rows [y-l, y+l] meet box rows [16 th - 1, 16 th + 16]
-      int th_lo = (y - l - 1) >> 4, th_hi = (y + l + 1) >> 4;
-      if (th_lo < 0) th_lo = 0;
-      if (th_hi > Q.tiles_h - 1) th_hi = Q.tiles_h - 1;
-      const int n_th = th_hi - th_lo + 1;
-      const int combos = __popc(planes) * n_th * 6;  // plane x th x kw x {first, second} tw candidate
-      for (int i = lane; i < combos; i += 32) {
-        const int cand = i % 2, kw = (i / 2) % 3, th = th_lo + (i / 6) % n_th;
-        const int p = (int)__fns(planes, 0, i / (6 * n_th) + 1);  // the n-th reachable plane
-        // columns [x-l, x+l] meet box columns [8 tw + kw - 1, 8 tw + kw + 6]
-        const int s_lo = x - l - 6 - kw, s_hi = x + l + 1 - kw;        // 8 tw in [s_lo, s_hi]
-        int tw = (s_lo + 7) >> 3;                                       // ceil(s_lo / 8)
+#pragma unroll
+    for (int l = 0; l < 3; ++l) {
+      if (l < Q.n_layers) {
+        // rows [y-l, y+l] meet box rows [16 th - 1, 16 th + 16]
+        int th_lo = (y - l - 1) >> 4, th_hi = (y + l + 1) >> 4;
+        if (th_lo < 0) th_lo = 0;
+        if (th_hi > Q.tiles_h - 1) th_hi = Q.tiles_h - 1;
+        const int th = th_lo + th_sel;
+        // columns [x-l, x+l] meet box columns [8 tw + kw - 1, 8 tw + kw + 6]:  8 tw in [s_lo, s_hi]
+        const int s_lo = x - l - 6 - kw, s_hi = x + l + 1 - kw;
+        int tw = (s_lo + 7) >> 3;  // ceil(s_lo / 8)
         if (tw < 0) tw = 0;
         tw += cand;
-        if (tw * 8 > s_hi || tw > Q.tiles_w - 1) continue;
-        uint8_t* f = Q.flags[l] + ((((size_t)b * Din + p) * Q.tiles_h + th) * Q.tiles_w + tw) * 3 + kw;
-        if (*f == 0) *f = 1;
-      }
-      // planes of the next layer's input that this voxel can reach
-      if (l + 1 < Q.n_layers) {
-        const int Dn = Q.Din[l + 1];
-        uint32_t next = 0;
-        for (int d = 0; d < Dn; ++d)
-          for (int kd = 0; kd < 3; ++kd) {
-            const int p = d * Q.stride_d[l] - Q.pad_d[l] + kd;
-            if (p >= 0 && p < Din && ((planes >> p) & 1)) next |= 1u << d;
+        const bool ok = th <= th_hi && tw * 8 <= s_hi && tw <= Q.tiles_w - 1;
+        uint8_t* base = Q.flags[l] + (size_t)b * Q.Din[l] * plane_stride + (th * Q.tiles_w + tw) * 3 + kw;
+        uint32_t pl = planes, next = 0;
+        while (pl) {
+          const int p = __ffs(pl) - 1;
+          pl &= pl - 1;
+          next |= Q.reach[l][p];
+          if (ok) {
+            uint8_t* f = base + (size_t)p * plane_stride;
+            if (*f == 0) *f = 1;
           }
+        }
         planes = next;
       }
     }
@@ -776,10 +836,19 @@ int vn_conv3d_mark_boxes(const int64_t* coords, int64_t K, const int32_t* n_voxe
     VN_REQUIRE((stride_d[l] == 1 || stride_d[l] == 2) && (pad_d[l] == 0 || pad_d[l] == 1) && din + 2 * pad_d[l] >= 3,
                "conv3d_mark_boxes: layer %d geometry", l);
     VN_REQUIRE(flags[l] != nullptr, "conv3d_mark_boxes: flags[%d] is null", l);
-    Q.Din[l] = din; Q.stride_d[l] = stride_d[l]; Q.pad_d[l] = pad_d[l]; Q.flags[l] = flags[l];
-    din = out_depth(din, stride_d[l], pad_d[l]);
+    Q.Din[l] = din; Q.flags[l] = flags[l];
+    const int dout = out_depth(din, stride_d[l], pad_d[l]);
+    VN_REQUIRE(dout >= 1 && dout <= kMaxPlanes, "conv3d_mark_boxes: layer %d output depth %d", l, dout);
+    for (int p = 0; p < din; ++p) {
+      uint16_t m = 0;
+      for (int d = 0; d < dout; ++d)
+        for (int kd = 0; kd < 3; ++kd)
+          if (d * stride_d[l] - pad_d[l] + kd == p) m |= (uint16_t)(1u << d);
+      Q.reach[l][p] = m;
+    }
+    din = dout;
   }
-  const int64_t want = (K + 7) / 8;
+  const int64_t want = (K + 15) / 16;  // 16 voxels per 256-thread block
   const int64_t cap = (int64_t)sm_count() * 8;
   k_mark_boxes<<<(unsigned)(want < cap ? want : cap), 256, 0, as_stream(stream)>>>(
       reinterpret_cast<const long long*>(coords), K, n_voxels_dev, Q);
