@@ -321,3 +321,50 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
             "vn_conv3d_bn_relu_fwd",
         )
     return out
+
+
+def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, stride_d: int, pad_d: int) -> dict:
+    """Diagnostics (blocking, host side): decode the work plan the last vn_conv3d_bn_relu_fwd call left
+    in `workspace` (PlanHeader | GroupDesc[n_tiles] | TilePlan[n_tiles], see vn_conv3d.cu) and count
+    what the kernel actually executed: live input boxes, tcgen05 FLOPs, operand bytes loaded by TMA.
+    Used by bench.py for the executed-work roofline; not part of the product path."""
+    import numpy as np
+
+    _require_cuda(workspace)
+    tiles_h, tiles_w = (H + 15) // 16, W // 8
+    n_tiles = B * tiles_h * tiles_w
+    raw = workspace.cpu().numpy()
+    hdr = raw[:16].view(np.int32)
+    tiles = raw[16 + 8 * n_tiles: 16 + 16 * n_tiles].view(np.uint32).reshape(n_tiles, 2)
+    live = tiles[:, 0]
+    touched = tiles[:, 1] & 0xFF
+    restore = (tiles[:, 1] >> 24) & 0xFF
+    Dout = conv3d_out_depth(Din, stride_d, pad_d)
+    nkd = []
+    for p in range(Din):
+        n = 0
+        for kd in range(3):
+            num = p + pad_d - kd
+            if num >= 0 and num % stride_d == 0 and num // stride_d < Dout:
+                n += 1
+        nkd.append(n)
+    nchunk = cin // 64
+    boxes = 0
+    flops = 0
+    for p in range(Din):
+        cnt = 0
+        for kw in range(3):
+            cnt += int(((live >> (p * 3 + kw)) & 1).sum())
+        boxes += cnt
+        flops += cnt * nchunk * 12 * 2 * 128 * 64 * nkd[p] * 16
+    popc = np.zeros(n_tiles, dtype=np.int64)
+    rpop = np.zeros(n_tiles, dtype=np.int64)
+    for d in range(8):
+        popc += (touched >> d) & 1
+        rpop += (restore >> d) & 1
+    return {
+        "tiles": int(n_tiles), "live_tiles": int((live != 0).sum()), "groups": int(hdr[0]),
+        "live_boxes": int(boxes), "boxes_total": int(n_tiles * sum(1 for n in nkd if n) * 3),
+        "touched_blocks": int(popc.sum()), "restored_blocks": int(rpop.sum()), "blocks_total": int(n_tiles * Dout),
+        "executed_flops": int(flops), "a_bytes": int(boxes * nchunk * 18432),
+    }
