@@ -242,17 +242,29 @@ def main():
             m.running_var.data = 0.5 + torch.rand(m.running_var.shape, generator=g)
     fe = vn.VoxelNetFrontEnd(fnet.to(dev), mnet.to(dev), target)
 
-    # ---- inputs: pinned host staging + resident device copy ---------------------------------
+    # ---- inputs: pinned host staging + resident device copies of TWO different batches --------------
+    # Steps alternate between them: the resident conv outputs are only rewritten where a voxel reaches
+    # now or reached in the previous step, so repeating one batch would hide the restore traffic.
     import numpy as np
 
-    sizes = [int(f.shape[0]) for f in frames]
-    offs_np = np.zeros(batch + 1, dtype=np.int32)
-    np.cumsum(sizes, out=offs_np[1:])
-    host_points = torch.from_numpy(np.concatenate(frames, 0)).pin_memory()
-    host_offsets = torch.from_numpy(offs_np).pin_memory()
-    max_n = max(sizes)
-    points = host_points.to(dev)
-    offsets = host_offsets.to(dev)
+    if args.config == "stress64":
+        frames_b = [make_frames(args.config, 0, 1, seed=5000 + i)[0] for i in mine]
+    else:
+        frames_b = make_frames(args.config, rank, batch, seed=1000 * rank + 500)
+
+    class Batch:
+        def __init__(self, fr):
+            sizes = [int(f.shape[0]) for f in fr]
+            self.offs_np = np.zeros(batch + 1, dtype=np.int32)
+            np.cumsum(sizes, out=self.offs_np[1:])
+            self.host_points = torch.from_numpy(np.concatenate(fr, 0)).pin_memory()
+            self.host_offsets = torch.from_numpy(self.offs_np).pin_memory()
+            self.max_n = max(sizes)
+            self.points = self.host_points.to(dev)
+            self.offsets = self.host_offsets.to(dev)
+
+    batches = [Batch(frames), Batch(frames_b)]
+    batches.sort(key=lambda x: -x.points.shape[0])  # the larger one first: buffers are sized once
     host_counts = torch.empty(batch + 1, dtype=torch.int32).pin_memory()
 
     def barrier():
@@ -260,48 +272,82 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    def step(i, timer=None):
+        bt = batches[i % 2]
+        return fe.forward_points(bt.points, bt.offsets, bt.max_n, timer=timer)
+
     # ---- device-resident timing ------------------------------------------------------------------
-    for _ in range(args.warmup):
-        fe.forward_points(points, offsets, max_n)
+    counts = []
+    for i in range(max(args.warmup, 2)):
+        step(i)
+        if i < 2:
+            torch.cuda.synchronize()
+            counts.append(fe.voxel_counts())  # also checks the voxel capacity
     torch.cuda.synchronize()
-    counts = fe.voxel_counts()  # also checks the voxel capacity
     sampler = ClockSampler(local_rank)
     sampler.start()
-    for _ in range(2):  # keep the GPU busy while nvidia-smi spins up
-        fe.forward_points(points, offsets, max_n)
+    for i in range(2):  # keep the GPU busy while nvidia-smi spins up
+        step(i)
     timer = StageTimer()
     barrier()
     wall0 = time.time()
     launches0 = _cabi.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
-    for _ in range(args.steps):
-        fe.forward_points(points, offsets, max_n, timer=timer)
+    for i in range(args.steps):
+        step(i, timer=timer)
     e1.record()
     barrier()
     wall1 = time.time()
     launches = _cabi.launch_count() - launches0
     clocks = sampler.stop(wall0, wall1)
     ms_total = e0.elapsed_time(e1)
+    # what the conv launches executed (decoded from the device-built plans of the last two steps)
+    plan = []
+    for i in range(2):
+        step(args.steps + i)
+        torch.cuda.synchronize()
+        plan.append(fe.plan_stats())
+    plan = [{k: (plan[0][l][k] + plan[1][l][k]) / 2 for k in plan[0][l]} for l in range(3)]
 
     # ---- end to end: host buffers in, voxel counts out ---------------------------------------------
-    pts_dev = torch.empty_like(points)
-    offs_dev = torch.empty_like(offsets)
+    # Two device staging buffers: the H2D copy of step i+1 runs on a copy stream while step i computes.
+    stage = [(torch.empty_like(batches[0].points), torch.empty_like(batches[0].offsets)) for _ in range(2)]
+    copy_stream = torch.cuda.Stream()
+    ready = [torch.cuda.Event() for _ in range(2)]
+    freed = [torch.cuda.Event() for _ in range(2)]
+    main = torch.cuda.current_stream()
 
-    def e2e_step():
-        pts_dev.copy_(host_points, non_blocking=True)
-        offs_dev.copy_(host_offsets, non_blocking=True)
-        fe.forward_points(pts_dev, offs_dev, max_n)
+    def e2e_upload(i):
+        bt, (pd, od) = batches[i % 2], stage[i % 2]
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(freed[i % 2])
+            pd[: bt.points.shape[0]].copy_(bt.host_points, non_blocking=True)
+            od.copy_(bt.host_offsets, non_blocking=True)
+            ready[i % 2].record(copy_stream)
+
+    def e2e_compute(i):
+        bt, (pd, od) = batches[i % 2], stage[i % 2]
+        main.wait_event(ready[i % 2])
+        fe.forward_points(pd[: bt.points.shape[0]], od, bt.max_n)
+        freed[i % 2].record(main)
         host_counts.copy_(fe.voxels.voxel_offsets, non_blocking=True)
 
-    for _ in range(2):
-        e2e_step()
+    def e2e_run(n):
+        for k in range(2):
+            freed[k].record(main)
+        e2e_upload(0)
+        for i in range(n):
+            if i + 1 < n:
+                e2e_upload(i + 1)
+            e2e_compute(i)
+            main.synchronize()  # the caller consumes host_counts every step
+
+    e2e_run(2)
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    for _ in range(args.steps):
-        e2e_step()
-        torch.cuda.current_stream().synchronize()  # the caller consumes host_counts every step
+    e2e_run(args.steps)
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)
@@ -319,41 +365,79 @@ def main():
         flops = conv_flops_per_frame(c.depth, c.height, c.width)
         ms_step = ms_total / args.steps
         value = frames_total / (ms_step * 1e-3)
-        conv1_ms = stages.get("conv1", float("nan"))
-        achieved = flops[0] * batch / (conv1_ms * 1e-3) / 1e12
-        K_total = counts[-1]
-        N_total = int(offs_np[-1])
+        K_total = sum(cc[-1] for cc in counts) / len(counts)
+        N_total = sum(int(bt.offs_np[-1]) for bt in batches) / 2
         T = c.points_per_voxel
+        # SURVEY 8(d) algorithmic bytes (the materialised data flow: [K,T,7] written then read) ...
         bytes_vox = 16 * N_total + 28 * T * K_total + 32 * K_total + 8 * K_total
         bytes_svfe = 28 * T * K_total + 512 * K_total
+        # ... and what the fused kernels really move: the feature buffer never exists
+        moved_vox = 16 * N_total + 5 * 4 * N_total                      # points in, per-point key/row/slot/bucket words
+        moved_svfe = 16 * N_total / 2 + 4 * N_total / 2 + 512 * K_total + 40 * K_total
+        bytes_scatter = 512 * K_total + 256 * K_total + 32 * K_total
         stage_roofline = {
-            "voxelize": {"bound": "hbm", "achieved": bytes_vox / (stages["voxelize"] * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s"},
-            "svfe": {"bound": "hbm", "achieved": bytes_svfe / (stages["svfe"] * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s"},
-            "conv1": {"bound": "tensor", "achieved": achieved, "peak": peaks["tflops"], "unit": "TFLOP/s"},
-            "conv2": {"bound": "tensor", "achieved": flops[1] * batch / (stages["conv2"] * 1e-3) / 1e12, "peak": peaks["tflops"], "unit": "TFLOP/s"},
-            "conv3": {"bound": "tensor", "achieved": flops[2] * batch / (stages["conv3"] * 1e-3) / 1e12, "peak": peaks["tflops"], "unit": "TFLOP/s"},
+            "voxelize": {"bound": "hbm", "achieved": bytes_vox / (stages["voxelize"] * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                         "moved_gbs": moved_vox / (stages["voxelize"] * 1e-3) / 1e9},
+            "svfe": {"bound": "hbm", "achieved": bytes_svfe / (stages["svfe"] * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                     "moved_gbs": moved_svfe / (stages["svfe"] * 1e-3) / 1e9,
+                     "fp32_tflops": (N_total / 2 + K_total) * (2 * 7 * 16 + 2 * 32 * 64) / (stages["svfe"] * 1e-3) / 1e12},
+            "scatter": {"bound": "hbm", "achieved": bytes_scatter / (stages["scatter"] * 1e-3) / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s"},
         }
-        for v in stage_roofline.values():
-            v["frac"] = v["achieved"] / v["peak"]
+        # Conv layers.  The kernels skip input boxes no voxel can reach and store only output blocks that
+        # are fed now or were fed in the previous step, so two figures are given per layer:
+        #   executed   FLOPs of the tcgen05.mma instructions actually issued (from the device-built plan)
+        #   dense_eq   SURVEY 8(d)'s dense-equivalent FLOPs of the layer / time (can exceed the peak)
+        # and the HBM side: unique live input blocks + stored output blocks + the weights once.
+        out_bytes = [128 * 64 * 2, 128 * 64 * 2, 128 * 64 * 4]
+        wbytes = [27 * 128 * 64 * 2, 27 * 64 * 64 * 2, 27 * 64 * 64 * 2]
+        conv_roof = []
+        for l, name in enumerate(("conv1", "conv2", "conv3")):
+            t = stages[name] * 1e-3
+            st = plan[l]
+            hbm = st["unique_input_bytes"] + (st["touched_blocks"] + st["restored_blocks"]) * out_bytes[l] + wbytes[l]
+            ent = {
+                "tensor": {"achieved": st["executed_flops"] / t / 1e12, "peak": peaks["tflops"], "unit": "TFLOP/s"},
+                "hbm": {"achieved": hbm / t / 1e9, "peak": peaks["hbm_gbs"], "unit": "GB/s", "bytes_per_launch": hbm},
+                "dense_equivalent_tflops": flops[l] * batch / t / 1e12,
+                "live_box_fraction": st["live_boxes"] / st["boxes_total"],
+                "stored_block_fraction": (st["touched_blocks"] + st["restored_blocks"]) / st["blocks_total"],
+                "restored_block_fraction": st["restored_blocks"] / st["blocks_total"],
+                "groups": st["groups"],
+            }
+            for k in ("tensor", "hbm"):
+                ent[k]["frac"] = ent[k]["achieved"] / ent[k]["peak"]
+            ent["bound"] = "tensor" if ent["tensor"]["frac"] >= ent["hbm"]["frac"] else "hbm"
+            stage_roofline[name] = ent
+            conv_roof.append(ent)
+        for k in ("voxelize", "svfe", "scatter"):
+            stage_roofline[k]["frac"] = stage_roofline[k]["achieved"] / stage_roofline[k]["peak"]
+        dom = max(range(3), key=lambda l: stages["conv%d" % (l + 1)])
+        dk = conv_roof[dom]
+        kind = dk["bound"]
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.config == "stress64" else "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": desc, "name": args.config, "batch_per_gpu": batch, "points_per_batch": N_total,
-                       "voxels_per_batch": K_total, "l2_policy": "working set (%.1f GB dense grid + activations) exceeds L2" % (fe.dense.numel() * 2 / 1e9),
+                       "voxels_per_batch": K_total,
+                       "inputs": "two different batches alternate step by step (resident outputs are restored where the previous batch reached)",
+                       "l2_policy": "working set (%.1f GB dense grid + activations) exceeds L2" % (fe.dense.numel() * 2 / 1e9),
                        "vfe": "fp32", "conv": "bf16 operands, fp32 accumulate (tcgen05)"},
             "ms_per_frame": ms_step / batch,
             "stages_ms": stages,
             "clocks": clocks,
             "e2e": {"value": frames_total / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
-                    "h2d_bytes_per_step": int(host_points.numel() * 4 + host_offsets.numel() * 4),
+                    "h2d_bytes_per_step": int(sum(bt.host_points.numel() * 4 + bt.host_offsets.numel() * 4 for bt in batches) / 2),
                     "d2h_bytes_per_step": int(host_counts.numel() * 4),
-                    "note": "result read back per step = per-frame voxel counts; the (B,128,H,W) tensor stays on the device for the RPN"},
+                    "note": "H2D of step i+1 overlaps step i on a copy stream (two staging buffers); result read back per step = "
+                            "per-frame voxel counts; the (B,128,H,W) tensor stays on the device for the RPN"},
             "gpu_launches": int(launches),
-            "roofline": {"kernel": "k_conv3d_bn_relu (layer 1: 128->64, D 10->5)", "bound": "tensor", "achieved": achieved,
-                         "peak": peaks["tflops"], "unit": "TFLOP/s", "frac": achieved / peaks["tflops"], "traffic": None,
-                         "peak_source": peaks["source"] + " (bf16_tflops_sustained)",
-                         "flops_per_launch": flops[0] * batch},
+            "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
+                         "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": None,
+                         "peak_source": peaks["source"] + (" (bf16_tflops_sustained)" if kind == "tensor" else " (hbm_gbs)"),
+                         "counts": "executed work: MMAs issued / blocks moved, decoded from the device-built plan; "
+                                   "dense-equivalent %.0f TFLOP/s" % dk["dense_equivalent_tflops"],
+                         "other_bound": {k: dk[k] for k in ("tensor", "hbm") if k != kind}},
             "stage_roofline": stage_roofline,
         }
         if world == 1 and not args.no_cpu_baseline:

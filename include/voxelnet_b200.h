@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 2
+#define VN_ABI_VERSION 3
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -120,17 +120,19 @@ int vn_svfe_fused_fwd(const float* feature, int64_t K, int32_t T, const int32_t*
 
 /* Fully fused fast path: phase 2 of the voxelizer and the stacked VFE in one kernel.  After
  * vn_voxelize_index, builds each voxel's distinct feature rows on chip (first-T selection, fp64
- * centroid - utils.py:78-88) and evaluates VFE-1 -> VFE-2 -> voxel-wise max on them (model.py:95-100),
- * writing voxelwise [max_voxels,128] f32 and coordinate_buffer [max_voxels,4] i64 (number_buffer may
- * be NULL).  The [K,T,7] feature buffer is never materialised; results are bit-identical to
- * vn_voxelize_fill followed by vn_svfe_fused_fwd. */
+ * centroid - utils.py:78-88) and evaluates VFE-1 -> VFE-2 -> voxel-wise max on them (model.py:95-100).
+ * Outputs: coordinate_buffer [max_voxels,4] i64 (number_buffer may be NULL) and the voxel-wise maxima,
+ * either as voxelwise [max_voxels,128] f32, or written straight into their cells of the resident bf16
+ * grid dense_bf16 [n_frames, D, H, W, 128] (the scatter of model.py:102-106, same rounding as
+ * vn_scatter_dense_bf16), or both; one of the two may be NULL.  The [K,T,7] feature buffer is never
+ * materialised; results are bit-identical to vn_voxelize_fill + vn_svfe_fused_fwd (+ scatter). */
 int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
                            int32_t n_frames, int64_t n_points_total, const int32_t* voxel_offsets,
                            int64_t max_voxels, const float* w1, const float* b1, const float* s1,
                            const float* t1, const float* w2, const float* b2, const float* s2,
-                           const float* t2, float* voxelwise, int64_t* coordinate_buffer,
-                           int64_t* number_buffer, void* workspace, size_t workspace_bytes,
-                           vn_stream_t stream);
+                           const float* t2, float* voxelwise, void* dense_bf16,
+                           int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace,
+                           size_t workspace_bytes, vn_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Sparse -> dense - replaces torch.sparse.FloatTensor(coords.t(), voxelwise, [B,D,H,W,128])
@@ -169,6 +171,9 @@ int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, v
  *   workspace  the per-call work plan (tile masks, tile groups, work counter); contents are scratch. */
 size_t vn_conv3d_box_flags_bytes(int32_t B, int32_t Din, int32_t H, int32_t W);
 size_t vn_conv3d_workspace_bytes(int32_t B, int32_t H, int32_t W);
+/*   out state  [B][ceil(H/16)][W/8] bytes kept next to an OUTPUT buffer that is reused from call to call
+ *              (see `out_state` below); fill with 0xFF when the buffer is new or the parameters changed. */
+size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W);
 
 #define VN_CONV_FLAGS_CONSUME 1     /* reset every flag that was read, leaving the table all-zero again */
 #define VN_CONV_FLAGS_BORDER_RING 2 /* also treat boxes that contain an H/W border position as live    */
@@ -189,13 +194,20 @@ size_t vn_conv3d_workspace_bytes(int32_t B, int32_t H, int32_t W);
  * box_flags (optional): flag[b][p][th][tw][kw] == 0 asserts that the input box
  *   x[b, p, 16*th-1 .. 16*th+16, 8*tw+kw-1 .. 8*tw+kw+6, :] is all zeros; its load and its MMAs are
  *   skipped (exact: zero operands contribute nothing).  NULL: every box is live.  flag_opts: VN_CONV_FLAGS_*.
+ * out_state (optional): makes y a RESIDENT buffer.  Where no live box reaches a 16x8 output block the
+ *   layer writes a constant that depends only on its parameters (0 for a deviation-coded layer).  Bit d
+ *   of out_state[b][th][tw] records that block (b, d, th, tw) of y currently holds anything else.  The
+ *   call then writes only the blocks that are fed now (setting the bit) or were fed by the previous
+ *   call on the same y (rewriting the constant, clearing the bit) - exact, and the untouched ~60 % of
+ *   a KITTI-shaped frame is neither computed nor stored.  Start from all 0xFF (every block is
+ *   written once).  NULL: every block of y is written.
  * workspace: vn_conv3d_workspace_bytes(B, H, W) bytes, 16-byte aligned. */
 int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin,
                           int32_t stride_d, int32_t pad_d, const void* packed_weight,
                           const float* scale /* [64] */, const float* shift_table, int32_t n_variants,
                           const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
-                          int32_t flag_opts, void* workspace, size_t workspace_bytes,
-                          vn_stream_t stream);
+                          int32_t flag_opts, uint8_t* out_state, void* workspace,
+                          size_t workspace_bytes, vn_stream_t stream);
 
 /* Background folding for a layer whose INPUT is stored as a deviation from a per-(plane, channel)
  * background bg_in [Din][cin] f32 (the previous layer's `sub`; NULL = zero background).  The

@@ -81,7 +81,17 @@ def test_fused_voxel_svfe_is_bit_identical_to_materialised_path(cuda_device, tar
     vw = torch.empty((K, 128), dtype=torch.float32, device=cuda_device)
     co = torch.empty((K, 4), dtype=torch.int64, device=cuda_device)
     nu = torch.empty((K,), dtype=torch.int64, device=cuda_device)
-    ops.voxelize_svfe_fused(grid, points, offsets, vo, fnet.vfe_1.folded(), fnet.vfe_2.folded(), vw, co, nu, ws)
+    dense = torch.zeros((3, grid.D, grid.H, grid.W, 128), dtype=torch.bfloat16, device=cuda_device)
+    ops.voxelize_svfe_fused(grid, points, offsets, vo, fnet.vfe_1.folded(), fnet.vfe_2.folded(), vw, co, nu, ws, dense=dense)
+    # the kernel's own scatter == vn_scatter_dense_bf16 of its voxelwise rows
+    dense2 = torch.zeros_like(dense)
+    ops.scatter_dense_bf16(want, vb.coordinate, dense2)
+    assert torch.equal(dense.view(torch.int16), dense2.view(torch.int16))
+    # dense-only mode (no voxelwise buffer) writes the same cells
+    dense3 = torch.zeros_like(dense)
+    co3 = torch.empty_like(co)
+    ops.voxelize_svfe_fused(grid, points, offsets, vo, fnet.vfe_1.folded(), fnet.vfe_2.folded(), None, co3, None, ws, dense=dense3)
+    assert torch.equal(dense3.view(torch.int16), dense2.view(torch.int16)) and torch.equal(co3, co)
     assert torch.equal(vo.cpu(), vb.voxel_offsets.cpu())
     assert torch.equal(co, vb.coordinate) and torch.equal(nu, vb.number)
     assert torch.equal(vw.view(torch.int32), want.view(torch.int32))
@@ -110,3 +120,32 @@ def test_front_end_sparse_and_dense_chains_agree(cuda_device):
     b = _build(cuda_device, "Pedestrian", sd, skip_empty_boxes=False).forward_frames(frames)
     assert rel_max_err(a, b) < 6e-3
     assert float((a - b).norm() / b.norm()) < 3e-3
+
+
+@pytest.mark.parametrize("target", ["Pedestrian", "Car"])
+def test_resident_outputs_are_bit_identical_over_a_frame_sequence(cuda_device, target):
+    """resident_outputs=True stores only the output blocks a voxel reaches now or reached in the previous
+    step; over a sequence of different batches (dense, nearly empty, dense again) every result must
+    equal, bit for bit, the result of the pipeline that rewrites every block."""
+    sd = OM.random_state_dict(16)
+    a, b = synth_frames(2, 90), synth_frames(2, 95)
+    sparse = [f[:300].copy() for f in b]
+    seq = [a, b, sparse, a, a]
+    res = _build(cuda_device, target, sd, resident_outputs=True)
+    full = _build(cuda_device, target, sd, resident_outputs=False)
+    for i, frames in enumerate(seq):
+        got = res.forward_frames(frames)
+        want = full.forward_frames(frames)
+        assert torch.equal(got.view(torch.int32), want.view(torch.int32)), "step %d" % i
+        assert torch.equal(res.act1.view(torch.int16), full.act1.view(torch.int16)), "act1 step %d" % i
+        assert torch.equal(res.act2.view(torch.int16), full.act2.view(torch.int16)), "act2 step %d" % i
+    stats = res.plan_stats()
+    assert all(s["restored_blocks"] == 0 for s in stats)  # the last two steps saw the same frames
+    assert all(0 < s["touched_blocks"] < s["blocks_total"] for s in stats)
+    # new parameters change the constants the untouched blocks hold: refresh must invalidate them
+    sd2 = OM.random_state_dict(17)
+    for fe in (res, full):
+        load_state(fe.feature_net, sd2, "")
+        load_state(fe.middle_net, sd2, "")
+        fe.refresh_parameters()
+    assert torch.equal(res.forward_frames(b), full.forward_frames(b))

@@ -14,7 +14,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 2
+VN_ABI_VERSION = 3
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 
@@ -45,7 +45,7 @@ PROTOTYPES = {
     "vn_vfe_layer_fwd": (C.c_int, [_p, _p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vn_feature_mask": (C.c_int, [_p, _i64, _i32, _i32, _p, _p]),
     "vn_svfe_fused_fwd": (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
-    "vn_voxelize_svfe_fused": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vn_voxelize_svfe_fused": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vn_fill_zero": (C.c_int, [_p, _sz, _p]),
     "vn_scatter_dense_f32": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p]),
     "vn_scatter_dense_bf16": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p]),
@@ -53,7 +53,8 @@ PROTOTYPES = {
     "vn_conv3d_pack_weights": (C.c_int, [_p, _i32, _i32, _p, _p]),
     "vn_conv3d_box_flags_bytes": (_sz, [_i32, _i32, _i32, _i32]),
     "vn_conv3d_workspace_bytes": (_sz, [_i32, _i32, _i32]),
-    "vn_conv3d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _i32, _p, _p, _i32, _p, _sz, _p]),
+    "vn_conv3d_out_state_bytes": (_sz, [_i32, _i32, _i32]),
+    "vn_conv3d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _i32, _p, _p, _i32, _p, _p, _sz, _p]),
     "vn_conv3d_fold_background": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vn_conv3d_mark_boxes": (C.c_int, [_p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "vn_launch_count": (_i64, []),

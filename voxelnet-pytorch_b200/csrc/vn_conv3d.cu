@@ -79,7 +79,8 @@ struct TilePlan {
   uint8_t slot0;    // first TMEM slot of the tile inside its group; accumulator d sits at
                     // slot0 + popcount(touched & ((1 << d) - 1))
   uint8_t nslots;   // popcount(touched)
-  uint8_t pad;
+  uint8_t restore;  // bit d: output block d holds stale content of an earlier call and no accumulator feeds
+                    // it now: rewrite it with the layer background (see PlanParams::out_state)
 };
 static_assert(sizeof(TilePlan) == 8 && sizeof(GroupDesc) == 8 && sizeof(PlanHeader) == 16, "plan layout");
 
@@ -106,6 +107,11 @@ struct PlanParams {
   uint8_t* box_flags;  // [B][Din][tiles_h][tiles_w][3] or nullptr (every box live)
   int consume;         // reset the flags that were read
   int force_ring;      // boxes containing an H/W border position are live (input deviates there)
+  // [B][tiles_h][tiles_w] bytes kept by the caller next to the OUTPUT buffer, or nullptr.  Bit d set:
+  // output block (tile, d) holds something other than what the layer writes there when no live box
+  // reaches it (a constant that depends on the layer parameters only).  With a state table the kernel
+  // writes only blocks that are fed now or were fed by the previous call; without, every block.
+  uint8_t* out_state;
   PlanHeader* hdr;
   GroupDesc* groups;
   TilePlan* tiles;
@@ -168,11 +174,13 @@ __device__ __forceinline__ uint32_t warp_or(uint32_t v) {
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ PlanParams Q) {
   __shared__ uint32_t s_live[kMaxTilesW];
-  __shared__ uint8_t s_touched[kMaxTilesW], s_slot0[kMaxTilesW];
+  __shared__ uint8_t s_touched[kMaxTilesW], s_slot0[kMaxTilesW], s_restore[kMaxTilesW];
   const int b = blockIdx.x / Q.tiles_h, th = blockIdx.x % Q.tiles_h;
+  const int tile_row0 = (b * Q.tiles_h + th) * Q.tiles_w;
   uint32_t valid = 0;
   for (int p = 0; p < Q.Din; ++p)
     if (Q.plane[p].nkd != 0) valid |= 7u << (p * 3);
+  const uint32_t all_out = (1u << Q.Dout) - 1u;
   // rows 16*th-1 .. 16*th+16 of this tile row's boxes
   const bool ring_h = Q.force_ring && (th == 0 || (16 * th - 1 <= Q.H - 1 && Q.H - 1 <= 16 * th + 16));
   for (int tw = threadIdx.x; tw < Q.tiles_w; tw += blockDim.x) {
@@ -191,27 +199,42 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
       live = ~0u;
     }
     live &= valid;
+    const uint32_t touched = touched_accumulators(Q, live);
+    uint32_t stale = all_out;
+    if (Q.out_state != nullptr) {
+      stale = Q.out_state[tile_row0 + tw];
+      Q.out_state[tile_row0 + tw] = (uint8_t)touched;
+    }
     s_live[tw] = live;
-    s_touched[tw] = (uint8_t)touched_accumulators(Q, live);
+    s_slot0[tw] = 0;
+    s_touched[tw] = (uint8_t)touched;
+    s_restore[tw] = (uint8_t)(stale & ~touched & all_out);
   }
   __syncthreads();
   if (threadIdx.x == 0) {
-    int start = 0, cur_slots = 0, cur_n = 0;
-    const int tile_row0 = (b * Q.tiles_h + th) * Q.tiles_w;
+    // a group starts at a tile that has something to do, runs over at most kMaxGroupTiles tiles and
+    // kSlots accumulators, and ends at its last tile that has something to do
+    int start = -1, last = -1, cur_slots = 0;
     for (int tw = 0; tw < Q.tiles_w; ++tw) {
       const int n = __popc((uint32_t)s_touched[tw]);
-      if (cur_n > 0 && (cur_slots + n > kSlots || cur_n == kMaxGroupTiles)) {
+      const bool active = n > 0 || s_restore[tw] != 0;
+      if (start >= 0 && (cur_slots + n > kSlots || tw - start == kMaxGroupTiles)) {
         const int g = atomicAdd(&Q.hdr->n_groups, 1);
-        Q.groups[g] = GroupDesc{tile_row0 + start, cur_n};
-        start = tw; cur_slots = 0; cur_n = 0;
+        Q.groups[g] = GroupDesc{tile_row0 + start, last - start + 1};
+        start = -1;
+      }
+      if (start < 0) {
+        if (!active) continue;
+        start = tw;
+        cur_slots = 0;
       }
       s_slot0[tw] = (uint8_t)cur_slots;
       cur_slots += n;
-      ++cur_n;
+      if (active) last = tw;
     }
-    if (cur_n > 0) {
+    if (start >= 0) {
       const int g = atomicAdd(&Q.hdr->n_groups, 1);
-      Q.groups[g] = GroupDesc{tile_row0 + start, cur_n};
+      Q.groups[g] = GroupDesc{tile_row0 + start, last - start + 1};
     }
   }
   __syncthreads();
@@ -221,8 +244,8 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
     tp.touched = s_touched[tw];
     tp.slot0 = s_slot0[tw];
     tp.nslots = (uint8_t)__popc((uint32_t)s_touched[tw]);
-    tp.pad = 0;
-    Q.tiles[(size_t)(b * Q.tiles_h + th) * Q.tiles_w + tw] = tp;
+    tp.restore = s_restore[tw];
+    Q.tiles[(size_t)tile_row0 + tw] = tp;
   }
 }
 
@@ -487,6 +510,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         const bool tile_interior = P.nvar == 1 ? (th + 1) * kTileH <= P.H : (rows_interior && tw > 0 && tw < P.tiles_w - 1);
         for (int dout = 0; dout < P.Dout; ++dout) {
           const bool has_acc = (touched >> dout) & 1;  // else: no live box reached this accumulator
+          if (!has_acc && !((tp.restore >> dout) & 1)) continue;  // the block already holds the layer background
           if (!has_acc && P.out_mode == 0 && tile_interior && ctl->row_zero[dout]) {
             // nothing but background in reach and the layer stores deviations: the 16 KB block is zero.
             // This warp clears tile rows 4*quad + 2*half, +1 (1 KB each, contiguous).
@@ -787,6 +811,11 @@ size_t vn_conv3d_workspace_bytes(int32_t B, int32_t H, int32_t W) {
   return plan_layout((int64_t)B * ((H + kTileH - 1) / kTileH) * (W / kTileW)).total;
 }
 
+size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W) {
+  if (B < 1 || H < 1 || W < 1 || W % kTileW != 0) return 0;
+  return (size_t)B * ((H + kTileH - 1) / kTileH) * (W / kTileW);
+}
+
 size_t vn_conv3d_packed_weight_bytes(int32_t cin) {
   if (cin != 64 && cin != 128) return 0;
   return (size_t)27 * cin * 64 * 2;
@@ -859,7 +888,8 @@ int vn_conv3d_mark_boxes(const int64_t* coords, int64_t K, const int32_t* n_voxe
 int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
                           int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
                           int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
-                          int32_t flag_opts, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+                          int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
+                          vn_stream_t stream) {
   VN_REQUIRE(x && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
@@ -919,6 +949,7 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
   Q.box_flags = box_flags;
   Q.consume = (flag_opts & VN_CONV_FLAGS_CONSUME) ? 1 : 0;
   Q.force_ring = (flag_opts & VN_CONV_FLAGS_BORDER_RING) ? 1 : 0;
+  Q.out_state = out_state;
   Q.hdr = hdr; Q.groups = groups; Q.tiles = tiles;
   if (plan_planes(Q, stride_d, pad_d) != 0) {
     set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);

@@ -11,6 +11,8 @@
 // Rows that are bit-identical (the reference's pad rows) are passed once: max() ignores multiplicity.
 #pragma once
 
+#include <cuda_bf16.h>
+
 #include "vn_common.cuh"
 
 namespace vn {
@@ -47,11 +49,108 @@ __device__ __forceinline__ void load_vfe2_lane(Vfe2Lane& q, const float* w2, con
   q.ta = t2[lane];  q.tb = t2[lane + 32];
 }
 
+// VFE-2 + voxel-wise max for ONE voxel whose R masked input rows ([x1 | agg1], 32 floats each) sit in
+// shared memory at x.  Lane l owns units (l, l + 32).  on_bits: bit r set <=> row r has mask 1 (rows with
+// mask 0 are all-zero inputs; they count for the unmasked aggregate but contribute exactly 0 to the
+// voxel-wise max).  o[i] = voxelwise channel (lane + 32 i).
+__device__ __forceinline__ void vfe2_voxel_max(const float (*x)[32], int R, uint64_t on_bits, const Vfe2Lane& q,
+                                               float (&o)[4]) {
+  float all_a = -INFINITY, all_b = -INFINITY;  // max over all rows (the reference's `agg`)
+  float on_a = -INFINITY, on_b = -INFINITY;    // max over rows with mask 1 of the pointwise part
+  int r = 0;
+  // two rows per trip: four independent FMA chains (a single row's two chains of 32 dependent FMAs
+  // leave the pipe idle three cycles out of four)
+  for (; r + 1 < R; r += 2) {
+    float a0 = q.ba, b0 = q.bb, a1 = q.ba, b1 = q.bb;
+    const float4* x0 = reinterpret_cast<const float4*>(x[r]);
+    const float4* x1 = reinterpret_cast<const float4*>(x[r + 1]);
+#pragma unroll
+    for (int k4 = 0; k4 < 8; ++k4) {
+      const float4 v = x0[k4], w = x1[k4];
+      a0 = fmaf(q.wa[4 * k4 + 0], v.x, a0);  b0 = fmaf(q.wb[4 * k4 + 0], v.x, b0);
+      a1 = fmaf(q.wa[4 * k4 + 0], w.x, a1);  b1 = fmaf(q.wb[4 * k4 + 0], w.x, b1);
+      a0 = fmaf(q.wa[4 * k4 + 1], v.y, a0);  b0 = fmaf(q.wb[4 * k4 + 1], v.y, b0);
+      a1 = fmaf(q.wa[4 * k4 + 1], w.y, a1);  b1 = fmaf(q.wb[4 * k4 + 1], w.y, b1);
+      a0 = fmaf(q.wa[4 * k4 + 2], v.z, a0);  b0 = fmaf(q.wb[4 * k4 + 2], v.z, b0);
+      a1 = fmaf(q.wa[4 * k4 + 2], w.z, a1);  b1 = fmaf(q.wb[4 * k4 + 2], w.z, b1);
+      a0 = fmaf(q.wa[4 * k4 + 3], v.w, a0);  b0 = fmaf(q.wb[4 * k4 + 3], v.w, b0);
+      a1 = fmaf(q.wa[4 * k4 + 3], w.w, a1);  b1 = fmaf(q.wb[4 * k4 + 3], w.w, b1);
+    }
+    a0 = fmaf(fmaxf(a0, 0.0f), q.sa, q.ta);
+    b0 = fmaf(fmaxf(b0, 0.0f), q.sb, q.tb);
+    a1 = fmaf(fmaxf(a1, 0.0f), q.sa, q.ta);
+    b1 = fmaf(fmaxf(b1, 0.0f), q.sb, q.tb);
+    all_a = fmaxf(all_a, fmaxf(a0, a1));
+    all_b = fmaxf(all_b, fmaxf(b0, b1));
+    const bool m0 = (on_bits >> r) & 1, m1 = (on_bits >> (r + 1)) & 1;
+    on_a = fmaxf(on_a, fmaxf(m0 ? a0 : -INFINITY, m1 ? a1 : -INFINITY));
+    on_b = fmaxf(on_b, fmaxf(m0 ? b0 : -INFINITY, m1 ? b1 : -INFINITY));
+  }
+  if (r < R) {
+    float a = q.ba, b = q.bb;
+    const float4* xr = reinterpret_cast<const float4*>(x[r]);
+#pragma unroll
+    for (int k4 = 0; k4 < 8; ++k4) {
+      const float4 v = xr[k4];
+      a = fmaf(q.wa[4 * k4 + 0], v.x, a);
+      b = fmaf(q.wb[4 * k4 + 0], v.x, b);
+      a = fmaf(q.wa[4 * k4 + 1], v.y, a);
+      b = fmaf(q.wb[4 * k4 + 1], v.y, b);
+      a = fmaf(q.wa[4 * k4 + 2], v.z, a);
+      b = fmaf(q.wb[4 * k4 + 2], v.z, b);
+      a = fmaf(q.wa[4 * k4 + 3], v.w, a);
+      b = fmaf(q.wb[4 * k4 + 3], v.w, b);
+    }
+    a = fmaf(fmaxf(a, 0.0f), q.sa, q.ta);
+    b = fmaf(fmaxf(b, 0.0f), q.sb, q.tb);
+    all_a = fmaxf(all_a, a);
+    all_b = fmaxf(all_b, b);
+    if ((on_bits >> r) & 1) {
+      on_a = fmaxf(on_a, a);
+      on_b = fmaxf(on_b, b);
+    }
+  }
+  // voxelwise[c] = max_t(mask_t * out2[t][c]): rows with mask 0 contribute exactly 0
+  const uint64_t evaluated = R >= 64 ? ~0ull : ((1ull << R) - 1ull);
+  const bool any_on = (on_bits & evaluated) != 0;
+  const bool any_off = (on_bits & evaluated) != evaluated;
+  const float floor0 = any_off ? 0.0f : -INFINITY;
+  o[0] = fmaxf(any_on ? on_a : -INFINITY, floor0);
+  o[1] = fmaxf(any_on ? on_b : -INFINITY, floor0);
+  o[2] = fmaxf(any_on ? all_a : -INFINITY, floor0);
+  o[3] = fmaxf(any_on ? all_b : -INFINITY, floor0);
+}
+
+// One voxel's 128 maxima -> voxelwise row (f32, model.py:100) and / or its cell of the resident bf16
+// grid (model.py:102-106; the same round-to-nearest conversion as vn_scatter_dense_bf16).  Either
+// destination may be null.
+__device__ __forceinline__ void store_voxel_out(const float (&o)[4], uint32_t lane, float* vw_row, void* dense_row) {
+  if (vw_row != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) vw_row[lane + 32 * i] = o[i];
+  }
+  if (dense_row != nullptr) {  // warp-uniform
+    // lane l holds channels l + 32 i; pair neighbouring lanes so that every lane stores 2 x bf16x2:
+    // even lanes write groups 0 and 2, odd lanes groups 1 and 3
+    const bool odd = lane & 1;
+    uint32_t* dst = reinterpret_cast<uint32_t*>(dense_row);
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      const float mine = odd ? o[2 * h + 1] : o[2 * h];       // the value of the group this lane writes
+      const float give = odd ? o[2 * h] : o[2 * h + 1];       // the value the neighbour needs
+      const float got = __shfl_xor_sync(0xffffffffu, give, 1);
+      const __nv_bfloat162 v = odd ? __floats2bfloat162_rn(got, mine) : __floats2bfloat162_rn(mine, got);
+      const int group = 2 * h + (odd ? 1 : 0);
+      dst[(group * 32 + (int)(lane & ~1u)) >> 1] = *reinterpret_cast<const uint32_t*>(&v);
+    }
+  }
+}
+
 // rows: shared memory, 7 floats per row.  Evaluated row r (0 <= r < R) is source row
 // (r < nu ? r : tlast).  x1: shared scratch of (R + 1) x 32 floats; row `aggrow` holds agg1.
-// dst: 128 floats in global memory.
+// o: the voxel's 128 maxima, channel (lane + 32 i) in o[i].
 __device__ __forceinline__ void svfe_eval_voxel(const float* rows, int nu, int R, int tlast, float (*x1)[32], int aggrow,
-                                                const Vfe1Params& p1, const Vfe2Lane& q, float* dst, uint32_t lane) {
+                                                const Vfe1Params& p1, const Vfe2Lane& q, float (&o)[4], uint32_t lane) {
   // ---- mask bits: bit r set <=> evaluated row r has max_j != 0 --------------------------------
   uint64_t on_bits = 0;
   for (int r0 = 0; r0 < R; r0 += 32) {
@@ -73,7 +172,7 @@ __device__ __forceinline__ void svfe_eval_voxel(const float* rows, int nu, int R
     float a = p1.b[u];
 #pragma unroll
     for (int j = 0; j < 7; ++j) a = fmaf(p1.w[u * 7 + j], f[j], a);
-    x1[r][u] = fmaxf(a, 0.0f) * p1.s[u] + p1.t[u];
+    x1[r][u] = fmaf(fmaxf(a, 0.0f), p1.s[u], p1.t[u]);
   }
   __syncwarp();
   if (lane < 16) {  // agg1[u] = max over evaluated rows (== max over all T rows)
@@ -90,42 +189,7 @@ __device__ __forceinline__ void svfe_eval_voxel(const float* rows, int nu, int R
     x1[r][c] = on ? val : 0.0f;
   }
   __syncwarp();
-  // ---- VFE-2: lane <-> units (lane, lane + 32); rows broadcast from shared memory -----------------
-  float all_a = -INFINITY, all_b = -INFINITY;  // max over all rows (the reference's `agg`)
-  float on_a = -INFINITY, on_b = -INFINITY;    // max over rows with mask 1 of the pointwise part
-  for (int r = 0; r < R; ++r) {
-    float a = q.ba, b = q.bb;
-    const float4* xr = reinterpret_cast<const float4*>(x1[r]);
-#pragma unroll
-    for (int k4 = 0; k4 < 8; ++k4) {
-      const float4 x = xr[k4];
-      a = fmaf(q.wa[4 * k4 + 0], x.x, a);
-      b = fmaf(q.wb[4 * k4 + 0], x.x, b);
-      a = fmaf(q.wa[4 * k4 + 1], x.y, a);
-      b = fmaf(q.wb[4 * k4 + 1], x.y, b);
-      a = fmaf(q.wa[4 * k4 + 2], x.z, a);
-      b = fmaf(q.wb[4 * k4 + 2], x.z, b);
-      a = fmaf(q.wa[4 * k4 + 3], x.w, a);
-      b = fmaf(q.wb[4 * k4 + 3], x.w, b);
-    }
-    a = fmaxf(a, 0.0f) * q.sa + q.ta;
-    b = fmaxf(b, 0.0f) * q.sb + q.tb;
-    all_a = fmaxf(all_a, a);
-    all_b = fmaxf(all_b, b);
-    if ((on_bits >> r) & 1) {
-      on_a = fmaxf(on_a, a);
-      on_b = fmaxf(on_b, b);
-    }
-  }
-  // voxelwise[c] = max_t(mask_t * out2[t][c]): rows with mask 0 contribute exactly 0
-  const uint64_t evaluated = R >= 64 ? ~0ull : ((1ull << R) - 1ull);
-  const bool any_on = on_bits != 0;
-  const bool any_off = (on_bits & evaluated) != evaluated;
-  const float floor0 = any_off ? 0.0f : -INFINITY;
-  dst[lane] = fmaxf(any_on ? on_a : -INFINITY, floor0);
-  dst[lane + 32] = fmaxf(any_on ? on_b : -INFINITY, floor0);
-  dst[lane + 64] = fmaxf(any_on ? all_a : -INFINITY, floor0);
-  dst[lane + 96] = fmaxf(any_on ? all_b : -INFINITY, floor0);
+  vfe2_voxel_max(x1, R, on_bits, q, o);
 }
 
 }  // namespace vn

@@ -56,7 +56,9 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
       if (b) nu = t0 + 32 - __clz(b);
     }
     const int R = nu < T ? nu + 1 : T;  // rows to evaluate: 0..nu-1 and (if any) the tail row T-1
-    svfe_eval_voxel(in, nu, R, T - 1, x1, T, p1, q, voxelwise + v * 128, lane);
+    float o[4];
+    svfe_eval_voxel(in, nu, R, T - 1, x1, T, p1, q, o, lane);
+    store_voxel_out(o, lane, voxelwise + v * 128, nullptr);
     __syncwarp();
   }
 }

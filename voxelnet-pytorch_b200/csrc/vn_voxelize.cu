@@ -31,6 +31,7 @@ struct VoxWorkspace {
   uint32_t* wordprefix;  // [n_frames * words]   exclusive popcount prefix within the frame
   int32_t* frame_k;      // [n_frames]           voxels per frame
   int32_t* cnt;          // [n_points]           points per voxel row (uncapped)
+  int32_t* counters;     // [64]                 work counters of the persistent kernels (zeroed with the bitmap)
   int32_t* keyrow;       // [n_points]           P1: cell key; P4 onwards: voxel row (-1 = cropped)
   int32_t* arrival;      // [n_points]           arrival slot inside the voxel
   int32_t* seg;          // [n_points]           segment start of each voxel row in pidx
@@ -54,6 +55,7 @@ __host__ VoxWorkspace carve(const vn_grid_t& g, int n_frames, int64_t n_points, 
   };
   w.bitmap = reinterpret_cast<uint32_t*>(take((size_t)n_frames * w.words * 4));
   w.cnt = reinterpret_cast<int32_t*>(take(np * 4));
+  w.counters = reinterpret_cast<int32_t*>(take(64 * 4));
   w.zero_bytes = off;
   w.wordprefix = reinterpret_cast<uint32_t*>(take((size_t)n_frames * w.words * 4));
   w.frame_k = reinterpret_cast<int32_t*>(take((size_t)n_frames * 4));
@@ -211,10 +213,11 @@ __global__ void __launch_bounds__(256) k_vox_count(const int32_t* __restrict__ f
 __global__ void __launch_bounds__(1024) k_vox_segment_scan(const int32_t* __restrict__ frame_offsets,
                                                             const int32_t* __restrict__ voxel_offsets,
                                                             const int32_t* __restrict__ cnt,
-                                                            int32_t* __restrict__ seg) {
+                                                            int32_t* __restrict__ seg, int32_t* __restrict__ counters) {
   __shared__ uint32_t warp_total[32];
   __shared__ uint32_t carry;
   const int f = blockIdx.x;
+  if (f == 0 && threadIdx.x < 64) counters[threadIdx.x] = 0;  // work counters of the kernels that follow
   const int r0 = voxel_offsets[f], r1 = voxel_offsets[f + 1];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) carry = (uint32_t)frame_offsets[f];
@@ -262,8 +265,11 @@ __device__ __forceinline__ float f4_comp(const float4& v, int j) {
 // ---- per-voxel point selection, shared by P7 and the fused voxel->SVFE kernel -----------------
 // Loads the voxel's bucket, orders it by original point index and leaves the first m = min(n, T)
 // points in pts[0..m) (shared memory, one float4 per slot).  Returns m.
+// scratch (optional): shared memory for scratch_cap ints; lets a voxel with 32 < n <= scratch_cap points be
+// ordered by rank counting instead of m passes over its bucket.
 __device__ __forceinline__ int warp_select_points(const float4* __restrict__ points, const int32_t* __restrict__ pidx,
-                                                  int n, int s0, int T, float4* pts, uint32_t lane) {
+                                                  int n, int s0, int T, float4* pts, uint32_t lane,
+                                                  int* scratch = nullptr, int scratch_cap = 0) {
   const int m = n < T ? n : T;
   if (n <= 32) {
     // rank of every index among the voxel's indices == its slot
@@ -271,6 +277,15 @@ __device__ __forceinline__ int warp_select_points(const float4* __restrict__ poi
     int rank = 0;
     for (int j = 0; j < n; ++j) rank += (__shfl_sync(0xffffffffu, idx, j) < idx) ? 1 : 0;
     if ((int)lane < n && rank < m) pts[rank] = points[idx];
+  } else if (n <= scratch_cap) {
+    for (int j = lane; j < n; j += 32) scratch[j] = pidx[s0 + j];
+    __syncwarp();
+    for (int e = lane; e < n; e += 32) {
+      const int idx = scratch[e];
+      int rank = 0;
+      for (int j = 0; j < n; ++j) rank += scratch[j] < idx ? 1 : 0;
+      if (rank < m) pts[rank] = points[idx];
+    }
   } else {
     // rare: more than a warp's worth of points.  Select the m smallest indices in ascending
     // order by repeated min-above-threshold over the segment.
@@ -319,9 +334,10 @@ __device__ __forceinline__ float feature_value(const float4* pts, int m, int t, 
   return __double2float_rn((double)b - c);  // float64 subtraction, rounded on store
 }
 
-__device__ __forceinline__ void write_coords(const vn_grid_t& g, const float4& p0, int n_frames,
-                                             const int32_t* __restrict__ voxel_offsets, int64_t row,
-                                             long long* __restrict__ coords) {
+// Returns the voxel's cell index ((b*D + z)*H + y)*W + x in the batched dense grid.
+__device__ __forceinline__ int64_t write_coords(const vn_grid_t& g, const float4& p0, int n_frames,
+                                                const int32_t* __restrict__ voxel_offsets, int64_t row,
+                                                long long* __restrict__ coords) {
   int z, y, x;
   point_cell(p0, g, z, y, x);
   int lo = 0, hi = n_frames;  // frame of this row: last f with voxel_offsets[f] <= row
@@ -329,11 +345,10 @@ __device__ __forceinline__ void write_coords(const vn_grid_t& g, const float4& p
     const int mid = (lo + hi) >> 1;
     if ((int64_t)voxel_offsets[mid] <= row) lo = mid; else hi = mid;
   }
-  long long* c = coords + row * 4;
-  c[0] = lo;
-  c[1] = z;
-  c[2] = y;
-  c[3] = x;
+  longlong2* c = reinterpret_cast<longlong2*>(coords + row * 4);
+  c[0] = make_longlong2(lo, z);
+  c[1] = make_longlong2(y, x);
+  return (((int64_t)lo * g.D + z) * g.H + y) * g.W + x;
 }
 
 // P7: one warp per voxel row -> materialised [T,7] feature rows (the reference's voxel dict).
@@ -367,53 +382,269 @@ __global__ void __launch_bounds__(kFeatWarps * 32) k_vox_features(
   }
 }
 
-// Fused P7 + stacked VFE: one warp per voxel builds the voxel's DISTINCT feature rows (its m real
-// points plus one representative pad row when m < T) in shared memory and evaluates VFE-1, VFE-2 and
-// the voxel-wise max on them - the [K,T,7] feature buffer is never written or read.  Bit-identical
-// to k_vox_features followed by k_svfe_fused (same row values, same instruction sequence).
-__global__ void __launch_bounds__(kFeatWarps * 32, 2) k_vox_svfe_fused(
+// ---------------------------------------------------------------------------------------------
+// Fused P7 + stacked VFE, packed: the [K,T,7] feature buffer is never written or read, and a warp
+// works on the rows of SEVERAL voxels at once (KITTI voxels hold 4.4 points on average, one voxel
+// per warp leaves most lanes idle outside the VFE-2 loop).
+//
+// A warp owns 32 consecutive voxel rows (lane <-> voxel for counts, segment starts, coordinates) and
+// cuts them into batches of whole voxels with <= 32 DISTINCT feature rows in total (a voxel with m <
+// T points has m real rows plus one representative of its T - m identical pad rows: max() ignores
+// multiplicity).  Inside a batch lane <-> row: bucket load, first-T order (rank of the
+// point index among the voxel's indices), 7-d features with the fp64 centroid arithmetic, mask, VFE-1.
+// agg1 is a (voxel, unit)-parallel pass over shared memory; VFE-2 runs voxel by voxel with lane <->
+// two output units and the rows broadcast from shared memory.  Voxels with more than 31 points (or
+// more than T) take the one-voxel-per-warp path (warp_select_points / svfe_eval_voxel).
+// Bit-identical to k_vox_features followed by k_svfe_fused (same values through the same operations).
+// ---------------------------------------------------------------------------------------------
+constexpr int kPackWarps = 8;
+constexpr int kPackRange = 8;   // voxels per work item (small: ~6 k voxels per frame over 2,368 resident warps)
+
+struct Vfe1Packed {   // VFE-1 parameters laid out for 128-bit broadcast loads
+  float4 wlo[16];     // w[u][0..3]
+  float4 whi[16];     // w[u][4..6], bias
+  float s[16], t[16];
+};
+
+struct PackWarp {
+  float x[32][32];      // batch rows: VFE-1 output | agg1, masked = VFE-2 input
+  float4 pts[32];       // the batch's points in slot order (row r of a voxel = its r-th point)
+  double mean[32][3];   // per batch voxel: centroid (utils.py:87-88)
+  float agg[32][16];    // per batch voxel: agg1
+  int rv[32];           // row -> owning voxel (lane of the 32-voxel range), start markers
+  uint8_t first[32], nrows[32], npts[32];  // per batch voxel
+};
+
+__device__ __forceinline__ size_t pack_warp_bytes(int T) {
+  const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
+  const size_t slow = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128;
+  const size_t fast = sizeof(PackWarp);
+  return ((slow > fast ? slow : fast) + 15) & ~(size_t)15;
+}
+
+__global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
     const vn_grid_t g, const float4* __restrict__ points, int n_frames,
     const int32_t* __restrict__ voxel_offsets, int64_t max_voxels, const int32_t* __restrict__ cnt,
     const int32_t* __restrict__ seg, const int32_t* __restrict__ pidx, const float* __restrict__ w1,
     const float* __restrict__ b1, const float* __restrict__ s1, const float* __restrict__ t1,
     const float* __restrict__ w2, const float* __restrict__ b2, const float* __restrict__ s2,
-    const float* __restrict__ t2, float* __restrict__ voxelwise, long long* __restrict__ coords,
-    long long* __restrict__ counts) {
-  // dynamic smem per warp: float4 pts[T] | float rows[(T+1)*7 padded] | float x1[T+1][32]
+    const float* __restrict__ t2, float* __restrict__ voxelwise, __nv_bfloat16* __restrict__ dense,
+    long long* __restrict__ coords, long long* __restrict__ counts, int32_t* __restrict__ work_counter) {
   extern __shared__ __align__(16) uint8_t dyn_smem[];
-  __shared__ Vfe1Params p1;
+  __shared__ Vfe1Params p1;   // one-voxel path
+  __shared__ Vfe1Packed pk;   // packed path
   const int T = g.T;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
-  const size_t per_warp = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128;
-  uint8_t* base = dyn_smem + warp * per_warp;
-  float4* pts = reinterpret_cast<float4*>(base);
-  float* rows = reinterpret_cast<float*>(base + (size_t)T * 16);
-  float(*x1)[32] = reinterpret_cast<float(*)[32]>(base + (size_t)T * 16 + rows_bytes);
+  uint8_t* wbase = dyn_smem + warp * pack_warp_bytes(T);
+  PackWarp& W = *reinterpret_cast<PackWarp*>(wbase);
   load_vfe1_params(p1, w1, b1, s1, t1);
+  if (threadIdx.x < 16) {
+    const int u = threadIdx.x;
+    pk.wlo[u] = make_float4(w1[u * 7 + 0], w1[u * 7 + 1], w1[u * 7 + 2], w1[u * 7 + 3]);
+    pk.whi[u] = make_float4(w1[u * 7 + 4], w1[u * 7 + 5], w1[u * 7 + 6], b1[u]);
+    pk.s[u] = s1[u];
+    pk.t[u] = t1[u];
+  }
   Vfe2Lane q;
   load_vfe2_lane(q, w2, b2, s2, t2, lane);
   __syncthreads();
 
   int64_t total = voxel_offsets[n_frames];
   if (total > max_voxels) total = max_voxels;
-  const int64_t nwarps = (int64_t)gridDim.x * kFeatWarps;
-  for (int64_t row = (int64_t)blockIdx.x * kFeatWarps + warp; row < total; row += nwarps) {
-    const int m = warp_select_points(points, pidx, cnt[row], seg[row], T, pts, lane);
-    double mx, my, mz;
-    warp_centroid(pts, m, T, lane, mx, my, mz);
-    const int R = m < T ? m + 1 : T;  // real rows 0..m-1, then one pad row at index m
-    for (int e = lane; e < R * 7; e += 32) {
-      const int t = e / 7, j = e - t * 7;
-      rows[e] = feature_value(pts, m, t, j, mx, my, mz);
+  const int64_t nranges = (total + kPackRange - 1) / kPackRange;
+  // work items are pulled from a counter (voxels near the sensor hold many more points than far ones);
+  // the next item is requested before the current one is processed
+  int nxt = 0;
+  if (lane == 0) nxt = atomicAdd(work_counter, 1);
+  for (;;) {
+    const int64_t rg = __shfl_sync(0xffffffffu, nxt, 0);
+    if (rg >= nranges) break;
+    if (lane == 0) nxt = atomicAdd(work_counter, 1);
+    // ---- lane <-> voxel: counts, bucket start, coordinates ----------------------------------------
+    const int64_t row = rg * kPackRange + lane;
+    const bool valid = (int)lane < kPackRange && row < total;
+    int c = 0, s0 = 0;
+    int64_t cell = 0;
+    if (valid) {
+      c = cnt[row];
+      s0 = seg[row];
+      cell = write_coords(g, points[pidx[s0]], n_frames, voxel_offsets, row, coords);
+      if (counts != nullptr) counts[row] = c < T ? c : T;
     }
-    __syncwarp();
-    svfe_eval_voxel(rows, m, R, m, x1, T, p1, q, voxelwise + row * 128, lane);
-    if (lane == 0) {
-      write_coords(g, pts[0], n_frames, voxel_offsets, row, coords);
-      if (counts != nullptr) counts[row] = m;
+    const bool big = valid && (c > 31 || c > T);
+    const int R = (valid && !big) ? c + (c < T ? 1 : 0) : 0;  // distinct rows of this voxel (<= 32)
+    const int incl = (int)warp_incl_scan((uint32_t)R, lane);
+    const int excl = incl - R;
+    const int Rall = __shfl_sync(0xffffffffu, incl, 31);
+    int base = 0, a = 0;
+    while (base < Rall) {
+      // ---- batch = voxels [a, b_end): as many whole voxels as fit 32 rows -------------------------
+      const int b_end = __popc(__ballot_sync(0xffffffffu, incl - base <= 32));
+      const int Rtot = __shfl_sync(0xffffffffu, incl, b_end - 1) - base;
+      const int nvox = b_end - a;
+      W.rv[lane] = -1;
+      __syncwarp();
+      const bool owner = (int)lane >= a && (int)lane < b_end;
+      if (owner) {
+        if (R > 0) W.rv[excl - base] = (int)lane;
+        W.first[lane - a] = (uint8_t)(excl - base);
+        W.nrows[lane - a] = (uint8_t)R;
+        W.npts[lane - a] = (uint8_t)c;
+      }
+      __syncwarp();
+      // ---- lane <-> row --------------------------------------------------------------------------
+      int w = W.rv[lane];
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {  // owners are ascending: inclusive max-scan fills the gaps
+        const int t = __shfl_up_sync(0xffffffffu, w, d);
+        if ((int)lane >= d) w = max(w, t);
+      }
+      const bool rowvalid = (int)lane < Rtot;
+      const int wsrc = rowvalid ? w : 0;
+      const int c_w = __shfl_sync(0xffffffffu, c, wsrc);
+      const int s_w = __shfl_sync(0xffffffffu, s0, wsrc);
+      const int first_w = __shfl_sync(0xffffffffu, excl, wsrc) - base;
+      const int j = (int)lane - first_w;          // row index inside the voxel; j == c_w is the pad row
+      const bool real = rowvalid && j < c_w;
+      int idx = 0x7fffffff;
+      float4 p = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+      if (real) {
+        idx = pidx[s_w + j];
+        p = points[idx];
+      }
+      // first-T rule (utils.py:78-84): slot = rank of the point index among the voxel's indices
+      const int maxc = __reduce_max_sync(0xffffffffu, real ? c_w : 0);
+      int rank = 0;
+      for (int jj = 0; jj < maxc; ++jj) {
+        const int o = __shfl_sync(0xffffffffu, idx, (first_w + jj) & 31);
+        rank += (jj < c_w && o < idx) ? 1 : 0;
+      }
+      if (real) W.pts[first_w + rank] = p;
+      __syncwarp();
+      // centroid (utils.py:87-88): fp32 sum in slot order incl. the +0.0 of the first pad, fp64 divide
+      for (int e0 = 0; e0 < nvox * 3; e0 += 32) {
+        const int e = e0 + (int)lane;
+        if (e < nvox * 3) {
+          const int k = e / 3, comp = e - 3 * k;
+          const int n = W.npts[k];
+          if (W.nrows[k] != 0) {
+            const float* src = reinterpret_cast<const float*>(&W.pts[W.first[k]]) + comp;
+            float sum = src[0];
+            for (int t = 1; t < n; ++t) sum = __fadd_rn(sum, src[4 * t]);
+            if (n < T) sum = __fadd_rn(sum, 0.0f);
+            W.mean[k][comp] = (double)sum / (double)n;
+          }
+        }
+      }
+      __syncwarp();
+      // 7-d features of my row (utils.py:71, 87-88), mask (model.py:95-96), VFE-1 (model.py:74-76)
+      bool on = false;
+      if (rowvalid) {
+        const int k = w - a;
+        const float4 pt = real ? W.pts[lane] : make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        float f[7];
+        f[0] = pt.x; f[1] = pt.y; f[2] = pt.z; f[3] = pt.w;
+        f[4] = __double2float_rn((double)pt.x - W.mean[k][0]);
+        f[5] = __double2float_rn((double)pt.y - W.mean[k][1]);
+        f[6] = __double2float_rn((double)pt.z - W.mean[k][2]);
+        float mx = f[0];
+#pragma unroll
+        for (int i = 1; i < 7; ++i) mx = fmaxf(mx, f[i]);
+        on = mx != 0.0f;
+        float4* xrow = reinterpret_cast<float4*>(W.x[lane]);
+#pragma unroll
+        for (int u4 = 0; u4 < 4; ++u4) {
+          float v[4];
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int u = u4 * 4 + i;
+            const float4 lo = pk.wlo[u], hi = pk.whi[u];
+            float acc = hi.w;
+            acc = fmaf(lo.x, f[0], acc);
+            acc = fmaf(lo.y, f[1], acc);
+            acc = fmaf(lo.z, f[2], acc);
+            acc = fmaf(lo.w, f[3], acc);
+            acc = fmaf(hi.x, f[4], acc);
+            acc = fmaf(hi.y, f[5], acc);
+            acc = fmaf(hi.z, f[6], acc);
+            v[i] = fmaf(fmaxf(acc, 0.0f), pk.s[u], pk.t[u]);
+          }
+          xrow[u4] = make_float4(v[0], v[1], v[2], v[3]);
+        }
+      }
+      const uint32_t on_bits = __ballot_sync(0xffffffffu, on);
+      __syncwarp();
+      // agg1[k][u] = max over the voxel's rows (all T rows of the reference: pads are represented)
+      for (int e = lane; e < nvox * 16; e += 32) {
+        const int k = e >> 4, u = e & 15;
+        const int n = W.nrows[k];
+        if (n != 0) {
+          const int f0 = W.first[k];
+          float m = W.x[f0][u];
+          for (int t = 1; t < n; ++t) m = fmaxf(m, W.x[f0 + t][u]);
+          W.agg[k][u] = m;
+        }
+      }
+      __syncwarp();
+      // concat + mask (model.py:78-82): rows with mask 0 become all-zero inputs of VFE-2
+      if (rowvalid) {
+        float4* xrow = reinterpret_cast<float4*>(W.x[lane]);
+        const float4* ag = reinterpret_cast<const float4*>(W.agg[w - a]);
+        const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          if (!on) xrow[i] = z4;
+          xrow[4 + i] = on ? ag[i] : z4;
+        }
+      }
+      __syncwarp();
+      // ---- VFE-2 + voxel-wise max, voxel by voxel (lane <-> output units) -----------------------------
+      for (int k = 0; k < nvox; ++k) {
+        const int n = W.nrows[k];
+        const int64_t cell_k = __shfl_sync(0xffffffffu, cell, a + k);
+        if (n == 0) continue;
+        const int f0 = W.first[k];
+        const uint32_t bits = (on_bits >> f0) & (n >= 32 ? 0xffffffffu : ((1u << n) - 1u));
+        float o[4];
+        vfe2_voxel_max(&W.x[f0], n, (uint64_t)bits, q, o);
+        const int64_t vrow = rg * kPackRange + a + k;
+        store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
+                        dense != nullptr ? dense + cell_k * 128 : nullptr);
+      }
+      __syncwarp();
+      base += Rtot;
+      a = b_end;
     }
-    __syncwarp();
+    // ---- the rare voxels with > 31 (or > T) points: one voxel per warp -------------------------------
+    uint32_t bigs = __ballot_sync(0xffffffffu, big);
+    while (bigs) {
+      const int v = __ffs(bigs) - 1;
+      bigs &= bigs - 1;
+      const int c_v = __shfl_sync(0xffffffffu, c, v), s_v = __shfl_sync(0xffffffffu, s0, v);
+      const int64_t cell_v = __shfl_sync(0xffffffffu, cell, v);
+      const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
+      float4* pts = reinterpret_cast<float4*>(wbase);
+      float* rows = reinterpret_cast<float*>(wbase + (size_t)T * 16);
+      float(*x1)[32] = reinterpret_cast<float(*)[32]>(wbase + (size_t)T * 16 + rows_bytes);
+      const int m = warp_select_points(points, pidx, c_v, s_v, T, pts, lane, reinterpret_cast<int*>(rows),
+                                       (int)((pack_warp_bytes(T) - (size_t)T * 16) / 4));
+      __syncwarp();
+      double mx, my, mz;
+      warp_centroid(pts, m, T, lane, mx, my, mz);
+      __syncwarp();
+      const int Rv = m < T ? m + 1 : T;  // real rows 0..m-1, then one pad row at index m
+      for (int e = lane; e < Rv * 7; e += 32) {
+        const int t = e / 7, jx = e - t * 7;
+        rows[e] = feature_value(pts, m, t, jx, mx, my, mz);
+      }
+      __syncwarp();
+      float o[4];
+      svfe_eval_voxel(rows, m, Rv, m, x1, T, p1, q, o, lane);
+      const int64_t vrow = rg * kPackRange + v;
+      store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
+                      dense != nullptr ? dense + cell_v * 128 : nullptr);
+      __syncwarp();
+    }
   }
 }
 
@@ -441,7 +672,7 @@ int check_common(const vn_grid_t* grid, const void* points, const int32_t* frame
 // P5 + P6: CSR segments per voxel and the bucketed point indices.
 int launch_bucket(const VoxWorkspace& w, const int32_t* frame_offsets, int n_frames, int64_t n_points_total,
                   const int32_t* voxel_offsets, cudaStream_t st) {
-  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg);
+  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg, w.counters);
   VN_LAUNCH_CHECK("k_vox_segment_scan");
   const int64_t want = (n_points_total + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 16;
@@ -530,30 +761,35 @@ int vn_voxelize_fill(const vn_grid_t* grid, const float* points, const int32_t* 
 int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
                            int64_t n_points_total, const int32_t* voxel_offsets, int64_t max_voxels, const float* w1,
                            const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
-                           const float* s2, const float* t2, float* voxelwise, int64_t* coordinate_buffer,
-                           int64_t* number_buffer, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+                           const float* s2, const float* t2, float* voxelwise, void* dense_bf16,
+                           int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace, size_t workspace_bytes,
+                           vn_stream_t stream) {
   int rc = check_common(grid, points, frame_offsets, n_frames, n_points_total, workspace, workspace_bytes);
   if (rc != VN_OK) return rc;
   VN_REQUIRE(voxel_offsets != nullptr, "voxelize_svfe_fused: voxel_offsets is null");
   VN_REQUIRE(max_voxels >= 0, "voxelize_svfe_fused: max_voxels < 0");
   if (max_voxels == 0 || n_points_total == 0) return VN_OK;
   VN_REQUIRE(w1 && b1 && s1 && t1 && w2 && b2 && s2 && t2, "voxelize_svfe_fused: null parameter pointer");
-  VN_REQUIRE(voxelwise && coordinate_buffer, "voxelize_svfe_fused: null output");
+  VN_REQUIRE((voxelwise || dense_bf16) && coordinate_buffer, "voxelize_svfe_fused: null output");
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(dense_bf16) & 3) == 0 && (reinterpret_cast<uintptr_t>(coordinate_buffer) & 15) == 0,
+             "voxelize_svfe_fused: misaligned output");
   cudaStream_t st = as_stream(stream);
   const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
   rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, st);
   if (rc != VN_OK) return rc;
   const int T = grid->T;
   const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
-  const size_t smem = kFeatWarps * ((size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128);
-  VN_CUDA(cudaFuncSetAttribute(k_vox_svfe_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  const int64_t want = (max_voxels + kFeatWarps - 1) / kFeatWarps;
+  const size_t slow = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128;
+  const size_t per_warp = ((slow > sizeof(PackWarp) ? slow : sizeof(PackWarp)) + 15) & ~(size_t)15;
+  const size_t smem = kPackWarps * per_warp;
+  VN_CUDA(cudaFuncSetAttribute(k_vox_svfe_packed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const int64_t want = (max_voxels + kPackRange * kPackWarps - 1) / (kPackRange * kPackWarps);
   const int64_t cap = (int64_t)sm_count() * 2;
-  k_vox_svfe_fused<<<(unsigned)(want < cap ? want : cap), kFeatWarps * 32, smem, st>>>(
+  k_vox_svfe_packed<<<(unsigned)(want < cap ? want : cap), kPackWarps * 32, smem, st>>>(
       *grid, reinterpret_cast<const float4*>(points), n_frames, voxel_offsets, max_voxels, w.cnt, w.seg, w.pidx, w1, b1,
-      s1, t1, w2, b2, s2, t2, voxelwise, reinterpret_cast<long long*>(coordinate_buffer),
-      reinterpret_cast<long long*>(number_buffer));
-  VN_LAUNCH_CHECK("k_vox_svfe_fused");
+      s1, t1, w2, b2, s2, t2, voxelwise, reinterpret_cast<__nv_bfloat16*>(dense_bf16),
+      reinterpret_cast<long long*>(coordinate_buffer), reinterpret_cast<long long*>(number_buffer), w.counters);
+  VN_LAUNCH_CHECK("k_vox_svfe_packed");
   return VN_OK;
 }
 

@@ -140,18 +140,30 @@ def svfe_fused_fwd(feature, p1, p2, out=None, n_voxels_dev=None) -> torch.Tensor
     return out
 
 
-def voxelize_svfe_fused(grid, points, frame_offsets, voxel_offsets, p1, p2, voxelwise, coords, counts, workspace) -> None:
-    """Voxelizer phase 2 fused with the stacked VFE: writes voxelwise (cap,128) f32 and coords
-    (cap,4) i64 (counts optional) without materialising the (K,T,7) feature buffer."""
-    _require_cuda(points, frame_offsets, voxel_offsets, voxelwise, coords, counts, workspace, *p1, *p2)
-    _contig(voxelwise, torch.float32), _contig(coords, torch.int64)
+def voxelize_svfe_fused(grid, points, frame_offsets, voxel_offsets, p1, p2, voxelwise, coords, counts, workspace,
+                        dense=None) -> None:
+    """Voxelizer phase 2 fused with the stacked VFE: writes coords (cap,4) i64 (counts optional) and the
+    voxel-wise maxima - as voxelwise (cap,128) f32 and/or straight into the resident bf16 grid
+    `dense` (B,D,H,W,128) - without materialising the (K,T,7) feature buffer."""
+    _require_cuda(points, frame_offsets, voxel_offsets, voxelwise, coords, counts, workspace, dense, *p1, *p2)
+    _contig(coords, torch.int64)
+    if voxelwise is None and dense is None:
+        raise RuntimeError("voxelize_svfe_fused needs voxelwise and/or dense")
+    if voxelwise is not None:
+        _contig(voxelwise, torch.float32)
+        if voxelwise.shape[0] != coords.shape[0]:
+            raise RuntimeError("voxelwise and coords capacities differ")
     n_frames = frame_offsets.numel() - 1
+    if dense is not None:
+        _contig(dense, torch.bfloat16)
+        if tuple(dense.shape) != (n_frames, grid.D, grid.H, grid.W, 128):
+            raise RuntimeError("dense must be (B,D,H,W,128) bf16 for this grid; got %s" % (tuple(dense.shape),))
     with torch.cuda.device(points.device):
         check(
             _cabi.lib().vn_voxelize_svfe_fused(
                 C.byref(grid), _ptr(points), _ptr(frame_offsets), n_frames, points.shape[0], _ptr(voxel_offsets),
-                voxelwise.shape[0], *[_ptr(_contig(t, torch.float32)) for t in p1],
-                *[_ptr(_contig(t, torch.float32)) for t in p2], _ptr(voxelwise), _ptr(coords), _ptr(counts),
+                coords.shape[0], *[_ptr(_contig(t, torch.float32)) for t in p1],
+                *[_ptr(_contig(t, torch.float32)) for t in p2], _ptr(voxelwise), _ptr(dense), _ptr(coords), _ptr(counts),
                 _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
             ),
             "vn_voxelize_svfe_fused",
@@ -233,6 +245,12 @@ def conv3d_new_box_flags(B: int, Din: int, H: int, W: int, device) -> torch.Tens
     return torch.zeros(conv3d_box_flags_bytes(B, Din, H, W), dtype=torch.uint8, device=device)
 
 
+def conv3d_new_out_state(B: int, H: int, W: int, device) -> torch.Tensor:
+    """State table of a resident conv output buffer (see `out_state` in the header), all blocks stale."""
+    n = int(_cabi.lib().vn_conv3d_out_state_bytes(B, H, W))
+    return torch.full((n,), 0xFF, dtype=torch.uint8, device=device)
+
+
 def conv3d_mark_boxes(coords, B: int, D: int, H: int, W: int, layers, flags, n_voxels_dev=None) -> None:
     """Flag the live input boxes of a chain of stacked middle layers from voxel coordinates (K,4) i64.
     layers: [(stride_d, pad_d), ...] (<= 3), flags: one uint8 table per layer (conv3d_new_box_flags)."""
@@ -279,14 +297,22 @@ def conv3d_fold_background(weight, din: int, stride_d: int, pad_d: int, scale, s
 
 
 def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int, final: bool = False, out=None,
-                       box_flags=None, consume_flags: bool = False, border_ring: bool = False, sub=None, workspace=None):
+                       box_flags=None, consume_flags: bool = False, border_ring: bool = False, sub=None, workspace=None,
+                       out_state=None):
     """x (B,Din,H,W,cin) bf16 NDHWC -> (B,Dout,H,W,64) bf16, or with final=True the reference's
     reshaped (B, 64*Dout, H, W) f32 (model.py:262).
 
     shift: (64,) plain BatchNorm shift, (Dout,64), or the (3,3,Dout,64) table of conv3d_fold_background.
     sub: optional (Dout,64) background subtracted after the ReLU.  box_flags: optional live-box table
-    (conv3d_mark_boxes); consume_flags resets it, border_ring forces boxes on the H/W border live."""
-    _require_cuda(x, packed_weight, scale, shift, box_flags, sub, workspace)
+    (conv3d_mark_boxes); consume_flags resets it, border_ring forces boxes on the H/W border live.
+    out_state: optional state table (conv3d_new_out_state) that makes `out` a resident buffer - only
+    blocks fed now or by the previous call are written."""
+    _require_cuda(x, packed_weight, scale, shift, box_flags, sub, workspace, out_state)
+    if out_state is not None:
+        if out is None:
+            raise RuntimeError("out_state needs the resident `out` buffer it describes")
+        if out_state.dtype != torch.uint8 or out_state.numel() != int(_cabi.lib().vn_conv3d_out_state_bytes(x.shape[0], x.shape[2], x.shape[3])):
+            raise RuntimeError("out_state must be a uint8 tensor of vn_conv3d_out_state_bytes(B, H, W) elements")
     _contig(x, torch.bfloat16)
     B, Din, H, W, cin = x.shape
     if box_flags is not None and (box_flags.dtype != torch.uint8 or box_flags.numel() != conv3d_box_flags_bytes(B, Din, H, W)):
@@ -316,7 +342,7 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
             _cabi.lib().vn_conv3d_bn_relu_fwd(
                 _ptr(x), B, Din, H, W, cin, stride_d, pad_d, _ptr(packed_weight), _ptr(_contig(scale, torch.float32)),
                 _ptr(shift), n_variants, _ptr(sub), 1 if final else 0, _ptr(out), _ptr(box_flags), opts,
-                _ptr(workspace), workspace.numel(), _stream(),
+                _ptr(out_state), _ptr(workspace), workspace.numel(), _stream(),
             ),
             "vn_conv3d_bn_relu_fwd",
         )
@@ -351,10 +377,12 @@ def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, str
     nchunk = cin // 64
     boxes = 0
     flops = 0
+    live_planes = 0
     for p in range(Din):
         cnt = 0
         for kw in range(3):
             cnt += int(((live >> (p * 3 + kw)) & 1).sum())
+        live_planes += int((((live >> (p * 3)) & 7) != 0).sum())
         boxes += cnt
         flops += cnt * nchunk * 12 * 2 * 128 * 64 * nkd[p] * 16
     popc = np.zeros(n_tiles, dtype=np.int64)
@@ -367,4 +395,5 @@ def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, str
         "live_boxes": int(boxes), "boxes_total": int(n_tiles * sum(1 for n in nkd if n) * 3),
         "touched_blocks": int(popc.sum()), "restored_blocks": int(rpop.sum()), "blocks_total": int(n_tiles * Dout),
         "executed_flops": int(flops), "a_bytes": int(boxes * nchunk * 18432),
+        "live_tile_planes": live_planes, "unique_input_bytes": int(live_planes * 128 * cin * 2),
     }

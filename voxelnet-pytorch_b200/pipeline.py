@@ -66,7 +66,7 @@ _NO_SPAN = _NoSpan()
 class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
                  voxels_per_frame_capacity: int = 32768, fuse_voxel_features: bool = True,
-                 skip_empty_boxes: bool = True):
+                 skip_empty_boxes: bool = True, resident_outputs: bool = True):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
         self.cfg = grid_config(target)
@@ -80,6 +80,11 @@ class VoxelNetFrontEnd:
         # constant the previous layer outputs over empty space, which are zero wherever no voxel is in
         # reach (vn_conv3d_fold_background / vn_conv3d_mark_boxes).  False: dense, plain activations.
         self.skip_empty_boxes = bool(skip_empty_boxes)
+        # True (needs skip_empty_boxes): the two intermediate activations and the returned tensor are
+        # resident buffers with a per-block state table; a step stores only the 16x8 output blocks a
+        # voxel can reach now or could reach in the previous step (those are rewritten with the layer's
+        # background constant).  Everything else already holds that constant - bit-identical result.
+        self.resident_outputs = bool(resident_outputs) and self.skip_empty_boxes
         self._shape = None
         self._layer_geometry = [(l.stride[0], l.padding[0]) for l in middle_net.middle_layer]
         self.refresh_parameters()
@@ -101,6 +106,9 @@ class VoxelNetFrontEnd:
                 self._tables.append(table)
                 self._bg.append(bg_out)
                 din, bg = bg_out.shape[0], bg_out
+        if getattr(self, "out_states", None) is not None:
+            for st in self.out_states:  # the constants the untouched blocks hold depend on the parameters
+                st.fill_(0xFF)
 
     def _ensure_buffers(self, n_frames: int, n_points: int, device) -> None:
         shape = (n_frames, n_points, str(device))
@@ -121,13 +129,15 @@ class VoxelNetFrontEnd:
             torch.zeros(n_frames + 1, dtype=torch.int32, device=device),
             n_frames,
         )
-        self.voxelwise = torch.empty((cap, 128), dtype=torch.float32, device=device)
+        self.voxelwise = torch.empty((0 if self.fuse_voxel_features else cap, 128), dtype=torch.float32, device=device)
         self.dense = torch.empty((B, D, H, W, 128), dtype=torch.bfloat16, device=device)
         ops.fill_zero(self.dense)  # paid once: the step re-zeroes only the rows it wrote
         # live-box tables of the three layers: set by mark_boxes from the voxel coordinates, reset by
         # the layer that consumes them
         self.box_flags = [ops.conv3d_new_box_flags(B, d, H, W, device) for d in (D, d1, d2)] if self.skip_empty_boxes else None
-        self.conv_workspace = torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=device)
+        # one plan per layer (kept after the step so that diagnostics can decode what was executed)
+        self.conv_workspaces = [torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=device) for _ in range(3)]
+        self.out_states = [ops.conv3d_new_out_state(B, H, W, device) for _ in range(3)] if self.resident_outputs else None
         self.act1 = torch.empty((B, d1, H, W, 64), dtype=torch.bfloat16, device=device)
         self.act2 = torch.empty((B, d2, H, W, 64), dtype=torch.bfloat16, device=device)
         self.out = torch.empty((B, 64 * d3, H, W), dtype=torch.float32, device=device)
@@ -137,7 +147,8 @@ class VoxelNetFrontEnd:
     def forward_points(self, points: torch.Tensor, frame_offsets: torch.Tensor, max_points_per_frame: int,
                        timer: StageTimer = None) -> torch.Tensor:
         """points (N,4) f32 cuda (frames concatenated), frame_offsets (B+1,) i32 cuda ->
-        (B,128,H,W) f32.  The returned tensor is an internal buffer reused by the next call."""
+        (B,128,H,W) f32.  The returned tensor is an internal buffer reused by the next call; with
+        resident_outputs it must not be modified by the caller (blocks no voxel reaches are not rewritten)."""
         n_frames = frame_offsets.numel() - 1
         self._ensure_buffers(n_frames, points.shape[0], points.device)
         vb = self.voxels
@@ -146,9 +157,9 @@ class VoxelNetFrontEnd:
         if self.fuse_voxel_features:
             with span("voxelize"):  # crop, cell keys, occupancy bitmap, ranks, per-voxel buckets
                 ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
-            with span("svfe"):      # bucket -> first-T selection -> 7-d rows on chip -> VFE-1/VFE-2/max
+            with span("svfe"):      # bucket -> first-T selection -> 7-d rows on chip -> VFE-1/VFE-2/max -> grid cell
                 ops.voxelize_svfe_fused(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2,
-                                        self.voxelwise, vb.coordinate, vb.number, self.workspace)
+                                        None, vb.coordinate, None, self.workspace, dense=self.dense)
         else:
             with span("voxelize"):
                 ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
@@ -157,35 +168,48 @@ class VoxelNetFrontEnd:
             with span("svfe"):
                 ops.svfe_fused_fwd(vb.feature, self._p1, self._p2, out=self.voxelwise, n_voxels_dev=k_dev)
         with span("scatter"):
-            ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
+            if not self.fuse_voxel_features:  # (the fused kernel wrote the grid cells itself)
+                ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
             if self.skip_empty_boxes:
                 ops.conv3d_mark_boxes(vb.coordinate, n_frames, self.cfg.depth, self.cfg.height, self.cfg.width,
                                       self._layer_geometry, self.box_flags, n_voxels_dev=k_dev)
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
-        ws = self.conv_workspace
+        ws0, ws1, ws2 = self.conv_workspaces
+        st0, st1, st2 = self.out_states if self.out_states is not None else (None, None, None)
         if self.skip_empty_boxes:
             f0, f1, f2 = self.box_flags
             with span("conv1"):  # zero background in, deviation from relu(shift) out
                 ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=f0, consume_flags=True,
-                                       sub=self._bg[0], workspace=ws)
+                                       sub=self._bg[0], workspace=ws0, out_state=st0)
             with span("unscatter"):
                 ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
             with span("conv2"):
                 ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
-                                       consume_flags=True, sub=self._bg[1], workspace=ws)
+                                       consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1)
             with span("conv3"):  # conv-2's zero padding makes its output deviate along the H/W border
                 ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
-                                       consume_flags=True, border_ring=True, workspace=ws)
+                                       consume_flags=True, border_ring=True, workspace=ws2, out_state=st2)
         else:
             with span("conv1"):
-                ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, workspace=ws)
+                ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, workspace=ws0)
             with span("unscatter"):
                 ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
             with span("conv2"):
-                ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2, workspace=ws)
+                ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2, workspace=ws1)
             with span("conv3"):
-                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out, workspace=ws)
+                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out, workspace=ws2)
         return self.out
+
+    def plan_stats(self) -> list:
+        """Blocking diagnostics: what the three conv launches of the last step executed (live boxes,
+        tcgen05 FLOPs, blocks stored) - see ops.conv3d_plan_stats."""
+        c = self.cfg
+        B = self._shape[0]
+        out, din = [], c.depth
+        for layer, ws in zip(self.middle_net.middle_layer, self.conv_workspaces):
+            out.append(ops.conv3d_plan_stats(ws, B, din, c.height, c.width, layer.cin, layer.stride[0], layer.padding[0]))
+            din = ops.conv3d_out_depth(din, layer.stride[0], layer.padding[0])
+        return out
 
     def forward_frames(self, frames: list) -> torch.Tensor:
         """Host frames [(N_i,4) f32 numpy] -> (B,128,H,W) f32 (includes the H2D copy)."""
