@@ -22,9 +22,17 @@ struct Vfe1Params {
   float b[16], s[16], t[16];
 };
 
-struct Vfe2Lane {  // VFE-2 parameters of the two output units (lane, lane + 32) owned by one lane
-  float wa[32], wb[32];
+constexpr int kXS = 16;  // floats per VFE-1 output row kept in shared memory
+
+// VFE-2 parameters.  A VFE-2 input row is [x1_row (16) | agg1 (16)] where agg1 is the same for every
+// row of a voxel, so  W2 x + b = (b + W2[:,16:32] agg1) + W2[:,0:16] x1_row : the second half of the
+// weights is applied once per voxel (read from shared memory), the first half per row (registers).
+struct Vfe2Lane {  // parameters of the two output units (lane, lane + 32) owned by one lane
+  float wa[16], wb[16];  // W2[unit][0..15]
   float ba, bb, sa, sb, ta, tb;
+};
+struct Vfe2Shared {
+  float whi[16][64];     // whi[k][unit] = W2[unit][16 + k]
 };
 
 __device__ __forceinline__ void load_vfe1_params(Vfe1Params& p1, const float* w1, const float* b1, const float* s1,
@@ -37,83 +45,96 @@ __device__ __forceinline__ void load_vfe1_params(Vfe1Params& p1, const float* w1
   }
 }
 
-__device__ __forceinline__ void load_vfe2_lane(Vfe2Lane& q, const float* w2, const float* b2, const float* s2,
-                                               const float* t2, uint32_t lane) {
+__device__ __forceinline__ void load_vfe2(Vfe2Lane& q, Vfe2Shared& sh, const float* w2, const float* b2, const float* s2,
+                                          const float* t2, uint32_t lane) {
 #pragma unroll
-  for (int k = 0; k < 32; ++k) {
+  for (int k = 0; k < 16; ++k) {
     q.wa[k] = w2[lane * 32 + k];
     q.wb[k] = w2[(lane + 32) * 32 + k];
   }
   q.ba = b2[lane];  q.bb = b2[lane + 32];
   q.sa = s2[lane];  q.sb = s2[lane + 32];
   q.ta = t2[lane];  q.tb = t2[lane + 32];
+  for (int i = threadIdx.x; i < 16 * 64; i += blockDim.x) sh.whi[i >> 6][i & 63] = w2[(i & 63) * 32 + 16 + (i >> 6)];
 }
 
-// VFE-2 + voxel-wise max for ONE voxel whose R masked input rows ([x1 | agg1], 32 floats each) sit in
-// shared memory at x.  Lane l owns units (l, l + 32).  on_bits: bit r set <=> row r has mask 1 (rows with
-// mask 0 are all-zero inputs; they count for the unmasked aggregate but contribute exactly 0 to the
-// voxel-wise max).  o[i] = voxelwise channel (lane + 32 i).
-__device__ __forceinline__ void vfe2_voxel_max(const float (*x)[32], int R, uint64_t on_bits, const Vfe2Lane& q,
-                                               float (&o)[4]) {
-  float all_a = -INFINITY, all_b = -INFINITY;  // max over all rows (the reference's `agg`)
-  float on_a = -INFINITY, on_b = -INFINITY;    // max over rows with mask 1 of the pointwise part
-  int r = 0;
-  // two rows per trip: four independent FMA chains (a single row's two chains of 32 dependent FMAs
-  // leave the pipe idle three cycles out of four)
-  for (; r + 1 < R; r += 2) {
-    float a0 = q.ba, b0 = q.bb, a1 = q.ba, b1 = q.bb;
-    const float4* x0 = reinterpret_cast<const float4*>(x[r]);
-    const float4* x1 = reinterpret_cast<const float4*>(x[r + 1]);
+// VFE-2 + voxel-wise max for ONE voxel.  x: the voxel's R VFE-1 output rows (kXS floats apart) in shared
+// memory; agg: its 16 agg1 values.  Lane l owns units (l, l + 32).  on_bits: bit r set <=> row r has mask 1.
+// A row with mask 0 is an all-zero VFE-2 input (model.py:82 masks the concat): its pointwise output is
+// relu(b)*s + t, it counts for the unmasked aggregate (model.py:77) and contributes exactly 0 to the
+// voxel-wise max of the masked output (model.py:100).  o[i] = voxelwise channel (lane + 32 i).
+__device__ __forceinline__ void vfe2_voxel_max(const float* x, const float* agg, int R, uint64_t on_bits,
+                                               const Vfe2Lane& q, const Vfe2Shared& sh, uint32_t lane, float (&o)[4]) {
+  const uint64_t evaluated = R >= 64 ? ~0ull : ((1ull << R) - 1ull);
+  on_bits &= evaluated;
+  const bool any_on = on_bits != 0;
+  const bool any_off = on_bits != evaluated;
+  // per-voxel part: bias + W2[:,16:32] agg1
+  float ca = q.ba, cb = q.bb;
+  {
+    const float4* g4 = reinterpret_cast<const float4*>(agg);
 #pragma unroll
-    for (int k4 = 0; k4 < 8; ++k4) {
-      const float4 v = x0[k4], w = x1[k4];
-      a0 = fmaf(q.wa[4 * k4 + 0], v.x, a0);  b0 = fmaf(q.wb[4 * k4 + 0], v.x, b0);
-      a1 = fmaf(q.wa[4 * k4 + 0], w.x, a1);  b1 = fmaf(q.wb[4 * k4 + 0], w.x, b1);
-      a0 = fmaf(q.wa[4 * k4 + 1], v.y, a0);  b0 = fmaf(q.wb[4 * k4 + 1], v.y, b0);
-      a1 = fmaf(q.wa[4 * k4 + 1], w.y, a1);  b1 = fmaf(q.wb[4 * k4 + 1], w.y, b1);
-      a0 = fmaf(q.wa[4 * k4 + 2], v.z, a0);  b0 = fmaf(q.wb[4 * k4 + 2], v.z, b0);
-      a1 = fmaf(q.wa[4 * k4 + 2], w.z, a1);  b1 = fmaf(q.wb[4 * k4 + 2], w.z, b1);
-      a0 = fmaf(q.wa[4 * k4 + 3], v.w, a0);  b0 = fmaf(q.wb[4 * k4 + 3], v.w, b0);
-      a1 = fmaf(q.wa[4 * k4 + 3], w.w, a1);  b1 = fmaf(q.wb[4 * k4 + 3], w.w, b1);
+    for (int k4 = 0; k4 < 4; ++k4) {
+      const float4 g = g4[k4];
+      ca = fmaf(sh.whi[4 * k4 + 0][lane], g.x, ca);  cb = fmaf(sh.whi[4 * k4 + 0][lane + 32], g.x, cb);
+      ca = fmaf(sh.whi[4 * k4 + 1][lane], g.y, ca);  cb = fmaf(sh.whi[4 * k4 + 1][lane + 32], g.y, cb);
+      ca = fmaf(sh.whi[4 * k4 + 2][lane], g.z, ca);  cb = fmaf(sh.whi[4 * k4 + 2][lane + 32], g.z, cb);
+      ca = fmaf(sh.whi[4 * k4 + 3][lane], g.w, ca);  cb = fmaf(sh.whi[4 * k4 + 3][lane + 32], g.w, cb);
     }
-    a0 = fmaf(fmaxf(a0, 0.0f), q.sa, q.ta);
-    b0 = fmaf(fmaxf(b0, 0.0f), q.sb, q.tb);
-    a1 = fmaf(fmaxf(a1, 0.0f), q.sa, q.ta);
-    b1 = fmaf(fmaxf(b1, 0.0f), q.sb, q.tb);
-    all_a = fmaxf(all_a, fmaxf(a0, a1));
-    all_b = fmaxf(all_b, fmaxf(b0, b1));
-    const bool m0 = (on_bits >> r) & 1, m1 = (on_bits >> (r + 1)) & 1;
-    on_a = fmaxf(on_a, fmaxf(m0 ? a0 : -INFINITY, m1 ? a1 : -INFINITY));
-    on_b = fmaxf(on_b, fmaxf(m0 ? b0 : -INFINITY, m1 ? b1 : -INFINITY));
   }
-  if (r < R) {
-    float a = q.ba, b = q.bb;
-    const float4* xr = reinterpret_cast<const float4*>(x[r]);
+  float on_a = -INFINITY, on_b = -INFINITY;  // max over the rows with mask 1
+  uint64_t todo = on_bits;
+  while (todo) {
+    const int r0 = __ffsll((long long)todo) - 1;
+    todo &= todo - 1;
+    if (todo) {  // two rows per trip: four independent FMA chains
+      const int r1 = __ffsll((long long)todo) - 1;
+      todo &= todo - 1;
+      float a0 = ca, b0 = cb, a1 = ca, b1 = cb;
+      const float4* x0 = reinterpret_cast<const float4*>(x + r0 * kXS);
+      const float4* x1 = reinterpret_cast<const float4*>(x + r1 * kXS);
 #pragma unroll
-    for (int k4 = 0; k4 < 8; ++k4) {
-      const float4 v = xr[k4];
-      a = fmaf(q.wa[4 * k4 + 0], v.x, a);
-      b = fmaf(q.wb[4 * k4 + 0], v.x, b);
-      a = fmaf(q.wa[4 * k4 + 1], v.y, a);
-      b = fmaf(q.wb[4 * k4 + 1], v.y, b);
-      a = fmaf(q.wa[4 * k4 + 2], v.z, a);
-      b = fmaf(q.wb[4 * k4 + 2], v.z, b);
-      a = fmaf(q.wa[4 * k4 + 3], v.w, a);
-      b = fmaf(q.wb[4 * k4 + 3], v.w, b);
-    }
-    a = fmaf(fmaxf(a, 0.0f), q.sa, q.ta);
-    b = fmaf(fmaxf(b, 0.0f), q.sb, q.tb);
-    all_a = fmaxf(all_a, a);
-    all_b = fmaxf(all_b, b);
-    if ((on_bits >> r) & 1) {
+      for (int k4 = 0; k4 < 4; ++k4) {
+        const float4 v = x0[k4], w = x1[k4];
+        a0 = fmaf(q.wa[4 * k4 + 0], v.x, a0);  b0 = fmaf(q.wb[4 * k4 + 0], v.x, b0);
+        a1 = fmaf(q.wa[4 * k4 + 0], w.x, a1);  b1 = fmaf(q.wb[4 * k4 + 0], w.x, b1);
+        a0 = fmaf(q.wa[4 * k4 + 1], v.y, a0);  b0 = fmaf(q.wb[4 * k4 + 1], v.y, b0);
+        a1 = fmaf(q.wa[4 * k4 + 1], w.y, a1);  b1 = fmaf(q.wb[4 * k4 + 1], w.y, b1);
+        a0 = fmaf(q.wa[4 * k4 + 2], v.z, a0);  b0 = fmaf(q.wb[4 * k4 + 2], v.z, b0);
+        a1 = fmaf(q.wa[4 * k4 + 2], w.z, a1);  b1 = fmaf(q.wb[4 * k4 + 2], w.z, b1);
+        a0 = fmaf(q.wa[4 * k4 + 3], v.w, a0);  b0 = fmaf(q.wb[4 * k4 + 3], v.w, b0);
+        a1 = fmaf(q.wa[4 * k4 + 3], w.w, a1);  b1 = fmaf(q.wb[4 * k4 + 3], w.w, b1);
+      }
+      a0 = fmaf(fmaxf(a0, 0.0f), q.sa, q.ta);
+      b0 = fmaf(fmaxf(b0, 0.0f), q.sb, q.tb);
+      a1 = fmaf(fmaxf(a1, 0.0f), q.sa, q.ta);
+      b1 = fmaf(fmaxf(b1, 0.0f), q.sb, q.tb);
+      on_a = fmaxf(on_a, fmaxf(a0, a1));
+      on_b = fmaxf(on_b, fmaxf(b0, b1));
+    } else {
+      float a = ca, b = cb;
+      const float4* xr = reinterpret_cast<const float4*>(x + r0 * kXS);
+#pragma unroll
+      for (int k4 = 0; k4 < 4; ++k4) {
+        const float4 v = xr[k4];
+        a = fmaf(q.wa[4 * k4 + 0], v.x, a);  b = fmaf(q.wb[4 * k4 + 0], v.x, b);
+        a = fmaf(q.wa[4 * k4 + 1], v.y, a);  b = fmaf(q.wb[4 * k4 + 1], v.y, b);
+        a = fmaf(q.wa[4 * k4 + 2], v.z, a);  b = fmaf(q.wb[4 * k4 + 2], v.z, b);
+        a = fmaf(q.wa[4 * k4 + 3], v.w, a);  b = fmaf(q.wb[4 * k4 + 3], v.w, b);
+      }
+      a = fmaf(fmaxf(a, 0.0f), q.sa, q.ta);
+      b = fmaf(fmaxf(b, 0.0f), q.sb, q.tb);
       on_a = fmaxf(on_a, a);
       on_b = fmaxf(on_b, b);
     }
   }
+  // unmasked aggregate: rows with mask 0 evaluate to relu(bias)*s + t
+  float all_a = on_a, all_b = on_b;
+  if (any_off) {
+    all_a = fmaxf(all_a, fmaf(fmaxf(q.ba, 0.0f), q.sa, q.ta));
+    all_b = fmaxf(all_b, fmaf(fmaxf(q.bb, 0.0f), q.sb, q.tb));
+  }
   // voxelwise[c] = max_t(mask_t * out2[t][c]): rows with mask 0 contribute exactly 0
-  const uint64_t evaluated = R >= 64 ? ~0ull : ((1ull << R) - 1ull);
-  const bool any_on = (on_bits & evaluated) != 0;
-  const bool any_off = (on_bits & evaluated) != evaluated;
   const float floor0 = any_off ? 0.0f : -INFINITY;
   o[0] = fmaxf(any_on ? on_a : -INFINITY, floor0);
   o[1] = fmaxf(any_on ? on_b : -INFINITY, floor0);
@@ -147,10 +168,11 @@ __device__ __forceinline__ void store_voxel_out(const float (&o)[4], uint32_t la
 }
 
 // rows: shared memory, 7 floats per row.  Evaluated row r (0 <= r < R) is source row
-// (r < nu ? r : tlast).  x1: shared scratch of (R + 1) x 32 floats; row `aggrow` holds agg1.
+// (r < nu ? r : tlast).  x1: shared scratch of (R + 1) x kXS floats; row R receives agg1.
 // o: the voxel's 128 maxima, channel (lane + 32 i) in o[i].
-__device__ __forceinline__ void svfe_eval_voxel(const float* rows, int nu, int R, int tlast, float (*x1)[32], int aggrow,
-                                                const Vfe1Params& p1, const Vfe2Lane& q, float (&o)[4], uint32_t lane) {
+__device__ __forceinline__ void svfe_eval_voxel(const float* rows, int nu, int R, int tlast, float* x1,
+                                                const Vfe1Params& p1, const Vfe2Lane& q, const Vfe2Shared& sh,
+                                                float (&o)[4], uint32_t lane) {
   // ---- mask bits: bit r set <=> evaluated row r has max_j != 0 --------------------------------
   uint64_t on_bits = 0;
   for (int r0 = 0; r0 < R; r0 += 32) {
@@ -172,24 +194,16 @@ __device__ __forceinline__ void svfe_eval_voxel(const float* rows, int nu, int R
     float a = p1.b[u];
 #pragma unroll
     for (int j = 0; j < 7; ++j) a = fmaf(p1.w[u * 7 + j], f[j], a);
-    x1[r][u] = fmaf(fmaxf(a, 0.0f), p1.s[u], p1.t[u]);
+    x1[r * kXS + u] = fmaf(fmaxf(a, 0.0f), p1.s[u], p1.t[u]);
   }
   __syncwarp();
-  if (lane < 16) {  // agg1[u] = max over evaluated rows (== max over all T rows)
-    float a = x1[0][lane];
-    for (int r = 1; r < R; ++r) a = fmaxf(a, x1[r][lane]);
-    x1[aggrow][lane] = a;
+  if (lane < 16) {  // agg1[u] = max over evaluated rows (== max over all T rows, masked or not)
+    float a = x1[lane];
+    for (int r = 1; r < R; ++r) a = fmaxf(a, x1[r * kXS + lane]);
+    x1[R * kXS + lane] = a;
   }
   __syncwarp();
-  // concat + mask: rows with mask 0 become all-zero inputs of VFE-2
-  for (int e = lane; e < R * 32; e += 32) {
-    const int r = e >> 5, c = e & 31;
-    const bool on = (on_bits >> r) & 1;
-    const float val = c < 16 ? x1[r][c] : x1[aggrow][c - 16];
-    x1[r][c] = on ? val : 0.0f;
-  }
-  __syncwarp();
-  vfe2_voxel_max(x1, R, on_bits, q, o);
+  vfe2_voxel_max(x1, x1 + R * kXS, R, on_bits, q, sh, lane, o);
 }
 
 }  // namespace vn

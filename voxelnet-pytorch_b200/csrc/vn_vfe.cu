@@ -14,20 +14,21 @@ namespace {
 constexpr int kMaxT = 64;
 constexpr int kWarps = 8;
 
-// 2 blocks of 8 warps per SM: the 64 VFE-2 weights per lane live in registers (<= 128 regs/thread).
-__global__ void __launch_bounds__(kWarps * 32, 2)
+// 3 blocks of 8 warps per SM: the per-row half of the VFE-2 weights lives in registers (32 per lane).
+__global__ void __launch_bounds__(kWarps * 32, 3)
     k_svfe_fused(const float* __restrict__ feature, int64_t K, int T, const int32_t* __restrict__ n_voxels_dev,
                  const float* __restrict__ w1, const float* __restrict__ b1, const float* __restrict__ s1,
                  const float* __restrict__ t1, const float* __restrict__ w2, const float* __restrict__ b2,
                  const float* __restrict__ s2, const float* __restrict__ t2, float* __restrict__ voxelwise) {
-  // dynamic shared memory: [kWarps][T+1][32] x1 rows (row T = agg1) | [kWarps][in_ld] staged inputs
+  // dynamic shared memory: [kWarps][T+1][kXS] x1 rows (+ agg1) | [kWarps][in_ld] staged inputs
   extern __shared__ __align__(16) float dyn_smem[];
   __shared__ Vfe1Params p1;
+  __shared__ Vfe2Shared sh;
   const int in_ld = (T * 7 + 3) & ~3;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   load_vfe1_params(p1, w1, b1, s1, t1);
   Vfe2Lane q;
-  load_vfe2_lane(q, w2, b2, s2, t2, lane);
+  load_vfe2(q, sh, w2, b2, s2, t2, lane);
   __syncthreads();
 
   int64_t total = K;
@@ -35,8 +36,8 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
     const int64_t live = *n_voxels_dev;
     if (live < total) total = live;
   }
-  float(*x1)[32] = reinterpret_cast<float(*)[32]>(dyn_smem + (size_t)warp * (T + 1) * 32);
-  float* in = dyn_smem + (size_t)kWarps * (T + 1) * 32 + (size_t)warp * in_ld;
+  float* x1 = dyn_smem + (size_t)warp * (T + 1) * kXS;
+  float* in = dyn_smem + (size_t)kWarps * (T + 1) * kXS + (size_t)warp * in_ld;
   const int64_t nwarps = (int64_t)gridDim.x * kWarps;
   for (int64_t v = (int64_t)blockIdx.x * kWarps + warp; v < total; v += nwarps) {
     const float* src = feature + v * (int64_t)(T * 7);
@@ -57,7 +58,7 @@ __global__ void __launch_bounds__(kWarps * 32, 2)
     }
     const int R = nu < T ? nu + 1 : T;  // rows to evaluate: 0..nu-1 and (if any) the tail row T-1
     float o[4];
-    svfe_eval_voxel(in, nu, R, T - 1, x1, T, p1, q, o, lane);
+    svfe_eval_voxel(in, nu, R, T - 1, x1, p1, q, sh, o, lane);
     store_voxel_out(o, lane, voxelwise + v * 128, nullptr);
     __syncwarp();
   }
@@ -188,10 +189,10 @@ int vn_svfe_fused_fwd(const float* feature, int64_t K, int32_t T, const int32_t*
   if (K == 0) return VN_OK;
   VN_REQUIRE(feature && w1 && b1 && s1 && t1 && w2 && b2 && s2 && t2 && voxelwise, "svfe_fused: null pointer");
   cudaStream_t st = as_stream(stream);
-  const size_t smem = sizeof(float) * ((size_t)kWarps * (T + 1) * 32 + (size_t)kWarps * ((T * 7 + 3) & ~3));
+  const size_t smem = sizeof(float) * ((size_t)kWarps * (T + 1) * kXS + (size_t)kWarps * ((T * 7 + 3) & ~3));
   VN_CUDA(cudaFuncSetAttribute(k_svfe_fused, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t want = (K + kWarps - 1) / kWarps;
-  const int64_t cap = (int64_t)sm_count() * 2;
+  const int64_t cap = (int64_t)sm_count() * 3;
   k_svfe_fused<<<(unsigned)(want < cap ? want : cap), kWarps * 32, smem, st>>>(feature, K, T, n_voxels_dev, w1, b1, s1,
                                                                               t1, w2, b2, s2, t2, voxelwise);
   VN_LAUNCH_CHECK("k_svfe_fused");

@@ -407,22 +407,22 @@ struct Vfe1Packed {   // VFE-1 parameters laid out for 128-bit broadcast loads
 };
 
 struct PackWarp {
-  float x[32][32];      // batch rows: VFE-1 output | agg1, masked = VFE-2 input
-  float4 pts[32];       // the batch's points in slot order (row r of a voxel = its r-th point)
-  double mean[32][3];   // per batch voxel: centroid (utils.py:87-88)
-  float agg[32][16];    // per batch voxel: agg1
-  int rv[32];           // row -> owning voxel (lane of the 32-voxel range), start markers
-  uint8_t first[32], nrows[32], npts[32];  // per batch voxel
+  float x[32][kXS];             // batch rows: VFE-1 output
+  float4 pts[32];               // the batch's points in slot order (row r of a voxel = its r-th point)
+  double mean[kPackRange][3];   // per batch voxel: centroid (utils.py:87-88)
+  float agg[kPackRange][16];    // per batch voxel: agg1
+  int rv[32];                   // row -> owning voxel (lane of the work item), start markers
+  uint8_t first[kPackRange], nrows[kPackRange], npts[kPackRange];  // per batch voxel
 };
 
 __device__ __forceinline__ size_t pack_warp_bytes(int T) {
   const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
-  const size_t slow = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128;
+  const size_t slow = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * kXS * 4;
   const size_t fast = sizeof(PackWarp);
   return ((slow > fast ? slow : fast) + 15) & ~(size_t)15;
 }
 
-__global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
+__global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
     const vn_grid_t g, const float4* __restrict__ points, int n_frames,
     const int32_t* __restrict__ voxel_offsets, int64_t max_voxels, const int32_t* __restrict__ cnt,
     const int32_t* __restrict__ seg, const int32_t* __restrict__ pidx, const float* __restrict__ w1,
@@ -433,6 +433,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
   extern __shared__ __align__(16) uint8_t dyn_smem[];
   __shared__ Vfe1Params p1;   // one-voxel path
   __shared__ Vfe1Packed pk;   // packed path
+  __shared__ Vfe2Shared sh;
   const int T = g.T;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   uint8_t* wbase = dyn_smem + warp * pack_warp_bytes(T);
@@ -446,7 +447,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
     pk.t[u] = t1[u];
   }
   Vfe2Lane q;
-  load_vfe2_lane(q, w2, b2, s2, t2, lane);
+  load_vfe2(q, sh, w2, b2, s2, t2, lane);
   __syncthreads();
 
   int64_t total = voxel_offsets[n_frames];
@@ -479,7 +480,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
     int base = 0, a = 0;
     while (base < Rall) {
       // ---- batch = voxels [a, b_end): as many whole voxels as fit 32 rows -------------------------
-      const int b_end = __popc(__ballot_sync(0xffffffffu, incl - base <= 32));
+      const int b_end = min(__popc(__ballot_sync(0xffffffffu, incl - base <= 32)), kPackRange);
       const int Rtot = __shfl_sync(0xffffffffu, incl, b_end - 1) - base;
       const int nvox = b_end - a;
       W.rv[lane] = -1;
@@ -586,18 +587,6 @@ __global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
         }
       }
       __syncwarp();
-      // concat + mask (model.py:78-82): rows with mask 0 become all-zero inputs of VFE-2
-      if (rowvalid) {
-        float4* xrow = reinterpret_cast<float4*>(W.x[lane]);
-        const float4* ag = reinterpret_cast<const float4*>(W.agg[w - a]);
-        const float4 z4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          if (!on) xrow[i] = z4;
-          xrow[4 + i] = on ? ag[i] : z4;
-        }
-      }
-      __syncwarp();
       // ---- VFE-2 + voxel-wise max, voxel by voxel (lane <-> output units) -----------------------------
       for (int k = 0; k < nvox; ++k) {
         const int n = W.nrows[k];
@@ -606,7 +595,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
         const int f0 = W.first[k];
         const uint32_t bits = (on_bits >> f0) & (n >= 32 ? 0xffffffffu : ((1u << n) - 1u));
         float o[4];
-        vfe2_voxel_max(&W.x[f0], n, (uint64_t)bits, q, o);
+        vfe2_voxel_max(W.x[f0], W.agg[k], n, (uint64_t)bits, q, sh, lane, o);
         const int64_t vrow = rg * kPackRange + a + k;
         store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
                         dense != nullptr ? dense + cell_k * 128 : nullptr);
@@ -625,7 +614,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
       const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
       float4* pts = reinterpret_cast<float4*>(wbase);
       float* rows = reinterpret_cast<float*>(wbase + (size_t)T * 16);
-      float(*x1)[32] = reinterpret_cast<float(*)[32]>(wbase + (size_t)T * 16 + rows_bytes);
+      float* x1 = reinterpret_cast<float*>(wbase + (size_t)T * 16 + rows_bytes);
       const int m = warp_select_points(points, pidx, c_v, s_v, T, pts, lane, reinterpret_cast<int*>(rows),
                                        (int)((pack_warp_bytes(T) - (size_t)T * 16) / 4));
       __syncwarp();
@@ -639,7 +628,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 2) k_vox_svfe_packed(
       }
       __syncwarp();
       float o[4];
-      svfe_eval_voxel(rows, m, Rv, m, x1, T, p1, q, o, lane);
+      svfe_eval_voxel(rows, m, Rv, m, x1, p1, q, sh, o, lane);
       const int64_t vrow = rg * kPackRange + v;
       store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
                       dense != nullptr ? dense + cell_v * 128 : nullptr);
@@ -779,12 +768,12 @@ int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int
   if (rc != VN_OK) return rc;
   const int T = grid->T;
   const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
-  const size_t slow = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * 128;
+  const size_t slow = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * kXS * 4;
   const size_t per_warp = ((slow > sizeof(PackWarp) ? slow : sizeof(PackWarp)) + 15) & ~(size_t)15;
   const size_t smem = kPackWarps * per_warp;
   VN_CUDA(cudaFuncSetAttribute(k_vox_svfe_packed, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   const int64_t want = (max_voxels + kPackRange * kPackWarps - 1) / (kPackRange * kPackWarps);
-  const int64_t cap = (int64_t)sm_count() * 2;
+  const int64_t cap = (int64_t)sm_count() * 3;
   k_vox_svfe_packed<<<(unsigned)(want < cap ? want : cap), kPackWarps * 32, smem, st>>>(
       *grid, reinterpret_cast<const float4*>(points), n_frames, voxel_offsets, max_voxels, w.cnt, w.seg, w.pidx, w1, b1,
       s1, t1, w2, b2, s2, t2, voxelwise, reinterpret_cast<__nv_bfloat16*>(dense_bf16),
