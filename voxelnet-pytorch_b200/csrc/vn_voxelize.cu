@@ -24,6 +24,7 @@ namespace vn {
 namespace {
 
 constexpr uint32_t kInvalidKey = 0xFFFFFFFFu;
+constexpr int kCtrItems = 0, kCtrBigCount = 1, kCtrBigNext = 2;  // VoxWorkspace::counters slots
 constexpr int kMaxT = 64;  // smem staging rows per warp (T is 35 or 45)
 
 struct VoxWorkspace {
@@ -36,6 +37,7 @@ struct VoxWorkspace {
   int32_t* arrival;      // [n_points]           arrival slot inside the voxel
   int32_t* seg;          // [n_points]           segment start of each voxel row in pidx
   int32_t* pidx;         // [n_points]           point indices bucketed per voxel
+  int32_t* biglist;      // [n_points / (min(31,T)+1) + 1]  voxel rows with more than 31 (or more than T) points
   size_t words;          // bitmap words per frame
   size_t zero_bytes;     // bitmap..cnt are contiguous: one fill
   size_t total_bytes;
@@ -63,6 +65,7 @@ __host__ VoxWorkspace carve(const vn_grid_t& g, int n_frames, int64_t n_points, 
   w.arrival = reinterpret_cast<int32_t*>(take(np * 4));
   w.seg = reinterpret_cast<int32_t*>(take(np * 4));
   w.pidx = reinterpret_cast<int32_t*>(take(np * 4));
+  w.biglist = reinterpret_cast<int32_t*>(take((np / (size_t)((g.T < 31 ? g.T : 31) + 1) + 1) * 4));
   w.total_bytes = off;
   return w;
 }
@@ -213,11 +216,11 @@ __global__ void __launch_bounds__(256) k_vox_count(const int32_t* __restrict__ f
 __global__ void __launch_bounds__(1024) k_vox_segment_scan(const int32_t* __restrict__ frame_offsets,
                                                             const int32_t* __restrict__ voxel_offsets,
                                                             const int32_t* __restrict__ cnt,
-                                                            int32_t* __restrict__ seg, int32_t* __restrict__ counters) {
+                                                            int32_t* __restrict__ seg, int32_t* __restrict__ counters,
+                                                            int32_t* __restrict__ biglist, int T) {
   __shared__ uint32_t warp_total[32];
   __shared__ uint32_t carry;
   const int f = blockIdx.x;
-  if (f == 0 && threadIdx.x < 64) counters[threadIdx.x] = 0;  // work counters of the kernels that follow
   const int r0 = voxel_offsets[f], r1 = voxel_offsets[f + 1];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   if (threadIdx.x == 0) carry = (uint32_t)frame_offsets[f];
@@ -225,6 +228,8 @@ __global__ void __launch_bounds__(1024) k_vox_segment_scan(const int32_t* __rest
   for (int base = r0; base < r1; base += 1024) {
     const int r = base + threadIdx.x;
     const uint32_t c = r < r1 ? (uint32_t)cnt[r] : 0;
+    // voxels the packed SVFE kernel handles one per warp (heavy items, scheduled first)
+    if (c > 31u || c > (uint32_t)T) biglist[atomicAdd(&counters[kCtrBigCount], 1)] = r;
     const uint32_t incl = warp_incl_scan(c, lane);
     if (lane == 31) warp_total[warp] = incl;
     __syncthreads();
@@ -429,7 +434,8 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
     const float* __restrict__ b1, const float* __restrict__ s1, const float* __restrict__ t1,
     const float* __restrict__ w2, const float* __restrict__ b2, const float* __restrict__ s2,
     const float* __restrict__ t2, float* __restrict__ voxelwise, __nv_bfloat16* __restrict__ dense,
-    long long* __restrict__ coords, long long* __restrict__ counts, int32_t* __restrict__ work_counter) {
+    long long* __restrict__ coords, long long* __restrict__ counts, int32_t* __restrict__ counters,
+    const int32_t* __restrict__ biglist) {
   extern __shared__ __align__(16) uint8_t dyn_smem[];
   __shared__ Vfe1Params p1;   // one-voxel path
   __shared__ Vfe1Packed pk;   // packed path
@@ -452,9 +458,51 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
 
   int64_t total = voxel_offsets[n_frames];
   if (total > max_voxels) total = max_voxels;
+  // ---- heavy items first: voxels with > 31 (or > T) points, one voxel per warp (they sit next to each
+  // other in row order - dense cells near the sensor - so leaving them inside the 8-voxel items makes
+  // stragglers) --------------------------------------------------------------------------------------
+  {
+    const int nbig = counters[kCtrBigCount];
+    for (;;) {
+      int bi = 0;
+      if (lane == 0) bi = atomicAdd(&counters[kCtrBigNext], 1);
+      bi = __shfl_sync(0xffffffffu, bi, 0);
+      if (bi >= nbig) break;
+      const int64_t vrow = biglist[bi];
+      if (vrow >= total) continue;
+      const int c_v = cnt[vrow], s_v = seg[vrow];
+      const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
+      float4* pts = reinterpret_cast<float4*>(wbase);
+      float* rows = reinterpret_cast<float*>(wbase + (size_t)T * 16);
+      float* x1 = reinterpret_cast<float*>(wbase + (size_t)T * 16 + rows_bytes);
+      const int m = warp_select_points(points, pidx, c_v, s_v, T, pts, lane, reinterpret_cast<int*>(rows),
+                                       (int)((pack_warp_bytes(T) - (size_t)T * 16) / 4));
+      __syncwarp();
+      int64_t cell_v = 0;
+      if (lane == 0) {
+        cell_v = write_coords(g, pts[0], n_frames, voxel_offsets, vrow, coords);
+        if (counts != nullptr) counts[vrow] = m;
+      }
+      cell_v = __shfl_sync(0xffffffffu, cell_v, 0);
+      double mx, my, mz;
+      warp_centroid(pts, m, T, lane, mx, my, mz);
+      __syncwarp();
+      const int Rv = m < T ? m + 1 : T;  // real rows 0..m-1, then one pad row at index m
+      for (int e = lane; e < Rv * 7; e += 32) {
+        const int t = e / 7, jx = e - t * 7;
+        rows[e] = feature_value(pts, m, t, jx, mx, my, mz);
+      }
+      __syncwarp();
+      float o[4];
+      svfe_eval_voxel(rows, m, Rv, m, x1, p1, q, sh, o, lane);
+      store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
+                      dense != nullptr ? dense + cell_v * 128 : nullptr);
+      __syncwarp();
+    }
+  }
   const int64_t nranges = (total + kPackRange - 1) / kPackRange;
-  // work items are pulled from a counter (voxels near the sensor hold many more points than far ones);
-  // the next item is requested before the current one is processed
+  // work items are pulled from a counter; the next item is requested before the current one is processed
+  int32_t* work_counter = counters + kCtrItems;
   int nxt = 0;
   if (lane == 0) nxt = atomicAdd(work_counter, 1);
   for (;;) {
@@ -469,10 +517,12 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
     if (valid) {
       c = cnt[row];
       s0 = seg[row];
-      cell = write_coords(g, points[pidx[s0]], n_frames, voxel_offsets, row, coords);
-      if (counts != nullptr) counts[row] = c < T ? c : T;
     }
-    const bool big = valid && (c > 31 || c > T);
+    const bool big = valid && (c > 31 || c > T);  // done above
+    if (valid && !big) {
+      cell = write_coords(g, points[pidx[s0]], n_frames, voxel_offsets, row, coords);
+      if (counts != nullptr) counts[row] = c;
+    }
     const int R = (valid && !big) ? c + (c < T ? 1 : 0) : 0;  // distinct rows of this voxel (<= 32)
     const int incl = (int)warp_incl_scan((uint32_t)R, lane);
     const int excl = incl - R;
@@ -604,36 +654,6 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
       base += Rtot;
       a = b_end;
     }
-    // ---- the rare voxels with > 31 (or > T) points: one voxel per warp -------------------------------
-    uint32_t bigs = __ballot_sync(0xffffffffu, big);
-    while (bigs) {
-      const int v = __ffs(bigs) - 1;
-      bigs &= bigs - 1;
-      const int c_v = __shfl_sync(0xffffffffu, c, v), s_v = __shfl_sync(0xffffffffu, s0, v);
-      const int64_t cell_v = __shfl_sync(0xffffffffu, cell, v);
-      const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
-      float4* pts = reinterpret_cast<float4*>(wbase);
-      float* rows = reinterpret_cast<float*>(wbase + (size_t)T * 16);
-      float* x1 = reinterpret_cast<float*>(wbase + (size_t)T * 16 + rows_bytes);
-      const int m = warp_select_points(points, pidx, c_v, s_v, T, pts, lane, reinterpret_cast<int*>(rows),
-                                       (int)((pack_warp_bytes(T) - (size_t)T * 16) / 4));
-      __syncwarp();
-      double mx, my, mz;
-      warp_centroid(pts, m, T, lane, mx, my, mz);
-      __syncwarp();
-      const int Rv = m < T ? m + 1 : T;  // real rows 0..m-1, then one pad row at index m
-      for (int e = lane; e < Rv * 7; e += 32) {
-        const int t = e / 7, jx = e - t * 7;
-        rows[e] = feature_value(pts, m, t, jx, mx, my, mz);
-      }
-      __syncwarp();
-      float o[4];
-      svfe_eval_voxel(rows, m, Rv, m, x1, p1, q, sh, o, lane);
-      const int64_t vrow = rg * kPackRange + v;
-      store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
-                      dense != nullptr ? dense + cell_v * 128 : nullptr);
-      __syncwarp();
-    }
   }
 }
 
@@ -660,8 +680,9 @@ int check_common(const vn_grid_t* grid, const void* points, const int32_t* frame
 
 // P5 + P6: CSR segments per voxel and the bucketed point indices.
 int launch_bucket(const VoxWorkspace& w, const int32_t* frame_offsets, int n_frames, int64_t n_points_total,
-                  const int32_t* voxel_offsets, cudaStream_t st) {
-  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg, w.counters);
+                  const int32_t* voxel_offsets, int T, cudaStream_t st) {
+  VN_CUDA(cudaMemsetAsync(w.counters, 0, 64 * sizeof(int32_t), st));
+  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg, w.counters, w.biglist, T);
   VN_LAUNCH_CHECK("k_vox_segment_scan");
   const int64_t want = (n_points_total + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 16;
@@ -732,7 +753,7 @@ int vn_voxelize_fill(const vn_grid_t* grid, const float* points, const int32_t* 
   cudaStream_t st = as_stream(stream);
   const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
   const int sms = sm_count();
-  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, st);
+  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, grid->T, st);
   if (rc != VN_OK) return rc;
   {
     // persistent warps: 8 resident blocks of 8 warps per SM
@@ -764,7 +785,7 @@ int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int
              "voxelize_svfe_fused: misaligned output");
   cudaStream_t st = as_stream(stream);
   const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
-  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, st);
+  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, grid->T, st);
   if (rc != VN_OK) return rc;
   const int T = grid->T;
   const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
@@ -777,7 +798,8 @@ int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int
   k_vox_svfe_packed<<<(unsigned)(want < cap ? want : cap), kPackWarps * 32, smem, st>>>(
       *grid, reinterpret_cast<const float4*>(points), n_frames, voxel_offsets, max_voxels, w.cnt, w.seg, w.pidx, w1, b1,
       s1, t1, w2, b2, s2, t2, voxelwise, reinterpret_cast<__nv_bfloat16*>(dense_bf16),
-      reinterpret_cast<long long*>(coordinate_buffer), reinterpret_cast<long long*>(number_buffer), w.counters);
+      reinterpret_cast<long long*>(coordinate_buffer), reinterpret_cast<long long*>(number_buffer), w.counters,
+      w.biglist);
   VN_LAUNCH_CHECK("k_vox_svfe_packed");
   return VN_OK;
 }
