@@ -100,6 +100,7 @@ struct ConvParams {
   const GroupDesc* groups;
   const TilePlan* tiles;
   PlaneInfo plane[kMaxPlanes];
+  unsigned long long* prof;  // debug: [grid][16] cycle counters (vn_conv3d_debug_profile), or nullptr
 };
 
 struct PlanParams {
@@ -302,6 +303,8 @@ __global__ void __launch_bounds__(kThreads, 1)
   if (warp == 0) {
     // ====== scheduler + planner + TMA producer (warp-uniform; one elected lane issues) ======
     uint32_t a_it = 0, b_it = 0, s_it = 0;
+    long long pw_a = 0, pw_b = 0, p_boxes = 0;
+    const long long p_t0 = clock64();
     for (;;) {
       const uint32_t ss = s_it % kSched;
       mbar_wait(&ctl->sched_empty[ss], ((s_it / kSched) & 1) ^ 1);
@@ -332,7 +335,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           const bool last_pass = (c == P.nchunk - 1) & (kw == last_kw);
           // all weights of this (chunk, kw): resident while the group's live boxes stream through
           const uint32_t sb = b_it % kNB;
-          mbar_wait(&ctl->empty_b[sb], ((b_it / kNB) & 1) ^ 1);
+          { const long long t = clock64(); mbar_wait(&ctl->empty_b[sb], ((b_it / kNB) & 1) ^ 1); pw_b += clock64() - t; }
           if (elect_one()) {
             mbar_arrive_expect_tx(&ctl->full_b[sb], kBSlotBytes);
             bulk_load_1d(smem_b + sb * kBSlotBytes, P.wpack + (size_t)(c * 3 + kw) * kBSlotBytes, kBSlotBytes,
@@ -357,7 +360,8 @@ __global__ void __launch_bounds__(kThreads, 1)
               const uint32_t flags = (uint32_t)pi.nkd | new_pass | (fresh << kMsgFreshShift) |
                                      ((fresh << slot_lo) << kMsgWaitShift);
               const uint32_t sa = a_it % kNA;
-              mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+              { const long long t = clock64(); mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1); pw_a += clock64() - t; }
+              ++p_boxes;
               if (elect_one()) {
                 ctl->msg[sa] = make_uint4(flags, slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
                 mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
@@ -394,6 +398,10 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       __syncwarp();
     }
+    if (P.prof != nullptr && lane == 0) {
+      unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
+      o[0] = (unsigned long long)(clock64() - p_t0); o[1] = pw_a; o[2] = pw_b; o[3] = p_boxes;
+    }
   } else if (warp == 1) {
     // ============ MMA issuer: interprets the producer's messages (warp-uniform) ============
     uint32_t a_it = 0, b_it = 0;
@@ -401,9 +409,11 @@ __global__ void __launch_bounds__(kThreads, 1)
     const uint32_t a_lo0 = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (1u << 16);
     const uint32_t b_lo0 = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | (1u << 16);
     uint32_t b_lo_pass = b_lo0;
+    long long mw_a = 0, mw_b = 0, mw_acc = 0;
+    const long long m_t0 = clock64();
     for (;;) {
       const uint32_t sa = a_it % kNA;
-      mbar_wait(&ctl->full_a[sa], (a_it / kNA) & 1);
+      { const long long t = clock64(); mbar_wait(&ctl->full_a[sa], (a_it / kNA) & 1); mw_a += clock64() - t; }
       const uint4 msg = ctl->msg[sa];
       const uint32_t f = msg.x;
       if (f & kMsgNewPass) {
@@ -411,7 +421,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           if (elect_one()) umma_commit(&ctl->empty_b[(b_it - 1) % kNB]);
           __syncwarp();
         }
-        mbar_wait(&ctl->full_b[b_it % kNB], (b_it / kNB) & 1);
+        { const long long t = clock64(); mbar_wait(&ctl->full_b[b_it % kNB], (b_it / kNB) & 1); mw_b += clock64() - t; }
         b_lo_pass = b_lo0 + (b_it % kNB) * (kBSlotBytes >> 4);
         ++b_it;
       }
@@ -421,7 +431,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         while (wm) {
           const uint32_t s = __ffs(wm) - 1;
           wm &= wm - 1;
-          mbar_wait(&ctl->acc_empty[s], ((acc_phase >> s) & 1) ^ 1);
+          { const long long t = clock64(); mbar_wait(&ctl->acc_empty[s], ((acc_phase >> s) & 1) ^ 1); mw_acc += clock64() - t; }
         }
         acc_phase ^= wait_mask;
       }
@@ -471,6 +481,10 @@ __global__ void __launch_bounds__(kThreads, 1)
       ++a_it;
       if (f & kMsgEnd) break;
     }
+    if (P.prof != nullptr && lane == 0) {
+      unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
+      o[4] = (unsigned long long)(clock64() - m_t0); o[5] = mw_a; o[6] = mw_b; o[7] = mw_acc;
+    }
   } else {
     // ===================== epilogue (warps 2..9) =====================
     // Two warps per TMEM lane quadrant (a warp may only read lanes 32*(warp%4)..+31): warps 2..5 take
@@ -481,9 +495,11 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int hl = m / kTileW, wl = m % kTileW;
     const float* scale_h = ctl->scale + half * 32;
     uint32_t s_it = 0, acc_phase = 0;
+    long long ew_sched = 0, ew_acc = 0;
+    const long long e_t0 = clock64();
     for (;;) {
       const uint32_t ss = s_it % kSched;
-      mbar_wait(&ctl->sched_full[ss], (s_it / kSched) & 1);
+      { const long long t = clock64(); mbar_wait(&ctl->sched_full[ss], (s_it / kSched) & 1); ew_sched += clock64() - t; }
       const int g = ctl->sched[ss];
       __syncwarp();
       if (lane == 0) mbar_arrive(&ctl->sched_empty[ss]);
@@ -527,7 +543,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           const uint32_t slot = tp.slot0 + __popc(touched & ((1u << dout) - 1u));
           uint32_t r[32];
           if (has_acc) {
-            mbar_wait(&ctl->acc_full[slot], (acc_phase >> slot) & 1);
+            { const long long t = clock64(); mbar_wait(&ctl->acc_full[slot], (acc_phase >> slot) & 1); ew_acc += clock64() - t; }
             tc_fence_after_sync();
             tmem_ld_32x32b_x32(tmem_base + ((quad * 32) << 16) + slot * 64 + half * 32, r);
             tmem_ld_wait();
@@ -570,6 +586,10 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
       }
       acc_phase ^= used;
+    }
+    if (P.prof != nullptr && threadIdx.x == 64) {
+      unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
+      o[8] = (unsigned long long)(clock64() - e_t0); o[9] = ew_sched; o[10] = ew_acc;
     }
   }
 
@@ -781,6 +801,8 @@ EncodeTiledFn encode_tiled_fn() {
   return fn;
 }
 
+unsigned long long* g_debug_prof = nullptr;
+
 int out_depth(int Din, int stride_d, int pad_d) { return (Din + 2 * pad_d - 3) / stride_d + 1; }
 
 struct PlanLayout {
@@ -815,6 +837,11 @@ size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W) {
   if (B < 1 || H < 1 || W < 1 || W % kTileW != 0) return 0;
   return (size_t)B * ((H + kTileH - 1) / kTileH) * (W / kTileW);
 }
+
+/* Debug aid (not in the public header's contract): the next conv launches write per-CTA cycle counters
+ * into buf [148][16] u64: producer {total, wait empty_a, wait empty_b, boxes}, MMA issuer {total, wait
+ * full_a, wait full_b, wait acc_empty}, epilogue warp 2 {total, wait sched, wait acc_full}.  NULL: off. */
+void vn_conv3d_debug_profile(void* buf) { g_debug_prof = static_cast<unsigned long long*>(buf); }
 
 size_t vn_conv3d_packed_weight_bytes(int32_t cin) {
   if (cin != 64 && cin != 128) return 0;
@@ -972,6 +999,7 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
   P.sub = sub;
   P.out = y;
   P.hdr = hdr; P.groups = groups; P.tiles = tiles;
+  P.prof = g_debug_prof;
   for (int p = 0; p < kMaxPlanes; ++p) P.plane[p] = Q.plane[p];
 
   const int grid = n_tiles < sm_count() ? (int)n_tiles : sm_count();
