@@ -65,7 +65,7 @@ _NO_SPAN = _NoSpan()
 
 class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
-                 voxels_per_frame_capacity: int = 32768, fuse_voxel_features: bool = True,
+                 voxels_per_frame_capacity: int = 49152, fuse_voxel_features: bool = True,
                  skip_empty_boxes: bool = True, resident_outputs: bool = True):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
