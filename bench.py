@@ -133,6 +133,7 @@ def cpu_reference_sample(target, frames, sd, seconds_budget=20.0, max_frames=Non
     import torch
     from oracle import cpu_chain
 
+    torch.set_num_threads(max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
     cpu_chain.front_end_cpu(frames[:1], sd, target)  # warm-up (thread pools, oneDNN primitives)
     times, stage_acc, n = [], {}, 0
     t_start = time.perf_counter()
@@ -156,6 +157,9 @@ def run_reference(args, rank, world):
         return
     import torch
     from oracle import model_torch as OM
+
+    # torchrun exports OMP_NUM_THREADS=1; the CPU arm uses every host core it can get
+    torch.set_num_threads(max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
 
     target, batch, _, desc = CONFIGS[args.config]
     frames = make_frames(args.config, 0, min(batch, 4))
@@ -212,6 +216,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
+        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
         dist.init_process_group("nccl", device_id=dev)
 
     import voxelnet_pytorch_b200 as vn
@@ -411,7 +417,15 @@ def main():
             conv_roof.append(ent)
         for k in ("voxelize", "svfe", "scatter"):
             stage_roofline[k]["frac"] = stage_roofline[k]["achieved"] / stage_roofline[k]["peak"]
+        traffic = None
+        try:  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                traffic_tab = json.load(f)
+        except Exception:
+            traffic_tab = {}
         dom = max(range(3), key=lambda l: stages["conv%d" % (l + 1)])
+        if world == 1 and args.config in traffic_tab:
+            traffic = traffic_tab[args.config].get("conv%d" % (dom + 1))
         dk = conv_roof[dom]
         kind = dk["bound"]
         line = {
@@ -433,7 +447,8 @@ def main():
                             "per-frame voxel counts; the (B,128,H,W) tensor stays on the device for the RPN"},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
-                         "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": None,
+                         "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": traffic,
+                         "traffic_source": traffic_tab.get("source") if traffic is not None else None,
                          "peak_source": peaks["source"] + (" (bf16_tflops_sustained)" if kind == "tensor" else " (hbm_gbs)"),
                          "counts": "executed work: MMAs issued / blocks moved, decoded from the device-built plan; "
                                    "dense-equivalent %.0f TFLOP/s" % dk["dense_equivalent_tflops"],

@@ -149,3 +149,22 @@ def test_resident_outputs_are_bit_identical_over_a_frame_sequence(cuda_device, t
         load_state(fe.middle_net, sd2, "")
         fe.refresh_parameters()
     assert torch.equal(res.forward_frames(b), full.forward_frames(b))
+
+
+def test_frames_are_independent_units_including_an_empty_one(cuda_device):
+    """Size-independent property at full Car size: a batch [A, B, empty, C] gives, frame by frame and bit
+    for bit, what each frame gives alone (no stage couples frames: eval BatchNorm, per-frame voxelization,
+    no cross-batch term in the convolutions) - the property the multi-GPU sharding rests on.  The empty
+    frame yields the all-background output, equal to a frame whose points are all outside the crop."""
+    sd = OM.random_state_dict(18)
+    a, b, c = synth_frames(3, 120)
+    empty = np.zeros((0, 4), np.float32)
+    far = np.array([[500.0, 0.0, 0.0, 0.5], [np.nan, 1.0, 1.0, 0.1], [10.0, np.inf, 0.0, 0.2]], np.float32)
+    fe = _build(cuda_device, "Car", sd)
+    batch = fe.forward_frames([a, b, empty, c]).clone()
+    assert list(np.diff(fe.voxel_counts()))[2] == 0
+    single = _build(cuda_device, "Car", sd)
+    for i, f in enumerate([a, b, far, c]):
+        alone = single.forward_frames([f])
+        assert torch.equal(alone[0].view(torch.int32), batch[i].view(torch.int32)), "frame %d" % i
+    assert bool(torch.isfinite(batch).all())
