@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 3
+#define VN_ABI_VERSION 4
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -230,6 +230,36 @@ int vn_conv3d_mark_boxes(const int64_t* coords, int64_t K, const int32_t* n_voxe
                          int32_t D, int32_t H, int32_t W, int32_t n_layers,
                          const int32_t* stride_d_host, const int32_t* pad_d_host,
                          uint8_t* const* flags_host, vn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Training-mode BatchNorm (model.train(True), voxelnet/train.py:148): batch statistics.
+ * ------------------------------------------------------------------------------------------ */
+
+/* The raw convolution for a ConvMD in training mode (model.py:159): y_raw = conv(x) + bias as bf16
+ * NDHWC [B, Dout, H, W, 64], no BatchNorm, no ReLU; and, from the fp32 accumulators, the per-channel
+ * sums BatchNorm3d's batch statistics need: stats[0..63] += sum(y), stats[64..127] += sum(y^2) over all
+ * B*Dout*H*W positions (fp64, zeroed by the caller).  `ones` is a [64] vector of 1.0f.  box_flags /
+ * flag_opts as in vn_conv3d_bn_relu_fwd (only exact for a zero-background input: the first layer). */
+int vn_conv3d_raw_stats_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin,
+                            int32_t stride_d, int32_t pad_d, const void* packed_weight,
+                            const float* ones, const float* bias, void* y_raw, double* stats,
+                            uint8_t* box_flags, int32_t flag_opts, void* workspace,
+                            size_t workspace_bytes, vn_stream_t stream);
+
+/* BatchNorm3d + ReLU applied to a stored raw convolution output (model.py:161-165) with the folded
+ * per-channel scale/shift: out = relu(raw * scale[c] + shift[c]).  raw: bf16 [B, D, H, W, 64].
+ * out_mode 0: bf16 [B, D, H, W, 64] (may alias raw); out_mode 1: f32 [B, 64*D, H, W], channel = c*D + d
+ * (the reshape of model.py:262). */
+int vn_bn_relu_apply(const void* raw_bf16, int32_t B, int32_t D, int32_t H, int32_t W, const float* scale,
+                     const float* shift, int32_t out_mode, void* out, vn_stream_t stream);
+
+/* Batch statistics of the two VFE BatchNorm1d layers (model.py:72,76) over all K*T rows of feature
+ * [K, T, 7], pad rows included.  stage 1: sums[0..15] += sum relu(W1 x + b1), sums[16..31] += sum of
+ * squares.  stage 2 (s1, t1 = VFE-1's BN folded from its batch statistics): sums[0..63] / sums[64..127]
+ * likewise for relu(W2 [masked concat] + b2).  sums: fp64, zeroed by the caller. */
+int vn_svfe_batch_stats(const float* feature, int64_t K, int32_t T, const int32_t* n_voxels_dev,
+                        int32_t stage, const float* w1, const float* b1, const float* s1, const float* t1,
+                        const float* w2, const float* b2, double* sums, vn_stream_t stream);
 
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);

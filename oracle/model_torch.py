@@ -37,7 +37,19 @@ def grid_dims(target: str):
     return (10, 400, 352, 35) if target == "Car" else (10, 200, 240, 45)
 
 
-def _bn_eval(x, sd, prefix):
+def _bn_train(x, sd, prefix, new_stats):
+    """nn.BatchNorm in training mode (the reference trains with model.train(True), train.py:148): batch
+    statistics, momentum 0.1; the updated running statistics are written to `new_stats` (if a dict)."""
+    rm, rv = sd[prefix + "running_mean"].clone(), sd[prefix + "running_var"].clone()
+    y = F.batch_norm(x, rm, rv, sd[prefix + "weight"], sd[prefix + "bias"], training=True, momentum=0.1, eps=BN_EPS)
+    if new_stats is not None:
+        new_stats[prefix + "running_mean"], new_stats[prefix + "running_var"] = rm, rv
+    return y
+
+
+def _bn_eval(x, sd, prefix, training=False, new_stats=None):
+    if training:
+        return _bn_train(x, sd, prefix, new_stats)
     return F.batch_norm(
         x,
         sd[prefix + "running_mean"],
@@ -49,7 +61,7 @@ def _bn_eval(x, sd, prefix):
     )
 
 
-def vfe_layer(inputs: torch.Tensor, mask: torch.Tensor, sd: dict, prefix: str) -> torch.Tensor:
+def vfe_layer(inputs: torch.Tensor, mask: torch.Tensor, sd: dict, prefix: str, training=False, new_stats=None) -> torch.Tensor:
     """model.py:74-82.  inputs (K,T,cin) f32, mask (K,T,1) bool -> (K,T,cout) f32.
 
     Linear -> ReLU -> BatchNorm1d over channels (eval mode) -> max over ALL T rows (unmasked)
@@ -57,7 +69,7 @@ def vfe_layer(inputs: torch.Tensor, mask: torch.Tensor, sd: dict, prefix: str) -
     """
     T = inputs.shape[1]
     pw = F.relu(F.linear(inputs, sd[prefix + "fcn.0.weight"], sd[prefix + "fcn.0.bias"]))
-    pw = _bn_eval(pw.transpose(1, 2), sd, prefix + "bn.").transpose(1, 2)
+    pw = _bn_eval(pw.transpose(1, 2), sd, prefix + "bn.", training, new_stats).transpose(1, 2)
     agg = pw.max(dim=1, keepdim=True)[0]
     cat = torch.cat([pw, agg.expand(-1, T, -1)], dim=2)
     return cat * mask.expand(-1, -1, cat.shape[2]).float()
@@ -68,11 +80,11 @@ def feature_mask(feature: torch.Tensor) -> torch.Tensor:
     return feature.max(dim=2, keepdim=True)[0] != 0
 
 
-def svfe_voxelwise(feature: torch.Tensor, sd: dict) -> torch.Tensor:
+def svfe_voxelwise(feature: torch.Tensor, sd: dict, training=False, new_stats=None) -> torch.Tensor:
     """model.py:95-100: (sum K, T, 7) -> (sum K, 128)."""
     mask = feature_mask(feature)
-    x = vfe_layer(feature, mask, sd, "vfe_1.")
-    x = vfe_layer(x, mask, sd, "vfe_2.")
+    x = vfe_layer(feature, mask, sd, "vfe_1.", training, new_stats)
+    x = vfe_layer(x, mask, sd, "vfe_2.", training, new_stats)
     return x.max(dim=1)[0]
 
 
@@ -91,14 +103,15 @@ def feature_learning_net(feature: list, coordinate: list, sd: dict, target: str 
     return scatter_dense(vw, torch.cat(coordinate, dim=0), len(feature), target)
 
 
-def conv_md3(x: torch.Tensor, sd: dict, prefix: str, stride, padding) -> torch.Tensor:
+def conv_md3(x: torch.Tensor, sd: dict, prefix: str, stride, padding, training=False, new_stats=None) -> torch.Tensor:
     """model.py:158-167 for input_dim == 3: Conv3d(k=3) -> BatchNorm3d (eval) -> ReLU."""
     x = F.conv3d(x, sd[prefix + "conv.weight"], sd[prefix + "conv.bias"], stride=stride, padding=padding)
-    x = _bn_eval(x, sd, prefix + "batch_norm.")
+    x = _bn_eval(x, sd, prefix + "batch_norm.", training, new_stats)
     return F.relu(x)
 
 
-def middle_layers(dense: torch.Tensor, sd: dict, upto: int = 3, prefix: str = "middle_layer.") -> torch.Tensor:
+def middle_layers(dense: torch.Tensor, sd: dict, upto: int = 3, prefix: str = "middle_layer.", training=False,
+                  new_stats=None) -> torch.Tensor:
     """model.py:257-262: (B,D,H,W,C) -> permute -> 3 x ConvMD -> reshape (B,128,H,W).
 
     `upto` < 3 returns the NCDHW activation after that many layers (for per-layer checks).
@@ -106,7 +119,7 @@ def middle_layers(dense: torch.Tensor, sd: dict, upto: int = 3, prefix: str = "m
     B, _, H, W, _ = dense.shape
     x = dense.permute(0, 4, 1, 2, 3)
     for i, (_, _, stride, padding) in enumerate(MIDDLE_LAYERS[:upto]):
-        x = conv_md3(x, sd, "%s%d." % (prefix, i), stride, padding)
+        x = conv_md3(x, sd, "%s%d." % (prefix, i), stride, padding, training, new_stats)
     if upto < 3:
         return x
     return x.reshape((B, -1, H, W))

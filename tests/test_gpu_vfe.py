@@ -82,9 +82,11 @@ def test_feature_mask(cuda_device):
     assert got.dtype == torch.bool and torch.equal(got.cpu(), want)
 
 
-def test_train_mode_raises(cuda_device):
+def test_single_layer_train_mode_raises_and_points_to_the_net(cuda_device):
+    """VFELayer.forward alone implements eval BatchNorm only (its batch statistics need the statistics of
+    its own input rows; FeatureLearningNet does the two reduction passes)."""
     import voxelnet_pytorch_b200 as vn
 
-    net = vn.FeatureLearningNet().to(cuda_device).train()
+    layer = vn.VFELayer(7, 32).to(cuda_device).train()
     with pytest.raises(NotImplementedError):
-        net.voxelwise(torch.zeros((1, 35, 7), device=cuda_device))
+        layer(torch.zeros((1, 35, 7), device=cuda_device), torch.ones((1, 35, 1), dtype=torch.bool, device=cuda_device))

@@ -73,6 +73,33 @@ def test_model_oracle_matches_reference_modules(target):
         assert torch.allclose(OM.middle_layers(x, sd), want_mid, rtol=1e-5, atol=1e-5)
 
 
+def test_training_mode_oracle_matches_reference_modules():
+    """model.train(True) (train.py:148): batch-statistics BatchNorm in both nets, and the running statistics
+    they leave behind."""
+    sd = OM.random_state_dict(32)
+    pcl = np.fromfile(R.kitti_frame_path(4), dtype=np.float32).reshape(-1, 4)[::8]
+    vox = OV.pcl_to_voxels_fast(pcl, "Car")
+    feat = torch.from_numpy(vox["feature_buffer"][:300].copy())
+    coord = torch.from_numpy(np.pad(vox["coordinate_buffer"][:300], ((0, 0), (1, 0)), constant_values=0))
+    with R.ref_model_cfg("Car") as ref, torch.no_grad():
+        fnet = ref.model.FeatureLearningNet().train()
+        fnet.load_state_dict({k: v for k, v in sd.items() if k.startswith("vfe_")})
+        want = fnet([feat], [coord])
+        new = {}
+        got = OM.scatter_dense(OM.svfe_voxelwise(feat, sd, training=True, new_stats=new), coord, 1, "Car")
+        assert torch.allclose(got, want, rtol=1e-5, atol=1e-6)
+        for k, v in new.items():
+            assert torch.allclose(v, fnet.state_dict()[k], rtol=1e-6, atol=1e-7), k
+        mid = ref.model.MiddleConvNet().train()
+        mid.load_state_dict({k: v for k, v in sd.items() if k.startswith("middle_layer.")}, strict=False)
+        x = torch.randn((2, 10, 16, 24, 128), generator=torch.Generator().manual_seed(2))
+        want_mid = mid.middle_layer(x.permute(0, 4, 1, 2, 3)).reshape((2, -1, 16, 24))
+        new = {}
+        assert torch.allclose(OM.middle_layers(x, sd, training=True, new_stats=new), want_mid, rtol=1e-4, atol=1e-5)
+        for k, v in new.items():
+            assert torch.allclose(v, mid.state_dict()[k], rtol=1e-5, atol=1e-6), k
+
+
 def test_state_dict_names_match_reference():
     ref = R.load_reference()
     import voxelnet_pytorch_b200 as vn

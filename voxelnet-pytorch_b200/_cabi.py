@@ -14,7 +14,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 3
+VN_ABI_VERSION = 4
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 
@@ -57,6 +57,9 @@ PROTOTYPES = {
     "vn_conv3d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _i32, _p, _p, _i32, _p, _p, _sz, _p]),
     "vn_conv3d_fold_background": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vn_conv3d_mark_boxes": (C.c_int, [_p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
+    "vn_conv3d_raw_stats_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _sz, _p]),
+    "vn_bn_relu_apply": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p, _i32, _p, _p]),
+    "vn_svfe_batch_stats": (C.c_int, [_p, _i64, _i32, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p]),
     "vn_launch_count": (_i64, []),
 }
 

@@ -101,6 +101,7 @@ struct ConvParams {
   const TilePlan* tiles;
   PlaneInfo plane[kMaxPlanes];
   unsigned long long* prof;  // debug: [grid][16] cycle counters (vn_conv3d_debug_profile), or nullptr
+  double* stats;             // training kernel: [2][64] per-channel sum / sum of squares of the raw output
 };
 
 struct PlanParams {
@@ -131,8 +132,9 @@ struct Control {
   uint4 msg[kNA];  // one message per A stage, written by the producer before it arms full_a (see kMsg*)
   float scale[64];
   float sub[kSlots * 64];
-  float table[kMaxTableRows * 64];
+  alignas(16) float table[kMaxTableRows * 64];  // training kernel: rows 16..19 hold the CTA-level partial sums
 };
+__device__ __forceinline__ double* ctl_stat(Control* ctl) { return reinterpret_cast<double*>(&ctl->table[16 * 64]); }
 constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + (uint32_t)sizeof(Control);
 static_assert(kSmemBytes <= 232448, "shared memory budget (227 KB)");
 
@@ -253,6 +255,11 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
 // ---------------------------------------------------------------------------------------------
 // The convolution.
 // ---------------------------------------------------------------------------------------------
+// kTrain = false: y = relu(acc*scale + shift) - sub (inference, BatchNorm folded).
+// kTrain = true:  y = acc*scale + shift (the raw convolution: scale = 1, shift = bias) stored as bf16, and the
+//                 per-channel sum / sum of squares of the fp32 values accumulated into P.stats - the batch
+//                 statistics BatchNorm3d needs in training mode (model.py:153,161-162).
+template <bool kTrain>
 __global__ void __launch_bounds__(kThreads, 1)
     k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ ConvParams P) {
   extern __shared__ uint8_t smem_raw[];
@@ -276,6 +283,7 @@ __global__ void __launch_bounds__(kThreads, 1)
   if (threadIdx.x >= 64) {
     const int t = threadIdx.x - 64;  // 0..255
     if (t < 64) ctl->scale[t] = P.scale[t];
+    if (kTrain && t < 128) ctl_stat(ctl)[t] = 0.0;
     const int nrow = P.nvar * P.Dout;
     for (int i = t; i < nrow * 64; i += 256) ctl->table[i] = P.table_plain ? P.table[i & 63] : P.table[i];
     for (int i = t; i < P.Dout * 64; i += 256) ctl->sub[i] = P.sub != nullptr ? P.sub[i] : 0.0f;
@@ -495,6 +503,9 @@ __global__ void __launch_bounds__(kThreads, 1)
     const int hl = m / kTileW, wl = m % kTileW;
     const float* scale_h = ctl->scale + half * 32;
     uint32_t s_it = 0, acc_phase = 0;
+    float st_s[kTrain ? 32 : 1], st_q[kTrain ? 32 : 1];
+#pragma unroll
+    for (int j = 0; j < (kTrain ? 32 : 1); ++j) { st_s[j] = 0.0f; st_q[j] = 0.0f; }
     long long ew_sched = 0, ew_acc = 0;
     const long long e_t0 = clock64();
     for (;;) {
@@ -527,7 +538,7 @@ __global__ void __launch_bounds__(kThreads, 1)
         for (int dout = 0; dout < P.Dout; ++dout) {
           const bool has_acc = (touched >> dout) & 1;  // else: no live box reached this accumulator
           if (!has_acc && !((tp.restore >> dout) & 1)) continue;  // the block already holds the layer background
-          if (!has_acc && P.out_mode == 0 && tile_interior && ctl->row_zero[dout]) {
+          if (!kTrain && !has_acc && P.out_mode == 0 && tile_interior && ctl->row_zero[dout]) {
             // nothing but background in reach and the layer stores deviations: the 16 KB block is zero.
             // This warp clears tile rows 4*quad + 2*half, +1 (1 KB each, contiguous).
             __nv_bfloat16* dst0 = reinterpret_cast<__nv_bfloat16*>(P.out) +
@@ -559,9 +570,18 @@ __global__ void __launch_bounds__(kThreads, 1)
             const float* shift_row = ctl->table + (variant * P.Dout + dout) * 64 + half * 32;
             const float* sub_row = ctl->sub + dout * 64 + half * 32;
             float v[32];
+            if (kTrain) {
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              v[j] = fmaxf(fmaf(__uint_as_float(r[j]), scale_h[j], shift_row[j]), 0.0f) - sub_row[j];
+              for (int j = 0; j < 32; ++j) {
+                v[j] = fmaf(__uint_as_float(r[j]), scale_h[j], shift_row[j]);
+                st_s[j] += v[j];
+                st_q[j] = fmaf(v[j], v[j], st_q[j]);
+              }
+            } else {
+#pragma unroll
+              for (int j = 0; j < 32; ++j)
+                v[j] = fmaxf(fmaf(__uint_as_float(r[j]), scale_h[j], shift_row[j]), 0.0f) - sub_row[j];
+            }
             if (P.out_mode == 0) {
               __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
                                    ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32;
@@ -591,6 +611,13 @@ __global__ void __launch_bounds__(kThreads, 1)
       unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
       o[8] = (unsigned long long)(clock64() - e_t0); o[9] = ew_sched; o[10] = ew_acc;
     }
+    if (kTrain) {
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        atomicAdd(&ctl_stat(ctl)[half * 32 + j], (double)st_s[j]);
+        atomicAdd(&ctl_stat(ctl)[64 + half * 32 + j], (double)st_q[j]);
+      }
+    }
   }
 
   tc_fence_before_sync();
@@ -599,6 +626,7 @@ __global__ void __launch_bounds__(kThreads, 1)
     tc_fence_after_sync();
     tmem_dealloc(tmem_base, kSlots * 64);
   }
+  if (kTrain && threadIdx.x >= 64 && threadIdx.x < 64 + 128) atomicAdd(&P.stats[threadIdx.x - 64], ctl_stat(ctl)[threadIdx.x - 64]);
 }
 
 // Weight image.  Depth taps are grouped into "kd classes" that can be valid for the same input plane:
@@ -912,11 +940,11 @@ int vn_conv3d_mark_boxes(const int64_t* coords, int64_t K, const int32_t* n_voxe
   return VN_OK;
 }
 
-int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
-                          int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
-                          int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
-                          int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
-                          vn_stream_t stream) {
+static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
+                       int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
+                       int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
+                       int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
+                       vn_stream_t stream, double* stats) {
   VN_REQUIRE(x && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
@@ -1003,10 +1031,35 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
   for (int p = 0; p < kMaxPlanes; ++p) P.plane[p] = Q.plane[p];
 
   const int grid = n_tiles < sm_count() ? (int)n_tiles : sm_count();
-  VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-  k_conv3d_bn_relu<<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+  P.stats = stats;
+  if (stats != nullptr) {
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<true><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+  } else {
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+  }
   VN_LAUNCH_CHECK("k_conv3d_bn_relu");
   return VN_OK;
+}
+
+int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
+                          int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
+                          int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
+                          int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
+                          vn_stream_t stream) {
+  return conv_launch(x, B, Din, H, W, cin, stride_d, pad_d, packed_weight, scale, shift_table, n_variants, sub, out_mode, y,
+                     box_flags, flag_opts, out_state, workspace, workspace_bytes, stream, nullptr);
+}
+
+int vn_conv3d_raw_stats_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
+                            int32_t pad_d, const void* packed_weight, const float* ones, const float* bias, void* y_raw,
+                            double* stats, uint8_t* box_flags, int32_t flag_opts, void* workspace,
+                            size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(stats != nullptr && ones != nullptr && bias != nullptr, "conv3d_raw_stats: null pointer");
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(stats) & 7) == 0, "conv3d_raw_stats: stats must be 8-byte aligned");
+  return conv_launch(x, B, Din, H, W, cin, stride_d, pad_d, packed_weight, ones, bias, 0, nullptr, 0, y_raw, box_flags,
+                     flag_opts, nullptr, workspace, workspace_bytes, stream, stats);
 }
 
 }  // extern "C"

@@ -13,8 +13,15 @@ Mirrors (same class names, constructor arguments, forward signatures, parameter 
 Parameters live in ordinary nn.Linear / nn.BatchNorm1d / nn.Conv3d / nn.BatchNorm3d containers so
 that a reference `state_dict()` loads by name (`vfe_1.fcn.0.weight`, `vfe_1.bn.running_mean`,
 `middle_layer.0.conv.weight`, `middle_layer.0.batch_norm.weight`, ...), but their forward is never
-called: every forward here launches kernels from the C ABI.  Only eval-mode BatchNorm (running
-statistics) is implemented; calling a module in training mode raises.
+called: every forward here launches kernels from the C ABI.
+
+BatchNorm: `.eval()` uses the running statistics (folded into the kernels' scale/shift).  `.train()`
+(the reference trains with model.train(True), train.py:148) normalises with the BATCH statistics -
+over all sum(K)*T rows incl. pad rows for the VFE layers, over B*D*H*W positions for the conv layers -
+and updates running_mean / running_var / num_batches_tracked exactly as nn.BatchNorm does
+(momentum 0.1, unbiased variance).  The training-mode FORWARD is implemented for `FeatureLearningNet`
+and `MiddleConvNet`; the backward kernels are not built yet, so outputs carry no
+autograd graph.
 """
 from __future__ import annotations
 
@@ -33,11 +40,29 @@ def _fold_bn(bn: nn.modules.batchnorm._BatchNorm):
     return scale.float().contiguous(), shift.float().contiguous()
 
 
+def _fold_batch_stats(bn: nn.modules.batchnorm._BatchNorm, sums: torch.Tensor, count: int):
+    """Training-mode BN from per-channel (sum, sum of squares) over `count` elements: returns the folded
+    (scale, shift) and updates the running statistics like nn.BatchNorm (momentum, unbiased variance).
+    A handful of 16/64-element tensor operations on the device - no host synchronisation."""
+    mean = sums[0] / count
+    var = (sums[1] / count - mean * mean).clamp_min(0.0)  # biased: what the normalisation uses
+    scale = bn.weight.detach().double() / torch.sqrt(var + bn.eps)
+    shift = bn.bias.detach().double() - mean * scale
+    with torch.no_grad():
+        if bn.track_running_stats and bn.running_mean is not None:
+            bn.num_batches_tracked += 1
+            m = bn.momentum if bn.momentum is not None else 1.0 / float(bn.num_batches_tracked)
+            unbiased = var * (count / max(count - 1, 1))
+            bn.running_mean.mul_(1 - m).add_(mean.to(bn.running_mean.dtype), alpha=m)
+            bn.running_var.mul_(1 - m).add_(unbiased.to(bn.running_var.dtype), alpha=m)
+    return scale.float().contiguous(), shift.float().contiguous()
+
+
 def _require_eval(module: nn.Module) -> None:
     if module.training:
         raise NotImplementedError(
-            "%s: only eval-mode BatchNorm is implemented on the B200 path (training statistics are "
-            "listed as 'next' in DESIGN.md); call .eval() first" % type(module).__name__
+            "%s: this entry point implements eval-mode BatchNorm only; training-mode batch statistics are "
+            "implemented by FeatureLearningNet.forward / voxelwise and ConvMD / MiddleConvNet.forward" % type(module).__name__
         )
 
 
@@ -59,7 +84,7 @@ class VFELayer(nn.Module):
         return lin.weight.detach().contiguous(), lin.bias.detach().contiguous(), scale, shift
 
     def forward(self, inputs, mask):
-        _require_eval(self)
+        _require_eval(self)  # a single layer in training mode needs the statistics of its own input; use FeatureLearningNet
         return ops.vfe_layer_fwd(inputs.contiguous(), mask, *self.folded())
 
 
@@ -73,10 +98,27 @@ class FeatureLearningNet(nn.Module):
         self.vfe_1 = VFELayer(7, 32)
         self.vfe_2 = VFELayer(32, 128)
 
+    def batch_folded(self, feature: torch.Tensor):
+        """Training mode: both VFE BatchNorms folded from the statistics of THIS batch (all K*T rows, pads
+        included - SURVEY F6); updates the running statistics.  Two reduction passes: VFE-2's input depends
+        on VFE-1's normalised output."""
+        K, T, _ = feature.shape
+        l1, l2 = self.vfe_1.fcn[0], self.vfe_2.fcn[0]
+        w1, b1 = l1.weight.detach().contiguous(), l1.bias.detach().contiguous()
+        w2, b2 = l2.weight.detach().contiguous(), l2.bias.detach().contiguous()
+        s1, t1 = _fold_batch_stats(self.vfe_1.bn, ops.svfe_batch_stats(feature, 1, w1, b1), K * T)
+        s2, t2 = _fold_batch_stats(self.vfe_2.bn, ops.svfe_batch_stats(feature, 2, w1, b1, s1, t1, w2, b2), K * T)
+        return (w1, b1, s1, t1), (w2, b2, s2, t2)
+
     def voxelwise(self, feature: torch.Tensor, out=None, n_voxels_dev=None) -> torch.Tensor:
         """model.py:95-100 as one fused kernel: (K,T,7) -> (K,128)."""
-        _require_eval(self)
-        return ops.svfe_fused_fwd(feature, self.vfe_1.folded(), self.vfe_2.folded(), out=out, n_voxels_dev=n_voxels_dev)
+        if self.training:
+            if n_voxels_dev is not None:
+                raise NotImplementedError("training-mode statistics need the exact K (pass feature[:K])")
+            p1, p2 = self.batch_folded(feature)
+        else:
+            p1, p2 = self.vfe_1.folded(), self.vfe_2.folded()
+        return ops.svfe_fused_fwd(feature, p1, p2, out=out, n_voxels_dev=n_voxels_dev)
 
     def forward(self, feature: list, coordinate: list):
         bs = len(feature)
@@ -129,7 +171,12 @@ class ConvMD(nn.Module):
         return self._packed, scale, shift
 
     def forward_ndhwc(self, x_bf16, final: bool = False, out=None):
-        _require_eval(self)
+        if self.training:  # model.py:159-165 with batch statistics: raw conv (+ sums) -> fold -> BN + ReLU
+            packed, _, _ = self.folded()
+            raw, sums = ops.conv3d_raw_stats_fwd(x_bf16, packed, self.conv.bias.detach(), self.stride[0], self.padding[0])
+            B, Dout, H, W, _ = raw.shape
+            scale, shift = _fold_batch_stats(self.batch_norm, sums, B * Dout * H * W)
+            return ops.bn_relu_apply(raw, scale, shift, final=final, out=out if final else raw)
         packed, scale, shift = self.folded()
         return ops.conv3d_bn_relu_fwd(x_bf16, packed, scale, shift, self.stride[0], self.padding[0], final=final, out=out)
 

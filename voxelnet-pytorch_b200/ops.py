@@ -397,3 +397,70 @@ def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, str
         "executed_flops": int(flops), "a_bytes": int(boxes * nchunk * 18432),
         "live_tile_planes": live_planes, "unique_input_bytes": int(live_planes * 128 * cin * 2),
     }
+
+
+# ---------------------------------------------------------------------------------------------
+# training-mode BatchNorm (batch statistics)
+# ---------------------------------------------------------------------------------------------
+def svfe_batch_stats(feature, stage: int, w1, b1, s1=None, t1=None, w2=None, b2=None, n_voxels_dev=None) -> torch.Tensor:
+    """Sums for the batch statistics of VFE-1 (stage 1 -> (2,16) f64) or VFE-2 (stage 2 -> (2,64) f64) over all
+    K*T rows of feature (K,T,7): row 0 = sum of relu(Linear), row 1 = sum of squares (model.py:75-76)."""
+    _require_cuda(feature, w1, b1, s1, t1, w2, b2)
+    _contig(feature, torch.float32)
+    K, T, cin = feature.shape
+    if cin != 7:
+        raise RuntimeError("svfe_batch_stats expects 7 input features per point")
+    units = 16 if stage == 1 else 64
+    sums = torch.zeros((2, units), dtype=torch.float64, device=feature.device)
+    f32 = lambda t: None if t is None else _ptr(_contig(t, torch.float32))
+    with torch.cuda.device(feature.device):
+        check(
+            _cabi.lib().vn_svfe_batch_stats(_ptr(feature), K, T, _ptr(n_voxels_dev), stage, f32(w1), f32(b1), f32(s1), f32(t1),
+                                            f32(w2), f32(b2), _ptr(sums), _stream()),
+            "vn_svfe_batch_stats",
+        )
+    return sums
+
+
+def conv3d_raw_stats_fwd(x, packed_weight, bias, stride_d: int, pad_d: int, out=None, box_flags=None,
+                         consume_flags: bool = False, workspace=None):
+    """Training-mode ConvMD, first half (model.py:159): x (B,Din,H,W,cin) bf16 -> (raw (B,Dout,H,W,64) bf16 =
+    conv(x)+bias, sums (2,64) f64 = per-channel sum / sum of squares of the fp32 raw output)."""
+    _require_cuda(x, packed_weight, bias, box_flags, workspace)
+    _contig(x, torch.bfloat16)
+    B, Din, H, W, cin = x.shape
+    Dout = conv3d_out_depth(Din, stride_d, pad_d)
+    if out is None:
+        out = torch.empty((B, Dout, H, W, 64), dtype=torch.bfloat16, device=x.device)
+    if workspace is None:
+        workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
+    ones = torch.ones(64, dtype=torch.float32, device=x.device)
+    sums = torch.zeros((2, 64), dtype=torch.float64, device=x.device)
+    opts = _cabi.VN_CONV_FLAGS_CONSUME if consume_flags else 0
+    with torch.cuda.device(x.device):
+        check(
+            _cabi.lib().vn_conv3d_raw_stats_fwd(_ptr(x), B, Din, H, W, cin, stride_d, pad_d, _ptr(packed_weight), _ptr(ones),
+                                                _ptr(_contig(bias, torch.float32)), _ptr(out), _ptr(sums), _ptr(box_flags), opts,
+                                                _ptr(workspace), workspace.numel(), _stream()),
+            "vn_conv3d_raw_stats_fwd",
+        )
+    return out, sums
+
+
+def bn_relu_apply(raw, scale, shift, final: bool = False, out=None):
+    """Training-mode ConvMD, second half (model.py:161-165): relu(raw*scale+shift).  raw (B,D,H,W,64) bf16 ->
+    bf16 same shape (in place when out is raw), or with final=True the (B, 64*D, H, W) f32 of model.py:262."""
+    _require_cuda(raw, scale, shift, out)
+    _contig(raw, torch.bfloat16)
+    B, D, H, W, Cc = raw.shape
+    if Cc != 64:
+        raise RuntimeError("bn_relu_apply expects 64 channels")
+    if out is None:
+        out = torch.empty((B, 64 * D, H, W), dtype=torch.float32, device=raw.device) if final else torch.empty_like(raw)
+    with torch.cuda.device(raw.device):
+        check(
+            _cabi.lib().vn_bn_relu_apply(_ptr(raw), B, D, H, W, _ptr(_contig(scale, torch.float32)),
+                                         _ptr(_contig(shift, torch.float32)), 1 if final else 0, _ptr(out), _stream()),
+            "vn_bn_relu_apply",
+        )
+    return out
