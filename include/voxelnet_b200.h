@@ -261,6 +261,13 @@ int vn_svfe_batch_stats(const float* feature, int64_t K, int32_t T, const int32_
                         int32_t stage, const float* w1, const float* b1, const float* s1, const float* t1,
                         const float* w2, const float* b2, double* sums, vn_stream_t stream);
 
+/* Weight gradient of a middle layer (autograd of nn.Conv3d, model.py:145-151 / train.py:149), bf16 operands on
+ * tcgen05 with fp32 accumulation:  x [B, Din, H, W, cin] bf16 (the layer input), dy [B, Dout, H, W, 64] bf16 (the
+ * gradient of the raw convolution output).  dw_taps [27][cin][64] f32, tap = (kd*3 + kh)*3 + kw, is ACCUMULATED
+ * into (zero it first):  dw_taps[tap][c][n] += sum_pos dy[pos][n] * x[pos + tap][c]. */
+int vn_conv3d_wgrad(const void* x, const void* dy, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin,
+                    int32_t stride_d, int32_t pad_d, float* dw_taps, vn_stream_t stream);
+
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);
 
