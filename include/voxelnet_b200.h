@@ -261,6 +261,15 @@ int vn_svfe_batch_stats(const float* feature, int64_t K, int32_t T, const int32_
                         int32_t stage, const float* w1, const float* b1, const float* s1, const float* t1,
                         const float* w2, const float* b2, double* sums, vn_stream_t stream);
 
+/* Data gradient of a middle layer with 64 input channels (layers 2 and 3): dx [B, Din_fwd, H, W, 64] bf16 from
+ * dy [B, Dout_fwd, H, W, 64] bf16 - the forward tcgen05 kernel run on the transposed depth geometry.
+ * packed_weight_t = vn_conv3d_pack_weights(W.flip(kd,kh,kw).transpose(0,1), cin 64, stride_d 1).  ones / zeros:
+ * [64] f32 vectors; stats_scratch: [128] f64 scratch (contents undefined afterwards). */
+int vn_conv3d_dgrad(const void* dy, int32_t B, int32_t Dout_fwd, int32_t H, int32_t W, int32_t Din_fwd,
+                    int32_t stride_d, int32_t pad_d, const void* packed_weight_t, const float* ones,
+                    const float* zeros, void* dx, double* stats_scratch, void* workspace,
+                    size_t workspace_bytes, vn_stream_t stream);
+
 /* Weight gradient of a middle layer (autograd of nn.Conv3d, model.py:145-151 / train.py:149), bf16 operands on
  * tcgen05 with fp32 accumulation:  x [B, Din, H, W, cin] bf16 (the layer input), dy [B, Dout, H, W, 64] bf16 (the
  * gradient of the raw convolution output).  dw_taps [27][cin][64] f32, tap = (kd*3 + kh)*3 + kw, is ACCUMULATED

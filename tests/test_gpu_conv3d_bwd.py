@@ -30,3 +30,24 @@ def test_wgrad_matches_autograd(cuda_device, idx, Din, H, W):
     got = ops.conv3d_wgrad(x.to(cuda_device).to(torch.bfloat16), dy.to(cuda_device).to(torch.bfloat16), stride[0], padding[0]).cpu()
     err = float((got - want).abs().max() / want.abs().max())
     assert got.shape == want.shape and err < 2e-4, err
+
+
+@pytest.mark.parametrize("idx,Din,H,W", [(1, 5, 24, 16), (2, 3, 40, 24), (2, 3, 17, 8)])
+def test_dgrad_matches_autograd(cuda_device, idx, Din, H, W):
+    """dX of layers 2 and 3 (64 input channels): the forward kernel on the transposed depth geometry."""
+    from voxelnet_pytorch_b200 import ops
+
+    cin, _, stride, padding = OM.MIDDLE_LAYERS[idx]
+    g = torch.Generator().manual_seed(50 + idx)
+    B = 2
+    Dout = (Din + 2 * padding[0] - 3) // stride[0] + 1
+    w = _bf16_exact((64, cin, 3, 3, 3), g, 0.05)
+    dy = _bf16_exact((B, Dout, H, W, 64), g)
+    x = torch.zeros((B, cin, Din, H, W), requires_grad=True)
+    y = F.conv3d(x, w, None, stride=stride, padding=padding)
+    y.backward(dy.permute(0, 4, 1, 2, 3))
+    want = x.grad.permute(0, 2, 3, 4, 1)
+    packed = ops.conv3d_pack_weights_dgrad(w.to(cuda_device))
+    got = ops.conv3d_dgrad(dy.to(cuda_device).to(torch.bfloat16), packed, Din, stride[0], padding[0]).float().cpu()
+    err = float((got - want).abs().max() / want.abs().max())
+    assert got.shape == want.shape and err < 6e-3, err  # bf16 storage of dx

@@ -60,6 +60,7 @@ PROTOTYPES = {
     "vn_conv3d_raw_stats_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _sz, _p]),
     "vn_bn_relu_apply": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p, _i32, _p, _p]),
     "vn_svfe_batch_stats": (C.c_int, [_p, _i64, _i32, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "vn_conv3d_dgrad": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vn_conv3d_wgrad": (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p]),
     "vn_launch_count": (_i64, []),
 }

@@ -813,6 +813,31 @@ int plan_planes(Params& P, int stride_d, int pad_d) {
   return 0;
 }
 
+// Transposed depth geometry (the data gradient of a forward layer with depth stride s, padding pad): plane d'
+// of dY feeds dX planes p = d'*s - pad + kd, kd = 0..2 ascending - consecutive, so the taps are fused along N like
+// the forward's.  Weights: the stride-1 image of W' = W.flip(kd,kh,kw).transpose(0,1) (tile j of the single kd
+// class holds W'[kd' = 2-j] = W[kd = j]).
+template <typename Params>
+int plan_planes_transposed(Params& P, int stride_d, int pad_d) {
+  for (int p = 0; p < kMaxPlanes; ++p) P.plane[p] = PlaneInfo{0, 0, 0, 0};
+  for (int d = 0; d < P.Din; ++d) {
+    int jfirst = -1, jlast = -1;
+    for (int j = 0; j < 3; ++j) {
+      const int p = d * stride_d - pad_d + j;
+      if (p < 0 || p >= P.Dout) continue;
+      if (jfirst < 0) jfirst = j;
+      jlast = j;
+    }
+    if (jfirst < 0) continue;
+    PlaneInfo& pi = P.plane[d];
+    pi.nkd = jlast - jfirst + 1;
+    pi.dmin = d * stride_d - pad_d + jfirst;
+    pi.woff = (uint32_t)jfirst * kBTapBytes;
+    pi.wstride = 3u * kBTapBytes;
+  }
+  return 0;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -944,7 +969,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                        int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
                        int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
                        int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
-                       vn_stream_t stream, double* stats) {
+                       vn_stream_t stream, double* stats, int32_t transposed_dout = 0) {
   VN_REQUIRE(x && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
@@ -954,8 +979,9 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   VN_REQUIRE(W % kTileW == 0 && W / kTileW <= kMaxTilesW, "conv3d: W=%d must be a multiple of %d, at most %d", W, kTileW,
              kTileW * kMaxTilesW);
   VN_REQUIRE(Din <= kMaxPlanes, "conv3d: Din=%d exceeds %d", Din, kMaxPlanes);
-  const int Dout = out_depth(Din, stride_d, pad_d);
-  VN_REQUIRE(Din + 2 * pad_d >= 3 && Dout >= 1 && Dout <= kSlots, "conv3d: Dout=%d outside [1,%d]", Dout, kSlots);
+  const int Dout = transposed_dout > 0 ? transposed_dout : out_depth(Din, stride_d, pad_d);
+  VN_REQUIRE((transposed_dout > 0 || Din + 2 * pad_d >= 3) && Dout >= 1 && Dout <= kSlots, "conv3d: Dout=%d outside [1,%d]",
+             Dout, kSlots);
   VN_REQUIRE(n_variants == 0 || n_variants == 1 || n_variants == 9, "conv3d: n_variants=%d (0: plain [64] shift, 1, 9)",
              n_variants);
   const int nvar = n_variants == 9 ? 9 : 1;
@@ -1006,7 +1032,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   Q.force_ring = (flag_opts & VN_CONV_FLAGS_BORDER_RING) ? 1 : 0;
   Q.out_state = out_state;
   Q.hdr = hdr; Q.groups = groups; Q.tiles = tiles;
-  if (plan_planes(Q, stride_d, pad_d) != 0) {
+  if ((transposed_dout > 0 ? plan_planes_transposed(Q, stride_d, pad_d) : plan_planes(Q, stride_d, pad_d)) != 0) {
     set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
     return VN_ERR_UNSUPPORTED;
   }
@@ -1050,6 +1076,15 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
                           vn_stream_t stream) {
   return conv_launch(x, B, Din, H, W, cin, stride_d, pad_d, packed_weight, scale, shift_table, n_variants, sub, out_mode, y,
                      box_flags, flag_opts, out_state, workspace, workspace_bytes, stream, nullptr);
+}
+
+int vn_conv3d_dgrad(const void* dy, int32_t B, int32_t Dout_fwd, int32_t H, int32_t W, int32_t Din_fwd, int32_t stride_d,
+                    int32_t pad_d, const void* packed_weight_t, const float* ones, const float* zeros, void* dx,
+                    double* stats_scratch, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(stats_scratch && ones && zeros, "conv3d_dgrad: null pointer");
+  VN_REQUIRE(Din_fwd >= 1 && Din_fwd <= kSlots, "conv3d_dgrad: Din_fwd=%d outside [1,%d]", Din_fwd, kSlots);
+  return conv_launch(dy, B, Dout_fwd, H, W, 64, stride_d, pad_d, packed_weight_t, ones, zeros, 0, nullptr, 0, dx, nullptr, 0,
+                     nullptr, workspace, workspace_bytes, stream, stats_scratch, Din_fwd);
 }
 
 int vn_conv3d_raw_stats_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,

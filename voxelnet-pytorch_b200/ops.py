@@ -483,3 +483,33 @@ def conv3d_wgrad(x, dy, stride_d: int, pad_d: int) -> torch.Tensor:
         check(_cabi.lib().vn_conv3d_wgrad(_ptr(x), _ptr(dy), B, Din, H, W, cin, stride_d, pad_d, _ptr(taps), _stream()),
               "vn_conv3d_wgrad")
     return taps.view(3, 3, 3, cin, 64).permute(4, 3, 0, 1, 2).contiguous()
+
+
+def conv3d_pack_weights_dgrad(weight) -> torch.Tensor:
+    """Packed bf16 image of the transposed, flipped filter for conv3d_dgrad (torch (64,64,3,3,3) f32 in)."""
+    w = weight.detach()
+    if w.shape[1] != 64:
+        raise RuntimeError("conv3d_dgrad supports layers with 64 input channels (the first layer's data gradient is the sparse gather)")
+    return conv3d_pack_weights(w.flip(2, 3, 4).transpose(0, 1).contiguous(), 1)
+
+
+def conv3d_dgrad(dy, packed_weight_t, din_fwd: int, stride_d: int, pad_d: int, workspace=None) -> torch.Tensor:
+    """dx (B,Din_fwd,H,W,64) bf16 from dy (B,Dout_fwd,H,W,64) bf16 (gradient of the raw convolution output)."""
+    _require_cuda(dy, packed_weight_t, workspace)
+    _contig(dy, torch.bfloat16)
+    B, Dout, H, W, Cc = dy.shape
+    if Cc != 64 or conv3d_out_depth(din_fwd, stride_d, pad_d) != Dout:
+        raise RuntimeError("dy shape %s does not match a layer with Din=%d stride_d=%d pad_d=%d" % (tuple(dy.shape), din_fwd, stride_d, pad_d))
+    dx = torch.empty((B, din_fwd, H, W, 64), dtype=torch.bfloat16, device=dy.device)
+    if workspace is None:
+        workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=dy.device)
+    ones = torch.ones(64, dtype=torch.float32, device=dy.device)
+    zeros = torch.zeros(64, dtype=torch.float32, device=dy.device)
+    scratch = torch.zeros(128, dtype=torch.float64, device=dy.device)
+    with torch.cuda.device(dy.device):
+        check(
+            _cabi.lib().vn_conv3d_dgrad(_ptr(dy), B, Dout, H, W, din_fwd, stride_d, pad_d, _ptr(packed_weight_t), _ptr(ones),
+                                        _ptr(zeros), _ptr(dx), _ptr(scratch), _ptr(workspace), workspace.numel(), _stream()),
+            "vn_conv3d_dgrad",
+        )
+    return dx
