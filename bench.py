@@ -36,6 +36,8 @@ CONFIGS = {
     "car16": ("Car", 16, {}, "VoxelNet Car forward, batch 16 synthetic KITTI-shaped frames (~120k pts) per GPU"),
     "ped16": ("Pedestrian", 16, {}, "VoxelNet Pedestrian/Cyclist forward, batch 16 per GPU"),
     "stress64": ("Car", 64, dict(azimuth_steps=4400, clutter=0.07), "dense-scene stress: ~300k pts/frame, batch 64 total"),
+    # BASELINE.json configs[4]: hot-path training step (forward + backward + gradient all-reduce + SGD)
+    "train16": ("Car", 16, {}, "VoxelNet Car training step of the hot path, batch 16 per GPU, NCCL gradient all-reduce"),
 }
 
 # dense-equivalent conv FLOPs per frame (padding taps counted)
@@ -187,6 +189,104 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+def run_train(args, rank, world, local_rank, dev):
+    """Training step of the hot path (BASELINE.json configs[4]; reference loop train.py:146-155):
+    model.train(True) forward with batch-statistics BatchNorm, backward from an upstream gradient of the
+    (B,128,H,W) tensor (a fixed random tensor standing for the stock-PyTorch RPN + loss, which are out of scope),
+    ONE flat all-reduce of the hot-path gradients over the ranks, clip_grad_norm_(5), SGD step, zero_grad.
+    Points are resident in HBM; per-rank batch is fixed (weak scaling)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+
+    import voxelnet_pytorch_b200 as vn
+    from voxelnet_pytorch_b200 import _cabi, sharding
+
+    target, batch, _, desc = CONFIGS[args.config]
+    torch.manual_seed(0)
+    fnet, mnet = vn.FeatureLearningNet(target).to(dev).train(), vn.MiddleConvNet().to(dev).train()
+    fe = vn.VoxelNetFrontEnd(fnet, mnet, target)
+    params = list(fnet.parameters()) + list(mnet.parameters())
+    opt = torch.optim.SGD(params, lr=1e-4)
+    sets = []
+    for seed in (None, 1000 * rank + 500):
+        fr = make_frames("car16", rank, batch, seed=seed)
+        sizes = [int(f.shape[0]) for f in fr]
+        offs = np.zeros(batch + 1, dtype=np.int32)
+        np.cumsum(sizes, out=offs[1:])
+        sets.append((torch.from_numpy(np.concatenate(fr, 0)).to(dev), torch.from_numpy(offs).to(dev), max(sizes)))
+    sets.sort(key=lambda x: -x[0].shape[0])
+    c = fe.cfg
+    dout = torch.randn((batch, 128, c.height, c.width), device=dev) * 1e-3
+    spans = {k: [] for k in ("forward", "backward", "allreduce", "optimizer")}
+
+    def ev():
+        e = torch.cuda.Event(enable_timing=True)
+        e.record()
+        return e
+
+    def step(i, record=False):
+        pts, offs, max_n = sets[i % 2]
+        t0 = ev()
+        out = fe.forward_points_train(pts, offs, max_n)
+        t1 = ev()
+        out.backward(dout)
+        t2 = ev()
+        n = sharding.allreduce_gradients(params)
+        t3 = ev()
+        torch.nn.utils.clip_grad_norm_(params, 5.0)
+        opt.step()
+        opt.zero_grad(set_to_none=False)
+        t4 = ev()
+        if record:
+            for k, a, b in (("forward", t0, t1), ("backward", t1, t2), ("allreduce", t2, t3), ("optimizer", t3, t4)):
+                spans[k].append((a, b))
+        return n
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(args.warmup):
+        step(i)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    step(0)
+    barrier()
+    wall0 = time.time()
+    launches0 = _cabi.launch_count()
+    e0 = ev()
+    for i in range(args.steps):
+        n_grad = step(i, record=True)
+    e1 = ev()
+    barrier()
+    wall1 = time.time()
+    launches = _cabi.launch_count() - launches0
+    clocks = sampler.stop(wall0, wall1)
+    ms = e0.elapsed_time(e1)
+    stage = {k: sum(a.elapsed_time(b) for a, b in v) / max(len(v), 1) for k, v in spans.items()}
+    ms_max = sharding.reduce_max([ms])[0]
+    voxels = fe.voxel_counts()[-1]
+    if rank != 0:
+        return
+    flops = sum(conv_flops_per_frame(c.depth, c.height, c.width))
+    line = {
+        "metric": "frames/s hot-path training step (Car cfg)", "value": world * batch * args.steps / (ms_max / 1e3), "unit": UNIT,
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": desc, "name": args.config, "batch_per_gpu": batch, "voxels_per_batch": voxels,
+                   "upstream_gradient": "fixed random (B,128,H,W) f32 tensor (RPN + loss are stock PyTorch, out of scope)",
+                   "optimizer": "SGD + clip_grad_norm_(5) (train.py:146-155)", "grad_elements_allreduced": n_grad,
+                   "l2_policy": "working set (dense grid, raw outputs, activations, gradients: > 15 GB) exceeds L2",
+                   "vfe": "fp32", "conv": "bf16 operands, fp32 accumulate (tcgen05 forward, dgrad, wgrad)"},
+        "stages_ms": stage,
+        "dense_equivalent_conv_tflops": 3 * flops * batch / (ms_max / args.steps / 1e3) / 1e12,
+        "clocks": clocks, "gpu_launches": launches,
+    }
+    print(json.dumps(line))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -225,6 +325,11 @@ def main():
     from voxelnet_pytorch_b200.pipeline import StageTimer
 
     target, batch_cfg, _, desc = CONFIGS[args.config]
+    if args.config == "train16":
+        run_train(args, rank, world, local_rank, dev)
+        if world > 1:
+            dist.destroy_process_group()
+        return
     if args.config == "stress64":  # strong-scaling stress: 64 frames in total, frame i -> rank i mod world
         from voxelnet_pytorch_b200 import sharding as _sh
 

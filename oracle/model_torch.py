@@ -161,3 +161,47 @@ def random_state_dict(seed: int = 0, nontrivial_bn: bool = True) -> dict:
         sd["middle_layer.%d.conv.bias" % i] = uniform((cout,), bound)
         bn("middle_layer.%d.batch_norm." % i, cout)
     return sd
+
+
+# ---------------------------------------------------------------------------------------------
+# bf16-emulating variant of the middle layers (checker for the GRADIENTS of the bf16 CUDA path)
+# ---------------------------------------------------------------------------------------------
+class _RoundBF16(torch.autograd.Function):
+    """x -> bf16 -> f32 with a straight-through gradient."""
+
+    @staticmethod
+    def forward(ctx, x):
+        return x.to(torch.bfloat16).float()
+
+    @staticmethod
+    def backward(ctx, g):
+        return g
+
+
+def middle_layers_bf16_emulated(dense: torch.Tensor, sd: dict, prefix: str = "middle_layer.", return_acts: bool = False):
+    """model.py:257-262 in training mode, fp32 arithmetic on values rounded to bf16 at the points where the CUDA
+    path stores bf16 (layer inputs, weights, the raw convolution output, the two intermediate activations).
+
+    Why it exists: against the plain fp32 oracle the forward differs by ~1e-2 of max, which flips the ReLU of the
+    few percent of elements that sit that close to zero; with a white-noise upstream gradient every flipped
+    element moves a gradient sum by O(1), so gradient errors of ~1e-1 of max against plain fp32 are rounding
+    noise, not bugs.  With the rounding points emulated the masks agree and the comparison is tight."""
+    rnd = _RoundBF16.apply
+    B, _, H, W, _ = dense.shape
+    x = rnd(dense).permute(0, 4, 1, 2, 3)
+    acts = []
+    for i, (_, _, stride, padding) in enumerate(MIDDLE_LAYERS):
+        p = "%s%d." % (prefix, i)
+        raw32 = F.conv3d(x, rnd(sd[p + "conv.weight"]), sd[p + "conv.bias"], stride=stride, padding=padding)
+        mean = raw32.mean(dim=(0, 2, 3, 4), keepdim=True)
+        var = raw32.var(dim=(0, 2, 3, 4), unbiased=False, keepdim=True)
+        scale = sd[p + "batch_norm.weight"].view(1, -1, 1, 1, 1) * torch.rsqrt(var + BN_EPS)
+        shift = sd[p + "batch_norm.bias"].view(1, -1, 1, 1, 1) - mean * scale
+        x = F.relu(rnd(raw32) * scale + shift)
+        if i < 2:
+            x = rnd(x)
+        if return_acts:
+            x.retain_grad()
+            acts.append(x)
+    out = x.reshape((B, -1, H, W))
+    return (out, acts) if return_acts else out

@@ -31,7 +31,13 @@ def _worker(rank, world, port, out_dir):
     counts = sharding.gather_ints(len(mine))
     allf = [None] * world
     dist.all_gather_object(allf, mine)
-    torch.save(dict(mine=mine, ms=ms, counts=counts, allf=allf), os.path.join(out_dir, "r%d.pt" % rank))
+    # training config: per-rank gradients of ragged shapes, one of them absent -> one flat all-reduce, averaged
+    params = [torch.nn.Parameter(torch.zeros(s)) for s in ((3, 4), (5,), (2, 2, 2))]
+    params[0].grad = torch.full((3, 4), float(rank + 1))
+    params[2].grad = torch.arange(8.0).view(2, 2, 2) * (rank + 1)
+    n = sharding.allreduce_gradients(params)
+    grads = [None if p.grad is None else p.grad.clone() for p in params]
+    torch.save(dict(mine=mine, ms=ms, counts=counts, allf=allf, n=n, grads=grads), os.path.join(out_dir, "r%d.pt" % rank))
     dist.destroy_process_group()
 
 
@@ -45,6 +51,10 @@ def test_sharding_world2(tmp_path):
     flat = sorted(r[0]["allf"][0] + r[0]["allf"][1])
     assert flat == list(range(64))                           # disjoint cover
     assert r[1]["mine"][:3] == [1, 3, 5]
+    for rr in r:  # mean over the two ranks: (1 + 2) / 2
+        assert rr["n"] == 20 and rr["grads"][1] is None
+        assert torch.equal(rr["grads"][0], torch.full((3, 4), 1.5))
+        assert torch.equal(rr["grads"][2], torch.arange(8.0).view(2, 2, 2) * 1.5)
 
 
 def test_sharding_single_process_and_ragged():
@@ -54,5 +64,8 @@ def test_sharding_single_process_and_ragged():
     assert sharding.shard_frames(3, 3, 4) == [3][:0] or sharding.shard_frames(3, 3, 4) == []
     assert sharding.reduce_max([1.5, 2.5]) == [1.5, 2.5]
     assert sharding.gather_ints(7) == [7]
+    p = torch.nn.Parameter(torch.zeros(2))
+    p.grad = torch.ones(2)
+    assert sharding.allreduce_gradients([p]) == 0 and torch.equal(p.grad, torch.ones(2))  # no group: untouched
     with pytest.raises(ValueError):
         sharding.shard_frames(4, 2, 2)

@@ -19,9 +19,11 @@ BatchNorm: `.eval()` uses the running statistics (folded into the kernels' scale
 (the reference trains with model.train(True), train.py:148) normalises with the BATCH statistics -
 over all sum(K)*T rows incl. pad rows for the VFE layers, over B*D*H*W positions for the conv layers -
 and updates running_mean / running_var / num_batches_tracked exactly as nn.BatchNorm does
-(momentum 0.1, unbiased variance).  The training-mode FORWARD is implemented for `FeatureLearningNet`
-and `MiddleConvNet`; the backward kernels are not built yet, so outputs carry no
-autograd graph.
+(momentum 0.1, unbiased variance).  In training mode `FeatureLearningNet` and `MiddleConvNet` build an autograd
+graph out of three kinds of nodes whose backward launches the library's gradient kernels (`_SVFETrainFn`,
+`_Conv1SparseTrainFn`, `_ConvTrainFn`): loss.backward() (train.py:149) fills `.grad` of every hot-path
+parameter.  The dense grid itself carries no gradient: the voxel-wise features reach the first conv layer's
+node through a side channel (`dense._vn_sparse`), and its data gradient is evaluated at the occupied cells only.
 """
 from __future__ import annotations
 
@@ -42,11 +44,12 @@ def _fold_bn(bn: nn.modules.batchnorm._BatchNorm):
 
 def _fold_batch_stats(bn: nn.modules.batchnorm._BatchNorm, sums: torch.Tensor, count: int):
     """Training-mode BN from per-channel (sum, sum of squares) over `count` elements: returns the folded
-    (scale, shift) and updates the running statistics like nn.BatchNorm (momentum, unbiased variance).
+    (scale, shift) plus (mean, invstd) for the backward, and updates the running statistics like nn.BatchNorm (momentum, unbiased variance).
     A handful of 16/64-element tensor operations on the device - no host synchronisation."""
     mean = sums[0] / count
     var = (sums[1] / count - mean * mean).clamp_min(0.0)  # biased: what the normalisation uses
-    scale = bn.weight.detach().double() / torch.sqrt(var + bn.eps)
+    invstd = torch.rsqrt(var + bn.eps)
+    scale = bn.weight.detach().double() * invstd
     shift = bn.bias.detach().double() - mean * scale
     with torch.no_grad():
         if bn.track_running_stats and bn.running_mean is not None:
@@ -55,7 +58,7 @@ def _fold_batch_stats(bn: nn.modules.batchnorm._BatchNorm, sums: torch.Tensor, c
             unbiased = var * (count / max(count - 1, 1))
             bn.running_mean.mul_(1 - m).add_(mean.to(bn.running_mean.dtype), alpha=m)
             bn.running_var.mul_(1 - m).add_(unbiased.to(bn.running_var.dtype), alpha=m)
-    return scale.float().contiguous(), shift.float().contiguous()
+    return scale.float().contiguous(), shift.float().contiguous(), mean.float().contiguous(), invstd.float().contiguous()
 
 
 def _require_eval(module: nn.Module) -> None:
@@ -64,6 +67,94 @@ def _require_eval(module: nn.Module) -> None:
             "%s: this entry point implements eval-mode BatchNorm only; training-mode batch statistics are "
             "implemented by FeatureLearningNet.forward / voxelwise and ConvMD / MiddleConvNet.forward" % type(module).__name__
         )
+
+
+# ---------------------------------------------------------------------------------------------
+# autograd nodes of the training path (backward = the library's gradient kernels)
+# ---------------------------------------------------------------------------------------------
+class _SVFETrainFn(torch.autograd.Function):
+    """feature (K,T,7) -> voxel-wise (K,128) with batch-statistics BatchNorm (model.py:95-100 in train mode)."""
+
+    @staticmethod
+    def forward(ctx, feature, w1, b1, g1, be1, w2, b2, g2, be2, net):
+        p1, p2 = net.batch_folded(feature)
+        bn1, bn2 = net._last_bn
+        vw = ops.svfe_fused_fwd(feature, p1, p2)
+        ctx.save_for_backward(feature, p1[0], p1[1], p2[0], p2[1], *bn1, *bn2)
+        return vw
+
+    @staticmethod
+    def backward(ctx, dvw):
+        feature, w1, b1, w2, b2, *bn = ctx.saved_tensors
+        g = ops.svfe_bwd(feature, dvw.contiguous().float(), w1, b1, w2, b2, bn[0:4], bn[4:8])
+        return None, g["w1"], g["b1"], g["gamma1"], g["beta1"], g["w2"], g["b2"], g["gamma2"], g["beta2"], None
+
+
+def _conv_train_forward(layer, x, final, out):
+    """raw conv (+ batch statistics in the epilogue) -> fold -> BN + ReLU into a separate buffer (the raw
+    output is kept for the backward)."""
+    packed, _, _ = layer.folded()
+    raw, sums = ops.conv3d_raw_stats_fwd(x, packed, layer.conv.bias.detach(), layer.stride[0], layer.padding[0])
+    B, Dout, H, W, _ = raw.shape
+    stats = _fold_batch_stats(layer.batch_norm, sums, B * Dout * H * W)
+    y = ops.bn_relu_apply(raw, stats[0], stats[1], final=final, out=out if final else None)
+    return y, raw, stats
+
+
+def _conv_train_backward(x, raw, stats, dy, final, stride_d, pad_d):
+    """-> (draw bf16, dW (64,cin,3,3,3) f32, dgamma, dbeta)."""
+    dy = dy.contiguous()
+    dy = dy.float() if final else dy.to(torch.bfloat16)
+    draw, dgamma, dbeta = ops.bn_relu_bwd(raw, dy, *stats, final=final)
+    dw = ops.conv3d_wgrad(x, draw, stride_d, pad_d)
+    return draw, dw, dgamma, dbeta
+
+
+class _ConvTrainFn(torch.autograd.Function):
+    """ConvMD in training mode on bf16 NDHWC (model.py:158-167).  The data gradient exists for the layers with
+    64 input channels; the first layer's goes through _Conv1SparseTrainFn."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, gamma, beta, layer, final):
+        y, raw, stats = _conv_train_forward(layer, x, final, None)
+        ctx.save_for_backward(x, raw, weight, *stats)
+        ctx.geom = (layer.stride[0], layer.padding[0], final)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, raw, weight, *stats = ctx.saved_tensors
+        stride_d, pad_d, final = ctx.geom
+        draw, dw, dgamma, dbeta = _conv_train_backward(x, raw, stats, dy, final, stride_d, pad_d)
+        dx = None
+        if ctx.needs_input_grad[0]:
+            if x.shape[-1] != 64:
+                raise RuntimeError("the first middle layer has no dense data gradient; feed it FeatureLearningNet's output")
+            dx = ops.conv3d_dgrad(draw, ops.conv3d_pack_weights_dgrad(weight), x.shape[1], stride_d, pad_d)
+        # the conv bias shifts the batch mean only: its gradient under batch-statistics BN is exactly zero
+        return dx, dw, torch.zeros_like(dgamma), dgamma, dbeta, None, None
+
+
+class _Conv1SparseTrainFn(torch.autograd.Function):
+    """to_dense (model.py:102-106) + first ConvMD in training mode.  `dense` already holds the scattered bf16
+    voxel-wise rows; the gradient flows to `vw` (K,128) through the occupied cells only."""
+
+    @staticmethod
+    def forward(ctx, vw, coords, dense, weight, bias, gamma, beta, layer):
+        y, raw, stats = _conv_train_forward(layer, dense, False, None)
+        ctx.save_for_backward(dense, raw, weight, coords, *stats)
+        ctx.geom = (layer.stride[0], layer.padding[0])
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        dense, raw, weight, coords, *stats = ctx.saved_tensors
+        stride_d, pad_d = ctx.geom
+        draw, dw, dgamma, dbeta = _conv_train_backward(dense, raw, stats, dy, False, stride_d, pad_d)
+        dvw = None
+        if ctx.needs_input_grad[0]:
+            dvw = ops.conv1_dgrad_gather(draw, ops.conv1_weight_taps(weight), coords, stride_d, pad_d)
+        return dvw, None, None, dw, torch.zeros_like(dgamma), dgamma, dbeta, None
 
 
 class VFELayer(nn.Module):
@@ -97,6 +188,9 @@ class FeatureLearningNet(nn.Module):
         self.target = target
         self.vfe_1 = VFELayer(7, 32)
         self.vfe_2 = VFELayer(32, 128)
+        # dtype of the dense grid `forward` returns: float32 is the reference's contract (model.py:102-106);
+        # bfloat16 is what the middle layers consume and saves the 2x larger buffer and its conversion
+        self.dense_dtype = torch.float32
 
     def batch_folded(self, feature: torch.Tensor):
         """Training mode: both VFE BatchNorms folded from the statistics of THIS batch (all K*T rows, pads
@@ -106,16 +200,20 @@ class FeatureLearningNet(nn.Module):
         l1, l2 = self.vfe_1.fcn[0], self.vfe_2.fcn[0]
         w1, b1 = l1.weight.detach().contiguous(), l1.bias.detach().contiguous()
         w2, b2 = l2.weight.detach().contiguous(), l2.bias.detach().contiguous()
-        s1, t1 = _fold_batch_stats(self.vfe_1.bn, ops.svfe_batch_stats(feature, 1, w1, b1), K * T)
-        s2, t2 = _fold_batch_stats(self.vfe_2.bn, ops.svfe_batch_stats(feature, 2, w1, b1, s1, t1, w2, b2), K * T)
-        return (w1, b1, s1, t1), (w2, b2, s2, t2)
+        bn1 = _fold_batch_stats(self.vfe_1.bn, ops.svfe_batch_stats(feature, 1, w1, b1), K * T)
+        s1, t1 = bn1[0], bn1[1]
+        bn2 = _fold_batch_stats(self.vfe_2.bn, ops.svfe_batch_stats(feature, 2, w1, b1, s1, t1, w2, b2), K * T)
+        self._last_bn = (bn1, bn2)  # (scale, shift, mean, invstd) of this batch, read by the backward node
+        return (w1, b1, s1, t1), (w2, b2, bn2[0], bn2[1])
 
     def voxelwise(self, feature: torch.Tensor, out=None, n_voxels_dev=None) -> torch.Tensor:
         """model.py:95-100 as one fused kernel: (K,T,7) -> (K,128)."""
         if self.training:
             if n_voxels_dev is not None:
                 raise NotImplementedError("training-mode statistics need the exact K (pass feature[:K])")
-            p1, p2 = self.batch_folded(feature)
+            l1, l2 = self.vfe_1, self.vfe_2
+            return _SVFETrainFn.apply(feature, l1.fcn[0].weight, l1.fcn[0].bias, l1.bn.weight, l1.bn.bias,
+                                      l2.fcn[0].weight, l2.fcn[0].bias, l2.bn.weight, l2.bn.bias, self)
         else:
             p1, p2 = self.vfe_1.folded(), self.vfe_2.folded()
         return ops.svfe_fused_fwd(feature, p1, p2, out=out, n_voxels_dev=n_voxels_dev)
@@ -126,9 +224,14 @@ class FeatureLearningNet(nn.Module):
         coordinate = torch.cat(coordinate, dim=0).contiguous()
         vw = self.voxelwise(feature)
         g = grid_config(self.target)
-        dense = torch.empty((bs, g.depth, g.height, g.width, 128), dtype=torch.float32, device=vw.device)
+        dense = torch.empty((bs, g.depth, g.height, g.width, 128), dtype=self.dense_dtype, device=vw.device)
         ops.fill_zero(dense)
-        ops.scatter_dense_f32(vw, coordinate, dense)
+        if self.dense_dtype == torch.bfloat16:
+            ops.scatter_dense_bf16(vw.detach(), coordinate, dense)
+        else:
+            ops.scatter_dense_f32(vw.detach(), coordinate, dense)
+        if vw.requires_grad:  # the gradient bypasses the dense grid: MiddleConvNet picks this up
+            dense._vn_sparse = (vw, coordinate)
         return dense
 
 
@@ -170,12 +273,20 @@ class ConvMD(nn.Module):
         shift = (self.conv.bias.detach().double() * scale.double() + bn_shift.double()).float().contiguous()
         return self._packed, scale, shift
 
-    def forward_ndhwc(self, x_bf16, final: bool = False, out=None):
+    def forward_ndhwc(self, x_bf16, final: bool = False, out=None, sparse=None):
         if self.training:  # model.py:159-165 with batch statistics: raw conv (+ sums) -> fold -> BN + ReLU
+            if torch.is_grad_enabled():
+                if sparse is not None:
+                    vw, coords = sparse
+                    return _Conv1SparseTrainFn.apply(vw, coords, x_bf16, self.conv.weight, self.conv.bias,
+                                                     self.batch_norm.weight, self.batch_norm.bias, self)
+                # (a caller-provided `out` is not used here: the node owns its output)
+                return _ConvTrainFn.apply(x_bf16, self.conv.weight, self.conv.bias, self.batch_norm.weight,
+                                          self.batch_norm.bias, self, final)
             packed, _, _ = self.folded()
             raw, sums = ops.conv3d_raw_stats_fwd(x_bf16, packed, self.conv.bias.detach(), self.stride[0], self.padding[0])
             B, Dout, H, W, _ = raw.shape
-            scale, shift = _fold_batch_stats(self.batch_norm, sums, B * Dout * H * W)
+            scale, shift, _, _ = _fold_batch_stats(self.batch_norm, sums, B * Dout * H * W)
             return ops.bn_relu_apply(raw, scale, shift, final=final, out=out if final else raw)
         packed, scale, shift = self.folded()
         return ops.conv3d_bn_relu_fwd(x_bf16, packed, scale, shift, self.stride[0], self.padding[0], final=final, out=out)
@@ -196,10 +307,11 @@ class MiddleConvNet(nn.Module):
         )
 
     def forward(self, x, out=None):
+        sparse = getattr(x, "_vn_sparse", None) if self.training else None
         if x.dtype != torch.bfloat16:
             x = x.to(torch.bfloat16)
         x = x.contiguous()
-        x = self.middle_layer[0].forward_ndhwc(x)
+        x = self.middle_layer[0].forward_ndhwc(x, sparse=sparse)
         x = self.middle_layer[1].forward_ndhwc(x)
         # the last layer writes fp32 straight into the (B, c*2+d, H, W) layout of model.py:262
         return self.middle_layer[2].forward_ndhwc(x, final=True, out=out)

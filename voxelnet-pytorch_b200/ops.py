@@ -513,3 +513,89 @@ def conv3d_dgrad(dy, packed_weight_t, din_fwd: int, stride_d: int, pad_d: int, w
             "vn_conv3d_dgrad",
         )
     return dx
+
+
+# ---------------------------------------------------------------------------------------------
+# backward of BatchNorm(batch statistics) + ReLU, of to_dense + conv-1 (sparse), and of the stacked VFE
+# ---------------------------------------------------------------------------------------------
+def bn_relu_bwd(raw, dy, scale, shift, mean, invstd, final: bool = False):
+    """Backward of relu(BatchNorm3d(raw)) in training mode (model.py:161-165).  raw (B,D,H,W,64) bf16; dy is the
+    gradient of the layer output: bf16 (B,D,H,W,64), or with final=True f32 (B,64*D,H,W) (model.py:262 layout).
+    Returns (draw (B,D,H,W,64) bf16 = gradient of the raw convolution output, dgamma (64,) f32, dbeta (64,) f32)."""
+    _require_cuda(raw, dy, scale, shift, mean, invstd)
+    _contig(raw, torch.bfloat16)
+    _contig(dy, torch.float32 if final else torch.bfloat16)
+    B, D, H, W, Cc = raw.shape
+    if Cc != 64:
+        raise RuntimeError("bn_relu_bwd expects 64 channels")
+    want = (B, 64 * D, H, W) if final else (B, D, H, W, 64)
+    if tuple(dy.shape) != want:
+        raise RuntimeError("dy must be %s, got %s" % (want, tuple(dy.shape)))
+    n = B * D * H * W
+    prm = torch.zeros((6, 64), dtype=torch.float32, device=raw.device)
+    prm[0], prm[1], prm[2], prm[3] = scale, shift, mean, invstd
+    sums = torch.zeros((2, 64), dtype=torch.float64, device=raw.device)
+    draw = torch.empty_like(raw)
+    mode = 1 if final else 0
+    with torch.cuda.device(raw.device):
+        check(_cabi.lib().vn_bn_relu_bwd(_ptr(raw), _ptr(dy), mode, B, D, H, W, _ptr(prm), 0, _ptr(sums), None, _stream()),
+              "vn_bn_relu_bwd(reduce)")
+        prm[4:6] = (sums / n).float()
+        check(_cabi.lib().vn_bn_relu_bwd(_ptr(raw), _ptr(dy), mode, B, D, H, W, _ptr(prm), 1, None, _ptr(draw), _stream()),
+              "vn_bn_relu_bwd(apply)")
+    return draw, sums[1].float(), sums[0].float()
+
+
+def conv1_weight_taps(weight) -> torch.Tensor:
+    """(64,128,3,3,3) f32 -> [27][64][128] f32 with the values the bf16 forward multiplied with."""
+    w = weight.detach().to(torch.bfloat16).float()
+    return w.permute(2, 3, 4, 0, 1).reshape(27, w.shape[0], w.shape[1]).contiguous()
+
+
+def conv1_dgrad_gather(draw, weight_taps, coords, stride_d: int, pad_d: int) -> torch.Tensor:
+    """Gradient of the (K,128) voxel-wise features through to_dense + the first conv layer: draw (B,Dr,H,W,64) bf16,
+    weight_taps from conv1_weight_taps, coords (K,4) i64 -> (K,128) f32."""
+    _require_cuda(draw, weight_taps, coords)
+    _contig(draw, torch.bfloat16), _contig(weight_taps, torch.float32), _contig(coords, torch.int64)
+    B, Dr, H, W, Cc = draw.shape
+    if Cc != 64 or tuple(weight_taps.shape) != (27, 64, 128):
+        raise RuntimeError("conv1_dgrad_gather: draw (B,Dr,H,W,64) and weight_taps (27,64,128) expected")
+    K = coords.shape[0]
+    dvw = torch.empty((K, 128), dtype=torch.float32, device=draw.device)
+    with torch.cuda.device(draw.device):
+        check(_cabi.lib().vn_conv1_dgrad_gather(_ptr(draw), _ptr(weight_taps), _ptr(coords), K, B, Dr, H, W, stride_d, pad_d,
+                                                _ptr(dvw), _stream()), "vn_conv1_dgrad_gather")
+    return dvw
+
+
+def svfe_bwd(feature, dvw, w1, b1, w2, b2, bn1, bn2) -> dict:
+    """Backward of the stacked VFE in training mode.  feature (K,T,7) f32, dvw (K,128) f32; bn1 / bn2 =
+    (scale, shift, mean, invstd) of the two batch-statistics BatchNorms as used by the forward.
+    Returns {'w1','b1','gamma1','beta1','w2','b2','gamma2','beta2'} gradients (f32)."""
+    _require_cuda(feature, dvw, w1, b1, w2, b2, *bn1, *bn2)
+    _contig(feature, torch.float32), _contig(dvw, torch.float32)
+    K, T, cin = feature.shape
+    if cin != 7 or tuple(dvw.shape) != (K, 128):
+        raise RuntimeError("svfe_bwd: feature (K,T,7) and dvw (K,128) expected")
+    dev = feature.device
+    p1 = torch.zeros((6, 16), dtype=torch.float32, device=dev)
+    p2 = torch.zeros((6, 64), dtype=torch.float32, device=dev)
+    for i in range(4):
+        p1[i], p2[i] = bn1[i], bn2[i]
+    acc = torch.zeros(2400, dtype=torch.float64, device=dev)
+    n = float(max(K * T, 1))
+    args = [_ptr(_contig(t, torch.float32)) for t in (w1, b1, w2, b2)]
+    with torch.cuda.device(dev):
+        def run(p):
+            check(_cabi.lib().vn_svfe_bwd(_ptr(feature), K, T, _ptr(dvw), p, *args, _ptr(p1), _ptr(p2), _ptr(acc), _stream()),
+                  "vn_svfe_bwd(pass %d)" % p)
+        run(1)
+        p2[4], p2[5] = (acc[2176:2240] / n).float(), (acc[2112:2176] / n).float()
+        run(2)
+        p1[4], p1[5] = (acc[2384:2400] / n).float(), (acc[2368:2384] / n).float()
+        run(3)
+    f = acc.float()
+    return {
+        "w2": f[0:2048].view(64, 32), "b2": f[2048:2112], "gamma2": f[2112:2176], "beta2": f[2176:2240],
+        "w1": f[2240:2352].view(16, 7), "b1": f[2352:2368], "gamma1": f[2368:2384], "beta1": f[2384:2400],
+    }

@@ -92,7 +92,10 @@ class VoxelNetFrontEnd:
     def refresh_parameters(self) -> None:
         """Re-fold BN / re-pack weights after the modules' parameters changed."""
         if self.feature_net.training or self.middle_net.training:
-            raise NotImplementedError("VoxelNetFrontEnd runs eval-mode BatchNorm only; call .eval() on both modules")
+            # training mode folds nothing ahead of time: BatchNorm uses the statistics of each batch
+            # (forward_points_train); the eval-mode fast path is set up by the next call after .eval()
+            self._p1 = None
+            return
         self._p1 = self.feature_net.vfe_1.folded()
         self._p2 = self.feature_net.vfe_2.folded()
         self._conv = [layer.folded() for layer in self.middle_net.middle_layer]
@@ -149,8 +152,13 @@ class VoxelNetFrontEnd:
         """points (N,4) f32 cuda (frames concatenated), frame_offsets (B+1,) i32 cuda ->
         (B,128,H,W) f32.  The returned tensor is an internal buffer reused by the next call; with
         resident_outputs it must not be modified by the caller (blocks no voxel reaches are not rewritten)."""
+        if self.feature_net.training or self.middle_net.training:
+            raise RuntimeError("forward_points is the eval-mode fast path; use forward_points_train in training mode")
+        if self._p1 is None:
+            self.refresh_parameters()
         n_frames = frame_offsets.numel() - 1
         self._ensure_buffers(n_frames, points.shape[0], points.device)
+        self._clear_train_cells()
         vb = self.voxels
         span = timer.span if timer is not None else (lambda stage: _NO_SPAN)
         k_dev = vb.n_voxels_dev
@@ -199,6 +207,55 @@ class VoxelNetFrontEnd:
             with span("conv3"):
                 ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out, workspace=ws2)
         return self.out
+
+    def _clear_train_cells(self) -> None:
+        """Re-zero the grid cells the previous training step wrote (the eval path clears its own)."""
+        prev = getattr(self, "_train_coords", None)
+        if prev is not None and prev.shape[0] > 0:
+            ops.scatter_dense_bf16(None, prev, self.dense, clear=True)
+        self._train_coords = None
+
+    def forward_points_train(self, points: torch.Tensor, frame_offsets: torch.Tensor, max_points_per_frame: int,
+                             timer: StageTimer = None) -> torch.Tensor:
+        """Training-mode step (model.train(True), train.py:148): the same path with batch-statistics BatchNorm
+        and an autograd graph.  points (N,4) f32 cuda, frame_offsets (B+1,) i32 cuda -> (B,128,H,W) f32 with a
+        grad_fn; `.backward()` on anything computed from it fills the .grad of every VFE / ConvMD parameter.
+
+        Differences from the eval path: the (K,T,7) feature buffer is materialised (the batch statistics need
+        two reduction passes over all rows before the VFE can be applied, and the backward re-reads it), the
+        exact voxel count is read back once per step, and every layer keeps its raw convolution output.  The
+        resident grid keeps this step's voxel rows until the next call (the weight gradient of the first conv
+        layer reads them in the backward), so call backward before the next forward."""
+        if not (self.feature_net.training and self.middle_net.training):
+            raise RuntimeError("forward_points_train needs both modules in .train() mode")
+        n_frames = frame_offsets.numel() - 1
+        self._ensure_buffers(n_frames, points.shape[0], points.device)
+        self._clear_train_cells()
+        if self.out_states is not None:
+            for st in self.out_states:  # the eval path's resident outputs are not maintained here
+                st.fill_(0xFF)
+        c, vb = self.cfg, self.voxels
+        span = timer.span if timer is not None else (lambda stage: _NO_SPAN)
+        with span("voxelize"):
+            ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
+            K = self.voxel_counts()[-1]  # blocking: the statistics are over exactly K*T rows
+            feat = getattr(self, "_train_feature", None)
+            if feat is None or feat.shape[0] < K or feat.device != points.device:
+                feat = torch.empty((max(K, 1) * 5 // 4, c.points_per_voxel, 7), dtype=torch.float32, device=points.device)
+                self._train_feature = feat
+            ops.voxelize_fill(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, feat,
+                              vb.coordinate, vb.number, self.workspace)
+        feature, coords = feat[:K], vb.coordinate[:K].clone()
+        with span("svfe"):
+            vw = self.feature_net.voxelwise(feature)
+        with span("scatter"):
+            ops.scatter_dense_bf16(vw.detach(), coords, self.dense)
+            self._train_coords = coords
+        dense = self.dense.view(self.dense.shape)  # a fresh tensor object for the side channel
+        if vw.requires_grad:
+            dense._vn_sparse = (vw, coords)
+        with span("conv"):
+            return self.middle_net(dense)
 
     def plan_stats(self) -> list:
         """Blocking diagnostics: what the three conv launches of the last step executed (live boxes,

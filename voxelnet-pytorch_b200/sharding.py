@@ -41,3 +41,23 @@ def gather_ints(value: int) -> list:
     out = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
     dist.all_gather(out, t)
     return [int(o.item()) for o in out]
+
+
+def allreduce_gradients(params, average: bool = True) -> int:
+    """Data-parallel gradient exchange of the training config: the .grad tensors of
+    `params` are packed into ONE flat fp32 buffer, summed over the ranks with a single all-reduce (NCCL over
+    NVLink/NVSwitch on the GPU box, gloo in the CPU tests), divided by the world size and unpacked in place.
+    Returns the number of gradient elements exchanged (0 without a process group or at world size 1)."""
+    grads = [p.grad for p in params if p.grad is not None]
+    if not grads or not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return 0
+    flat = torch.cat([g.reshape(-1).float() for g in grads])
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM)
+    if average:
+        flat.div_(dist.get_world_size())
+    off = 0
+    for g in grads:
+        n = g.numel()
+        g.copy_(flat[off:off + n].view_as(g))
+        off += n
+    return int(flat.numel())
