@@ -51,3 +51,26 @@ def test_dgrad_matches_autograd(cuda_device, idx, Din, H, W):
     got = ops.conv3d_dgrad(dy.to(cuda_device).to(torch.bfloat16), packed, Din, stride[0], padding[0]).float().cpu()
     err = float((got - want).abs().max() / want.abs().max())
     assert got.shape == want.shape and err < 6e-3, err  # bf16 storage of dx
+
+
+def test_wgrad_skips_dead_boxes_exactly(cuda_device):
+    """First layer on a sparse voxel grid: with the live-box table of vn_conv3d_mark_boxes the units whose
+    input boxes hold only zeros are skipped; the result equals the unflagged run up to summation order."""
+    from voxelnet_pytorch_b200 import ops
+
+    g = torch.Generator().manual_seed(70)
+    B, D, H, W = 2, 10, 40, 32
+    occ = torch.rand((B, D, H, W), generator=g) < 0.002
+    occ[0, 0, 0, 0] = occ[1, 9, H - 1, W - 1] = True
+    coords = occ.nonzero().contiguous().to(cuda_device)
+    x = torch.zeros((B, D, H, W, 128))
+    x[occ] = _bf16_exact((int(occ.sum()), 128), g)
+    dy = _bf16_exact((B, 5, H, W, 64), g, 0.5)
+    xd, dyd = x.to(cuda_device).to(torch.bfloat16), dy.to(cuda_device).to(torch.bfloat16)
+    flags = ops.conv3d_new_box_flags(B, D, H, W, cuda_device)
+    ops.conv3d_mark_boxes(coords, B, D, H, W, [(2, 1)], [flags])
+    assert 0 < int(flags.sum()) < flags.numel()
+    dense = ops.conv3d_wgrad(xd, dyd, 2, 1)
+    sparse = ops.conv3d_wgrad(xd, dyd, 2, 1, box_flags=flags)
+    err = float((dense - sparse).abs().max() / dense.abs().max())
+    assert err < 1e-5, err

@@ -34,6 +34,9 @@ struct WgParams {
   int tiles_h, tiles_w;
   int n_groups, n_slices;
   float* dw;  // [27][cin][64] fp32, accumulated into
+  // live-box table of the layer input ([B][Din][tiles_h][tiles_w][3], vn_conv3d_mark_boxes) or nullptr: a unit
+  // whose X boxes hold only zeros contributes nothing and is skipped (exact for the voxel grid of layer 1)
+  const uint8_t* flags;
 };
 
 struct WgControl {
@@ -124,23 +127,40 @@ __global__ void __launch_bounds__(kWgThreads, 1)
   tc_fence_after_sync();
   const uint32_t tmem_base = ctl->tmem_base;
 
-  // Units of this CTA: u = slice, slice + S, ...; unit -> (b, d', th, tw); X plane p = d'*s - pad + kd.
-  auto decode = [&](int64_t u, int& b, int& d, int& th, int& tw, int& p) {
+  // Units of this CTA: u = slice, slice + S, ...; unit -> (b, d', th, tw); X plane p = d'*s - pad + G.kd.
+  auto geometry = [&](int64_t u, int& b, int& d, int& th, int& tw, int& p) {
     tw = (int)(u % P.tiles_w); u /= P.tiles_w;
     th = (int)(u % P.tiles_h); u /= P.tiles_h;
     d = (int)(u % P.Dout);
     b = (int)(u / P.Dout);
     p = d * P.stride_d - P.pad_d + G.kd;
-    return p >= 0 && p < P.Din;
+  };
+  // The warp tests 32 candidate units at once (one per lane: the live-box flags are a global-memory read each)
+  // and returns the mask of those that have work; producer and issuer walk identical sequences.
+  auto live_mask = [&](int64_t u0) -> uint32_t {
+    const int64_t u = u0 + (int64_t)lane * P.n_slices;
+    bool ok = false;
+    if (u < n_units) {
+      int b, d, th, tw, p;
+      geometry(u, b, d, th, tw, p);
+      ok = p >= 0 && p < P.Din;
+      if (ok && P.flags != nullptr) {
+        const uint8_t* f = P.flags + ((((size_t)b * P.Din + p) * P.tiles_h + th) * P.tiles_w + tw) * 3;
+        ok = false;
+        for (int i = 0; i < G.nboxes; ++i) ok |= f[G.box_kw[i]] != 0;
+      }
+    }
+    return __ballot_sync(0xffffffffu, ok);
   };
 
   if (warp == 0) {
     // ================= TMA producer =================
     uint32_t it = 0;
     const uint32_t bytes = kYBytes + (uint32_t)G.nboxes * kXBytes;
-    for (int64_t u = slice; u < n_units; u += P.n_slices) {
+    for (int64_t u0 = slice; u0 < n_units; u0 += 32 * (int64_t)P.n_slices)
+    for (uint32_t todo = live_mask(u0); todo != 0; todo &= todo - 1) {
       int b, d, th, tw, p;
-      if (!decode(u, b, d, th, tw, p)) continue;
+      geometry(u0 + (int64_t)(__ffs(todo) - 1) * P.n_slices, b, d, th, tw, p);
       const uint32_t s = it % kStages;
       mbar_wait(&ctl->empty[s], ((it / kStages) & 1) ^ 1);
       if (elect_one()) {
@@ -159,9 +179,8 @@ __global__ void __launch_bounds__(kWgThreads, 1)
     uint32_t it = 0;
     // M = 128, N = 64, bf16 x bf16 -> f32, A and B MN-major (bits 15, 16)
     const uint32_t idesc = umma_idesc_bf16(128, 64) | (1u << 15) | (1u << 16);
-    for (int64_t u = slice; u < n_units; u += P.n_slices) {
-      int b, d, th, tw, p;
-      if (!decode(u, b, d, th, tw, p)) continue;
+    for (int64_t u0 = slice; u0 < n_units; u0 += 32 * (int64_t)P.n_slices)
+    for (uint32_t todo = live_mask(u0); todo != 0; todo &= todo - 1) {
       const uint32_t s = it % kStages;
       mbar_wait(&ctl->full[s], (it / kStages) & 1);
       tc_fence_after_sync();
@@ -272,7 +291,7 @@ using namespace vn;
 extern "C" {
 
 int vn_conv3d_wgrad(const void* x, const void* dy, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin,
-                    int32_t stride_d, int32_t pad_d, float* dw_taps, vn_stream_t stream) {
+                    int32_t stride_d, int32_t pad_d, float* dw_taps, const uint8_t* box_flags, vn_stream_t stream) {
   VN_REQUIRE(x && dy && dw_taps, "conv3d_wgrad: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d_wgrad: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1 && W % kTileW == 0, "conv3d_wgrad: bad shape");
@@ -294,6 +313,7 @@ int vn_conv3d_wgrad(const void* x, const void* dy, int32_t B, int32_t Din, int32
   P.n_slices = sm_count() / P.n_groups;
   if (P.n_slices < 1) P.n_slices = 1;
   P.dw = dw_taps;
+  P.flags = box_flags;
   VN_CUDA(cudaFuncSetAttribute(k_conv3d_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kWgSmem));
   k_conv3d_wgrad<<<P.n_groups * P.n_slices, kWgThreads, kWgSmem, as_stream(stream)>>>(mx, my, P);
   VN_LAUNCH_CHECK("k_conv3d_wgrad");

@@ -51,12 +51,19 @@ __global__ void __launch_bounds__(256)
 }
 
 // out_mode 1: f32 [B, 64*D, H, W] with channel = c*D + d (the reshape of model.py:262).
-// One block = 32 consecutive w positions of one (b, d, h) row: bf16 [32][64] in, transposed through shared
-// memory, 64 rows of 32 floats (128 B) out.
+// One block iteration = 32 consecutive w positions of one (b, d, h) row: bf16 [32][64] in as 16-byte vectors
+// (8 channels of one position per thread), transposed through shared memory, 64 rows of 32 floats out as float4.
 __global__ void __launch_bounds__(256)
     k_bn_relu_apply_final(const __nv_bfloat16* __restrict__ raw, int B, int D, int H, int W,
                           const float* __restrict__ scale, const float* __restrict__ shift, float* __restrict__ out) {
   __shared__ float tile[64][33];
+  const int p = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 8;
+  float s[8], t[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    s[j] = scale[c0 + j];
+    t[j] = shift[c0 + j];
+  }
   const int wblocks = (W + 31) / 32;
   const int64_t n_blocks = (int64_t)B * D * H * wblocks;
   for (int64_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
@@ -66,19 +73,25 @@ __global__ void __launch_bounds__(256)
     const int d = (int)(r % D);
     const int b = (int)(r / D);
     const int w0 = wb * 32;
-    const __nv_bfloat16* src = raw + ((((int64_t)b * D + d) * H + h) * W + w0) * 64;
-    for (int e = threadIdx.x; e < 32 * 64; e += 256) {
-      const int p = e >> 6, c = e & 63;
-      float v = 0.0f;
-      if (w0 + p < W) v = fmaxf(fmaf(__bfloat162float(src[e]), scale[c], shift[c]), 0.0f);
-      tile[c][p] = v;
+    __syncthreads();
+    if (w0 + p < W) {
+      const uint4 rv = *reinterpret_cast<const uint4*>(raw + ((((int64_t)b * D + d) * H + h) * W + w0 + p) * 64 + c0);
+      const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
+        tile[c0 + 2 * e][p] = fmaxf(fmaf(x.x, s[2 * e], t[2 * e]), 0.0f);
+        tile[c0 + 2 * e + 1][p] = fmaxf(fmaf(x.y, s[2 * e + 1], t[2 * e + 1]), 0.0f);
+      }
     }
     __syncthreads();
-    for (int e = threadIdx.x; e < 64 * 32; e += 256) {
-      const int c = e >> 5, p = e & 31;
-      if (w0 + p < W) out[(((int64_t)b * 64 * D + (int64_t)c * D + d) * H + h) * W + w0 + p] = tile[c][p];
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {
+      const int e = threadIdx.x + 256 * i, c = e >> 3, q = (e & 7) * 4;
+      if (w0 + q < W)
+        *reinterpret_cast<float4*>(out + (((int64_t)b * 64 * D + (int64_t)c * D + d) * H + h) * W + w0 + q) =
+            make_float4(tile[c][q], tile[c][q + 1], tile[c][q + 2], tile[c][q + 3]);
     }
-    __syncthreads();
   }
 }
 
@@ -248,6 +261,7 @@ int vn_bn_relu_apply(const void* raw_bf16, int32_t B, int32_t D, int32_t H, int3
   VN_REQUIRE(raw_bf16 && scale && shift && out, "bn_relu_apply: null pointer");
   VN_REQUIRE(B >= 1 && D >= 1 && H >= 1 && W >= 1, "bn_relu_apply: empty tensor");
   VN_REQUIRE(out_mode == 0 || out_mode == 1, "bn_relu_apply: out_mode=%d", out_mode);
+  VN_REQUIRE(out_mode == 0 || W % 4 == 0, "bn_relu_apply: W=%d must be a multiple of 4 for the (B, c*D+d, H, W) layout", W);
   VN_REQUIRE((reinterpret_cast<uintptr_t>(raw_bf16) & 15) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0,
              "bn_relu_apply: buffers must be 16-byte aligned");
   cudaStream_t st = as_stream(stream);

@@ -85,7 +85,9 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// dy in the final layout: f32 [B, 64*D, H, W], channel = c*D + d.  One block = 32 consecutive w of one (b,d,h).
+// dy in the final layout: f32 [B, 64*D, H, W], channel = c*D + d.  One block iteration = 32 consecutive w of one
+// (b,d,h): the 64 x 32 fp32 dy tile is read as 128-byte rows (float4 per thread) and transposed through shared
+// memory; raw / draw move as 16-byte vectors (8 channels of one position per thread).  W % 4 == 0.
 template <bool APPLY>
 __global__ void __launch_bounds__(256)
     k_bn_bwd_final(const __nv_bfloat16* __restrict__ raw, const float* __restrict__ dy, int B, int D, int H, int W,
@@ -93,10 +95,19 @@ __global__ void __launch_bounds__(256)
   __shared__ float tile[64][33];
   __shared__ float blk[128];
   if (threadIdx.x < 128) blk[threadIdx.x] = 0.0f;
-  const int c = threadIdx.x & 63, p0 = threadIdx.x >> 6;
-  const float s = prm[c], t = prm[64 + c], mu = prm[128 + c], is = prm[192 + c];
-  const float k1 = APPLY ? prm[256 + c] : 0.0f, k2 = APPLY ? prm[320 + c] : 0.0f;
-  float a1 = 0.0f, a2 = 0.0f;
+  const int p = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 8;  // compute role: position p, channels c0 .. c0+7
+  float s[8], t[8], mu[8], is[8], k1[8], k2[8], a1[8], a2[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    s[j] = prm[c0 + j];
+    t[j] = prm[64 + c0 + j];
+    mu[j] = prm[128 + c0 + j];
+    is[j] = prm[192 + c0 + j];
+    k1[j] = APPLY ? prm[256 + c0 + j] : 0.0f;
+    k2[j] = APPLY ? prm[320 + c0 + j] : 0.0f;
+    a1[j] = 0.0f;
+    a2[j] = 0.0f;
+  }
   const int wblocks = (W + 31) / 32;
   const int64_t n_blocks = (int64_t)B * D * H * wblocks;
   for (int64_t b_ = blockIdx.x; b_ < n_blocks; b_ += gridDim.x) {
@@ -107,32 +118,52 @@ __global__ void __launch_bounds__(256)
     const int b = (int)(r / D);
     const int w0 = wb * 32;
     __syncthreads();
-    for (int e = threadIdx.x; e < 64 * 32; e += 256) {
-      const int cc = e >> 5, p = e & 31;
-      tile[cc][p] = (w0 + p < W) ? dy[(((int64_t)b * 64 * D + (int64_t)cc * D + d) * H + h) * W + w0 + p] : 0.0f;
+#pragma unroll
+    for (int i = 0; i < 2; ++i) {  // 64 rows x 8 float4
+      const int e = threadIdx.x + 256 * i, cc = e >> 3, q = (e & 7) * 4;
+      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (w0 + q < W)
+        v = *reinterpret_cast<const float4*>(dy + (((int64_t)b * 64 * D + (int64_t)cc * D + d) * H + h) * W + w0 + q);
+      tile[cc][q] = v.x; tile[cc][q + 1] = v.y; tile[cc][q + 2] = v.z; tile[cc][q + 3] = v.w;
     }
     __syncthreads();
-    const int64_t base = ((((int64_t)b * D + d) * H + h) * W + w0) * 64;
+    if (w0 + p < W) {
+      const int64_t off = ((((int64_t)b * D + d) * H + h) * W + w0 + p) * 64 + c0;
+      const uint4 rv = *reinterpret_cast<const uint4*>(raw + off);
+      const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+      uint32_t o[4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int p = p0 + 4 * i;
-      if (w0 + p < W) {
-        const float x = __bfloat162float(raw[base + p * 64 + c]);
-        const float dz = fmaf(x, s, t) > 0.0f ? tile[c][p] : 0.0f;
-        const float xh = (x - mu) * is;
+      for (int e = 0; e < 4; ++e) {
+        const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
+        const float xs[2] = {x.x, x.y};
+        float dd[2];
+#pragma unroll
+        for (int hh = 0; hh < 2; ++hh) {
+          const int j = 2 * e + hh;
+          const float dz = fmaf(xs[hh], s[j], t[j]) > 0.0f ? tile[c0 + j][p] : 0.0f;
+          const float xh = (xs[hh] - mu[j]) * is[j];
+          if (APPLY) {
+            dd[hh] = s[j] * (dz - k1[j] - xh * k2[j]);
+          } else {
+            a1[j] += dz;
+            a2[j] = fmaf(dz, xh, a2[j]);
+          }
+        }
         if (APPLY) {
-          draw[base + p * 64 + c] = __float2bfloat16_rn(s * (dz - k1 - xh * k2));
-        } else {
-          a1 += dz;
-          a2 = fmaf(dz, xh, a2);
+          const __nv_bfloat162 rr = __floats2bfloat162_rn(dd[0], dd[1]);
+          o[e] = *reinterpret_cast<const uint32_t*>(&rr);
         }
       }
+      if (APPLY) *reinterpret_cast<uint4*>(draw + off) = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
   if (!APPLY) {
     __syncthreads();
-    atomicAdd(&blk[c], a1);
-    atomicAdd(&blk[64 + c], a2);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      atomicAdd(&blk[c0 + j], a1[j]);
+      atomicAdd(&blk[64 + c0 + j], a2[j]);
+    }
     __syncthreads();
     if (threadIdx.x < 128) atomicAdd(&sums[threadIdx.x], (double)blk[threadIdx.x]);
   }
@@ -534,6 +565,7 @@ int vn_bn_relu_bwd(const void* raw_bf16, const void* dy, int32_t dy_mode, int32_
   VN_REQUIRE(B >= 1 && D >= 1 && H >= 1 && W >= 1, "bn_relu_bwd: empty tensor");
   VN_REQUIRE(dy_mode == 0 || dy_mode == 1, "bn_relu_bwd: dy_mode=%d", dy_mode);
   VN_REQUIRE(apply ? draw_bf16 != nullptr : sums != nullptr, "bn_relu_bwd: missing output");
+  VN_REQUIRE(dy_mode == 0 || W % 4 == 0, "bn_relu_bwd: W=%d must be a multiple of 4 for the (B, c*D+d, H, W) layout", W);
   VN_REQUIRE((reinterpret_cast<uintptr_t>(raw_bf16) & 15) == 0 && (reinterpret_cast<uintptr_t>(dy) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(draw_bf16) & 15) == 0,
              "bn_relu_bwd: buffers must be 16-byte aligned");

@@ -90,23 +90,24 @@ class _SVFETrainFn(torch.autograd.Function):
         return None, g["w1"], g["b1"], g["gamma1"], g["beta1"], g["w2"], g["b2"], g["gamma2"], g["beta2"], None
 
 
-def _conv_train_forward(layer, x, final, out):
+def _conv_train_forward(layer, x, final, out, box_flags=None):
     """raw conv (+ batch statistics in the epilogue) -> fold -> BN + ReLU into a separate buffer (the raw
     output is kept for the backward)."""
     packed, _, _ = layer.folded()
-    raw, sums = ops.conv3d_raw_stats_fwd(x, packed, layer.conv.bias.detach(), layer.stride[0], layer.padding[0])
+    raw, sums = ops.conv3d_raw_stats_fwd(x, packed, layer.conv.bias.detach(), layer.stride[0], layer.padding[0],
+                                         box_flags=box_flags)
     B, Dout, H, W, _ = raw.shape
     stats = _fold_batch_stats(layer.batch_norm, sums, B * Dout * H * W)
     y = ops.bn_relu_apply(raw, stats[0], stats[1], final=final, out=out if final else None)
     return y, raw, stats
 
 
-def _conv_train_backward(x, raw, stats, dy, final, stride_d, pad_d):
+def _conv_train_backward(x, raw, stats, dy, final, stride_d, pad_d, box_flags=None):
     """-> (draw bf16, dW (64,cin,3,3,3) f32, dgamma, dbeta)."""
     dy = dy.contiguous()
     dy = dy.float() if final else dy.to(torch.bfloat16)
     draw, dgamma, dbeta = ops.bn_relu_bwd(raw, dy, *stats, final=final)
-    dw = ops.conv3d_wgrad(x, draw, stride_d, pad_d)
+    dw = ops.conv3d_wgrad(x, draw, stride_d, pad_d, box_flags=box_flags)
     return draw, dw, dgamma, dbeta
 
 
@@ -141,16 +142,21 @@ class _Conv1SparseTrainFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, vw, coords, dense, weight, bias, gamma, beta, layer):
-        y, raw, stats = _conv_train_forward(layer, dense, False, None)
-        ctx.save_for_backward(dense, raw, weight, coords, *stats)
+        # boxes of the grid no voxel lies in are all-zero: their MMAs are skipped in the forward and in the
+        # weight gradient (exact); every output block is still written
+        B, D, H, W, _ = dense.shape
+        flags = ops.conv3d_new_box_flags(B, D, H, W, dense.device)
+        ops.conv3d_mark_boxes(coords, B, D, H, W, [(layer.stride[0], layer.padding[0])], [flags])
+        y, raw, stats = _conv_train_forward(layer, dense, False, None, box_flags=flags)
+        ctx.save_for_backward(dense, raw, weight, coords, flags, *stats)
         ctx.geom = (layer.stride[0], layer.padding[0])
         return y
 
     @staticmethod
     def backward(ctx, dy):
-        dense, raw, weight, coords, *stats = ctx.saved_tensors
+        dense, raw, weight, coords, flags, *stats = ctx.saved_tensors
         stride_d, pad_d = ctx.geom
-        draw, dw, dgamma, dbeta = _conv_train_backward(dense, raw, stats, dy, False, stride_d, pad_d)
+        draw, dw, dgamma, dbeta = _conv_train_backward(dense, raw, stats, dy, False, stride_d, pad_d, box_flags=flags)
         dvw = None
         if ctx.needs_input_grad[0]:
             dvw = ops.conv1_dgrad_gather(draw, ops.conv1_weight_taps(weight), coords, stride_d, pad_d)

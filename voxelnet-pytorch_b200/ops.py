@@ -469,10 +469,11 @@ def bn_relu_apply(raw, scale, shift, final: bool = False, out=None):
 # ---------------------------------------------------------------------------------------------
 # backward of the Conv3d middle layers
 # ---------------------------------------------------------------------------------------------
-def conv3d_wgrad(x, dy, stride_d: int, pad_d: int) -> torch.Tensor:
+def conv3d_wgrad(x, dy, stride_d: int, pad_d: int, box_flags=None) -> torch.Tensor:
     """Weight gradient in torch layout (64, cin, 3, 3, 3) f32 from the layer input x (B,Din,H,W,cin) bf16 and the
-    gradient dy (B,Dout,H,W,64) bf16 of the raw convolution output (tcgen05, fp32 accumulation)."""
-    _require_cuda(x, dy)
+    gradient dy (B,Dout,H,W,64) bf16 of the raw convolution output (tcgen05, fp32 accumulation).  box_flags: live-box
+    table of x (conv3d_mark_boxes); dead boxes must be all-zero and are skipped."""
+    _require_cuda(x, dy, box_flags)
     _contig(x, torch.bfloat16), _contig(dy, torch.bfloat16)
     B, Din, H, W, cin = x.shape
     Dout = conv3d_out_depth(Din, stride_d, pad_d)
@@ -480,7 +481,8 @@ def conv3d_wgrad(x, dy, stride_d: int, pad_d: int) -> torch.Tensor:
         raise RuntimeError("dy must be (B,Dout,H,W,64) = %s, got %s" % ((B, Dout, H, W, 64), tuple(dy.shape)))
     taps = torch.zeros((27, cin, 64), dtype=torch.float32, device=x.device)
     with torch.cuda.device(x.device):
-        check(_cabi.lib().vn_conv3d_wgrad(_ptr(x), _ptr(dy), B, Din, H, W, cin, stride_d, pad_d, _ptr(taps), _stream()),
+        check(_cabi.lib().vn_conv3d_wgrad(_ptr(x), _ptr(dy), B, Din, H, W, cin, stride_d, pad_d, _ptr(taps), _ptr(box_flags),
+                                          _stream()),
               "vn_conv3d_wgrad")
     return taps.view(3, 3, 3, cin, 64).permute(4, 3, 0, 1, 2).contiguous()
 
