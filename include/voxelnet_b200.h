@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 6
+#define VN_ABI_VERSION 8
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -293,21 +293,23 @@ int vn_bn_relu_bwd(const void* raw_bf16, const void* dy, int32_t dy_mode, int32_
 
 /* Backward of to_dense (model.py:102-106) fused with the data gradient of the first middle layer: the
  * transposed convolution is evaluated only at the K occupied cells.  draw [B, Dr, H, W, 64] bf16 = gradient of
- * that layer's raw output; weight_taps [27][64][128] f32 = W[n][c][kd][kh][kw] as [tap][n][c]; coords [K,4]
- * (b, z, y, x); dvw [K,128] f32 = gradient of the voxel-wise features. */
-int vn_conv1_dgrad_gather(const void* draw_bf16, const float* weight_taps, const int64_t* coords, int64_t K,
+ * that layer's raw output; weight_taps [27][128][64] bf16 = W[n][c][kd][kh][kw] as [tap][c][n]; coords [K,4]
+ * (b, z, y, x); dvw [K,128] f32 = gradient of the voxel-wise features.  A gather-GEMM on tcgen05: 128 voxels x
+ * 128 channels per CTA, K = 64 per valid tap, fp32 accumulation in TMEM. */
+int vn_conv1_dgrad_gather(const void* draw_bf16, const void* weight_taps, const int64_t* coords, int64_t K,
                           int32_t B, int32_t Dr, int32_t H, int32_t W, int32_t stride_d, int32_t pad_d,
                           float* dvw, vn_stream_t stream);
 
 /* Backward of the stacked VFE with batch-statistics BatchNorm1d (autograd of model.py:74-82, 95-100) from the
  * gradient dvw [K,128] of the voxel-wise features; feature [K, T, 7] as in vn_svfe_fused_fwd.  Three passes
  * (each recomputes the forward on chip): pass 1 -> dgamma2, dbeta2; pass 2 (needs bn2 rows 4, 5) -> dW2, db2,
- * dgamma1, dbeta1; pass 3 (needs bn1 rows 4, 5 too) -> dW1, db1.  bn1 [6][16], bn2 [6][64] f32 = scale, shift,
+ * dgamma1, dbeta1, and the VFE-1 output gradient of every evaluated row into row_scratch [K][T][16] f32 (caller-
+ * allocated, may be NULL for pass 1); pass 3 (needs bn1 rows 4, 5 and row_scratch) -> dW1, db1.  bn1 [6][16], bn2 [6][64] f32 = scale, shift,
  * mean, invstd, dbeta/N, dgamma/N with N = K*T.  acc: 2400 fp64, accumulated into: dW2[64][32] @0, db2 @2048,
  * dgamma2 @2112, dbeta2 @2176, dW1[16][7] @2240, db1 @2352, dgamma1 @2368, dbeta1 @2384. */
 int vn_svfe_bwd(const float* feature, int64_t K, int32_t T, const float* dvw, int32_t pass, const float* w1,
                 const float* b1, const float* w2, const float* b2, const float* bn1, const float* bn2,
-                double* acc, vn_stream_t stream);
+                float* row_scratch, double* acc, vn_stream_t stream);
 
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);

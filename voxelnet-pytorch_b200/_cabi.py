@@ -14,7 +14,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 6
+VN_ABI_VERSION = 8
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 
@@ -64,7 +64,7 @@ PROTOTYPES = {
     "vn_conv3d_wgrad": (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p]),
     "vn_bn_relu_bwd": (C.c_int, [_p, _p, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _p]),
     "vn_conv1_dgrad_gather": (C.c_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p]),
-    "vn_svfe_bwd": (C.c_int, [_p, _i64, _i32, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "vn_svfe_bwd": (C.c_int, [_p, _i64, _i32, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "vn_launch_count": (_i64, []),
 }
 

@@ -170,91 +170,130 @@ __global__ void __launch_bounds__(256)
 }
 
 // ---------------------------------------------------------------------------------------------------------
-// First conv layer: data gradient at the occupied cells only.
+// First conv layer: data gradient at the occupied cells only, as a gather-GEMM on tcgen05.
 //   dvw[v][c] = sum over taps (kd,kh,kw) and n of draw[b, d', y+1-kh, x+1-kw][n] * W[n][c][kd][kh][kw],
 //   d' = (z + pad - kd) / stride when divisible and inside [0, Dr).
-// Block = 32 consecutive voxels (np.unique order: they mostly share z, so whole taps drop out), thread = one
-// of the 128 input channels, 32 fp32 accumulators per thread; per tap the 64x128 weight slice and the 32
-// gathered gradient rows sit in shared memory.
+// CTA = 128 consecutive voxels (np.unique order: they mostly share z, so the taps of the other depth parity drop
+// out for the whole CTA).  Per tap: thread r gathers voxel r's 128-byte gradient row (or zeros) into row r of a
+// SWIZZLE_128B K-major A tile and copies row r of the tap's [128 c][64 n] weight slice into the B tile; one
+// thread then issues 4 x tcgen05.mma (M = 128 voxels, N = 128 channels, K = 16) accumulating into a 128-column
+// TMEM tile.  Two stages: the gather of the next tap overlaps the MMAs of this one.
 // ---------------------------------------------------------------------------------------------------------
-constexpr int kGV = 32;
+constexpr int kGV = 128;
+constexpr uint32_t kGTile = 128 * 128;  // 16 KB: 128 rows x 64 bf16
 
-__global__ void __launch_bounds__(128)
-    k_conv1_dgrad_gather(const __nv_bfloat16* __restrict__ draw, const float* __restrict__ wt /* [27][64][128] */,
+struct GatherCtl {
+  uint64_t mma_done[2];
+  uint32_t tmem_base;
+  uint32_t pad;
+};
+constexpr uint32_t kGatherSmem = 4 * kGTile + 1024 + (uint32_t)sizeof(GatherCtl);
+
+__global__ void __launch_bounds__(kGV)
+    k_conv1_dgrad_gather(const __nv_bfloat16* __restrict__ draw, const __nv_bfloat16* __restrict__ wt /* [27][128][64] */,
                          const long long* __restrict__ coords, int64_t K, int Dr, int H, int W, int stride_d,
                          int pad_d, float* __restrict__ dvw) {
-  __shared__ __align__(16) float Ws[64 * 128];
-  __shared__ __align__(16) float As[kGV * 64];
-  __shared__ int vb[kGV], vz[kGV], vy[kGV], vx[kGV];
-  const int tid = threadIdx.x;
-  const int64_t v0 = (int64_t)blockIdx.x * kGV;
-  if (tid < kGV) {
-    const int64_t v = v0 + tid;
-    if (v < K) {
-      vb[tid] = (int)coords[v * 4 + 0];
-      vz[tid] = (int)coords[v * 4 + 1];
-      vy[tid] = (int)coords[v * 4 + 2];
-      vx[tid] = (int)coords[v * 4 + 3];
-    } else {
-      vb[tid] = -1;
-      vz[tid] = vy[tid] = vx[tid] = 0;
-    }
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  GatherCtl* ctl = reinterpret_cast<GatherCtl*>(smem + 4 * kGTile);
+  const uint32_t r = threadIdx.x, warp = r >> 5;
+  if (r == 0) {
+    mbar_init(&ctl->mma_done[0], 1);
+    mbar_init(&ctl->mma_done[1], 1);
+    mbar_fence_init();
   }
+  if (warp == 0) {
+    tmem_alloc(&ctl->tmem_base, 128);
+    tmem_relinquish();
+  }
+  tc_fence_before_sync();
   __syncthreads();
-  float acc[kGV];
-#pragma unroll
-  for (int v = 0; v < kGV; ++v) acc[v] = 0.0f;
-  const int gv = tid >> 2, gq = tid & 3;  // gather role: voxel gv, channels 16*gq .. +15
+  tc_fence_after_sync();
+  const uint32_t tmem_base = ctl->tmem_base;
+
+  const int64_t v = (int64_t)blockIdx.x * kGV + r;
+  int vb = -1, vz = 0, vy = 0, vx = 0;
+  if (v < K) {
+    vb = (int)coords[v * 4 + 0];
+    vz = (int)coords[v * 4 + 1];
+    vy = (int)coords[v * 4 + 2];
+    vx = (int)coords[v * 4 + 3];
+  }
+  const uint32_t row_off = r * 128, sw = r & 7;
+  const uint32_t idesc = umma_idesc_bf16(128, 128);
+  uint32_t it = 0;
   for (int tap = 0; tap < 27; ++tap) {
     const int kd = tap / 9, kh = (tap / 3) % 3, kw = tap % 3;
-    bool valid = vb[gv] >= 0;
-    const int zz = vz[gv] + pad_d - kd;
+    const int zz = vz + pad_d - kd;
     const int dd = zz / stride_d;
-    const int hh = vy[gv] + 1 - kh, ww = vx[gv] + 1 - kw;
-    valid = valid && zz >= 0 && (zz % stride_d) == 0 && dd < Dr && hh >= 0 && hh < H && ww >= 0 && ww < W;
-    if (!__syncthreads_or(valid)) continue;  // (also the barrier that protects Ws / As from the previous tap)
+    const int hh = vy + 1 - kh, ww = vx + 1 - kw;
+    const bool valid = vb >= 0 && zz >= 0 && (zz % stride_d) == 0 && dd < Dr && hh >= 0 && hh < H && ww >= 0 && ww < W;
+    if (!__syncthreads_or(valid)) continue;
+    const uint32_t s = it & 1;
+    if (it >= 2) mbar_wait(&ctl->mma_done[s], ((it >> 1) - 1) & 1);  // the MMAs that read this stage are done
+    uint8_t* a_tile = smem + s * 2 * kGTile;
+    uint8_t* b_tile = a_tile + kGTile;
     {
-      float4 f[4];
+      uint4 q[8];
       if (valid) {
-        const uint4* src = reinterpret_cast<const uint4*>(draw + ((((int64_t)vb[gv] * Dr + dd) * H + hh) * W + ww) * 64 + gq * 16);
-        const uint4 q0 = src[0], q1 = src[1];
-        const uint32_t wds[8] = {q0.x, q0.y, q0.z, q0.w, q1.x, q1.y, q1.z, q1.w};
+        const uint4* src = reinterpret_cast<const uint4*>(draw + ((((int64_t)vb * Dr + dd) * H + hh) * W + ww) * 64);
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 lo = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wds[2 * e]));
-          const float2 hi = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&wds[2 * e + 1]));
-          f[e] = make_float4(lo.x, lo.y, hi.x, hi.y);
-        }
+        for (int j = 0; j < 8; ++j) q[j] = src[j];
       } else {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) f[e] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int j = 0; j < 8; ++j) q[j] = make_uint4(0u, 0u, 0u, 0u);
       }
-      float4* dst = reinterpret_cast<float4*>(As + gv * 64 + gq * 16);
 #pragma unroll
-      for (int e = 0; e < 4; ++e) dst[e] = f[e];
-      const float4* wsrc = reinterpret_cast<const float4*>(wt + (size_t)tap * 64 * 128);
-      float4* wdst = reinterpret_cast<float4*>(Ws);
-#pragma unroll 4
-      for (int i = 0; i < 16; ++i) wdst[tid + 128 * i] = wsrc[tid + 128 * i];
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(a_tile + row_off + (((uint32_t)j ^ sw) << 4)) = q[j];
+      const uint4* wsrc = reinterpret_cast<const uint4*>(wt + ((size_t)tap * 128 + r) * 64);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) q[j] = wsrc[j];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) *reinterpret_cast<uint4*>(b_tile + row_off + (((uint32_t)j ^ sw) << 4)) = q[j];
     }
+    fence_proxy_async_smem();
     __syncthreads();
-#pragma unroll 1
-    for (int n4 = 0; n4 < 16; ++n4) {
-      const float w0 = Ws[(4 * n4 + 0) * 128 + tid], w1 = Ws[(4 * n4 + 1) * 128 + tid];
-      const float w2 = Ws[(4 * n4 + 2) * 128 + tid], w3 = Ws[(4 * n4 + 3) * 128 + tid];
+    if (warp == 0) {
+      if (elect_one()) {
+        tc_fence_after_sync();
+        const uint32_t a_addr = smem_u32(a_tile), b_addr = smem_u32(b_tile);
 #pragma unroll
-      for (int v = 0; v < kGV; ++v) {
-        const float4 a = *reinterpret_cast<const float4*>(As + v * 64 + 4 * n4);
-        acc[v] = fmaf(a.x, w0, acc[v]);
-        acc[v] = fmaf(a.y, w1, acc[v]);
-        acc[v] = fmaf(a.z, w2, acc[v]);
-        acc[v] = fmaf(a.w, w3, acc[v]);
+        for (int k = 0; k < 4; ++k)
+          umma_bf16_ss(tmem_base, umma_desc_sw128(a_addr + k * 32, 1024), umma_desc_sw128(b_addr + k * 32, 1024), idesc,
+                       (it == 0 && k == 0) ? 0u : 1u);
+        umma_commit(&ctl->mma_done[s]);
+      }
+      __syncwarp();
+    }
+    ++it;
+  }
+  if (it > 0) mbar_wait(&ctl->mma_done[(it - 1) & 1], ((it - 1) >> 1) & 1);
+  tc_fence_after_sync();
+  {  // tcgen05.ld is warp-collective: every lane loads its row, only rows of real voxels are stored
+    float* dst = dvw + v * 128;
+#pragma unroll
+    for (int c4 = 0; c4 < 4; ++c4) {
+      uint32_t o[32];
+      if (it > 0) {  // block-uniform
+        tmem_ld_32x32b_x32(tmem_base + ((warp * 32) << 16) + c4 * 32, o);
+        tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) o[j] = 0u;
+      }
+      if (v < K) {
+#pragma unroll
+        for (int j = 0; j < 32; j += 4)
+          *reinterpret_cast<uint4*>(dst + c4 * 32 + j) = make_uint4(o[j], o[j + 1], o[j + 2], o[j + 3]);
       }
     }
   }
-#pragma unroll
-  for (int v = 0; v < kGV; ++v)
-    if (v0 + v < K) dvw[(v0 + v) * 128 + tid] = acc[v];
+  tc_fence_before_sync();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after_sync();
+    tmem_dealloc(tmem_base, 128);
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------
@@ -268,69 +307,85 @@ __global__ void __launch_bounds__(128)
 //           -(dbeta + xhat*dgamma)/N over EVERY row, pads included, so three passes are needed:
 //   PASS 1: dbeta2, dgamma2                       (needs dvw)
 //   PASS 2: dW2, db2, dbeta1, dgamma1             (needs dbeta2/N, dgamma2/N)
-//   PASS 3: dW1, db1                              (needs dbeta1/N, dgamma1/N as well)
+//   PASS 3: dW1, db1                              (needs dbeta1/N, dgamma1/N and PASS 2's row gradients)
 // bn1: [6][16], bn2: [6][64] = scale, shift, mean, invstd, dbeta/N, dgamma/N.
 // acc (fp64): dW2[64][32] @0, db2 @2048, dgamma2 @2112, dbeta2 @2176, dW1[16][7] @2240, db1 @2352,
 //             dgamma1 @2368, dbeta1 @2384; 2400 values.
 // ---------------------------------------------------------------------------------------------------------
+// PASS 2 also stores each evaluated row's VFE-1 output gradient (16 floats) to `rows` [K][T][16], so that PASS 3
+// only redoes the cheap VFE-1 forward.
 constexpr int kBwWarps = 8;
 constexpr int kAccN = 2400;
 constexpr int kOffW2 = 0, kOffB2 = 2048, kOffG2 = 2112, kOffBe2 = 2176, kOffW1 = 2240, kOffB1 = 2352, kOffG1 = 2368,
               kOffBe1 = 2384;
+constexpr int kW2kN = 2 * 32 * 16 + 16;  // [half][u][k] with the second half 16 floats further (bank spread)
 
 struct SvfeBwdShared {
   float w1[16 * 7], b1[16];
   float bn1[6][16];
   float b2[64];
   float bn2[6][64];
-  float whi[16][64];    // whi[k][unit] = W2[unit][16 + k]
-  float w2t[64 * 33];   // w2t[unit * 33 + k] = W2[unit][k], k < 32
+  float whi[16][64];   // whi[k][unit] = W2[unit][16 + k]          (forward, per-voxel half)
+  float w2lo[kW2kN];   // W2[unit][k],      k < 16, as [half][unit & 31][k]  (gradient of the per-row half)
+  float w2hi[kW2kN];   // W2[unit][16 + k], k < 16, same layout              (gradient of agg1)
   float blk[kAccN];
 };
+__device__ __forceinline__ int w2k_index(int unit, int k) { return (unit >> 5) * (32 * 16 + 16) + (unit & 31) * 16 + k; }
 
 template <int PASS>
-__global__ void __launch_bounds__(kBwWarps * 32, 1)
+__global__ void __launch_bounds__(kBwWarps * 32, PASS == 2 ? 1 : 2)
     k_svfe_bwd(const float* __restrict__ feature, int64_t K, int T, const float* __restrict__ dvw,
                const float* __restrict__ w1, const float* __restrict__ b1, const float* __restrict__ w2,
                const float* __restrict__ b2, const float* __restrict__ bn1, const float* __restrict__ bn2,
-               double* __restrict__ acc_out) {
+               float* __restrict__ rows, double* __restrict__ acc_out) {
   extern __shared__ __align__(16) float dyn_smem[];
   __shared__ SvfeBwdShared S;
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   for (int i = threadIdx.x; i < 16 * 7; i += blockDim.x) S.w1[i] = w1[i];
   for (int i = threadIdx.x; i < 16; i += blockDim.x) S.b1[i] = b1[i];
   for (int i = threadIdx.x; i < 6 * 16; i += blockDim.x) S.bn1[i >> 4][i & 15] = bn1[i];
-  for (int i = threadIdx.x; i < 64; i += blockDim.x) S.b2[i] = b2[i];
-  for (int i = threadIdx.x; i < 6 * 64; i += blockDim.x) S.bn2[i >> 6][i & 63] = bn2[i];
-  for (int i = threadIdx.x; i < 16 * 64; i += blockDim.x) S.whi[i >> 6][i & 63] = w2[(i & 63) * 32 + 16 + (i >> 6)];
-  for (int i = threadIdx.x; i < 64 * 32; i += blockDim.x) S.w2t[(i >> 5) * 33 + (i & 31)] = w2[i];
   for (int i = threadIdx.x; i < kAccN; i += blockDim.x) S.blk[i] = 0.0f;
+  if (PASS != 3) {
+    for (int i = threadIdx.x; i < 64; i += blockDim.x) S.b2[i] = b2[i];
+    for (int i = threadIdx.x; i < 6 * 64; i += blockDim.x) S.bn2[i >> 6][i & 63] = bn2[i];
+    for (int i = threadIdx.x; i < 16 * 64; i += blockDim.x) S.whi[i >> 6][i & 63] = w2[(i & 63) * 32 + 16 + (i >> 6)];
+    for (int i = threadIdx.x; i < 64 * 16; i += blockDim.x) {
+      const int unit = i >> 4, k = i & 15;
+      S.w2lo[w2k_index(unit, k)] = w2[unit * 32 + k];
+      S.w2hi[w2k_index(unit, k)] = w2[unit * 32 + 16 + k];
+    }
+  }
   __syncthreads();
 
-  // per-warp scratch: in[T*7 (+pad)], n1[(T+1)*16], h1[T*16], g1[T*16], dzs[64]
+  // per-warp scratch: in[T*7 (+pad)], n1[(T+1)*16], h1[T*16], g1[T*16], dzs[72]
   const int in_ld = (T * 7 + 3) & ~3;
-  const int per_warp = in_ld + (T + 1) * 16 + T * 16 + T * 16 + 64;
+  const int per_warp = in_ld + (T + 1) * 16 + T * 16 + T * 16 + 72;
   float* in = dyn_smem + (size_t)warp * per_warp;
   float* n1 = in + in_ld;
   float* h1s = n1 + (T + 1) * 16;
   float* g1 = h1s + T * 16;
-  float* dzs = g1 + T * 16;
+  float* dzs = g1 + T * 16;  // unit u at dzs[u + (u >> 5)] (the two halves in different banks)
 
   // lane owns VFE-2 units a = lane, b = lane + 32
   float wa[16], wb[16];
+  float b2a = 0.f, b2b = 0.f, s2a = 0.f, s2b = 0.f, t2a = 0.f, t2b = 0.f, m2a = 0.f, m2b = 0.f, i2a = 0.f, i2b = 0.f;
+  float A2a = 0.f, A2b = 0.f, B2a = 0.f, B2b = 0.f;
+  if (PASS != 3) {
 #pragma unroll
-  for (int k = 0; k < 16; ++k) {
-    wa[k] = S.w2t[lane * 33 + k];
-    wb[k] = S.w2t[(lane + 32) * 33 + k];
+    for (int k = 0; k < 16; ++k) {
+      wa[k] = w2[lane * 32 + k];
+      wb[k] = w2[(lane + 32) * 32 + k];
+    }
+    b2a = S.b2[lane]; b2b = S.b2[lane + 32];
+    s2a = S.bn2[0][lane]; s2b = S.bn2[0][lane + 32];
+    t2a = S.bn2[1][lane]; t2b = S.bn2[1][lane + 32];
+    m2a = S.bn2[2][lane]; m2b = S.bn2[2][lane + 32];
+    i2a = S.bn2[3][lane]; i2b = S.bn2[3][lane + 32];
+    A2a = S.bn2[4][lane]; A2b = S.bn2[4][lane + 32];
+    B2a = S.bn2[5][lane]; B2b = S.bn2[5][lane + 32];
   }
-  const float b2a = S.b2[lane], b2b = S.b2[lane + 32];
-  const float s2a = S.bn2[0][lane], s2b = S.bn2[0][lane + 32];
-  const float t2a = S.bn2[1][lane], t2b = S.bn2[1][lane + 32];
-  const float m2a = S.bn2[2][lane], m2b = S.bn2[2][lane + 32];
-  const float i2a = S.bn2[3][lane], i2b = S.bn2[3][lane + 32];
-  const float A2a = S.bn2[4][lane], A2b = S.bn2[4][lane + 32];
-  const float B2a = S.bn2[5][lane], B2b = S.bn2[5][lane + 32];
-  const int u1 = lane & 15;  // VFE-1 unit of this lane in the (row, unit) sweeps
+  const int u1 = lane & 15;  // VFE-1 unit of this lane in the (row, unit) sweeps; also the k of the dc sweeps
+  const int half = lane >> 4;
   const float s1u = S.bn1[0][u1], t1u = S.bn1[1][u1], m1u = S.bn1[2][u1], i1u = S.bn1[3][u1];
   const float A1u = S.bn1[4][u1], B1u = S.bn1[5][u1];
 
@@ -362,6 +417,7 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
     }
     const int R = nu < T ? nu + 1 : T;
     const float tail_mult = (float)(T - nu);
+    float* grow = rows + v * (int64_t)(T * 16);
     // ---- VFE-1 forward ----
     for (int e = lane; e < R * 16; e += 32) {
       const int r = e >> 4;
@@ -372,7 +428,24 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
       const float h = fmaxf(a, 0.0f);
       h1s[e] = h;
       n1[e] = fmaf(h, s1u, t1u);
-      g1[e] = 0.0f;
+      g1[e] = PASS == 3 ? grow[e] : 0.0f;
+    }
+    __syncwarp();
+    if (PASS == 3) {
+      // ---- VFE-1 backward from the stored row gradients ----
+      for (int e = lane; e < R * 16; e += 32) {
+        const int r = e >> 4;
+        const float g = g1[e], h = h1s[e];
+        const float xh = (h - m1u) * i1u;
+        const float m = (r == nu) ? tail_mult : 1.0f;
+        const float dz = h > 0.0f ? s1u * (g - m * fmaf(xh, B1u, A1u)) : 0.0f;
+        const float* f = in + (r < nu ? r : T - 1) * 7;
+        db1 += dz;
+#pragma unroll
+        for (int j = 0; j < 7; ++j) dW1[j] = fmaf(dz, f[j], dW1[j]);
+      }
+      __syncwarp();
+      continue;
     }
     uint64_t on_bits = 0;
     for (int r0 = 0; r0 < R; r0 += 32) {
@@ -387,7 +460,6 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
       }
       on_bits |= (uint64_t)__ballot_sync(0xffffffffu, on) << r0;
     }
-    __syncwarp();
     int arg1 = 0;
     if (lane < 16) {
       float a = n1[lane];
@@ -446,9 +518,8 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
       __syncwarp();
       continue;
     }
-    // ---- sweep 2: dz2 per row, dW2 / db2, gradient of the VFE-2 input ----
-    float dagg = 0.0f;                 // lanes 16..31: sum over on rows of d c1[r][16 + (lane - 16)]
-    float dzon_a = 0.0f, dzon_b = 0.0f;
+    // ---- sweep 2: dz2 per row, dW2 / db2, gradient of the per-row half of the VFE-2 input ----
+    float dzon_a = 0.0f, dzon_b = 0.0f;  // sum of dz2 over the rows with mask 1 (the agg1 half sees only this sum)
     for (int r = 0; r < R; ++r) {
       const bool on = (on_bits >> r) & 1;
       const float m = (r == nu) ? tail_mult : 1.0f;
@@ -467,59 +538,54 @@ __global__ void __launch_bounds__(kBwWarps * 32, 1)
       const float dnb = (r == ron_b ? g_b : 0.0f) + (r == rall_b ? gp_b : 0.0f);
       const float dza = ha > 0.0f ? s2a * (dna - m * fmaf((ha - m2a) * i2a, B2a, A2a)) : 0.0f;
       const float dzb = hb > 0.0f ? s2b * (dnb - m * fmaf((hb - m2b) * i2b, B2b, A2b)) : 0.0f;
-      if (PASS == 2) {
-        db2a += dza;
-        db2b += dzb;
-      }
+      db2a += dza;
+      db2b += dzb;
       if (on) {  // warp-uniform
-        if (PASS == 2) {
 #pragma unroll
-          for (int k = 0; k < 16; ++k) {
-            dWa[k] = fmaf(dza, xr[k], dWa[k]);
-            dWb[k] = fmaf(dzb, xr[k], dWb[k]);
-          }
-          dzon_a += dza;
-          dzon_b += dzb;
+        for (int k = 0; k < 16; ++k) {
+          dWa[k] = fmaf(dza, xr[k], dWa[k]);
+          dWb[k] = fmaf(dzb, xr[k], dWb[k]);
         }
+        dzon_a += dza;
+        dzon_b += dzb;
         dzs[lane] = dza;
-        dzs[lane + 32] = dzb;
+        dzs[lane + 33] = dzb;
         __syncwarp();
+        // d c1[r][k] for k < 16: lane = (k, half of the 64 units)
         float dc = 0.0f;
+        const float* wk = S.w2lo + half * (32 * 16 + 16) + u1;
+        const float* dzh = dzs + half * 33;
 #pragma unroll 8
-        for (int u = 0; u < 64; ++u) dc = fmaf(S.w2t[u * 33 + lane], dzs[u], dc);
+        for (int u = 0; u < 32; ++u) dc = fmaf(wk[u * 16], dzh[u], dc);
+        dc += __shfl_xor_sync(0xffffffffu, dc, 16);
         if (lane < 16) g1[r * 16 + lane] = dc;
-        else dagg += dc;
         __syncwarp();
       }
     }
-    if (PASS == 2) {
 #pragma unroll
-      for (int k = 0; k < 16; ++k) {
-        dWa[16 + k] = fmaf(dzon_a, agg1[k], dWa[16 + k]);
-        dWb[16 + k] = fmaf(dzon_b, agg1[k], dWb[16 + k]);
-      }
+    for (int k = 0; k < 16; ++k) {
+      dWa[16 + k] = fmaf(dzon_a, agg1[k], dWa[16 + k]);
+      dWb[16 + k] = fmaf(dzon_b, agg1[k], dWb[16 + k]);
     }
-    {  // agg1's gradient goes to the row that attains it
-      const float val = __shfl_sync(0xffffffffu, dagg, (lane & 15) + 16);
-      if (lane < 16) g1[arg1 * 16 + lane] += val;
+    {  // agg1's gradient = W2[:,16:32]^T (sum of dz2 over the on rows); it goes to the row that attains the max
+      dzs[lane] = dzon_a;
+      dzs[lane + 33] = dzon_b;
+      __syncwarp();
+      float dc = 0.0f;
+      const float* wk = S.w2hi + half * (32 * 16 + 16) + u1;
+      const float* dzh = dzs + half * 33;
+#pragma unroll 8
+      for (int u = 0; u < 32; ++u) dc = fmaf(wk[u * 16], dzh[u], dc);
+      dc += __shfl_xor_sync(0xffffffffu, dc, 16);
+      if (lane < 16) g1[arg1 * 16 + lane] += dc;
     }
     __syncwarp();
-    // ---- VFE-1 backward ----
+    // ---- BatchNorm-1 sums; row gradients kept for PASS 3 ----
     for (int e = lane; e < R * 16; e += 32) {
-      const int r = e >> 4;
       const float g = g1[e], h = h1s[e];
-      const float xh = (h - m1u) * i1u;
-      if (PASS == 2) {
-        dbe1 += g;
-        dg1 = fmaf(g, xh, dg1);
-      } else {
-        const float m = (r == nu) ? tail_mult : 1.0f;
-        const float dz = h > 0.0f ? s1u * (g - m * fmaf(xh, B1u, A1u)) : 0.0f;
-        const float* f = in + (r < nu ? r : T - 1) * 7;
-        db1 += dz;
-#pragma unroll
-        for (int j = 0; j < 7; ++j) dW1[j] = fmaf(dz, f[j], dW1[j]);
-      }
+      dbe1 += g;
+      dg1 = fmaf(g, (h - m1u) * i1u, dg1);
+      grow[e] = g;
     }
     __syncwarp();
   }
@@ -597,7 +663,7 @@ int vn_bn_relu_bwd(const void* raw_bf16, const void* dy, int32_t dy_mode, int32_
   return VN_OK;
 }
 
-int vn_conv1_dgrad_gather(const void* draw_bf16, const float* weight_taps, const int64_t* coords, int64_t K, int32_t B,
+int vn_conv1_dgrad_gather(const void* draw_bf16, const void* weight_taps, const int64_t* coords, int64_t K, int32_t B,
                           int32_t Dr, int32_t H, int32_t W, int32_t stride_d, int32_t pad_d, float* dvw,
                           vn_stream_t stream) {
   VN_REQUIRE(K >= 0 && B >= 1 && Dr >= 1 && H >= 1 && W >= 1, "conv1_dgrad_gather: bad shape");
@@ -607,34 +673,37 @@ int vn_conv1_dgrad_gather(const void* draw_bf16, const float* weight_taps, const
   VN_REQUIRE(draw_bf16 && weight_taps && coords && dvw, "conv1_dgrad_gather: null pointer");
   VN_REQUIRE((reinterpret_cast<uintptr_t>(draw_bf16) & 15) == 0 && (reinterpret_cast<uintptr_t>(weight_taps) & 15) == 0,
              "conv1_dgrad_gather: buffers must be 16-byte aligned");
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(dvw) & 15) == 0, "conv1_dgrad_gather: dvw must be 16-byte aligned");
   const int64_t blocks = (K + kGV - 1) / kGV;
   VN_REQUIRE(blocks < (int64_t)0x7fffffff, "conv1_dgrad_gather: too many voxels");
-  k_conv1_dgrad_gather<<<(unsigned)blocks, 128, 0, as_stream(stream)>>>(
-      reinterpret_cast<const __nv_bfloat16*>(draw_bf16), weight_taps, reinterpret_cast<const long long*>(coords), K, Dr, H, W,
-      stride_d, pad_d, dvw);
+  VN_CUDA(cudaFuncSetAttribute(k_conv1_dgrad_gather, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kGatherSmem));
+  k_conv1_dgrad_gather<<<(unsigned)blocks, kGV, kGatherSmem, as_stream(stream)>>>(
+      reinterpret_cast<const __nv_bfloat16*>(draw_bf16), reinterpret_cast<const __nv_bfloat16*>(weight_taps),
+      reinterpret_cast<const long long*>(coords), K, Dr, H, W, stride_d, pad_d, dvw);
   VN_LAUNCH_CHECK("k_conv1_dgrad_gather");
   return VN_OK;
 }
 
 int vn_svfe_bwd(const float* feature, int64_t K, int32_t T, const float* dvw, int32_t pass, const float* w1,
-                const float* b1, const float* w2, const float* b2, const float* bn1, const float* bn2, double* acc,
-                vn_stream_t stream) {
+                const float* b1, const float* w2, const float* b2, const float* bn1, const float* bn2,
+                float* row_scratch, double* acc, vn_stream_t stream) {
   VN_REQUIRE(K >= 0, "svfe_bwd: K < 0");
   VN_REQUIRE(T >= 1 && T <= 64, "svfe_bwd: T=%d outside [1,64]", T);
   VN_REQUIRE(pass >= 1 && pass <= 3, "svfe_bwd: pass=%d", pass);
   if (K == 0) return VN_OK;
   VN_REQUIRE(feature && dvw && w1 && b1 && w2 && b2 && bn1 && bn2 && acc, "svfe_bwd: null pointer");
+  VN_REQUIRE(pass == 1 || row_scratch != nullptr, "svfe_bwd: passes 2 and 3 need row_scratch [K][T][16]");
   VN_REQUIRE((reinterpret_cast<uintptr_t>(acc) & 7) == 0, "svfe_bwd: acc must be 8-byte aligned");
   cudaStream_t st = as_stream(stream);
   const int in_ld = (T * 7 + 3) & ~3;
-  const size_t smem = sizeof(float) * (size_t)kBwWarps * (in_ld + (T + 1) * 16 + T * 16 + T * 16 + 64);
+  const size_t smem = sizeof(float) * (size_t)kBwWarps * (in_ld + (T + 1) * 16 + T * 16 + T * 16 + 72);
   const int64_t want = (K + kBwWarps - 1) / kBwWarps;
   const int64_t cap = (int64_t)sm_count() * 2;
   const unsigned grid = (unsigned)(want < cap ? want : cap);
 #define VN_SVFE_BWD(P)                                                                                              \
   do {                                                                                                              \
     VN_CUDA(cudaFuncSetAttribute(k_svfe_bwd<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));           \
-    k_svfe_bwd<P><<<grid, kBwWarps * 32, smem, st>>>(feature, K, T, dvw, w1, b1, w2, b2, bn1, bn2, acc);            \
+    k_svfe_bwd<P><<<grid, kBwWarps * 32, smem, st>>>(feature, K, T, dvw, w1, b1, w2, b2, bn1, bn2, row_scratch, acc);            \
   } while (0)
   if (pass == 1) VN_SVFE_BWD(1);
   else if (pass == 2) VN_SVFE_BWD(2);

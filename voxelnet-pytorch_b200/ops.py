@@ -549,19 +549,20 @@ def bn_relu_bwd(raw, dy, scale, shift, mean, invstd, final: bool = False):
 
 
 def conv1_weight_taps(weight) -> torch.Tensor:
-    """(64,128,3,3,3) f32 -> [27][64][128] f32 with the values the bf16 forward multiplied with."""
-    w = weight.detach().to(torch.bfloat16).float()
-    return w.permute(2, 3, 4, 0, 1).reshape(27, w.shape[0], w.shape[1]).contiguous()
+    """(64,128,3,3,3) f32 -> [27][128 c][64 n] bf16: the values the bf16 forward multiplied with, one K-major
+    B tile per tap for the gather-GEMM."""
+    w = weight.detach().to(torch.bfloat16)
+    return w.permute(2, 3, 4, 1, 0).reshape(27, w.shape[1], w.shape[0]).contiguous()
 
 
 def conv1_dgrad_gather(draw, weight_taps, coords, stride_d: int, pad_d: int) -> torch.Tensor:
     """Gradient of the (K,128) voxel-wise features through to_dense + the first conv layer: draw (B,Dr,H,W,64) bf16,
     weight_taps from conv1_weight_taps, coords (K,4) i64 -> (K,128) f32."""
     _require_cuda(draw, weight_taps, coords)
-    _contig(draw, torch.bfloat16), _contig(weight_taps, torch.float32), _contig(coords, torch.int64)
+    _contig(draw, torch.bfloat16), _contig(weight_taps, torch.bfloat16), _contig(coords, torch.int64)
     B, Dr, H, W, Cc = draw.shape
-    if Cc != 64 or tuple(weight_taps.shape) != (27, 64, 128):
-        raise RuntimeError("conv1_dgrad_gather: draw (B,Dr,H,W,64) and weight_taps (27,64,128) expected")
+    if Cc != 64 or tuple(weight_taps.shape) != (27, 128, 64):
+        raise RuntimeError("conv1_dgrad_gather: draw (B,Dr,H,W,64) and weight_taps (27,128,64) expected")
     K = coords.shape[0]
     dvw = torch.empty((K, 128), dtype=torch.float32, device=draw.device)
     with torch.cuda.device(draw.device):
@@ -585,11 +586,12 @@ def svfe_bwd(feature, dvw, w1, b1, w2, b2, bn1, bn2) -> dict:
     for i in range(4):
         p1[i], p2[i] = bn1[i], bn2[i]
     acc = torch.zeros(2400, dtype=torch.float64, device=dev)
+    rows = torch.empty((K, T, 16), dtype=torch.float32, device=dev)  # only the evaluated rows are touched
     n = float(max(K * T, 1))
     args = [_ptr(_contig(t, torch.float32)) for t in (w1, b1, w2, b2)]
     with torch.cuda.device(dev):
         def run(p):
-            check(_cabi.lib().vn_svfe_bwd(_ptr(feature), K, T, _ptr(dvw), p, *args, _ptr(p1), _ptr(p2), _ptr(acc), _stream()),
+            check(_cabi.lib().vn_svfe_bwd(_ptr(feature), K, T, _ptr(dvw), p, *args, _ptr(p1), _ptr(p2), _ptr(rows), _ptr(acc), _stream()),
                   "vn_svfe_bwd(pass %d)" % p)
         run(1)
         p2[4], p2[5] = (acc[2176:2240] / n).float(), (acc[2112:2176] / n).float()
