@@ -422,37 +422,21 @@ def main():
     plan = [{k: (plan[0][l][k] + plan[1][l][k]) / 2 for k in plan[0][l]} for l in range(3)]
 
     # ---- end to end: host buffers in, voxel counts out ---------------------------------------------
-    # Two device staging buffers: the H2D copy of step i+1 runs on a copy stream while step i computes.
-    stage = [(torch.empty_like(batches[0].points), torch.empty_like(batches[0].offsets)) for _ in range(2)]
-    copy_stream = torch.cuda.Stream()
-    ready = [torch.cuda.Event() for _ in range(2)]
-    freed = [torch.cuda.Event() for _ in range(2)]
-    main = torch.cuda.current_stream()
+    # Through the package's public feeding API (pipeline.HostFrameStream): two device staging slots, the H2D
+    # copy of step i+1 runs on a copy stream while step i computes; every copy is inside the timed region.
+    from voxelnet_pytorch_b200 import HostFrameStream, PinnedFrameBatch
 
-    def e2e_upload(i):
-        bt, (pd, od) = batches[i % 2], stage[i % 2]
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(freed[i % 2])
-            pd[: bt.points.shape[0]].copy_(bt.host_points, non_blocking=True)
-            od.copy_(bt.host_offsets, non_blocking=True)
-            ready[i % 2].record(copy_stream)
-
-    def e2e_compute(i):
-        bt, (pd, od) = batches[i % 2], stage[i % 2]
-        main.wait_event(ready[i % 2])
-        fe.forward_points(pd[: bt.points.shape[0]], od, bt.max_n)
-        freed[i % 2].record(main)
-        host_counts.copy_(fe.voxels.voxel_offsets, non_blocking=True)
+    host_batches = [PinnedFrameBatch.from_frames(fr) for fr in (frames, frames_b)]
+    host_batches.sort(key=lambda hb: -hb.n_points)
+    stream = HostFrameStream(fe, batch, host_batches[0].n_points)
 
     def e2e_run(n):
-        for k in range(2):
-            freed[k].record(main)
-        e2e_upload(0)
+        stream.upload(host_batches[0])
         for i in range(n):
             if i + 1 < n:
-                e2e_upload(i + 1)
-            e2e_compute(i)
-            main.synchronize()  # the caller consumes host_counts every step
+                stream.upload(host_batches[(i + 1) % 2])
+            stream.forward()
+            stream.voxel_counts_host()  # the caller consumes the per-frame voxel counts every step (synchronises)
 
     e2e_run(2)
     barrier()
@@ -548,7 +532,7 @@ def main():
             "e2e": {"value": frames_total / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(sum(bt.host_points.numel() * 4 + bt.host_offsets.numel() * 4 for bt in batches) / 2),
                     "d2h_bytes_per_step": int(host_counts.numel() * 4),
-                    "note": "H2D of step i+1 overlaps step i on a copy stream (two staging buffers); result read back per step = "
+                    "note": "through voxelnet_pytorch_b200.HostFrameStream: H2D of step i+1 overlaps step i on a copy stream (two staging buffers); result read back per step = "
                             "per-frame voxel counts; the (B,128,H,W) tensor stays on the device for the RPN"},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],

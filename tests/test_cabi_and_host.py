@@ -151,3 +151,32 @@ def test_synthetic_frames_are_kitti_shaped():
     K = len(v["number_buffer"])
     assert 9_000 < K < 16_000, K  # KITTI-typical 12-14k
     assert 3.5 < v["number_buffer"].mean() < 6.5
+
+
+def test_raw_point_input_pipeline_host_side(tmp_path):
+    """dataset.py:51 loader and the pinned CSR packing of the raw-point input pipeline."""
+    import numpy as np
+
+    from voxelnet_pytorch_b200 import PinnedFrameBatch, load_velodyne_bin
+
+    rng = np.random.default_rng(3)
+    frames = [rng.standard_normal((n, 4)).astype(np.float32) for n in (5, 0, 17)]
+    paths = []
+    for i, f in enumerate(frames):
+        p = tmp_path / ("%06d.bin" % i)
+        f.tofile(p)
+        paths.append(str(p))
+    assert np.array_equal(load_velodyne_bin(paths[2]), frames[2])
+    hb = PinnedFrameBatch.from_files(paths)
+    assert hb.n_points == 22 and hb.max_points_per_frame == 17
+    assert hb.offsets.tolist() == [0, 5, 5, 22]
+    assert np.array_equal(hb.points.numpy()[:22], np.concatenate(frames))
+    hb.fill([frames[2][:3], frames[0], frames[1]])  # reuse of the pinned allocation
+    assert hb.offsets.tolist() == [0, 3, 8, 8] and hb.n_points == 8
+    with pytest.raises(ValueError):
+        hb.fill(frames[:2])
+    with pytest.raises(ValueError):
+        hb.fill([np.zeros((30, 4), np.float32)] * 3)
+    (tmp_path / "bad.bin").write_bytes(b"\0" * 20)
+    with pytest.raises(ValueError):
+        load_velodyne_bin(str(tmp_path / "bad.bin"))

@@ -168,3 +168,32 @@ def test_frames_are_independent_units_including_an_empty_one(cuda_device):
         alone = single.forward_frames([f])
         assert torch.equal(alone[0].view(torch.int32), batch[i].view(torch.int32)), "frame %d" % i
     assert bool(torch.isfinite(batch).all())
+
+
+def test_host_frame_stream_matches_direct_forward(cuda_device):
+    """The end-to-end feeding API (pinned batches, two staging slots, copy stream) returns what forward_points
+    returns on the same frames, batch after batch, and reports the per-frame voxel counts."""
+    import voxelnet_pytorch_b200 as vn
+
+    sd = OM.random_state_dict(9)
+    fnet, mnet = vn.FeatureLearningNet("Pedestrian").eval(), vn.MiddleConvNet().eval()
+    load_state(fnet, sd, "")
+    load_state(mnet, sd, "")
+    fe = vn.VoxelNetFrontEnd(fnet.to(cuda_device), mnet.to(cuda_device), "Pedestrian")
+    sets = [[f[::5].copy() for f in synth_frames(2, s)] for s in (300, 310, 320)]
+    want, counts = [], []
+    for fr in sets:
+        want.append(fe.forward_frames(fr).clone())
+        counts.append(fe.voxel_counts())
+    hbs = [vn.PinnedFrameBatch.from_frames(fr) for fr in sets]
+    stream = vn.HostFrameStream(fe, 2, max(hb.n_points for hb in hbs))
+    stream.upload(hbs[0])
+    for i in range(3):
+        if i + 1 < 3:
+            stream.upload(hbs[i + 1])
+        out = stream.forward()
+        got_counts = stream.voxel_counts_host().tolist()
+        assert got_counts == counts[i]
+        assert torch.equal(out, want[i]), i
+    with pytest.raises(RuntimeError):
+        stream.forward()

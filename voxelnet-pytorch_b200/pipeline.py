@@ -279,3 +279,69 @@ class VoxelNetFrontEnd:
         if offs[-1] > self.capacity:
             raise RuntimeError("voxel capacity %d exceeded (%d voxels): raise voxels_per_frame_capacity" % (self.capacity, offs[-1]))
         return offs
+
+
+class HostFrameStream:
+    """End-to-end feeding of a VoxelNetFrontEnd from pinned host batches (`dataset.PinnedFrameBatch`).
+
+    Two device staging slots: `upload(batch)` enqueues the host->device copy of a batch on a copy stream,
+    `forward()` runs the front end on the oldest uploaded batch on the current stream, so the copy of
+    batch i+1 overlaps the compute of batch i.  Replaces the reference's per-element `.to(device)` of
+    voxelized features (model.py:302-303) - only raw points cross PCIe.
+
+        stream = HostFrameStream(front_end, n_frames=16, max_points=2_100_000)
+        stream.upload(b0)
+        for nxt in batches[1:] + [None]:
+            if nxt is not None: stream.upload(nxt)
+            out = stream.forward()                # (B,128,H,W) on the device, for the RPN
+            counts = stream.voxel_counts_host()   # blocks until this step is done
+    """
+
+    def __init__(self, front_end: VoxelNetFrontEnd, n_frames: int, max_points: int, device=None):
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self.fe, self.device = front_end, dev
+        self.slots = [(torch.empty((int(max_points), 4), dtype=torch.float32, device=dev),
+                       torch.empty(n_frames + 1, dtype=torch.int32, device=dev)) for _ in range(2)]
+        self.copy_stream = torch.cuda.Stream(device=dev)
+        self.ready = [torch.cuda.Event() for _ in range(2)]
+        self.freed = [torch.cuda.Event() for _ in range(2)]
+        for e in self.freed:
+            e.record(torch.cuda.current_stream(dev))
+        self.pending = []  # (slot, n_points, max_points_per_frame)
+        self.next_slot = 0
+        self.host_counts = torch.empty(n_frames + 1, dtype=torch.int32).pin_memory()
+        self.h2d_bytes = 0
+
+    def upload(self, batch) -> None:
+        if len(self.pending) >= 2:
+            raise RuntimeError("both staging slots hold batches that were not consumed: call forward() first")
+        k = self.next_slot
+        pts, offs = self.slots[k]
+        if batch.n_points > pts.shape[0] or batch.offsets.numel() != offs.numel():
+            raise ValueError("batch does not fit the staging slot (points %d > %d or frame count differs)" % (batch.n_points, pts.shape[0]))
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.freed[k])
+            pts[: batch.n_points].copy_(batch.points[: batch.n_points], non_blocking=True)
+            offs.copy_(batch.offsets, non_blocking=True)
+            self.ready[k].record(self.copy_stream)
+        self.h2d_bytes = batch.n_points * 16 + offs.numel() * 4
+        self.pending.append((k, batch.n_points, batch.max_points_per_frame))
+        self.next_slot = 1 - k
+
+    def forward(self, timer: StageTimer = None) -> torch.Tensor:
+        if not self.pending:
+            raise RuntimeError("forward() without an uploaded batch")
+        k, n, max_n = self.pending.pop(0)
+        pts, offs = self.slots[k]
+        main = torch.cuda.current_stream(self.device)
+        main.wait_event(self.ready[k])
+        fn = self.fe.forward_points_train if self.fe.feature_net.training else self.fe.forward_points
+        out = fn(pts[:n], offs, max_n, timer=timer)
+        self.freed[k].record(main)
+        self.host_counts.copy_(self.fe.voxels.voxel_offsets, non_blocking=True)
+        return out
+
+    def voxel_counts_host(self) -> torch.Tensor:
+        """Blocking: the per-frame voxel prefix (B+1,) int32 of the last forward(), in pinned host memory."""
+        torch.cuda.current_stream(self.device).synchronize()
+        return self.host_counts
