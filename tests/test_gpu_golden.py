@@ -69,3 +69,43 @@ def test_middle_layers_cuda_match_reference_golden(cuda_device):
     assert rel_max_err(got, want) < 1e-2  # bf16 operands vs the reference's fp32 CPU result
     y1 = net.middle_layer[0](xd.to(cuda_device).permute(0, 4, 1, 2, 3)).cpu()
     assert rel_max_err(y1, torch.from_numpy(g["middle_layer0_out"])) < 1e-2
+
+
+def test_training_step_gradients_against_reference_golden(cuda_device, golden_dir):
+    """The CUDA training step (points -> voxelize -> SVFE -> grid -> 3 x ConvMD, batch-statistics BN, backward)
+    against gradients the UNMODIFIED fp32 reference produced for the same frame, parameters and upstream gradient
+    (tests/golden/train_grads_ped.npz).  The conv path is bf16: a few ReLUs near zero flip against fp32, so the
+    bar here is direction and scale (cosine >= 0.995, norm within 2 %, max deviation <= 8e-2 of max); the tight
+    per-kernel bars are in test_gpu_train_backward.py."""
+    import voxelnet_pytorch_b200 as vn
+    from tests.helpers import load_state
+    from tests.test_oracle_golden import _train_golden_inputs
+    from voxelnet_pytorch_b200.utils import pack_frames
+
+    g, points, target, sd, dout = _train_golden_inputs(golden_dir)
+    fnet, mnet = vn.FeatureLearningNet(target), vn.MiddleConvNet()
+    load_state(fnet, sd, "")
+    load_state(mnet, sd, "")
+    fe = vn.VoxelNetFrontEnd(fnet.to(cuda_device).train(), mnet.to(cuda_device).train(), target)
+    pts, offs, max_n = pack_frames([points])
+    out = fe.forward_points_train(pts, offs, max_n)
+    assert fe.voxel_counts()[-1] == int(g["n_voxels"])
+    sample = out.detach()[0, ::16, ::8, ::8].cpu().numpy()
+    assert np.abs(sample - g["out_sample"]).max() <= 1e-2 * float(g["out_abs_max"])
+    out.backward(dout.to(cuda_device))
+    stride = int(g["conv_stride"])
+    report = {}
+    for mod in (fnet, mnet):
+        for name, p in mod.named_parameters():
+            if name.endswith("conv.bias"):
+                continue
+            want = g["grad:" + name].astype(np.float64).reshape(-1)
+            got = p.grad.detach().double().cpu().numpy().reshape(-1)
+            if name.endswith("conv.weight"):
+                assert abs(np.linalg.norm(got) - float(g["norm:" + name])) < 2e-2 * float(g["norm:" + name]), name
+                got = got[::stride]
+            cos = float(got @ want / (np.linalg.norm(got) * np.linalg.norm(want)))
+            dev = float(np.abs(got - want).max() / np.abs(want).max())
+            report[name] = (round(cos, 5), round(dev, 4))
+    bad = {k: v for k, v in report.items() if not (v[0] >= 0.995 and v[1] <= 8e-2)}
+    assert not bad, report

@@ -1,4 +1,6 @@
 """CPU: the oracle against the golden vectors frozen from the unmodified reference."""
+import os
+
 import numpy as np
 import pytest
 import torch
@@ -80,3 +82,48 @@ def test_middle_oracle_matches_reference_golden():
         y1 = OM.middle_layers(xd, sd, upto=1)
     assert torch.allclose(y1, torch.from_numpy(g["middle_layer0_out"]), rtol=1e-5, atol=1e-5)
     assert torch.allclose(y, torch.from_numpy(g["middle_out"]), rtol=1e-5, atol=1e-5)
+
+
+def _train_golden_inputs(golden_dir):
+    """Inputs of tests/golden/train_grads_ped.npz (made by oracle/make_golden_train.py from the live reference)."""
+    import torch
+
+    from oracle.make_golden_train import upstream_gradient
+
+    g = np.load(os.path.join(golden_dir, "train_grads_ped.npz"))
+    points = np.load(os.path.join(golden_dir, "voxelize_kitti0_sub_car.npz"))["points"]
+    target = str(g["target"])
+    D, H, W, _ = OM.grid_dims(target)
+    dout = upstream_gradient((1, 128, H, W), int(g["dout_seed"]))
+    return g, points, target, OM.random_state_dict(int(g["state_seed"])), dout
+
+
+def test_oracle_training_gradients_match_reference_golden(golden_dir):
+    """Autograd through the oracle in training mode reproduces the gradients the UNMODIFIED reference produced
+    (train.py:148-149 semantics: batch-statistics BN in both VFE layers and the three ConvMD layers)."""
+    import torch
+
+    g, points, target, sd, dout = _train_golden_inputs(golden_dir)
+    v = OV.pcl_to_voxels_fast(points, target)
+    assert len(v["number_buffer"]) == int(g["n_voxels"])
+    keys = [k for k in sd if k.endswith("weight") or k.endswith("bias")]
+    leaf = {k: (sd[k].clone().requires_grad_(True) if k in keys else sd[k]) for k in sd}
+    feats, _, coords = OV.prepare_voxel([v])
+    vw = OM.svfe_voxelwise(torch.from_numpy(feats[0]), leaf, training=True)
+    dense = OM.scatter_dense(vw, torch.from_numpy(coords[0]), 1, target)
+    out = OM.middle_layers(dense, leaf, training=True)
+    assert abs(float(out.detach().abs().max()) - float(g["out_abs_max"])) < 1e-4 * float(g["out_abs_max"])
+    assert np.allclose(out.detach()[0, ::16, ::8, ::8].numpy(), g["out_sample"], rtol=1e-4, atol=1e-4)
+    out.backward(dout)
+    stride = int(g["conv_stride"])
+    for k in keys:
+        want = g["grad:" + k]
+        got = leaf[k].grad.numpy()
+        if k.endswith("conv.weight"):
+            assert abs(float(np.linalg.norm(got)) - float(g["norm:" + k])) < 1e-3 * float(g["norm:" + k]), k
+            got = got.reshape(-1)[::stride]
+        scale = max(float(np.abs(want).max()), 1e-20)
+        if k.endswith("conv.bias"):  # rounding noise around zero in both
+            assert float(np.abs(got).max()) < 1e-2 * float(np.abs(g["grad:" + k.replace("bias", "weight")]).max())
+            continue
+        assert float(np.abs(got - want).max()) / scale < 2e-3, (k, float(np.abs(got - want).max()) / scale)
