@@ -204,3 +204,38 @@ def test_front_end_training_step_end_to_end(cuda_device):
         mod.zero_grad()
     out2 = fe.forward_points_train(points, offsets, max_n)
     assert rel_max_err(out2.detach().cpu(), out_ref.detach()) < 1e-2
+
+
+def test_training_step_with_an_empty_frame_and_through_the_host_stream(cuda_device):
+    """Ragged batch: one frame without a single point in range next to a normal one; fed through the pinned
+    host stream.  The step equals the one-frame-at-index-1 oracle forward and leaves finite gradients; a batch
+    with no voxel at all raises (as BatchNorm does on an empty batch)."""
+    import voxelnet_pytorch_b200 as vn
+
+    target = "Pedestrian"
+    sd = OM.random_state_dict(37)
+    full = synth_frames(1, 160)[0][::4].copy()
+    empty = np.array([[500.0, 500.0, 50.0, 0.1]], np.float32)  # out of range: cropped
+    _, feats, _, coords = oracle_batch([empty, full], target)
+    assert feats[0].shape[0] == 0
+    with torch.no_grad():
+        vw = OM.svfe_voxelwise(torch.from_numpy(feats[1]), sd, training=True)
+        ref = OM.middle_layers(OM.scatter_dense(vw, torch.from_numpy(coords[1]), 2, target), sd, training=True)
+    fnet, mnet = vn.FeatureLearningNet(target), vn.MiddleConvNet()
+    load_state(fnet, sd, "")
+    load_state(mnet, sd, "")
+    fe = vn.VoxelNetFrontEnd(fnet.to(cuda_device).train(), mnet.to(cuda_device).train(), target)
+    hb = vn.PinnedFrameBatch.from_frames([empty, full])
+    stream = vn.HostFrameStream(fe, 2, hb.n_points)
+    stream.upload(hb)
+    out = stream.forward()
+    assert stream.voxel_counts_host().tolist() == [0, 0, feats[1].shape[0]]
+    assert rel_max_err(out.detach().cpu(), ref) < 1e-2
+    out.backward(torch.ones_like(out) * 1e-3)
+    for mod in (fnet, mnet):
+        for name, p in mod.named_parameters():
+            assert bool(torch.isfinite(p.grad).all()), name
+    hb0 = vn.PinnedFrameBatch.from_frames([empty, empty])
+    stream.upload(hb0)
+    with pytest.raises(RuntimeError):
+        stream.forward()

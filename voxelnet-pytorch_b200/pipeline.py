@@ -239,6 +239,8 @@ class VoxelNetFrontEnd:
         with span("voxelize"):
             ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
             K = self.voxel_counts()[-1]  # blocking: the statistics are over exactly K*T rows
+            if K == 0:  # nn.BatchNorm1d raises on an empty batch as well (model.py:76 in train mode)
+                raise RuntimeError("forward_points_train: the batch has no voxel inside the crop range")
             feat = getattr(self, "_train_feature", None)
             if feat is None or feat.shape[0] < K or feat.device != points.device:
                 feat = torch.empty((max(K, 1) * 5 // 4, c.points_per_voxel, 7), dtype=torch.float32, device=points.device)
