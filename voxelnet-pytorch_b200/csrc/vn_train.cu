@@ -51,20 +51,21 @@ __global__ void __launch_bounds__(256)
 }
 
 // out_mode 1: f32 [B, 64*D, H, W] with channel = c*D + d (the reshape of model.py:262).
-// One block iteration = 32 consecutive w positions of one (b, d, h) row: bf16 [32][64] in as 16-byte vectors
-// (8 channels of one position per thread), transposed through shared memory, 64 rows of 32 floats out as float4.
+// One block iteration = kFinW consecutive w positions of one (b, d, h) row: bf16 [kFinW][64] in as 16-byte vectors
+// (8 channels of one position per thread), transposed through shared memory, 64 rows of kFinW floats out as float4.
+constexpr int kFinW = 64;  // w positions per block iteration: 256-byte output rows
 __global__ void __launch_bounds__(256)
     k_bn_relu_apply_final(const __nv_bfloat16* __restrict__ raw, int B, int D, int H, int W,
                           const float* __restrict__ scale, const float* __restrict__ shift, float* __restrict__ out) {
-  __shared__ float tile[64][33];
-  const int p = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 8;
+  __shared__ float tile[64][kFinW + 1];
+  const int p0 = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 8;
   float s[8], t[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     s[j] = scale[c0 + j];
     t[j] = shift[c0 + j];
   }
-  const int wblocks = (W + 31) / 32;
+  const int wblocks = (W + kFinW - 1) / kFinW;
   const int64_t n_blocks = (int64_t)B * D * H * wblocks;
   for (int64_t blk = blockIdx.x; blk < n_blocks; blk += gridDim.x) {
     const int wb = (int)(blk % wblocks);
@@ -72,22 +73,26 @@ __global__ void __launch_bounds__(256)
     const int h = (int)(r % H); r /= H;
     const int d = (int)(r % D);
     const int b = (int)(r / D);
-    const int w0 = wb * 32;
+    const int w0 = wb * kFinW;
     __syncthreads();
-    if (w0 + p < W) {
-      const uint4 rv = *reinterpret_cast<const uint4*>(raw + ((((int64_t)b * D + d) * H + h) * W + w0 + p) * 64 + c0);
-      const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
-        tile[c0 + 2 * e][p] = fmaxf(fmaf(x.x, s[2 * e], t[2 * e]), 0.0f);
-        tile[c0 + 2 * e + 1][p] = fmaxf(fmaf(x.y, s[2 * e + 1], t[2 * e + 1]), 0.0f);
+    for (int i = 0; i < kFinW / 32; ++i) {
+      const int p = p0 + 32 * i;
+      if (w0 + p < W) {
+        const uint4 rv = *reinterpret_cast<const uint4*>(raw + ((((int64_t)b * D + d) * H + h) * W + w0 + p) * 64 + c0);
+        const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
+          tile[c0 + 2 * e][p] = fmaxf(fmaf(x.x, s[2 * e], t[2 * e]), 0.0f);
+          tile[c0 + 2 * e + 1][p] = fmaxf(fmaf(x.y, s[2 * e + 1], t[2 * e + 1]), 0.0f);
+        }
       }
     }
     __syncthreads();
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {
-      const int e = threadIdx.x + 256 * i, c = e >> 3, q = (e & 7) * 4;
+    for (int i = 0; i < kFinW / 16; ++i) {
+      const int e = threadIdx.x + 256 * i, c = e / (kFinW / 4), q = (e % (kFinW / 4)) * 4;
       if (w0 + q < W)
         *reinterpret_cast<float4*>(out + (((int64_t)b * 64 * D + (int64_t)c * D + d) * H + h) * W + w0 + q) =
             make_float4(tile[c][q], tile[c][q + 1], tile[c][q + 2], tile[c][q + 3]);
@@ -274,7 +279,7 @@ int vn_bn_relu_apply(const void* raw_bf16, int32_t B, int32_t D, int32_t H, int3
         reinterpret_cast<const uint4*>(raw_bf16), n_vec, scale, shift, reinterpret_cast<uint4*>(out));
     VN_LAUNCH_CHECK("k_bn_relu_apply_bf16");
   } else {
-    const int64_t want = (int64_t)B * D * H * ((W + 31) / 32);
+    const int64_t want = (int64_t)B * D * H * ((W + kFinW - 1) / kFinW);
     const int64_t cap = (int64_t)sm_count() * 16;
     k_bn_relu_apply_final<<<(unsigned)(want < cap ? want : cap), 256, 0, st>>>(
         reinterpret_cast<const __nv_bfloat16*>(raw_bf16), B, D, H, W, scale, shift, reinterpret_cast<float*>(out));

@@ -85,17 +85,18 @@ __global__ void __launch_bounds__(256)
   }
 }
 
-// dy in the final layout: f32 [B, 64*D, H, W], channel = c*D + d.  One block iteration = 32 consecutive w of one
-// (b,d,h): the 64 x 32 fp32 dy tile is read as 128-byte rows (float4 per thread) and transposed through shared
+// dy in the final layout: f32 [B, 64*D, H, W], channel = c*D + d.  One block iteration = kFinW consecutive w of one
+// (b,d,h): the 64 x kFinW fp32 dy tile is read as 256-byte rows (float4 per thread) and transposed through shared
 // memory; raw / draw move as 16-byte vectors (8 channels of one position per thread).  W % 4 == 0.
+constexpr int kFinW = 64;  // w positions per block iteration: 256-byte dy rows
 template <bool APPLY>
 __global__ void __launch_bounds__(256)
     k_bn_bwd_final(const __nv_bfloat16* __restrict__ raw, const float* __restrict__ dy, int B, int D, int H, int W,
                    const float* __restrict__ prm, double* __restrict__ sums, __nv_bfloat16* __restrict__ draw) {
-  __shared__ float tile[64][33];
+  __shared__ float tile[64][kFinW + 1];
   __shared__ float blk[128];
   if (threadIdx.x < 128) blk[threadIdx.x] = 0.0f;
-  const int p = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 8;  // compute role: position p, channels c0 .. c0+7
+  const int p0 = threadIdx.x >> 3, c0 = (threadIdx.x & 7) * 8;  // compute role: positions p0 + 32 i, channels c0 .. c0+7
   float s[8], t[8], mu[8], is[8], k1[8], k2[8], a1[8], a2[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -108,7 +109,7 @@ __global__ void __launch_bounds__(256)
     a1[j] = 0.0f;
     a2[j] = 0.0f;
   }
-  const int wblocks = (W + 31) / 32;
+  const int wblocks = (W + kFinW - 1) / kFinW;
   const int64_t n_blocks = (int64_t)B * D * H * wblocks;
   for (int64_t b_ = blockIdx.x; b_ < n_blocks; b_ += gridDim.x) {
     const int wb = (int)(b_ % wblocks);
@@ -116,45 +117,49 @@ __global__ void __launch_bounds__(256)
     const int h = (int)(r % H); r /= H;
     const int d = (int)(r % D);
     const int b = (int)(r / D);
-    const int w0 = wb * 32;
+    const int w0 = wb * kFinW;
     __syncthreads();
 #pragma unroll
-    for (int i = 0; i < 2; ++i) {  // 64 rows x 8 float4
-      const int e = threadIdx.x + 256 * i, cc = e >> 3, q = (e & 7) * 4;
+    for (int i = 0; i < kFinW / 16; ++i) {  // 64 rows x (kFinW / 4) float4
+      const int e = threadIdx.x + 256 * i, cc = e / (kFinW / 4), q = (e % (kFinW / 4)) * 4;
       float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
       if (w0 + q < W)
         v = *reinterpret_cast<const float4*>(dy + (((int64_t)b * 64 * D + (int64_t)cc * D + d) * H + h) * W + w0 + q);
       tile[cc][q] = v.x; tile[cc][q + 1] = v.y; tile[cc][q + 2] = v.z; tile[cc][q + 3] = v.w;
     }
     __syncthreads();
-    if (w0 + p < W) {
-      const int64_t off = ((((int64_t)b * D + d) * H + h) * W + w0 + p) * 64 + c0;
-      const uint4 rv = *reinterpret_cast<const uint4*>(raw + off);
-      const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
-      uint32_t o[4];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) {
-        const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
-        const float xs[2] = {x.x, x.y};
-        float dd[2];
+    for (int i = 0; i < kFinW / 32; ++i) {
+      const int p = p0 + 32 * i;
+      if (w0 + p < W) {
+        const int64_t off = ((((int64_t)b * D + d) * H + h) * W + w0 + p) * 64 + c0;
+        const uint4 rv = *reinterpret_cast<const uint4*>(raw + off);
+        const uint32_t rw[4] = {rv.x, rv.y, rv.z, rv.w};
+        uint32_t o[4];
 #pragma unroll
-        for (int hh = 0; hh < 2; ++hh) {
-          const int j = 2 * e + hh;
-          const float dz = fmaf(xs[hh], s[j], t[j]) > 0.0f ? tile[c0 + j][p] : 0.0f;
-          const float xh = (xs[hh] - mu[j]) * is[j];
+        for (int e = 0; e < 4; ++e) {
+          const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&rw[e]));
+          const float xs[2] = {x.x, x.y};
+          float dd[2];
+#pragma unroll
+          for (int hh = 0; hh < 2; ++hh) {
+            const int j = 2 * e + hh;
+            const float dz = fmaf(xs[hh], s[j], t[j]) > 0.0f ? tile[c0 + j][p] : 0.0f;
+            const float xh = (xs[hh] - mu[j]) * is[j];
+            if (APPLY) {
+              dd[hh] = s[j] * (dz - k1[j] - xh * k2[j]);
+            } else {
+              a1[j] += dz;
+              a2[j] = fmaf(dz, xh, a2[j]);
+            }
+          }
           if (APPLY) {
-            dd[hh] = s[j] * (dz - k1[j] - xh * k2[j]);
-          } else {
-            a1[j] += dz;
-            a2[j] = fmaf(dz, xh, a2[j]);
+            const __nv_bfloat162 rr = __floats2bfloat162_rn(dd[0], dd[1]);
+            o[e] = *reinterpret_cast<const uint32_t*>(&rr);
           }
         }
-        if (APPLY) {
-          const __nv_bfloat162 rr = __floats2bfloat162_rn(dd[0], dd[1]);
-          o[e] = *reinterpret_cast<const uint32_t*>(&rr);
-        }
+        if (APPLY) *reinterpret_cast<uint4*>(draw + off) = make_uint4(o[0], o[1], o[2], o[3]);
       }
-      if (APPLY) *reinterpret_cast<uint4*>(draw + off) = make_uint4(o[0], o[1], o[2], o[3]);
     }
   }
   if (!APPLY) {
@@ -649,7 +654,7 @@ int vn_bn_relu_bwd(const void* raw_bf16, const void* dy, int32_t dy_mode, int32_
       k_bn_bwd_ndhwc<false><<<grid, 256, 0, st>>>(reinterpret_cast<const uint4*>(raw_bf16), reinterpret_cast<const uint4*>(dy),
                                                   n_vec, prm, sums, nullptr);
   } else {
-    const int64_t want = (int64_t)B * D * H * ((W + 31) / 32);
+    const int64_t want = (int64_t)B * D * H * ((W + kFinW - 1) / kFinW);
     const unsigned grid = (unsigned)(want < cap ? want : cap);
     if (apply)
       k_bn_bwd_final<true><<<grid, 256, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(raw_bf16),
