@@ -204,6 +204,12 @@ def test_front_end_training_step_end_to_end(cuda_device):
         mod.zero_grad()
     out2 = fe.forward_points_train(points, offsets, max_n)
     assert rel_max_err(out2.detach().cpu(), out_ref.detach()) < 1e-2
+    # back to eval on the same front end: BN is re-folded from the running statistics the two steps updated
+    fnet.eval(), mnet.eval()
+    got_eval = fe.forward_points(points, offsets, max_n).clone()
+    fresh = vn.VoxelNetFrontEnd(fnet, mnet, target)
+    assert torch.equal(got_eval, fresh.forward_points(points, offsets, max_n))
+    assert int(fnet.vfe_1.bn.num_batches_tracked) == 2 and int(mnet.middle_layer[2].batch_norm.num_batches_tracked) == 2
 
 
 def test_training_step_with_an_empty_frame_and_through_the_host_stream(cuda_device):

@@ -231,6 +231,7 @@ class VoxelNetFrontEnd:
         n_frames = frame_offsets.numel() - 1
         self._ensure_buffers(n_frames, points.shape[0], points.device)
         self._clear_train_cells()
+        self._p1 = None  # running statistics (and soon the weights) change: the eval path re-folds on its next call
         if self.out_states is not None:
             for st in self.out_states:  # the eval path's resident outputs are not maintained here
                 st.fill_(0xFF)
