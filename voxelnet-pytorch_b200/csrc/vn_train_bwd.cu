@@ -338,7 +338,7 @@ struct SvfeBwdShared {
 __device__ __forceinline__ int w2k_index(int unit, int k) { return (unit >> 5) * (32 * 16 + 16) + (unit & 31) * 16 + k; }
 
 template <int PASS>
-__global__ void __launch_bounds__(kBwWarps * 32, PASS == 2 ? 1 : 2)
+__global__ void __launch_bounds__(kBwWarps * 32, 2)
     k_svfe_bwd(const float* __restrict__ feature, int64_t K, int T, const float* __restrict__ dvw,
                const float* __restrict__ w1, const float* __restrict__ b1, const float* __restrict__ w2,
                const float* __restrict__ b2, const float* __restrict__ bn1, const float* __restrict__ bn2,
