@@ -197,3 +197,35 @@ def test_host_frame_stream_matches_direct_forward(cuda_device):
         assert torch.equal(out, want[i]), i
     with pytest.raises(RuntimeError):
         stream.forward()
+
+
+def test_cuda_graph_replay_equals_eager(cuda_device):
+    """capture_graph / HostFrameStream(cuda_graphs=True): replays of the captured step give bit-identical tensors
+    and voxel counts to eager launches, with graphs of different batches interleaved."""
+    import voxelnet_pytorch_b200 as vn
+
+    sd = OM.random_state_dict(10)
+    fnet, mnet = vn.FeatureLearningNet("Pedestrian").eval(), vn.MiddleConvNet().eval()
+    load_state(fnet, sd, "")
+    load_state(mnet, sd, "")
+    fe = vn.VoxelNetFrontEnd(fnet.to(cuda_device), mnet.to(cuda_device), "Pedestrian")
+    sets = [[f[::5].copy() for f in synth_frames(2, s)] for s in (400, 410)]
+    packed = [vn.pack_frames(fr) for fr in sets]
+    packed.sort(key=lambda p: -p[0].shape[0])
+    want = [fe.forward_points(*p).clone() for p in packed]
+    graphs = [fe.capture_graph(*p) for p in packed]
+    for i in (0, 1, 1, 0, 1):
+        graphs[i].replay()
+        torch.cuda.synchronize()
+        assert torch.equal(fe.out, want[i]), i
+    hbs = [vn.PinnedFrameBatch.from_frames(fr) for fr in sets]
+    stream = vn.HostFrameStream(fe, 2, max(hb.n_points for hb in hbs), cuda_graphs=True)
+    ref = [fe.forward_frames(fr).clone() for fr in sets]
+    stream.upload(hbs[0])
+    for i in range(6):  # slots alternate: each (slot, batch) pair is seen eagerly once, then captured, then replayed
+        if i + 1 < 6:
+            stream.upload(hbs[(i + 1) % 2])
+        out = stream.forward()
+        stream.voxel_counts_host()
+        assert torch.equal(out, ref[i % 2]), i
+    assert len(stream._graphs) == 2 and not torch.equal(ref[0], ref[1])
