@@ -41,6 +41,29 @@ CONFIGS = {
 }
 
 # dense-equivalent conv FLOPs per frame (padding taps counted)
+_RESULT_FD = None
+
+
+def quiet_stdout() -> None:
+    """stdout carries exactly ONE line - the JSON result.  Libraries write there too (NCCL prints its version banner
+    on stdout at communicator creation), so file descriptor 1 is pointed at stderr for the run and the result goes
+    to a duplicate of the original stdout."""
+    global _RESULT_FD
+    if _RESULT_FD is None:
+        sys.stdout.flush()
+        _RESULT_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict) -> None:
+    data = (json.dumps(line) + "\n").encode()
+    if _RESULT_FD is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_RESULT_FD, data)
+
+
 def conv_flops_per_frame(D, H, W):
     d1 = (D + 2 - 3) // 2 + 1
     d2 = d1 - 2
@@ -186,7 +209,7 @@ def run_reference(args, rank, world):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_train(args, rank, world, local_rank, dev):
@@ -284,7 +307,7 @@ def run_train(args, rank, world, local_rank, dev):
         "dense_equivalent_conv_tflops": 3 * flops * batch / (ms_max / args.steps / 1e3) / 1e12,
         "clocks": clocks, "gpu_launches": launches,
     }
-    print(json.dumps(line))
+    emit(line)
 
 
 def main():
@@ -303,6 +326,7 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    quiet_stdout()
 
     if args.impl == "reference":
         run_reference(args, rank, world)
@@ -579,7 +603,7 @@ def main():
                           "(numpy voxelizer with per-point loop + torch-CPU VFE/scatter/Conv3d)" % cpu["frames"],
                 "mean_s_per_frame": cpu["mean_s"], "stages_mean_s": cpu["stages_mean_s"], "host_cpus": cpu["host_cpus"],
             }
-        print(json.dumps(line), flush=True)
+        emit(line)
 
     if world > 1:
         dist.destroy_process_group()
