@@ -478,12 +478,19 @@ def main():
     stream = HostFrameStream(fe, batch, host_batches[0].n_points, cuda_graphs=not args.no_cuda_graph)
 
     def e2e_run(n):
+        # every step: H2D of its points (on the copy stream, overlapping the previous step), the step itself, and a
+        # D2H read of its per-frame voxel counts.  The host consumes the counts of step i-1 while step i runs (one
+        # step of latency, the device queue never drains) and the last step's before the clock stops.
         stream.upload(host_batches[0])
+        seen = 0
         for i in range(n):
             if i + 1 < n:
                 stream.upload(host_batches[(i + 1) % 2])
             stream.forward()
-            stream.voxel_counts_host()  # the caller consumes the per-frame voxel counts every step (synchronises)
+            if i > 0:
+                seen += int(stream.voxel_counts_host(lag=1)[-1])
+        seen += int(stream.voxel_counts_host()[-1])
+        return seen
 
     e2e_run(4)  # (with CUDA graphs: each staging slot's step is captured on its second visit)
     barrier()
@@ -582,7 +589,7 @@ def main():
                     "h2d_bytes_per_step": int(sum(bt.host_points.numel() * 4 + bt.host_offsets.numel() * 4 for bt in batches) / 2),
                     "d2h_bytes_per_step": int(host_counts.numel() * 4),
                     "note": "through voxelnet_pytorch_b200.HostFrameStream: H2D of step i+1 overlaps step i on a copy stream (two staging buffers); result read back per step = "
-                            "per-frame voxel counts; the (B,128,H,W) tensor stays on the device for the RPN"},
+                            "per-frame voxel counts (consumed one step later, the last one before the clock stops); the (B,128,H,W) tensor stays on the device for the RPN"},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
                          "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": traffic,

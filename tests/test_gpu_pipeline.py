@@ -229,3 +229,36 @@ def test_cuda_graph_replay_equals_eager(cuda_device):
         stream.voxel_counts_host()
         assert torch.equal(out, ref[i % 2]), i
     assert len(stream._graphs) == 2 and not torch.equal(ref[0], ref[1])
+
+
+def test_host_stream_lagged_counts(cuda_device):
+    """voxel_counts_host(lag=1) returns the previous step's counts without waiting for the running step."""
+    import voxelnet_pytorch_b200 as vn
+
+    sd = OM.random_state_dict(11)
+    fnet, mnet = vn.FeatureLearningNet("Pedestrian").eval(), vn.MiddleConvNet().eval()
+    load_state(fnet, sd, "")
+    load_state(mnet, sd, "")
+    fe = vn.VoxelNetFrontEnd(fnet.to(cuda_device), mnet.to(cuda_device), "Pedestrian")
+    sets = [[f[::6].copy() for f in synth_frames(2, s)] for s in (500, 510, 520)]
+    want = []
+    for fr in sets:
+        fe.forward_frames(fr)
+        want.append(fe.voxel_counts())
+    hbs = [vn.PinnedFrameBatch.from_frames(fr) for fr in sets]
+    stream = vn.HostFrameStream(fe, 2, max(hb.n_points for hb in hbs))
+    with pytest.raises(RuntimeError):
+        stream.voxel_counts_host()
+    stream.upload(hbs[0])
+    got = []
+    for i in range(3):
+        if i + 1 < 3:
+            stream.upload(hbs[i + 1])
+        stream.forward()
+        if i == 0:
+            with pytest.raises(RuntimeError):
+                stream.voxel_counts_host(lag=1)
+        else:
+            got.append(stream.voxel_counts_host(lag=1).tolist())
+    got.append(stream.voxel_counts_host().tolist())
+    assert got == want

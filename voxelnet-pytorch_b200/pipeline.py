@@ -331,7 +331,10 @@ class HostFrameStream:
             e.record(torch.cuda.current_stream(dev))
         self.pending = []  # (slot, n_points, max_points_per_frame)
         self.next_slot = 0
-        self.host_counts = torch.empty(n_frames + 1, dtype=torch.int32).pin_memory()
+        # per-frame voxel prefix of the last two steps (pinned), each with the event that marks its D2H copy done
+        self._counts = [torch.zeros(n_frames + 1, dtype=torch.int32).pin_memory() for _ in range(2)]
+        self._counts_done = [torch.cuda.Event() for _ in range(2)]
+        self._steps = 0
         self.h2d_bytes = 0
 
     def upload(self, batch) -> None:
@@ -370,10 +373,22 @@ class HostFrameStream:
             fn = self.fe.forward_points_train if training else self.fe.forward_points
             out = fn(pts[:n], offs, max_n, timer=timer)
         self.freed[k].record(main)
-        self.host_counts.copy_(self.fe.voxels.voxel_offsets, non_blocking=True)
+        slot = self._steps % 2
+        self._counts[slot].copy_(self.fe.voxels.voxel_offsets, non_blocking=True)
+        self._counts_done[slot].record(main)
+        self._steps += 1
         return out
 
-    def voxel_counts_host(self) -> torch.Tensor:
-        """Blocking: the per-frame voxel prefix (B+1,) int32 of the last forward(), in pinned host memory."""
-        torch.cuda.current_stream(self.device).synchronize()
-        return self.host_counts
+    @property
+    def host_counts(self) -> torch.Tensor:
+        return self._counts[(self._steps - 1) % 2]
+
+    def voxel_counts_host(self, lag: int = 0) -> torch.Tensor:
+        """The per-frame voxel prefix (B+1,) int32, in pinned host memory, of the last forward() (lag 0) or of the
+        one before (lag 1).  Blocks only until THAT step's device->host copy is done: with lag 1 the device queue
+        never drains while the host reads results (one step of latency for the consumer)."""
+        if lag not in (0, 1) or self._steps - lag < 1:
+            raise RuntimeError("voxel_counts_host(lag=%d): no such step yet" % lag)
+        slot = (self._steps - 1 - lag) % 2
+        self._counts_done[slot].synchronize()
+        return self._counts[slot]
