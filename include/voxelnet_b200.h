@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 8
+#define VN_ABI_VERSION 9
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -177,6 +177,7 @@ size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W);
 
 #define VN_CONV_FLAGS_CONSUME 1     /* reset every flag that was read, leaving the table all-zero again */
 #define VN_CONV_FLAGS_BORDER_RING 2 /* also treat boxes that contain an H/W border position as live    */
+#define VN_CONV_FLAGS_PLANNED 4     /* the work plan in `workspace` was built by vn_conv3d_plan already    */
 
 /* x: [B, Din, H, W, cin] bf16 (NDHWC).  cin in {64, 128}, cout = 64, kernel 3x3x3, H/W stride 1 and
  * padding 1; depth stride/padding (stride_d, pad_d) in {(2,1), (1,0)}; Din <= 10, W % 8 == 0.
@@ -260,6 +261,15 @@ int vn_bn_relu_apply(const void* raw_bf16, int32_t B, int32_t D, int32_t H, int3
 int vn_svfe_batch_stats(const float* feature, int64_t K, int32_t T, const int32_t* n_voxels_dev,
                         int32_t stage, const float* w1, const float* b1, const float* s1, const float* t1,
                         const float* w2, const float* b2, double* sums, vn_stream_t stream);
+
+/* The planning step of vn_conv3d_bn_relu_fwd on its own: reads (and with VN_CONV_FLAGS_CONSUME resets) the live-box
+ * table, updates the output state table and writes the work plan into `workspace`.  It depends on the voxel
+ * coordinates only, not on the layer input, so the plans of all three layers can be built while an earlier layer
+ * still computes (another stream / a parallel branch of a CUDA graph); the forward call then gets the same
+ * box_flags / out_state / workspace and flag_opts | VN_CONV_FLAGS_PLANNED. */
+int vn_conv3d_plan(int32_t B, int32_t Din, int32_t H, int32_t W, int32_t stride_d, int32_t pad_d,
+                   uint8_t* box_flags, int32_t flag_opts, uint8_t* out_state, void* workspace,
+                   size_t workspace_bytes, vn_stream_t stream);
 
 /* Data gradient of a middle layer with 64 input channels (layers 2 and 3): dx [B, Din_fwd, H, W, 64] bf16 from
  * dy [B, Dout_fwd, H, W, 64] bf16 - the forward tcgen05 kernel run on the transposed depth geometry.

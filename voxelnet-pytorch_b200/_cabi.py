@@ -14,9 +14,10 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 8
+VN_ABI_VERSION = 9
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
+VN_CONV_FLAGS_PLANNED = 4
 
 
 class VnGrid(C.Structure):
@@ -55,6 +56,7 @@ PROTOTYPES = {
     "vn_conv3d_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "vn_conv3d_out_state_bytes": (_sz, [_i32, _i32, _i32]),
     "vn_conv3d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _i32, _p, _p, _i32, _p, _p, _sz, _p]),
+    "vn_conv3d_plan": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _sz, _p]),
     "vn_conv3d_fold_background": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p]),
     "vn_conv3d_mark_boxes": (C.c_int, [_p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p]),
     "vn_conv3d_raw_stats_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _sz, _p]),

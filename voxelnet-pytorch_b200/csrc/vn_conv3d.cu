@@ -1036,9 +1036,11 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
     set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
     return VN_ERR_UNSUPPORTED;
   }
-  VN_CUDA(cudaMemsetAsync(hdr, 0, sizeof(PlanHeader), st));
-  k_conv3d_plan<<<B * tiles_h, 64, 0, st>>>(Q);
-  VN_LAUNCH_CHECK("k_conv3d_plan");
+  if (!(flag_opts & VN_CONV_FLAGS_PLANNED)) {  // else: vn_conv3d_plan already built the plan in this workspace
+    VN_CUDA(cudaMemsetAsync(hdr, 0, sizeof(PlanHeader), st));
+    k_conv3d_plan<<<B * tiles_h, 64, 0, st>>>(Q);
+    VN_LAUNCH_CHECK("k_conv3d_plan");
+  }
 
   ConvParams P{};
   P.B = B; P.Din = Din; P.Dout = Dout; P.H = H; P.W = W;
@@ -1076,6 +1078,45 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
                           vn_stream_t stream) {
   return conv_launch(x, B, Din, H, W, cin, stride_d, pad_d, packed_weight, scale, shift_table, n_variants, sub, out_mode, y,
                      box_flags, flag_opts, out_state, workspace, workspace_bytes, stream, nullptr);
+}
+
+int vn_conv3d_plan(int32_t B, int32_t Din, int32_t H, int32_t W, int32_t stride_d, int32_t pad_d, uint8_t* box_flags,
+                   int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(B >= 1 && Din >= 1 && Din <= kMaxPlanes && H >= 1 && W >= 1, "conv3d_plan: bad shape");
+  VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d_plan: stride_d=%d pad_d=%d unsupported",
+             stride_d, pad_d);
+  VN_REQUIRE(W % kTileW == 0 && W / kTileW <= kMaxTilesW, "conv3d_plan: W=%d must be a multiple of %d, at most %d", W, kTileW,
+             kTileW * kMaxTilesW);
+  const int Dout = out_depth(Din, stride_d, pad_d);
+  VN_REQUIRE(Din + 2 * pad_d >= 3 && Dout >= 1 && Dout <= kSlots, "conv3d_plan: Dout=%d outside [1,%d]", Dout, kSlots);
+  VN_REQUIRE(workspace != nullptr && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "conv3d_plan: workspace missing or misaligned");
+  const int tiles_h = (H + kTileH - 1) / kTileH, tiles_w = W / kTileW;
+  const int64_t n_tiles = (int64_t)B * tiles_h * tiles_w;
+  VN_REQUIRE(n_tiles < (int64_t)0x7fffffff, "conv3d_plan: too many tiles");
+  const PlanLayout L = plan_layout(n_tiles);
+  if (workspace_bytes < L.total) {
+    set_error("conv3d_plan: workspace %zu < %zu bytes", workspace_bytes, L.total);
+    return VN_ERR_WORKSPACE;
+  }
+  uint8_t* ws = static_cast<uint8_t*>(workspace);
+  PlanParams Q{};
+  Q.B = B; Q.Din = Din; Q.Dout = Dout; Q.H = H; Q.W = W; Q.tiles_h = tiles_h; Q.tiles_w = tiles_w;
+  Q.box_flags = box_flags;
+  Q.consume = (flag_opts & VN_CONV_FLAGS_CONSUME) ? 1 : 0;
+  Q.force_ring = (flag_opts & VN_CONV_FLAGS_BORDER_RING) ? 1 : 0;
+  Q.out_state = out_state;
+  Q.hdr = reinterpret_cast<PlanHeader*>(ws);
+  Q.groups = reinterpret_cast<GroupDesc*>(ws + L.groups_off);
+  Q.tiles = reinterpret_cast<TilePlan*>(ws + L.tiles_off);
+  if (plan_planes(Q, stride_d, pad_d) != 0) {
+    set_error("conv3d_plan: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
+    return VN_ERR_UNSUPPORTED;
+  }
+  cudaStream_t st = as_stream(stream);
+  VN_CUDA(cudaMemsetAsync(Q.hdr, 0, sizeof(PlanHeader), st));
+  k_conv3d_plan<<<B * tiles_h, 64, 0, st>>>(Q);
+  VN_LAUNCH_CHECK("k_conv3d_plan");
+  return VN_OK;
 }
 
 int vn_conv3d_dgrad(const void* dy, int32_t B, int32_t Dout_fwd, int32_t H, int32_t W, int32_t Din_fwd, int32_t stride_d,

@@ -296,9 +296,20 @@ def conv3d_fold_background(weight, din: int, stride_d: int, pad_d: int, scale, s
     return table, bg_out
 
 
+def conv3d_plan(B: int, Din: int, H: int, W: int, stride_d: int, pad_d: int, box_flags, workspace, consume_flags: bool = False,
+                border_ring: bool = False, out_state=None) -> None:
+    """Build the work plan of a conv3d_bn_relu_fwd call ahead of time (it depends on the voxel coordinates only);
+    pass the same box_flags / out_state / workspace and planned=True to the forward call."""
+    _require_cuda(box_flags, workspace, out_state)
+    opts = (_cabi.VN_CONV_FLAGS_CONSUME if consume_flags else 0) | (_cabi.VN_CONV_FLAGS_BORDER_RING if border_ring else 0)
+    with torch.cuda.device(workspace.device):
+        check(_cabi.lib().vn_conv3d_plan(B, Din, H, W, stride_d, pad_d, _ptr(box_flags), opts, _ptr(out_state), _ptr(workspace),
+                                         workspace.numel(), _stream()), "vn_conv3d_plan")
+
+
 def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int, final: bool = False, out=None,
                        box_flags=None, consume_flags: bool = False, border_ring: bool = False, sub=None, workspace=None,
-                       out_state=None):
+                       out_state=None, planned: bool = False):
     """x (B,Din,H,W,cin) bf16 NDHWC -> (B,Dout,H,W,64) bf16, or with final=True the reference's
     reshaped (B, 64*Dout, H, W) f32 (model.py:262).
 
@@ -337,6 +348,8 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
     if workspace is None:
         workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
     opts = (_cabi.VN_CONV_FLAGS_CONSUME if consume_flags else 0) | (_cabi.VN_CONV_FLAGS_BORDER_RING if border_ring else 0)
+    if planned:
+        opts |= _cabi.VN_CONV_FLAGS_PLANNED
     with torch.cuda.device(x.device):
         check(
             _cabi.lib().vn_conv3d_bn_relu_fwd(

@@ -85,6 +85,9 @@ class VoxelNetFrontEnd:
         # voxel can reach now or could reach in the previous step (those are rewritten with the layer's
         # background constant).  Everything else already holds that constant - bit-identical result.
         self.resident_outputs = bool(resident_outputs) and self.skip_empty_boxes
+        # True: conv-2/3 planning and the grid re-zeroing run on a side stream next to conv-1 / conv-2 (when no
+        # StageTimer is attached: stage times are measured on the serial launch order)
+        self.overlap_small_kernels = True
         self._shape = None
         self._layer_geometry = [(l.stride[0], l.padding[0]) for l in middle_net.middle_layer]
         self.refresh_parameters()
@@ -184,7 +187,36 @@ class VoxelNetFrontEnd:
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
         ws0, ws1, ws2 = self.conv_workspaces
         st0, st1, st2 = self.out_states if self.out_states is not None else (None, None, None)
-        if self.skip_empty_boxes:
+        if self.skip_empty_boxes and timer is None and self.overlap_small_kernels:
+            # Same launches as the serial branch below, with the small latency-bound kernels off the critical path:
+            # the work plans of conv-2/3 depend on the voxel coordinates only and are built on a side stream while
+            # conv-1 runs; the re-zeroing of the grid cells runs there next to conv-2.  (Fork / join by events: a
+            # CUDA graph captured from this call keeps the branches parallel.)
+            f0, f1, f2 = self.box_flags
+            B, H, W = n_frames, self.cfg.height, self.cfg.width
+            main = torch.cuda.current_stream(points.device)
+            aux = self._aux_stream(points.device)
+            ev = self._events
+            ev[0].record(main)
+            aux.wait_event(ev[0])
+            with torch.cuda.stream(aux):
+                ops.conv3d_plan(B, self.act1.shape[1], H, W, 1, 0, f1, ws1, consume_flags=True, out_state=st1)
+                ops.conv3d_plan(B, self.act2.shape[1], H, W, 2, 1, f2, ws2, consume_flags=True, border_ring=True, out_state=st2)
+                ev[1].record(aux)
+            ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=f0, consume_flags=True,
+                                   sub=self._bg[0], workspace=ws0, out_state=st0)
+            ev[2].record(main)
+            with torch.cuda.stream(aux):
+                aux.wait_event(ev[2])
+                ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+                ev[3].record(aux)
+            main.wait_event(ev[1])
+            ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
+                                   consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
+            ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
+                                   consume_flags=True, border_ring=True, workspace=ws2, out_state=st2, planned=True)
+            main.wait_event(ev[3])  # join: the next step's grid writes come after the clear
+        elif self.skip_empty_boxes:
             f0, f1, f2 = self.box_flags
             with span("conv1"):  # zero background in, deviation from relu(shift) out
                 ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=f0, consume_flags=True,
@@ -207,6 +239,12 @@ class VoxelNetFrontEnd:
             with span("conv3"):
                 ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out, workspace=ws2)
         return self.out
+
+    def _aux_stream(self, device):
+        if getattr(self, "_aux", None) is None or self._aux.device != device:
+            self._aux = torch.cuda.Stream(device=device)
+            self._events = [torch.cuda.Event() for _ in range(4)]
+        return self._aux
 
     def capture_graph(self, points: torch.Tensor, frame_offsets: torch.Tensor, max_points_per_frame: int):
         """Capture one eval-mode step on these (static) input buffers into a CUDA graph; `graph.replay()` then
