@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 9
+#define VN_ABI_VERSION 10
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -127,6 +127,22 @@ int vn_svfe_fused_fwd(const float* feature, int64_t K, int32_t T, const int32_t*
  * vn_scatter_dense_bf16), or both; one of the two may be NULL.  The [K,T,7] feature buffer is never
  * materialised; results are bit-identical to vn_voxelize_fill + vn_svfe_fused_fwd (+ scatter). */
 int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                           int32_t n_frames, int64_t n_points_total, const int32_t* voxel_offsets,
+                           int64_t max_voxels, const float* w1, const float* b1, const float* s1,
+                           const float* t1, const float* w2, const float* b2, const float* s2,
+                           const float* t2, float* voxelwise, void* dense_bf16,
+                           int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace,
+                           size_t workspace_bytes, vn_stream_t stream);
+
+/* The same in two calls, for pipelines that want the voxel coordinates early: vn_voxelize_bucket_coords does the
+ * bucketing and writes coordinate_buffer [max_voxels,4] (everything that depends on the coordinates only - live-box
+ * marking, conv planning - can then run on another stream next to the SVFE kernel); vn_voxelize_svfe_bucketed is
+ * vn_voxelize_svfe_fused without the bucketing step and must follow it on the same workspace. */
+int vn_voxelize_bucket_coords(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                              int32_t n_frames, int64_t n_points_total, const int32_t* voxel_offsets,
+                              int64_t max_voxels, int64_t* coordinate_buffer, void* workspace,
+                              size_t workspace_bytes, vn_stream_t stream);
+int vn_voxelize_svfe_bucketed(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
                            int32_t n_frames, int64_t n_points_total, const int32_t* voxel_offsets,
                            int64_t max_voxels, const float* w1, const float* b1, const float* s1,
                            const float* t1, const float* w2, const float* b2, const float* s2,

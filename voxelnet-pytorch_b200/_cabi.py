@@ -14,7 +14,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 9
+VN_ABI_VERSION = 10
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 VN_CONV_FLAGS_PLANNED = 4
@@ -47,6 +47,8 @@ PROTOTYPES = {
     "vn_feature_mask": (C.c_int, [_p, _i64, _i32, _i32, _p, _p]),
     "vn_svfe_fused_fwd": (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "vn_voxelize_svfe_fused": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vn_voxelize_svfe_bucketed": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vn_voxelize_bucket_coords": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _sz, _p]),
     "vn_fill_zero": (C.c_int, [_p, _sz, _p]),
     "vn_scatter_dense_f32": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p]),
     "vn_scatter_dense_bf16": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p]),

@@ -678,6 +678,20 @@ int check_common(const vn_grid_t* grid, const void* points, const int32_t* frame
   return VN_OK;
 }
 
+// Coordinates of every voxel row right after the bucketing (one thread per row: the voxel's cell is the cell of
+// the first point of its bucket).  The fused voxel->SVFE kernel writes the same values again later; having them
+// early lets everything that depends on the coordinates only (live-box marking, conv planning) run next to it.
+__global__ void __launch_bounds__(256) k_vox_coords(const vn_grid_t g, const float4* __restrict__ points, int n_frames,
+                                                   const int32_t* __restrict__ voxel_offsets, int64_t max_voxels,
+                                                   const int32_t* __restrict__ seg, const int32_t* __restrict__ pidx,
+                                                   long long* __restrict__ coords) {
+  int64_t total = voxel_offsets[n_frames];
+  if (total > max_voxels) total = max_voxels;
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+  for (int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; row < total; row += stride)
+    write_coords(g, points[pidx[seg[row]]], n_frames, voxel_offsets, row, coords);
+}
+
 // P5 + P6: CSR segments per voxel and the bucketed point indices.
 int launch_bucket(const VoxWorkspace& w, const int32_t* frame_offsets, int n_frames, int64_t n_points_total,
                   const int32_t* voxel_offsets, int T, cudaStream_t st) {
@@ -768,12 +782,12 @@ int vn_voxelize_fill(const vn_grid_t* grid, const float* points, const int32_t* 
   return VN_OK;
 }
 
-int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
+static int svfe_fused_impl(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
                            int64_t n_points_total, const int32_t* voxel_offsets, int64_t max_voxels, const float* w1,
                            const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
                            const float* s2, const float* t2, float* voxelwise, void* dense_bf16,
                            int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace, size_t workspace_bytes,
-                           vn_stream_t stream) {
+                           vn_stream_t stream, bool bucketed) {
   int rc = check_common(grid, points, frame_offsets, n_frames, n_points_total, workspace, workspace_bytes);
   if (rc != VN_OK) return rc;
   VN_REQUIRE(voxel_offsets != nullptr, "voxelize_svfe_fused: voxel_offsets is null");
@@ -785,8 +799,10 @@ int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int
              "voxelize_svfe_fused: misaligned output");
   cudaStream_t st = as_stream(stream);
   const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
-  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, grid->T, st);
-  if (rc != VN_OK) return rc;
+  if (!bucketed) {  // else vn_voxelize_bucket_coords ran: segments, buckets and the zeroed work counters are in place
+    rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, grid->T, st);
+    if (rc != VN_OK) return rc;
+  }
   const int T = grid->T;
   const size_t rows_bytes = ((size_t)(T + 1) * 7 * 4 + 15) & ~(size_t)15;
   const size_t slow = (size_t)T * 16 + rows_bytes + (size_t)(T + 1) * kXS * 4;
@@ -801,6 +817,50 @@ int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int
       reinterpret_cast<long long*>(coordinate_buffer), reinterpret_cast<long long*>(number_buffer), w.counters,
       w.biglist);
   VN_LAUNCH_CHECK("k_vox_svfe_packed");
+  return VN_OK;
+}
+
+int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
+                           int64_t n_points_total, const int32_t* voxel_offsets, int64_t max_voxels, const float* w1,
+                           const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
+                           const float* s2, const float* t2, float* voxelwise, void* dense_bf16,
+                           int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace, size_t workspace_bytes,
+                           vn_stream_t stream) {
+  return svfe_fused_impl(grid, points, frame_offsets, n_frames, n_points_total, voxel_offsets, max_voxels, w1, b1, s1, t1, w2,
+                         b2, s2, t2, voxelwise, dense_bf16, coordinate_buffer, number_buffer, workspace, workspace_bytes,
+                         stream, false);
+}
+
+int vn_voxelize_svfe_bucketed(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
+                              int64_t n_points_total, const int32_t* voxel_offsets, int64_t max_voxels, const float* w1,
+                              const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
+                              const float* s2, const float* t2, float* voxelwise, void* dense_bf16,
+                              int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace,
+                              size_t workspace_bytes, vn_stream_t stream) {
+  return svfe_fused_impl(grid, points, frame_offsets, n_frames, n_points_total, voxel_offsets, max_voxels, w1, b1, s1, t1, w2,
+                         b2, s2, t2, voxelwise, dense_bf16, coordinate_buffer, number_buffer, workspace, workspace_bytes,
+                         stream, true);
+}
+
+int vn_voxelize_bucket_coords(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
+                              int64_t n_points_total, const int32_t* voxel_offsets, int64_t max_voxels,
+                              int64_t* coordinate_buffer, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  int rc = check_common(grid, points, frame_offsets, n_frames, n_points_total, workspace, workspace_bytes);
+  if (rc != VN_OK) return rc;
+  VN_REQUIRE(voxel_offsets != nullptr && max_voxels >= 0, "voxelize_bucket_coords: bad argument");
+  if (max_voxels == 0 || n_points_total == 0) return VN_OK;
+  VN_REQUIRE(coordinate_buffer != nullptr && (reinterpret_cast<uintptr_t>(coordinate_buffer) & 15) == 0,
+             "voxelize_bucket_coords: coordinate_buffer null or misaligned");
+  cudaStream_t st = as_stream(stream);
+  const VoxWorkspace w = carve(*grid, n_frames, n_points_total, workspace);
+  rc = launch_bucket(w, frame_offsets, n_frames, n_points_total, voxel_offsets, grid->T, st);
+  if (rc != VN_OK) return rc;
+  const int64_t want = (max_voxels + 255) / 256;
+  const int64_t cap = (int64_t)sm_count() * 8;
+  k_vox_coords<<<(unsigned)(want < cap ? want : cap), 256, 0, st>>>(*grid, reinterpret_cast<const float4*>(points), n_frames,
+                                                                  voxel_offsets, max_voxels, w.seg, w.pidx,
+                                                                  reinterpret_cast<long long*>(coordinate_buffer));
+  VN_LAUNCH_CHECK("k_vox_coords");
   return VN_OK;
 }
 

@@ -140,8 +140,23 @@ def svfe_fused_fwd(feature, p1, p2, out=None, n_voxels_dev=None) -> torch.Tensor
     return out
 
 
+def voxelize_bucket_coords(grid, points, frame_offsets, voxel_offsets, coords, workspace) -> None:
+    """Bucketing step of voxelizer phase 2 + the (cap,4) i64 voxel coordinates, ahead of voxelize_svfe_fused(...,
+    bucketed=True): what depends on the coordinates only can then run next to the SVFE kernel."""
+    _require_cuda(points, frame_offsets, voxel_offsets, coords, workspace)
+    _contig(coords, torch.int64)
+    n_frames = frame_offsets.numel() - 1
+    with torch.cuda.device(points.device):
+        check(
+            _cabi.lib().vn_voxelize_bucket_coords(C.byref(grid), _ptr(points), _ptr(frame_offsets), n_frames, points.shape[0],
+                                                  _ptr(voxel_offsets), coords.shape[0], _ptr(coords), _ptr(workspace),
+                                                  workspace.numel() * workspace.element_size(), _stream()),
+            "vn_voxelize_bucket_coords",
+        )
+
+
 def voxelize_svfe_fused(grid, points, frame_offsets, voxel_offsets, p1, p2, voxelwise, coords, counts, workspace,
-                        dense=None) -> None:
+                        dense=None, bucketed: bool = False) -> None:
     """Voxelizer phase 2 fused with the stacked VFE: writes coords (cap,4) i64 (counts optional) and the
     voxel-wise maxima - as voxelwise (cap,128) f32 and/or straight into the resident bf16 grid
     `dense` (B,D,H,W,128) - without materialising the (K,T,7) feature buffer."""
@@ -158,9 +173,10 @@ def voxelize_svfe_fused(grid, points, frame_offsets, voxel_offsets, p1, p2, voxe
         _contig(dense, torch.bfloat16)
         if tuple(dense.shape) != (n_frames, grid.D, grid.H, grid.W, 128):
             raise RuntimeError("dense must be (B,D,H,W,128) bf16 for this grid; got %s" % (tuple(dense.shape),))
+    fn = _cabi.lib().vn_voxelize_svfe_bucketed if bucketed else _cabi.lib().vn_voxelize_svfe_fused
     with torch.cuda.device(points.device):
         check(
-            _cabi.lib().vn_voxelize_svfe_fused(
+            fn(
                 C.byref(grid), _ptr(points), _ptr(frame_offsets), n_frames, points.shape[0], _ptr(voxel_offsets),
                 coords.shape[0], *[_ptr(_contig(t, torch.float32)) for t in p1],
                 *[_ptr(_contig(t, torch.float32)) for t in p2], _ptr(voxelwise), _ptr(dense), _ptr(coords), _ptr(counts),

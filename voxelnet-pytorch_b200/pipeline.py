@@ -165,7 +165,33 @@ class VoxelNetFrontEnd:
         vb = self.voxels
         span = timer.span if timer is not None else (lambda stage: _NO_SPAN)
         k_dev = vb.n_voxels_dev
-        if self.fuse_voxel_features:
+        overlap = self.skip_empty_boxes and timer is None and self.overlap_small_kernels
+        early = overlap and self.fuse_voxel_features
+        if early:
+            # coordinates right after the bucketing; live-box marking and the three conv plans then run on the side
+            # stream next to the SVFE kernel
+            ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
+            ops.voxelize_bucket_coords(self.grid, points, frame_offsets, vb.voxel_offsets, vb.coordinate, self.workspace)
+            main = torch.cuda.current_stream(points.device)
+            aux = self._aux_stream(points.device)
+            ev = self._events
+            ev[4].record(main)
+            with torch.cuda.stream(aux):
+                aux.wait_event(ev[4])
+                ops.conv3d_mark_boxes(vb.coordinate, n_frames, self.cfg.depth, self.cfg.height, self.cfg.width,
+                                      self._layer_geometry, self.box_flags, n_voxels_dev=k_dev)
+                st_ = self.out_states if self.out_states is not None else (None, None, None)
+                B_, H_, W_ = n_frames, self.cfg.height, self.cfg.width
+                ops.conv3d_plan(B_, self.cfg.depth, H_, W_, 2, 1, self.box_flags[0], self.conv_workspaces[0], consume_flags=True,
+                                out_state=st_[0])
+                ops.conv3d_plan(B_, self.act1.shape[1], H_, W_, 1, 0, self.box_flags[1], self.conv_workspaces[1],
+                                consume_flags=True, out_state=st_[1])
+                ops.conv3d_plan(B_, self.act2.shape[1], H_, W_, 2, 1, self.box_flags[2], self.conv_workspaces[2],
+                                consume_flags=True, border_ring=True, out_state=st_[2])
+                ev[1].record(aux)
+            ops.voxelize_svfe_fused(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2,
+                                    None, vb.coordinate, None, self.workspace, dense=self.dense, bucketed=True)
+        elif self.fuse_voxel_features:
             with span("voxelize"):  # crop, cell keys, occupancy bitmap, ranks, per-voxel buckets
                 ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
             with span("svfe"):      # bucket -> first-T selection -> 7-d rows on chip -> VFE-1/VFE-2/max -> grid cell
@@ -181,13 +207,13 @@ class VoxelNetFrontEnd:
         with span("scatter"):
             if not self.fuse_voxel_features:  # (the fused kernel wrote the grid cells itself)
                 ops.scatter_dense_bf16(self.voxelwise, vb.coordinate, self.dense, clear=False, n_voxels_dev=k_dev)
-            if self.skip_empty_boxes:
+            if self.skip_empty_boxes and not early:
                 ops.conv3d_mark_boxes(vb.coordinate, n_frames, self.cfg.depth, self.cfg.height, self.cfg.width,
                                       self._layer_geometry, self.box_flags, n_voxels_dev=k_dev)
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
         ws0, ws1, ws2 = self.conv_workspaces
         st0, st1, st2 = self.out_states if self.out_states is not None else (None, None, None)
-        if self.skip_empty_boxes and timer is None and self.overlap_small_kernels:
+        if overlap:
             # Same launches as the serial branch below, with the small latency-bound kernels off the critical path:
             # the work plans of conv-2/3 depend on the voxel coordinates only and are built on a side stream while
             # conv-1 runs; the re-zeroing of the grid cells runs there next to conv-2.  (Fork / join by events: a
@@ -197,20 +223,24 @@ class VoxelNetFrontEnd:
             main = torch.cuda.current_stream(points.device)
             aux = self._aux_stream(points.device)
             ev = self._events
-            ev[0].record(main)
-            aux.wait_event(ev[0])
-            with torch.cuda.stream(aux):
-                ops.conv3d_plan(B, self.act1.shape[1], H, W, 1, 0, f1, ws1, consume_flags=True, out_state=st1)
-                ops.conv3d_plan(B, self.act2.shape[1], H, W, 2, 1, f2, ws2, consume_flags=True, border_ring=True, out_state=st2)
-                ev[1].record(aux)
+            if early:  # all three plans were built next to the SVFE kernel
+                main.wait_event(ev[1])
+            else:
+                ev[0].record(main)
+                aux.wait_event(ev[0])
+                with torch.cuda.stream(aux):
+                    ops.conv3d_plan(B, self.act1.shape[1], H, W, 1, 0, f1, ws1, consume_flags=True, out_state=st1)
+                    ops.conv3d_plan(B, self.act2.shape[1], H, W, 2, 1, f2, ws2, consume_flags=True, border_ring=True, out_state=st2)
+                    ev[1].record(aux)
             ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=f0, consume_flags=True,
-                                   sub=self._bg[0], workspace=ws0, out_state=st0)
+                                   sub=self._bg[0], workspace=ws0, out_state=st0, planned=early)
             ev[2].record(main)
             with torch.cuda.stream(aux):
                 aux.wait_event(ev[2])
                 ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
                 ev[3].record(aux)
-            main.wait_event(ev[1])
+            if not early:
+                main.wait_event(ev[1])
             ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
                                    consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
             ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
@@ -243,7 +273,7 @@ class VoxelNetFrontEnd:
     def _aux_stream(self, device):
         if getattr(self, "_aux", None) is None or self._aux.device != device:
             self._aux = torch.cuda.Stream(device=device)
-            self._events = [torch.cuda.Event() for _ in range(4)]
+            self._events = [torch.cuda.Event() for _ in range(5)]
         return self._aux
 
     def capture_graph(self, points: torch.Tensor, frame_offsets: torch.Tensor, max_points_per_frame: int):
