@@ -137,7 +137,8 @@ int vn_voxelize_svfe_fused(const vn_grid_t* grid, const float* points, const int
 /* The same in two calls, for pipelines that want the voxel coordinates early: vn_voxelize_bucket_coords does the
  * bucketing and writes coordinate_buffer [max_voxels,4] (everything that depends on the coordinates only - live-box
  * marking, conv planning - can then run on another stream next to the SVFE kernel); vn_voxelize_svfe_bucketed is
- * vn_voxelize_svfe_fused without the bucketing step and must follow it on the same workspace. */
+ * vn_voxelize_svfe_fused without the bucketing step and must follow it on the same workspace; it takes the same
+ * coordinate_buffer but does not write it again (another stream may be reading it). */
 int vn_voxelize_bucket_coords(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
                               int32_t n_frames, int64_t n_points_total, const int32_t* voxel_offsets,
                               int64_t max_voxels, int64_t* coordinate_buffer, void* workspace,

@@ -350,9 +350,11 @@ __device__ __forceinline__ int64_t write_coords(const vn_grid_t& g, const float4
     const int mid = (lo + hi) >> 1;
     if ((int64_t)voxel_offsets[mid] <= row) lo = mid; else hi = mid;
   }
-  longlong2* c = reinterpret_cast<longlong2*>(coords + row * 4);
-  c[0] = make_longlong2(lo, z);
-  c[1] = make_longlong2(y, x);
+  if (coords != nullptr) {  // null: k_vox_coords already wrote them and a side stream may be reading
+    longlong2* c = reinterpret_cast<longlong2*>(coords + row * 4);
+    c[0] = make_longlong2(lo, z);
+    c[1] = make_longlong2(y, x);
+  }
   return (((int64_t)lo * g.D + z) * g.H + y) * g.W + x;
 }
 
@@ -814,8 +816,8 @@ static int svfe_fused_impl(const vn_grid_t* grid, const float* points, const int
   k_vox_svfe_packed<<<(unsigned)(want < cap ? want : cap), kPackWarps * 32, smem, st>>>(
       *grid, reinterpret_cast<const float4*>(points), n_frames, voxel_offsets, max_voxels, w.cnt, w.seg, w.pidx, w1, b1,
       s1, t1, w2, b2, s2, t2, voxelwise, reinterpret_cast<__nv_bfloat16*>(dense_bf16),
-      reinterpret_cast<long long*>(coordinate_buffer), reinterpret_cast<long long*>(number_buffer), w.counters,
-      w.biglist);
+      bucketed ? nullptr : reinterpret_cast<long long*>(coordinate_buffer), reinterpret_cast<long long*>(number_buffer),
+      w.counters, w.biglist);
   VN_LAUNCH_CHECK("k_vox_svfe_packed");
   return VN_OK;
 }
