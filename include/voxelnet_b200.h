@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 10
+#define VN_ABI_VERSION 11
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -337,6 +337,29 @@ int vn_conv1_dgrad_gather(const void* draw_bf16, const void* weight_taps, const 
 int vn_svfe_bwd(const float* feature, int64_t K, int32_t T, const float* dvw, int32_t pass, const float* w1,
                 const float* b1, const float* w2, const float* b2, const float* bn1, const float* bn2,
                 float* row_scratch, double* acc, vn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * RPN target assignment - replaces the interpreter loops of bbox_iou
+ * (voxelnet/utils.py:344-373) and the per-frame body of generate_targets (utils.py:395-462).
+ * ------------------------------------------------------------------------------------------ */
+/* overlaps [N,K] f32 of box1 [N,4] and box2 [K,4] (x1, y1, x2, y2; f32, 16-byte aligned), float32 arithmetic in
+ * the reference's operation order, bit-identical to utils.bbox_iou (including its anchor-area term as written at
+ * utils.py:366-367).  N == 0 or K == 0 is a no-op. */
+int vn_bbox_iou(const float* box1, const float* box2, int64_t N, int32_t K, float* overlaps, vn_stream_t stream);
+
+size_t vn_rpn_targets_workspace_bytes(int32_t n_frames, int32_t n_anchors, int32_t n_boxes_total);
+
+/* One batch of generate_targets.  anchors_standup [A,4] f32 and gt_standup [G,4] f32 are the float32 stand-up boxes
+ * the reference hands to bbox_iou (utils.py:397-409); anchors [A,7] f64 and gt_boxes [G,7] f64 are (x,y,z,h,w,l,r);
+ * gt_offsets [n_frames+1] i32 is the CSR of the boxes per frame (a frame may have none: all its anchors are
+ * negative).  pos_iou / neg_iou = cfg.OBJECT.RPN_POS_IOU / RPN_NEG_IOU as float32 (the dtype numpy compares in),
+ * anchor_h = cfg.OBJECT.ANCHOR_H.  Outputs, every element written: pos_equal_one, neg_equal_one [n_frames, A] f64
+ * (= [B, H, W, 2]) and targets [n_frames, A, 7] f64 (= [B, H, W, 14]).  Index sets are identical to the
+ * reference's; target values are IEEE-exact except the three log() terms (1 ulp). */
+int vn_rpn_targets(const float* anchors_standup, const double* anchors, int32_t n_anchors, const float* gt_standup,
+                   const double* gt_boxes, const int32_t* gt_offsets, int32_t n_frames, int32_t n_boxes_total,
+                   float pos_iou, float neg_iou, double anchor_h, double* pos_equal_one, double* neg_equal_one,
+                   double* targets, void* workspace, size_t workspace_bytes, vn_stream_t stream);
 
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);

@@ -632,3 +632,47 @@ def svfe_bwd(feature, dvw, w1, b1, w2, b2, bn1, bn2) -> dict:
         "w2": f[0:2048].view(64, 32), "b2": f[2048:2112], "gamma2": f[2112:2176], "beta2": f[2176:2240],
         "w1": f[2240:2352].view(16, 7), "b1": f[2352:2368], "gamma1": f[2368:2384], "beta1": f[2384:2400],
     }
+
+
+# ---------------------------------------------------------------------------------------------
+# RPN target assignment
+# ---------------------------------------------------------------------------------------------
+def bbox_iou(box1, box2) -> torch.Tensor:
+    """(N,4) f32 x (K,4) f32 stand-up boxes -> (N,K) f32 overlaps, bit-identical to utils.py:344-373."""
+    _require_cuda(box1, box2)
+    _contig(box1, torch.float32), _contig(box2, torch.float32)
+    if box1.dim() != 2 or box2.dim() != 2 or box1.shape[1] != 4 or box2.shape[1] != 4:
+        raise RuntimeError("bbox_iou expects (N,4) and (K,4) boxes; got %s, %s" % (tuple(box1.shape), tuple(box2.shape)))
+    out = torch.zeros((box1.shape[0], box2.shape[0]), dtype=torch.float32, device=box1.device)
+    with torch.cuda.device(box1.device):
+        check(
+            _cabi.lib().vn_bbox_iou(_ptr(box1), _ptr(box2), box1.shape[0], box2.shape[0], _ptr(out), _stream()),
+            "vn_bbox_iou",
+        )
+    return out
+
+
+def rpn_targets(anchors_standup, anchors, gt_standup, gt_boxes, gt_offsets, pos_iou: float, neg_iou: float,
+                anchor_h: float):
+    """One batch of generate_targets (see header).  Returns (pos, neg) (B,A) f64 and targets (B,A,7) f64."""
+    _require_cuda(anchors_standup, anchors, gt_standup, gt_boxes, gt_offsets)
+    _contig(anchors_standup, torch.float32), _contig(anchors, torch.float64)
+    _contig(gt_standup, torch.float32), _contig(gt_boxes, torch.float64), _contig(gt_offsets, torch.int32)
+    A, B, G = anchors.shape[0], gt_offsets.numel() - 1, gt_boxes.shape[0]
+    if anchors_standup.shape != (A, 4) or anchors.shape != (A, 7) or gt_standup.shape != (G, 4) or gt_boxes.shape != (G, 7):
+        raise RuntimeError("rpn_targets: inconsistent shapes")
+    dev = anchors.device
+    pos = torch.empty((B, A), dtype=torch.float64, device=dev)
+    neg = torch.empty((B, A), dtype=torch.float64, device=dev)
+    targets = torch.empty((B, A, 7), dtype=torch.float64, device=dev)
+    ws = torch.empty(int(_cabi.lib().vn_rpn_targets_workspace_bytes(B, A, G)), dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        check(
+            _cabi.lib().vn_rpn_targets(
+                _ptr(anchors_standup), _ptr(anchors), A, _ptr(gt_standup) if G else None, _ptr(gt_boxes) if G else None,
+                _ptr(gt_offsets), B, G, pos_iou, neg_iou, anchor_h, _ptr(pos), _ptr(neg), _ptr(targets), _ptr(ws),
+                ws.numel(), _stream(),
+            ),
+            "vn_rpn_targets",
+        )
+    return pos, neg, targets
