@@ -109,3 +109,25 @@ def test_state_dict_names_match_reference():
     rm = {k for k in ref.model.MiddleConvNet().state_dict().keys() if k.startswith("middle_layer.")}
     assert rm == set(vn.MiddleConvNet().state_dict().keys())
     assert rf | rm == set(OM.random_state_dict(0).keys())
+
+
+def test_target_assignment_against_live_reference():
+    """A second seed of label lines through the reference's generate_targets vs oracle + the product's host side."""
+    from oracle import make_golden_targets as MG
+    from oracle import targets_np as OT
+    from voxelnet_pytorch_b200 import targets as T
+
+    ref = R.load_reference()
+    labels = MG.synthetic_labels(seed=5)[::2]  # the 10-line frame and the single-object frame
+    lab = np.empty(len(labels), dtype=object)
+    for i, f in enumerate(labels):
+        lab[i] = f
+    anchors = ref.utils.generate_anchors()
+    assert np.array_equal(anchors, T.generate_anchors("Car"))
+    want_boxes = ref.utils.label_to_gt_box_3d(lab, "Car", "lidar")
+    boxes = T.label_to_gt_box_3d(labels, "Car", "lidar")
+    assert all(np.array_equal(a, b) for a, b in zip(boxes, want_boxes))
+    wp, wn, wt = ref.utils.generate_targets(lab, anchors.shape[:2], anchors)
+    c = T.anchor_config("Car")
+    gp, gn, gt = OT.generate_targets(boxes, anchors.shape[:2], anchors, c.rpn_pos_iou, c.rpn_neg_iou, c.anchor_h)
+    assert np.array_equal(gp, wp) and np.array_equal(gn, wn) and np.array_equal(gt, wt) and wp.sum() > 0
