@@ -76,7 +76,7 @@ def test_training_step_gradients_against_reference_golden(cuda_device, golden_di
     against gradients the UNMODIFIED fp32 reference produced for the same frame, parameters and upstream gradient
     (tests/golden/train_grads_ped.npz).  The conv path is bf16: a few ReLUs near zero flip against fp32, so the
     bar here is direction and scale (cosine >= 0.995, norm within 2 %, max deviation <= 0.12 of max; observed:
-    cosine >= 0.9987, deviation <= 0.079 - tools/print_train_margins.py); the tight
+    cosine >= 0.9987, deviation <= 0.079 - tests/tools/print_train_margins.py); the tight
     per-kernel bars are in test_gpu_train_backward.py."""
     import voxelnet_pytorch_b200 as vn
     from tests.helpers import load_state

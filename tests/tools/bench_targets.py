@@ -1,6 +1,6 @@
 """Timing of the RPN target assignment (Car, 16 frames x 8 boxes): device kernels vs the CPU restatements.
 
-    python tools/bench_targets.py            # prints one JSON object
+    python tests/tools/bench_targets.py            # prints one JSON object
 
 `device_ms`: vn_rpn_targets alone (CUDA events, inputs resident); `api_ms`: TargetAssigner.assign wall time incl. the
 host-side box preparation, uploads and a device sync; `oracle_vectorised_ms`: oracle/targets_np.py (numpy arrays);
@@ -14,7 +14,7 @@ import time
 import numpy as np
 import torch
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import voxelnet_pytorch_b200  # noqa: E402,F401
 from voxelnet_pytorch_b200 import ops, targets as T  # noqa: E402
 from oracle import targets_np as OT  # noqa: E402

@@ -1,6 +1,6 @@
 """Debug aid: per-tensor gradient errors of the training backward vs the CPU oracle (run on the GPU box)."""
 import sys, os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 from oracle import model_torch as OM
 from tests.helpers import load_state, oracle_batch, rel_max_err, synth_frames

@@ -1,6 +1,6 @@
 """Print the observed gradient-parity numbers of the training tests (how far each is from its stated bar)."""
 import os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import numpy as np, torch
 import voxelnet_pytorch_b200 as vn
 from tests.helpers import load_state
@@ -8,7 +8,7 @@ from tests.test_oracle_golden import _train_golden_inputs
 from voxelnet_pytorch_b200.utils import pack_frames
 
 dev = torch.device("cuda", 0)
-gd = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden")
+gd = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "golden")
 for rep in range(3):
     g, points, target, sd, dout = _train_golden_inputs(gd)
     fnet, mnet = vn.FeatureLearningNet(target), vn.MiddleConvNet()
