@@ -64,6 +64,14 @@ def test_bad_arguments_are_rejected_without_a_gpu():
     assert lib.vn_conv3d_box_flags_bytes(16, 10, 400, 352) == 16 * 10 * 25 * 44 * 3
     assert lib.vn_conv3d_mark_boxes(None, 5, None, 1, 10, 16, 16, 4, None, None, None, None) == -1
     assert lib.vn_conv3d_packed_weight_bytes(128) == 27 * 128 * 64 * 2 and lib.vn_conv3d_packed_weight_bytes(32) == 0
+    assert lib.vn_bbox_iou(None, None, 0, 5, None, None) == 0  # empty: no-op
+    assert lib.vn_bbox_iou(None, p16, 3, 5, p16, None) == -1 and b"null" in lib.vn_last_error()
+    assert lib.vn_bbox_iou(ctypes.c_void_p(20), p16, 3, 5, p16, None) == -1 and b"aligned" in lib.vn_last_error()
+    need = lib.vn_rpn_targets_workspace_bytes(2, 70400, 9)
+    assert need >= 9 * 8 + 2 * 70400 * 8 and lib.vn_rpn_targets_workspace_bytes(-1, 4, 4) == 0
+    targ = (p16, p16, 70400, p16, p16, p16, 2, 9, 0.6, 0.45, 1.56, p16, p16, p16, p16)
+    assert lib.vn_rpn_targets(*targ, need - 1, None) == -1 and b"workspace" in lib.vn_last_error()
+    assert lib.vn_rpn_targets(p16, p16, 70400, None, None, p16, 2, 9, 0.6, 0.45, 1.56, p16, p16, p16, p16, need, None) == -1
     with pytest.raises(_cabi.VnError):
         _cabi.check(rc, "probe")
 
