@@ -320,6 +320,8 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget for the cpu_baseline leg (rank 0, N=1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cuda-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
+    ap.add_argument("--in-flight", type=int, default=2,
+                    help="eval steps in flight per GPU (front ends on their own streams; 1 = strictly one step at a time)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -425,30 +427,52 @@ def main():
     for i in range(2):  # keep the GPU busy while nvidia-smi spins up
         step(i)
     # One CUDA graph per alternating batch (the step is host-sync free); eager launches if capture fails.
+    # --in-flight P > 1: P front ends (own grid, workspaces, resident outputs; shared modules), step i on front end
+    # i % P on that pipeline's stream, so the latency-bound index / bucketing kernels of one step run beside the
+    # convolution kernels of another.  Every front end keeps alternating between the two batches.
+    P = max(1, args.in_flight)
+    fes = [fe] + [vn.VoxelNetFrontEnd(fnet, mnet, target) for _ in range(P - 1)]
+    pipes = [torch.cuda.Stream(device=dev) for _ in range(P)] if P > 1 else [torch.cuda.current_stream(dev)]
+
+    def batch_of(i):
+        return (i // P + i % P) % 2
+
     graphs, launch_mode, per_step_launches = None, "eager launches", None
     if not args.no_cuda_graph:
         try:
             l0 = _cabi.launch_count()
-            graphs = [fe.capture_graph(bt.points, bt.offsets, bt.max_n) for bt in batches]
-            per_step_launches = (_cabi.launch_count() - l0) // (3 * len(batches))  # 2 warm-ups + 1 captured run each
-            launch_mode = "CUDA graph replay (one graph per alternating batch)"
-            for i in range(4):
-                graphs[i % 2].replay()
+            graphs = [[f.capture_graph(bt.points, bt.offsets, bt.max_n) for bt in batches] for f in fes]
+            per_step_launches = (_cabi.launch_count() - l0) // (3 * len(batches) * P)  # 2 warm-ups + 1 captured run each
+            launch_mode = "CUDA graph replay (one graph per front end and alternating batch)"
         except Exception as exc:  # noqa: BLE001 - fall back to the eager path, say so in the line
             graphs, launch_mode = None, "eager launches (graph capture failed: %s)" % type(exc).__name__
             torch.cuda.synchronize()
+
+    def issue(i):
+        with torch.cuda.stream(pipes[i % P]):
+            if graphs is not None:
+                graphs[i % P][batch_of(i)].replay()
+            else:
+                bt = batches[batch_of(i)]
+                fes[i % P].forward_points(bt.points, bt.offsets, bt.max_n)
+
+    for i in range(4 * P):
+        issue(i)
     barrier()
     wall0 = time.time()
     launches0 = _cabi.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    if graphs is not None:
-        for i in range(args.steps):
-            graphs[i % 2].replay()
-    else:
-        for i in range(args.steps):
-            step(i)
-    e1.record()
+    main_stream = torch.cuda.current_stream(dev)
+    e0.record(main_stream)
+    if P > 1:
+        for ps in pipes:
+            ps.wait_event(e0)
+    for i in range(args.steps):
+        issue(i)
+    if P > 1:
+        for ps in pipes:
+            main_stream.wait_stream(ps)
+    e1.record(main_stream)
     barrier()
     wall1 = time.time()
     launches = per_step_launches * args.steps if graphs is not None else _cabi.launch_count() - launches0
@@ -475,24 +499,27 @@ def main():
 
     host_batches = [PinnedFrameBatch.from_frames(fr) for fr in (frames, frames_b)]
     host_batches.sort(key=lambda hb: -hb.n_points)
-    stream = HostFrameStream(fe, batch, host_batches[0].n_points, cuda_graphs=not args.no_cuda_graph)
+    stream = HostFrameStream(fes if P > 1 else fe, batch, host_batches[0].n_points, cuda_graphs=not args.no_cuda_graph)
 
     def e2e_run(n):
         # every step: H2D of its points (on the copy stream, overlapping the previous step), the step itself, and a
         # D2H read of its per-frame voxel counts.  The host consumes the counts of step i-1 while step i runs (one
         # step of latency, the device queue never drains) and the last step's before the clock stops.
-        stream.upload(host_batches[0])
+        # With P front ends in flight the host reads P steps behind, and front end i % P alternates batches.
+        for j in range(min(P, n)):
+            stream.upload(host_batches[batch_of(j)])
         seen = 0
         for i in range(n):
-            if i + 1 < n:
-                stream.upload(host_batches[(i + 1) % 2])
+            if i + P < n:
+                stream.upload(host_batches[batch_of(i + P)])
             stream.forward()
-            if i > 0:
-                seen += int(stream.voxel_counts_host(lag=1)[-1])
-        seen += int(stream.voxel_counts_host()[-1])
+            if i >= P:
+                seen += int(stream.voxel_counts_host(lag=P)[-1])
+        for lag in range(min(P, n) - 1, -1, -1):
+            seen += int(stream.voxel_counts_host(lag=lag)[-1])
         return seen
 
-    e2e_run(4)  # (with CUDA graphs: each staging slot's step is captured on its second visit)
+    e2e_run(4 * P * (P + 1))  # (with CUDA graphs: every (front end, staging slot, batch) step is captured on its second visit)
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
@@ -581,6 +608,8 @@ def main():
                        "l2_policy": "working set (%.1f GB dense grid + activations) exceeds L2" % (fe.dense.numel() * 2 / 1e9),
                        "vfe": "fp32", "conv": "bf16 operands, fp32 accumulate (tcgen05)",
                        "launch": launch_mode,
+                       "in_flight": "%d step(s) in flight per GPU (%s); ms_per_step = timed region / steps" % (
+                           P, "one front end per pipeline stream, own grid/workspaces/outputs" if P > 1 else "one stream"),
                        "stage_times": "stages_ms / stage_roofline come from a separate eager pass with CUDA events between the stages"},
             "ms_per_frame": ms_step / batch,
             "stages_ms": stages,

@@ -262,3 +262,47 @@ def test_host_stream_lagged_counts(cuda_device):
             got.append(stream.voxel_counts_host(lag=1).tolist())
     got.append(stream.voxel_counts_host().tolist())
     assert got == want
+
+
+@pytest.mark.parametrize("graphs", [False, True])
+def test_host_stream_with_two_front_ends_in_flight(cuda_device, graphs):
+    """HostFrameStream over TWO front ends (two steps in flight on two streams, three staging slots): every step's
+    tensor - consumed on the caller's stream before the next call - and its voxel counts (read up to two steps
+    behind) are bit-identical to the single-front-end run of the same batch sequence."""
+    import voxelnet_pytorch_b200 as vn
+
+    sd = OM.random_state_dict(12)
+    fnet, mnet = vn.FeatureLearningNet("Pedestrian").eval(), vn.MiddleConvNet().eval()
+    load_state(fnet, sd, "")
+    load_state(mnet, sd, "")
+    fnet, mnet = fnet.to(cuda_device), mnet.to(cuda_device)
+    fes = [vn.VoxelNetFrontEnd(fnet, mnet, "Pedestrian") for _ in range(3)]
+    sets = [[f[::5].copy() for f in synth_frames(2, s)] for s in (600, 610, 620)]
+    want, counts = [], []
+    for fr in sets:
+        want.append(fes[2].forward_frames(fr).clone())
+        counts.append(fes[2].voxel_counts())
+    assert not torch.equal(want[0], want[1])
+    hbs = [vn.PinnedFrameBatch.from_frames(fr) for fr in sets]
+    stream = vn.HostFrameStream(fes[:2], 2, max(hb.n_points for hb in hbs), cuda_graphs=graphs)
+    order = [0, 1, 2, 1, 0, 2, 2, 1] * (4 if graphs else 1)  # with graphs: long enough for captures and replays
+    n = len(order)
+    stream.upload(hbs[order[0]])
+    stream.upload(hbs[order[1]])
+    checksum = torch.zeros((), dtype=torch.float64, device=cuda_device)
+    got_counts = []
+    for i in range(n):
+        if i + 2 < n:
+            stream.upload(hbs[order[i + 2]])
+        out = stream.forward()
+        assert torch.equal(out, want[order[i]]), i                 # consumed on the current stream, before the next call
+        checksum += out.double().sum()                             # (and an asynchronous consumer as well)
+        if i >= 2:
+            got_counts.append(stream.voxel_counts_host(lag=2).tolist())
+    got_counts += [stream.voxel_counts_host(lag=1).tolist(), stream.voxel_counts_host().tolist()]
+    assert got_counts == [counts[b] for b in order]
+    assert float(checksum) == float(sum(want[b].double().sum() for b in order))
+    if graphs:
+        assert len(stream._graphs) > 0
+    with pytest.raises(RuntimeError):
+        stream.voxel_counts_host(lag=3)

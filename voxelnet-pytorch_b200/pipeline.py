@@ -382,32 +382,43 @@ class HostFrameStream:
             counts = stream.voxel_counts_host()   # blocks until this step is done
     """
 
-    def __init__(self, front_end: VoxelNetFrontEnd, n_frames: int, max_points: int, device=None, cuda_graphs: bool = False):
+    def __init__(self, front_end, n_frames: int, max_points: int, device=None, cuda_graphs: bool = False):
         dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
-        self.fe, self.device = front_end, dev
+        # front_end: one VoxelNetFrontEnd, or a list of P of them (sharing the same modules) to keep P steps in
+        # flight: step s runs on front end s % P on that pipeline's own stream, so the short latency-bound kernels
+        # of one step (index, bucketing) run beside the long convolution kernels of the other.  Each front end owns
+        # its grid, workspaces and resident outputs.  forward() still hands every output to the CURRENT stream (the
+        # current stream waits for the step), and as with one front end the returned buffer must be consumed - work
+        # enqueued on the current stream - before the next forward() call.
+        self.fes = list(front_end) if isinstance(front_end, (list, tuple)) else [front_end]
+        self.fe, self.device = self.fes[0], dev
+        P = self.n_pipes = len(self.fes)
+        self.compute = [torch.cuda.Stream(device=dev) for _ in range(P)] if P > 1 else [None]
+        self._consumed = []  # events on the caller's stream, one per forward() call (the last P are kept)
         # cuda_graphs: an eval-mode step on a staging slot is captured into a CUDA graph the second time the same
-        # (slot, point count, max points per frame) comes by, and replayed from then on (fixed-size batches in a
-        # steady stream hit this; anything else keeps running eagerly)
+        # (pipeline, slot, point count, max points per frame) comes by, and replayed from then on (fixed-size batches
+        # in a steady stream hit this; anything else keeps running eagerly)
         self.cuda_graphs = bool(cuda_graphs)
         self._graphs, self._seen = {}, set()
+        self.n_slots = P + 1  # one uploading while P compute
         self.slots = [(torch.empty((int(max_points), 4), dtype=torch.float32, device=dev),
-                       torch.empty(n_frames + 1, dtype=torch.int32, device=dev)) for _ in range(2)]
+                       torch.empty(n_frames + 1, dtype=torch.int32, device=dev)) for _ in range(self.n_slots)]
         self.copy_stream = torch.cuda.Stream(device=dev)
-        self.ready = [torch.cuda.Event() for _ in range(2)]
-        self.freed = [torch.cuda.Event() for _ in range(2)]
+        self.ready = [torch.cuda.Event() for _ in range(self.n_slots)]
+        self.freed = [torch.cuda.Event() for _ in range(self.n_slots)]
         for e in self.freed:
             e.record(torch.cuda.current_stream(dev))
         self.pending = []  # (slot, n_points, max_points_per_frame)
         self.next_slot = 0
-        # per-frame voxel prefix of the last two steps (pinned), each with the event that marks its D2H copy done
-        self._counts = [torch.zeros(n_frames + 1, dtype=torch.int32).pin_memory() for _ in range(2)]
-        self._counts_done = [torch.cuda.Event() for _ in range(2)]
+        # per-frame voxel prefix of the last P+1 steps (pinned), each with the event that marks its D2H copy done
+        self._counts = [torch.zeros(n_frames + 1, dtype=torch.int32).pin_memory() for _ in range(P + 1)]
+        self._counts_done = [torch.cuda.Event() for _ in range(P + 1)]
         self._steps = 0
         self.h2d_bytes = 0
 
     def upload(self, batch) -> None:
-        if len(self.pending) >= 2:
-            raise RuntimeError("both staging slots hold batches that were not consumed: call forward() first")
+        if len(self.pending) >= self.n_slots:
+            raise RuntimeError("every staging slot holds a batch that was not consumed: call forward() first")
         k = self.next_slot
         pts, offs = self.slots[k]
         if batch.n_points > pts.shape[0] or batch.offsets.numel() != offs.numel():
@@ -419,7 +430,7 @@ class HostFrameStream:
             self.ready[k].record(self.copy_stream)
         self.h2d_bytes = batch.n_points * 16 + offs.numel() * 4
         self.pending.append((k, batch.n_points, batch.max_points_per_frame))
-        self.next_slot = 1 - k
+        self.next_slot = (k + 1) % self.n_slots
 
     def forward(self, timer: StageTimer = None) -> torch.Tensor:
         if not self.pending:
@@ -427,36 +438,55 @@ class HostFrameStream:
         k, n, max_n = self.pending.pop(0)
         pts, offs = self.slots[k]
         main = torch.cuda.current_stream(self.device)
-        main.wait_event(self.ready[k])
-        training = self.fe.feature_net.training
-        key = (k, n, max_n)
-        graph = self._graphs.get(key) if (self.cuda_graphs and not training and timer is None) else None
-        if graph is None and self.cuda_graphs and not training and timer is None and key in self._seen:
-            graph = self._graphs[key] = self.fe.capture_graph(pts[:n], offs, max_n)
-        self._seen.add(key)
-        if graph is not None:
-            graph.replay()
-            out = self.fe.out
-        else:
-            fn = self.fe.forward_points_train if training else self.fe.forward_points
-            out = fn(pts[:n], offs, max_n, timer=timer)
-        self.freed[k].record(main)
-        slot = self._steps % 2
-        self._counts[slot].copy_(self.fe.voxels.voxel_offsets, non_blocking=True)
-        self._counts_done[slot].record(main)
+        P = self.n_pipes
+        pipe = self._steps % P
+        fe = self.fes[pipe]
+        cs = main
+        if P > 1:
+            cs = self.compute[pipe]
+            # this step overwrites the buffers of step s-P (same front end); its output was consumed by work enqueued
+            # before call s-P+1, i.e. before the event recorded at the start of that call
+            ev = torch.cuda.Event()
+            ev.record(main)
+            self._consumed = (self._consumed + [ev])[-P:]
+            if len(self._consumed) == P:
+                cs.wait_event(self._consumed[0])
+        cs.wait_event(self.ready[k])
+        training = fe.feature_net.training
+        if training and P > 1:
+            raise RuntimeError("several front ends in flight are an eval-mode feature (they would race on the parameters' .grad)")
+        key = (pipe, k, n, max_n)
+        use_graph = self.cuda_graphs and not training and timer is None
+        with torch.cuda.stream(cs):
+            graph = self._graphs.get(key) if use_graph else None
+            if graph is None and use_graph and key in self._seen:
+                graph = self._graphs[key] = fe.capture_graph(pts[:n], offs, max_n)
+            self._seen.add(key)
+            if graph is not None:
+                graph.replay()
+                out = fe.out
+            else:
+                fn = fe.forward_points_train if training else fe.forward_points
+                out = fn(pts[:n], offs, max_n, timer=timer)
+            self.freed[k].record(cs)
+            slot = self._steps % (P + 1)
+            self._counts[slot].copy_(fe.voxels.voxel_offsets, non_blocking=True)
+            self._counts_done[slot].record(cs)
+        if P > 1:
+            main.wait_event(self._counts_done[slot])  # the consumer's stream sees the finished step
         self._steps += 1
         return out
 
     @property
     def host_counts(self) -> torch.Tensor:
-        return self._counts[(self._steps - 1) % 2]
+        return self._counts[(self._steps - 1) % (self.n_pipes + 1)]
 
     def voxel_counts_host(self, lag: int = 0) -> torch.Tensor:
-        """The per-frame voxel prefix (B+1,) int32, in pinned host memory, of the last forward() (lag 0) or of the
-        one before (lag 1).  Blocks only until THAT step's device->host copy is done: with lag 1 the device queue
+        """The per-frame voxel prefix (B+1,) int32, in pinned host memory, of the last forward() (lag 0) or of an
+        earlier one (lag up to the number of front ends; 1 with a single front end).  Blocks only until THAT step's device->host copy is done: with lag 1 the device queue
         never drains while the host reads results (one step of latency for the consumer)."""
-        if lag not in (0, 1) or self._steps - lag < 1:
-            raise RuntimeError("voxel_counts_host(lag=%d): no such step yet" % lag)
-        slot = (self._steps - 1 - lag) % 2
+        if not 0 <= lag <= self.n_pipes or self._steps - lag < 1:
+            raise RuntimeError("voxel_counts_host(lag=%d): no such step (yet), or more than %d steps back" % (lag, self.n_pipes))
+        slot = (self._steps - 1 - lag) % (self.n_pipes + 1)
         self._counts_done[slot].synchronize()
         return self._counts[slot]
