@@ -320,8 +320,9 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget for the cpu_baseline leg (rank 0, N=1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cuda-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
-    ap.add_argument("--in-flight", type=int, default=2,
-                    help="eval steps in flight per GPU (front ends on their own streams; 1 = strictly one step at a time)")
+    ap.add_argument("--in-flight", type=int, default=None,
+                    help="eval steps in flight per GPU (front ends on their own streams; 1 = strictly one step at a time); "
+                         "default 3, or 1 for batches above 16 frames per GPU (each pipeline holds its own grid and outputs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -430,7 +431,7 @@ def main():
     # --in-flight P > 1: P front ends (own grid, workspaces, resident outputs; shared modules), step i on front end
     # i % P on that pipeline's stream, so the latency-bound index / bucketing kernels of one step run beside the
     # convolution kernels of another.  Every front end keeps alternating between the two batches.
-    P = max(1, args.in_flight)
+    P = max(1, args.in_flight) if args.in_flight is not None else (3 if batch <= 16 else 1)
     fes = [fe] + [vn.VoxelNetFrontEnd(fnet, mnet, target) for _ in range(P - 1)]
     pipes = [torch.cuda.Stream(device=dev) for _ in range(P)] if P > 1 else [torch.cuda.current_stream(dev)]
 
