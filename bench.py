@@ -88,13 +88,14 @@ class ClockSampler:
 
     Q = "timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
-    def __init__(self, index: int):
-        self.index, self.proc, self.lines = index, None, []
+    def __init__(self, index: int, period_ms: int = 10):
+        # 10 ms on a single GPU (a 50-step timed region is ~80 ms); 50 ms when several ranks share the host cores
+        self.index, self.proc, self.lines, self.period_ms = index, None, [], int(period_ms)
 
     def start(self):
         try:
             self.proc = subprocess.Popen(
-                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "10"],
+                ["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", str(self.period_ms)],
                 stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._pump, daemon=True)
             self.thread.start()
@@ -273,7 +274,7 @@ def run_train(args, rank, world, local_rank, dev):
 
     for i in range(args.warmup):
         step(i)
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, 10 if world == 1 else 50)
     sampler.start()
     step(0)
     barrier()
@@ -423,7 +424,7 @@ def main():
             torch.cuda.synchronize()
             counts.append(fe.voxel_counts())  # also checks the voxel capacity
     torch.cuda.synchronize()
-    sampler = ClockSampler(local_rank)
+    sampler = ClockSampler(local_rank, 10 if world == 1 else 50)
     sampler.start()
     for i in range(2):  # keep the GPU busy while nvidia-smi spins up
         step(i)
