@@ -99,3 +99,36 @@ def test_product_targets_fail_loudly_without_cuda():
         T.bbox_iou(np.zeros((2, 4), np.float32), np.zeros((1, 4), np.float32))
     with pytest.raises(RuntimeError):
         T.generate_targets([[]], (200, 176), T.generate_anchors("Car"))
+
+
+@pytest.mark.parametrize("seed", range(4))
+def test_iou_array_restatement_equals_the_literal_loop(seed):
+    """The array form of the IoU (what the GPU parity tests compare against at full size) has the bits of the literal
+    double loop on random, degenerate, touching and disjoint boxes."""
+    rng = np.random.default_rng(seed)
+    lo = rng.uniform(-5, 5, size=(60, 2)).astype(np.float32)
+    box1 = np.concatenate([lo, lo + rng.uniform(0, 4, size=(60, 2)).astype(np.float32)], axis=1)
+    box1[::3, 2:] = box1[::3, :2]                      # points, like the reference's anchors
+    lo = rng.uniform(-5, 5, size=(7, 2)).astype(np.float32)
+    box2 = np.concatenate([lo, lo + rng.uniform(0, 4, size=(7, 2)).astype(np.float32)], axis=1)
+    box2[0] = box1[1]                                  # identical boxes
+    box2[1] = box1[2] + np.float32(100)                # far away: iw <= 0
+    box1[4] = (0, 1, 0, 1)                             # anchor-area term (y1 - x1 + 1) = 2, (y2 - y1 + 1) = 1
+    a, b = OT.bbox_iou(box1, box2), OT.bbox_iou_loop(box1, box2)
+    assert np.array_equal(a.view(np.uint32), b.view(np.uint32))
+    assert (a[:, 1] == 0).all()
+
+
+def test_generate_targets_oracle_edge_cases():
+    """No boxes at all -> everything negative; one box far outside the range -> its arg-max anchor still becomes
+    positive only if its IoU is > 0."""
+    from voxelnet_pytorch_b200 import targets as T
+
+    anchors = T.generate_anchors("Pedestrian")
+    c = T.anchor_config("Pedestrian")
+    fms = anchors.shape[:2]
+    pos, neg, tg = OT.generate_targets([np.zeros((0, 7))], fms, anchors, c.rpn_pos_iou, c.rpn_neg_iou, c.anchor_h)
+    assert pos.sum() == 0 and neg.sum() == neg.size and not tg.any()
+    far = np.array([[500.0, 500.0, -1.0, 1.7, 0.6, 0.8, 0.3]])
+    pos, neg, tg = OT.generate_targets([far], fms, anchors, c.rpn_pos_iou, c.rpn_neg_iou, c.anchor_h)
+    assert pos.sum() == 0 and neg.sum() == neg.size
