@@ -612,7 +612,7 @@ def main():
                        "launch": launch_mode,
                        "in_flight": "%d step(s) in flight per GPU (%s); ms_per_step = timed region / steps" % (
                            P, "one front end per pipeline stream, own grid/workspaces/outputs" if P > 1 else "one stream"),
-                       "stage_times": "stages_ms / stage_roofline come from a separate eager pass with CUDA events between the stages"},
+                       "stage_times": "stages_ms / stage_roofline come from a separate eager pass of ONE front end with CUDA events between the stages; with several steps in flight their sum exceeds ms_per_step (the steps overlap)"},
             "ms_per_frame": ms_step / batch,
             "stages_ms": stages,
             "clocks": clocks,
