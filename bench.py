@@ -619,8 +619,9 @@ def main():
             "e2e": {"value": frames_total / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(sum(bt.host_points.numel() * 4 + bt.host_offsets.numel() * 4 for bt in batches) / 2),
                     "d2h_bytes_per_step": int(host_counts.numel() * 4),
-                    "note": "through voxelnet_pytorch_b200.HostFrameStream: H2D of step i+1 overlaps step i on a copy stream (two staging buffers); result read back per step = "
-                            "per-frame voxel counts (consumed one step later, the last one before the clock stops); the (B,128,H,W) tensor stays on the device for the RPN"},
+                    "note": "through voxelnet_pytorch_b200.HostFrameStream with %d front end(s) in flight: the H2D copy of a later step overlaps the running ones on a copy stream "
+                            "(%d staging buffers); result read back per step = per-frame voxel counts (consumed %d step(s) later, the last ones before the clock stops); "
+                            "the (B,128,H,W) tensor stays on the device for the RPN" % (P, P + 1, P)},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
                          "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": traffic,
