@@ -11,8 +11,13 @@ the public API with the H2D copy and a D2H read of the per-frame voxel counts in
 region.  Frames are independent, so N GPUs run N replicas on their own frames with no collective
 (weak scaling); timing is CUDA events on the launching stream, max over ranks.
 
-`--impl reference` times the reference's CPU path (oracle port, see oracle/cpu_chain.py) on the host
-cores; under torchrun only rank 0 runs it.  Prints ONE JSON line on rank 0.
+`--impl reference` times the reference's own CPU path on the host cores: the UNMODIFIED reference modules from
+`baseline/_ref/` (or /root/reference) through oracle/ref_chain.py - `cpu_baseline.kind = "reference"` - and only if
+that copy is absent the oracle port (oracle/cpu_chain.py, kind "port", reason stated).  Under torchrun only rank 0 runs
+it.  Prints ONE JSON line on rank 0.
+
+`--data kitti` replaces the synthetic frames by real ones from the reference's bundled KITTI drive
+(baseline/_ref/data, placed there by oracle/install_ref.py) - the real-data cross-check.
 """
 from __future__ import annotations
 
@@ -28,8 +33,13 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "frames/s voxelize->VFE->Conv3d-middle (Car cfg)"
 UNIT = "frames/s"
+
+
+def metric_name(config: str) -> str:
+    target = CONFIGS[config][0]
+    return "frames/s voxelize->VFE->Conv3d-middle (%s cfg)" % ("Car" if target == "Car" else "Ped/Cyc")
+
 
 CONFIGS = {
     # name: (target, batch per GPU, generator kwargs, description)
@@ -147,25 +157,59 @@ class ClockSampler:
                 "reasons": reasons}
 
 
+KITTI_DIRS = [os.path.join(ROOT, "baseline", "_ref", "data/2011_09_26/2011_09_26_drive_0001_sync/velodyne_points/data"),
+              "/root/reference/data/2011_09_26/2011_09_26_drive_0001_sync/velodyne_points/data"]
+DATA = "synthetic"
+
+
+def kitti_frames(first: int, n: int) -> list:
+    """n real frames of the reference's bundled KITTI drive starting at index `first` (wrapping over the files present)."""
+    from voxelnet_pytorch_b200.dataset import load_velodyne_bin
+
+    for d in KITTI_DIRS:
+        if os.path.isdir(d):
+            files = sorted(f for f in os.listdir(d) if f.endswith(".bin"))
+            if files:
+                return [load_velodyne_bin(os.path.join(d, files[(first + i) % len(files)])) for i in range(n)]
+    raise SystemExit("bench.py --data kitti: no KITTI frames under baseline/_ref/data (run `python -m oracle.install_ref` in the container)")
+
+
 def make_frames(cfg_name, rank, batch, seed=None):
     from voxelnet_pytorch_b200 import synth
 
     _, _, kw, _ = CONFIGS[cfg_name]
-    return synth.lidar_batch(batch, seed0=1000 * rank if seed is None else seed, **kw)
+    seed0 = 1000 * rank if seed is None else seed
+    if DATA == "kitti":
+        return kitti_frames(seed0 % 997, batch)
+    return synth.lidar_batch(batch, seed0=seed0, **kw)
+
+
+def reference_chain():
+    """(callable(frames, sd, target) -> (out, stage seconds), kind, note): the unmodified reference when a copy is
+    reachable, else the oracle port."""
+    from oracle import cpu_chain, ref_chain
+
+    if ref_chain.available():
+        from oracle import ref_import
+
+        return (lambda fr, sd, tg: ref_chain.front_end_reference(fr, sd, tg, shuffle=True)), "reference", \
+            "unmodified reference modules from %s (pcl_to_voxels with its shuffle -> prepare_voxel -> FeatureLearningNet -> middle_layer + reshape, predict.py:52-60)" % ref_import.REFERENCE_ROOT
+    return (lambda fr, sd, tg: cpu_chain.front_end_cpu(fr, sd, tg)), "port", \
+        "oracle port (baseline/_ref absent on this host: run `python -m oracle.install_ref` where /root/reference exists)"
 
 
 def cpu_reference_sample(target, frames, sd, seconds_budget=20.0, max_frames=None):
-    """Time the oracle port (reference CPU path) one frame at a time within a time budget."""
+    """Time the reference's CPU path (the reference itself, else the oracle port) one frame at a time within a time budget."""
     import torch
-    from oracle import cpu_chain
 
+    chain, kind, note = reference_chain()
     torch.set_num_threads(max(1, len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)))
-    cpu_chain.front_end_cpu(frames[:1], sd, target)  # warm-up (thread pools, oneDNN primitives)
+    chain(frames[:1], sd, target)  # warm-up (thread pools, oneDNN primitives)
     times, stage_acc, n = [], {}, 0
     t_start = time.perf_counter()
     while True:
         f = frames[n % len(frames)]
-        _, t = cpu_chain.front_end_cpu([f], sd, target)
+        _, t = chain([f], sd, target)
         times.append(t["total"])
         for k, v in t.items():
             stage_acc[k] = stage_acc.get(k, 0.0) + v
@@ -174,11 +218,11 @@ def cpu_reference_sample(target, frames, sd, seconds_budget=20.0, max_frames=Non
             break
     best = min(times)
     return dict(frames=n, best_s=best, mean_s=sum(times) / n, stages_mean_s={k: v / n for k, v in stage_acc.items()},
-                cores=torch.get_num_threads(), host_cpus=os.cpu_count())
+                cores=torch.get_num_threads(), host_cpus=os.cpu_count(), kind=kind, note=note)
 
 
 def run_reference(args, rank, world):
-    """--impl reference: the reference's CPU path (oracle port) on the host cores, rank 0 only."""
+    """--impl reference: the reference's own CPU path on the host cores, rank 0 only."""
     if rank != 0:
         return
     import torch
@@ -190,23 +234,23 @@ def run_reference(args, rank, world):
     target, batch, _, desc = CONFIGS[args.config]
     frames = make_frames(args.config, 0, min(batch, 4))
     sd = OM.random_state_dict(0)
-    from oracle import cpu_chain
+    chain, kind, note = reference_chain()
 
     for _ in range(max(args.warmup, 1)):
-        cpu_chain.front_end_cpu(frames[:1], sd, target)
+        chain(frames[:1], sd, target)
     times = []
     for i in range(args.steps):
-        _, t = cpu_chain.front_end_cpu([frames[i % len(frames)]], sd, target)
+        _, t = chain([frames[i % len(frames)]], sd, target)
         times.append(t["total"])
     total = sum(times)
     value = args.steps / total  # each step is a bounded sample: ONE frame of the workload
     line = {
-        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "impl": "reference", "metric": metric_name(args.config), "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": 1e3 * total / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "vs_baseline": None, "dtype": "f32", "data": DATA,
         "config": {"workload": desc, "name": args.config, "sample": "1 frame per step (bounded sample of the batch)"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",
-                         "sample": "%d steps x 1 frame, numpy voxelizer with the reference's per-point loop + torch-CPU VFE/scatter/Conv3d" % args.steps},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": torch.get_num_threads(), "kind": kind,
+                         "sample": "%d steps x 1 frame: %s" % (args.steps, note)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -298,7 +342,7 @@ def run_train(args, rank, world, local_rank, dev):
     line = {
         "metric": "frames/s hot-path training step (Car cfg)", "value": world * batch * args.steps / (ms_max / 1e3), "unit": UNIT,
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_max / args.steps,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": DATA,
         "config": {"workload": desc, "name": args.config, "batch_per_gpu": batch, "voxels_per_batch": voxels,
                    "upstream_gradient": "fixed random (B,128,H,W) f32 tensor (RPN + loss are stock PyTorch, out of scope)",
                    "optimizer": "SGD + clip_grad_norm_(5) (train.py:146-155)", "grad_elements_allreduced": n_grad,
@@ -321,11 +365,16 @@ def main():
     ap.add_argument("--cpu-seconds", type=float, default=20.0, help="budget for the cpu_baseline leg (rank 0, N=1)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-cuda-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
+    ap.add_argument("--data", default="synthetic", choices=["synthetic", "kitti"],
+                    help="kitti: real frames of the reference's bundled drive from baseline/_ref/data (cross-check)")
+    ap.add_argument("--host-threads", type=int, default=None, help="threads of the host frame packer (default: cores / ranks, 2..8)")
     ap.add_argument("--in-flight", type=int, default=None,
                     help="eval steps in flight per GPU (front ends on their own streams; 1 = strictly one step at a time); "
                          "default 3, or 1 for batches above 16 frames per GPU (each pipeline holds its own grid and outputs)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    global DATA
+    DATA = args.data
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -345,8 +394,8 @@ def main():
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
     if world > 1:
-        if os.environ.get("NCCL_DEBUG", "VERSION").upper() == "VERSION":
-            os.environ["NCCL_DEBUG"] = "WARN"  # keep NCCL's version banner off stdout: rank 0 prints ONE JSON line
+        # NCCL_DEBUG is the caller's; stdout is already pointed at stderr (quiet_stdout), so NCCL's banner cannot
+        # reach the result line
         dist.init_process_group("nccl", device_id=dev)
 
     import voxelnet_pytorch_b200 as vn
@@ -494,26 +543,46 @@ def main():
         plan.append(fe.plan_stats())
     plan = [{k: (plan[0][l][k] + plan[1][l][k]) / 2 for k in plan[0][l]} for l in range(3)]
 
-    # ---- end to end: host buffers in, voxel counts out ---------------------------------------------
-    # Through the package's public feeding API (pipeline.HostFrameStream): two device staging slots, the H2D
-    # copy of step i+1 runs on a copy stream while step i computes; every copy is inside the timed region.
+    # ---- end to end: per-frame host arrays in, voxel counts out --------------------------------------
+    # Starts where the reference starts: a list of per-frame (N_i, 4) float32 numpy arrays in ordinary (pageable)
+    # host memory (voxelnet/dataset.py:51).  Inside the timed region, EVERY step: its 16 arrays are packed into a
+    # pinned batch by the library's host thread pool (PinnedFrameBatch.fill_async -> vn_host_pack_submit), the batch
+    # is copied to a device staging slot on a copy stream, the step runs, and its per-frame voxel counts are read
+    # back.  The arrays of consecutive steps are distinct objects from a ring larger than the CPU's last-level cache
+    # (contents alternate between the two batches like the device-resident leg).  All through the package's public
+    # feeding API (dataset.PinnedFrameBatch + pipeline.HostFrameStream).
     from voxelnet_pytorch_b200 import HostFrameStream, PinnedFrameBatch
 
-    host_batches = [PinnedFrameBatch.from_frames(fr) for fr in (frames, frames_b)]
-    host_batches.sort(key=lambda hb: -hb.n_points)
-    stream = HostFrameStream(fes if P > 1 else fe, batch, host_batches[0].n_points, cuda_graphs=not args.no_cuda_graph)
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 8)
+    n_pack = args.host_threads if args.host_threads else max(2, min(8, cores // max(world, 1) - 1))
+    n_pack = _cabi.lib().vn_host_pack_threads(n_pack) or n_pack
+    ring_len = 4 if batch <= 16 else 1  # host copies per content: 8 x 31 MB at car16
+    frame_sets = (frames, frames_b)
+    sets_sorted = sorted(range(2), key=lambda c: -sum(int(f.shape[0]) for f in frame_sets[c]))  # like `batches`
+    host_ring = [[[np.array(f, copy=True) for f in frame_sets[c]] for _ in range(ring_len)] for c in sets_sorted]
+    max_points = max(sum(int(f.shape[0]) for f in fs) for fs in frame_sets)
+    stream = HostFrameStream(fes if P > 1 else fe, batch, max_points, cuda_graphs=not args.no_cuda_graph)
+    NP = P + 3
+    pinned = [PinnedFrameBatch(batch, max_points) for _ in range(NP)]
 
-    def e2e_run(n):
-        # every step: H2D of its points (on the copy stream, overlapping the previous step), the step itself, and a
-        # D2H read of its per-frame voxel counts.  The host consumes the counts of step i-1 while step i runs (one
-        # step of latency, the device queue never drains) and the last step's before the clock stops.
-        # With P front ends in flight the host reads P steps behind, and front end i % P alternates batches.
+    def src(i):
+        return host_ring[batch_of(i)][(i // 2) % ring_len]
+
+    def e2e_run(n, prepacked=None):
+        # step i: (pack i+P+1 starts) -> upload i+P -> forward i -> counts of step i-P.  The host consumes the counts P
+        # steps behind (the device queue never drains) and the last P before the clock stops.
+        # prepacked: the pinned batches are filled already (a loader that reads files straight into pinned memory).
+        if prepacked is None:
+            for j in range(min(P + 1, n)):
+                pinned[j % NP].fill_async(src(j))
         for j in range(min(P, n)):
-            stream.upload(host_batches[batch_of(j)])
+            stream.upload(pinned[j % NP] if prepacked is None else prepacked[batch_of(j)])
         seen = 0
         for i in range(n):
+            if prepacked is None and i + P + 1 < n:
+                pinned[(i + P + 1) % NP].fill_async(src(i + P + 1))
             if i + P < n:
-                stream.upload(host_batches[batch_of(i + P)])
+                stream.upload(pinned[(i + P) % NP] if prepacked is None else prepacked[batch_of(i + P)])
             stream.forward()
             if i >= P:
                 seen += int(stream.voxel_counts_host(lag=P)[-1])
@@ -529,10 +598,36 @@ def main():
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1)
+    # second figure: the same loop from batches that already sit in pinned memory (round 1's e2e definition)
+    prepacked = [PinnedFrameBatch.from_frames(frame_sets[c]) for c in sets_sorted]
+    e2e_run(2 * P * (P + 1), prepacked)
+    barrier()
+    f0.record()
+    e2e_run(args.steps, prepacked)
+    f1.record()
+    barrier()
+    ms_e2e_prepacked = f0.elapsed_time(f1)
+
+    # ---- one step at a time (P = 1) beside the in-flight figure -------------------------------------------
+    ms_single = None
+    if P > 1:
+        for i in range(4):
+            (graphs[0][i % 2].replay() if graphs is not None else step(i))
+        barrier()
+        f0.record()
+        for i in range(args.steps):
+            (graphs[0][i % 2].replay() if graphs is not None else step(i))
+        f1.record()
+        barrier()
+        ms_single = f0.elapsed_time(f1)
 
     from voxelnet_pytorch_b200 import sharding
 
-    ms_total, ms_e2e = sharding.reduce_max([ms_total, ms_e2e])  # device time, max over ranks
+    per_rank_ms = sharding.gather_floats(ms_total / args.steps)
+    per_rank_e2e_ms = sharding.gather_floats(ms_e2e / args.steps)
+    ms_total, ms_e2e, ms_e2e_prepacked = sharding.reduce_max([ms_total, ms_e2e, ms_e2e_prepacked])  # device time, max over ranks
+    if ms_single is not None:
+        ms_single = sharding.reduce_max([ms_single])[0]
     frames_total = sum(sharding.gather_ints(batch))
 
     stages = {k: v[0] for k, v in timer.summary().items()}
@@ -601,9 +696,9 @@ def main():
         dk = conv_roof[dom]
         kind = dk["bound"]
         line = {
-            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "metric": metric_name(args.config), "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms_step, "higher_is_better": True, "scaling": "strong" if args.config == "stress64" else "weak", "vs_baseline": None,
-            "dtype": "bf16", "data": "synthetic",
+            "dtype": "bf16", "data": DATA,
             "config": {"workload": desc, "name": args.config, "batch_per_gpu": batch, "points_per_batch": N_total,
                        "voxels_per_batch": K_total,
                        "inputs": "two different batches alternate step by step (resident outputs are restored where the previous batch reached)",
@@ -619,9 +714,19 @@ def main():
             "e2e": {"value": frames_total / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(sum(bt.host_points.numel() * 4 + bt.host_offsets.numel() * 4 for bt in batches) / 2),
                     "d2h_bytes_per_step": int(host_counts.numel() * 4),
-                    "note": "through voxelnet_pytorch_b200.HostFrameStream with %d front end(s) in flight: the H2D copy of a later step overlaps the running ones on a copy stream "
-                            "(%d staging buffers); result read back per step = per-frame voxel counts (consumed %d step(s) later, the last ones before the clock stops); "
-                            "the (B,128,H,W) tensor stays on the device for the RPN" % (P, P + 1, P)},
+                    "from": "per-frame (N_i,4) float32 numpy arrays in pageable host memory (where the reference starts, dataset.py:51); "
+                            "fresh array objects every step from a ring of %d x %.0f MB" % (2 * ring_len, max_points * 16 / 1e6),
+                    "host_pack_threads": int(n_pack),
+                    "value_from_prepacked_pinned_batches": frames_total / (ms_e2e_prepacked / args.steps * 1e-3),
+                    "ms_per_step_by_rank": per_rank_e2e_ms,
+                    "note": "every step inside the timed region: pack its %d frame arrays into a pinned batch (library thread pool), H2D copy on a copy stream, the step "
+                            "(voxelnet_pytorch_b200.HostFrameStream, %d front end(s) in flight, %d staging buffers), D2H of its per-frame voxel counts "
+                            "(consumed %d step(s) later, the last ones before the clock stops).  The %.2f GB (B,128,H,W) result stays on the device: its consumer, "
+                            "the RPN, runs on the same GPU" % (batch, P, P + 1, P, fe.out.numel() * 4 / 1e9)},
+            "ms_per_step_by_rank": per_rank_ms,
+            "single_pipeline": None if ms_single is None else {
+                "value": frames_total / (ms_single / args.steps * 1e-3), "ms_per_step": ms_single / args.steps,
+                "note": "ONE step at a time (graph replays back to back on one stream): the latency of a step; `value` above is throughput with %d steps in flight" % P},
             "gpu_launches": int(launches),
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
                          "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": traffic,
@@ -637,9 +742,8 @@ def main():
 
             cpu = cpu_reference_sample(target, frames[:4], OM.random_state_dict(0), args.cpu_seconds)
             line["cpu_baseline"] = {
-                "value": 1.0 / cpu["best_s"], "unit": UNIT, "cores": cpu["cores"], "kind": "port",
-                "sample": "%d single frames of the same workload (best of), reference CPU path restated in oracle/ "
-                          "(numpy voxelizer with per-point loop + torch-CPU VFE/scatter/Conv3d)" % cpu["frames"],
+                "value": 1.0 / cpu["best_s"], "unit": UNIT, "cores": cpu["cores"], "kind": cpu["kind"],
+                "sample": "%d single frames of the same workload (best of): %s" % (cpu["frames"], cpu["note"]),
                 "mean_s_per_frame": cpu["mean_s"], "stages_mean_s": cpu["stages_mean_s"], "host_cpus": cpu["host_cpus"],
             }
         emit(line)

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 11
+#define VN_ABI_VERSION 12
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -104,6 +104,14 @@ int vn_vfe_layer_fwd(const float* inputs, const uint8_t* mask, int64_t K, int32_
                      int32_t units, const float* weight /* [units, cin] */,
                      const float* bias /* [units] */, const float* bn_scale, const float* bn_shift,
                      float* out, vn_stream_t stream);
+
+/* Training-mode statistics of ONE stand-alone layer (VFELayer.forward under .train(), model.py:74-76): the
+ * BatchNorm1d there normalises relu(Linear(x)) with the statistics of all K*T rows (pad rows included).
+ * sums [2][units] f64 <- per-unit sum and sum of squares of relu(W x + b); zeroed by the call.  The caller folds
+ * them into (bn_scale, bn_shift) for vn_vfe_layer_fwd and updates the running statistics. */
+int vn_vfe_layer_batch_stats(const float* inputs, int64_t K, int32_t T, int32_t cin, int32_t units,
+                             const float* weight, const float* bias, double* sums /* [2][units] */,
+                             vn_stream_t stream);
 
 /* model.py:95-96: mask[k, t] = (max_j feature[k, t, j] != 0). */
 int vn_feature_mask(const float* feature, int64_t K, int32_t T, int32_t cin, uint8_t* mask,
@@ -360,6 +368,23 @@ int vn_rpn_targets(const float* anchors_standup, const double* anchors, int32_t 
                    const double* gt_boxes, const int32_t* gt_offsets, int32_t n_frames, int32_t n_boxes_total,
                    float pos_iou, float neg_iou, double anchor_h, double* pos_equal_one, double* neg_equal_one,
                    double* targets, void* workspace, size_t workspace_bytes, vn_stream_t stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Host-side frame packer (HOST pointers only; no CUDA call) - the head of the input path that replaces the
+ * reference's per-frame host voxelization + per-element `.to(device)` (voxelnet/dataset.py:51-58,
+ * voxelnet/model.py:302-303): a list of per-frame (N_i, 4) float32 arrays is gathered into ONE (page-locked) point
+ * buffer plus its CSR frame offsets by a pool of worker threads, so that a single asynchronous copy ships the batch.
+ *
+ * vn_host_pack_threads(n): sets the pool size before its first use (n > 0; default 4 or $VN_HOST_THREADS) and
+ *   returns the size in effect (0 = not created yet and no size requested).
+ * vn_host_pack_submit: enqueues the copy and returns a ticket > 0 at once (frame_offsets_host is filled before it
+ *   returns; the frame arrays and the destination must stay valid until the ticket is waited for), or a VN_ERR_*.
+ * vn_host_pack_wait(ticket): blocks until that job and every job submitted before it are complete.
+ * ------------------------------------------------------------------------------------------ */
+int vn_host_pack_threads(int32_t n_threads);
+int64_t vn_host_pack_submit(const float* const* frames_host, const int64_t* n_points_host, int32_t n_frames,
+                            float* points_host, int64_t capacity_points, int32_t* frame_offsets_host /* [n_frames+1] */);
+int vn_host_pack_wait(int64_t ticket);
 
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);

@@ -1,8 +1,10 @@
-"""TEST INFRASTRUCTURE (container-only): import the UNMODIFIED reference from /root/reference.
+"""TEST INFRASTRUCTURE: import the UNMODIFIED reference.
 
-Only `oracle/make_golden.py` and `tests/test_oracle_vs_reference.py` use this module, and only
-when `/root/reference` exists (it does not exist on the GPU box).  Nothing is copied: the
-reference sources are imported from where they lie.
+Where from: `$VN_REFERENCE_ROOT` if set, else `/root/reference` (this container), else `baseline/_ref/` - the
+byte-for-byte, git-ignored copy `oracle/install_ref.py` makes so that the reference travels to the GPU box
+(`/root/reference` does not exist there).  Users: `oracle/make_golden*.py`, `tests/test_oracle_vs_reference.py`,
+and `bench.py`'s `--impl reference` arm / `cpu_baseline` leg (the reference itself is what is timed, kind
+"reference").  The sources are imported from where they lie; nothing here edits them.
 
 The reference needs `yacs` (voxelnet/config.py:1), which is not installed in this image; a
 minimal stand-in for `yacs.config.CfgNode` (attribute-access dict with `clone()`) is injected
@@ -18,7 +20,18 @@ import os
 import sys
 import types
 
-REFERENCE_ROOT = "/root/reference"
+_REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _find_root() -> str:
+    cands = [os.environ.get("VN_REFERENCE_ROOT"), "/root/reference", os.path.join(_REPO, "baseline", "_ref")]
+    for c in cands:
+        if c and os.path.isfile(os.path.join(c, "voxelnet", "utils.py")):
+            return c
+    return "/root/reference"
+
+
+REFERENCE_ROOT = _find_root()
 REFERENCE_PKG = os.path.join(REFERENCE_ROOT, "voxelnet")
 
 

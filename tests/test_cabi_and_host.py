@@ -130,7 +130,7 @@ def test_modules_keep_reference_parameter_names_and_shapes():
     assert m.middle_layer[1].conv.stride == (1, 1, 1) and m.middle_layer[1].conv.padding == (0, 1, 1)
     with pytest.raises(ValueError):
         vn.ConvMD(2, 128, 128, 3, (1, 1), (1, 1))
-    with pytest.raises(NotImplementedError):
+    with pytest.raises(RuntimeError):  # train mode runs the statistics kernel: CUDA only, like every entry point
         vn.VFELayer(7, 32).train()(torch.zeros(1, 35, 7), torch.ones(1, 35, 1, dtype=torch.bool))
 
 
@@ -188,3 +188,37 @@ def test_raw_point_input_pipeline_host_side(tmp_path):
     (tmp_path / "bad.bin").write_bytes(b"\0" * 20)
     with pytest.raises(ValueError):
         load_velodyne_bin(str(tmp_path / "bad.bin"))
+
+
+def test_host_frame_packer_packs_ragged_frames_and_is_reusable():
+    """PinnedFrameBatch.fill / fill_async (vn_host_pack_submit / _wait, the library's host thread pool): ragged and
+    empty frames, non-float32 / non-contiguous inputs, reuse of the same buffer, capacity and shape errors."""
+    import voxelnet_pytorch_b200 as vn
+
+    rng = np.random.default_rng(3)
+    frames = [rng.random((n, 4), dtype=np.float32) for n in (70001, 0, 5, 333333, 1)]
+    pb = vn.PinnedFrameBatch(5, 500000)
+    pb.fill(frames)
+    want = np.concatenate(frames, 0)
+    assert pb.n_points == len(want) and pb.max_points_per_frame == 333333
+    assert pb.offsets.tolist() == [0, 70001, 70001, 70006, 403339, 403340]
+    assert np.array_equal(pb.points.numpy()[: pb.n_points], want)
+    # reuse with other dtypes / strides, asynchronously, several jobs in flight
+    others = [vn.PinnedFrameBatch(2, 1000) for _ in range(3)]
+    srcs = [[rng.random((300, 8))[:, ::2], rng.random((17, 4)).astype(np.float64)] for _ in others]
+    for o, fr in zip(others, srcs):
+        o.fill_async(fr)
+    pb.fill_async(frames[::-1])
+    for o, fr in zip(others, srcs):
+        o.wait_filled()
+        assert np.array_equal(o.points.numpy()[: o.n_points], np.concatenate([f.astype(np.float32) for f in fr], 0))
+    pb.wait_filled()
+    assert np.array_equal(pb.points.numpy()[: pb.n_points], np.concatenate(frames[::-1], 0))
+    with pytest.raises(ValueError):
+        pb.fill(frames[:4])
+    with pytest.raises(ValueError):
+        vn.PinnedFrameBatch(1, 10).fill([rng.random((11, 4), dtype=np.float32)])
+    with pytest.raises(ValueError):
+        vn.PinnedFrameBatch(1, 10).fill([rng.random((5, 3), dtype=np.float32)])
+    empty = vn.PinnedFrameBatch(2, 4).fill([np.zeros((0, 4), np.float32)] * 2)
+    assert empty.n_points == 0 and empty.offsets.tolist() == [0, 0, 0]

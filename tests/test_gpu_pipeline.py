@@ -42,7 +42,9 @@ def test_front_end_matches_oracle_ped(cuda_device):
     assert int(fe.dense.view(torch.int16).ne(0).sum()) == 0
 
 
-def test_front_end_car_shapes_and_determinism(cuda_device):
+def test_front_end_matches_oracle_car(cuda_device):
+    """Full chain on the Car grid (two full-size frames) against the oracle, plus determinism.  The benchmarked
+    configuration (4-frame batches, graph replay, three front ends in flight) is in tests/test_gpu_bench_parity.py."""
     sd = OM.random_state_dict(12)
     frames = synth_frames(2, 50)
     fe = _build(cuda_device, "Car", sd)
@@ -50,7 +52,10 @@ def test_front_end_car_shapes_and_determinism(cuda_device):
     b = fe.forward_frames(frames)
     assert a.shape == (2, 128, 400, 352)
     assert torch.equal(a, b)
-    assert bool(torch.isfinite(a).all())
+    _, feats, _, coords = oracle_batch(frames, "Car")
+    dense = OM.feature_learning_net([torch.from_numpy(f) for f in feats], [torch.from_numpy(c) for c in coords], sd, "Car")
+    want = OM.middle_layers(dense, sd)
+    assert rel_max_err(a.cpu(), want) < 1e-2
 
 
 @pytest.mark.parametrize("target", ["Car", "Pedestrian"])

@@ -82,11 +82,38 @@ def test_feature_mask(cuda_device):
     assert got.dtype == torch.bool and torch.equal(got.cpu(), want)
 
 
-def test_single_layer_train_mode_raises_and_points_to_the_net(cuda_device):
-    """VFELayer.forward alone implements eval BatchNorm only (its batch statistics need the statistics of
-    its own input rows; FeatureLearningNet does the two reduction passes)."""
+@pytest.mark.parametrize("cin,cout,T", [(7, 32, 35), (32, 128, 45)])
+def test_single_layer_train_mode_matches_oracle(cuda_device, cin, cout, T):
+    """VFELayer.forward alone under .train() (model.py:74-82): BatchNorm1d with the statistics of its own K*T input
+    rows (pads included), running statistics updated like nn.BatchNorm1d; gradients of the stand-alone layer against
+    autograd over the oracle."""
     import voxelnet_pytorch_b200 as vn
 
-    layer = vn.VFELayer(7, 32).to(cuda_device).train()
-    with pytest.raises(NotImplementedError):
-        layer(torch.zeros((1, 35, 7), device=cuda_device), torch.ones((1, 35, 1), dtype=torch.bool, device=cuda_device))
+    sd = OM.random_state_dict(61)
+    prefix = "vfe_1." if cin == 7 else "vfe_2."
+    g = torch.Generator().manual_seed(62)
+    x = torch.randn((97, T, cin), generator=g)
+    mask = torch.rand((97, T, 1), generator=g) > 0.4
+    layer = vn.VFELayer(cin, cout)
+    load_state(layer, sd, prefix)
+    layer = layer.to(cuda_device).train()
+    new_stats = {}
+    want = OM.vfe_layer(x, mask, sd, prefix, training=True, new_stats=new_stats)
+    with torch.no_grad():
+        got = layer(x.to(cuda_device), mask.to(cuda_device))
+    assert got.shape == want.shape
+    assert torch.allclose(got.cpu(), want, rtol=1e-4, atol=2e-5)
+    assert torch.allclose(layer.bn.running_mean.cpu(), new_stats[prefix + "bn.running_mean"], rtol=1e-5, atol=1e-6)
+    assert torch.allclose(layer.bn.running_var.cpu(), new_stats[prefix + "bn.running_var"], rtol=1e-5, atol=1e-6)
+    assert int(layer.bn.num_batches_tracked) == 1
+    # with gradients: the autograd node of the stand-alone layer
+    leaves = {k: v.clone().requires_grad_(True) for k, v in sd.items() if k.startswith(prefix) and v.dtype.is_floating_point}
+    xo = x.clone().requires_grad_(True)
+    up = torch.randn(want.shape, generator=g)
+    OM.vfe_layer(xo, mask, {**sd, **leaves}, prefix, training=True).backward(up)
+    xg = x.to(cuda_device).requires_grad_(True)
+    layer.zero_grad()
+    layer(xg, mask.to(cuda_device)).backward(up.to(cuda_device))
+    assert torch.allclose(xg.grad.cpu(), xo.grad, rtol=1e-3, atol=1e-5)
+    for name, p in (("fcn.0.weight", layer.fcn[0].weight), ("fcn.0.bias", layer.fcn[0].bias), ("bn.weight", layer.bn.weight), ("bn.bias", layer.bn.bias)):
+        assert torch.allclose(p.grad.cpu(), leaves[prefix + name].grad, rtol=1e-3, atol=1e-4), name

@@ -127,3 +127,27 @@ def test_oracle_training_gradients_match_reference_golden(golden_dir):
             assert float(np.abs(got).max()) < 1e-2 * float(np.abs(g["grad:" + k.replace("bias", "weight")]).max())
             continue
         assert float(np.abs(got - want).max()) / scale < 2e-3, (k, float(np.abs(got - want).max()) / scale)
+
+
+def test_oracle_whole_chain_matches_reference_golden_on_a_full_kitti_frame():
+    """CPU: the oracle chain on the committed full KITTI frame against the golden the UNMODIFIED reference produced
+    (oracle/make_golden_chain.py).  fp32 on both sides; only the conv primitive's summation order may differ
+    between hosts, hence 1e-5 of max instead of bit equality."""
+    import os
+
+    import torch
+
+    from oracle import cpu_chain
+
+    g = G.load("chain_kitti0_car.npz")
+    pcl = np.fromfile(os.path.join(G.GOLDEN, "kitti_0000000000.bin"), dtype=np.float32).reshape(-1, 4)
+    v = OV.pcl_to_voxels_fast(pcl, "Car")
+    assert G.sha(v["coordinate_buffer"]) == str(g["coordinate_sha256"])
+    assert G.sha(v["number_buffer"]) == str(g["number_sha256"])
+    assert G.sha(v["feature_buffer"]) == str(g["feature_sha256"])
+    out, _ = cpu_chain.front_end_cpu([pcl], OM.random_state_dict(int(g["state_seed"])), "Car", faithful_voxelizer=False)
+    assert tuple(out.shape) == tuple(g["out_shape"])
+    err = float((out[:, :, 1::4, 2::4] - torch.from_numpy(g["out_sample"])).abs().max()) / float(g["out_max_abs"])
+    assert err < 1e-5, err
+    sums = out.double().sum(dim=(0, 2, 3)).numpy()
+    assert np.allclose(sums, g["out_channel_sums"], rtol=1e-6, atol=1e-3)

@@ -14,7 +14,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 11
+VN_ABI_VERSION = 12
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 VN_CONV_FLAGS_PLANNED = 4
@@ -44,6 +44,7 @@ PROTOTYPES = {
     "vn_voxelize_fill": (C.c_int, [_G, _p, _p, _i32, _i64, _i32, _p, _i64, _p, _p, _p, _p, _sz, _p]),
     "vn_voxelize_counts_host": (C.c_int, [_p, _i32, _p, _p]),
     "vn_vfe_layer_fwd": (C.c_int, [_p, _p, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _p]),
+    "vn_vfe_layer_batch_stats": (C.c_int, [_p, _i64, _i32, _i32, _i32, _p, _p, _p, _p]),
     "vn_feature_mask": (C.c_int, [_p, _i64, _i32, _i32, _p, _p]),
     "vn_svfe_fused_fwd": (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "vn_voxelize_svfe_fused": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
@@ -74,6 +75,9 @@ PROTOTYPES = {
     "vn_conv1_dgrad_gather": (C.c_int, [_p, _p, _p, _i64, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p]),
     "vn_svfe_bwd": (C.c_int, [_p, _i64, _i32, _p, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "vn_launch_count": (_i64, []),
+    "vn_host_pack_threads": (C.c_int, [_i32]),
+    "vn_host_pack_submit": (_i64, [_p, _p, _i32, _p, _i64, _p]),
+    "vn_host_pack_wait": (C.c_int, [_i64]),
 }
 
 _lib = None

@@ -21,7 +21,7 @@ OBJ_DIR = os.path.join(HERE, "build")
 LIB_DIR = os.path.join(HERE, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libvoxelnet_b200.so")
 
-SOURCES = ["vn_api.cu", "vn_voxelize.cu", "vn_vfe.cu", "vn_scatter.cu", "vn_conv3d.cu", "vn_train.cu", "vn_conv3d_bwd.cu", "vn_train_bwd.cu", "vn_targets.cu"]
+SOURCES = ["vn_api.cu", "vn_voxelize.cu", "vn_vfe.cu", "vn_scatter.cu", "vn_conv3d.cu", "vn_train.cu", "vn_conv3d_bwd.cu", "vn_train_bwd.cu", "vn_targets.cu", "vn_host.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

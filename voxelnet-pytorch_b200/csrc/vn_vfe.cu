@@ -123,6 +123,80 @@ __global__ void __launch_bounds__(kWarps * 32)
   }
 }
 
+// Training-mode statistics of ONE stand-alone layer (VFELayer.forward in .train(), model.py:74-76: BatchNorm1d over
+// all K*T rows of relu(Linear(x)), pad rows included): per-unit sum and sum of squares in fp64.
+// One warp per voxel like k_vfe_layer; a lane owns unit u (and u+32) and adds per-voxel fp32 partials into doubles.
+template <int CIN, int UNITS>
+__global__ void __launch_bounds__(kWarps * 32)
+    k_vfe_layer_stats(const float* __restrict__ inputs, int64_t K, int T, const float* __restrict__ weight,
+                      const float* __restrict__ bias, double* __restrict__ sums /* [2][UNITS] */) {
+  constexpr int LD = CIN + 1;
+  constexpr int NU = UNITS < 32 ? 1 : UNITS / 32;
+  extern __shared__ float smem[];
+  float* s_w = smem;                // [UNITS][LD]
+  float* s_b = s_w + UNITS * LD;    // [UNITS]
+  float* s_rows = s_b + UNITS;      // [kWarps][kMaxT][LD]
+  __shared__ double s_acc[2 * 64];
+  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  for (int i = threadIdx.x; i < UNITS * CIN; i += blockDim.x) s_w[(i / CIN) * LD + i % CIN] = weight[i];
+  for (int i = threadIdx.x; i < UNITS; i += blockDim.x) s_b[i] = bias[i];
+  for (int i = threadIdx.x; i < 2 * 64; i += blockDim.x) s_acc[i] = 0.0;
+  __syncthreads();
+  float* rows = s_rows + warp * kMaxT * LD;
+  double acc_s[NU], acc_q[NU];
+#pragma unroll
+  for (int i = 0; i < NU; ++i) { acc_s[i] = 0.0; acc_q[i] = 0.0; }
+  const int tstep = UNITS < 32 ? 32 / UNITS : 1;
+  const int tfirst = UNITS < 32 ? lane / UNITS : 0;
+  const int64_t nwarps = (int64_t)gridDim.x * kWarps;
+  for (int64_t v = (int64_t)blockIdx.x * kWarps + warp; v < K; v += nwarps) {
+    const float* src = inputs + v * (int64_t)T * CIN;
+    for (int e = lane; e < T * CIN; e += 32) rows[(e / CIN) * LD + e % CIN] = src[e];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < NU; ++i) {
+      const int u = i * 32 + (lane % (UNITS < 32 ? UNITS : 32));
+      float ps = 0.0f, pq = 0.0f;
+      for (int t = tfirst; t < T; t += tstep) {
+        float a = s_b[u];
+#pragma unroll
+        for (int k = 0; k < CIN; ++k) a = fmaf(s_w[u * LD + k], rows[t * LD + k], a);
+        a = fmaxf(a, 0.0f);
+        ps += a;
+        pq = fmaf(a, a, pq);
+      }
+      acc_s[i] += (double)ps;
+      acc_q[i] += (double)pq;
+    }
+    __syncwarp();
+  }
+#pragma unroll
+  for (int i = 0; i < NU; ++i) {
+    const int u = i * 32 + (lane % (UNITS < 32 ? UNITS : 32));
+    atomicAdd(&s_acc[u], acc_s[i]);
+    atomicAdd(&s_acc[64 + u], acc_q[i]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < UNITS; i += blockDim.x) {
+    atomicAdd(&sums[i], s_acc[i]);
+    atomicAdd(&sums[UNITS + i], s_acc[64 + i]);
+  }
+}
+
+template <int CIN, int UNITS>
+int launch_vfe_layer_stats(const float* inputs, int64_t K, int T, const float* weight, const float* bias, double* sums,
+                           cudaStream_t st) {
+  constexpr int LD = CIN + 1;
+  const size_t smem = sizeof(float) * (UNITS * LD + UNITS + kWarps * kMaxT * LD);
+  VN_CUDA(cudaFuncSetAttribute(k_vfe_layer_stats<CIN, UNITS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  VN_CUDA(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * UNITS, st));
+  const int64_t want = (K + kWarps - 1) / kWarps;
+  const int64_t cap = (int64_t)sm_count() * 4;
+  k_vfe_layer_stats<CIN, UNITS><<<(unsigned)(want < cap ? want : cap), kWarps * 32, smem, st>>>(inputs, K, T, weight, bias, sums);
+  VN_LAUNCH_CHECK("k_vfe_layer_stats");
+  return VN_OK;
+}
+
 __global__ void __launch_bounds__(256)
     k_feature_mask(const float* __restrict__ feature, int64_t rows, int cin, uint8_t* __restrict__ mask) {
   const int64_t stride = (int64_t)gridDim.x * blockDim.x;
@@ -166,6 +240,19 @@ int vn_vfe_layer_fwd(const float* inputs, const uint8_t* mask, int64_t K, int32_
   if (cin == 7 && units == 16) return launch_vfe_layer<7, 16>(inputs, mask, K, T, weight, bias, bn_scale, bn_shift, out, st);
   if (cin == 32 && units == 64) return launch_vfe_layer<32, 64>(inputs, mask, K, T, weight, bias, bn_scale, bn_shift, out, st);
   set_error("vfe_layer: unsupported (cin=%d, units=%d); the reference instantiates (7,16) and (32,64)", cin, units);
+  return VN_ERR_UNSUPPORTED;
+}
+
+int vn_vfe_layer_batch_stats(const float* inputs, int64_t K, int32_t T, int32_t cin, int32_t units, const float* weight,
+                             const float* bias, double* sums, vn_stream_t stream) {
+  VN_REQUIRE(K >= 1, "vfe_layer_batch_stats: K < 1 (BatchNorm needs at least one row)");
+  VN_REQUIRE(T >= 1 && T <= kMaxT, "vfe_layer_batch_stats: T=%d outside [1,%d]", T, kMaxT);
+  VN_REQUIRE(inputs && weight && bias && sums, "vfe_layer_batch_stats: null pointer");
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(sums) & 7) == 0, "vfe_layer_batch_stats: sums must be 8-byte aligned");
+  cudaStream_t st = as_stream(stream);
+  if (cin == 7 && units == 16) return launch_vfe_layer_stats<7, 16>(inputs, K, T, weight, bias, sums, st);
+  if (cin == 32 && units == 64) return launch_vfe_layer_stats<32, 64>(inputs, K, T, weight, bias, sums, st);
+  set_error("vfe_layer_batch_stats: unsupported (cin=%d, units=%d); the reference instantiates (7,16) and (32,64)", cin, units);
   return VN_ERR_UNSUPPORTED;
 }
 

@@ -66,7 +66,15 @@ def load_velodyne_bin(path: str) -> np.ndarray:
 class PinnedFrameBatch:
     """A batch of frames concatenated in pinned host memory with its CSR frame offsets - what
     `HostFrameStream.upload` copies to the device asynchronously.  Buffers are reusable: `fill` packs a
-    new list of frames into the same pinned allocation (capacity = `max_points`)."""
+    new list of frames into the same pinned allocation (capacity = `max_points`).
+
+    Packing is done by the library's host thread pool (`vn_host_pack_submit`, include/voxelnet_b200.h): 31 MB per
+    Car batch of 16 is more than one thread copies within a 1.5 ms step.  `fill_async` returns at once and the
+    copy runs beside the caller; `upload` (or `wait_filled`) waits for it.
+
+    Reuse is safe: `upload` leaves an event on the batch that marks the end of its host->device copy and
+    `fill` / `fill_async` wait for that event before they overwrite the pinned points.  To keep the host from
+    blocking there, rotate at least (front ends in flight + 2) batches."""
 
     def __init__(self, n_frames: int, max_points: int):
         self.n_frames = int(n_frames)
@@ -74,26 +82,57 @@ class PinnedFrameBatch:
         self.offsets = _pinned(torch.zeros(self.n_frames + 1, dtype=torch.int32))
         self.n_points = 0
         self.max_points_per_frame = 0
+        self._ticket = 0        # pending vn_host_pack job (0: none)
+        self._keep = None       # the frame arrays of the pending job (they must outlive it)
+        self._in_flight = None  # torch.cuda.Event: end of the last H2D copy that reads this batch
 
-    def fill(self, frames: list) -> "PinnedFrameBatch":
+    def _check(self, frames: list) -> list:
         if len(frames) != self.n_frames:
             raise ValueError("expected %d frames, got %d" % (self.n_frames, len(frames)))
-        sizes = [int(f.shape[0]) for f in frames]
-        total = sum(sizes)
-        if total > self.points.shape[0]:
-            raise ValueError("batch of %d points exceeds the pinned capacity %d" % (total, self.points.shape[0]))
-        dst, off = self.points.numpy(), 0
-        offs = self.offsets.numpy()
-        offs[0] = 0
+        out = []
         for i, f in enumerate(frames):
             if f.ndim != 2 or f.shape[1] != 4:
                 raise ValueError("frame %d has shape %s, expected (N,4)" % (i, f.shape))
-            dst[off:off + sizes[i]] = f  # converts to float32 if needed
-            off += sizes[i]
-            offs[i + 1] = off
-        self.n_points = total
-        self.max_points_per_frame = max(sizes) if sizes else 0
+            if f.dtype != np.float32 or not f.flags["C_CONTIGUOUS"]:
+                f = np.ascontiguousarray(f, dtype=np.float32)  # the reference's loader yields float32 already
+            out.append(f)
+        total = sum(int(f.shape[0]) for f in out)
+        if total > self.points.shape[0]:
+            raise ValueError("batch of %d points exceeds the pinned capacity %d" % (total, self.points.shape[0]))
+        return out
+
+    def fill_async(self, frames: list) -> "PinnedFrameBatch":
+        """Start packing `frames` (list of (N_i,4) float32 arrays); returns immediately."""
+        import ctypes as C
+
+        from . import _cabi
+
+        self.wait_filled()
+        if self._in_flight is not None:  # the previous upload of this buffer must have left the host memory
+            self._in_flight.synchronize()
+            self._in_flight = None
+        fr = self._check(frames)
+        n = self.n_frames
+        ptrs = (C.c_void_p * max(n, 1))(*[f.ctypes.data for f in fr])
+        sizes = (C.c_int64 * max(n, 1))(*[int(f.shape[0]) for f in fr])
+        t = _cabi.lib().vn_host_pack_submit(ptrs, sizes, n, self.points.data_ptr(), self.points.shape[0], self.offsets.data_ptr())
+        if t <= 0:
+            _cabi.check(int(t), "vn_host_pack_submit")
+        self._ticket, self._keep = int(t), (fr, ptrs, sizes)
+        self.n_points = sum(int(f.shape[0]) for f in fr)
+        self.max_points_per_frame = max([int(f.shape[0]) for f in fr], default=0)
         return self
+
+    def wait_filled(self) -> "PinnedFrameBatch":
+        if self._ticket:
+            from . import _cabi
+
+            _cabi.check(_cabi.lib().vn_host_pack_wait(self._ticket), "vn_host_pack_wait")
+            self._ticket, self._keep = 0, None
+        return self
+
+    def fill(self, frames: list) -> "PinnedFrameBatch":
+        return self.fill_async(frames).wait_filled()
 
     @classmethod
     def from_frames(cls, frames: list) -> "PinnedFrameBatch":

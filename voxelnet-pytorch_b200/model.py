@@ -163,6 +163,35 @@ class _Conv1SparseTrainFn(torch.autograd.Function):
         return dvw, None, None, dw, torch.zeros_like(dgamma), dgamma, dbeta, None
 
 
+class _VFELayerTrainFn(torch.autograd.Function):
+    """A stand-alone VFELayer in training mode (model.py:74-82).  Forward: the library kernels (statistics kernel +
+    vfe_layer_fwd with the batch statistics folded).  Backward: a convenience outside the hot path - training goes
+    through FeatureLearningNet, whose backward is the fused `vn_svfe_bwd` kernels - so it is written with tensor
+    operations (recompute Linear -> ReLU -> batch-statistics BN -> max -> concat -> mask and differentiate that)."""
+
+    @staticmethod
+    def forward(ctx, inputs, mask, weight, bias, gamma, beta, stats, eps):
+        ctx.save_for_backward(inputs, mask, weight, bias, gamma, beta)
+        ctx.eps = eps
+        return ops.vfe_layer_fwd(inputs, mask, weight.detach().contiguous(), bias.detach().contiguous(), stats[0], stats[1])
+
+    @staticmethod
+    def backward(ctx, dout):
+        inputs, mask, weight, bias, gamma, beta = ctx.saved_tensors
+        with torch.enable_grad():
+            x = inputs.detach().requires_grad_(True)
+            leaves = [t.detach().requires_grad_(True) for t in (weight, bias, gamma, beta)]
+            w, b, g, be = leaves
+            pw = torch.relu(torch.nn.functional.linear(x, w, b))
+            flat = pw.reshape(-1, pw.shape[-1])
+            mean, var = flat.mean(0), flat.var(0, unbiased=False)
+            pw = (pw - mean) * torch.rsqrt(var + ctx.eps) * g + be
+            agg = pw.max(dim=1, keepdim=True)[0]
+            out = torch.cat([pw, agg.expand(-1, pw.shape[1], -1)], dim=2) * mask.reshape(pw.shape[0], pw.shape[1], 1).float()
+            grads = torch.autograd.grad(out, [x] + leaves, dout)
+        return grads[0], None, grads[1], grads[2], grads[3], grads[4], None, None
+
+
 class VFELayer(nn.Module):
     """model.py:60-82.  forward(inputs (K,T,cin) f32, mask (K,T,1) bool) -> (K,T,cout) f32."""
 
@@ -181,8 +210,21 @@ class VFELayer(nn.Module):
         return lin.weight.detach().contiguous(), lin.bias.detach().contiguous(), scale, shift
 
     def forward(self, inputs, mask):
-        _require_eval(self)  # a single layer in training mode needs the statistics of its own input; use FeatureLearningNet
-        return ops.vfe_layer_fwd(inputs.contiguous(), mask, *self.folded())
+        inputs = inputs.contiguous()
+        if not self.training:
+            return ops.vfe_layer_fwd(inputs, mask, *self.folded())
+        # model.py:74-76 under .train(): BatchNorm1d with the statistics of THIS input - all K*T rows of
+        # relu(Linear(x)), pad rows included - and the usual running-statistics update.
+        lin = self.fcn[0]
+        w, b = lin.weight.detach().contiguous(), lin.bias.detach().contiguous()
+        K, T, _ = inputs.shape
+        if K == 0:
+            raise ValueError("Expected more than 1 value per channel when training (an empty voxel batch)")
+        stats = _fold_batch_stats(self.bn, ops.vfe_layer_batch_stats(inputs.detach(), w, b), K * T)
+        needs_grad = torch.is_grad_enabled() and (inputs.requires_grad or any(p.requires_grad for p in self.parameters()))
+        if needs_grad:
+            return _VFELayerTrainFn.apply(inputs, mask, lin.weight, lin.bias, self.bn.weight, self.bn.bias, stats, self.bn.eps)
+        return ops.vfe_layer_fwd(inputs, mask, w, b, stats[0], stats[1])
 
 
 class FeatureLearningNet(nn.Module):

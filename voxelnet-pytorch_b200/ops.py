@@ -431,6 +431,23 @@ def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, str
 # ---------------------------------------------------------------------------------------------
 # training-mode BatchNorm (batch statistics)
 # ---------------------------------------------------------------------------------------------
+def vfe_layer_batch_stats(inputs, weight, bias) -> torch.Tensor:
+    """Sums for the batch statistics of ONE stand-alone VFE layer (model.py:74-76 in train mode): inputs (K,T,cin) f32
+    -> (2, units) f64, row 0 = sum over all K*T rows of relu(W x + b), row 1 = sum of squares."""
+    _require_cuda(inputs, weight, bias)
+    _contig(inputs, torch.float32)
+    K, T, cin = inputs.shape
+    units = weight.shape[0]
+    sums = torch.empty((2, units), dtype=torch.float64, device=inputs.device)
+    with torch.cuda.device(inputs.device):
+        check(
+            _cabi.lib().vn_vfe_layer_batch_stats(_ptr(inputs), K, T, cin, units, _ptr(_contig(weight, torch.float32)),
+                                                 _ptr(_contig(bias, torch.float32)), _ptr(sums), _stream()),
+            "vn_vfe_layer_batch_stats",
+        )
+    return sums
+
+
 def svfe_batch_stats(feature, stage: int, w1, b1, s1=None, t1=None, w2=None, b2=None, n_voxels_dev=None) -> torch.Tensor:
     """Sums for the batch statistics of VFE-1 (stage 1 -> (2,16) f64) or VFE-2 (stage 2 -> (2,64) f64) over all
     K*T rows of feature (K,T,7): row 0 = sum of relu(Linear), row 1 = sum of squares (model.py:75-76)."""

@@ -89,11 +89,27 @@ class VoxelNetFrontEnd:
         # StageTimer is attached: stage times are measured on the serial launch order)
         self.overlap_small_kernels = True
         self._shape = None
+        # bumped whenever the device buffers are (re)allocated: CUDA graphs captured before hold stale pointers
+        self._generation = 0
         self._layer_geometry = [(l.stride[0], l.padding[0]) for l in middle_net.middle_layer]
         self.refresh_parameters()
 
+    def _param_signature(self) -> tuple:
+        """(storage, version) of every parameter and buffer the folded tables are derived from: in-place updates
+        (optimizer steps, load_state_dict) bump `_version`, re-assignment changes the pointer."""
+        sig = []
+        for mod in (self.feature_net, self.middle_net.middle_layer):
+            for t in list(mod.parameters()) + list(mod.buffers()):
+                sig.append((t.data_ptr(), t._version))
+        return tuple(sig)
+
     def refresh_parameters(self) -> None:
-        """Re-fold BN / re-pack weights after the modules' parameters changed."""
+        """Re-fold BN / re-pack weights after the modules' parameters changed.  `forward_points` calls this by itself
+        when a parameter or BatchNorm buffer was modified since the last fold (checked by tensor version).  The folded
+        tables are new tensors, so steps captured before (`capture_graph`) become invalid: the generation is bumped
+        and their `replay()` raises instead of reading freed tables."""
+        self._sig = self._param_signature()
+        self._generation += 1
         if self.feature_net.training or self.middle_net.training:
             # training mode folds nothing ahead of time: BatchNorm uses the statistics of each batch
             # (forward_points_train); the eval-mode fast path is set up by the next call after .eval()
@@ -116,10 +132,27 @@ class VoxelNetFrontEnd:
             for st in self.out_states:  # the constants the untouched blocks hold depend on the parameters
                 st.fill_(0xFF)
 
+    def reserve(self, n_frames: int, max_points: int, device=None) -> None:
+        """Size every device buffer once for batches of `n_frames` frames and up to `max_points` points in total.
+        Later batches that fit reuse the buffers (and the CUDA graphs captured on them); a larger batch reallocates
+        everything, bumps `generation` and thereby invalidates every step captured before."""
+        dev = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        self._ensure_buffers(int(n_frames), int(max_points), dev)
+
+    @property
+    def generation(self) -> int:
+        return self._generation
+
     def _ensure_buffers(self, n_frames: int, n_points: int, device) -> None:
         shape = (n_frames, n_points, str(device))
         if self._shape is not None and self._shape[0] == n_frames and self._shape[1] >= n_points and self._shape[2] == str(device):
             return
+        if self._shape is not None:
+            # drop the old set first: two ~10 GB buffer sets per front end must not coexist
+            for name in ("workspace", "voxels", "voxelwise", "dense", "box_flags", "conv_workspaces", "out_states", "act1", "act2", "out"):
+                setattr(self, name, None)
+            self._train_coords = None
+        self._generation += 1
         c = self.cfg
         cap = min(self.cap_per_frame * n_frames, max(n_points, 1))
         T = c.points_per_voxel
@@ -157,7 +190,7 @@ class VoxelNetFrontEnd:
         resident_outputs it must not be modified by the caller (blocks no voxel reaches are not rewritten)."""
         if self.feature_net.training or self.middle_net.training:
             raise RuntimeError("forward_points is the eval-mode fast path; use forward_points_train in training mode")
-        if self._p1 is None:
+        if self._p1 is None or self._sig != self._param_signature():
             self.refresh_parameters()
         n_frames = frame_offsets.numel() - 1
         self._ensure_buffers(n_frames, points.shape[0], points.device)
@@ -288,7 +321,7 @@ class VoxelNetFrontEnd:
         side = torch.cuda.Stream(device=points.device)
         with torch.cuda.graph(graph, stream=side):
             self.forward_points(points, frame_offsets, max_points_per_frame)
-        return graph
+        return CapturedStep(self, graph)
 
     def _clear_train_cells(self) -> None:
         """Re-zero the grid cells the previous training step wrote (the eval path clears its own)."""
@@ -366,6 +399,25 @@ class VoxelNetFrontEnd:
         return offs
 
 
+class CapturedStep:
+    """A CUDA graph of one eval-mode step, tied to the buffer generation of its front end: `replay()` refuses to run
+    once the front end reallocated its buffers (a batch larger than any seen before, see `VoxelNetFrontEnd.reserve`)
+    - the captured kernels would write through stale pointers."""
+
+    def __init__(self, front_end, graph):
+        self.front_end, self.graph, self.generation = front_end, graph, front_end.generation
+
+    @property
+    def valid(self) -> bool:
+        return self.generation == self.front_end.generation
+
+    def replay(self) -> None:
+        if not self.valid:
+            raise RuntimeError("captured step is stale: the front end reallocated its buffers (generation %d -> %d); "
+                               "call reserve() with the largest batch first and capture again" % (self.generation, self.front_end.generation))
+        self.graph.replay()
+
+
 class HostFrameStream:
     """End-to-end feeding of a VoxelNetFrontEnd from pinned host batches (`dataset.PinnedFrameBatch`).
 
@@ -392,6 +444,8 @@ class HostFrameStream:
         # enqueued on the current stream - before the next forward() call.
         self.fes = list(front_end) if isinstance(front_end, (list, tuple)) else [front_end]
         self.fe, self.device = self.fes[0], dev
+        for fe in self.fes:  # sized once for the largest batch the staging slots can hold: no reallocation under a graph
+            fe.reserve(n_frames, max_points, dev)
         P = self.n_pipes = len(self.fes)
         self.compute = [torch.cuda.Stream(device=dev) for _ in range(P)] if P > 1 else [None]
         self._consumed = []  # events on the caller's stream, one per forward() call (the last P are kept)
@@ -421,6 +475,7 @@ class HostFrameStream:
             raise RuntimeError("every staging slot holds a batch that was not consumed: call forward() first")
         k = self.next_slot
         pts, offs = self.slots[k]
+        batch.wait_filled()  # a pending fill_async must have landed in the pinned buffer
         if batch.n_points > pts.shape[0] or batch.offsets.numel() != offs.numel():
             raise ValueError("batch does not fit the staging slot (points %d > %d or frame count differs)" % (batch.n_points, pts.shape[0]))
         with torch.cuda.stream(self.copy_stream):
@@ -428,6 +483,10 @@ class HostFrameStream:
             pts[: batch.n_points].copy_(batch.points[: batch.n_points], non_blocking=True)
             offs.copy_(batch.offsets, non_blocking=True)
             self.ready[k].record(self.copy_stream)
+            # the host may overwrite the pinned batch once this copy is done (PinnedFrameBatch.fill waits for it)
+            done = torch.cuda.Event()
+            done.record(self.copy_stream)
+            batch._in_flight = done
         self.h2d_bytes = batch.n_points * 16 + offs.numel() * 4
         self.pending.append((k, batch.n_points, batch.max_points_per_frame))
         self.next_slot = (k + 1) % self.n_slots
@@ -455,12 +514,17 @@ class HostFrameStream:
         training = fe.feature_net.training
         if training and P > 1:
             raise RuntimeError("several front ends in flight are an eval-mode feature (they would race on the parameters' .grad)")
-        key = (pipe, k, n, max_n)
+        key = (pipe, k, n, max_n, fe.generation)
         use_graph = self.cuda_graphs and not training and timer is None
         with torch.cuda.stream(cs):
             graph = self._graphs.get(key) if use_graph else None
+            if graph is None and use_graph:
+                for old in [q for q in self._graphs if q[0] == pipe and q[4] != fe.generation]:
+                    del self._graphs[old]  # captured before the front end replaced buffers or tables
             if graph is None and use_graph and key in self._seen:
                 graph = self._graphs[key] = fe.capture_graph(pts[:n], offs, max_n)
+                if not graph.valid:  # (cannot happen after reserve(); kept as a guard)
+                    raise RuntimeError("front end reallocated its buffers during graph capture")
             self._seen.add(key)
             if graph is not None:
                 graph.replay()
@@ -489,4 +553,8 @@ class HostFrameStream:
             raise RuntimeError("voxel_counts_host(lag=%d): no such step (yet), or more than %d steps back" % (lag, self.n_pipes))
         slot = (self._steps - 1 - lag) % (self.n_pipes + 1)
         self._counts_done[slot].synchronize()
-        return self._counts[slot]
+        counts = self._counts[slot]
+        fe = self.fes[(self._steps - 1 - lag) % self.n_pipes]
+        if int(counts[-1]) > fe.capacity:  # the kernels clamp: voxels beyond the capacity were dropped from the step
+            raise RuntimeError("voxel capacity %d exceeded (%d voxels): raise voxels_per_frame_capacity" % (fe.capacity, int(counts[-1])))
+        return counts

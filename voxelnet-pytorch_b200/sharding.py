@@ -43,6 +43,16 @@ def gather_ints(value: int) -> list:
     return [int(o.item()) for o in out]
 
 
+def gather_floats(value: float) -> list:
+    """Every rank's float (e.g. its own device-timed ms per step) on every rank, in rank order."""
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        return [float(value)]
+    t = torch.tensor([float(value)], dtype=torch.float64, device=_device_for_backend())
+    out = [torch.zeros_like(t) for _ in range(dist.get_world_size())]
+    dist.all_gather(out, t)
+    return [float(o.item()) for o in out]
+
+
 def allreduce_gradients(params, average: bool = True) -> int:
     """Data-parallel gradient exchange of the training config: the .grad tensors of
     `params` are packed into ONE flat fp32 buffer, summed over the ranks with a single all-reduce (NCCL over
