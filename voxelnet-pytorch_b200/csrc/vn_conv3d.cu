@@ -63,7 +63,8 @@ struct PlaneInfo {
   uint32_t wstride;   // bytes between the kh = 0, 1, 2 tile rows of the plane's kd class
 };
 
-// Work plan in the caller's workspace: header | groups[n_tiles] | tiles[n_tiles].
+// Work plan in the caller's workspace: header | groups[n_tiles] | tiles[n_tiles] | gtiles[n_tiles][kMaxGroupTiles]
+// (gtiles[g][i] = copy of the plan of the group's i-th tile: the conv kernel fetches a group with ONE dependent access).
 struct PlanHeader {
   int32_t n_groups;    // written by k_conv3d_plan (zeroed before it)
   int32_t next_group;  // the conv kernel's work counter (zeroed before it)
@@ -72,6 +73,8 @@ struct PlanHeader {
 struct GroupDesc {
   int32_t tile0;   // first tile (global tile index = (b * tiles_h + th) * tiles_w + tw)
   int32_t ntiles;  // consecutive tiles of the same tile row
+  int32_t b;       // frame ...
+  int16_t th, tw0; // ... tile row and first tile column (= tile0 decomposed: no integer divisions in the conv kernel)
 };
 struct TilePlan {
   uint32_t live;    // bit p*3 + kw: input box (p, kw) of this tile is live
@@ -82,7 +85,7 @@ struct TilePlan {
   uint8_t restore;  // bit d: output block d holds stale content of an earlier call and no accumulator feeds
                     // it now: rewrite it with the layer background (see PlanParams::out_state)
 };
-static_assert(sizeof(TilePlan) == 8 && sizeof(GroupDesc) == 8 && sizeof(PlanHeader) == 16, "plan layout");
+static_assert(sizeof(TilePlan) == 8 && sizeof(GroupDesc) == 16 && sizeof(PlanHeader) == 16, "plan layout");
 
 struct ConvParams {
   int B, Din, Dout, H, W;
@@ -99,8 +102,12 @@ struct ConvParams {
   PlanHeader* hdr;
   const GroupDesc* groups;
   const TilePlan* tiles;
+  const TilePlan* gtiles;
   PlaneInfo plane[kMaxPlanes];
-  unsigned long long* prof;  // debug: [grid][16] cycle counters (vn_conv3d_debug_profile), or nullptr
+  unsigned long long* prof;  // kDebug instantiation only: [grid][16] cycle counters (vn_conv3d_debug_profile)
+  int debug;                 // kDebug instantiation only: VN_DBG_* experiment switches (results are then wrong)
+  unsigned long long* trace; // kDebug: [trace_n][4] per message of CTA 0: producer acquire / issuer saw / issued / flags
+  int trace_n;
   double* stats;             // training kernel: [2][64] per-channel sum / sum of squares of the raw output
 };
 
@@ -117,6 +124,7 @@ struct PlanParams {
   PlanHeader* hdr;
   GroupDesc* groups;
   TilePlan* tiles;
+  TilePlan* gtiles;
   PlaneInfo plane[kMaxPlanes];
 };
 
@@ -126,8 +134,10 @@ struct Control {
   uint64_t acc_full[kSlots], acc_empty[kSlots];
   uint64_t sched_full[kSched], sched_empty[kSched];
   int32_t sched[kSched];
+  GroupDesc sched_gd[kSched];                     // the scheduled group's descriptor ...
+  TilePlan sched_tiles[kSched][kMaxGroupTiles];   // ... and tile plans, published by the producer for the epilogue
   uint32_t tmem_base;
-  uint32_t pad[3];
+  uint32_t pad[1];
   uint32_t row_zero[kSlots];  // [dout]: relu(interior shift row) - sub == 0 for all channels
   uint4 msg[kNA];  // one message per A stage, written by the producer before it arms full_a (see kMsg*)
   float scale[64];
@@ -148,6 +158,11 @@ constexpr uint32_t kMsgFreshShift = 4;   // bits 4-6: tap j starts its accumulat
 constexpr uint32_t kMsgEnd = 0x80;       // no more work
 constexpr uint32_t kMsgCommitShift = 8;  // bits 8-15: TMEM slots that are complete after this message
 constexpr uint32_t kMsgWaitShift = 16;   // bits 16-23: TMEM slots the epilogue must have drained before the MMAs
+// experiment switches of the kDebug instantiation (tools/prof_conv.py): what the kernel costs WITHOUT ...
+constexpr int kDbgNoALoad = 1;   // ... the TMA loads of the input boxes (the MMAs read stale shared memory)
+constexpr int kDbgNoBLoad = 2;   // ... the bulk loads of the weights
+constexpr int kDbgNoMma = 4;     // ... the tcgen05.mma instructions (commits only)
+constexpr int kDbgNoStore = 8;   // ... the epilogue's global stores
 constexpr uint32_t kDescHi = 0x40004040u;  // SW128 K-major descriptor, high word: SBO = 1024 B, version 1, layout 2
 
 __device__ __forceinline__ uint64_t desc_from_lo(uint32_t lo) { return ((uint64_t)kDescHi << 32) | lo; }
@@ -178,6 +193,8 @@ __device__ __forceinline__ uint32_t warp_or(uint32_t v) {
 __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ PlanParams Q) {
   __shared__ uint32_t s_live[kMaxTilesW];
   __shared__ uint8_t s_touched[kMaxTilesW], s_slot0[kMaxTilesW], s_restore[kMaxTilesW];
+  __shared__ int32_t s_group[kMaxTilesW];  // group of the tile (-1: in no group) ...
+  __shared__ uint8_t s_gpos[kMaxTilesW];   // ... and its position inside it
   const int b = blockIdx.x / Q.tiles_h, th = blockIdx.x % Q.tiles_h;
   const int tile_row0 = (b * Q.tiles_h + th) * Q.tiles_w;
   uint32_t valid = 0;
@@ -209,6 +226,7 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
       Q.out_state[tile_row0 + tw] = (uint8_t)touched;
     }
     s_live[tw] = live;
+    s_group[tw] = -1;
     s_slot0[tw] = 0;
     s_touched[tw] = (uint8_t)touched;
     s_restore[tw] = (uint8_t)(stale & ~touched & all_out);
@@ -223,7 +241,8 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
       const bool active = n > 0 || s_restore[tw] != 0;
       if (start >= 0 && (cur_slots + n > kSlots || tw - start == kMaxGroupTiles)) {
         const int g = atomicAdd(&Q.hdr->n_groups, 1);
-        Q.groups[g] = GroupDesc{tile_row0 + start, last - start + 1};
+        Q.groups[g] = GroupDesc{tile_row0 + start, last - start + 1, b, (int16_t)th, (int16_t)start};
+        for (int i = start; i <= last; ++i) { s_group[i] = g; s_gpos[i] = (uint8_t)(i - start); }
         start = -1;
       }
       if (start < 0) {
@@ -237,7 +256,8 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
     }
     if (start >= 0) {
       const int g = atomicAdd(&Q.hdr->n_groups, 1);
-      Q.groups[g] = GroupDesc{tile_row0 + start, last - start + 1};
+      Q.groups[g] = GroupDesc{tile_row0 + start, last - start + 1, b, (int16_t)th, (int16_t)start};
+      for (int i = start; i <= last; ++i) { s_group[i] = g; s_gpos[i] = (uint8_t)(i - start); }
     }
   }
   __syncthreads();
@@ -249,6 +269,7 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
     tp.nslots = (uint8_t)__popc((uint32_t)s_touched[tw]);
     tp.restore = s_restore[tw];
     Q.tiles[(size_t)tile_row0 + tw] = tp;
+    if (s_group[tw] >= 0) Q.gtiles[(size_t)s_group[tw] * kMaxGroupTiles + s_gpos[tw]] = tp;
   }
 }
 
@@ -259,7 +280,19 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
 // kTrain = true:  y = acc*scale + shift (the raw convolution: scale = 1, shift = bias) stored as bf16, and the
 //                 per-channel sum / sum of squares of the fp32 values accumulated into P.stats - the batch
 //                 statistics BatchNorm3d needs in training mode (model.py:153,161-162).
-template <bool kTrain>
+// kDebug = false is what every product call launches: no cycle counters, no experiment switches.
+#define VN_TIMED(acc, stmt)                    \
+  do {                                         \
+    if constexpr (kDebug) {                    \
+      const long long t_ = clock64();          \
+      stmt;                                    \
+      acc += clock64() - t_;                   \
+    } else {                                   \
+      stmt;                                    \
+    }                                          \
+  } while (0)
+
+template <bool kTrain, bool kDebug>
 __global__ void __launch_bounds__(kThreads, 1)
     k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ ConvParams P) {
   extern __shared__ uint8_t smem_raw[];
@@ -312,30 +345,55 @@ __global__ void __launch_bounds__(kThreads, 1)
     // ====== scheduler + planner + TMA producer (warp-uniform; one elected lane issues) ======
     uint32_t a_it = 0, b_it = 0, s_it = 0;
     long long pw_a = 0, pw_b = 0, p_boxes = 0;
-    const long long p_t0 = clock64();
+    const long long p_t0 = kDebug ? clock64() : 0;
+    const int dbg = kDebug ? P.debug : 0;
+    // The next group is fetched while the current one is processed: after the boxes of a group's first weight pass
+    // are on their way, the work counter is bumped and the next group's descriptor and tile plans are loaded (ONE
+    // dependent access: gtiles is indexed by the group); they are consumed when the group ends.  The ~1,500 clk of
+    // memory latency sit where the 4-deep box ring hides them, not between two groups (measured before: ~4,000 clk
+    // of idle tensor pipe per group switch - 3 dependent L2 accesses, then a cold first box).
+    int g_raw = 0;
+    if (lane == 0) g_raw = atomicAdd(&P.hdr->next_group, 1);
+    int g = __shfl_sync(0xffffffffu, g_raw, 0);
+    if (g >= n_groups) g = -1;
+    GroupDesc gd = GroupDesc{0, 0};
+    TilePlan tp = TilePlan{0u, 0, 0, 0, 0};
+    if (g >= 0) {
+      gd = P.groups[g];
+      if (lane < kMaxGroupTiles) tp = P.gtiles[(size_t)g * kMaxGroupTiles + lane];
+      if ((int)lane >= gd.ntiles) tp = TilePlan{0u, 0, 0, 0, 0};
+    }
     for (;;) {
       const uint32_t ss = s_it % kSched;
       mbar_wait(&ctl->sched_empty[ss], ((s_it / kSched) & 1) ^ 1);
-      int g = 0;
+      if (g >= 0 && lane < kMaxGroupTiles) ctl->sched_tiles[ss][lane] = tp;
+      __syncwarp();
       if (lane == 0) {
-        g = atomicAdd(&P.hdr->next_group, 1);
-        if (g >= n_groups) g = -1;
         ctl->sched[ss] = g;
+        ctl->sched_gd[ss] = gd;
         mbar_arrive(&ctl->sched_full[ss]);
       }
-      g = __shfl_sync(0xffffffffu, g, 0);
       ++s_it;
       if (g < 0) break;
-      const GroupDesc gd = P.groups[g];
-      TilePlan tp = TilePlan{0u, 0, 0, 0, 0};
-      if ((int)lane < gd.ntiles) tp = P.tiles[gd.tile0 + lane];
+      bool have_next = false;
+      int g_next = -1;
+      GroupDesc gd_next = GroupDesc{0, 0};
+      TilePlan tp_next = TilePlan{0u, 0, 0, 0, 0};
+      auto load_next = [&]() {
+        if (lane == 0) g_raw = atomicAdd(&P.hdr->next_group, 1);
+        g_next = __shfl_sync(0xffffffffu, g_raw, 0);
+        if (g_next >= n_groups) g_next = -1;
+        if (g_next >= 0) {
+          gd_next = P.groups[g_next];
+          if (lane < kMaxGroupTiles) tp_next = P.gtiles[(size_t)g_next * kMaxGroupTiles + lane];
+        }
+        have_next = true;
+      };
       const uint32_t mylive = tp.live, mytouched = tp.touched, myslot0 = tp.slot0;
       uint32_t mystarted = 0;  // lane t: accumulators of tile t that already hold a partial sum
       const uint32_t any = warp_or(mylive);
       const int last_kw = (any & kw_bits(2)) ? 2 : ((any & kw_bits(1)) ? 1 : 0);
-      const int tw0 = gd.tile0 % P.tiles_w;
-      const int th = (gd.tile0 / P.tiles_w) % P.tiles_h;
-      const int b = gd.tile0 / (P.tiles_w * P.tiles_h);
+      const int tw0 = gd.tw0, th = gd.th, b = gd.b;
       const int h0 = th * kTileH;
       for (int c = 0; c < P.nchunk; ++c) {
         for (int kw = 0; kw < 3; ++kw) {
@@ -343,11 +401,15 @@ __global__ void __launch_bounds__(kThreads, 1)
           const bool last_pass = (c == P.nchunk - 1) & (kw == last_kw);
           // all weights of this (chunk, kw): resident while the group's live boxes stream through
           const uint32_t sb = b_it % kNB;
-          { const long long t = clock64(); mbar_wait(&ctl->empty_b[sb], ((b_it / kNB) & 1) ^ 1); pw_b += clock64() - t; }
+          VN_TIMED(pw_b, mbar_wait(&ctl->empty_b[sb], ((b_it / kNB) & 1) ^ 1));
           if (elect_one()) {
-            mbar_arrive_expect_tx(&ctl->full_b[sb], kBSlotBytes);
-            bulk_load_1d(smem_b + sb * kBSlotBytes, P.wpack + (size_t)(c * 3 + kw) * kBSlotBytes, kBSlotBytes,
-                         &ctl->full_b[sb]);
+            if (kDebug && (dbg & kDbgNoBLoad)) {
+              mbar_arrive(&ctl->full_b[sb]);
+            } else {
+              mbar_arrive_expect_tx(&ctl->full_b[sb], kBSlotBytes);
+              bulk_load_1d(smem_b + sb * kBSlotBytes, P.wpack + (size_t)(c * 3 + kw) * kBSlotBytes, kBSlotBytes,
+                           &ctl->full_b[sb]);
+            }
           }
           __syncwarp();
           ++b_it;
@@ -368,12 +430,22 @@ __global__ void __launch_bounds__(kThreads, 1)
               const uint32_t flags = (uint32_t)pi.nkd | new_pass | (fresh << kMsgFreshShift) |
                                      ((fresh << slot_lo) << kMsgWaitShift);
               const uint32_t sa = a_it % kNA;
-              { const long long t = clock64(); mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1); pw_a += clock64() - t; }
-              ++p_boxes;
+              VN_TIMED(pw_a, mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1));
+              if (kDebug) {
+                ++p_boxes;
+                if (P.trace != nullptr && blockIdx.x == 0 && lane == 0 && (int)a_it < P.trace_n) {
+                  P.trace[(size_t)a_it * 4 + 0] = (unsigned long long)clock64();
+                  P.trace[(size_t)a_it * 4 + 3] = flags;
+                }
+              }
               if (elect_one()) {
                 ctl->msg[sa] = make_uint4(flags, slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
-                mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
-                tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
+                if (kDebug && (dbg & kDbgNoALoad)) {
+                  mbar_arrive(&ctl->full_a[sa]);
+                } else {
+                  mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
+                  tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
+                }
               }
               __syncwarp();
               started |= range;
@@ -394,8 +466,14 @@ __global__ void __launch_bounds__(kThreads, 1)
               ++a_it;
             }
           }
+          if (!have_next) load_next();  // (after the first pass: the counter bump has returned by now)
         }
       }
+      if (!have_next) load_next();
+      if ((int)lane >= gd_next.ntiles) tp_next = TilePlan{0u, 0, 0, 0, 0};
+      g = g_next;
+      gd = gd_next;
+      tp = tp_next;
     }
     {  // tell the issuing warp to stop
       const uint32_t sa = a_it % kNA;
@@ -406,76 +484,89 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
       __syncwarp();
     }
-    if (P.prof != nullptr && lane == 0) {
+    if (kDebug && P.prof != nullptr && lane == 0) {
       unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
       o[0] = (unsigned long long)(clock64() - p_t0); o[1] = pw_a; o[2] = pw_b; o[3] = p_boxes;
     }
   } else if (warp == 1) {
-    // ============ MMA issuer: interprets the producer's messages (warp-uniform) ============
-    uint32_t a_it = 0, b_it = 0;
-    uint32_t acc_phase = 0;  // bit s: parity of the number of times TMEM slot s has been (re)started
-    const uint32_t a_lo0 = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (1u << 16);
-    const uint32_t b_lo0 = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | (1u << 16);
-    uint32_t b_lo_pass = b_lo0;
+    // ============ MMA issuer: ONE thread interprets the producer's messages ============
+    // Software-pipelined.  Measured with the instrumented instantiation (tools/prof_conv.py, tools/probes/mma_probe.cu):
+    // the tensor pipe accepts only ~2 MMAs ahead of the one it executes (a 128x64x16 MMA takes 48 clk, 128x128x16 64 clk),
+    // so whatever the issuing thread does between two MMAs that takes longer than that leaves the pipe idle - and it used
+    // to spend ~300 clk between the last MMA of one message and the first of the next (warp-wide waits, elections, the
+    // message read).  Now a single thread runs the loop (no warp collectives), and the next message is probed, read and
+    // decoded BETWEEN the MMAs of the current one; only what may legitimately block (a new weight pass, an accumulator
+    // the epilogue still holds) stays in front of a message's first MMA.
     long long mw_a = 0, mw_b = 0, mw_acc = 0;
-    const long long m_t0 = clock64();
-    for (;;) {
-      const uint32_t sa = a_it % kNA;
-      { const long long t = clock64(); mbar_wait(&ctl->full_a[sa], (a_it / kNA) & 1); mw_a += clock64() - t; }
-      const uint4 msg = ctl->msg[sa];
-      const uint32_t f = msg.x;
-      if (f & kMsgNewPass) {
-        if (b_it != 0) {  // the previous pass is fully issued: its weights may be overwritten once it completes
-          if (elect_one()) umma_commit(&ctl->empty_b[(b_it - 1) % kNB]);
-          __syncwarp();
+    const long long m_t0 = kDebug ? clock64() : 0;
+    if (elect_one()) {
+      uint32_t a_it = 0, b_it = 0;
+      uint32_t acc_phase = 0;  // bit s: parity of the number of times TMEM slot s has been (re)started
+      const uint32_t a_lo0 = ((smem_u32(smem_a) >> 4) & 0x3FFFu) | (1u << 16);
+      const uint32_t b_lo0 = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | (1u << 16);
+      uint32_t b_lo_pass = b_lo0;
+      const bool no_mma = kDebug && (P.debug & kDbgNoMma);
+      VN_TIMED(mw_a, mbar_wait(&ctl->full_a[0], 0));
+      uint4 msg = lds_u4(&ctl->msg[0]);
+      for (;;) {
+        const uint32_t sa = a_it % kNA;
+        const bool tr = kDebug && P.trace != nullptr && blockIdx.x == 0 && (int)a_it < P.trace_n;
+        if (tr) P.trace[(size_t)a_it * 4 + 1] = (unsigned long long)clock64();
+        const uint32_t f = msg.x;
+        if (f & kMsgNewPass) {
+          // the previous pass is fully issued: its weights may be overwritten once it completes
+          if (b_it != 0) umma_commit(&ctl->empty_b[(b_it - 1) % kNB]);
+          VN_TIMED(mw_b, mbar_wait(&ctl->full_b[b_it % kNB], (b_it / kNB) & 1));
+          b_lo_pass = b_lo0 + (b_it % kNB) * (kBSlotBytes >> 4);
+          ++b_it;
         }
-        { const long long t = clock64(); mbar_wait(&ctl->full_b[b_it % kNB], (b_it / kNB) & 1); mw_b += clock64() - t; }
-        b_lo_pass = b_lo0 + (b_it % kNB) * (kBSlotBytes >> 4);
-        ++b_it;
-      }
-      const uint32_t wait_mask = (f >> kMsgWaitShift) & 0xffu;
-      if (wait_mask) {  // accumulators started by this box must have been drained by the epilogue
-        uint32_t wm = wait_mask;
-        while (wm) {
-          const uint32_t s = __ffs(wm) - 1;
-          wm &= wm - 1;
-          { const long long t = clock64(); mbar_wait(&ctl->acc_empty[s], ((acc_phase >> s) & 1) ^ 1); mw_acc += clock64() - t; }
+        const uint32_t wait_mask = (f >> kMsgWaitShift) & 0xffu;
+        if (wait_mask) {  // accumulators started by this box must have been drained by the epilogue
+          uint32_t wm = wait_mask;
+          while (wm) {
+            const uint32_t s = __ffs(wm) - 1;
+            wm &= wm - 1;
+            VN_TIMED(mw_acc, mbar_wait(&ctl->acc_empty[s], ((acc_phase >> s) & 1) ^ 1));
+          }
+          acc_phase ^= wait_mask;
         }
-        acc_phase ^= wait_mask;
-      }
-      tc_fence_after_sync();
-      const uint32_t nkd = f & kMsgNkdMask;
-      if (nkd != 0) {
-        if (elect_one()) {
+        tc_fence_after_sync();
+        const uint32_t nkd = f & kMsgNkdMask;
+        const uint32_t sn = (a_it + 1) % kNA, pn = ((a_it + 1) / kNA) & 1;
+        bool have_next = false;
+        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
+        if (nkd != 0) {
           const uint32_t d_tmem = tmem_base + msg.y;
           const uint32_t a_lo = a_lo0 + sa * (kABytes >> 4);
           const uint32_t b_lo = b_lo_pass + msg.z;
           const uint32_t idesc = umma_idesc_bf16(128, 64) + ((nkd - 1u) << 20);  // N = 64 * nkd
           const uint32_t fresh = (f >> kMsgFreshShift) & 7u;
           const bool split = fresh != 0 && fresh != (1u << nkd) - 1u;  // rare: neighbours in different states
+          if (!no_mma) {  // kh = 0
+            if (split) {  // first k-step per accumulator (N = 64): accumulate only where a partial sum exists
+              for (uint32_t j = 0; j < nkd; ++j)
+                umma_bf16_ss(d_tmem + j * 64, desc_from_lo(a_lo), desc_from_lo(b_lo + j * (kBTapBytes >> 4)),
+                             umma_idesc_bf16(128, 64), ((fresh >> j) & 1) ^ 1);
+            } else {
+              umma_bf16_ss(d_tmem, desc_from_lo(a_lo), desc_from_lo(b_lo), idesc, fresh ? 0u : 1u);
+            }
 #pragma unroll
-          for (int kh = 0; kh < 3; ++kh) {
-            const uint32_t a = a_lo + kh * ((kTileW * 128) >> 4);
-            const uint32_t bq = b_lo + kh * msg.w;
+            for (int k = 1; k < 4; ++k) umma_bf16_ss(d_tmem, desc_from_lo(a_lo + k * 2), desc_from_lo(b_lo + k * 2), idesc, 1u);
+          }
+          // in the shadow of those MMAs: is the next message there already?  (normally yes: the producer runs ahead)
+          have_next = mbar_test_wait(&ctl->full_a[sn], pn);
+          if (have_next) nxt = lds_u4(&ctl->msg[sn]);
+          if (!no_mma) {  // kh = 1, 2
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-              if (kh == 0 && k == 0) {
-                if (split) {  // first k-step per accumulator (N = 64): accumulate only where a partial sum exists
-                  for (uint32_t j = 0; j < nkd; ++j)
-                    umma_bf16_ss(d_tmem + j * 64, desc_from_lo(a), desc_from_lo(bq + j * (kBTapBytes >> 4)),
-                                 umma_idesc_bf16(128, 64), ((fresh >> j) & 1) ^ 1);
-                } else {
-                  umma_bf16_ss(d_tmem, desc_from_lo(a), desc_from_lo(bq), idesc, fresh ? 0u : 1u);
-                }
-              } else {
-                umma_bf16_ss(d_tmem, desc_from_lo(a + k * 2), desc_from_lo(bq + k * 2), idesc, 1u);
-              }
+            for (int kh = 1; kh < 3; ++kh) {
+              const uint32_t a = a_lo + kh * ((kTileW * 128) >> 4);
+              const uint32_t bq = b_lo + kh * msg.w;
+#pragma unroll
+              for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, desc_from_lo(a + k * 2), desc_from_lo(bq + k * 2), idesc, 1u);
             }
           }
           umma_commit(&ctl->empty_a[sa]);
-        }
-      } else {
-        if (elect_one()) {
+        } else {
           uint32_t cm = (f >> kMsgCommitShift) & 0xffu;
           while (cm) {
             const uint32_t s = __ffs(cm) - 1;
@@ -484,15 +575,21 @@ __global__ void __launch_bounds__(kThreads, 1)
           }
           mbar_arrive(&ctl->empty_a[sa]);
         }
+        if (tr) P.trace[(size_t)a_it * 4 + 2] = (unsigned long long)clock64();
+        ++a_it;
+        if (f & kMsgEnd) break;
+        if (!have_next) {
+          VN_TIMED(mw_a, mbar_wait(&ctl->full_a[sn], pn));
+          nxt = lds_u4(&ctl->msg[sn]);
+        }
+        msg = nxt;
       }
-      __syncwarp();
-      ++a_it;
-      if (f & kMsgEnd) break;
+      if (kDebug && P.prof != nullptr) {
+        unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
+        o[4] = (unsigned long long)(clock64() - m_t0); o[5] = mw_a; o[6] = mw_b; o[7] = mw_acc;
+      }
     }
-    if (P.prof != nullptr && lane == 0) {
-      unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
-      o[4] = (unsigned long long)(clock64() - m_t0); o[5] = mw_a; o[6] = mw_b; o[7] = mw_acc;
-    }
+    __syncwarp();
   } else {
     // ===================== epilogue (warps 2..9) =====================
     // Two warps per TMEM lane quadrant (a warp may only read lanes 32*(warp%4)..+31): warps 2..5 take
@@ -507,19 +604,16 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
     for (int j = 0; j < (kTrain ? 32 : 1); ++j) { st_s[j] = 0.0f; st_q[j] = 0.0f; }
     long long ew_sched = 0, ew_acc = 0;
-    const long long e_t0 = clock64();
+    const long long e_t0 = kDebug ? clock64() : 0;
+    const bool no_store = kDebug && (P.debug & kDbgNoStore);
     for (;;) {
       const uint32_t ss = s_it % kSched;
-      { const long long t = clock64(); mbar_wait(&ctl->sched_full[ss], (s_it / kSched) & 1); ew_sched += clock64() - t; }
+      VN_TIMED(ew_sched, mbar_wait(&ctl->sched_full[ss], (s_it / kSched) & 1));
       const int g = ctl->sched[ss];
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->sched_empty[ss]);
       ++s_it;
       if (g < 0) break;
-      const GroupDesc gd = P.groups[g];
-      const int tw0 = gd.tile0 % P.tiles_w;
-      const int th = (gd.tile0 / P.tiles_w) % P.tiles_h;
-      const int b = gd.tile0 / (P.tiles_w * P.tiles_h);
+      const GroupDesc gd = ctl->sched_gd[ss];  // (the ring slot is handed back when the group is done, below)
+      const int tw0 = gd.tw0, th = gd.th, b = gd.b;
       const int h = th * kTileH + hl;
       const bool inside = h < P.H;
       const int vh = h == 0 ? 1 : (h == P.H - 1 ? 2 : 0);
@@ -527,7 +621,7 @@ __global__ void __launch_bounds__(kThreads, 1)
       const bool rows_interior = th > 0 && (th + 1) * kTileH < P.H;
       uint32_t used = 0;
       for (int t = 0; t < gd.ntiles; ++t) {
-        const TilePlan tp = P.tiles[gd.tile0 + t];
+        const TilePlan tp = ctl->sched_tiles[ss][t];
         const uint32_t touched = tp.touched;
         used |= ((1u << tp.nslots) - 1u) << tp.slot0;
         const int tw = tw0 + t;
@@ -539,6 +633,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           const bool has_acc = (touched >> dout) & 1;  // else: no live box reached this accumulator
           if (!has_acc && !((tp.restore >> dout) & 1)) continue;  // the block already holds the layer background
           if (!kTrain && !has_acc && P.out_mode == 0 && tile_interior && ctl->row_zero[dout]) {
+            if (no_store) continue;
             // nothing but background in reach and the layer stores deviations: the 16 KB block is zero.
             // This warp clears tile rows 4*quad + 2*half, +1 (1 KB each, contiguous).
             __nv_bfloat16* dst0 = reinterpret_cast<__nv_bfloat16*>(P.out) +
@@ -554,7 +649,7 @@ __global__ void __launch_bounds__(kThreads, 1)
           const uint32_t slot = tp.slot0 + __popc(touched & ((1u << dout) - 1u));
           uint32_t r[32];
           if (has_acc) {
-            { const long long t = clock64(); mbar_wait(&ctl->acc_full[slot], (acc_phase >> slot) & 1); ew_acc += clock64() - t; }
+            VN_TIMED(ew_acc, mbar_wait(&ctl->acc_full[slot], (acc_phase >> slot) & 1));
             tc_fence_after_sync();
             tmem_ld_32x32b_x32(tmem_base + ((quad * 32) << 16) + slot * 64 + half * 32, r);
             tmem_ld_wait();
@@ -566,7 +661,7 @@ __global__ void __launch_bounds__(kThreads, 1)
 #pragma unroll
             for (int j = 0; j < 32; ++j) r[j] = 0u;
           }
-          if (inside) {
+          if (inside && !no_store) {
             const float* shift_row = ctl->table + (variant * P.Dout + dout) * 64 + half * 32;
             const float* sub_row = ctl->sub + dout * 64 + half * 32;
             float v[32];
@@ -606,8 +701,10 @@ __global__ void __launch_bounds__(kThreads, 1)
         }
       }
       acc_phase ^= used;
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->sched_empty[ss]);
     }
-    if (P.prof != nullptr && threadIdx.x == 64) {
+    if (kDebug && P.prof != nullptr && threadIdx.x == 64) {
       unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
       o[8] = (unsigned long long)(clock64() - e_t0); o[9] = ew_sched; o[10] = ew_acc;
     }
@@ -855,17 +952,21 @@ EncodeTiledFn encode_tiled_fn() {
 }
 
 unsigned long long* g_debug_prof = nullptr;
+int g_debug_flags = 0;
+unsigned long long* g_debug_trace = nullptr;
+int g_debug_trace_n = 0;
 
 int out_depth(int Din, int stride_d, int pad_d) { return (Din + 2 * pad_d - 3) / stride_d + 1; }
 
 struct PlanLayout {
-  size_t groups_off, tiles_off, total;
+  size_t groups_off, tiles_off, gtiles_off, total;
 };
 PlanLayout plan_layout(int64_t n_tiles) {
   PlanLayout L;
   L.groups_off = sizeof(PlanHeader);
   L.tiles_off = L.groups_off + (size_t)n_tiles * sizeof(GroupDesc);
-  L.total = L.tiles_off + (size_t)n_tiles * sizeof(TilePlan);
+  L.gtiles_off = L.tiles_off + (size_t)n_tiles * sizeof(TilePlan);
+  L.total = L.gtiles_off + (size_t)n_tiles * kMaxGroupTiles * sizeof(TilePlan);  // (at most one group per tile)
   return L;
 }
 
@@ -895,6 +996,13 @@ size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W) {
  * into buf [148][16] u64: producer {total, wait empty_a, wait empty_b, boxes}, MMA issuer {total, wait
  * full_a, wait full_b, wait acc_empty}, epilogue warp 2 {total, wait sched, wait acc_full}.  NULL: off. */
 void vn_conv3d_debug_profile(void* buf) { g_debug_prof = static_cast<unsigned long long*>(buf); }
+/* Debug aid: experiment switches of the instrumented instantiation (1: no input-box loads, 2: no weight loads, 4: no
+ * MMAs, 8: no epilogue stores).  Results are wrong while any is set; a non-NULL profile buffer or a non-zero flag word
+ * selects the instrumented kernel, otherwise the production instantiation (no counters) runs. */
+void vn_conv3d_debug_flags(int32_t flags) { g_debug_flags = flags; }
+/* Debug aid: per-message timestamps of CTA 0 of the next conv launches into buf [n][4] u64 (producer acquired the stage,
+ * issuer saw it, issuer done with it, message flags).  Only read by the instrumented instantiation. */
+void vn_conv3d_debug_trace(void* buf, int32_t n) { g_debug_trace = static_cast<unsigned long long*>(buf); g_debug_trace_n = n; }
 
 size_t vn_conv3d_packed_weight_bytes(int32_t cin) {
   if (cin != 64 && cin != 128) return 0;
@@ -1004,6 +1112,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   PlanHeader* hdr = reinterpret_cast<PlanHeader*>(ws);
   GroupDesc* groups = reinterpret_cast<GroupDesc*>(ws + L.groups_off);
   TilePlan* tiles = reinterpret_cast<TilePlan*>(ws + L.tiles_off);
+  TilePlan* gtiles = reinterpret_cast<TilePlan*>(ws + L.gtiles_off);
 
   EncodeTiledFn encode = encode_tiled_fn();
   if (encode == nullptr) {
@@ -1031,7 +1140,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   Q.consume = (flag_opts & VN_CONV_FLAGS_CONSUME) ? 1 : 0;
   Q.force_ring = (flag_opts & VN_CONV_FLAGS_BORDER_RING) ? 1 : 0;
   Q.out_state = out_state;
-  Q.hdr = hdr; Q.groups = groups; Q.tiles = tiles;
+  Q.hdr = hdr; Q.groups = groups; Q.tiles = tiles; Q.gtiles = gtiles;
   if ((transposed_dout > 0 ? plan_planes_transposed(Q, stride_d, pad_d) : plan_planes(Q, stride_d, pad_d)) != 0) {
     set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
     return VN_ERR_UNSUPPORTED;
@@ -1054,18 +1163,24 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   P.table_plain = n_variants == 0 ? 1 : 0;
   P.sub = sub;
   P.out = y;
-  P.hdr = hdr; P.groups = groups; P.tiles = tiles;
+  P.hdr = hdr; P.groups = groups; P.tiles = tiles; P.gtiles = gtiles;
   P.prof = g_debug_prof;
+  P.debug = g_debug_flags;
+  P.trace = g_debug_trace;
+  P.trace_n = g_debug_trace_n;
   for (int p = 0; p < kMaxPlanes; ++p) P.plane[p] = Q.plane[p];
 
   const int grid = n_tiles < sm_count() ? (int)n_tiles : sm_count();
   P.stats = stats;
   if (stats != nullptr) {
-    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    k_conv3d_bn_relu<true><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<true, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+  } else if (P.prof != nullptr || P.debug != 0) {
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<false, true><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   } else {
-    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    k_conv3d_bn_relu<false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<false, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   }
   VN_LAUNCH_CHECK("k_conv3d_bn_relu");
   return VN_OK;
@@ -1108,6 +1223,7 @@ int vn_conv3d_plan(int32_t B, int32_t Din, int32_t H, int32_t W, int32_t stride_
   Q.hdr = reinterpret_cast<PlanHeader*>(ws);
   Q.groups = reinterpret_cast<GroupDesc*>(ws + L.groups_off);
   Q.tiles = reinterpret_cast<TilePlan*>(ws + L.tiles_off);
+  Q.gtiles = reinterpret_cast<TilePlan*>(ws + L.gtiles_off);
   if (plan_planes(Q, stride_d, pad_d) != 0) {
     set_error("conv3d_plan: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
     return VN_ERR_UNSUPPORTED;

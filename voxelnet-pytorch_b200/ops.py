@@ -380,7 +380,7 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
 
 def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, stride_d: int, pad_d: int) -> dict:
     """Diagnostics (blocking, host side): decode the work plan the last vn_conv3d_bn_relu_fwd call left
-    in `workspace` (PlanHeader | GroupDesc[n_tiles] | TilePlan[n_tiles], see vn_conv3d.cu) and count
+    in `workspace` (PlanHeader 16 B | GroupDesc[n_tiles] 16 B each | TilePlan[n_tiles] 8 B each | per-group copies, see vn_conv3d.cu) and count
     what the kernel actually executed: live input boxes, tcgen05 FLOPs, operand bytes loaded by TMA.
     Used by bench.py for the executed-work roofline; not part of the product path."""
     import numpy as np
@@ -390,7 +390,7 @@ def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, str
     n_tiles = B * tiles_h * tiles_w
     raw = workspace.cpu().numpy()
     hdr = raw[:16].view(np.int32)
-    tiles = raw[16 + 8 * n_tiles: 16 + 16 * n_tiles].view(np.uint32).reshape(n_tiles, 2)
+    tiles = raw[16 + 16 * n_tiles: 16 + 24 * n_tiles].view(np.uint32).reshape(n_tiles, 2)
     live = tiles[:, 0]
     touched = tiles[:, 1] & 0xFF
     restore = (tiles[:, 1] >> 24) & 0xFF
