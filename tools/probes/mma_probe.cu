@@ -48,6 +48,50 @@ __global__ void __launch_bounds__(128, 1) k_probe(int N, int rounds, int a_strid
         }
         umma_commit(&bar);
       }
+    } else if (mode >= 100) {
+      // switch the destination accumulator every `period` MMAs (mode = 100 + period), rotating over 4 accumulators
+      const int sh = mode - 100;  // period = 1 << sh
+      if (elect_one()) {
+        t0 = clock64();
+        int cnt = 0;
+        for (int r = 0; r < rounds; ++r) {
+          const uint32_t a = a_lo0 + (r & 3) * a_stride16;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const uint32_t d = tmem + ((cnt >> sh) & 3) * 128;
+            umma_bf16_ss(d, hi | (a + k * 2), hi | (b_lo0 + k * 2), idesc, 1u);
+            ++cnt;
+          }
+        }
+        umma_commit(&bar);
+      }
+    } else if (mode >= 4) {
+      // single-thread issuer as in k_conv3d_bn_relu: per "message" 12 MMAs + commit; mode bits: 1 = tcgen05.fence::after_thread_sync
+      // per message, 2 = barrier probe + message read between the MMA groups, 4 (mode 8+) = first MMA overwrites + rotating accumulators
+      const int opt = mode - 4;
+      if (elect_one()) {
+        t0 = clock64();
+        uint32_t acc = 0;
+        for (int r = 0; r < rounds; r += 3) {
+          const int m = r / 3;
+          const uint32_t a = a_lo0 + (m & 3) * a_stride16;
+          const uint32_t d = (opt & 4) ? tmem + ((m * 3) & 7) * 64 % (512 - N) : tmem;
+          if (opt & 1) tc_fence_after_sync();
+          umma_bf16_ss(d, hi | a, hi | b_lo0, idesc, (opt & 8) ? 0u : 1u);
+#pragma unroll
+          for (int k = 1; k < 4; ++k) umma_bf16_ss(d, hi | (a + k * 2), hi | (b_lo0 + k * 2), idesc, 1u);
+          if (opt & 2) {
+            const bool ok = mbar_test_wait(&bars[m & 3], 1);
+            const uint4 mm = lds_u4(&msgs[m & 3]);
+            acc += mm.x + (ok ? 1 : 0);
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) umma_bf16_ss(d, hi | (a + 64 + k * 2), hi | (b_lo0 + 512 + k * 2), idesc, 1u);
+          umma_commit(&bars[m & 3]);
+        }
+        umma_commit(&bar);
+        if (acc == 0xdeadbeef) out[200] = acc;
+      }
     } else {  // the conv issuer's structure: per 12 MMAs a warp-wide barrier probe + message read + three elect sections
       t0 = clock64();
       uint32_t acc = 0;
@@ -86,9 +130,9 @@ int main() {
   cudaMalloc(&out, 256 * 8);
   cudaFuncSetAttribute(k_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
   const int rounds = 2000;
-  for (int mode : {0, 1, 2, 3})
+  for (int mode : {100, 101, 102, 103, 104, 106, 120})
   for (int grid : {148}) {
-    for (int N : {64, 128, 192}) {
+    for (int N : {64, 128}) {  // (N = 128 at rotating offsets 0,128,256,384)
       k_probe<<<grid, 128, 98 * 1024 + 1024>>>(N, rounds - rounds % 3, 1152, out, mode);
       cudaError_t e = cudaDeviceSynchronize();
       if (e != cudaSuccess) { printf("error %s\n", cudaGetErrorString(e)); return 1; }
@@ -96,6 +140,7 @@ int main() {
       cudaMemcpy(h, out, grid * 8, cudaMemcpyDeviceToHost);
       double s = 0;
       for (int i = 0; i < grid; ++i) s += h[i];
+      if (mode == 4 && N == 64) printf("mode 4 = same D, accumulate; 8 = rotating D, accumulate; 12 = same D, first MMA of 12 overwrites; 16 = rotating D + overwrite\n");
       printf("mode %d grid %3d  N=%3d  clk per MMA = %.1f  (pipe floor %d)\n", mode, grid, N, s / grid / ((rounds - rounds % 3) * 4.0), 128 * N / 256);
     }
   }

@@ -150,12 +150,15 @@ static_assert(kSmemBytes <= 232448, "shared memory budget (227 KB)");
 
 // Producer -> MMA issuer messages (Control::msg[stage]).  The producer does all the bookkeeping
 // (which accumulators a box feeds, whether they are fresh, when a tile is complete); the issuing warp
-// only interprets: x = flags, y = TMEM column of the first accumulator, z / w = (offset of the plane's
-// first weight tile, distance between its kh rows) >> 4.
+// only interprets: x = flags, y = TMEM address of the first accumulator, z / w = (offset of the plane's
+// first weight tile, distance between its kh rows) >> 4.  Everything that can be decided ahead of time is decided by
+// the producer (it has slack; the issuing thread's instructions between two MMAs are on the critical path).
 constexpr uint32_t kMsgNkdMask = 3;      // bits 0-1: depth taps fused along N (0: control message, no A box)
 constexpr uint32_t kMsgNewPass = 4;      // first box of a weight pass: release the previous slot, wait for the next
 constexpr uint32_t kMsgFreshShift = 4;   // bits 4-6: tap j starts its accumulator (accumulate = 0 on the first k-step)
 constexpr uint32_t kMsgEnd = 0x80;       // no more work
+constexpr uint32_t kMsgSplit = 1u << 24;       // the taps of this box are in different states (some fresh, some not): rare
+constexpr uint32_t kMsgAccumulate = 1u << 25;  // no tap is fresh: the first MMA accumulates
 constexpr uint32_t kMsgCommitShift = 8;  // bits 8-15: TMEM slots that are complete after this message
 constexpr uint32_t kMsgWaitShift = 16;   // bits 16-23: TMEM slots the epilogue must have drained before the MMAs
 // experiment switches of the kDebug instantiation (tools/prof_conv.py): what the kernel costs WITHOUT ...
@@ -427,8 +430,10 @@ __global__ void __launch_bounds__(kThreads, 1)
               const uint32_t range = ((1u << pi.nkd) - 1u) << pi.dmin;
               const uint32_t fresh = (range & ~started) >> pi.dmin;  // bit j: tap j starts its accumulator
               const uint32_t slot_lo = slot0 + __popc(touched & ((1u << pi.dmin) - 1u));
+              const uint32_t full = (1u << pi.nkd) - 1u;
               const uint32_t flags = (uint32_t)pi.nkd | new_pass | (fresh << kMsgFreshShift) |
-                                     ((fresh << slot_lo) << kMsgWaitShift);
+                                     ((fresh << slot_lo) << kMsgWaitShift) | (fresh == 0 ? kMsgAccumulate : 0u) |
+                                     ((fresh != 0 && fresh != full) ? kMsgSplit : 0u);
               const uint32_t sa = a_it % kNA;
               VN_TIMED(pw_a, mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1));
               if (kDebug) {
@@ -439,7 +444,7 @@ __global__ void __launch_bounds__(kThreads, 1)
                 }
               }
               if (elect_one()) {
-                ctl->msg[sa] = make_uint4(flags, slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
+                ctl->msg[sa] = make_uint4(flags, tmem_base + slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
                 if (kDebug && (dbg & kDbgNoALoad)) {
                   mbar_arrive(&ctl->full_a[sa]);
                 } else {
@@ -506,24 +511,39 @@ __global__ void __launch_bounds__(kThreads, 1)
       const uint32_t b_lo0 = ((smem_u32(smem_b) >> 4) & 0x3FFFu) | (1u << 16);
       uint32_t b_lo_pass = b_lo0;
       const bool no_mma = kDebug && (P.debug & kDbgNoMma);
+      // decoded message: everything the MMAs of a box need, computed as soon as the message has been read
+      struct Dec {
+        uint32_t f, d_tmem, a_lo, bz, bw, idesc, nkd;
+      };
+      auto decode = [&](const uint4& m, uint32_t it) {
+        Dec d;
+        d.f = m.x;
+        d.nkd = m.x & kMsgNkdMask;
+        d.d_tmem = m.y;
+        d.a_lo = a_lo0 + (it % kNA) * (kABytes >> 4);
+        d.bz = m.z;
+        d.bw = m.w;
+        d.idesc = umma_idesc_bf16(128, 64) + ((d.nkd - 1u) << 20);  // N = 64 * nkd
+        return d;
+      };
       VN_TIMED(mw_a, mbar_wait(&ctl->full_a[0], 0));
-      uint4 msg = lds_u4(&ctl->msg[0]);
+      Dec cur = decode(lds_u4(&ctl->msg[0]), 0);
       for (;;) {
         const uint32_t sa = a_it % kNA;
         const bool tr = kDebug && P.trace != nullptr && blockIdx.x == 0 && (int)a_it < P.trace_n;
         if (tr) P.trace[(size_t)a_it * 4 + 1] = (unsigned long long)clock64();
-        const uint32_t f = msg.x;
-        if (f & kMsgNewPass) {
-          // the previous pass is fully issued: its weights may be overwritten once it completes
-          if (b_it != 0) umma_commit(&ctl->empty_b[(b_it - 1) % kNB]);
-          VN_TIMED(mw_b, mbar_wait(&ctl->full_b[b_it % kNB], (b_it / kNB) & 1));
-          b_lo_pass = b_lo0 + (b_it % kNB) * (kBSlotBytes >> 4);
-          ++b_it;
-        }
-        const uint32_t wait_mask = (f >> kMsgWaitShift) & 0xffu;
-        if (wait_mask) {  // accumulators started by this box must have been drained by the epilogue
+        const uint32_t f = cur.f;
+        if (f & (kMsgNewPass | (0xffu << kMsgWaitShift))) {  // (rare) things that may block in front of the MMAs
+          if (f & kMsgNewPass) {
+            // the previous pass is fully issued: its weights may be overwritten once it completes
+            if (b_it != 0) umma_commit(&ctl->empty_b[(b_it - 1) % kNB]);
+            VN_TIMED(mw_b, mbar_wait(&ctl->full_b[b_it % kNB], (b_it / kNB) & 1));
+            b_lo_pass = b_lo0 + (b_it % kNB) * (kBSlotBytes >> 4);
+            ++b_it;
+          }
+          const uint32_t wait_mask = (f >> kMsgWaitShift) & 0xffu;
           uint32_t wm = wait_mask;
-          while (wm) {
+          while (wm) {  // accumulators started by this box must have been drained by the epilogue
             const uint32_t s = __ffs(wm) - 1;
             wm &= wm - 1;
             VN_TIMED(mw_acc, mbar_wait(&ctl->acc_empty[s], ((acc_phase >> s) & 1) ^ 1));
@@ -531,36 +551,33 @@ __global__ void __launch_bounds__(kThreads, 1)
           acc_phase ^= wait_mask;
         }
         tc_fence_after_sync();
-        const uint32_t nkd = f & kMsgNkdMask;
         const uint32_t sn = (a_it + 1) % kNA, pn = ((a_it + 1) / kNA) & 1;
         bool have_next = false;
-        uint4 nxt = make_uint4(0u, 0u, 0u, 0u);
-        if (nkd != 0) {
-          const uint32_t d_tmem = tmem_base + msg.y;
-          const uint32_t a_lo = a_lo0 + sa * (kABytes >> 4);
-          const uint32_t b_lo = b_lo_pass + msg.z;
-          const uint32_t idesc = umma_idesc_bf16(128, 64) + ((nkd - 1u) << 20);  // N = 64 * nkd
-          const uint32_t fresh = (f >> kMsgFreshShift) & 7u;
-          const bool split = fresh != 0 && fresh != (1u << nkd) - 1u;  // rare: neighbours in different states
+        Dec nxt = cur;
+        if (cur.nkd != 0) {
+          const uint32_t d_tmem = cur.d_tmem, a_lo = cur.a_lo, idesc = cur.idesc;
+          const uint32_t b_lo = b_lo_pass + cur.bz;
           if (!no_mma) {  // kh = 0
-            if (split) {  // first k-step per accumulator (N = 64): accumulate only where a partial sum exists
-              for (uint32_t j = 0; j < nkd; ++j)
+            if (f & kMsgSplit) {  // first k-step per accumulator (N = 64): accumulate only where a partial sum exists
+              const uint32_t fresh = (f >> kMsgFreshShift) & 7u;
+              for (uint32_t j = 0; j < cur.nkd; ++j)
                 umma_bf16_ss(d_tmem + j * 64, desc_from_lo(a_lo), desc_from_lo(b_lo + j * (kBTapBytes >> 4)),
                              umma_idesc_bf16(128, 64), ((fresh >> j) & 1) ^ 1);
             } else {
-              umma_bf16_ss(d_tmem, desc_from_lo(a_lo), desc_from_lo(b_lo), idesc, fresh ? 0u : 1u);
+              umma_bf16_ss(d_tmem, desc_from_lo(a_lo), desc_from_lo(b_lo), idesc, (f & kMsgAccumulate) ? 1u : 0u);
             }
 #pragma unroll
             for (int k = 1; k < 4; ++k) umma_bf16_ss(d_tmem, desc_from_lo(a_lo + k * 2), desc_from_lo(b_lo + k * 2), idesc, 1u);
           }
           // in the shadow of those MMAs: is the next message there already?  (normally yes: the producer runs ahead)
+          // Read and decode it now, so that after this box's last MMA only the uniform-register moves are left.
           have_next = mbar_test_wait(&ctl->full_a[sn], pn);
-          if (have_next) nxt = lds_u4(&ctl->msg[sn]);
+          if (have_next) nxt = decode(lds_u4(&ctl->msg[sn]), a_it + 1);
           if (!no_mma) {  // kh = 1, 2
 #pragma unroll
             for (int kh = 1; kh < 3; ++kh) {
               const uint32_t a = a_lo + kh * ((kTileW * 128) >> 4);
-              const uint32_t bq = b_lo + kh * msg.w;
+              const uint32_t bq = b_lo + kh * cur.bw;
 #pragma unroll
               for (int k = 0; k < 4; ++k) umma_bf16_ss(d_tmem, desc_from_lo(a + k * 2), desc_from_lo(bq + k * 2), idesc, 1u);
             }
@@ -580,9 +597,9 @@ __global__ void __launch_bounds__(kThreads, 1)
         if (f & kMsgEnd) break;
         if (!have_next) {
           VN_TIMED(mw_a, mbar_wait(&ctl->full_a[sn], pn));
-          nxt = lds_u4(&ctl->msg[sn]);
+          nxt = decode(lds_u4(&ctl->msg[sn]), a_it);
         }
-        msg = nxt;
+        cur = nxt;
       }
       if (kDebug && P.prof != nullptr) {
         unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
