@@ -60,7 +60,7 @@ def test_bad_arguments_are_rejected_without_a_gpu():
     assert rc == -1 and b"multiple of 8" in lib.vn_last_error()
     assert lib.vn_conv3d_bn_relu_fwd(p16, 1, 10, 16, 16, 128, 2, 1, p16, p16, p16, 0, None, 0, p16, None, 0, None, p16, 8, None) == -2
     assert lib.vn_conv3d_out_state_bytes(16, 400, 352) == 16 * 25 * 44
-    assert lib.vn_conv3d_workspace_bytes(16, 400, 352) == 16 + 16 * 25 * 44 * 16
+    assert lib.vn_conv3d_workspace_bytes(16, 400, 352) == 16 + 16 * 25 * 44 * (16 + 8 + 8 * 8)
     assert lib.vn_conv3d_box_flags_bytes(16, 10, 400, 352) == 16 * 10 * 25 * 44 * 3
     assert lib.vn_conv3d_mark_boxes(None, 5, None, 1, 10, 16, 16, 4, None, None, None, None) == -1
     assert lib.vn_conv3d_packed_weight_bytes(128) == 27 * 128 * 64 * 2 and lib.vn_conv3d_packed_weight_bytes(32) == 0
