@@ -702,7 +702,9 @@ def main():
             "config": {"workload": desc, "name": args.config, "batch_per_gpu": batch, "points_per_batch": N_total,
                        "voxels_per_batch": K_total,
                        "inputs": "two different batches alternate step by step (resident outputs are restored where the previous batch reached)",
-                       "l2_policy": "working set (%.1f GB dense grid + activations) exceeds L2" % (fe.dense.numel() * 2 / 1e9),
+                       "l2_policy": "working set (%.2f GB of activations, outputs and row tables per front end) exceeds L2" % (fe.device_bytes()["total"] / 1e9),
+                       "device_bytes_per_front_end": fe.device_bytes(),
+                       "grid": "never materialised: (K,128) bf16 rows + the voxelizer's occupancy index feed conv-1 (vn_conv3d_bn_relu_fwd_rows)" if fe.dense is None else "resident bf16 grid",
                        "vfe": "fp32", "conv": "bf16 operands, fp32 accumulate (tcgen05)",
                        "launch": launch_mode,
                        "in_flight": "%d step(s) in flight per GPU (%s); ms_per_step = timed region / steps" % (

@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 12
+#define VN_ABI_VERSION 13
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -159,6 +159,19 @@ int vn_voxelize_svfe_bucketed(const vn_grid_t* grid, const float* points, const 
                            int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace,
                            size_t workspace_bytes, vn_stream_t stream);
 
+/* The never-materialised form of the sparse -> dense step (voxelnet/model.py:102-106, consumer :207): the 128 voxel-wise
+ * maxima of voxel row r go to rows_bf16[r][0..127] (bf16, RNE) - a compact (max_voxels,128) table in np.unique row
+ * order - and NO (B,D,H,W,128) tensor is written.  The cell -> row map is the voxelizer's own occupancy index inside
+ * `workspace` (bitmap + popcount prefix, see vn_conv3d_bn_relu_fwd_rows), so nothing else is stored.  bucketed != 0: the
+ * call follows vn_voxelize_bucket_coords on the same workspace (coordinate_buffer is then not written again); 0: it
+ * does the bucketing itself and writes coordinate_buffer. */
+int vn_voxelize_svfe_rows(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets,
+                          int32_t n_frames, int64_t n_points_total, const int32_t* voxel_offsets,
+                          int64_t max_voxels, const float* w1, const float* b1, const float* s1,
+                          const float* t1, const float* w2, const float* b2, const float* s2,
+                          const float* t2, void* rows_bf16, int64_t* coordinate_buffer, int32_t bucketed,
+                          void* workspace, size_t workspace_bytes, vn_stream_t stream);
+
 /* ------------------------------------------------------------------------------------------
  * Sparse -> dense - replaces torch.sparse.FloatTensor(coords.t(), voxelwise, [B,D,H,W,128])
  * .to_dense() (voxelnet/model.py:102-106).  Layout of `dense`: [B, D, H, W, C] contiguous.
@@ -234,6 +247,24 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
                           const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
                           int32_t flag_opts, uint8_t* out_state, void* workspace,
                           size_t workspace_bytes, vn_stream_t stream);
+
+/* vn_conv3d_bn_relu_fwd for the FIRST middle layer (voxelnet/model.py:207) reading the voxel-wise rows directly:
+ * x is never a tensor.  Input cell (b, z, y, x) is rows_bf16[r] if bit (z*H + y)*W + x of frame b's occupancy bitmap is
+ * set, r = voxel_offsets[b] + (set bits before it in the frame) < min(voxel_offsets[n_frames], max_voxels), else zero.
+ * The bitmap and its per-word popcount prefix are the ones vn_voxelize_index left in vox_workspace for
+ * (grid, n_frames, n_points_total) - pass the same three values; rows_bf16 comes from vn_voxelize_svfe_rows.  The
+ * kernel's box-filling warps build each 18 x 8 x 64-channel operand box in shared memory from the few occupied rows
+ * (everything else stays zero), so neither the 360 MB/frame grid nor its scatter / re-zero passes exist.  B = n_frames,
+ * Din = grid->D, cin = 128; every other argument as in vn_conv3d_bn_relu_fwd.  Results are bit-identical to running
+ * vn_conv3d_bn_relu_fwd on the scattered grid. */
+int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int64_t max_voxels,
+                               const int32_t* voxel_offsets, int32_t n_frames, int64_t n_points_total,
+                               const void* vox_workspace, size_t vox_workspace_bytes, int32_t stride_d,
+                               int32_t pad_d, const void* packed_weight, const float* scale,
+                               const float* shift_table, int32_t n_variants, const float* sub,
+                               int32_t out_mode, void* y, uint8_t* box_flags, int32_t flag_opts,
+                               uint8_t* out_state, void* workspace, size_t workspace_bytes,
+                               vn_stream_t stream);
 
 /* Background folding for a layer whose INPUT is stored as a deviation from a per-(plane, channel)
  * background bg_in [Din][cin] f32 (the previous layer's `sub`; NULL = zero background).  The

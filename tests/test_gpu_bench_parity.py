@@ -176,3 +176,33 @@ def test_real_kitti_frame_whole_chain_against_reference_golden(cuda_device):
         bias = (out[b].double().sum(dim=(1, 2)) - sums).abs() / (out.shape[2] * out.shape[3] * float(g["out_max_abs"]))
         assert float(bias.max()) < 1e-3, (b, float(bias.max()))
     assert torch.equal(out[0], out[3])
+
+
+def test_never_materialised_grid_is_bit_identical_to_the_resident_grid(cuda_device, car_case):
+    """the default front end keeps (K,128) bf16 rows + the voxelizer's occupancy index and the first
+    conv layer fills its operand boxes from them (vn_voxelize_svfe_rows / vn_conv3d_bn_relu_fwd_rows); no (B,10,400,352,128)
+    tensor exists.  Same bits as the round-1 form that scatters into a resident grid, over the sequence A, B, A, with
+    live-box skipping on and off, and when the voxel capacity clamps the batch."""
+    import voxelnet_pytorch_b200 as vn
+
+    sd, sets, want, _ = car_case
+    fnet, mnet = _nets(cuda_device, sd)
+    fe_rows = vn.VoxelNetFrontEnd(fnet, mnet, "Car")
+    fe_grid = vn.VoxelNetFrontEnd(fnet, mnet, "Car", materialise_grid=True)
+    for step, b in enumerate((0, 1, 0)):
+        a = fe_rows.forward_frames(sets[b])
+        assert torch.equal(a, fe_grid.forward_frames(sets[b])), "step %d" % step
+        _check(a, want[b], "row-table path step %d" % step)
+    assert fe_rows.dense is None and fe_rows.rows is not None and fe_grid.dense is not None
+    mem_rows, mem_grid = fe_rows.device_bytes(), fe_grid.device_bytes()
+    assert mem_rows["dense"] == 0 and mem_grid["dense"] == 4 * 10 * 400 * 352 * 128 * 2
+    assert mem_rows["total"] < mem_grid["total"] - 1_000_000_000
+    del fe_grid
+    # every box live (no flag table): the filling warps see mostly empty boxes
+    a = vn.VoxelNetFrontEnd(fnet, mnet, "Car", skip_empty_boxes=False).forward_frames(sets[0][:2]).clone()
+    b = vn.VoxelNetFrontEnd(fnet, mnet, "Car", skip_empty_boxes=False, materialise_grid=True).forward_frames(sets[0][:2])
+    assert torch.equal(a, b)
+    # capacity clamp: voxel rows beyond the capacity do not exist in either form
+    a = vn.VoxelNetFrontEnd(fnet, mnet, "Car", voxels_per_frame_capacity=3000).forward_frames(sets[1]).clone()
+    b = vn.VoxelNetFrontEnd(fnet, mnet, "Car", voxels_per_frame_capacity=3000, materialise_grid=True).forward_frames(sets[1])
+    assert torch.equal(a, b) and not torch.equal(a, want[1])

@@ -14,7 +14,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 12
+VN_ABI_VERSION = 13
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 VN_CONV_FLAGS_PLANNED = 4
@@ -49,6 +49,9 @@ PROTOTYPES = {
     "vn_svfe_fused_fwd": (C.c_int, [_p, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "vn_voxelize_svfe_fused": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "vn_voxelize_svfe_bucketed": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
+    "vn_voxelize_svfe_rows": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _sz, _p]),
+    "vn_conv3d_bn_relu_fwd_rows": (C.c_int, [_G, _p, _i64, _p, _i32, _i64, _p, _sz, _i32, _i32, _p, _p, _p, _i32, _p, _i32, _p, _p, _i32, _p, _p,
+                                             _sz, _p]),
     "vn_voxelize_bucket_coords": (C.c_int, [_G, _p, _p, _i32, _i64, _p, _i64, _p, _p, _sz, _p]),
     "vn_fill_zero": (C.c_int, [_p, _sz, _p]),
     "vn_scatter_dense_f32": (C.c_int, [_p, _p, _i64, _p, _i32, _i32, _i32, _i32, _i32, _p, _p]),

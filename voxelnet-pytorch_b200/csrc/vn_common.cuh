@@ -50,6 +50,12 @@ inline int sm_count() {
   return n;
 }
 
+// Views into a voxelizer workspace laid out by vn_voxelize_index for (grid, n_frames, n_points_total): the per-frame
+// occupancy bitmap (cell = (z*H + y)*W + x) and its exclusive popcount prefix per 32-bit word; `words` per frame.
+// Returns non-zero if the workspace is smaller than that layout.  (vn_voxelize.cu)
+int occupancy_views(const vn_grid_t& grid, int n_frames, int64_t n_points_total, const void* workspace, size_t workspace_bytes,
+                    const uint32_t** bitmap, const uint32_t** wordprefix, size_t* words);
+
 __host__ __device__ constexpr size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // ---- device side ------------------------------------------------------------------------------

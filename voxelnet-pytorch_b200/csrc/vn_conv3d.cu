@@ -35,6 +35,7 @@
 //              warps 2..5 = epilogue (TMEM -> registers -> scale/shift/ReLU -> global).
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <string.h>
 
 #include "vn_common.cuh"
 
@@ -53,6 +54,7 @@ constexpr int kMaxGroupTiles = 8;
 constexpr int kMaxTilesW = 128;
 constexpr int kMaxTableRows = 27;                    // shift-table rows (variants x Dout) kept in smem
 constexpr int kThreads = 10 * 32;            // producer, MMA issuer, 8 epilogue warps
+constexpr int kThreadsGather = kThreads + kNA * 32;  // + one box-filling warp per A stage (k_conv3d_bn_relu<.., kGather>)
 constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBSlotBytes;  // 221184
 
 // What one input plane contributes (host-computed; see plan_planes()).
@@ -109,6 +111,15 @@ struct ConvParams {
   unsigned long long* trace; // kDebug: [trace_n][4] per message of CTA 0: producer acquire / issuer saw / issued / flags
   int trace_n;
   double* stats;             // training kernel: [2][64] per-channel sum / sum of squares of the raw output
+  // kGather instantiation: the input is never a dense tensor.  Cell (b, p, h, w) holds row
+  //   voxel_offsets[b] + prefix[b][word] + popc(bits below) of `rows` if its bit is set in the voxelizer's occupancy bitmap
+  // (cell index (p*H + h)*W + w inside the frame; rows at or beyond min(voxel_offsets[B], max_voxels) do not exist), else zero.
+  const uint32_t* g_bitmap;     // [B][g_words]
+  const uint32_t* g_prefix;     // [B][g_words] exclusive popcount prefix inside the frame
+  const int32_t* g_voxoff;      // [B+1]
+  const __nv_bfloat16* g_rows;  // [max_voxels][128]
+  long long g_max_voxels;
+  uint32_t g_words;
 };
 
 struct PlanParams {
@@ -140,6 +151,8 @@ struct Control {
   uint32_t pad[1];
   uint32_t row_zero[kSlots];  // [dout]: relu(interior shift row) - sub == 0 for all channels
   uint4 msg[kNA];  // one message per A stage, written by the producer before it arms full_a (see kMsg*)
+  uint64_t req_full[kNA];  // kGather: the producer asks the stage's filling warp for a box ...
+  int4 req[kNA];           // ... {first column, first row, plane | chunk << 8, frame (-1: stop)}
   float scale[64];
   float sub[kSlots * 64];
   alignas(16) float table[kMaxTableRows * 64];  // training kernel: rows 16..19 hold the CTA-level partial sums
@@ -295,8 +308,13 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
     }                                          \
   } while (0)
 
-template <bool kTrain, bool kDebug>
-__global__ void __launch_bounds__(kThreads, 1)
+// kGather = true (the first layer of the eval fast path): there is no dense input tensor and no TMA box.  Warp 0 sends
+//                 every box as a request to the filling warp of its A stage (warps 10..13), which re-zeroes what it
+//                 wrote into the stage the last time, looks the 18 x 8 cells up in the voxelizer's occupancy bitmap,
+//                 copies the few occupied rows (64 channels = 128 B each) from the compact (K,128) row table into the
+//                 SWIZZLE_128B image the MMA expects, and arms the stage's full barrier.  tmap_x is unused.
+template <bool kTrain, bool kDebug, bool kGather>
+__global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ ConvParams P) {
   extern __shared__ uint8_t smem_raw[];
   // SWIZZLE_128B operands need 1024-byte aligned tiles
@@ -312,9 +330,15 @@ __global__ void __launch_bounds__(kThreads, 1)
     for (int i = 0; i < kNB; ++i) { mbar_init(&ctl->full_b[i], 1); mbar_init(&ctl->empty_b[i], 1); }
     for (int i = 0; i < kSlots; ++i) { mbar_init(&ctl->acc_full[i], 1); mbar_init(&ctl->acc_empty[i], 8); }
     for (int i = 0; i < kSched; ++i) { mbar_init(&ctl->sched_full[i], 1); mbar_init(&ctl->sched_empty[i], 8); }
+    if (kGather)
+      for (int i = 0; i < kNA; ++i) mbar_init(&ctl->req_full[i], 1);
     mbar_fence_init();
     fence_proxy_async_smem();
-    tma_prefetch_desc(&tmap_x);
+    if (!kGather) tma_prefetch_desc(&tmap_x);
+  }
+  if (kGather) {  // the A stages start all-zero and every filling warp restores that after each box
+    for (uint32_t i = threadIdx.x; i < kNA * kABytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem_a)[i] = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async_smem();
   }
   if (threadIdx.x >= 64) {
     const int t = threadIdx.x - 64;  // 0..255
@@ -445,7 +469,10 @@ __global__ void __launch_bounds__(kThreads, 1)
               }
               if (elect_one()) {
                 ctl->msg[sa] = make_uint4(flags, tmem_base + slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
-                if (kDebug && (dbg & kDbgNoALoad)) {
+                if (kGather) {
+                  ctl->req[sa] = make_int4(w0 + kw - 1, h0 - 1, p | (c << 8), b);
+                  mbar_arrive(&ctl->req_full[sa]);
+                } else if (kDebug && (dbg & kDbgNoALoad)) {
                   mbar_arrive(&ctl->full_a[sa]);
                 } else {
                   mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
@@ -486,6 +513,18 @@ __global__ void __launch_bounds__(kThreads, 1)
       if (elect_one()) {
         ctl->msg[sa] = make_uint4(kMsgEnd, 0u, 0u, 0u);
         mbar_arrive(&ctl->full_a[sa]);
+      }
+      __syncwarp();
+      ++a_it;
+    }
+    if (kGather) {
+      // every other stage's last use has been released (so its filling warp is idle): tell the filling warps to stop
+      for (int i = 0; i < kNA - 1; ++i, ++a_it) mbar_wait(&ctl->empty_a[a_it % kNA], ((a_it / kNA) & 1) ^ 1);
+      if (elect_one()) {
+        for (int i = 0; i < kNA; ++i) {
+          ctl->req[i] = make_int4(0, 0, 0, -1);
+          mbar_arrive(&ctl->req_full[i]);
+        }
       }
       __syncwarp();
     }
@@ -607,6 +646,70 @@ __global__ void __launch_bounds__(kThreads, 1)
       }
     }
     __syncwarp();
+  } else if (kGather && warp >= 10) {
+    // ===================== box filling (warps 10..13, one per A stage) =====================
+    const int j = (int)warp - 10;
+    uint8_t* stage = smem_a + j * kABytes;
+    long long total = P.g_voxoff[P.B];
+    if (total > P.g_max_voxels) total = P.g_max_voxels;
+    uint32_t n_req = 0, filled = 0;  // filled bit k: this lane wrote box row lane + 32 k the last time
+    for (;;) {
+      mbar_wait(&ctl->req_full[j], n_req & 1);
+      ++n_req;
+      const uint4 rq_u = lds_u4(&ctl->req[j]);
+      const int4 rq = make_int4((int)rq_u.x, (int)rq_u.y, (int)rq_u.z, (int)rq_u.w);
+      if (rq.w < 0) break;
+#pragma unroll
+      for (int k = 0; k < 5; ++k)
+        if ((filled >> k) & 1) {
+          uint4* dst = reinterpret_cast<uint4*>(stage + (lane + 32 * k) * 128);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) dst[q] = make_uint4(0u, 0u, 0u, 0u);
+        }
+      filled = 0;
+      // lanes 0..17: occupancy bits of image row rq.y + lane, columns rq.x .. rq.x + 7, and the row-table index of the first
+      uint32_t mask = 0, first = 0;
+      const int h = rq.y + (int)lane;
+      if (lane < (uint32_t)kHaloH && h >= 0 && h < P.H) {
+        const int lo_w = rq.x < 0 ? 0 : rq.x;
+        const int hi_w = rq.x + kTileW > P.W ? P.W : rq.x + kTileW;
+        const int nb = hi_w - lo_w;
+        const uint32_t cell = (uint32_t)(((rq.z & 0xff) * P.H + h) * P.W + lo_w);
+        const uint32_t word = cell >> 5, sh = cell & 31u;
+        const uint32_t* bm = P.g_bitmap + (size_t)rq.w * P.g_words;
+        const uint32_t w_lo = __ldg(bm + word);
+        const uint32_t w_hi = sh + (uint32_t)nb > 32u ? __ldg(bm + word + 1) : 0u;
+        const uint32_t win = __funnelshift_r(w_lo, w_hi, sh) & ((1u << nb) - 1u);
+        if (win != 0) {
+          mask = win << (lo_w - rq.x);
+          first = (uint32_t)P.g_voxoff[rq.w] + __ldg(P.g_prefix + (size_t)rq.w * P.g_words + word) + __popc(w_lo & ((1u << sh) - 1u));
+        }
+      }
+      const __nv_bfloat16* src0 = P.g_rows + (rq.z >> 8) * 64;
+#pragma unroll
+      for (int k = 0; k < 5; ++k) {
+        const uint32_t c = lane + 32 * k;           // box row = (image row, column) = (c / 8, c % 8)
+        const uint32_t r = c < 144u ? c >> 3 : 17u, i = c & 7u;
+        const uint32_t m_r = __shfl_sync(0xffffffffu, mask, r);
+        const uint32_t f_r = __shfl_sync(0xffffffffu, first, r);
+        if (c < 144u && ((m_r >> i) & 1u)) {
+          const long long row = (long long)f_r + __popc(m_r & ((1u << i) - 1u));
+          if (row < total) {
+            const uint4* src = reinterpret_cast<const uint4*>(src0 + row * 128);
+            uint4 v[8];
+#pragma unroll
+            for (int q = 0; q < 8; ++q) v[q] = __ldg(src + q);
+            uint8_t* dst = stage + c * 128;
+#pragma unroll
+            for (int q = 0; q < 8; ++q) *reinterpret_cast<uint4*>(dst + ((q ^ (c & 7u)) << 4)) = v[q];
+            filled |= 1u << k;
+          }
+        }
+      }
+      fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's reads
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&ctl->full_a[j]);
+    }
   } else {
     // ===================== epilogue (warps 2..9) =====================
     // Two warps per TMEM lane quadrant (a warp may only read lanes 32*(warp%4)..+31): warps 2..5 take
@@ -1090,12 +1193,22 @@ int vn_conv3d_mark_boxes(const int64_t* coords, int64_t K, const int32_t* n_voxe
   return VN_OK;
 }
 
+// Input of the gather instantiation (vn_conv3d_bn_relu_fwd_rows): occupancy index + compact row table instead of x.
+struct GatherSrc {
+  const uint32_t* bitmap;
+  const uint32_t* prefix;
+  size_t words;
+  const int32_t* voxel_offsets;
+  const void* rows;
+  int64_t max_voxels;
+};
+
 static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t W, int32_t cin, int32_t stride_d,
                        int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
                        int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
                        int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
-                       vn_stream_t stream, double* stats, int32_t transposed_dout = 0) {
-  VN_REQUIRE(x && packed_weight && scale && shift_table && y, "conv3d: null pointer");
+                       vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr) {
+  VN_REQUIRE((x || gather) && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
   VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d: stride_d=%d pad_d=%d unsupported",
@@ -1112,7 +1225,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   const int nvar = n_variants == 9 ? 9 : 1;
   VN_REQUIRE(nvar * Dout <= kMaxTableRows, "conv3d: shift table of %d x %d rows exceeds %d", nvar, Dout, kMaxTableRows);
   VN_REQUIRE(nvar == 1 || H >= 2, "conv3d: border variants need H >= 2");
-  VN_REQUIRE((reinterpret_cast<uintptr_t>(x) & 15) == 0 && (reinterpret_cast<uintptr_t>(packed_weight) & 15) == 0 &&
+  VN_REQUIRE((reinterpret_cast<uintptr_t>(gather ? gather->rows : x) & 15) == 0 && (reinterpret_cast<uintptr_t>(packed_weight) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(y) & 15) == 0,
              "conv3d: buffers must be 16-byte aligned");
   VN_REQUIRE(workspace != nullptr && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "conv3d: workspace missing or misaligned");
@@ -1131,12 +1244,14 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   TilePlan* tiles = reinterpret_cast<TilePlan*>(ws + L.tiles_off);
   TilePlan* gtiles = reinterpret_cast<TilePlan*>(ws + L.gtiles_off);
 
+  CUtensorMap tmap;
+  memset(&tmap, 0, sizeof(tmap));
+  if (gather == nullptr) {
   EncodeTiledFn encode = encode_tiled_fn();
   if (encode == nullptr) {
     set_error("conv3d: cuTensorMapEncodeTiled not available from the driver");
     return VN_ERR_DRIVER;
   }
-  CUtensorMap tmap;
   const cuuint64_t gdim[5] = {(cuuint64_t)cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Din, (cuuint64_t)B};
   const cuuint64_t gstr[4] = {(cuuint64_t)cin * 2, (cuuint64_t)W * cin * 2, (cuuint64_t)H * W * cin * 2,
                               (cuuint64_t)Din * H * W * cin * 2};
@@ -1148,6 +1263,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   if (cr != CUDA_SUCCESS) {
     set_error("conv3d: cuTensorMapEncodeTiled failed with CUresult %d", (int)cr);
     return VN_ERR_DRIVER;
+  }
   }
 
   cudaStream_t st = as_stream(stream);
@@ -1189,15 +1305,28 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
 
   const int grid = n_tiles < sm_count() ? (int)n_tiles : sm_count();
   P.stats = stats;
-  if (stats != nullptr) {
-    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    k_conv3d_bn_relu<true, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+  if (gather != nullptr) {
+    VN_REQUIRE(stats == nullptr && cin == 128, "conv3d: the row-table input serves the first inference layer only");
+    P.g_bitmap = gather->bitmap; P.g_prefix = gather->prefix; P.g_words = (uint32_t)gather->words;
+    P.g_voxoff = gather->voxel_offsets;
+    P.g_rows = reinterpret_cast<const __nv_bfloat16*>(gather->rows);
+    P.g_max_voxels = gather->max_voxels;
+    if (P.prof != nullptr || P.debug != 0) {
+      VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+      k_conv3d_bn_relu<false, true, true><<<grid, kThreadsGather, kSmemBytes, st>>>(tmap, P);
+    } else {
+      VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+      k_conv3d_bn_relu<false, false, true><<<grid, kThreadsGather, kSmemBytes, st>>>(tmap, P);
+    }
+  } else if (stats != nullptr) {
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<true, false, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   } else if (P.prof != nullptr || P.debug != 0) {
-    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    k_conv3d_bn_relu<false, true><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<false, true, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   } else {
-    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    k_conv3d_bn_relu<false, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<false, false, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   }
   VN_LAUNCH_CHECK("k_conv3d_bn_relu");
   return VN_OK;
@@ -1210,6 +1339,30 @@ int vn_conv3d_bn_relu_fwd(const void* x, int32_t B, int32_t Din, int32_t H, int3
                           vn_stream_t stream) {
   return conv_launch(x, B, Din, H, W, cin, stride_d, pad_d, packed_weight, scale, shift_table, n_variants, sub, out_mode, y,
                      box_flags, flag_opts, out_state, workspace, workspace_bytes, stream, nullptr);
+}
+
+int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int64_t max_voxels, const int32_t* voxel_offsets,
+                               int32_t n_frames, int64_t n_points_total, const void* vox_workspace,
+                               size_t vox_workspace_bytes, int32_t stride_d, int32_t pad_d, const void* packed_weight,
+                               const float* scale, const float* shift_table, int32_t n_variants, const float* sub,
+                               int32_t out_mode, void* y, uint8_t* box_flags, int32_t flag_opts, uint8_t* out_state,
+                               void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(grid != nullptr && rows_bf16 != nullptr && voxel_offsets != nullptr && vox_workspace != nullptr,
+             "conv3d_rows: null pointer");
+  VN_REQUIRE(max_voxels >= 0 && n_frames >= 1 && n_points_total >= 0, "conv3d_rows: bad sizes");
+  VN_REQUIRE(grid->D >= 1 && grid->D <= kMaxPlanes && (int64_t)grid->D * grid->H * grid->W < ((int64_t)1 << 31),
+             "conv3d_rows: grid depth %d outside [1,%d] or too many cells", grid->D, kMaxPlanes);
+  GatherSrc g{};
+  if (occupancy_views(*grid, n_frames, n_points_total, vox_workspace, vox_workspace_bytes, &g.bitmap, &g.prefix, &g.words) != 0) {
+    set_error("conv3d_rows: voxelizer workspace of %zu bytes is too small for this batch", vox_workspace_bytes);
+    return VN_ERR_WORKSPACE;
+  }
+  g.voxel_offsets = voxel_offsets;
+  g.rows = rows_bf16;
+  g.max_voxels = max_voxels;
+  return conv_launch(nullptr, n_frames, grid->D, grid->H, grid->W, 128, stride_d, pad_d, packed_weight, scale, shift_table,
+                     n_variants, sub, out_mode, y, box_flags, flag_opts, out_state, workspace, workspace_bytes, stream, nullptr,
+                     0, &g);
 }
 
 int vn_conv3d_plan(int32_t B, int32_t Din, int32_t H, int32_t W, int32_t stride_d, int32_t pad_d, uint8_t* box_flags,

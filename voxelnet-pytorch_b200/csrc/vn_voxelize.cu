@@ -437,7 +437,8 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
     const float* __restrict__ w2, const float* __restrict__ b2, const float* __restrict__ s2,
     const float* __restrict__ t2, float* __restrict__ voxelwise, __nv_bfloat16* __restrict__ dense,
     long long* __restrict__ coords, long long* __restrict__ counts, int32_t* __restrict__ counters,
-    const int32_t* __restrict__ biglist) {
+    const int32_t* __restrict__ biglist, int dense_rows) {
+  // dense_rows != 0: `dense` is the compact (K,128) bf16 row table (row = voxel row) instead of the (B,D,H,W,128) grid
   extern __shared__ __align__(16) uint8_t dyn_smem[];
   __shared__ Vfe1Params p1;   // one-voxel path
   __shared__ Vfe1Packed pk;   // packed path
@@ -498,7 +499,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
       float o[4];
       svfe_eval_voxel(rows, m, Rv, m, x1, p1, q, sh, o, lane);
       store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
-                      dense != nullptr ? dense + cell_v * 128 : nullptr);
+                      dense != nullptr ? dense + (dense_rows ? vrow : cell_v) * 128 : nullptr);
       __syncwarp();
     }
   }
@@ -650,7 +651,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
         vfe2_voxel_max(W.x[f0], W.agg[k], n, (uint64_t)bits, q, sh, lane, o);
         const int64_t vrow = rg * kPackRange + a + k;
         store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
-                        dense != nullptr ? dense + cell_k * 128 : nullptr);
+                        dense != nullptr ? dense + (dense_rows ? vrow : cell_k) * 128 : nullptr);
       }
       __syncwarp();
       base += Rtot;
@@ -711,6 +712,18 @@ int launch_bucket(const VoxWorkspace& w, const int32_t* frame_offsets, int n_fra
 }  // namespace vn
 
 using namespace vn;
+
+namespace vn {
+int occupancy_views(const vn_grid_t& grid, int n_frames, int64_t n_points_total, const void* workspace, size_t workspace_bytes,
+                    const uint32_t** bitmap, const uint32_t** wordprefix, size_t* words) {
+  const VoxWorkspace w = carve(grid, n_frames, n_points_total, const_cast<void*>(workspace));
+  if (workspace_bytes < w.total_bytes) return -1;
+  *bitmap = w.bitmap;
+  *wordprefix = w.wordprefix;
+  *words = w.words;
+  return 0;
+}
+}  // namespace vn
 
 extern "C" {
 
@@ -789,7 +802,7 @@ static int svfe_fused_impl(const vn_grid_t* grid, const float* points, const int
                            const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
                            const float* s2, const float* t2, float* voxelwise, void* dense_bf16,
                            int64_t* coordinate_buffer, int64_t* number_buffer, void* workspace, size_t workspace_bytes,
-                           vn_stream_t stream, bool bucketed) {
+                           vn_stream_t stream, bool bucketed, bool dense_rows = false) {
   int rc = check_common(grid, points, frame_offsets, n_frames, n_points_total, workspace, workspace_bytes);
   if (rc != VN_OK) return rc;
   VN_REQUIRE(voxel_offsets != nullptr, "voxelize_svfe_fused: voxel_offsets is null");
@@ -817,7 +830,7 @@ static int svfe_fused_impl(const vn_grid_t* grid, const float* points, const int
       *grid, reinterpret_cast<const float4*>(points), n_frames, voxel_offsets, max_voxels, w.cnt, w.seg, w.pidx, w1, b1,
       s1, t1, w2, b2, s2, t2, voxelwise, reinterpret_cast<__nv_bfloat16*>(dense_bf16),
       bucketed ? nullptr : reinterpret_cast<long long*>(coordinate_buffer), reinterpret_cast<long long*>(number_buffer),
-      w.counters, w.biglist);
+      w.counters, w.biglist, dense_rows ? 1 : 0);
   VN_LAUNCH_CHECK("k_vox_svfe_packed");
   return VN_OK;
 }
@@ -842,6 +855,17 @@ int vn_voxelize_svfe_bucketed(const vn_grid_t* grid, const float* points, const 
   return svfe_fused_impl(grid, points, frame_offsets, n_frames, n_points_total, voxel_offsets, max_voxels, w1, b1, s1, t1, w2,
                          b2, s2, t2, voxelwise, dense_bf16, coordinate_buffer, number_buffer, workspace, workspace_bytes,
                          stream, true);
+}
+
+int vn_voxelize_svfe_rows(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,
+                          int64_t n_points_total, const int32_t* voxel_offsets, int64_t max_voxels, const float* w1,
+                          const float* b1, const float* s1, const float* t1, const float* w2, const float* b2,
+                          const float* s2, const float* t2, void* rows_bf16, int64_t* coordinate_buffer, int32_t bucketed,
+                          void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(rows_bf16 != nullptr && (reinterpret_cast<uintptr_t>(rows_bf16) & 15) == 0, "voxelize_svfe_rows: rows null or misaligned");
+  return svfe_fused_impl(grid, points, frame_offsets, n_frames, n_points_total, voxel_offsets, max_voxels, w1, b1, s1, t1, w2,
+                         b2, s2, t2, nullptr, rows_bf16, coordinate_buffer, nullptr, workspace, workspace_bytes, stream,
+                         bucketed != 0, true);
 }
 
 int vn_voxelize_bucket_coords(const vn_grid_t* grid, const float* points, const int32_t* frame_offsets, int32_t n_frames,

@@ -186,6 +186,27 @@ def voxelize_svfe_fused(grid, points, frame_offsets, voxel_offsets, p1, p2, voxe
         )
 
 
+def voxelize_svfe_rows(grid, points, frame_offsets, voxel_offsets, p1, p2, rows, coords, workspace, bucketed: bool = False) -> None:
+    """voxelize_svfe_fused without any dense tensor (model.py:102-106 never materialised): the voxel-wise maxima of voxel
+    row r go to rows[r] ((cap,128) bf16, np.unique row order); the cell -> row map is the occupancy index the voxelizer
+    left in `workspace` (consumed by conv3d_bn_relu_fwd_rows)."""
+    _require_cuda(points, frame_offsets, voxel_offsets, rows, coords, workspace, *p1, *p2)
+    _contig(coords, torch.int64), _contig(rows, torch.bfloat16)
+    if rows.dim() != 2 or rows.shape[1] != 128 or rows.shape[0] != coords.shape[0]:
+        raise RuntimeError("rows must be (cap,128) bf16 with the capacity of coords; got %s" % (tuple(rows.shape),))
+    n_frames = frame_offsets.numel() - 1
+    with torch.cuda.device(points.device):
+        check(
+            _cabi.lib().vn_voxelize_svfe_rows(
+                C.byref(grid), _ptr(points), _ptr(frame_offsets), n_frames, points.shape[0], _ptr(voxel_offsets),
+                coords.shape[0], *[_ptr(_contig(t, torch.float32)) for t in p1],
+                *[_ptr(_contig(t, torch.float32)) for t in p2], _ptr(rows), _ptr(coords), 1 if bucketed else 0,
+                _ptr(workspace), workspace.numel() * workspace.element_size(), _stream(),
+            ),
+            "vn_voxelize_svfe_rows",
+        )
+
+
 # ---------------------------------------------------------------------------------------------
 # sparse -> dense
 # ---------------------------------------------------------------------------------------------
@@ -374,6 +395,48 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
                 _ptr(out_state), _ptr(workspace), workspace.numel(), _stream(),
             ),
             "vn_conv3d_bn_relu_fwd",
+        )
+    return out
+
+
+def conv3d_bn_relu_fwd_rows(grid, rows, voxel_offsets, n_points_total: int, vox_workspace, packed_weight, scale, shift,
+                            stride_d: int, pad_d: int, out, box_flags=None, consume_flags: bool = False, sub=None,
+                            workspace=None, out_state=None, planned: bool = False):
+    """conv3d_bn_relu_fwd for the first middle layer (model.py:207) straight from the voxel-wise rows: rows (cap,128)
+    bf16 from voxelize_svfe_rows, the occupancy index in `vox_workspace` (left by voxelize_index for the same grid,
+    frame count and n_points_total) as the cell -> row map.  No (B,D,H,W,128) tensor exists; bit-identical to
+    conv3d_bn_relu_fwd on the scattered grid.  out: (B,Dout,H,W,64) bf16."""
+    _require_cuda(rows, voxel_offsets, vox_workspace, packed_weight, scale, shift, box_flags, sub, workspace, out_state, out)
+    _contig(rows, torch.bfloat16), _contig(out, torch.bfloat16)
+    B = voxel_offsets.numel() - 1
+    Dout = conv3d_out_depth(grid.D, stride_d, pad_d)
+    if tuple(out.shape) != (B, Dout, grid.H, grid.W, 64):
+        raise RuntimeError("out must be (B,Dout,H,W,64) bf16; got %s" % (tuple(out.shape),))
+    _contig(shift, torch.float32)
+    if tuple(shift.shape) == (64,):
+        n_variants = 0
+    elif tuple(shift.shape) == (Dout, 64):
+        n_variants = 1
+    elif tuple(shift.shape) == (3, 3, Dout, 64):
+        n_variants = 9
+    else:
+        raise RuntimeError("shift must have shape (64,), (Dout,64) or (3,3,Dout,64); got %s" % (tuple(shift.shape),))
+    if sub is not None and (tuple(sub.shape) != (Dout, 64) or sub.dtype != torch.float32 or not sub.is_contiguous()):
+        raise RuntimeError("sub must be a contiguous (Dout,64) float32 tensor")
+    if box_flags is not None and (box_flags.dtype != torch.uint8 or box_flags.numel() != conv3d_box_flags_bytes(B, grid.D, grid.H, grid.W)):
+        raise RuntimeError("box_flags must be a uint8 tensor of conv3d_box_flags_bytes(B, D, H, W) elements")
+    if workspace is None:
+        workspace = torch.empty(conv3d_workspace_bytes(B, grid.H, grid.W), dtype=torch.uint8, device=rows.device)
+    opts = (_cabi.VN_CONV_FLAGS_CONSUME if consume_flags else 0) | (_cabi.VN_CONV_FLAGS_PLANNED if planned else 0)
+    with torch.cuda.device(rows.device):
+        check(
+            _cabi.lib().vn_conv3d_bn_relu_fwd_rows(
+                C.byref(grid), _ptr(rows), rows.shape[0], _ptr(voxel_offsets), B, int(n_points_total), _ptr(vox_workspace),
+                vox_workspace.numel() * vox_workspace.element_size(), stride_d, pad_d, _ptr(packed_weight),
+                _ptr(_contig(scale, torch.float32)), _ptr(shift), n_variants, _ptr(sub), 0, _ptr(out), _ptr(box_flags), opts,
+                _ptr(out_state), _ptr(workspace), workspace.numel(), _stream(),
+            ),
+            "vn_conv3d_bn_relu_fwd_rows",
         )
     return out
 

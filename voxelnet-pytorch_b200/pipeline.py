@@ -66,7 +66,7 @@ _NO_SPAN = _NoSpan()
 class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
                  voxels_per_frame_capacity: int = 49152, fuse_voxel_features: bool = True,
-                 skip_empty_boxes: bool = True, resident_outputs: bool = True):
+                 skip_empty_boxes: bool = True, resident_outputs: bool = True, materialise_grid: bool = False):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
         self.cfg = grid_config(target)
@@ -75,6 +75,13 @@ class VoxelNetFrontEnd:
         # True: the (K,T,7) feature buffer is never materialised (vn_voxelize_svfe_fused);
         # False: voxel dict written then read back by the SVFE kernel (the reference's data flow)
         self.fuse_voxel_features = bool(fuse_voxel_features)
+        # False (default, eval fast path): the (B,D,H,W,128) tensor of model.py:102-106 is never materialised.  The SVFE
+        # kernel writes a compact (K,128) bf16 row table and the first conv layer builds its operand boxes from it
+        # through the voxelizer's occupancy index (vn_voxelize_svfe_rows / vn_conv3d_bn_relu_fwd_rows).  True: the
+        # round-1 form - a resident, zero-between-steps bf16 grid (5.8 GB at Car batch 16) that is written at the K
+        # occupied cells, read by TMA and re-zeroed.  Bit-identical outputs.  The voxel-dict data flow
+        # (fuse_voxel_features=False) and the training step always use the grid (allocated on first use).
+        self.materialise_grid = bool(materialise_grid) or not self.fuse_voxel_features
         # True: the middle layers skip input boxes that hold only background.  conv-1's input is the
         # ~99 % empty voxel grid (exact skip); conv-2/3 then read their inputs as deviations from the
         # constant the previous layer outputs over empty space, which are zero wherever no voxel is in
@@ -149,10 +156,11 @@ class VoxelNetFrontEnd:
             return
         if self._shape is not None:
             # drop the old set first: two ~10 GB buffer sets per front end must not coexist
-            for name in ("workspace", "voxels", "voxelwise", "dense", "box_flags", "conv_workspaces", "out_states", "act1", "act2", "out"):
+            for name in ("workspace", "voxels", "voxelwise", "dense", "rows", "box_flags", "conv_workspaces", "out_states", "act1", "act2", "out"):
                 setattr(self, name, None)
             self._train_coords = None
         self._generation += 1
+        self._pending_frames = n_frames
         c = self.cfg
         cap = min(self.cap_per_frame * n_frames, max(n_points, 1))
         T = c.points_per_voxel
@@ -169,8 +177,12 @@ class VoxelNetFrontEnd:
             n_frames,
         )
         self.voxelwise = torch.empty((0 if self.fuse_voxel_features else cap, 128), dtype=torch.float32, device=device)
-        self.dense = torch.empty((B, D, H, W, 128), dtype=torch.bfloat16, device=device)
-        ops.fill_zero(self.dense)  # paid once: the step re-zeroes only the rows it wrote
+        self.dense = None
+        self.rows = None
+        if self.materialise_grid:
+            self._ensure_dense(device)
+        else:
+            self.rows = torch.empty((cap, 128), dtype=torch.bfloat16, device=device)
         # live-box tables of the three layers: set by mark_boxes from the voxel coordinates, reset by
         # the layer that consumes them
         self.box_flags = [ops.conv3d_new_box_flags(B, d, H, W, device) for d in (D, d1, d2)] if self.skip_empty_boxes else None
@@ -182,6 +194,26 @@ class VoxelNetFrontEnd:
         self.out = torch.empty((B, 64 * d3, H, W), dtype=torch.float32, device=device)
         self.capacity = cap
         self._shape = shape
+
+    def _ensure_dense(self, device) -> None:
+        """The resident bf16 grid (materialise_grid, the voxel-dict data flow, the training step): zero-filled once,
+        every step re-zeroes the cells it wrote."""
+        if getattr(self, "dense", None) is None:
+            c = self.cfg
+            self.dense = torch.empty((self._pending_frames, c.depth, c.height, c.width, 128), dtype=torch.bfloat16, device=device)
+            ops.fill_zero(self.dense)
+
+    def device_bytes(self) -> dict:
+        """Bytes of device memory this front end holds, by buffer (after the first call / reserve())."""
+        out = {}
+        for name in ("workspace", "dense", "rows", "act1", "act2", "out"):
+            t = getattr(self, name, None)
+            out[name] = 0 if t is None else t.numel() * t.element_size()
+        out["coordinates"] = self.voxels.coordinate.numel() * 8 if getattr(self, "voxels", None) is not None else 0
+        out["plans_flags_states"] = sum(t.numel() * t.element_size() for lst in (self.box_flags, self.conv_workspaces, self.out_states)
+                                        if lst is not None for t in lst)
+        out["total"] = sum(out.values())
+        return out
 
     def forward_points(self, points: torch.Tensor, frame_offsets: torch.Tensor, max_points_per_frame: int,
                        timer: StageTimer = None) -> torch.Tensor:
@@ -200,6 +232,10 @@ class VoxelNetFrontEnd:
         k_dev = vb.n_voxels_dev
         overlap = self.skip_empty_boxes and timer is None and self.overlap_small_kernels
         early = overlap and self.fuse_voxel_features
+        use_rows = not self.materialise_grid
+        if not use_rows:
+            self._ensure_dense(points.device)
+        n_pts = points.shape[0]
         if early:
             # coordinates right after the bucketing; live-box marking and the three conv plans then run on the side
             # stream next to the SVFE kernel
@@ -222,14 +258,22 @@ class VoxelNetFrontEnd:
                 ops.conv3d_plan(B_, self.act2.shape[1], H_, W_, 2, 1, self.box_flags[2], self.conv_workspaces[2],
                                 consume_flags=True, border_ring=True, out_state=st_[2])
                 ev[1].record(aux)
-            ops.voxelize_svfe_fused(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2,
-                                    None, vb.coordinate, None, self.workspace, dense=self.dense, bucketed=True)
+            if use_rows:
+                ops.voxelize_svfe_rows(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2, self.rows,
+                                       vb.coordinate, self.workspace, bucketed=True)
+            else:
+                ops.voxelize_svfe_fused(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2,
+                                        None, vb.coordinate, None, self.workspace, dense=self.dense, bucketed=True)
         elif self.fuse_voxel_features:
             with span("voxelize"):  # crop, cell keys, occupancy bitmap, ranks, per-voxel buckets
                 ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
-            with span("svfe"):      # bucket -> first-T selection -> 7-d rows on chip -> VFE-1/VFE-2/max -> grid cell
-                ops.voxelize_svfe_fused(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2,
-                                        None, vb.coordinate, None, self.workspace, dense=self.dense)
+            with span("svfe"):      # bucket -> first-T selection -> 7-d rows on chip -> VFE-1/VFE-2/max -> row table / grid cell
+                if use_rows:
+                    ops.voxelize_svfe_rows(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2, self.rows,
+                                           vb.coordinate, self.workspace)
+                else:
+                    ops.voxelize_svfe_fused(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2,
+                                            None, vb.coordinate, None, self.workspace, dense=self.dense)
         else:
             with span("voxelize"):
                 ops.voxelize_index(self.grid, points, frame_offsets, max_points_per_frame, vb.voxel_offsets, self.workspace)
@@ -246,6 +290,17 @@ class VoxelNetFrontEnd:
         (w0, s0, t0), (w1, s1, t1), (w2, s2, t2) = self._conv
         ws0, ws1, ws2 = self.conv_workspaces
         st0, st1, st2 = self.out_states if self.out_states is not None else (None, None, None)
+
+        def conv1(**kw):  # the first layer: from the row table (no grid) or from the resident grid
+            if use_rows:
+                return ops.conv3d_bn_relu_fwd_rows(self.grid, self.rows, vb.voxel_offsets, n_pts, self.workspace, w0, s0, t0, 2, 1,
+                                                   out=self.act1, **kw)
+            return ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, **kw)
+
+        def clear_grid():  # re-zero the grid cells of this step (nothing to do without a grid)
+            if not use_rows:
+                ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+
         if overlap:
             # Same launches as the serial branch below, with the small latency-bound kernels off the critical path:
             # the work plans of conv-2/3 depend on the voxel coordinates only and are built on a side stream while
@@ -265,38 +320,43 @@ class VoxelNetFrontEnd:
                     ops.conv3d_plan(B, self.act1.shape[1], H, W, 1, 0, f1, ws1, consume_flags=True, out_state=st1)
                     ops.conv3d_plan(B, self.act2.shape[1], H, W, 2, 1, f2, ws2, consume_flags=True, border_ring=True, out_state=st2)
                     ev[1].record(aux)
-            ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=f0, consume_flags=True,
-                                   sub=self._bg[0], workspace=ws0, out_state=st0, planned=early)
-            ev[2].record(main)
-            with torch.cuda.stream(aux):
-                aux.wait_event(ev[2])
-                ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
-                ev[3].record(aux)
+            conv1(box_flags=f0, consume_flags=True, sub=self._bg[0], workspace=ws0, out_state=st0, planned=early)
+            if not use_rows:
+                ev[2].record(main)
+                with torch.cuda.stream(aux):
+                    aux.wait_event(ev[2])
+                    clear_grid()
+                    ev[3].record(aux)
             if not early:
                 main.wait_event(ev[1])
             ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
                                    consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
             ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
                                    consume_flags=True, border_ring=True, workspace=ws2, out_state=st2, planned=True)
-            main.wait_event(ev[3])  # join: the next step's grid writes come after the clear
+            if not use_rows:
+                main.wait_event(ev[3])  # join: the next step's grid writes come after the clear
         elif self.skip_empty_boxes:
             f0, f1, f2 = self.box_flags
+            B_, H_, W_ = n_frames, self.cfg.height, self.cfg.width
+            with span("plan"):  # the three device-built work plans (in the overlapped order they run on the side stream)
+                ops.conv3d_plan(B_, self.cfg.depth, H_, W_, 2, 1, f0, ws0, consume_flags=True, out_state=st0)
+                ops.conv3d_plan(B_, self.act1.shape[1], H_, W_, 1, 0, f1, ws1, consume_flags=True, out_state=st1)
+                ops.conv3d_plan(B_, self.act2.shape[1], H_, W_, 2, 1, f2, ws2, consume_flags=True, border_ring=True, out_state=st2)
             with span("conv1"):  # zero background in, deviation from relu(shift) out
-                ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, box_flags=f0, consume_flags=True,
-                                       sub=self._bg[0], workspace=ws0, out_state=st0)
+                conv1(box_flags=f0, consume_flags=True, sub=self._bg[0], workspace=ws0, out_state=st0, planned=True)
             with span("unscatter"):
-                ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+                clear_grid()
             with span("conv2"):
                 ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
-                                       consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1)
+                                       consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
             with span("conv3"):  # conv-2's zero padding makes its output deviate along the H/W border
                 ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
-                                       consume_flags=True, border_ring=True, workspace=ws2, out_state=st2)
+                                       consume_flags=True, border_ring=True, workspace=ws2, out_state=st2, planned=True)
         else:
             with span("conv1"):
-                ops.conv3d_bn_relu_fwd(self.dense, w0, s0, t0, 2, 1, out=self.act1, workspace=ws0)
+                conv1(workspace=ws0)
             with span("unscatter"):
-                ops.scatter_dense_bf16(None, vb.coordinate, self.dense, clear=True, n_voxels_dev=k_dev)
+                clear_grid()
             with span("conv2"):
                 ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2, workspace=ws1)
             with span("conv3"):
@@ -326,7 +386,7 @@ class VoxelNetFrontEnd:
     def _clear_train_cells(self) -> None:
         """Re-zero the grid cells the previous training step wrote (the eval path clears its own)."""
         prev = getattr(self, "_train_coords", None)
-        if prev is not None and prev.shape[0] > 0:
+        if prev is not None and prev.shape[0] > 0 and self.dense is not None:
             ops.scatter_dense_bf16(None, prev, self.dense, clear=True)
         self._train_coords = None
 
@@ -345,6 +405,7 @@ class VoxelNetFrontEnd:
             raise RuntimeError("forward_points_train needs both modules in .train() mode")
         n_frames = frame_offsets.numel() - 1
         self._ensure_buffers(n_frames, points.shape[0], points.device)
+        self._ensure_dense(points.device)  # the training kernels (sparse wgrad of layer 1) read the resident grid
         self._clear_train_cells()
         self._p1 = None  # running statistics (and soon the weights) change: the eval path re-folds on its next call
         if self.out_states is not None:
