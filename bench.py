@@ -568,21 +568,45 @@ def main():
     def src(i):
         return host_ring[batch_of(i)][(i // 2) % ring_len]
 
-    def e2e_run(n, prepacked=None):
-        # step i: (pack i+P+1 starts) -> upload i+P -> forward i -> counts of step i-P.  The host consumes the counts P
-        # steps behind (the device queue never drains) and the last P before the clock stops.
-        # prepacked: the pinned batches are filled already (a loader that reads files straight into pinned memory).
-        if prepacked is None:
+    # the same ring in page-locked memory: what a loader that reads .bin files into pinned arrays hands over
+    # (dataset.load_velodyne_bin(pinned=True)); HostFrameStream.upload_frames copies these straight into the device slot
+    from voxelnet_pytorch_b200 import pinned_frame
+
+    def to_pinned(f):
+        a = pinned_frame(f.shape[0])
+        a[...] = f
+        return a
+
+    pinned_ring = [[[to_pinned(f) for f in fs] for fs in ring] for ring in host_ring]
+
+    def src_pinned(i):
+        return pinned_ring[batch_of(i)][(i // 2) % ring_len]
+
+    def e2e_run(n, mode, prepacked=None):
+        # step i: upload i+P -> forward i -> counts of step i-P.  The host consumes the counts P steps behind (the device
+        # queue never drains) and the last P before the clock stops.
+        #   mode "pinned_frames": per-frame page-locked arrays, one async copy per frame (no host packing)
+        #   mode "pageable":      per-frame pageable arrays, packed into a pinned batch by the host thread pool first
+        #   mode "prepacked":     batches that already sit packed in pinned memory (round 1's e2e definition)
+        def up(j):
+            if mode == "pinned_frames":
+                stream.upload_frames(src_pinned(j))
+            elif mode == "pageable":
+                stream.upload(pinned[j % NP])
+            else:
+                stream.upload(prepacked[batch_of(j)])
+
+        if mode == "pageable":
             for j in range(min(P + 1, n)):
                 pinned[j % NP].fill_async(src(j))
         for j in range(min(P, n)):
-            stream.upload(pinned[j % NP] if prepacked is None else prepacked[batch_of(j)])
+            up(j)
         seen = 0
         for i in range(n):
-            if prepacked is None and i + P + 1 < n:
+            if mode == "pageable" and i + P + 1 < n:
                 pinned[(i + P + 1) % NP].fill_async(src(i + P + 1))
             if i + P < n:
-                stream.upload(pinned[(i + P) % NP] if prepacked is None else prepacked[batch_of(i + P)])
+                up(i + P)
             stream.forward()
             if i >= P:
                 seen += int(stream.voxel_counts_host(lag=P)[-1])
@@ -590,23 +614,18 @@ def main():
             seen += int(stream.voxel_counts_host(lag=lag)[-1])
         return seen
 
-    e2e_run(4 * P * (P + 1))  # (with CUDA graphs: every (front end, staging slot, batch) step is captured on its second visit)
-    barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    e2e_run(args.steps)
-    f1.record()
-    barrier()
-    ms_e2e = f0.elapsed_time(f1)
-    # second figure: the same loop from batches that already sit in pinned memory (round 1's e2e definition)
     prepacked = [PinnedFrameBatch.from_frames(frame_sets[c]) for c in sets_sorted]
-    e2e_run(2 * P * (P + 1), prepacked)
-    barrier()
-    f0.record()
-    e2e_run(args.steps, prepacked)
-    f1.record()
-    barrier()
-    ms_e2e_prepacked = f0.elapsed_time(f1)
+    ms_by_mode = {}
+    for mode in ("pinned_frames", "pageable", "prepacked"):
+        e2e_run(4 * P * (P + 1), mode, prepacked)  # (with CUDA graphs: every (front end, staging slot, batch) step is captured on its second visit)
+        barrier()
+        f0.record()
+        e2e_run(args.steps, mode, prepacked)
+        f1.record()
+        barrier()
+        ms_by_mode[mode] = f0.elapsed_time(f1)
+    ms_e2e, ms_e2e_pageable, ms_e2e_prepacked = ms_by_mode["pinned_frames"], ms_by_mode["pageable"], ms_by_mode["prepacked"]
 
     # ---- one step at a time (P = 1) beside the in-flight figure -------------------------------------------
     ms_single = None
@@ -625,7 +644,7 @@ def main():
 
     per_rank_ms = sharding.gather_floats(ms_total / args.steps)
     per_rank_e2e_ms = sharding.gather_floats(ms_e2e / args.steps)
-    ms_total, ms_e2e, ms_e2e_prepacked = sharding.reduce_max([ms_total, ms_e2e, ms_e2e_prepacked])  # device time, max over ranks
+    ms_total, ms_e2e, ms_e2e_prepacked, ms_e2e_pageable = sharding.reduce_max([ms_total, ms_e2e, ms_e2e_prepacked, ms_e2e_pageable])  # device time, max over ranks
     if ms_single is not None:
         ms_single = sharding.reduce_max([ms_single])[0]
     frames_total = sum(sharding.gather_ints(batch))
@@ -716,12 +735,17 @@ def main():
             "e2e": {"value": frames_total / (ms_e2e / args.steps * 1e-3), "unit": UNIT,
                     "h2d_bytes_per_step": int(sum(bt.host_points.numel() * 4 + bt.host_offsets.numel() * 4 for bt in batches) / 2),
                     "d2h_bytes_per_step": int(host_counts.numel() * 4),
-                    "from": "per-frame (N_i,4) float32 numpy arrays in pageable host memory (where the reference starts, dataset.py:51); "
-                            "fresh array objects every step from a ring of %d x %.0f MB" % (2 * ring_len, max_points * 16 / 1e6),
+                    "from": "a list of per-frame (N_i,4) float32 numpy arrays per step (what the reference's loader yields, dataset.py:51) held in "
+                            "page-locked memory (dataset.load_velodyne_bin(pinned=True) / pinned_frame): HostFrameStream.upload_frames issues one "
+                            "asynchronous copy per frame into the device CSR slot, no host-side packing; fresh array objects every step from a "
+                            "ring of %d x %.0f MB" % (2 * ring_len, max_points * 16 / 1e6),
+                    "value_from_pageable_arrays": frames_total / (ms_e2e_pageable / args.steps * 1e-3),
+                    "pageable_note": "the same list in ordinary pageable memory: packed into a pinned batch by the library's host thread pool "
+                                     "(%d threads per rank) before the copy - host-memory-bound when 8 ranks share one host" % int(n_pack),
                     "host_pack_threads": int(n_pack),
                     "value_from_prepacked_pinned_batches": frames_total / (ms_e2e_prepacked / args.steps * 1e-3),
                     "ms_per_step_by_rank": per_rank_e2e_ms,
-                    "note": "every step inside the timed region: pack its %d frame arrays into a pinned batch (library thread pool), H2D copy on a copy stream, the step "
+                    "note": "every step inside the timed region: %d per-frame H2D copies on a copy stream, the step "
                             "(voxelnet_pytorch_b200.HostFrameStream, %d front end(s) in flight, %d staging buffers), D2H of its per-frame voxel counts "
                             "(consumed %d step(s) later, the last ones before the clock stops).  The %.2f GB (B,128,H,W) result stays on the device: its consumer, "
                             "the RPN, runs on the same GPU" % (batch, P, P + 1, P, fe.out.numel() * 4 / 1e9)},

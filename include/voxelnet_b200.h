@@ -417,6 +417,14 @@ int64_t vn_host_pack_submit(const float* const* frames_host, const int64_t* n_po
                             float* points_host, int64_t capacity_points, int32_t* frame_offsets_host /* [n_frames+1] */);
 int vn_host_pack_wait(int64_t ticket);
 
+/* The same batch WITHOUT the host-side gather, for loaders that keep every frame in page-locked memory: frame i is
+ * copied to points_dev + 4 * offset_i by its own cudaMemcpyAsync on `stream` (offsets = running sum of n_points_host),
+ * the n_frames + 1 offsets are written to the page-locked frame_offsets_host and copied to frame_offsets_dev last.
+ * Only enqueues; the frame arrays and frame_offsets_host must stay untouched until the stream has passed the copies. */
+int vn_upload_frames(const float* const* frames_host, const int64_t* n_points_host, int32_t n_frames,
+                     float* points_dev, int64_t capacity_points, int32_t* frame_offsets_host,
+                     int32_t* frame_offsets_dev, vn_stream_t stream);
+
 /* Number of kernel launches the library has enqueued since load (for bench.py's gpu_launches). */
 int64_t vn_launch_count(void);
 

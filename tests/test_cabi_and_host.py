@@ -222,3 +222,18 @@ def test_host_frame_packer_packs_ragged_frames_and_is_reusable():
         vn.PinnedFrameBatch(1, 10).fill([rng.random((5, 3), dtype=np.float32)])
     empty = vn.PinnedFrameBatch(2, 4).fill([np.zeros((0, 4), np.float32)] * 2)
     assert empty.n_points == 0 and empty.offsets.tolist() == [0, 0, 0]
+
+
+def test_load_velodyne_bin_pinned_reads_the_same_points():
+    """dataset.load_velodyne_bin(pinned=True) (page-locked on a CUDA host, plain memory here) against np.fromfile."""
+    import os
+
+    import voxelnet_pytorch_b200 as vn
+    from tests import golden_util as GU
+
+    path = os.path.join(GU.GOLDEN, "kitti_0000000000.bin")
+    a = vn.load_velodyne_bin(path, pinned=True)
+    b = vn.load_velodyne_bin(path)
+    assert a.dtype == np.float32 and a.shape == b.shape == (os.path.getsize(path) // 16, 4)
+    assert np.array_equal(a, b)
+    assert vn.pinned_frame(7).shape == (7, 4)

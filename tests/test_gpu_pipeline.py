@@ -207,6 +207,33 @@ def test_host_frame_stream_matches_direct_forward(cuda_device):
         assert torch.equal(out, want[i]), i
     with pytest.raises(RuntimeError):
         stream.forward()
+    # the same batches as per-frame arrays: page-locked ones are copied frame by frame with no host packing
+    # (vn_upload_frames), pageable ones go through the library's packer - same tensors, same counts
+    import os
+
+    from tests import golden_util as GU
+
+    kitti = vn.load_velodyne_bin(os.path.join(GU.GOLDEN, "kitti_0000000000.bin"), pinned=True)
+    assert torch.from_numpy(kitti).is_pinned()
+    assert np.array_equal(kitti, np.fromfile(os.path.join(GU.GOLDEN, "kitti_0000000000.bin"), dtype=np.float32).reshape(-1, 4))
+    for pinned in (True, False):
+        def host(f):
+            if not pinned:
+                return f.copy()
+            a = vn.pinned_frame(f.shape[0])
+            a[...] = f
+            return a
+
+        assert torch.from_numpy(host(sets[0][0])).is_pinned() == pinned
+        stream.upload_frames([host(f) for f in sets[0]])
+        for i in range(3):
+            if i + 1 < 3:
+                stream.upload_frames([host(f) for f in sets[i + 1]])
+            out = stream.forward()
+            assert stream.voxel_counts_host().tolist() == counts[i]
+            assert torch.equal(out, want[i]), (pinned, i)
+    with pytest.raises(ValueError):
+        stream.upload_frames([sets[0][0]])  # wrong frame count
 
 
 def test_cuda_graph_replay_equals_eager(cuda_device):

@@ -36,7 +36,8 @@ lib.vn_conv3d_debug_flags.argtypes = [C.c_int32]
 lib.vn_conv3d_debug_flags.restype = None
 
 names = ['p_total', 'p_wait_empty_a', 'p_wait_empty_b', 'p_boxes', 'm_total', 'm_wait_full_a', 'm_wait_full_b',
-         'm_wait_acc_empty', 'e_total', 'e_wait_sched', 'e_wait_acc_full']
+         'm_wait_acc_empty', 'e_total', 'e_wait_sched', 'e_wait_acc_full', 'f0_wait_request', 'f0_lookup', 'f0_wait_stage',
+         'f0_clean_store', 'f0_fence']
 out = {}
 
 
@@ -53,27 +54,30 @@ def timed(flags, reps=6):
 base = timed(0)
 print('production kernel      ', {k: base[k] for k in ('conv1', 'conv2', 'conv3')})
 out['production'] = base
-LABEL = {0: 'instrumented', 1: 'no A loads', 2: 'no B loads', 3: 'no A+B loads', 4: 'no MMA', 8: 'no stores', 11: 'no A+B loads, no stores',
+LABEL = {16: 'no fill fence', 32: 'no lookups', 48: 'no lookups, no fence', 0: 'instrumented', 1: 'no A loads', 2: 'no B loads', 3: 'no A+B loads', 4: 'no MMA', 8: 'no stores', 11: 'no A+B loads, no stores',
          12: 'no MMA, no stores', 7: 'no loads, no MMA', 15: 'nothing but control'}
 # flags 0 with the profile buffer = instrumented kernel
 orig = ops.conv3d_bn_relu_fwd
+orig_rows = ops.conv3d_bn_relu_fwd_rows
 bufs = []
 
 
-def wrapped(*a, **k):
-    buf = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
-    lib.vn_conv3d_debug_profile(C.c_void_p(buf.data_ptr()))
-    r = orig(*a, **k)
-    lib.vn_conv3d_debug_profile(None)
-    bufs.append(buf)
-    return r
+def wrap(fn):
+    def wrapped(*a, **k):
+        buf = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
+        lib.vn_conv3d_debug_profile(C.c_void_p(buf.data_ptr()))
+        r = fn(*a, **k)
+        lib.vn_conv3d_debug_profile(None)
+        bufs.append(buf)
+        return r
+    return wrapped
 
 
-ops.conv3d_bn_relu_fwd = wrapped
+ops.conv3d_bn_relu_fwd, ops.conv3d_bn_relu_fwd_rows = wrap(orig), wrap(orig_rows)
 t = StageTimer()
 fe.forward_points(*pa, timer=t)
 torch.cuda.synchronize()
-ops.conv3d_bn_relu_fwd = orig
+ops.conv3d_bn_relu_fwd, ops.conv3d_bn_relu_fwd_rows = orig, orig_rows
 out['counters'] = {}
 for l, b in enumerate(bufs):
     x = b.cpu().numpy().reshape(148, 16)
@@ -81,7 +85,7 @@ for l, b in enumerate(bufs):
     row['m_total_max'], row['m_total_min'] = int(x[:, 4].max()), int(x[:, 4].min())
     out['counters']['conv%d' % (l + 1)] = row
     print('conv%d counters' % (l + 1), row)
-for flags in (1, 2, 3, 8, 11, 4, 12, 7, 15):
+for flags in (16, 32, 48, 1, 2, 3, 8, 11, 4, 12, 7, 15):
     r = timed(flags)
     out[LABEL[flags]] = r
     print('%-24s' % LABEL[flags], {k: r[k] for k in ('conv1', 'conv2', 'conv3')})
@@ -94,26 +98,28 @@ NTR = 1024
 traces = []
 
 
-def traced(*a, **k):
-    tb = torch.zeros(NTR * 4, dtype=torch.int64, device=dev)
-    pbuf = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
-    lib.vn_conv3d_debug_profile(C.c_void_p(pbuf.data_ptr()))
-    lib.vn_conv3d_debug_trace(C.c_void_p(tb.data_ptr()), NTR)
-    r = orig(*a, **k)
-    lib.vn_conv3d_debug_trace(None, 0)
-    lib.vn_conv3d_debug_profile(None)
-    traces.append(tb)
-    return r
+def trace(fn):
+    def traced(*a, **k):
+        tb = torch.zeros(NTR * 4, dtype=torch.int64, device=dev)
+        pbuf = torch.zeros(148 * 16, dtype=torch.int64, device=dev)
+        lib.vn_conv3d_debug_profile(C.c_void_p(pbuf.data_ptr()))
+        lib.vn_conv3d_debug_trace(C.c_void_p(tb.data_ptr()), NTR)
+        r = fn(*a, **k)
+        lib.vn_conv3d_debug_trace(None, 0)
+        lib.vn_conv3d_debug_profile(None)
+        traces.append(tb)
+        return r
+    return traced
 
 
 for flags in (0, 15):
     traces.clear()
-    ops.conv3d_bn_relu_fwd = traced
+    ops.conv3d_bn_relu_fwd, ops.conv3d_bn_relu_fwd_rows = trace(orig), trace(orig_rows)
     lib.vn_conv3d_debug_flags(flags)
     fe.forward_points(*pa, timer=StageTimer())
     torch.cuda.synchronize()
     lib.vn_conv3d_debug_flags(0)
-    ops.conv3d_bn_relu_fwd = orig
+    ops.conv3d_bn_relu_fwd, ops.conv3d_bn_relu_fwd_rows = orig, orig_rows
     for l, tb in enumerate(traces):
         x = tb.cpu().numpy().reshape(NTR, 4)
         box = (x[:, 0] != 0) & (x[:, 1] != 0)
@@ -135,7 +141,7 @@ for flags in (0, 15):
         out['trace_flags%d_conv%d' % (flags, l + 1)] = row
         print('trace flags=%d conv%d' % (flags, l + 1), row)
         if flags == 0 and l == 0:
-            out['trace_raw_conv1'] = x[:256].tolist()
+            out['trace_raw_conv1'] = x[:400].tolist()
 stats = fe.plan_stats()
 out['plan'] = stats
 print(stats)

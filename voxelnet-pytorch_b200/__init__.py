@@ -7,7 +7,7 @@ Importing the package does not load the CUDA library; the first call into `ops` 
 loudly if `lib/libvoxelnet_b200.so` is missing and cannot be built, or if no CUDA device exists.
 """
 from .config import CAR, PED_CYC, GridConfig, grid_config  # noqa: F401
-from .dataset import PinnedFrameBatch, collate_fn, load_velodyne_bin, prepare_voxel  # noqa: F401
+from .dataset import PinnedFrameBatch, collate_fn, load_velodyne_bin, pinned_frame, prepare_voxel  # noqa: F401
 from .model import ConvMD, FeatureLearningNet, MiddleConvNet, VFELayer  # noqa: F401
 from .pipeline import HostFrameStream, VoxelNetFrontEnd  # noqa: F401
 from .targets import TargetAssigner, bbox_iou, generate_anchors, generate_targets, label_to_gt_box_3d  # noqa: F401
@@ -15,6 +15,6 @@ from .utils import VoxelBatch, pack_frames, pcl_to_voxels, voxelize_batch  # noq
 
 __all__ = [
     "CAR", "PED_CYC", "GridConfig", "grid_config", "collate_fn", "prepare_voxel", "ConvMD", "FeatureLearningNet",
-    "MiddleConvNet", "VFELayer", "VoxelNetFrontEnd", "HostFrameStream", "PinnedFrameBatch", "load_velodyne_bin", "VoxelBatch", "pack_frames", "pcl_to_voxels", "voxelize_batch",
+    "MiddleConvNet", "VFELayer", "VoxelNetFrontEnd", "HostFrameStream", "PinnedFrameBatch", "load_velodyne_bin", "pinned_frame", "VoxelBatch", "pack_frames", "pcl_to_voxels", "voxelize_batch",
     "TargetAssigner", "bbox_iou", "generate_anchors", "generate_targets", "label_to_gt_box_3d",
 ]

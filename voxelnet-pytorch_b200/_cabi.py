@@ -81,6 +81,7 @@ PROTOTYPES = {
     "vn_host_pack_threads": (C.c_int, [_i32]),
     "vn_host_pack_submit": (_i64, [_p, _p, _i32, _p, _i64, _p]),
     "vn_host_pack_wait": (C.c_int, [_i64]),
+    "vn_upload_frames": (C.c_int, [_p, _p, _i32, _p, _i64, _p, _p, _p]),
 }
 
 _lib = None

@@ -54,7 +54,9 @@ constexpr int kMaxGroupTiles = 8;
 constexpr int kMaxTilesW = 128;
 constexpr int kMaxTableRows = 27;                    // shift-table rows (variants x Dout) kept in smem
 constexpr int kThreads = 10 * 32;            // producer, MMA issuer, 8 epilogue warps
-constexpr int kThreadsGather = kThreads + kNA * 32;  // + one box-filling warp per A stage (k_conv3d_bn_relu<.., kGather>)
+constexpr int kFill = 4;                              // box-filling warps of k_conv3d_bn_relu<.., kGather>: message i -> warp i % kFill
+constexpr int kThreadsGather = kThreads + kFill * 32;
+constexpr int kGatherTableRows = 8;                   // kGather: shift-table rows kept in smem; the rest of Control::table holds the mailboxes
 constexpr uint32_t kSmemData = kNA * kABytes + kNB * kBSlotBytes;  // 221184
 
 // What one input plane contributes (host-computed; see plan_planes()).
@@ -151,12 +153,24 @@ struct Control {
   uint32_t pad[1];
   uint32_t row_zero[kSlots];  // [dout]: relu(interior shift row) - sub == 0 for all channels
   uint4 msg[kNA];  // one message per A stage, written by the producer before it arms full_a (see kMsg*)
-  uint64_t req_full[kNA];  // kGather: the producer asks the stage's filling warp for a box ...
-  int4 req[kNA];           // ... {first column, first row, plane | chunk << 8, frame (-1: stop)}
   float scale[64];
   float sub[kSlots * 64];
   alignas(16) float table[kMaxTableRows * 64];  // training kernel: rows 16..19 hold the CTA-level partial sums
 };
+// kGather: message i (a box or a control message) goes through the one-slot mailbox of filling warp i % kFill, which
+// fills stage i % kNA and owns its full / empty barriers from then on: {first column, first row, plane | chunk << 8 |
+// kind << 16, frame} + the issuer message.  dirty[s][lane] bit k: box row lane + 32 k of stage s holds a voxel row.
+// Lives in Control::table behind the kGatherTableRows rows the first layer's epilogue needs.
+struct Mailboxes {
+  uint64_t full[kFill], empty[kFill];
+  int4 req[kFill];
+  uint4 msg[kFill];
+  uint8_t dirty[kNA][32];
+  uint32_t turn[kNA];  // uses of the stage armed so far (two warps take turns on a stage: see the wait in the filling loop)
+};
+static_assert(kFill % kNA == 0, "filling warps per stage");
+static_assert(sizeof(Mailboxes) <= (kMaxTableRows - kGatherTableRows) * 64 * sizeof(float), "mailboxes fit behind the table rows");
+__device__ __forceinline__ Mailboxes* ctl_mail(Control* ctl) { return reinterpret_cast<Mailboxes*>(&ctl->table[kGatherTableRows * 64]); }
 __device__ __forceinline__ double* ctl_stat(Control* ctl) { return reinterpret_cast<double*>(&ctl->table[16 * 64]); }
 constexpr uint32_t kSmemBytes = kSmemData + 1024 /*align slack*/ + (uint32_t)sizeof(Control);
 static_assert(kSmemBytes <= 232448, "shared memory budget (227 KB)");
@@ -179,6 +193,9 @@ constexpr int kDbgNoALoad = 1;   // ... the TMA loads of the input boxes (the MM
 constexpr int kDbgNoBLoad = 2;   // ... the bulk loads of the weights
 constexpr int kDbgNoMma = 4;     // ... the tcgen05.mma instructions (commits only)
 constexpr int kDbgNoStore = 8;   // ... the epilogue's global stores
+constexpr int kDbgNoFence = 16;  // kGather: ... the filling warps' proxy fence
+constexpr int kDbgNoLookup = 32; // kGather: ... the occupancy lookups (every box is treated as empty)
+constexpr int kReqBox = 0, kReqControl = 1, kReqStop = 2;  // kGather mailbox kinds (Control::req[].z >> 16)
 constexpr uint32_t kDescHi = 0x40004040u;  // SW128 K-major descriptor, high word: SBO = 1024 B, version 1, layout 2
 
 __device__ __forceinline__ uint64_t desc_from_lo(uint32_t lo) { return ((uint64_t)kDescHi << 32) | lo; }
@@ -331,12 +348,14 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     for (int i = 0; i < kSlots; ++i) { mbar_init(&ctl->acc_full[i], 1); mbar_init(&ctl->acc_empty[i], 8); }
     for (int i = 0; i < kSched; ++i) { mbar_init(&ctl->sched_full[i], 1); mbar_init(&ctl->sched_empty[i], 8); }
     if (kGather)
-      for (int i = 0; i < kNA; ++i) mbar_init(&ctl->req_full[i], 1);
+      for (int i = 0; i < kFill; ++i) { mbar_init(&ctl_mail(ctl)->full[i], 1); mbar_init(&ctl_mail(ctl)->empty[i], 1); }
     mbar_fence_init();
     fence_proxy_async_smem();
     if (!kGather) tma_prefetch_desc(&tmap_x);
   }
   if (kGather) {  // the A stages start all-zero and every filling warp restores that after each box
+    if (threadIdx.x < kNA * 32) ctl_mail(ctl)->dirty[threadIdx.x >> 5][threadIdx.x & 31] = 0;
+    if (threadIdx.x < kNA) ctl_mail(ctl)->turn[threadIdx.x] = 0;
     for (uint32_t i = threadIdx.x; i < kNA * kABytes / 16; i += blockDim.x) reinterpret_cast<uint4*>(smem_a)[i] = make_uint4(0u, 0u, 0u, 0u);
     fence_proxy_async_smem();
   }
@@ -459,7 +478,18 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
                                      ((fresh << slot_lo) << kMsgWaitShift) | (fresh == 0 ? kMsgAccumulate : 0u) |
                                      ((fresh != 0 && fresh != full) ? kMsgSplit : 0u);
               const uint32_t sa = a_it % kNA;
-              VN_TIMED(pw_a, mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1));
+              const uint32_t sf = a_it % kFill;  // kGather: the message's mailbox
+              VN_TIMED(pw_a, mbar_wait(kGather ? &ctl_mail(ctl)->empty[sf] : &ctl->empty_a[sa], ((a_it / (kGather ? kFill : kNA)) & 1) ^ 1));
+              if (kGather && lane < (uint32_t)kHaloH) {
+                // the occupancy words the filling warp will look up, on their way into this SM's L1 while the request waits
+                const int hh = h0 - 1 + (int)lane;
+                if (hh >= 0 && hh < P.H) {
+                  const int ww = w0 + kw - 1 < 0 ? 0 : w0 + kw - 1;
+                  const size_t word = (size_t)b * P.g_words + ((uint32_t)((p * P.H + hh) * P.W + ww) >> 5);
+                  prefetch_l1(P.g_bitmap + word);
+                  prefetch_l1(P.g_prefix + word);
+                }
+              }
               if (kDebug) {
                 ++p_boxes;
                 if (P.trace != nullptr && blockIdx.x == 0 && lane == 0 && (int)a_it < P.trace_n) {
@@ -468,13 +498,16 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
                 }
               }
               if (elect_one()) {
-                ctl->msg[sa] = make_uint4(flags, tmem_base + slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
+                const uint4 msg = make_uint4(flags, tmem_base + slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
                 if (kGather) {
-                  ctl->req[sa] = make_int4(w0 + kw - 1, h0 - 1, p | (c << 8), b);
-                  mbar_arrive(&ctl->req_full[sa]);
+                  ctl_mail(ctl)->req[sf] = make_int4(w0 + kw - 1, h0 - 1, p | (c << 8) | (kReqBox << 16), b);
+                  ctl_mail(ctl)->msg[sf] = msg;
+                  mbar_arrive(&ctl_mail(ctl)->full[sf]);
                 } else if (kDebug && (dbg & kDbgNoALoad)) {
+                  ctl->msg[sa] = msg;
                   mbar_arrive(&ctl->full_a[sa]);
                 } else {
+                  ctl->msg[sa] = msg;
                   mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
                   tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, w0 + kw - 1, h0 - 1, p, b);
                 }
@@ -489,10 +522,18 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
             if (last_pass && touched != 0) {
               const uint32_t done = ((1u << __popc(touched)) - 1u) << slot0;
               const uint32_t sa = a_it % kNA;
-              mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+              const uint32_t sf = a_it % kFill;
+              mbar_wait(kGather ? &ctl_mail(ctl)->empty[sf] : &ctl->empty_a[sa], ((a_it / (kGather ? kFill : kNA)) & 1) ^ 1);
               if (elect_one()) {
-                ctl->msg[sa] = make_uint4(done << kMsgCommitShift, 0u, 0u, 0u);
-                mbar_arrive(&ctl->full_a[sa]);
+                const uint4 msg = make_uint4(done << kMsgCommitShift, 0u, 0u, 0u);
+                if (kGather) {
+                  ctl_mail(ctl)->req[sf] = make_int4(0, 0, kReqControl << 16, 0);
+                  ctl_mail(ctl)->msg[sf] = msg;
+                  mbar_arrive(&ctl_mail(ctl)->full[sf]);
+                } else {
+                  ctl->msg[sa] = msg;
+                  mbar_arrive(&ctl->full_a[sa]);
+                }
               }
               __syncwarp();
               ++a_it;
@@ -509,24 +550,32 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     }
     {  // tell the issuing warp to stop
       const uint32_t sa = a_it % kNA;
-      mbar_wait(&ctl->empty_a[sa], ((a_it / kNA) & 1) ^ 1);
+      const uint32_t sf = a_it % kFill;
+      mbar_wait(kGather ? &ctl_mail(ctl)->empty[sf] : &ctl->empty_a[sa], ((a_it / (kGather ? kFill : kNA)) & 1) ^ 1);
       if (elect_one()) {
-        ctl->msg[sa] = make_uint4(kMsgEnd, 0u, 0u, 0u);
-        mbar_arrive(&ctl->full_a[sa]);
+        const uint4 msg = make_uint4(kMsgEnd, 0u, 0u, 0u);
+        if (kGather) {
+          ctl_mail(ctl)->req[sf] = make_int4(0, 0, kReqControl << 16, 0);
+          ctl_mail(ctl)->msg[sf] = msg;
+          mbar_arrive(&ctl_mail(ctl)->full[sf]);
+        } else {
+          ctl->msg[sa] = msg;
+          mbar_arrive(&ctl->full_a[sa]);
+        }
       }
       __syncwarp();
       ++a_it;
     }
-    if (kGather) {
-      // every other stage's last use has been released (so its filling warp is idle): tell the filling warps to stop
-      for (int i = 0; i < kNA - 1; ++i, ++a_it) mbar_wait(&ctl->empty_a[a_it % kNA], ((a_it / kNA) & 1) ^ 1);
-      if (elect_one()) {
-        for (int i = 0; i < kNA; ++i) {
-          ctl->req[i] = make_int4(0, 0, 0, -1);
-          mbar_arrive(&ctl->req_full[i]);
+    if (kGather) {  // ... and then every filling warp (each sees its requests in order)
+      for (int i = 0; i < kFill; ++i, ++a_it) {
+        const uint32_t sf = a_it % kFill;
+        mbar_wait(&ctl_mail(ctl)->empty[sf], ((a_it / kFill) & 1) ^ 1);
+        if (elect_one()) {
+          ctl_mail(ctl)->req[sf] = make_int4(0, 0, kReqStop << 16, 0);
+          mbar_arrive(&ctl_mail(ctl)->full[sf]);
         }
+        __syncwarp();
       }
-      __syncwarp();
     }
     if (kDebug && P.prof != nullptr && lane == 0) {
       unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
@@ -647,68 +696,143 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     }
     __syncwarp();
   } else if (kGather && warp >= 10) {
-    // ===================== box filling (warps 10..13, one per A stage) =====================
-    const int j = (int)warp - 10;
+    // ===================== box filling (warps 10 .. 10 + kFill - 1; warp 10 + f takes messages f, f + kFill, ...) =====================
+    // Box row c = 8 * (image row) + column, 0..143, belongs to lane c % 32 (five candidates per lane).  Per request:
+    // look the 18 x 8 cells up (occupancy words + popcount prefix: ONE round of independent L2 accesses), load the
+    // occupied rows of this lane into registers (a second round), and only then wait for the stage - both latencies
+    // sit behind the MMAs that still read the stage.  Then: re-zero what this lane wrote the last time, store the new
+    // rows in the SWIZZLE_128B image (16-byte chunk q of row c at q ^ (c & 7)), publish the issuer message, arm full_a.
+    const int f = (int)warp - 10, j = f % kNA;  // mailbox, stage (with kFill = 2 kNA two warps use a stage alternately)
+    Mailboxes* mail = ctl_mail(ctl);
     uint8_t* stage = smem_a + j * kABytes;
     long long total = P.g_voxoff[P.B];
     if (total > P.g_max_voxels) total = P.g_max_voxels;
-    uint32_t n_req = 0, filled = 0;  // filled bit k: this lane wrote box row lane + 32 k the last time
+    uint32_t n_use = 0;  // messages this warp has taken
+    long long fw_req = 0, f_look = 0, fw_empty = 0, f_store = 0, f_boxes = 0;
     for (;;) {
-      mbar_wait(&ctl->req_full[j], n_req & 1);
-      ++n_req;
-      const uint4 rq_u = lds_u4(&ctl->req[j]);
+      VN_TIMED(fw_req, mbar_wait(&mail->full[f], n_use & 1));
+      const long long f_t1 = kDebug ? clock64() : 0;
+      const uint4 rq_u = lds_u4(&mail->req[f]);
+      const uint4 msg = lds_u4(&mail->msg[f]);
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&mail->empty[f]);
       const int4 rq = make_int4((int)rq_u.x, (int)rq_u.y, (int)rq_u.z, (int)rq_u.w);
-      if (rq.w < 0) break;
-#pragma unroll
-      for (int k = 0; k < 5; ++k)
-        if ((filled >> k) & 1) {
-          uint4* dst = reinterpret_cast<uint4*>(stage + (lane + 32 * k) * 128);
-#pragma unroll
-          for (int q = 0; q < 8; ++q) dst[q] = make_uint4(0u, 0u, 0u, 0u);
-        }
-      filled = 0;
-      // lanes 0..17: occupancy bits of image row rq.y + lane, columns rq.x .. rq.x + 7, and the row-table index of the first
-      uint32_t mask = 0, first = 0;
-      const int h = rq.y + (int)lane;
-      if (lane < (uint32_t)kHaloH && h >= 0 && h < P.H) {
-        const int lo_w = rq.x < 0 ? 0 : rq.x;
-        const int hi_w = rq.x + kTileW > P.W ? P.W : rq.x + kTileW;
-        const int nb = hi_w - lo_w;
-        const uint32_t cell = (uint32_t)(((rq.z & 0xff) * P.H + h) * P.W + lo_w);
-        const uint32_t word = cell >> 5, sh = cell & 31u;
-        const uint32_t* bm = P.g_bitmap + (size_t)rq.w * P.g_words;
-        const uint32_t w_lo = __ldg(bm + word);
-        const uint32_t w_hi = sh + (uint32_t)nb > 32u ? __ldg(bm + word + 1) : 0u;
-        const uint32_t win = __funnelshift_r(w_lo, w_hi, sh) & ((1u << nb) - 1u);
-        if (win != 0) {
+      const int kind = rq.z >> 16;
+      if (kind == kReqStop) break;
+      uint32_t mine = 0;
+      int row_of[5] = {0, 0, 0, 0, 0};
+      uint4 v0[8], v1[8];
+      int k0 = -1, k1 = -1;
+      const __nv_bfloat16* src0 = P.g_rows + ((rq.z >> 8) & 0xff) * 64;
+      if (kind == kReqBox) {
+        // lanes 0..17: occupancy bits of image row rq.y + lane, columns rq.x .. rq.x + 7, and the table row of the first
+        uint32_t mask = 0, first = 0;
+        const int h = rq.y + (int)lane;
+        if (lane < (uint32_t)kHaloH && h >= 0 && h < P.H && !(kDebug && (P.debug & kDbgNoLookup))) {
+          const int lo_w = rq.x < 0 ? 0 : rq.x;
+          const int hi_w = rq.x + kTileW > P.W ? P.W : rq.x + kTileW;
+          const int nb = hi_w - lo_w;
+          const uint32_t cell = (uint32_t)(((rq.z & 0xff) * P.H + h) * P.W + lo_w);
+          const uint32_t word = cell >> 5, sh = cell & 31u;
+          const uint32_t* bm = P.g_bitmap + (size_t)rq.w * P.g_words + word;
+          const uint32_t w_lo = __ldg(bm);
+          const uint32_t w_hi = sh + (uint32_t)nb > 32u ? __ldg(bm + 1) : 0u;
+          const uint32_t pre = __ldg(P.g_prefix + (size_t)rq.w * P.g_words + word);
+          const uint32_t off = (uint32_t)__ldg(P.g_voxoff + rq.w);
+          const uint32_t win = __funnelshift_r(w_lo, w_hi, sh) & ((1u << nb) - 1u);
           mask = win << (lo_w - rq.x);
-          first = (uint32_t)P.g_voxoff[rq.w] + __ldg(P.g_prefix + (size_t)rq.w * P.g_words + word) + __popc(w_lo & ((1u << sh) - 1u));
+          first = off + pre + __popc(w_lo & ((1u << sh) - 1u));
         }
-      }
-      const __nv_bfloat16* src0 = P.g_rows + (rq.z >> 8) * 64;
 #pragma unroll
-      for (int k = 0; k < 5; ++k) {
-        const uint32_t c = lane + 32 * k;           // box row = (image row, column) = (c / 8, c % 8)
-        const uint32_t r = c < 144u ? c >> 3 : 17u, i = c & 7u;
-        const uint32_t m_r = __shfl_sync(0xffffffffu, mask, r);
-        const uint32_t f_r = __shfl_sync(0xffffffffu, first, r);
-        if (c < 144u && ((m_r >> i) & 1u)) {
+        for (int k = 0; k < 5; ++k) {
+          const uint32_t c = lane + 32 * k;
+          const uint32_t r = c < 144u ? c >> 3 : 17u, i = c & 7u;
+          const uint32_t m_r = __shfl_sync(0xffffffffu, mask, r);
+          const uint32_t f_r = __shfl_sync(0xffffffffu, first, r);
           const long long row = (long long)f_r + __popc(m_r & ((1u << i) - 1u));
-          if (row < total) {
-            const uint4* src = reinterpret_cast<const uint4*>(src0 + row * 128);
-            uint4 v[8];
-#pragma unroll
-            for (int q = 0; q < 8; ++q) v[q] = __ldg(src + q);
-            uint8_t* dst = stage + c * 128;
-#pragma unroll
-            for (int q = 0; q < 8; ++q) *reinterpret_cast<uint4*>(dst + ((q ^ (c & 7u)) << 4)) = v[q];
-            filled |= 1u << k;
+          if (c < 144u && ((m_r >> i) & 1u) && row < total) {
+            mine |= 1u << k;
+            row_of[k] = (int)row;
           }
         }
+        if (kDebug) f_look += clock64() - f_t1 + (mine & 0u);
+        // the first two occupied candidates of this lane travel while the stage is still being read
+        uint32_t rest = mine;
+        if (rest) { k0 = __ffs(rest) - 1; rest &= rest - 1; }
+        if (rest) { k1 = __ffs(rest) - 1; }
+        if (k0 >= 0) {
+          const int r0 = k0 == 0 ? row_of[0] : (k0 == 1 ? row_of[1] : (k0 == 2 ? row_of[2] : (k0 == 3 ? row_of[3] : row_of[4])));
+          const uint4* src = reinterpret_cast<const uint4*>(src0 + (size_t)r0 * 128);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) v0[q] = __ldg(src + q);
+        }
+        if (k1 >= 0) {
+          const int r1 = k1 == 1 ? row_of[1] : (k1 == 2 ? row_of[2] : (k1 == 3 ? row_of[3] : row_of[4]));
+          const uint4* src = reinterpret_cast<const uint4*>(src0 + (size_t)r1 * 128);
+#pragma unroll
+          for (int q = 0; q < 8; ++q) v1[q] = __ldg(src + q);
+        }
       }
-      fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's reads
+      // This is use number u = (kFill / kNA) n + f / kNA of the stage.  A parity wait can only tell "the previous phase is over" from
+      // "it is not", and this warp could otherwise get here before the other warp of the stage has even armed use u - 1
+      // (two phases back reads as over): first wait until use u - 1 is armed, then until its MMAs are complete.
+      const uint32_t use = (uint32_t)(kFill / kNA) * n_use + (uint32_t)(f / kNA);
+      {
+        const long long t_ = kDebug ? clock64() : 0;
+        while (*reinterpret_cast<volatile uint32_t*>(&mail->turn[j]) != use) {
+        }
+        mbar_wait(&ctl->empty_a[j], (use & 1) ^ 1);
+        if (kDebug) fw_empty += clock64() - t_;
+      }
+      ++n_use;
+      const long long f_t4 = kDebug ? clock64() : 0;
+      if (kind == kReqBox && !(kDebug && (P.debug & kDbgNoALoad))) {
+        const uint32_t prev = mail->dirty[j][lane];
+#pragma unroll
+        for (int k = 0; k < 5; ++k)
+          if ((prev >> k) & 1) {
+            uint4* dst = reinterpret_cast<uint4*>(stage + (lane + 32 * k) * 128);
+#pragma unroll
+            for (int q = 0; q < 8; ++q) dst[q] = make_uint4(0u, 0u, 0u, 0u);
+          }
+        if (k0 >= 0) {
+          const uint32_t c = lane + 32 * k0;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) *reinterpret_cast<uint4*>(stage + c * 128 + ((q ^ (c & 7u)) << 4)) = v0[q];
+        }
+        if (k1 >= 0) {
+          const uint32_t c = lane + 32 * k1;
+#pragma unroll
+          for (int q = 0; q < 8; ++q) *reinterpret_cast<uint4*>(stage + c * 128 + ((q ^ (c & 7u)) << 4)) = v1[q];
+        }
+        const uint32_t more = mine & ~((k0 >= 0 ? 1u << k0 : 0u) | (k1 >= 0 ? 1u << k1 : 0u));
+        if (more) {  // (rare) a third .. fifth occupied candidate
+#pragma unroll
+          for (int k = 2; k < 5; ++k)
+            if ((more >> k) & 1) {
+              const uint4* src = reinterpret_cast<const uint4*>(src0 + (size_t)row_of[k] * 128);
+              const uint32_t c = lane + 32 * k;
+#pragma unroll
+              for (int q = 0; q < 8; ++q) v0[q] = __ldg(src + q);
+#pragma unroll
+              for (int q = 0; q < 8; ++q) *reinterpret_cast<uint4*>(stage + c * 128 + ((q ^ (c & 7u)) << 4)) = v0[q];
+            }
+        }
+        mail->dirty[j][lane] = (uint8_t)mine;
+        if (kDebug) { f_store += clock64() - f_t4; f_boxes -= clock64(); }
+        if (!(kDebug && (P.debug & kDbgNoFence))) fence_proxy_async_smem();  // generic-proxy stores -> visible to the tensor core's operand reads
+        if (kDebug) f_boxes += clock64();
+      }
+      if (lane == 0) ctl->msg[j] = msg;
       __syncwarp();
-      if (lane == 0) mbar_arrive(&ctl->full_a[j]);
+      if (lane == 0) {
+        mbar_arrive(&ctl->full_a[j]);
+        *reinterpret_cast<volatile uint32_t*>(&mail->turn[j]) = use + 1u;
+      }
+    }
+    if (kDebug && P.prof != nullptr && f == 0 && lane == 0) {
+      unsigned long long* o = P.prof + (size_t)blockIdx.x * 16;
+      o[11] = fw_req; o[12] = f_look; o[13] = fw_empty; o[14] = f_store; o[15] = f_boxes;
     }
   } else {
     // ===================== epilogue (warps 2..9) =====================
@@ -1307,6 +1431,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   P.stats = stats;
   if (gather != nullptr) {
     VN_REQUIRE(stats == nullptr && cin == 128, "conv3d: the row-table input serves the first inference layer only");
+    VN_REQUIRE(nvar * Dout <= kGatherTableRows, "conv3d: the row-table input takes a plain or per-depth shift (%d x %d table rows > %d)", nvar, Dout, kGatherTableRows);
     P.g_bitmap = gather->bitmap; P.g_prefix = gather->prefix; P.g_words = (uint32_t)gather->words;
     P.g_voxoff = gather->voxel_offsets;
     P.g_rows = reinterpret_cast<const __nv_bfloat16*>(gather->rows);

@@ -55,12 +55,32 @@ def _pinned(t: torch.Tensor) -> torch.Tensor:
     return t.pin_memory() if torch.cuda.is_available() else t
 
 
-def load_velodyne_bin(path: str) -> np.ndarray:
-    """dataset.py:51: a KITTI velodyne file -> (N,4) float32 (x, y, z, reflectance)."""
-    pcl = np.fromfile(path, dtype=np.float32)
-    if pcl.size % 4 != 0:
-        raise ValueError("%s: %d floats is not a whole number of (x, y, z, r) points" % (path, pcl.size))
-    return pcl.reshape(-1, 4)
+def pinned_frame(n_points: int) -> np.ndarray:
+    """An (n_points, 4) float32 numpy array in page-locked host memory (plain memory on a host without CUDA): what
+    `HostFrameStream.upload_frames` copies to the device without any host-side packing.  The array keeps its
+    allocation alive."""
+    return _pinned(torch.empty((int(n_points), 4), dtype=torch.float32)).numpy()
+
+
+def load_velodyne_bin(path: str, pinned: bool = False) -> np.ndarray:
+    """dataset.py:51: a KITTI velodyne file -> (N,4) float32 (x, y, z, reflectance).  pinned=True reads the file
+    straight into page-locked memory (see pinned_frame)."""
+    if not pinned:
+        pcl = np.fromfile(path, dtype=np.float32)
+        if pcl.size % 4 != 0:
+            raise ValueError("%s: %d floats is not a whole number of (x, y, z, r) points" % (path, pcl.size))
+        return pcl.reshape(-1, 4)
+    import os
+
+    size = os.path.getsize(path)
+    if size % 16 != 0:
+        raise ValueError("%s: %d bytes is not a whole number of (x, y, z, r) float32 points" % (path, size))
+    out = pinned_frame(size // 16)
+    with open(path, "rb") as f:
+        got = f.readinto(memoryview(out).cast("B"))
+    if got != size:
+        raise IOError("%s: short read (%d of %d bytes)" % (path, got, size))
+    return out
 
 
 class PinnedFrameBatch:

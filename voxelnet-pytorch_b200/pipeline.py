@@ -552,6 +552,58 @@ class HostFrameStream:
         self.pending.append((k, batch.n_points, batch.max_points_per_frame))
         self.next_slot = (k + 1) % self.n_slots
 
+    def upload_frames(self, frames: list) -> None:
+        """`upload` for a list of per-frame (N_i,4) float32 numpy arrays (what the reference's loader yields,
+        dataset.py:51).  Arrays in page-locked memory (`dataset.pinned_frame`, `load_velodyne_bin(pinned=True)`) are
+        copied straight into the device CSR slot, one asynchronous copy per frame and no host-side packing
+        (vn_upload_frames); the arrays must then stay untouched until this batch's `forward()` has been called and a
+        later `upload*` call reuses the slot (or the copy stream is synchronised).  If any array is ordinary pageable
+        memory the batch goes through an internal ring of PinnedFrameBatch (host thread pool) instead."""
+        import ctypes as C
+
+        import numpy as np
+
+        from . import _cabi
+
+        if len(self.pending) >= self.n_slots:
+            raise RuntimeError("every staging slot holds a batch that was not consumed: call forward() first")
+        k = self.next_slot
+        pts, offs = self.slots[k]
+        n = offs.numel() - 1
+        if len(frames) != n:
+            raise ValueError("expected %d frames, got %d" % (n, len(frames)))
+        fr = [f if (f.dtype == np.float32 and f.flags["C_CONTIGUOUS"]) else np.ascontiguousarray(f, dtype=np.float32) for f in frames]
+        for i, f in enumerate(fr):
+            if f.ndim != 2 or f.shape[1] != 4:
+                raise ValueError("frame %d has shape %s, expected (N,4)" % (i, f.shape))
+        if not all(torch.from_numpy(f).is_pinned() for f in fr if f.shape[0] > 0):
+            if getattr(self, "_pack_ring", None) is None:
+                from .dataset import PinnedFrameBatch
+
+                self._pack_ring = [PinnedFrameBatch(n, pts.shape[0]) for _ in range(self.n_slots + 1)]
+                self._pack_next = 0
+            pb = self._pack_ring[self._pack_next]
+            self._pack_next = (self._pack_next + 1) % len(self._pack_ring)
+            return self.upload(pb.fill(fr))
+        total = sum(int(f.shape[0]) for f in fr)
+        if total > pts.shape[0]:
+            raise ValueError("batch does not fit the staging slot (points %d > %d)" % (total, pts.shape[0]))
+        if getattr(self, "_offs_host", None) is None:
+            self._offs_host = [torch.zeros(n + 1, dtype=torch.int32).pin_memory() for _ in range(self.n_slots)]
+            self._frames_alive = [None] * self.n_slots
+        self.ready[k].synchronize()  # the previous copy out of this slot's pinned offsets is over
+        ptrs = (C.c_void_p * n)(*[f.ctypes.data for f in fr])
+        sizes = (C.c_int64 * n)(*[int(f.shape[0]) for f in fr])
+        with torch.cuda.stream(self.copy_stream):
+            self.copy_stream.wait_event(self.freed[k])
+            _cabi.check(_cabi.lib().vn_upload_frames(ptrs, sizes, n, pts.data_ptr(), pts.shape[0], self._offs_host[k].data_ptr(),
+                                                     offs.data_ptr(), torch.cuda.current_stream().cuda_stream), "vn_upload_frames")
+            self.ready[k].record(self.copy_stream)
+        self._frames_alive[k] = fr
+        self.h2d_bytes = total * 16 + offs.numel() * 4
+        self.pending.append((k, total, max([int(f.shape[0]) for f in fr], default=0)))
+        self.next_slot = (k + 1) % self.n_slots
+
     def forward(self, timer: StageTimer = None) -> torch.Tensor:
         if not self.pending:
             raise RuntimeError("forward() without an uploaded batch")
