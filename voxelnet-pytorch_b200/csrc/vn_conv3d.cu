@@ -466,6 +466,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
             const uint32_t slot0 = __shfl_sync(0xffffffffu, myslot0, t);
             uint32_t started = __shfl_sync(0xffffffffu, mystarted, t);
             const int w0 = (tw0 + t) * kTileW;
+            const bool tile_has_box = m != 0;
             while (m) {
               const int p = (__ffs(m) - 1) / 3;
               m &= m - 1;
@@ -474,7 +475,10 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
               const uint32_t fresh = (range & ~started) >> pi.dmin;  // bit j: tap j starts its accumulator
               const uint32_t slot_lo = slot0 + __popc(touched & ((1u << pi.dmin) - 1u));
               const uint32_t full = (1u << pi.nkd) - 1u;
-              const uint32_t flags = (uint32_t)pi.nkd | new_pass | (fresh << kMsgFreshShift) |
+              // the tile's last box of the group's last weight pass also carries the "accumulators complete" bits (no
+              // separate control message, which would take a ring slot away from the boxes in flight)
+              const uint32_t done = (last_pass && m == 0) ? ((1u << __popc(touched)) - 1u) << slot0 : 0u;
+              const uint32_t flags = (uint32_t)pi.nkd | new_pass | (fresh << kMsgFreshShift) | (done << kMsgCommitShift) |
                                      ((fresh << slot_lo) << kMsgWaitShift) | (fresh == 0 ? kMsgAccumulate : 0u) |
                                      ((fresh != 0 && fresh != full) ? kMsgSplit : 0u);
               const uint32_t sa = a_it % kNA;
@@ -518,8 +522,8 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
               ++a_it;
             }
             if ((int)lane == t) mystarted = started;
-            // last weight pass of the group: tile t has received everything it will get
-            if (last_pass && touched != 0) {
+            // last weight pass of the group: tile t has received everything it will get (no box of its own in this pass)
+            if (last_pass && touched != 0 && !tile_has_box) {
               const uint32_t done = ((1u << __popc(touched)) - 1u) << slot0;
               const uint32_t sa = a_it % kNA;
               const uint32_t sf = a_it % kFill;
@@ -671,6 +675,12 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
             }
           }
           umma_commit(&ctl->empty_a[sa]);
+          uint32_t cm = (f >> kMsgCommitShift) & 0xffu;  // (tile complete after this box)
+          while (cm) {
+            const uint32_t s = __ffs(cm) - 1;
+            cm &= cm - 1;
+            umma_commit(&ctl->acc_full[s]);
+          }
         } else {
           uint32_t cm = (f >> kMsgCommitShift) & 0xffu;
           while (cm) {
