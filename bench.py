@@ -367,6 +367,8 @@ def main():
     ap.add_argument("--no-cuda-graph", action="store_true", help="time eager launches instead of CUDA-graph replays")
     ap.add_argument("--data", default="synthetic", choices=["synthetic", "kitti"],
                     help="kitti: real frames of the reference's bundled drive from baseline/_ref/data (cross-check)")
+    ap.add_argument("--grid", default="auto", choices=["auto", "resident", "rows"],
+                    help="sparse->dense form of the eval path: resident bf16 grid, never-materialised row table, or the library's default policy")
     ap.add_argument("--host-threads", type=int, default=None, help="threads of the host frame packer (default: cores / ranks, 2..8)")
     ap.add_argument("--in-flight", type=int, default=None,
                     help="eval steps in flight per GPU (front ends on their own streams; 1 = strictly one step at a time); "
@@ -429,7 +431,8 @@ def main():
             m.bias.data = (torch.rand(m.bias.shape, generator=g) - 0.5) * 0.6
             m.running_mean.data = (torch.rand(m.running_mean.shape, generator=g) - 0.5) * 0.4
             m.running_var.data = 0.5 + torch.rand(m.running_var.shape, generator=g)
-    fe = vn.VoxelNetFrontEnd(fnet.to(dev), mnet.to(dev), target)
+    grid_kw = {"auto": {}, "resident": {"materialise_grid": True}, "rows": {"materialise_grid": False}}[args.grid]
+    fe = vn.VoxelNetFrontEnd(fnet.to(dev), mnet.to(dev), target, **grid_kw)
 
     # ---- inputs: pinned host staging + resident device copies of TWO different batches --------------
     # Steps alternate between them: the resident conv outputs are only rewritten where a voxel reaches
@@ -482,7 +485,7 @@ def main():
     # i % P on that pipeline's stream, so the latency-bound index / bucketing kernels of one step run beside the
     # convolution kernels of another.  Every front end keeps alternating between the two batches.
     P = max(1, args.in_flight) if args.in_flight is not None else (3 if batch <= 16 else 1)
-    fes = [fe] + [vn.VoxelNetFrontEnd(fnet, mnet, target) for _ in range(P - 1)]
+    fes = [fe] + [vn.VoxelNetFrontEnd(fnet, mnet, target, **grid_kw) for _ in range(P - 1)]
     pipes = [torch.cuda.Stream(device=dev) for _ in range(P)] if P > 1 else [torch.cuda.current_stream(dev)]
 
     def batch_of(i):
@@ -640,6 +643,30 @@ def main():
         barrier()
         ms_single = f0.elapsed_time(f1)
 
+    # ---- the other sparse->dense form beside the timed one (N = 1 only): one step at a time, graph replay ----------
+    other_form = None
+    if world == 1 and batch <= 16 and graphs is not None:
+        fe_o = vn.VoxelNetFrontEnd(fnet, mnet, target, materialise_grid=fe.dense is None)
+        g_o = [fe_o.capture_graph(bt.points, bt.offsets, bt.max_n) for bt in batches]
+        for i in range(4):
+            g_o[i % 2].replay()
+        barrier()
+        f0.record()
+        for i in range(args.steps):
+            g_o[i % 2].replay()
+        f1.record()
+        barrier()
+        t_o = StageTimer()
+        for i in range(10):
+            fe_o.forward_points(batches[i % 2].points, batches[i % 2].offsets, batches[i % 2].max_n, timer=t_o)
+        torch.cuda.synchronize()
+        other_form = {"form": "resident bf16 grid" if fe_o.dense is not None else "never materialised: row table + occupancy index (vn_conv3d_bn_relu_fwd_rows)",
+                      "single_pipeline_ms_per_step": f0.elapsed_time(f1) / args.steps,
+                      "stages_ms": {k: v[0] for k, v in t_o.summary().items()},
+                      "device_bytes_per_front_end": fe_o.device_bytes(),
+                      "note": "bit-identical output (tests/test_gpu_bench_parity.py); compare with single_pipeline.ms_per_step and config.device_bytes_per_front_end"}
+        del g_o, fe_o
+
     from voxelnet_pytorch_b200 import sharding
 
     per_rank_ms = sharding.gather_floats(ms_total / args.steps)
@@ -705,7 +732,7 @@ def main():
             stage_roofline[k]["frac"] = stage_roofline[k]["achieved"] / stage_roofline[k]["peak"]
         traffic = None
         try:  # DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+            with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
                 traffic_tab = json.load(f)
         except Exception:
             traffic_tab = {}
@@ -723,7 +750,8 @@ def main():
                        "inputs": "two different batches alternate step by step (resident outputs are restored where the previous batch reached)",
                        "l2_policy": "working set (%.2f GB of activations, outputs and row tables per front end) exceeds L2" % (fe.device_bytes()["total"] / 1e9),
                        "device_bytes_per_front_end": fe.device_bytes(),
-                       "grid": "never materialised: (K,128) bf16 rows + the voxelizer's occupancy index feed conv-1 (vn_conv3d_bn_relu_fwd_rows)" if fe.dense is None else "resident bf16 grid",
+                       "grid": "never materialised: (K,128) bf16 rows + the voxelizer's occupancy index feed conv-1 (vn_conv3d_bn_relu_fwd_rows)" if fe.dense is None
+                               else "resident bf16 grid (default policy: it fits the 8 GiB budget); --grid rows times the never-materialised form",
                        "vfe": "fp32", "conv": "bf16 operands, fp32 accumulate (tcgen05)",
                        "launch": launch_mode,
                        "in_flight": "%d step(s) in flight per GPU (%s); ms_per_step = timed region / steps" % (
@@ -753,6 +781,7 @@ def main():
             "single_pipeline": None if ms_single is None else {
                 "value": frames_total / (ms_single / args.steps * 1e-3), "ms_per_step": ms_single / args.steps,
                 "note": "ONE step at a time (graph replays back to back on one stream): the latency of a step; `value` above is throughput with %d steps in flight" % P},
+            "other_sparse_to_dense_form": other_form,
             "gpu_launches": int(launches),
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
                          "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": traffic,

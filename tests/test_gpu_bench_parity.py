@@ -179,15 +179,16 @@ def test_real_kitti_frame_whole_chain_against_reference_golden(cuda_device):
 
 
 def test_never_materialised_grid_is_bit_identical_to_the_resident_grid(cuda_device, car_case):
-    """the default front end keeps (K,128) bf16 rows + the voxelizer's occupancy index and the first
-    conv layer fills its operand boxes from them (vn_voxelize_svfe_rows / vn_conv3d_bn_relu_fwd_rows); no (B,10,400,352,128)
+    """with materialise_grid=False (the default policy picks it whenever the grid exceeds its memory
+    budget) the front end keeps (K,128) bf16 rows + the voxelizer's occupancy index and the first conv layer fills its
+    operand boxes from them (vn_voxelize_svfe_rows / vn_conv3d_bn_relu_fwd_rows); no (B,10,400,352,128)
     tensor exists.  Same bits as the round-1 form that scatters into a resident grid, over the sequence A, B, A, with
     live-box skipping on and off, and when the voxel capacity clamps the batch."""
     import voxelnet_pytorch_b200 as vn
 
     sd, sets, want, _ = car_case
     fnet, mnet = _nets(cuda_device, sd)
-    fe_rows = vn.VoxelNetFrontEnd(fnet, mnet, "Car")
+    fe_rows = vn.VoxelNetFrontEnd(fnet, mnet, "Car", materialise_grid=False)
     fe_grid = vn.VoxelNetFrontEnd(fnet, mnet, "Car", materialise_grid=True)
     for step, b in enumerate((0, 1, 0)):
         a = fe_rows.forward_frames(sets[b])
@@ -199,10 +200,51 @@ def test_never_materialised_grid_is_bit_identical_to_the_resident_grid(cuda_devi
     assert mem_rows["total"] < mem_grid["total"] - 1_000_000_000
     del fe_grid
     # every box live (no flag table): the filling warps see mostly empty boxes
-    a = vn.VoxelNetFrontEnd(fnet, mnet, "Car", skip_empty_boxes=False).forward_frames(sets[0][:2]).clone()
+    a = vn.VoxelNetFrontEnd(fnet, mnet, "Car", skip_empty_boxes=False, materialise_grid=False).forward_frames(sets[0][:2]).clone()
     b = vn.VoxelNetFrontEnd(fnet, mnet, "Car", skip_empty_boxes=False, materialise_grid=True).forward_frames(sets[0][:2])
     assert torch.equal(a, b)
     # capacity clamp: voxel rows beyond the capacity do not exist in either form
-    a = vn.VoxelNetFrontEnd(fnet, mnet, "Car", voxels_per_frame_capacity=3000).forward_frames(sets[1]).clone()
+    a = vn.VoxelNetFrontEnd(fnet, mnet, "Car", voxels_per_frame_capacity=3000, materialise_grid=False).forward_frames(sets[1]).clone()
     b = vn.VoxelNetFrontEnd(fnet, mnet, "Car", voxels_per_frame_capacity=3000, materialise_grid=True).forward_frames(sets[1])
     assert torch.equal(a, b) and not torch.equal(a, want[1])
+
+
+def test_row_table_front_end_under_graph_replay_and_host_stream(cuda_device, car_case):
+    """The never-materialised form driven the way the bench drives the default: CUDA-graph replays over A, B, A and a
+    HostFrameStream over two front ends in flight fed by per-frame page-locked arrays (vn_upload_frames)."""
+    import voxelnet_pytorch_b200 as vn
+
+    sd, sets, want, counts = car_case
+    fnet, mnet = _nets(cuda_device, sd)
+    fe = vn.VoxelNetFrontEnd(fnet, mnet, "Car", materialise_grid=False)
+    packed = [vn.pack_frames(fr) for fr in sets]
+    fe.reserve(4, max(p[0].shape[0] for p in packed))
+    graphs = [fe.capture_graph(*p) for p in packed]
+    for step, b in enumerate((0, 1, 0, 0, 1)):
+        graphs[b].replay()
+        torch.cuda.synchronize()
+        _check(fe.out, want[b], "row-table graph replay step %d" % step)
+    assert fe.dense is None
+
+    def pinned(fr):
+        out = []
+        for f in fr:
+            a = vn.pinned_frame(f.shape[0])
+            a[...] = f
+            out.append(a)
+        return out
+
+    P = 2
+    fes = [vn.VoxelNetFrontEnd(fnet, mnet, "Car", materialise_grid=False) for _ in range(P)]
+    stream = vn.HostFrameStream(fes, 4, max(sum(len(f) for f in fr) for fr in sets), cuda_graphs=True)
+    host = [pinned(fr) for fr in sets]
+    n = 16
+    order = [(i // P + i % P) % 2 for i in range(n)]
+    for j in range(P):
+        stream.upload_frames(host[order[j]])
+    for i in range(n):
+        if i + P < n:
+            stream.upload_frames(host[order[i + P]])
+        out = stream.forward()
+        _check(out, want[order[i]], "row-table stream step %d" % i)
+        assert list(np.diff(stream.voxel_counts_host().numpy())) == counts[order[i]]

@@ -39,12 +39,16 @@ def test_front_end_matches_oracle_ped(cuda_device):
     dense2 = OM.feature_learning_net([torch.from_numpy(f) for f in feats2], [torch.from_numpy(c) for c in coords2], sd, "Pedestrian")
     want2 = OM.middle_layers(dense2, sd)
     assert rel_max_err(got2, want2) < 1e-2
-    assert fe.dense is None and fe.rows is not None  # default: the (B,D,H,W,128) tensor is never materialised
-    # the round-1 form (resident grid) gives the same bits and leaves its grid zero
-    fe_grid = _build(cuda_device, "Pedestrian", sd, materialise_grid=True)
-    assert torch.equal(fe_grid.forward_frames(frames).cpu(), got)
-    assert torch.equal(fe_grid.forward_frames(frames2).cpu(), got2)
-    assert int(fe_grid.dense.view(torch.int16).ne(0).sum()) == 0
+    # default policy: a grid this small is materialised (resident, re-zeroed by the step itself) ...
+    assert fe.materialise_grid and fe.rows is None and int(fe.dense.view(torch.int16).ne(0).sum()) == 0
+    # ... the never-materialised form (row table + occupancy index) gives the same bits
+    fe_rows = _build(cuda_device, "Pedestrian", sd, materialise_grid=False)
+    assert torch.equal(fe_rows.forward_frames(frames).cpu(), got)
+    assert torch.equal(fe_rows.forward_frames(frames2).cpu(), got2)
+    assert fe_rows.dense is None and fe_rows.rows is not None
+    # and it is what the default policy picks when the grid would not fit the budget
+    fe_auto = _build(cuda_device, "Pedestrian", sd, grid_budget_bytes=1 << 20)
+    assert torch.equal(fe_auto.forward_frames(frames2).cpu(), got2) and fe_auto.dense is None
 
 
 def test_front_end_matches_oracle_car(cuda_device):

@@ -66,7 +66,8 @@ _NO_SPAN = _NoSpan()
 class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
                  voxels_per_frame_capacity: int = 49152, fuse_voxel_features: bool = True,
-                 skip_empty_boxes: bool = True, resident_outputs: bool = True, materialise_grid: bool = False):
+                 skip_empty_boxes: bool = True, resident_outputs: bool = True, materialise_grid=None,
+                 grid_budget_bytes: int = 8 << 30):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
         self.cfg = grid_config(target)
@@ -75,13 +76,19 @@ class VoxelNetFrontEnd:
         # True: the (K,T,7) feature buffer is never materialised (vn_voxelize_svfe_fused);
         # False: voxel dict written then read back by the SVFE kernel (the reference's data flow)
         self.fuse_voxel_features = bool(fuse_voxel_features)
-        # False (default, eval fast path): the (B,D,H,W,128) tensor of model.py:102-106 is never materialised.  The SVFE
-        # kernel writes a compact (K,128) bf16 row table and the first conv layer builds its operand boxes from it
-        # through the voxelizer's occupancy index (vn_voxelize_svfe_rows / vn_conv3d_bn_relu_fwd_rows).  True: the
-        # round-1 form - a resident, zero-between-steps bf16 grid (5.8 GB at Car batch 16) that is written at the K
-        # occupied cells, read by TMA and re-zeroed.  Bit-identical outputs.  The voxel-dict data flow
-        # (fuse_voxel_features=False) and the training step always use the grid (allocated on first use).
-        self.materialise_grid = bool(materialise_grid) or not self.fuse_voxel_features
+        # The sparse -> dense step (model.py:102-106) of the eval fast path has two bit-identical forms:
+        #   False: the (B,D,H,W,128) tensor is NEVER materialised.  The SVFE kernel writes a compact (K,128) bf16 row
+        #          table and the first conv layer builds its operand boxes from it through the voxelizer's occupancy
+        #          index (vn_voxelize_svfe_rows / vn_conv3d_bn_relu_fwd_rows): 0.2 GB instead of 5.8 GB at Car batch 16,
+        #          0.30 instead of 1.04 GB of DRAM traffic in conv-1, no scatter / re-zero pass - but conv-1 itself is
+        #          ~25 % slower (boxes built by warps instead of one TMA each).
+        #   True:  a resident, zero-between-steps bf16 grid that is written at the K occupied cells, read by TMA and
+        #          re-zeroed (the round-1 form; ~3 % more frames/s at Car batch 16).
+        #   None (default): the grid if it fits `grid_budget_bytes` (8 GiB: Car up to 22 frames per batch), else rows.
+        # The voxel-dict data flow (fuse_voxel_features=False) and the training step always use the grid.
+        self._grid_request = None if materialise_grid is None else bool(materialise_grid)
+        self.grid_budget_bytes = int(grid_budget_bytes)
+        self.materialise_grid = True if not self.fuse_voxel_features else self._grid_request  # None until the batch size is known
         # True: the middle layers skip input boxes that hold only background.  conv-1's input is the
         # ~99 % empty voxel grid (exact skip); conv-2/3 then read their inputs as deviations from the
         # constant the previous layer outputs over empty space, which are zero wherever no voxel is in
@@ -179,6 +186,10 @@ class VoxelNetFrontEnd:
         self.voxelwise = torch.empty((0 if self.fuse_voxel_features else cap, 128), dtype=torch.float32, device=device)
         self.dense = None
         self.rows = None
+        if not self.fuse_voxel_features:
+            self.materialise_grid = True
+        elif self._grid_request is None:
+            self.materialise_grid = B * D * H * W * 128 * 2 <= self.grid_budget_bytes
         if self.materialise_grid:
             self._ensure_dense(device)
         else:
