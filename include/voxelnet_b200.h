@@ -216,6 +216,8 @@ size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W);
 #define VN_CONV_FLAGS_CONSUME 1     /* reset every flag that was read, leaving the table all-zero again */
 #define VN_CONV_FLAGS_BORDER_RING 2 /* also treat boxes that contain an H/W border position as live    */
 #define VN_CONV_FLAGS_PLANNED 4     /* the work plan in `workspace` was built by vn_conv3d_plan already    */
+#define VN_CONV_FLAGS_REVERSE 8     /* walk the plan last group first (same result; use it on every other layer of a
+                                       chain: the blocks the previous layer wrote last are still in L2)          */
 
 /* x: [B, Din, H, W, cin] bf16 (NDHWC).  cin in {64, 128}, cout = 64, kernel 3x3x3, H/W stride 1 and
  * padding 1; depth stride/padding (stride_d, pad_d) in {(2,1), (1,0)}; Din <= 10, W % 8 == 0.

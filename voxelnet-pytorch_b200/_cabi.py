@@ -18,6 +18,7 @@ VN_ABI_VERSION = 13
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 VN_CONV_FLAGS_PLANNED = 4
+VN_CONV_FLAGS_REVERSE = 8
 
 
 class VnGrid(C.Structure):

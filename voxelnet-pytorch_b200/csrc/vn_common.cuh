@@ -92,6 +92,11 @@ __device__ __forceinline__ void st_global_v8(void* p, const uint32_t (&v)[8]) {
                : "memory");
 }
 
+// Streaming (evict-first) scalar store.
+__device__ __forceinline__ void st_global_cs_f32(float* p, float v) {
+  asm volatile("st.global.cs.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
 __device__ __forceinline__ uint4 lds_u4(const void* p) {
   uint4 v;
   asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(smem_u32(p)) : "memory");

@@ -100,6 +100,7 @@ struct ConvParams {
   const uint8_t* wpack;
   const float* scale;   // [64]
   const float* table;   // [nvar][Dout][64] (or [64] when table_plain)
+  int reverse;          // take the groups of the plan last to first (VN_CONV_FLAGS_REVERSE)
   int table_plain;      // table is a plain [64] shift vector used for every row
   const float* sub;     // [Dout][64] subtracted after the ReLU, or nullptr
   void* out;
@@ -402,6 +403,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     if (lane == 0) g_raw = atomicAdd(&P.hdr->next_group, 1);
     int g = __shfl_sync(0xffffffffu, g_raw, 0);
     if (g >= n_groups) g = -1;
+    else if (P.reverse) g = n_groups - 1 - g;  // groups in the opposite order of the layer that wrote the input: its last blocks are still in L2
     GroupDesc gd = GroupDesc{0, 0};
     TilePlan tp = TilePlan{0u, 0, 0, 0, 0};
     if (g >= 0) {
@@ -429,6 +431,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
         if (lane == 0) g_raw = atomicAdd(&P.hdr->next_group, 1);
         g_next = __shfl_sync(0xffffffffu, g_raw, 0);
         if (g_next >= n_groups) g_next = -1;
+        else if (P.reverse) g_next = n_groups - 1 - g_next;
         if (g_next >= 0) {
           gd_next = P.groups[g_next];
           if (lane < kMaxGroupTiles) tp_next = P.gtiles[(size_t)g_next * kMaxGroupTiles + lane];
@@ -949,7 +952,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
               float* dst = reinterpret_cast<float*>(P.out) +
                            ((size_t)b * 64 * P.Dout + (size_t)(half * 32) * P.Dout + dout) * plane + (size_t)h * P.W + w;
 #pragma unroll
-              for (int j = 0; j < 32; ++j) dst[(size_t)j * P.Dout * plane] = v[j];
+              for (int j = 0; j < 32; ++j) st_global_cs_f32(dst + (size_t)j * P.Dout * plane, v[j]);  // written once, read by another kernel: do not displace the input boxes in L2
             }
           }
         }
@@ -1428,6 +1431,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   P.scale = scale;
   P.table = shift_table;
   P.table_plain = n_variants == 0 ? 1 : 0;
+  P.reverse = (flag_opts & VN_CONV_FLAGS_REVERSE) ? 1 : 0;
   P.sub = sub;
   P.out = y;
   P.hdr = hdr; P.groups = groups; P.tiles = tiles; P.gtiles = gtiles;

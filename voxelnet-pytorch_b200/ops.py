@@ -346,7 +346,7 @@ def conv3d_plan(B: int, Din: int, H: int, W: int, stride_d: int, pad_d: int, box
 
 def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int, final: bool = False, out=None,
                        box_flags=None, consume_flags: bool = False, border_ring: bool = False, sub=None, workspace=None,
-                       out_state=None, planned: bool = False):
+                       out_state=None, planned: bool = False, reverse: bool = False):
     """x (B,Din,H,W,cin) bf16 NDHWC -> (B,Dout,H,W,64) bf16, or with final=True the reference's
     reshaped (B, 64*Dout, H, W) f32 (model.py:262).
 
@@ -387,6 +387,8 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
     opts = (_cabi.VN_CONV_FLAGS_CONSUME if consume_flags else 0) | (_cabi.VN_CONV_FLAGS_BORDER_RING if border_ring else 0)
     if planned:
         opts |= _cabi.VN_CONV_FLAGS_PLANNED
+    if reverse:  # walk the plan last group first (same bits): the blocks the previous layer wrote last are still in L2
+        opts |= _cabi.VN_CONV_FLAGS_REVERSE
     with torch.cuda.device(x.device):
         check(
             _cabi.lib().vn_conv3d_bn_relu_fwd(

@@ -340,7 +340,7 @@ class VoxelNetFrontEnd:
                     ev[3].record(aux)
             if not early:
                 main.wait_event(ev[1])
-            ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
+            ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1, reverse=True,
                                    consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
             ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
                                    consume_flags=True, border_ring=True, workspace=ws2, out_state=st2, planned=True)
@@ -358,7 +358,7 @@ class VoxelNetFrontEnd:
             with span("unscatter"):
                 clear_grid()
             with span("conv2"):
-                ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1,
+                ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1, reverse=True,
                                        consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
             with span("conv3"):  # conv-2's zero padding makes its output deviate along the H/W border
                 ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
