@@ -751,7 +751,7 @@ def main():
                        "l2_policy": "working set (%.2f GB of activations, outputs and row tables per front end) exceeds L2" % (fe.device_bytes()["total"] / 1e9),
                        "device_bytes_per_front_end": fe.device_bytes(),
                        "grid": "never materialised: (K,128) bf16 rows + the voxelizer's occupancy index feed conv-1 (vn_conv3d_bn_relu_fwd_rows)" if fe.dense is None
-                               else "resident bf16 grid (default policy: it fits the 8 GiB budget); --grid rows times the never-materialised form",
+                               else "resident bf16 grid (default policy: it fits the 16 GiB budget); --grid rows times the never-materialised form",
                        "vfe": "fp32", "conv": "bf16 operands, fp32 accumulate (tcgen05)",
                        "launch": launch_mode,
                        "in_flight": "%d step(s) in flight per GPU (%s); ms_per_step = timed region / steps" % (

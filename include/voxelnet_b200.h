@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 13
+#define VN_ABI_VERSION 14
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -229,9 +229,10 @@ size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W);
  * shift_table / n_variants: n_variants 0: a plain [64] vector (BatchNorm shift with the conv bias
  *   folded in) - the drop-in case.  n_variants 1: [Dout][64].  n_variants 9: [3][3][Dout][64] from
  *   vn_conv3d_fold_background, indexed by (h class, w class) of the output position
- *   (0 interior, 1 first row/column, 2 last row/column).
- * sub (optional): [Dout][64] subtracted after the ReLU - the layer's own background, so that the
- *   output is stored as a deviation that is exactly zero wherever the input was all background.
+ *   (0 interior, 1 first row/column, 2 last row/column).  n_variants 25: [5][5][Dout][64] (see
+ *   vn_conv3d_fold_background with bg_classes 9).
+ * sub (optional): [Dout][64] - or [3][3][Dout][64] when n_variants is 9 - subtracted after the ReLU: the layer's own
+ *   background, so that the output is stored as a deviation that is exactly zero wherever the input was all background.
  * box_flags (optional): flag[b][p][th][tw][kw] == 0 asserts that the input box
  *   x[b, p, 16*th-1 .. 16*th+16, 8*tw+kw-1 .. 8*tw+kw+6, :] is all zeros; its load and its MMAs are
  *   skipped (exact: zero operands contribute nothing).  NULL: every box is live.  flag_opts: VN_CONV_FLAGS_*.
@@ -268,16 +269,21 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
                                uint8_t* out_state, void* workspace, size_t workspace_bytes,
                                vn_stream_t stream);
 
-/* Background folding for a layer whose INPUT is stored as a deviation from a per-(plane, channel)
- * background bg_in [Din][cin] f32 (the previous layer's `sub`; NULL = zero background).  The
- * reference zero-pads, so out-of-image taps see 0 rather than the background: the constant the
- * background contributes depends on the output depth and on the border class of the output
- * position.  Writes shift_table [3][3][Dout][64] (= bias*scale + shift, for n_variants 9) and, if
- * bg_out is not NULL, the layer's own output background bg_out [Dout][64] = relu(interior row).
+/* Background folding for a layer whose INPUT is stored as a deviation from a background (what the previous
+ * layer outputs wherever ITS input was all background; NULL = zero background).  The reference zero-pads, so
+ * out-of-image taps see 0 rather than the background: the constant the background contributes to an output depends on
+ * the output depth and on the border class of the output position.
+ *   bg_classes 1: bg_in [Din][cin], the same at every position.  Writes shift_table [3][3][Dout][64] (= bias*scale +
+ *     shift, for n_variants 9; classes: 0 interior, 1 first, 2 last row / column) and, if bg_out is not NULL, the
+ *     layer's own output background per class bg_out [3][3][Dout][64] = relu(shift_table) - pass it as `sub`
+ *     (n_variants 9) so that the stored deviation is exactly zero wherever no voxel is in reach, borders included.
+ *   bg_classes 9: bg_in [3][3][Din][cin] is such a per-class background.  Writes shift_table [5][5][Dout][64] (for
+ *     n_variants 25; classes 3 / 4: second / last but one row or column, which still see the border row of the input);
+ *     bg_out must be NULL.
  * weight is the torch-layout fp32 tensor; it is rounded to bf16 exactly as the packed image is. */
 int vn_conv3d_fold_background(const float* weight, int32_t cin, int32_t Din, int32_t stride_d,
                               int32_t pad_d, const float* scale, const float* shift,
-                              const float* bg_in, float* shift_table, float* bg_out,
+                              const float* bg_in, int32_t bg_classes, float* shift_table, float* bg_out,
                               vn_stream_t stream);
 
 /* Live-box flags for a chain of n_layers (<= 3) stacked middle layers from the voxel coordinates

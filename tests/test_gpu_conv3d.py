@@ -238,14 +238,20 @@ def test_background_delta_chain_matches_dense_chain(cuda_device, density, H, W):
     net = net.to(cuda_device)
     plain = net(dense).cpu()
 
+    # layer 1: zero background in, one output background; layer 2: per-border-class output background (9 classes)
+    # subtracted on store; layer 3: 5 x 5-variant shift table - no layer treats the border ring as live
     x, bg, din = dense, None, D
     for i, layer in enumerate(net.middle_layer):
         packed, scale, shift = layer.folded()
         table, bg_out = ops.conv3d_fold_background(layer.conv.weight, din, layer.stride[0], layer.padding[0], scale, shift, bg)
-        last = i == 2
-        x = ops.conv3d_bn_relu_fwd(x, packed, scale, table if i else shift, layer.stride[0], layer.padding[0], final=last,
-                                   box_flags=flags[i], consume_flags=True, border_ring=last, sub=None if last else bg_out)
-        din, bg = bg_out.shape[0], bg_out
+        assert tuple(table.shape[:2]) == ((3, 3) if i < 2 else (5, 5)) and (bg_out is None) == (i == 2)
+        sub = [bg_out[0, 0].contiguous(), bg_out, None][i] if i < 2 else None
+        if i == 0:
+            assert all(torch.equal(bg_out[a, b], bg_out[0, 0]) for a in range(3) for b in range(3))
+        x = ops.conv3d_bn_relu_fwd(x, packed, scale, table if i else shift, layer.stride[0], layer.padding[0], final=i == 2,
+                                   box_flags=flags[i], consume_flags=True, sub=sub)
+        if i < 2:
+            din, bg = sub.shape[-2], sub
     sparse = x.cpu()
     assert all(int(f.sum()) == 0 for f in flags)
     want = OM.middle_layers(dense.float().cpu(), sd)

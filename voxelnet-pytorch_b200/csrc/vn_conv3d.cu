@@ -96,7 +96,9 @@ struct ConvParams {
   int nchunk;      // Cin / 64
   int tiles_h, tiles_w, n_tiles;
   int out_mode;    // 0: bf16 NDHWC, 1: f32 [B, 64*Dout, H, W] with channel = c*Dout + d
-  int nvar;        // 1: shift rows [Dout][64]; 9: [3 h-classes][3 w-classes][Dout][64]
+  int nvar;        // 1: shift rows [Dout][64]; 9: [3 h-classes][3 w-classes][Dout][64]; 25: [5][5][Dout][64]
+  int table_smem;  // every table row is in shared memory (else only the interior variant: border rows come from global memory)
+  int sub_classes; // 1: sub [Dout][64]; 9: sub [3][3][Dout][64] indexed like the 9-variant shift table
   const uint8_t* wpack;
   const float* scale;   // [64]
   const float* table;   // [nvar][Dout][64] (or [64] when table_plain)
@@ -364,7 +366,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     const int t = threadIdx.x - 64;  // 0..255
     if (t < 64) ctl->scale[t] = P.scale[t];
     if (kTrain && t < 128) ctl_stat(ctl)[t] = 0.0;
-    const int nrow = P.nvar * P.Dout;
+    const int nrow = (P.table_smem ? P.nvar : 1) * P.Dout;
     for (int i = t; i < nrow * 64; i += 256) ctl->table[i] = P.table_plain ? P.table[i & 63] : P.table[i];
     for (int i = t; i < P.Dout * 64; i += 256) ctl->sub[i] = P.sub != nullptr ? P.sub[i] : 0.0f;
     if (t < kSlots) {  // does the interior shift row of depth t cancel against `sub` exactly?
@@ -873,9 +875,10 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
       const int tw0 = gd.tw0, th = gd.th, b = gd.b;
       const int h = th * kTileH + hl;
       const bool inside = h < P.H;
-      const int vh = h == 0 ? 1 : (h == P.H - 1 ? 2 : 0);
-      // tile rows 1..H-2 only, all of them inside the image: every position is of the interior class
-      const bool rows_interior = th > 0 && (th + 1) * kTileH < P.H;
+      // border class of the output row: 0 interior, 1 first, 2 last (and with 25 variants 3 second, 4 last but one)
+      const int vh = h == 0 ? 1 : (h == P.H - 1 ? 2 : (P.nvar == 25 ? (h == 1 ? 3 : (h == P.H - 2 ? 4 : 0)) : 0));
+      // tile rows 1..H-2 (2..H-3) only, all of them inside the image: every position is of the interior class
+      const bool rows_interior = th > 0 && (th + 1) * kTileH + (P.nvar == 25 ? 1 : 0) < P.H;
       uint32_t used = 0;
       for (int t = 0; t < gd.ntiles; ++t) {
         const TilePlan tp = ctl->sched_tiles[ss][t];
@@ -883,8 +886,8 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
         used |= ((1u << tp.nslots) - 1u) << tp.slot0;
         const int tw = tw0 + t;
         const int w = tw * kTileW + wl;
-        const int vw = w == 0 ? 1 : (w == P.W - 1 ? 2 : 0);
-        const int variant = P.nvar == 9 ? vh * 3 + vw : 0;
+        const int vw = w == 0 ? 1 : (w == P.W - 1 ? 2 : (P.nvar == 25 ? (w == 1 ? 3 : (w == P.W - 2 ? 4 : 0)) : 0));
+        const int variant = P.nvar == 9 ? vh * 3 + vw : (P.nvar == 25 ? vh * 5 + vw : 0);
         const bool tile_interior = P.nvar == 1 ? (th + 1) * kTileH <= P.H : (rows_interior && tw > 0 && tw < P.tiles_w - 1);
         for (int dout = 0; dout < P.Dout; ++dout) {
           const bool has_acc = (touched >> dout) & 1;  // else: no live box reached this accumulator
@@ -919,8 +922,10 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
             for (int j = 0; j < 32; ++j) r[j] = 0u;
           }
           if (inside && !no_store) {
-            const float* shift_row = ctl->table + (variant * P.Dout + dout) * 64 + half * 32;
-            const float* sub_row = ctl->sub + dout * 64 + half * 32;
+            const float* shift_row = (variant == 0 || P.table_smem) ? ctl->table + (variant * P.Dout + dout) * 64 + half * 32
+                                                                    : P.table + (variant * P.Dout + dout) * 64 + half * 32;
+            const float* sub_row = (variant == 0 || P.sub_classes == 1) ? ctl->sub + dout * 64 + half * 32
+                                                                         : P.sub + (variant * P.Dout + dout) * 64 + half * 32;
             float v[32];
             if (kTrain) {
 #pragma unroll
@@ -1042,26 +1047,35 @@ __global__ void __launch_bounds__(256)
 // the background): 3 h-classes (interior, h = 0, h = H-1) x 3 w-classes.  This kernel evaluates
 //   bias[v][d'][n] = sum over in-image taps (kd, kh, kw), channels c of bf16(W[n][c][kd][kh][kw]) * bg_in[p][c]
 // and writes the epilogue's shift table  table[v][d'][n] = bias * scale[n] + shift[n]  plus the layer's
-// own output background  bg_out[d'][n] = relu(table[interior][d'][n]).
+// own output background per border class  bg_out[v][d'][n] = relu(table[v][d'][n]).
 // One block per (variant, d'), one thread per output channel.
 __global__ void __launch_bounds__(64)
     k_fold_background(const float* __restrict__ w, int cin, int Din, int Dout, int stride_d, int pad_d,
                       const float* __restrict__ scale, const float* __restrict__ shift,
-                      const float* __restrict__ bg_in, float* __restrict__ table, float* __restrict__ bg_out) {
+                      const float* __restrict__ bg_in, int bg_classes, float* __restrict__ table, float* __restrict__ bg_out) {
+  // bg_classes 1: bg_in [Din][cin], the same at every position -> 3 x 3 output variants (interior / first / last row, column).
+  // bg_classes 9: bg_in [3][3][Din][cin] by the border class of the INPUT position (what a layer with 3 x 3 variants
+  //               outputs over empty space) -> 5 x 5 output variants: interior, first, last, second, last but one row
+  //               (column) - an output in row 1 still sees input row 0, whose background is the "first row" one.
+  const int nv = bg_classes == 9 ? 5 : 3;
   const int v = blockIdx.x / Dout, d = blockIdx.x % Dout, n = threadIdx.x;
-  const int vh = v / 3, vw = v % 3;
+  const int vh = v / nv, vw = v % nv;
   double acc = 0.0;
   if (bg_in != nullptr) {
     for (int kd = 0; kd < 3; ++kd) {
       const int p = d * stride_d - pad_d + kd;
       if (p < 0 || p >= Din) continue;
       for (int kh = 0; kh < 3; ++kh) {
-        if ((vh == 1 && kh == 0) || (vh == 2 && kh == 2)) continue;
+        if ((vh == 1 && kh == 0) || (vh == 2 && kh == 2)) continue;  // tap outside the image
+        // border class of the input row this tap reads: output row 0 / 1 read input row 0 with kh = 1 / 0, ...
+        const int ch = ((vh == 1 && kh == 1) || (vh == 3 && kh == 0)) ? 1 : (((vh == 2 && kh == 1) || (vh == 4 && kh == 2)) ? 2 : 0);
         for (int kw = 0; kw < 3; ++kw) {
           if ((vw == 1 && kw == 0) || (vw == 2 && kw == 2)) continue;
+          const int cw = ((vw == 1 && kw == 1) || (vw == 3 && kw == 0)) ? 1 : (((vw == 2 && kw == 1) || (vw == 4 && kw == 2)) ? 2 : 0);
+          const float* bg = bg_in + (bg_classes == 9 ? (size_t)(ch * 3 + cw) * Din * cin : 0);
           for (int c = 0; c < cin; ++c) {
             const float wv = __bfloat162float(__float2bfloat16_rn(w[((((size_t)n * cin + c) * 3 + kd) * 3 + kh) * 3 + kw]));
-            acc += (double)wv * (double)bg_in[p * cin + c];
+            acc += (double)wv * (double)bg[p * cin + c];
           }
         }
       }
@@ -1069,7 +1083,7 @@ __global__ void __launch_bounds__(64)
   }
   const float t = (float)(acc * (double)scale[n] + (double)shift[n]);
   table[((size_t)v * Dout + d) * 64 + n] = t;
-  if (v == 0 && bg_out != nullptr) bg_out[d * 64 + n] = fmaxf(t, 0.0f);
+  if (bg_out != nullptr) bg_out[((size_t)v * Dout + d) * 64 + n] = fmaxf(t, 0.0f);  // (3 x 3 variants only: checked by the host)
 }
 
 // Voxel coordinates -> live-box flags of a chain of up to three stacked 3x3x3 layers.  A voxel at
@@ -1277,17 +1291,20 @@ int vn_conv3d_pack_weights(const float* weight, int32_t cin, int32_t stride_d, v
 }
 
 int vn_conv3d_fold_background(const float* weight, int32_t cin, int32_t Din, int32_t stride_d, int32_t pad_d,
-                              const float* scale, const float* shift, const float* bg_in, float* shift_table,
-                              float* bg_out, vn_stream_t stream) {
+                              const float* scale, const float* shift, const float* bg_in, int32_t bg_classes,
+                              float* shift_table, float* bg_out, vn_stream_t stream) {
   VN_REQUIRE(weight && scale && shift && shift_table, "conv3d_fold_background: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d_fold_background: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d_fold_background: stride_d=%d pad_d=%d",
              stride_d, pad_d);
   VN_REQUIRE(Din >= 1 && Din <= kMaxPlanes && Din + 2 * pad_d >= 3, "conv3d_fold_background: Din=%d", Din);
+  VN_REQUIRE(bg_classes == 1 || (bg_classes == 9 && bg_in != nullptr && bg_out == nullptr),
+             "conv3d_fold_background: bg_classes=%d (1, or 9 with bg_in and without bg_out)", bg_classes);
   const int Dout = out_depth(Din, stride_d, pad_d);
   VN_REQUIRE(Dout >= 1 && Dout <= kSlots, "conv3d_fold_background: Dout=%d outside [1,%d]", Dout, kSlots);
-  k_fold_background<<<9 * Dout, 64, 0, as_stream(stream)>>>(weight, cin, Din, Dout, stride_d, pad_d, scale, shift, bg_in,
-                                                            shift_table, bg_out);
+  const int nv = bg_classes == 9 ? 25 : 9;
+  k_fold_background<<<nv * Dout, 64, 0, as_stream(stream)>>>(weight, cin, Din, Dout, stride_d, pad_d, scale, shift, bg_in,
+                                                             bg_classes, shift_table, bg_out);
   VN_LAUNCH_CHECK("k_fold_background");
   return VN_OK;
 }
@@ -1357,11 +1374,10 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   const int Dout = transposed_dout > 0 ? transposed_dout : out_depth(Din, stride_d, pad_d);
   VN_REQUIRE((transposed_dout > 0 || Din + 2 * pad_d >= 3) && Dout >= 1 && Dout <= kSlots, "conv3d: Dout=%d outside [1,%d]",
              Dout, kSlots);
-  VN_REQUIRE(n_variants == 0 || n_variants == 1 || n_variants == 9, "conv3d: n_variants=%d (0: plain [64] shift, 1, 9)",
-             n_variants);
-  const int nvar = n_variants == 9 ? 9 : 1;
-  VN_REQUIRE(nvar * Dout <= kMaxTableRows, "conv3d: shift table of %d x %d rows exceeds %d", nvar, Dout, kMaxTableRows);
-  VN_REQUIRE(nvar == 1 || H >= 2, "conv3d: border variants need H >= 2");
+  VN_REQUIRE(n_variants == 0 || n_variants == 1 || n_variants == 9 || n_variants == 25,
+             "conv3d: n_variants=%d (0: plain [64] shift, 1, 9, 25)", n_variants);
+  const int nvar = n_variants == 9 ? 9 : (n_variants == 25 ? 25 : 1);
+  VN_REQUIRE(nvar == 1 || (H >= 5 && W >= 5), "conv3d: border variants need H, W >= 5");
   VN_REQUIRE((reinterpret_cast<uintptr_t>(gather ? gather->rows : x) & 15) == 0 && (reinterpret_cast<uintptr_t>(packed_weight) & 15) == 0 &&
                  (reinterpret_cast<uintptr_t>(y) & 15) == 0,
              "conv3d: buffers must be 16-byte aligned");
@@ -1427,6 +1443,8 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   P.tiles_h = tiles_h; P.tiles_w = tiles_w; P.n_tiles = (int)n_tiles;
   P.out_mode = out_mode;
   P.nvar = nvar;
+  P.table_smem = nvar * Dout <= kMaxTableRows ? 1 : 0;
+  P.sub_classes = (nvar == 9 && sub != nullptr) ? 9 : 1;
   P.wpack = reinterpret_cast<const uint8_t*>(packed_weight);
   P.scale = scale;
   P.table = shift_table;

@@ -312,21 +312,26 @@ def conv3d_mark_boxes(coords, B: int, D: int, H: int, W: int, layers, flags, n_v
         )
 
 
-def conv3d_fold_background(weight, din: int, stride_d: int, pad_d: int, scale, shift, bg_in=None):
-    """(shift_table (3,3,Dout,64) f32, bg_out (Dout,64) f32) for a layer whose input is stored as a
-    deviation from the background bg_in (Din,cin) f32 (None: zero) - see vn_conv3d_fold_background."""
+def conv3d_fold_background(weight, din: int, stride_d: int, pad_d: int, scale, shift, bg_in=None, want_bg_out: bool = True):
+    """Shift table (and output background) of a layer whose input is stored as a deviation from the background bg_in -
+    see vn_conv3d_fold_background.  bg_in None (zero) or (Din,cin): -> (shift_table (3,3,Dout,64), bg_out (3,3,Dout,64));
+    bg_in (3,3,Din,cin) (the bg_out of such a layer): -> (shift_table (5,5,Dout,64), None)."""
     _require_cuda(weight, scale, shift, bg_in)
     w = _contig(weight.detach(), torch.float32)
     cin = w.shape[1]
     dout = conv3d_out_depth(din, stride_d, pad_d)
-    if bg_in is not None and (tuple(bg_in.shape) != (din, cin) or bg_in.dtype != torch.float32 or not bg_in.is_contiguous()):
-        raise RuntimeError("bg_in must be a contiguous (Din, cin) float32 tensor")
-    table = torch.empty((3, 3, dout, 64), dtype=torch.float32, device=w.device)
-    bg_out = torch.empty((dout, 64), dtype=torch.float32, device=w.device)
+    classes = 1
+    if bg_in is not None:
+        if bg_in.dtype != torch.float32 or not bg_in.is_contiguous() or tuple(bg_in.shape) not in ((din, cin), (3, 3, din, cin)):
+            raise RuntimeError("bg_in must be a contiguous (Din, cin) or (3, 3, Din, cin) float32 tensor")
+        classes = 9 if bg_in.dim() == 4 else 1
+    nv = 5 if classes == 9 else 3
+    table = torch.empty((nv, nv, dout, 64), dtype=torch.float32, device=w.device)
+    bg_out = torch.empty((3, 3, dout, 64), dtype=torch.float32, device=w.device) if (want_bg_out and classes == 1) else None
     with torch.cuda.device(w.device):
         check(
             _cabi.lib().vn_conv3d_fold_background(_ptr(w), cin, din, stride_d, pad_d, _ptr(_contig(scale, torch.float32)),
-                                                  _ptr(_contig(shift, torch.float32)), _ptr(bg_in), _ptr(table), _ptr(bg_out),
+                                                  _ptr(_contig(shift, torch.float32)), _ptr(bg_in), classes, _ptr(table), _ptr(bg_out),
                                                   _stream()),
             "vn_conv3d_fold_background",
         )
@@ -373,10 +378,13 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
         n_variants = 1
     elif tuple(shift.shape) == (3, 3, Dout, 64):
         n_variants = 9
+    elif tuple(shift.shape) == (5, 5, Dout, 64):
+        n_variants = 25
     else:
-        raise RuntimeError("shift must have shape (64,), (Dout,64) or (3,3,Dout,64); got %s" % (tuple(shift.shape),))
-    if sub is not None and (tuple(sub.shape) != (Dout, 64) or sub.dtype != torch.float32 or not sub.is_contiguous()):
-        raise RuntimeError("sub must be a contiguous (Dout,64) float32 tensor")
+        raise RuntimeError("shift must have shape (64,), (Dout,64), (3,3,Dout,64) or (5,5,Dout,64); got %s" % (tuple(shift.shape),))
+    want_sub = (3, 3, Dout, 64) if n_variants == 9 else (Dout, 64)  # with a 9-variant table the background has 9 classes too
+    if sub is not None and (tuple(sub.shape) != want_sub or sub.dtype != torch.float32 or not sub.is_contiguous()):
+        raise RuntimeError("sub must be a contiguous %s float32 tensor (shift has %d variants); got %s" % (want_sub, n_variants, tuple(sub.shape)))
     if out is None:
         if final:
             out = torch.empty((B, 64 * Dout, H, W), dtype=torch.float32, device=x.device)

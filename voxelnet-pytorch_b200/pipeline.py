@@ -67,7 +67,7 @@ class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
                  voxels_per_frame_capacity: int = 49152, fuse_voxel_features: bool = True,
                  skip_empty_boxes: bool = True, resident_outputs: bool = True, materialise_grid=None,
-                 grid_budget_bytes: int = 8 << 30):
+                 grid_budget_bytes: int = 16 << 30):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
         self.cfg = grid_config(target)
@@ -84,7 +84,7 @@ class VoxelNetFrontEnd:
         #          ~25 % slower (boxes built by warps instead of one TMA each).
         #   True:  a resident, zero-between-steps bf16 grid that is written at the K occupied cells, read by TMA and
         #          re-zeroed (the round-1 form; ~3 % more frames/s at Car batch 16).
-        #   None (default): the grid if it fits `grid_budget_bytes` (8 GiB: Car up to 22 frames per batch), else rows.
+        #   None (default): the grid if it fits `grid_budget_bytes` (16 GiB: Car up to 44 frames per batch), else rows.
         # The voxel-dict data flow (fuse_voxel_features=False) and the training step always use the grid.
         self._grid_request = None if materialise_grid is None else bool(materialise_grid)
         self.grid_budget_bytes = int(grid_budget_bytes)
@@ -136,12 +136,23 @@ class VoxelNetFrontEnd:
         # layer's own output background (subtracted on store, so the stored deviation is sparse)
         self._tables, self._bg = [], []
         if self.skip_empty_boxes:
-            din, bg = self.cfg.depth, None
-            for layer, (_, scale, shift) in zip(self.middle_net.middle_layer, self._conv):
-                table, bg_out = ops.conv3d_fold_background(layer.conv.weight, din, layer.stride[0], layer.padding[0], scale, shift, bg)
-                self._tables.append(table)
-                self._bg.append(bg_out)
-                din, bg = bg_out.shape[0], bg_out
+            # layer 1 reads the zero grid: its output background relu(shift) is the same at every position.  Layer 2's own
+            # background depends on the border class of the position (the reference zero-pads), and so does what it subtracts
+            # on store: the stored deviation is exactly zero wherever no voxel is in reach, borders included, and layer 3 folds
+            # the per-class background of its input into a 5 x 5-variant shift table - no layer has to treat the H/W border
+            # ring as live.
+            layers = list(self.middle_net.middle_layer)
+            din = self.cfg.depth
+            t1, bg1 = ops.conv3d_fold_background(layers[0].conv.weight, din, layers[0].stride[0], layers[0].padding[0],
+                                                 self._conv[0][1], self._conv[0][2], None)
+            bg1 = bg1[0, 0].contiguous()                      # (D1, 64)
+            din = bg1.shape[0]
+            t2, bg2 = ops.conv3d_fold_background(layers[1].conv.weight, din, layers[1].stride[0], layers[1].padding[0],
+                                                 self._conv[1][1], self._conv[1][2], bg1)      # (3,3,D2,64) each
+            din = bg2.shape[2]
+            t3, _ = ops.conv3d_fold_background(layers[2].conv.weight, din, layers[2].stride[0], layers[2].padding[0],
+                                               self._conv[2][1], self._conv[2][2], bg2)        # (5,5,D3,64)
+            self._tables, self._bg = [t1, t2, t3], [bg1, bg2]
         if getattr(self, "out_states", None) is not None:
             for st in self.out_states:  # the constants the untouched blocks hold depend on the parameters
                 st.fill_(0xFF)
@@ -267,7 +278,7 @@ class VoxelNetFrontEnd:
                 ops.conv3d_plan(B_, self.act1.shape[1], H_, W_, 1, 0, self.box_flags[1], self.conv_workspaces[1],
                                 consume_flags=True, out_state=st_[1])
                 ops.conv3d_plan(B_, self.act2.shape[1], H_, W_, 2, 1, self.box_flags[2], self.conv_workspaces[2],
-                                consume_flags=True, border_ring=True, out_state=st_[2])
+                                consume_flags=True, out_state=st_[2])
                 ev[1].record(aux)
             if use_rows:
                 ops.voxelize_svfe_rows(self.grid, points, frame_offsets, vb.voxel_offsets, self._p1, self._p2, self.rows,
@@ -329,7 +340,7 @@ class VoxelNetFrontEnd:
                 aux.wait_event(ev[0])
                 with torch.cuda.stream(aux):
                     ops.conv3d_plan(B, self.act1.shape[1], H, W, 1, 0, f1, ws1, consume_flags=True, out_state=st1)
-                    ops.conv3d_plan(B, self.act2.shape[1], H, W, 2, 1, f2, ws2, consume_flags=True, border_ring=True, out_state=st2)
+                    ops.conv3d_plan(B, self.act2.shape[1], H, W, 2, 1, f2, ws2, consume_flags=True, out_state=st2)
                     ev[1].record(aux)
             conv1(box_flags=f0, consume_flags=True, sub=self._bg[0], workspace=ws0, out_state=st0, planned=early)
             if not use_rows:
@@ -343,7 +354,7 @@ class VoxelNetFrontEnd:
             ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1, reverse=True,
                                    consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
             ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
-                                   consume_flags=True, border_ring=True, workspace=ws2, out_state=st2, planned=True)
+                                   consume_flags=True, workspace=ws2, out_state=st2, planned=True)
             if not use_rows:
                 main.wait_event(ev[3])  # join: the next step's grid writes come after the clear
         elif self.skip_empty_boxes:
@@ -352,7 +363,7 @@ class VoxelNetFrontEnd:
             with span("plan"):  # the three device-built work plans (in the overlapped order they run on the side stream)
                 ops.conv3d_plan(B_, self.cfg.depth, H_, W_, 2, 1, f0, ws0, consume_flags=True, out_state=st0)
                 ops.conv3d_plan(B_, self.act1.shape[1], H_, W_, 1, 0, f1, ws1, consume_flags=True, out_state=st1)
-                ops.conv3d_plan(B_, self.act2.shape[1], H_, W_, 2, 1, f2, ws2, consume_flags=True, border_ring=True, out_state=st2)
+                ops.conv3d_plan(B_, self.act2.shape[1], H_, W_, 2, 1, f2, ws2, consume_flags=True, out_state=st2)
             with span("conv1"):  # zero background in, deviation from relu(shift) out
                 conv1(box_flags=f0, consume_flags=True, sub=self._bg[0], workspace=ws0, out_state=st0, planned=True)
             with span("unscatter"):
@@ -360,9 +371,9 @@ class VoxelNetFrontEnd:
             with span("conv2"):
                 ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1, reverse=True,
                                        consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
-            with span("conv3"):  # conv-2's zero padding makes its output deviate along the H/W border
+            with span("conv3"):
                 ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
-                                       consume_flags=True, border_ring=True, workspace=ws2, out_state=st2, planned=True)
+                                       consume_flags=True, workspace=ws2, out_state=st2, planned=True)
         else:
             with span("conv1"):
                 conv1(workspace=ws0)
