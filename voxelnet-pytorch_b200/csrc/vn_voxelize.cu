@@ -26,6 +26,7 @@ namespace {
 constexpr uint32_t kInvalidKey = 0xFFFFFFFFu;
 constexpr int kCtrItems = 0, kCtrBigCount = 1, kCtrBigNext = 2;  // VoxWorkspace::counters slots
 constexpr int kMaxT = 64;  // smem staging rows per warp (T is 35 or 45)
+constexpr int kScanChunk = 1024;  // elements per block of the two-level scans (256 threads x 4)
 
 struct VoxWorkspace {
   uint32_t* bitmap;      // [n_frames * words]   occupancy bits, cell = (z*H + y)*W + x
@@ -38,6 +39,9 @@ struct VoxWorkspace {
   int32_t* seg;          // [n_points]           segment start of each voxel row in pidx
   int32_t* pidx;         // [n_points]           point indices bucketed per voxel
   int32_t* biglist;      // [n_points / (min(31,T)+1) + 1]  voxel rows with more than 31 (or more than T) points
+  uint32_t* wordpart;    // [n_frames * word_chunks]  popcount of each 1024-word chunk of the bitmap (two-level scan)
+  int32_t* segpart;      // [n_frames * seg_chunks]   points in each 1024-row chunk of a frame's voxel rows
+  size_t word_chunks, seg_chunks;
   size_t words;          // bitmap words per frame
   size_t zero_bytes;     // bitmap..cnt are contiguous: one fill
   size_t total_bytes;
@@ -66,6 +70,10 @@ __host__ VoxWorkspace carve(const vn_grid_t& g, int n_frames, int64_t n_points, 
   w.seg = reinterpret_cast<int32_t*>(take(np * 4));
   w.pidx = reinterpret_cast<int32_t*>(take(np * 4));
   w.biglist = reinterpret_cast<int32_t*>(take((np / (size_t)((g.T < 31 ? g.T : 31) + 1) + 1) * 4));
+  w.word_chunks = (w.words + kScanChunk - 1) / kScanChunk;
+  w.seg_chunks = ((cells < np ? cells : np) + kScanChunk - 1) / kScanChunk;  // a frame has at most min(cells, points) voxels
+  w.wordpart = reinterpret_cast<uint32_t*>(take((size_t)n_frames * w.word_chunks * 4));
+  w.segpart = reinterpret_cast<int32_t*>(take((size_t)n_frames * w.seg_chunks * 4));
   w.total_bytes = off;
   return w;
 }
@@ -124,40 +132,76 @@ __device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v, uint32_t lane) {
   return v;
 }
 
-// P2: one 1024-thread block per frame.  Each warp owns a contiguous, 32-word-aligned range.
-__global__ void __launch_bounds__(1024) k_vox_scan_words(const uint32_t* __restrict__ bitmap,
-                                                          uint32_t* __restrict__ wordprefix, size_t words,
-                                                          int32_t* __restrict__ frame_k) {
-  __shared__ uint32_t warp_total[32];
-  const int f = blockIdx.x;
+// Block-wide exclusive scan of one value per thread (256 threads); returns the prefix, *total = block sum.
+__device__ __forceinline__ uint32_t block_excl_scan_256(uint32_t v, uint32_t* total) {
+  __shared__ uint32_t warp_sum[8];
   const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  const uint32_t* bm = bitmap + (size_t)f * words;
-  uint32_t* wp = wordprefix + (size_t)f * words;
-  const size_t per_warp = align_up((words + 31) / 32, 32);
-  const size_t w0 = (size_t)warp * per_warp;
-  const size_t w1 = w0 + per_warp < words ? w0 + per_warp : words;
-
-  uint32_t sum = 0;
-  for (size_t w = w0 + lane; w < w1; w += 32) sum += __popc(bm[w]);
+  const uint32_t incl = warp_incl_scan(v, lane);
+  __syncthreads();  // (warp_sum may still be read from the previous call)
+  if (lane == 31) warp_sum[warp] = incl;
+  __syncthreads();
+  uint32_t base = 0, all = 0;
 #pragma unroll
-  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
-  if (lane == 0) warp_total[warp] = sum;
-  __syncthreads();
-  if (warp == 0) {
-    const uint32_t t = warp_total[lane];
-    const uint32_t incl = warp_incl_scan(t, lane);
-    warp_total[lane] = incl - t;
-    if (lane == 31) frame_k[f] = (int32_t)incl;
+  for (int i = 0; i < 8; ++i) {
+    const uint32_t t = warp_sum[i];
+    if (i < (int)warp) base += t;
+    all += t;
+  }
+  *total = all;
+  return base + incl - v;
+}
+
+// P2, two levels (a frame's 44,032 bitmap words used to be scanned by ONE block: 16 blocks on 148 SMs).
+// a: popcount of every 1024-word chunk.  b: chunk base = sum of the chunks before it, then the scan inside the chunk;
+// the block of a frame's last chunk also writes the frame's voxel count.
+__global__ void __launch_bounds__(256) k_vox_word_partials(const uint32_t* __restrict__ bitmap, size_t words, int chunks,
+                                                            uint32_t* __restrict__ wordpart) {
+  const int f = blockIdx.y, c = blockIdx.x;
+  const uint32_t* bm = bitmap + (size_t)f * words + (size_t)c * kScanChunk;
+  const size_t left = words - (size_t)c * kScanChunk;
+  uint32_t sum = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const size_t i = (size_t)threadIdx.x * 4 + j;
+    if (i < left) sum += __popc(bm[i]);
+  }
+  uint32_t total;
+  block_excl_scan_256(sum, &total);
+  if (threadIdx.x == 0) wordpart[(size_t)f * chunks + c] = total;
+}
+
+__global__ void __launch_bounds__(256) k_vox_word_scan(const uint32_t* __restrict__ bitmap, size_t words, int chunks,
+                                                        const uint32_t* __restrict__ wordpart,
+                                                        uint32_t* __restrict__ wordprefix, int32_t* __restrict__ frame_k) {
+  __shared__ uint32_t s_base;
+  const int f = blockIdx.y, c = blockIdx.x;
+  if (threadIdx.x < 32) {
+    uint32_t b = 0;
+    for (int i = threadIdx.x; i < c; i += 32) b += wordpart[(size_t)f * chunks + i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) b += __shfl_xor_sync(0xffffffffu, b, d);
+    if (threadIdx.x == 0) s_base = b;
   }
   __syncthreads();
-  uint32_t run = warp_total[warp];
-  for (size_t w = w0; w < w1; w += 32) {  // w1 - w0 is a multiple of 32 except possibly at the very end
-    const size_t i = w + lane;
-    const uint32_t c = i < w1 ? __popc(bm[i]) : 0;
-    const uint32_t incl = warp_incl_scan(c, lane);
-    if (i < w1) wp[i] = run + incl - c;
-    run += __shfl_sync(0xffffffffu, incl, 31);
+  const uint32_t* bm = bitmap + (size_t)f * words + (size_t)c * kScanChunk;
+  uint32_t* wp = wordprefix + (size_t)f * words + (size_t)c * kScanChunk;
+  const size_t left = words - (size_t)c * kScanChunk;
+  uint32_t pc[4], sum = 0;
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const size_t i = (size_t)threadIdx.x * 4 + j;
+    pc[j] = i < left ? __popc(bm[i]) : 0;
+    sum += pc[j];
   }
+  uint32_t total;
+  uint32_t run = s_base + block_excl_scan_256(sum, &total);
+#pragma unroll
+  for (int j = 0; j < 4; ++j) {
+    const size_t i = (size_t)threadIdx.x * 4 + j;
+    if (i < left) wp[i] = run;
+    run += pc[j];
+  }
+  if (c == chunks - 1 && threadIdx.x == 0) frame_k[f] = (int32_t)(s_base + total);
 }
 
 // P3: exclusive prefix over frames (one warp).
@@ -212,37 +256,64 @@ __global__ void __launch_bounds__(256) k_vox_count(const int32_t* __restrict__ f
   }
 }
 
-// P5: one 1024-thread block per frame; seg[row] = frame's first point + exclusive prefix of cnt.
-__global__ void __launch_bounds__(1024) k_vox_segment_scan(const int32_t* __restrict__ frame_offsets,
-                                                            const int32_t* __restrict__ voxel_offsets,
-                                                            const int32_t* __restrict__ cnt,
-                                                            int32_t* __restrict__ seg, int32_t* __restrict__ counters,
-                                                            int32_t* __restrict__ biglist, int T) {
-  __shared__ uint32_t warp_total[32];
-  __shared__ uint32_t carry;
-  const int f = blockIdx.x;
+// P5, two levels: seg[row] = frame's first point + exclusive prefix of cnt over the frame's voxel rows.  Up to 64 blocks per
+// frame, each taking the frame's 1024-row chunks c = blockIdx.x, + gridDim.x, ... (a KITTI frame has ~12 chunks).
+// a: points per chunk.  b: chunk base from the partials, scan inside the chunk, and the list of the voxels the packed SVFE
+// kernel handles one per warp (heavy items, scheduled first).
+__global__ void __launch_bounds__(256) k_vox_seg_partials(const int32_t* __restrict__ voxel_offsets, const int32_t* __restrict__ cnt,
+                                                           int chunks, int32_t* __restrict__ segpart) {
+  const int f = blockIdx.y;
   const int r0 = voxel_offsets[f], r1 = voxel_offsets[f + 1];
-  const uint32_t lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  if (threadIdx.x == 0) carry = (uint32_t)frame_offsets[f];
-  __syncthreads();
-  for (int base = r0; base < r1; base += 1024) {
-    const int r = base + threadIdx.x;
-    const uint32_t c = r < r1 ? (uint32_t)cnt[r] : 0;
-    // voxels the packed SVFE kernel handles one per warp (heavy items, scheduled first)
-    if (c > 31u || c > (uint32_t)T) biglist[atomicAdd(&counters[kCtrBigCount], 1)] = r;
-    const uint32_t incl = warp_incl_scan(c, lane);
-    if (lane == 31) warp_total[warp] = incl;
+  const int nch = (r1 - r0 + kScanChunk - 1) / kScanChunk;
+  for (int c = blockIdx.x; c < nch && c < chunks; c += gridDim.x) {
+    uint32_t sum = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = r0 + c * kScanChunk + (int)threadIdx.x * 4 + j;
+      if (r < r1) sum += (uint32_t)cnt[r];
+    }
+    uint32_t total;
+    block_excl_scan_256(sum, &total);
+    if (threadIdx.x == 0) segpart[(size_t)f * chunks + c] = (int32_t)total;
+  }
+}
+
+__global__ void __launch_bounds__(256) k_vox_segment_scan(const int32_t* __restrict__ frame_offsets,
+                                                           const int32_t* __restrict__ voxel_offsets,
+                                                           const int32_t* __restrict__ cnt, int chunks,
+                                                           const int32_t* __restrict__ segpart,
+                                                           int32_t* __restrict__ seg, int32_t* __restrict__ counters,
+                                                           int32_t* __restrict__ biglist, int T) {
+  __shared__ uint32_t s_base;
+  const int f = blockIdx.y;
+  const int r0 = voxel_offsets[f], r1 = voxel_offsets[f + 1];
+  const int nch = (r1 - r0 + kScanChunk - 1) / kScanChunk;
+  for (int c = blockIdx.x; c < nch && c < chunks; c += gridDim.x) {
     __syncthreads();
-    const uint32_t start = carry;
-    if (warp == 0) {
-      const uint32_t t = warp_total[lane];
-      const uint32_t ti = warp_incl_scan(t, lane);
-      warp_total[lane] = ti - t;
-      if (lane == 31) carry = start + ti;
+    if (threadIdx.x < 32) {
+      uint32_t b = 0;
+      for (int i = threadIdx.x; i < c; i += 32) b += (uint32_t)segpart[(size_t)f * chunks + i];
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) b += __shfl_xor_sync(0xffffffffu, b, d);
+      if (threadIdx.x == 0) s_base = (uint32_t)frame_offsets[f] + b;
     }
     __syncthreads();
-    if (r < r1) seg[r] = (int32_t)(start + warp_total[warp] + incl - c);
-    __syncthreads();
+    uint32_t v[4], sum = 0;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = r0 + c * kScanChunk + (int)threadIdx.x * 4 + j;
+      v[j] = r < r1 ? (uint32_t)cnt[r] : 0u;
+      if (v[j] > 31u || v[j] > (uint32_t)T) biglist[atomicAdd(&counters[kCtrBigCount], 1)] = r;
+      sum += v[j];
+    }
+    uint32_t total;
+    uint32_t run = s_base + block_excl_scan_256(sum, &total);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int r = r0 + c * kScanChunk + (int)threadIdx.x * 4 + j;
+      if (r < r1) seg[r] = (int32_t)run;
+      run += v[j];
+    }
   }
 }
 
@@ -699,7 +770,11 @@ __global__ void __launch_bounds__(256) k_vox_coords(const vn_grid_t g, const flo
 int launch_bucket(const VoxWorkspace& w, const int32_t* frame_offsets, int n_frames, int64_t n_points_total,
                   const int32_t* voxel_offsets, int T, cudaStream_t st) {
   VN_CUDA(cudaMemsetAsync(w.counters, 0, 64 * sizeof(int32_t), st));
-  k_vox_segment_scan<<<n_frames, 1024, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, w.seg, w.counters, w.biglist, T);
+  const int seg_blocks = (int)(w.seg_chunks < 64 ? w.seg_chunks : 64);
+  k_vox_seg_partials<<<dim3(seg_blocks, n_frames), 256, 0, st>>>(voxel_offsets, w.cnt, (int)w.seg_chunks, w.segpart);
+  VN_LAUNCH_CHECK("k_vox_seg_partials");
+  k_vox_segment_scan<<<dim3(seg_blocks, n_frames), 256, 0, st>>>(frame_offsets, voxel_offsets, w.cnt, (int)w.seg_chunks, w.segpart,
+                                                                 w.seg, w.counters, w.biglist, T);
   VN_LAUNCH_CHECK("k_vox_segment_scan");
   const int64_t want = (n_points_total + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 16;
@@ -755,8 +830,11 @@ int vn_voxelize_index(const vn_grid_t* grid, const float* points, const int32_t*
                                                    frame_offsets, w.bitmap, w.words, w.keyrow);
     VN_LAUNCH_CHECK("k_vox_mark");
   }
-  k_vox_scan_words<<<n_frames, 1024, 0, st>>>(w.bitmap, w.wordprefix, w.words, w.frame_k);
-  VN_LAUNCH_CHECK("k_vox_scan_words");
+  k_vox_word_partials<<<dim3((unsigned)w.word_chunks, n_frames), 256, 0, st>>>(w.bitmap, w.words, (int)w.word_chunks, w.wordpart);
+  VN_LAUNCH_CHECK("k_vox_word_partials");
+  k_vox_word_scan<<<dim3((unsigned)w.word_chunks, n_frames), 256, 0, st>>>(w.bitmap, w.words, (int)w.word_chunks, w.wordpart,
+                                                                            w.wordprefix, w.frame_k);
+  VN_LAUNCH_CHECK("k_vox_word_scan");
   k_vox_frame_offsets<<<1, 32, 0, st>>>(w.frame_k, n_frames, voxel_offsets);
   VN_LAUNCH_CHECK("k_vox_frame_offsets");
   if (n_points_total > 0) {
