@@ -369,6 +369,8 @@ def main():
                     help="kitti: real frames of the reference's bundled drive from baseline/_ref/data (cross-check)")
     ap.add_argument("--grid", default="auto", choices=["auto", "resident", "rows"],
                     help="sparse->dense form of the eval path: resident bf16 grid, never-materialised row table, or the library's default policy")
+    ap.add_argument("--output", default="nchw_f32", choices=["nchw_f32", "nhwc_bf16"],
+                    help="format of the returned tensor: the reference's float32 (B,128,H,W) (default), or bf16 channels-last for a bf16 RPN")
     ap.add_argument("--host-threads", type=int, default=None, help="threads of the host frame packer (default: cores / ranks, 2..8)")
     ap.add_argument("--in-flight", type=int, default=None,
                     help="eval steps in flight per GPU (front ends on their own streams; 1 = strictly one step at a time); "
@@ -431,7 +433,9 @@ def main():
             m.bias.data = (torch.rand(m.bias.shape, generator=g) - 0.5) * 0.6
             m.running_mean.data = (torch.rand(m.running_mean.shape, generator=g) - 0.5) * 0.4
             m.running_var.data = 0.5 + torch.rand(m.running_var.shape, generator=g)
-    grid_kw = {"auto": {}, "resident": {"materialise_grid": True}, "rows": {"materialise_grid": False}}[args.grid]
+    grid_kw = dict({"auto": {}, "resident": {"materialise_grid": True}, "rows": {"materialise_grid": False}}[args.grid])
+    if args.output != "nchw_f32":
+        grid_kw["output_format"] = args.output
     fe = vn.VoxelNetFrontEnd(fnet.to(dev), mnet.to(dev), target, **grid_kw)
 
     # ---- inputs: pinned host staging + resident device copies of TWO different batches --------------
@@ -707,7 +711,7 @@ def main():
         #   executed   FLOPs of the tcgen05.mma instructions actually issued (from the device-built plan)
         #   dense_eq   SURVEY 8(d)'s dense-equivalent FLOPs of the layer / time (can exceed the peak)
         # and the HBM side: unique live input blocks + stored output blocks + the weights once.
-        out_bytes = [128 * 64 * 2, 128 * 64 * 2, 128 * 64 * 4]
+        out_bytes = [128 * 64 * 2, 128 * 64 * 2, 128 * 64 * (4 if args.output == "nchw_f32" else 2)]
         wbytes = [27 * 128 * 64 * 2, 27 * 64 * 64 * 2, 27 * 64 * 64 * 2]
         conv_roof = []
         for l, name in enumerate(("conv1", "conv2", "conv3")):
@@ -753,6 +757,7 @@ def main():
                        "grid": "never materialised: (K,128) bf16 rows + the voxelizer's occupancy index feed conv-1 (vn_conv3d_bn_relu_fwd_rows)" if fe.dense is None
                                else "resident bf16 grid (default policy: it fits the 16 GiB budget); --grid rows times the never-materialised form",
                        "vfe": "fp32", "conv": "bf16 operands, fp32 accumulate (tcgen05)",
+                       "output": "float32 (B,128,H,W), the reference's tensor" if args.output == "nchw_f32" else "bf16 channels-last (B,128,H,W) view, channel d*64+c (option for a bf16 RPN; NOT the drop-in tensor)",
                        "launch": launch_mode,
                        "in_flight": "%d step(s) in flight per GPU (%s); ms_per_step = timed region / steps" % (
                            P, "one front end per pipeline stream, own grid/workspaces/outputs" if P > 1 else "one stream"),

@@ -226,6 +226,8 @@ size_t vn_conv3d_out_state_bytes(int32_t B, int32_t H, int32_t W);
  *
  * out_mode 0: y [B, Dout, H, W, 64] bf16 (NDHWC) - feeds the next layer.
  * out_mode 1: y [B, 64*Dout, H, W] f32 with channel = c*Dout + d - the reshape of model.py:262.
+ * out_mode 2: y [B, H, W, 64*Dout] bf16 (channels last) with channel = d*64 + c - for a bf16 channels-last consumer
+ *             (permute the input channels of its first convolution once: reference channel c*Dout + d <- d*64 + c).
  * shift_table / n_variants: n_variants 0: a plain [64] vector (BatchNorm shift with the conv bias
  *   folded in) - the drop-in case.  n_variants 1: [Dout][64].  n_variants 9: [3][3][Dout][64] from
  *   vn_conv3d_fold_background, indexed by (h class, w class) of the output position

@@ -347,3 +347,25 @@ def test_host_stream_with_two_front_ends_in_flight(cuda_device, graphs):
         assert len(stream._graphs) > 0
     with pytest.raises(RuntimeError):
         stream.voxel_counts_host(lag=3)
+
+
+def test_bf16_channels_last_output_option(cuda_device):
+    """output_format="nhwc_bf16": the same numbers as the float32 drop-in tensor, rounded to bf16, in channels-last memory
+    with the documented channel permutation (what a bf16 channels-last RPN consumes without a cast / layout pass);
+    resident outputs over a frame sequence included."""
+    sd = OM.random_state_dict(21)
+    sets = [synth_frames(2, s) for s in (500, 510, 500)]
+    fe32 = _build(cuda_device, "Pedestrian", sd)
+    fe16 = _build(cuda_device, "Pedestrian", sd, output_format="nhwc_bf16")
+    perm = fe16.reference_channel_of_output().to(cuda_device)
+    assert torch.equal(fe32.reference_channel_of_output(), torch.arange(128))
+    for fr in sets:
+        a = fe32.forward_frames(fr)
+        b = fe16.forward_frames(fr)
+        assert b.dtype == torch.bfloat16 and b.shape == a.shape and b.is_contiguous(memory_format=torch.channels_last)
+        assert torch.equal(b, a[:, perm].to(torch.bfloat16))
+    # a convolution with its input channels permuted once sees the same tensor
+    w = torch.randn(8, 128, 3, 3, device=cuda_device)
+    ref = torch.nn.functional.conv2d(a.to(torch.bfloat16).float(), w, padding=1)
+    got = torch.nn.functional.conv2d(b.float(), w[:, perm], padding=1)
+    assert rel_max_err(got.cpu(), ref.cpu()) < 1e-5

@@ -95,7 +95,7 @@ struct ConvParams {
   int B, Din, Dout, H, W;
   int nchunk;      // Cin / 64
   int tiles_h, tiles_w, n_tiles;
-  int out_mode;    // 0: bf16 NDHWC, 1: f32 [B, 64*Dout, H, W] with channel = c*Dout + d
+  int out_mode;    // 0: bf16 NDHWC, 1: f32 [B, 64*Dout, H, W] with channel = c*Dout + d, 2: bf16 [B, H, W, 64*Dout] with channel = d*64 + c
   int nvar;        // 1: shift rows [Dout][64]; 9: [3 h-classes][3 w-classes][Dout][64]; 25: [5][5][Dout][64]
   int table_smem;  // every table row is in shared memory (else only the interior variant: border rows come from global memory)
   int sub_classes; // 1: sub [Dout][64]; 9: sub [3][3][Dout][64] indexed like the 9-variant shift table
@@ -939,9 +939,10 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
               for (int j = 0; j < 32; ++j)
                 v[j] = fmaxf(fmaf(__uint_as_float(r[j]), scale_h[j], shift_row[j]), 0.0f) - sub_row[j];
             }
-            if (P.out_mode == 0) {
+            if (P.out_mode != 1) {
               __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
-                                   ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32;
+                                   (P.out_mode == 0 ? ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32
+                                                    : (((size_t)b * P.H + h) * P.W + w) * (64 * P.Dout) + dout * 64 + half * 32);
 #pragma unroll
               for (int q = 0; q < 2; ++q) {  // 2 x 32 B: one full sector per lane per store
                 uint32_t pk[8];
@@ -1367,7 +1368,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
   VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d: stride_d=%d pad_d=%d unsupported",
              stride_d, pad_d);
-  VN_REQUIRE(out_mode == 0 || out_mode == 1, "conv3d: out_mode=%d", out_mode);
+  VN_REQUIRE(out_mode == 0 || out_mode == 1 || out_mode == 2, "conv3d: out_mode=%d", out_mode);
   VN_REQUIRE(W % kTileW == 0 && W / kTileW <= kMaxTilesW, "conv3d: W=%d must be a multiple of %d, at most %d", W, kTileW,
              kTileW * kMaxTilesW);
   VN_REQUIRE(Din <= kMaxPlanes, "conv3d: Din=%d exceeds %d", Din, kMaxPlanes);

@@ -353,7 +353,8 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
                        box_flags=None, consume_flags: bool = False, border_ring: bool = False, sub=None, workspace=None,
                        out_state=None, planned: bool = False, reverse: bool = False):
     """x (B,Din,H,W,cin) bf16 NDHWC -> (B,Dout,H,W,64) bf16, or with final=True the reference's
-    reshaped (B, 64*Dout, H, W) f32 (model.py:262).
+    reshaped (B, 64*Dout, H, W) f32 (model.py:262), or with final="nhwc_bf16" a (B,H,W,64*Dout) bf16 tensor
+    whose channel d*64 + c is the reference's channel c*Dout + d.
 
     shift: (64,) plain BatchNorm shift, (Dout,64), or the (3,3,Dout,64) table of conv3d_fold_background.
     sub: optional (Dout,64) background subtracted after the ReLU.  box_flags: optional live-box table
@@ -385,11 +386,19 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
     want_sub = (3, 3, Dout, 64) if n_variants == 9 else (Dout, 64)  # with a 9-variant table the background has 9 classes too
     if sub is not None and (tuple(sub.shape) != want_sub or sub.dtype != torch.float32 or not sub.is_contiguous()):
         raise RuntimeError("sub must be a contiguous %s float32 tensor (shift has %d variants); got %s" % (want_sub, n_variants, tuple(sub.shape)))
+    if final not in (False, True, "nhwc_bf16"):
+        raise RuntimeError("final must be False, True or 'nhwc_bf16'")
+    out_mode = 2 if final == "nhwc_bf16" else (1 if final else 0)
     if out is None:
-        if final:
+        if out_mode == 1:
             out = torch.empty((B, 64 * Dout, H, W), dtype=torch.float32, device=x.device)
+        elif out_mode == 2:
+            out = torch.empty((B, H, W, 64 * Dout), dtype=torch.bfloat16, device=x.device)
         else:
             out = torch.empty((B, Dout, H, W, 64), dtype=torch.bfloat16, device=x.device)
+    want_out = [((B, Dout, H, W, 64), torch.bfloat16), ((B, 64 * Dout, H, W), torch.float32), ((B, H, W, 64 * Dout), torch.bfloat16)][out_mode]
+    if tuple(out.shape) != want_out[0] or out.dtype != want_out[1] or not out.is_contiguous():
+        raise RuntimeError("out must be a contiguous %s %s tensor; got %s %s" % (want_out[0], want_out[1], tuple(out.shape), out.dtype))
     if workspace is None:
         workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
     opts = (_cabi.VN_CONV_FLAGS_CONSUME if consume_flags else 0) | (_cabi.VN_CONV_FLAGS_BORDER_RING if border_ring else 0)
@@ -401,7 +410,7 @@ def conv3d_bn_relu_fwd(x, packed_weight, scale, shift, stride_d: int, pad_d: int
         check(
             _cabi.lib().vn_conv3d_bn_relu_fwd(
                 _ptr(x), B, Din, H, W, cin, stride_d, pad_d, _ptr(packed_weight), _ptr(_contig(scale, torch.float32)),
-                _ptr(shift), n_variants, _ptr(sub), 1 if final else 0, _ptr(out), _ptr(box_flags), opts,
+                _ptr(shift), n_variants, _ptr(sub), out_mode, _ptr(out), _ptr(box_flags), opts,
                 _ptr(out_state), _ptr(workspace), workspace.numel(), _stream(),
             ),
             "vn_conv3d_bn_relu_fwd",

@@ -67,7 +67,7 @@ class VoxelNetFrontEnd:
     def __init__(self, feature_net: FeatureLearningNet, middle_net: MiddleConvNet, target: str = "Car",
                  voxels_per_frame_capacity: int = 49152, fuse_voxel_features: bool = True,
                  skip_empty_boxes: bool = True, resident_outputs: bool = True, materialise_grid=None,
-                 grid_budget_bytes: int = 16 << 30):
+                 grid_budget_bytes: int = 16 << 30, output_format: str = "nchw_f32"):
         self.feature_net, self.middle_net = feature_net, middle_net
         self.target = target
         self.cfg = grid_config(target)
@@ -86,6 +86,15 @@ class VoxelNetFrontEnd:
         #          re-zeroed (the round-1 form; ~3 % more frames/s at Car batch 16).
         #   None (default): the grid if it fits `grid_budget_bytes` (16 GiB: Car up to 44 frames per batch), else rows.
         # The voxel-dict data flow (fuse_voxel_features=False) and the training step always use the grid.
+        # "nchw_f32": the reference's (B,128,H,W) float32 tensor, channel c*2+d (model.py:262) - the drop-in.
+        # "nhwc_bf16": the same values rounded to bf16 in channels-last memory, returned as a (B,128,H,W) view whose
+        #   channel k = d*64 + c holds the reference's channel c*2 + d (`reference_channel_of_output()`): for an RPN that
+        #   runs in bf16 channels-last - permute the input channels of its first convolution once
+        #   (`weight[:, front_end.reference_channel_of_output()]`) and the two feed it bit for bit the same numbers, with
+        #   half the bytes written by the last conv layer and no cast / layout pass in between.
+        if output_format not in ("nchw_f32", "nhwc_bf16"):
+            raise ValueError("output_format must be 'nchw_f32' or 'nhwc_bf16'")
+        self.output_format = output_format
         self._grid_request = None if materialise_grid is None else bool(materialise_grid)
         self.grid_budget_bytes = int(grid_budget_bytes)
         self.materialise_grid = True if not self.fuse_voxel_features else self._grid_request  # None until the batch size is known
@@ -174,7 +183,7 @@ class VoxelNetFrontEnd:
             return
         if self._shape is not None:
             # drop the old set first: two ~10 GB buffer sets per front end must not coexist
-            for name in ("workspace", "voxels", "voxelwise", "dense", "rows", "box_flags", "conv_workspaces", "out_states", "act1", "act2", "out"):
+            for name in ("workspace", "voxels", "voxelwise", "dense", "rows", "_out_store", "box_flags", "conv_workspaces", "out_states", "act1", "act2", "out"):
                 setattr(self, name, None)
             self._train_coords = None
         self._generation += 1
@@ -213,7 +222,11 @@ class VoxelNetFrontEnd:
         self.out_states = [ops.conv3d_new_out_state(B, H, W, device) for _ in range(3)] if self.resident_outputs else None
         self.act1 = torch.empty((B, d1, H, W, 64), dtype=torch.bfloat16, device=device)
         self.act2 = torch.empty((B, d2, H, W, 64), dtype=torch.bfloat16, device=device)
-        self.out = torch.empty((B, 64 * d3, H, W), dtype=torch.float32, device=device)
+        if self.output_format == "nhwc_bf16":
+            self._out_store = torch.empty((B, H, W, 64 * d3), dtype=torch.bfloat16, device=device)
+            self.out = self._out_store.permute(0, 3, 1, 2)  # (B,128,H,W), channels-last strides
+        else:
+            self._out_store = self.out = torch.empty((B, 64 * d3, H, W), dtype=torch.float32, device=device)
         self.capacity = cap
         self._shape = shape
 
@@ -224,6 +237,17 @@ class VoxelNetFrontEnd:
             c = self.cfg
             self.dense = torch.empty((self._pending_frames, c.depth, c.height, c.width, 128), dtype=torch.bfloat16, device=device)
             ops.fill_zero(self.dense)
+
+    @property
+    def _final(self):
+        return "nhwc_bf16" if self.output_format == "nhwc_bf16" else True
+
+    def reference_channel_of_output(self) -> torch.Tensor:
+        """For every channel k of the returned tensor the channel of the reference's (B,128,H,W) tensor it holds
+        (identity for "nchw_f32"; for "nhwc_bf16" k = d*64 + c holds reference channel c*D3 + d)."""
+        d3 = ops.conv3d_out_depth(ops.conv3d_out_depth(ops.conv3d_out_depth(self.cfg.depth, 2, 1), 1, 0), 2, 1)
+        k = torch.arange(64 * d3)
+        return k if self.output_format == "nchw_f32" else (k % 64) * d3 + k // 64
 
     def device_bytes(self) -> dict:
         """Bytes of device memory this front end holds, by buffer (after the first call / reserve())."""
@@ -353,7 +377,7 @@ class VoxelNetFrontEnd:
                 main.wait_event(ev[1])
             ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1, reverse=True,
                                    consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
-            ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
+            ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=self._final, out=self._out_store, box_flags=f2,
                                    consume_flags=True, workspace=ws2, out_state=st2, planned=True)
             if not use_rows:
                 main.wait_event(ev[3])  # join: the next step's grid writes come after the clear
@@ -372,7 +396,7 @@ class VoxelNetFrontEnd:
                 ops.conv3d_bn_relu_fwd(self.act1, w1, s1, self._tables[1], 1, 0, out=self.act2, box_flags=f1, reverse=True,
                                        consume_flags=True, sub=self._bg[1], workspace=ws1, out_state=st1, planned=True)
             with span("conv3"):
-                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=True, out=self.out, box_flags=f2,
+                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, self._tables[2], 2, 1, final=self._final, out=self._out_store, box_flags=f2,
                                        consume_flags=True, workspace=ws2, out_state=st2, planned=True)
         else:
             with span("conv1"):
@@ -382,7 +406,7 @@ class VoxelNetFrontEnd:
             with span("conv2"):
                 ops.conv3d_bn_relu_fwd(self.act1, w1, s1, t1, 1, 0, out=self.act2, workspace=ws1)
             with span("conv3"):
-                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=True, out=self.out, workspace=ws2)
+                ops.conv3d_bn_relu_fwd(self.act2, w2, s2, t2, 2, 1, final=self._final, out=self._out_store, workspace=ws2)
         return self.out
 
     def _aux_stream(self, device):
