@@ -1,0 +1,111 @@
+"""The stride-1 3x3 RPN layers (reference ConvMD(2, 128, 128, 3, (1,1), (1,1)), voxelnet/model.py:111-167, 212-242) on the
+tcgen05 conv kernel: `vn_conv2d_bn_relu_fwd` / `ConvMD2d` / `RPNBlockTail` against plain PyTorch fp32.
+
+Tolerances: bf16 operands, fp32 accumulation, bf16 output.  Against the SAME bf16-rounded operands the result must be
+the fp32 result rounded to bf16 up to one bf16 ulp (catches any wrong tap, swizzle, channel group or descriptor);
+against the unrounded fp32 module (Conv2d -> BatchNorm2d -> ReLU) max|err| / max|ref| <= 1e-2 like the 3-D layers.
+"""
+import pytest
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+
+from tests.helpers import rel_max_err
+
+pytestmark = pytest.mark.gpu
+
+
+class RefConvMD2d(nn.Module):
+    """What the reference's ConvMD(2, cin, cout, k, stride, padding) is (model.py:132-167)."""
+
+    def __init__(self, cin, cout, k=3, stride=1, padding=1):
+        super().__init__()
+        self.conv = nn.Conv2d(cin, cout, k, stride, padding)
+        self.batch_norm = nn.BatchNorm2d(cout)
+
+    def forward(self, x):
+        return F.relu(self.batch_norm(self.conv(x)))
+
+
+def _randomise(m, g):
+    for mod in m.modules():
+        if isinstance(mod, nn.BatchNorm2d):
+            mod.weight.data = 0.5 + torch.rand(mod.weight.shape, generator=g)
+            mod.bias.data = (torch.rand(mod.bias.shape, generator=g) - 0.5) * 0.4
+            mod.running_mean.data = (torch.rand(mod.running_mean.shape, generator=g) - 0.5) * 0.3
+            mod.running_var.data = 0.5 + torch.rand(mod.running_var.shape, generator=g)
+    return m.eval()
+
+
+@pytest.mark.parametrize("cin,cout,B,H,W", [(128, 128, 2, 24, 16), (64, 64, 1, 16, 8), (128, 192, 1, 37, 24), (64, 128, 3, 100, 88)])
+def test_conv2d_bn_relu_matches_torch(cuda_device, cin, cout, B, H, W):
+    import voxelnet_pytorch_b200 as vn
+
+    g = torch.Generator().manual_seed(cin + cout + H)
+    ref = _randomise(RefConvMD2d(cin, cout), g)
+    x = (torch.randn((B, cin, H, W), generator=g) * (torch.rand((B, cin, H, W), generator=g) < 0.6)).to(torch.bfloat16)
+    layer = vn.ConvMD2d.from_reference(ref.to(cuda_device))
+    assert set(layer.state_dict()) == set(ref.state_dict())
+    xg = x.to(cuda_device).contiguous(memory_format=torch.channels_last)
+    got = layer(xg)
+    assert got.dtype == torch.bfloat16 and got.shape == (B, cout, H, W) and got.is_contiguous(memory_format=torch.channels_last)
+    with torch.no_grad():
+        want = ref.cpu().double()(x.double())
+        # the same arithmetic on the operands the kernel sees: weights * BN scale rounded to bf16, fp32-exact accumulation
+        bn = ref.batch_norm
+        scale = (bn.weight.double() / torch.sqrt(bn.running_var.double() + bn.eps)).float()
+        w_q = (ref.conv.weight.float() * scale[:, None, None, None]).to(torch.bfloat16).double()
+        shift = (ref.conv.bias.double() * scale.double() + bn.bias.double() - bn.running_mean.double() * scale.double()).float().double()
+        exact = F.relu(F.conv2d(x.double(), w_q, None, 1, 1) + shift[None, :, None, None])
+    got64 = got.cpu().double()
+    assert rel_max_err(got64, want) < 1e-2
+    ulp = exact.abs().clamp_min(2.0 ** -100) * 2.0 ** -7  # one bf16 ulp is at most 2^-7 of the value
+    assert bool(((got64 - exact).abs() <= ulp + 1e-6).all()), float(((got64 - exact).abs() - ulp).max())
+
+
+def test_rpn_block_tail_matches_the_reference_block(cuda_device):
+    """A block shaped like the reference's block2 (stride-2 head + stride-1 layers, model.py:232-240), at reduced
+    size: the head runs on stock PyTorch, the tail on the tcgen05 kernel, bf16 channels-last in between."""
+    import voxelnet_pytorch_b200 as vn
+
+    g = torch.Generator().manual_seed(5)
+    block = nn.Sequential(RefConvMD2d(128, 128, 3, 2, 1), *[RefConvMD2d(128, 128) for _ in range(3)])
+    _randomise(block, g)
+    x = torch.randn((2, 128, 80, 96), generator=g).relu()
+    with torch.no_grad():
+        want = block.double()(x.double())
+    tail = vn.RPNBlockTail(block.float().to(cuda_device))
+    assert [type(m).__name__ for m in tail.layers] == ["RefConvMD2d", "ConvMD2d", "ConvMD2d", "ConvMD2d"]
+    with torch.no_grad():
+        got = tail(x.to(cuda_device))
+    assert got.shape == (2, 128, 40, 48) and got.dtype == torch.bfloat16
+    assert rel_max_err(got.cpu().double(), want) < 2e-2  # four bf16 layers in a row
+    rel_l2 = float((got.cpu().double() - want).norm() / want.norm())
+    assert rel_l2 < 1e-2, rel_l2
+
+
+def test_front_end_bf16_output_feeds_a_conv2d_layer(cuda_device):
+    """VoxelNetFrontEnd(output_format="nhwc_bf16") -> ConvMD2d with its input channels permuted once == the same layer
+    with the reference's channel order on the float32 drop-in tensor rounded to bf16."""
+    import voxelnet_pytorch_b200 as vn
+    from oracle import model_torch as OM
+    from tests.helpers import load_state, synth_frames
+
+    sd = OM.random_state_dict(31)
+    fnet, mnet = vn.FeatureLearningNet("Pedestrian").eval(), vn.MiddleConvNet().eval()
+    load_state(fnet, sd, "")
+    load_state(mnet, sd, "")
+    fnet, mnet = fnet.to(cuda_device), mnet.to(cuda_device)
+    frames = synth_frames(2, 600)
+    fe32 = vn.VoxelNetFrontEnd(fnet, mnet, "Pedestrian")
+    fe16 = vn.VoxelNetFrontEnd(fnet, mnet, "Pedestrian", output_format="nhwc_bf16")
+    g = torch.Generator().manual_seed(6)
+    ref = _randomise(RefConvMD2d(128, 128), g).to(cuda_device)
+    a = vn.ConvMD2d.from_reference(ref)(fe32.forward_frames(frames).to(torch.bfloat16))
+    perm = fe16.reference_channel_of_output().to(cuda_device)
+    ref_p = RefConvMD2d(128, 128).to(cuda_device)
+    ref_p.load_state_dict(ref.state_dict())
+    ref_p.conv.weight.data = ref.conv.weight.data[:, perm].contiguous()
+    b = vn.ConvMD2d.from_reference(ref_p.eval())(fe16.forward_frames(frames))
+    # (the K order of the two sums differs by the channel permutation: equal up to a bf16 ulp of the output)
+    assert rel_max_err(a.float().cpu(), b.float().cpu()) < 5e-3

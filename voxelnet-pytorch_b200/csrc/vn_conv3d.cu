@@ -1207,6 +1207,46 @@ int plan_planes_transposed(Params& P, int stride_d, int pad_d) {
   return 0;
 }
 
+// 2-D convolution on the same kernel (RPN blocks, voxelnet/model.py:212-251): ONE input plane whose "depth taps" are the
+// G groups of 64 output channels - one MMA of N = 64 G multiplies the box with the G weight tiles laid side by side and
+// lands in G adjacent accumulators ("output depth" g = channels 64 g .. 64 g + 63).
+template <typename Params>
+int plan_planes_2d(Params& P, int groups) {
+  for (int p = 0; p < kMaxPlanes; ++p) P.plane[p] = PlaneInfo{0, 0, 0, 0};
+  if (groups < 1 || groups > 3) return -1;
+  P.plane[0].nkd = groups;
+  P.plane[0].dmin = 0;
+  P.plane[0].woff = 0;
+  P.plane[0].wstride = (uint32_t)groups * kBTapBytes;
+  return 0;
+}
+
+// torch Conv2d weight [cout][cin][3][3] fp32 (times an optional per-output-channel scale: BatchNorm folded) -> the image
+// the kernel reads for the schedule above: per (chunk, kw) a 72 KB slot holding [kh][group][n = 64][k = 64] bf16 tiles
+// (rows 128B-swizzled); 64 floats of 1.0 behind the last slot serve as the epilogue's scale vector.
+__global__ void __launch_bounds__(256)
+    k_pack_weights2d(const float* __restrict__ w, const float* __restrict__ scale, int cin, int cout, uint8_t* __restrict__ packed) {
+  const int nchunk = cin / 64, groups = cout / 64;
+  const int total = 9 * cin * cout;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    int r = i;
+    const int k = r % 64; r /= 64;
+    const int n = r % 64; r /= 64;
+    const int j = r % groups; r /= groups;
+    const int kh = r % 3; r /= 3;
+    const int kw = r % 3; r /= 3;
+    const int c = r;
+    const int co = j * 64 + n, ci = c * 64 + k;
+    float v = w[(((size_t)co * cin + ci) * 3 + kh) * 3 + kw];
+    if (scale != nullptr) v *= scale[co];
+    const size_t tile = (size_t)(c * 3 + kw) * kBSlotBytes + (size_t)(kh * groups + j) * kBTapBytes;
+    const size_t off = tile + (size_t)n * 128 + ((((k >> 3) ^ (n & 7)) << 4) | ((k & 7) << 1));
+    *reinterpret_cast<__nv_bfloat16*>(packed + off) = __float2bfloat16_rn(v);
+  }
+  if (blockIdx.x == 0 && threadIdx.x < 64)
+    reinterpret_cast<float*>(packed + (size_t)nchunk * 3 * kBSlotBytes)[threadIdx.x] = 1.0f;
+}
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                   CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
@@ -1362,7 +1402,8 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                        int32_t pad_d, const void* packed_weight, const float* scale, const float* shift_table,
                        int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
                        int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
-                       vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr) {
+                       vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr,
+                       int32_t groups2d = 0) {
   VN_REQUIRE((x || gather) && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
@@ -1372,8 +1413,9 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   VN_REQUIRE(W % kTileW == 0 && W / kTileW <= kMaxTilesW, "conv3d: W=%d must be a multiple of %d, at most %d", W, kTileW,
              kTileW * kMaxTilesW);
   VN_REQUIRE(Din <= kMaxPlanes, "conv3d: Din=%d exceeds %d", Din, kMaxPlanes);
-  const int Dout = transposed_dout > 0 ? transposed_dout : out_depth(Din, stride_d, pad_d);
-  VN_REQUIRE((transposed_dout > 0 || Din + 2 * pad_d >= 3) && Dout >= 1 && Dout <= kSlots, "conv3d: Dout=%d outside [1,%d]",
+  VN_REQUIRE(groups2d == 0 || (Din == 1 && groups2d >= 1 && groups2d <= 3), "conv2d: %d output channel groups (1..3), Din=%d", groups2d, Din);
+  const int Dout = groups2d > 0 ? groups2d : (transposed_dout > 0 ? transposed_dout : out_depth(Din, stride_d, pad_d));
+  VN_REQUIRE((transposed_dout > 0 || groups2d > 0 || Din + 2 * pad_d >= 3) && Dout >= 1 && Dout <= kSlots, "conv3d: Dout=%d outside [1,%d]",
              Dout, kSlots);
   VN_REQUIRE(n_variants == 0 || n_variants == 1 || n_variants == 9 || n_variants == 25,
              "conv3d: n_variants=%d (0: plain [64] shift, 1, 9, 25)", n_variants);
@@ -1428,7 +1470,8 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   Q.force_ring = (flag_opts & VN_CONV_FLAGS_BORDER_RING) ? 1 : 0;
   Q.out_state = out_state;
   Q.hdr = hdr; Q.groups = groups; Q.tiles = tiles; Q.gtiles = gtiles;
-  if ((transposed_dout > 0 ? plan_planes_transposed(Q, stride_d, pad_d) : plan_planes(Q, stride_d, pad_d)) != 0) {
+  if ((groups2d > 0 ? plan_planes_2d(Q, groups2d)
+                    : (transposed_dout > 0 ? plan_planes_transposed(Q, stride_d, pad_d) : plan_planes(Q, stride_d, pad_d))) != 0) {
     set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
     return VN_ERR_UNSUPPORTED;
   }
@@ -1580,6 +1623,32 @@ int vn_conv3d_raw_stats_fwd(const void* x, int32_t B, int32_t Din, int32_t H, in
   VN_REQUIRE((reinterpret_cast<uintptr_t>(stats) & 7) == 0, "conv3d_raw_stats: stats must be 8-byte aligned");
   return conv_launch(x, B, Din, H, W, cin, stride_d, pad_d, packed_weight, ones, bias, 0, nullptr, 0, y_raw, box_flags,
                      flag_opts, nullptr, workspace, workspace_bytes, stream, stats);
+}
+
+size_t vn_conv2d_packed_weight_bytes(int32_t cin) {
+  if (cin != 64 && cin != 128) return 0;
+  return (size_t)(cin / 64) * 3 * kBSlotBytes + 64 * sizeof(float);
+}
+
+int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, void* packed, vn_stream_t stream) {
+  VN_REQUIRE(cin == 64 || cin == 128, "conv2d_pack_weights: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d_pack_weights: cout=%d (supported: 64, 128, 192)", cout);
+  VN_REQUIRE(weight != nullptr && packed != nullptr && (reinterpret_cast<uintptr_t>(packed) & 15) == 0,
+             "conv2d_pack_weights: null or misaligned pointer");
+  VN_CUDA(cudaMemsetAsync(packed, 0, vn_conv2d_packed_weight_bytes(cin), as_stream(stream)));
+  k_pack_weights2d<<<sm_count() * 2, 256, 0, as_stream(stream)>>>(weight, scale, cin, cout, reinterpret_cast<uint8_t*>(packed));
+  VN_LAUNCH_CHECK("k_pack_weights2d");
+  return VN_OK;
+}
+
+int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout, const void* packed_weight,
+                          const float* shift, void* y, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d: cout=%d (supported: 64, 128, 192)", cout);
+  VN_REQUIRE(cin == 64 || cin == 128, "conv2d: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(packed_weight != nullptr && shift != nullptr, "conv2d: null pointer");
+  const float* ones = reinterpret_cast<const float*>(static_cast<const uint8_t*>(packed_weight) + (size_t)(cin / 64) * 3 * kBSlotBytes);
+  return conv_launch(x, B, 1, H, W, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr, 0, nullptr, workspace,
+                     workspace_bytes, stream, nullptr, 0, nullptr, cout / 64);
 }
 
 }  // extern "C"

@@ -460,6 +460,45 @@ def conv3d_bn_relu_fwd_rows(grid, rows, voxel_offsets, n_points_total: int, vox_
     return out
 
 
+# ---------------------------------------------------------------------------------------------
+# 2-D 3x3 convolution (RPN blocks, model.py:212-251) on the same tcgen05 kernel
+# ---------------------------------------------------------------------------------------------
+def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
+    """weight (cout,cin,3,3) f32 [* scale (cout,): BatchNorm folded in] -> the packed bf16 image of vn_conv2d_bn_relu_fwd."""
+    _require_cuda(weight, scale)
+    w = _contig(weight.detach(), torch.float32)
+    cout, cin = int(w.shape[0]), int(w.shape[1])
+    if tuple(w.shape[2:]) != (3, 3):
+        raise RuntimeError("conv2d_pack_weights: 3x3 kernels only; got %s" % (tuple(w.shape),))
+    nbytes = int(_cabi.lib().vn_conv2d_packed_weight_bytes(cin))
+    if nbytes == 0:
+        raise RuntimeError("conv2d_pack_weights: cin=%d unsupported (64, 128)" % cin)
+    packed = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
+    with torch.cuda.device(w.device):
+        check(_cabi.lib().vn_conv2d_pack_weights(_ptr(w), _ptr(None if scale is None else _contig(scale, torch.float32)), cin, cout,
+                                                 _ptr(packed), _stream()), "vn_conv2d_pack_weights")
+    return packed
+
+
+def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None) -> torch.Tensor:
+    """x (B,H,W,cin) bf16 channels-last -> relu(conv3x3(x) + shift) as (B,H,W,cout) bf16 (stride 1, padding 1);
+    shift (cout,) f32 carries the bias and the BatchNorm shift, the BatchNorm scale sits in the packed weights."""
+    _require_cuda(x, packed_weight, shift, out, workspace)
+    _contig(x, torch.bfloat16), _contig(shift, torch.float32)
+    B, H, W, cin = x.shape
+    cout = int(shift.numel())
+    if out is None:
+        out = torch.empty((B, H, W, cout), dtype=torch.bfloat16, device=x.device)
+    elif tuple(out.shape) != (B, H, W, cout) or out.dtype != torch.bfloat16 or not out.is_contiguous():
+        raise RuntimeError("out must be a contiguous (B,H,W,cout) bf16 tensor")
+    if workspace is None:
+        workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        check(_cabi.lib().vn_conv2d_bn_relu_fwd(_ptr(x), B, H, W, cin, cout, _ptr(packed_weight), _ptr(shift), _ptr(out),
+                                                _ptr(workspace), workspace.numel(), _stream()), "vn_conv2d_bn_relu_fwd")
+    return out
+
+
 def conv3d_plan_stats(workspace, B: int, Din: int, H: int, W: int, cin: int, stride_d: int, pad_d: int) -> dict:
     """Diagnostics (blocking, host side): decode the work plan the last vn_conv3d_bn_relu_fwd call left
     in `workspace` (PlanHeader 16 B | GroupDesc[n_tiles] 16 B each | TilePlan[n_tiles] 8 B each | per-group copies, see vn_conv3d.cu) and count
