@@ -279,13 +279,18 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
  *   taps of the 3-D layers do (one 128 x cout x 16 MMA per k-step).
  * vn_conv2d_pack_weights: weight [cout][cin][3][3] f32 (torch layout), scale [cout] = BatchNorm gamma / sqrt(var + eps) or
  *   NULL; packed: vn_conv2d_packed_weight_bytes(cin) bytes.  shift [cout] = beta + (bias - mean) * scale.
- * workspace: vn_conv3d_workspace_bytes(B, H, W).  Stride-2 layers, deconvolutions and the 1x1 heads are not covered. */
+ * y has y_channels channels per position and the launch writes channels y_channel_offset .. + cout of it (a 256-channel
+ *   layer is two launches of 128 into one tensor; ConvTranspose2d(k 3, stride 1, padding 1) = this convolution with the
+ *   kernel flipped and its channel axes swapped: voxelnet/model.py:229 deconv1).
+ * workspace: vn_conv3d_workspace_bytes(B, H, W).  Stride-2 layers, the strided deconvolutions and the 1x1 heads are not
+ * covered. */
 size_t vn_conv2d_packed_weight_bytes(int32_t cin);
 int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, void* packed,
                            vn_stream_t stream);
 int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout,
-                          const void* packed_weight, const float* shift, void* y, void* workspace,
-                          size_t workspace_bytes, vn_stream_t stream);
+                          const void* packed_weight, const float* shift, void* y, int32_t y_channels,
+                          int32_t y_channel_offset, void* workspace, size_t workspace_bytes,
+                          vn_stream_t stream);
 
 /* Background folding for a layer whose INPUT is stored as a deviation from a background (what the previous
  * layer outputs wherever ITS input was all background; NULL = zero background).  The reference zero-pads, so

@@ -63,6 +63,34 @@ def test_conv2d_bn_relu_matches_torch(cuda_device, cin, cout, B, H, W):
     assert bool(((got64 - exact).abs() <= ulp + 1e-6).all()), float(((got64 - exact).abs() - ulp).max())
 
 
+@pytest.mark.parametrize("cin,cout,H,W", [(128, 256, 40, 32), (64, 192, 20, 16)])
+def test_deconv_3x3_stride1_matches_torch(cuda_device, cin, cout, H, W):
+    """The reference's deconv1 (DeConv2d(128, 256, 3, (1,1), (1,1)), model.py:229): ConvTranspose2d -> BN -> ReLU, 256
+    output channels = two launches of 128 into one tensor."""
+    import voxelnet_pytorch_b200 as vn
+
+    class RefDeConv(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.deconv = nn.ConvTranspose2d(cin, cout, 3, 1, 1)
+            self.batch_norm = nn.BatchNorm2d(cout)
+
+        def forward(self, x):
+            return F.relu(self.batch_norm(self.deconv(x)))
+
+    g = torch.Generator().manual_seed(cout)
+    ref = _randomise(RefDeConv(), g)
+    x = torch.randn((2, cin, H, W), generator=g).relu().to(torch.bfloat16)
+    layer = vn.DeConvMD2d.from_reference(ref.to(cuda_device))
+    assert set(layer.state_dict()) == set(ref.state_dict())
+    got = layer(x.to(cuda_device).contiguous(memory_format=torch.channels_last))
+    with torch.no_grad():
+        want = ref.cpu().double()(x.double())
+    assert got.shape == want.shape and got.dtype == torch.bfloat16
+    assert rel_max_err(got.cpu().double(), want) < 1e-2
+    assert float((got.cpu().double() - want).norm() / want.norm()) < 5e-3
+
+
 def test_rpn_block_tail_matches_the_reference_block(cuda_device):
     """A block shaped like the reference's block2 (stride-2 head + stride-1 layers, model.py:232-240), at reduced
     size: the head runs on stock PyTorch, the tail on the tcgen05 kernel, bf16 channels-last in between."""

@@ -103,6 +103,7 @@ struct ConvParams {
   const float* scale;   // [64]
   const float* table;   // [nvar][Dout][64] (or [64] when table_plain)
   int reverse;          // take the groups of the plan last to first (VN_CONV_FLAGS_REVERSE)
+  int out_ctotal, out_coff;  // out_mode 2: channels per position of y and the first channel this launch writes
   int table_plain;      // table is a plain [64] shift vector used for every row
   const float* sub;     // [Dout][64] subtracted after the ReLU, or nullptr
   void* out;
@@ -942,7 +943,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
             if (P.out_mode != 1) {
               __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
                                    (P.out_mode == 0 ? ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32
-                                                    : (((size_t)b * P.H + h) * P.W + w) * (64 * P.Dout) + dout * 64 + half * 32);
+                                                    : (((size_t)b * P.H + h) * P.W + w) * P.out_ctotal + P.out_coff + dout * 64 + half * 32);
 #pragma unroll
               for (int q = 0; q < 2; ++q) {  // 2 x 32 B: one full sector per lane per store
                 uint32_t pk[8];
@@ -1403,7 +1404,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                        int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
                        int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
                        vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr,
-                       int32_t groups2d = 0) {
+                       int32_t groups2d = 0, int32_t out_ctotal = 0, int32_t out_coff = 0) {
   VN_REQUIRE((x || gather) && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
@@ -1494,6 +1495,8 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   P.table = shift_table;
   P.table_plain = n_variants == 0 ? 1 : 0;
   P.reverse = (flag_opts & VN_CONV_FLAGS_REVERSE) ? 1 : 0;
+  P.out_ctotal = out_ctotal > 0 ? out_ctotal : 64 * Dout;
+  P.out_coff = out_coff;
   P.sub = sub;
   P.out = y;
   P.hdr = hdr; P.groups = groups; P.tiles = tiles; P.gtiles = gtiles;
@@ -1642,13 +1645,17 @@ int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin,
 }
 
 int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout, const void* packed_weight,
-                          const float* shift, void* y, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+                          const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset, void* workspace,
+                          size_t workspace_bytes, vn_stream_t stream) {
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d: cout=%d (supported: 64, 128, 192)", cout);
   VN_REQUIRE(cin == 64 || cin == 128, "conv2d: cin=%d (supported: 64, 128)", cin);
   VN_REQUIRE(packed_weight != nullptr && shift != nullptr, "conv2d: null pointer");
+  VN_REQUIRE(y_channels >= cout && y_channel_offset >= 0 && y_channel_offset + cout <= y_channels && y_channels % 16 == 0 &&
+                 y_channel_offset % 16 == 0,
+             "conv2d: channels %d..%d of %d (multiples of 16 inside y)", y_channel_offset, y_channel_offset + cout, y_channels);
   const float* ones = reinterpret_cast<const float*>(static_cast<const uint8_t*>(packed_weight) + (size_t)(cin / 64) * 3 * kBSlotBytes);
   return conv_launch(x, B, 1, H, W, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr, 0, nullptr, workspace,
-                     workspace_bytes, stream, nullptr, 0, nullptr, cout / 64);
+                     workspace_bytes, stream, nullptr, 0, nullptr, cout / 64, y_channels, y_channel_offset);
 }
 
 }  // extern "C"

@@ -480,22 +480,24 @@ def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
     return packed
 
 
-def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None) -> torch.Tensor:
+def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channel_offset: int = 0) -> torch.Tensor:
     """x (B,H,W,cin) bf16 channels-last -> relu(conv3x3(x) + shift) as (B,H,W,cout) bf16 (stride 1, padding 1);
-    shift (cout,) f32 carries the bias and the BatchNorm shift, the BatchNorm scale sits in the packed weights."""
+    shift (cout,) f32 carries the bias and the BatchNorm shift, the BatchNorm scale sits in the packed weights.
+    `out` may have more channels than cout: the launch writes channels channel_offset .. + cout of it."""
     _require_cuda(x, packed_weight, shift, out, workspace)
     _contig(x, torch.bfloat16), _contig(shift, torch.float32)
     B, H, W, cin = x.shape
     cout = int(shift.numel())
     if out is None:
         out = torch.empty((B, H, W, cout), dtype=torch.bfloat16, device=x.device)
-    elif tuple(out.shape) != (B, H, W, cout) or out.dtype != torch.bfloat16 or not out.is_contiguous():
-        raise RuntimeError("out must be a contiguous (B,H,W,cout) bf16 tensor")
+    elif tuple(out.shape[:3]) != (B, H, W) or out.dtype != torch.bfloat16 or not out.is_contiguous():
+        raise RuntimeError("out must be a contiguous (B,H,W,C) bf16 tensor")
     if workspace is None:
         workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
         check(_cabi.lib().vn_conv2d_bn_relu_fwd(_ptr(x), B, H, W, cin, cout, _ptr(packed_weight), _ptr(shift), _ptr(out),
-                                                _ptr(workspace), workspace.numel(), _stream()), "vn_conv2d_bn_relu_fwd")
+                                                int(out.shape[3]), int(channel_offset), _ptr(workspace), workspace.numel(), _stream()),
+              "vn_conv2d_bn_relu_fwd")
     return out
 
 

@@ -7,7 +7,10 @@ Conv2d layers and 61 of its ~110 GFLOP per frame.  `ConvMD2d` keeps the referenc
 `forward(x)` takes and returns a `(B,C,H,W)` bf16 tensor in `torch.channels_last` memory format - what
 `VoxelNetFrontEnd(output_format="nhwc_bf16")` hands over - so a block chains without a cast or layout pass.
 
-The stride-2 layers, the `256`-channel block 3 (W = 44 is not a multiple of the 8-wide tile), the three
+`DeConvMD2d` is the reference's `deconv1 = DeConv2d(128, 256, 3, (1,1), (1,1))` (model.py:229; 21 GFLOP per frame): a
+stride-1 transposed convolution is a convolution with the flipped kernel.  Together: 75 of the RPN's ~110 GFLOP.
+
+The stride-2 layers, the `256`-channel block 3 (W = 44 is not a multiple of the 8-wide tile), the two strided
 `ConvTranspose2d` and the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
 wraps a reference block so that its head runs on stock PyTorch and its stride-1 tail here.
 """
@@ -20,53 +23,114 @@ from . import ops
 from .model import _fold_bn
 
 
-class ConvMD2d(nn.Module):
-    """model.py:111-167, 2-D case, kernel 3, stride 1, padding 1, BatchNorm + ReLU, cin in {64,128}, cout in {64,128,192}."""
+class _Conv3x3BnRelu(nn.Module):
+    """Shared eval-mode path: a 3x3 / stride 1 / padding 1 convolution in torch Conv2d weight form + BatchNorm2d + ReLU,
+    split into launches of <= 192 output channels that write their slice of one channels-last output tensor."""
 
-    def __init__(self, cin: int, cout: int):
-        super().__init__()
-        if cin not in (64, 128) or cout not in (64, 128, 192):
-            raise ValueError("ConvMD2d: cin=%d, cout=%d unsupported by the B200 kernel (cin 64/128, cout 64/128/192)" % (cin, cout))
-        self.cin, self.cout = cin, cout
-        self.conv = nn.Conv2d(cin, cout, 3, 1, 1)
-        self.batch_norm = nn.BatchNorm2d(cout)
-        self._packed, self._key = None, None
+    cin: int
+    cout: int
+    batch_norm: nn.BatchNorm2d
 
-    @classmethod
-    def from_reference(cls, layer) -> "ConvMD2d":
-        """A reference `ConvMD(2, ...)` (or anything with `.conv` Conv2d and `.batch_norm` BatchNorm2d) -> ConvMD2d sharing
-        its parameter values."""
-        conv = layer.conv
-        if tuple(conv.kernel_size) != (3, 3) or tuple(conv.stride) != (1, 1) or tuple(conv.padding) != (1, 1):
-            raise ValueError("ConvMD2d covers 3x3 / stride 1 / padding 1 layers only")
-        m = cls(conv.in_channels, conv.out_channels)
-        m.load_state_dict({k: v for k, v in layer.state_dict().items()})
-        return m.to(conv.weight.device).eval()
+    def _conv_weight_bias(self):
+        raise NotImplementedError
+
+    def _tracked(self):
+        raise NotImplementedError
 
     def folded(self):
-        """(packed bf16 weights with the BatchNorm scale folded in, shift (cout,) f32)."""
-        ts = [self.conv.weight, self.conv.bias, self.batch_norm.weight, self.batch_norm.bias, self.batch_norm.running_mean,
-              self.batch_norm.running_var]
+        """[(first output channel, packed bf16 weights with the BatchNorm scale folded in, shift (n,) f32), ...]."""
+        ts = self._tracked() + [self.batch_norm.weight, self.batch_norm.bias, self.batch_norm.running_mean, self.batch_norm.running_var]
         key = tuple((t.data_ptr(), t._version) for t in ts)
-        if self._packed is None or self._key != key:
+        if getattr(self, "_packed", None) is None or self._key != key:
+            w, bias = self._conv_weight_bias()
             scale, bn_shift = _fold_bn(self.batch_norm)
-            shift = (self.conv.bias.detach().double() * scale.double() + bn_shift.double()).float().contiguous()
-            self._packed = (ops.conv2d_pack_weights(self.conv.weight, scale), shift)
-            self._key = key
+            shift = (bias.detach().double() * scale.double() + bn_shift.double()).float().contiguous()
+            parts, o = [], 0
+            while o < self.cout:
+                n = min(128 if self.cout - o != 192 else 192, self.cout - o)
+                parts.append((o, ops.conv2d_pack_weights(w[o:o + n].contiguous(), scale[o:o + n].contiguous()), shift[o:o + n].contiguous()))
+                o += n
+            self._packed, self._key = parts, key
         return self._packed
 
     def forward_nhwc(self, x_nhwc: torch.Tensor, out=None, workspace=None) -> torch.Tensor:
         """(B,H,W,cin) bf16 contiguous -> (B,H,W,cout) bf16."""
         if self.training:
-            raise NotImplementedError("ConvMD2d implements eval-mode BatchNorm (inference); train the RPN on stock PyTorch")
-        packed, shift = self.folded()
-        return ops.conv2d_bn_relu_fwd(x_nhwc, packed, shift, out=out, workspace=workspace)
+            raise NotImplementedError("%s implements eval-mode BatchNorm (inference); train the RPN on stock PyTorch" % type(self).__name__)
+        B, H, W, _ = x_nhwc.shape
+        if out is None:
+            out = torch.empty((B, H, W, self.cout), dtype=torch.bfloat16, device=x_nhwc.device)
+        if workspace is None:
+            workspace = torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x_nhwc.device)
+        for o, packed, shift in self.folded():
+            ops.conv2d_bn_relu_fwd(x_nhwc, packed, shift, out=out, workspace=workspace, channel_offset=o)
+        return out
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
         """(B,cin,H,W) bf16, channels_last memory -> (B,cout,H,W) bf16, channels_last memory."""
         if x.dtype != torch.bfloat16 or not x.is_contiguous(memory_format=torch.channels_last):
             x = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
         return self.forward_nhwc(x.permute(0, 2, 3, 1)).permute(0, 3, 1, 2)
+
+
+class ConvMD2d(_Conv3x3BnRelu):
+    """model.py:111-167, 2-D case, kernel 3, stride 1, padding 1, BatchNorm + ReLU; cin in {64,128}, cout a multiple of 64."""
+
+    def __init__(self, cin: int, cout: int):
+        super().__init__()
+        if cin not in (64, 128) or cout % 64 != 0 or cout < 64:
+            raise ValueError("ConvMD2d: cin=%d, cout=%d unsupported by the B200 kernel (cin 64/128, cout a multiple of 64)" % (cin, cout))
+        self.cin, self.cout = cin, cout
+        self.conv = nn.Conv2d(cin, cout, 3, 1, 1)
+        self.batch_norm = nn.BatchNorm2d(cout)
+
+    @classmethod
+    def from_reference(cls, layer) -> "ConvMD2d":
+        """A reference `ConvMD(2, ...)` (or anything with `.conv` Conv2d and `.batch_norm` BatchNorm2d) -> ConvMD2d sharing
+        its parameter values."""
+        conv = getattr(layer, "conv", None)
+        if not isinstance(conv, nn.Conv2d) or tuple(conv.kernel_size) != (3, 3) or tuple(conv.stride) != (1, 1) or tuple(conv.padding) != (1, 1):
+            raise ValueError("ConvMD2d covers 3x3 / stride 1 / padding 1 Conv2d layers only")
+        m = cls(conv.in_channels, conv.out_channels)
+        m.load_state_dict(layer.state_dict())
+        return m.to(conv.weight.device).eval()
+
+    def _conv_weight_bias(self):
+        return self.conv.weight.detach().float(), self.conv.bias
+
+    def _tracked(self):
+        return [self.conv.weight, self.conv.bias]
+
+
+class DeConvMD2d(_Conv3x3BnRelu):
+    """model.py:170-199 for kernel 3, stride 1, padding 1 (`deconv1 = DeConv2d(128, 256, 3, (1,1), (1,1))`, model.py:229):
+    ConvTranspose2d -> BatchNorm2d -> ReLU.  A stride-1 transposed convolution is the convolution with the kernel flipped
+    and its channel axes swapped, so it runs on the same kernel.  Parameter names as in the reference (`deconv.*`,
+    `batch_norm.*`)."""
+
+    def __init__(self, cin: int, cout: int):
+        super().__init__()
+        if cin not in (64, 128) or cout % 64 != 0 or cout < 64:
+            raise ValueError("DeConvMD2d: cin=%d, cout=%d unsupported by the B200 kernel" % (cin, cout))
+        self.cin, self.cout = cin, cout
+        self.deconv = nn.ConvTranspose2d(cin, cout, 3, 1, 1)
+        self.batch_norm = nn.BatchNorm2d(cout)
+
+    @classmethod
+    def from_reference(cls, layer) -> "DeConvMD2d":
+        d = getattr(layer, "deconv", None)
+        if not isinstance(d, nn.ConvTranspose2d) or tuple(d.kernel_size) != (3, 3) or tuple(d.stride) != (1, 1) or tuple(d.padding) != (1, 1) \
+                or tuple(d.output_padding) != (0, 0):
+            raise ValueError("DeConvMD2d covers 3x3 / stride 1 / padding 1 ConvTranspose2d layers only")
+        m = cls(d.in_channels, d.out_channels)
+        m.load_state_dict(layer.state_dict())
+        return m.to(d.weight.device).eval()
+
+    def _conv_weight_bias(self):
+        return self.deconv.weight.detach().float().permute(1, 0, 2, 3).flip(2, 3).contiguous(), self.deconv.bias
+
+    def _tracked(self):
+        return [self.deconv.weight, self.deconv.bias]
 
 
 class RPNBlockTail(nn.Module):
