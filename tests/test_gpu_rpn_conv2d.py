@@ -103,7 +103,9 @@ def test_rpn_block_tail_matches_the_reference_block(cuda_device):
     with torch.no_grad():
         want = block.double()(x.double())
     tail = vn.RPNBlockTail(block.float().to(cuda_device))
-    assert [type(m).__name__ for m in tail.layers] == ["RefConvMD2d", "ConvMD2d", "ConvMD2d", "ConvMD2d"]
+    assert [type(m).__name__ for m in tail.fast] == ["Identity", "ConvMD2d", "ConvMD2d", "ConvMD2d"]
+    assert tail.on_tensor_cores(96) == [False, True, True, True]
+    assert block[0].conv.weight.dtype == torch.float32  # the caller's module is left alone
     with torch.no_grad():
         got = tail(x.to(cuda_device))
     assert got.shape == (2, 128, 40, 48) and got.dtype == torch.bfloat16
@@ -137,3 +139,72 @@ def test_front_end_bf16_output_feeds_a_conv2d_layer(cuda_device):
     b = vn.ConvMD2d.from_reference(ref_p.eval())(fe16.forward_frames(frames))
     # (the K order of the two sums differs by the channel permutation: equal up to a bf16 ulp of the output)
     assert rel_max_err(a.float().cpu(), b.float().cpu()) < 5e-3
+
+
+class RefRPN(nn.Module):
+    """The RPN half of the reference's MiddleConvNet for Car (model.py:212-254, forward :263-281), same attribute names."""
+
+    def __init__(self):
+        super().__init__()
+
+        class DeConv(nn.Module):
+            def __init__(self, cin, cout, k, s, p):
+                super().__init__()
+                self.deconv = nn.ConvTranspose2d(cin, cout, k, s, p)
+                self.batch_norm = nn.BatchNorm2d(cout)
+
+            def forward(self, x):
+                return F.relu(self.batch_norm(self.deconv(x)))
+
+        class Head(nn.Module):
+            def __init__(self, cin, cout):
+                super().__init__()
+                self.conv = nn.Conv2d(cin, cout, 1, 1, 0)
+
+            def forward(self, x):
+                return self.conv(x)
+
+        self.block1 = nn.Sequential(RefConvMD2d(128, 128, 3, 2, 1), *[RefConvMD2d(128, 128) for _ in range(4)])
+        self.deconv1 = DeConv(128, 256, 3, 1, 1)
+        self.block2 = nn.Sequential(RefConvMD2d(128, 128, 3, 2, 1), *[RefConvMD2d(128, 128) for _ in range(5)])
+        self.deconv2 = DeConv(128, 256, 2, 2, 0)
+        self.block3 = nn.Sequential(RefConvMD2d(128, 256, 3, 2, 1), *[RefConvMD2d(256, 256) for _ in range(5)])
+        self.deconv3 = DeConv(256, 256, 4, 4, 0)
+        self.prob_conv, self.reg_conv = Head(768, 2), Head(768, 14)
+
+    def forward(self, x):
+        x = self.block1(x)
+        d1 = self.deconv1(x)
+        x = self.block2(x)
+        d2 = self.deconv2(x)
+        x = self.block3(x)
+        d3 = self.deconv3(x)
+        x = torch.cat([d3, d2, d1], dim=1)
+        return torch.sigmoid(self.prob_conv(x)), self.reg_conv(x)
+
+
+def test_hybrid_rpn_matches_the_fp32_rpn(cuda_device):
+    """HybridRPN (block1 / block2 tails and deconv1 on the tcgen05 kernel, the rest stock bf16) against the float32 RPN of
+    the same parameters: 20 bf16 layers deep, so the bar is rel-L2 <= 2e-2 on the regression map and 2e-2 absolute on
+    the probabilities; the all-stock bf16 RPN is held to the same bar as a yardstick."""
+    import voxelnet_pytorch_b200 as vn
+
+    g = torch.Generator().manual_seed(9)
+    ref = _randomise(RefRPN(), g)
+    x = torch.randn((2, 128, 128, 96), generator=g).relu()
+    with torch.no_grad():
+        p_want, r_want = ref(x)
+    rpn = vn.HybridRPN(ref.to(cuda_device))
+    assert rpn.block1.on_tensor_cores(96) == [False, True, True, True, True]
+    assert rpn.block2.on_tensor_cores(48) == [False, True, True, True, True, True]
+    assert not any(rpn.block3.on_tensor_cores(24))
+    assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and not isinstance(rpn.deconv_fast[1], vn.DeConvMD2d)
+    with torch.no_grad():
+        p_got, r_got = rpn(x.to(cuda_device))
+        stock = ref.to(dtype=torch.bfloat16, memory_format=torch.channels_last)
+        p_st, r_st = stock(x.to(cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
+    assert p_got.shape == (2, 2, 64, 48) and r_got.shape == (2, 14, 64, 48) and p_got.dtype == torch.float32
+    for name, got in (("hybrid", (p_got, r_got)), ("stock bf16", (p_st.float(), r_st.float()))):
+        p, r = got[0].cpu(), got[1].cpu()
+        assert float((p - p_want).abs().max()) < 2e-2, name
+        assert float((r - r_want).norm() / r_want.norm()) < 2e-2, name

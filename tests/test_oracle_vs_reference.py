@@ -131,3 +131,20 @@ def test_target_assignment_against_live_reference():
     c = T.anchor_config("Car")
     gp, gn, gt = OT.generate_targets(boxes, anchors.shape[:2], anchors, c.rpn_pos_iou, c.rpn_neg_iou, c.anchor_h)
     assert np.array_equal(gp, wp) and np.array_equal(gn, wn) and np.array_equal(gt, wt) and wp.sum() > 0
+
+
+def test_hybrid_rpn_wraps_the_live_reference_rpn():
+    """HybridRPN takes the unmodified reference's MiddleConvNet: the attribute and parameter names it relies on exist, and
+    it picks the layers the tcgen05 kernel covers (block1 / block2 stride-1 tails, deconv1).  Construction only - the
+    kernels need a GPU (tests/test_gpu_rpn_conv2d.py)."""
+    import voxelnet_pytorch_b200 as vn
+
+    ref = R.load_reference()
+    net = ref.model.MiddleConvNet().eval()
+    rpn = vn.HybridRPN(net)
+    assert rpn.block1.on_tensor_cores(352) == [False, True, True, True, True]
+    assert rpn.block2.on_tensor_cores(176) == [False, True, True, True, True, True]
+    assert not any(rpn.block3.on_tensor_cores(88))
+    assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and not isinstance(rpn.deconv_fast[2], vn.DeConvMD2d)
+    assert set(rpn.block1.fast[1].state_dict()) == set(net.block1[1].state_dict())
+    assert net.block1[0].conv.weight.dtype == torch.float32

@@ -68,3 +68,42 @@ for name, H, W, L in (("block1_tail", 200, 176, 4), ("block2_tail", 100, 88, 5))
     print(name, out[name])
 if len(sys.argv) > 1:
     json.dump(out, open(sys.argv[1], 'w'), indent=1)
+
+# ---- the whole RPN half (model.py:212-254, :263-281), Car, batch 16: hybrid vs stock ---------------------------------------
+sys.path.insert(0, '/root/repo/tests')
+from test_gpu_rpn_conv2d import RefRPN, _randomise  # the reference's RPN architecture restated with its attribute names
+
+g = torch.Generator().manual_seed(1)
+ref_rpn = _randomise(RefRPN(), g).to(dev)
+hyb = vn.HybridRPN(ref_rpn)
+import copy
+
+stock16 = copy.deepcopy(ref_rpn).to(dtype=torch.bfloat16, memory_format=torch.channels_last)
+x32 = torch.randn(16, 128, 400, 352, device=dev).relu()
+x16 = x32.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+with torch.no_grad():
+    p0, r0 = ref_rpn(x32[:2])
+    p1, r1 = hyb(x16[:2])
+    t_h = timed(lambda: hyb(x16), 10)
+    t_s = timed(lambda: stock16(x16), 10)
+    t_f = timed(lambda: ref_rpn(x32), 5)
+out["rpn_car16"] = {"ms_hybrid_tcgen05": t_h, "ms_stock_bf16_nhwc": t_s, "ms_stock_fp32": t_f,
+                    "reg_rel_l2_vs_fp32": float((r1 - r0).norm() / r0.norm()), "prob_max_abs_err": float((p1 - p0).abs().max()),
+                    "layers_on_tcgen05": "block1[1:5], block2[1:6], deconv1 (75 of ~110 GFLOP per frame)"}
+print("rpn_car16", out["rpn_car16"])
+
+# ---- points -> RPN maps: the fused front end (bf16 channels-last output) + the hybrid RPN, one step at a time ----------------
+from voxelnet_pytorch_b200 import synth
+
+fnet, mnet = vn.FeatureLearningNet('Car').eval().to(dev), vn.MiddleConvNet().eval().to(dev)
+fe = vn.VoxelNetFrontEnd(fnet, mnet, 'Car', output_format="nhwc_bf16")
+hyb.permute_input_channels(fe.reference_channel_of_output())
+pts, offs, max_n = vn.pack_frames(synth.lidar_batch(16, seed0=0))
+with torch.no_grad():
+    t_all = timed(lambda: hyb(fe.forward_points(pts, offs, max_n)), 10)
+    t_fe = timed(lambda: fe.forward_points(pts, offs, max_n), 10)
+out["points_to_rpn_maps_car16"] = {"ms_per_batch": t_all, "frames_per_s": 16 / t_all * 1e3, "ms_front_end_alone": t_fe,
+                                   "note": "eager launches on one stream; front end returns bf16 channels-last, RPN = HybridRPN"}
+print("points_to_rpn_maps_car16", out["points_to_rpn_maps_car16"])
+if len(sys.argv) > 1:
+    json.dump(out, open(sys.argv[1], 'w'), indent=1)

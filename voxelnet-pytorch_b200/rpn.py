@@ -12,7 +12,8 @@ stride-1 transposed convolution is a convolution with the flipped kernel.  Toget
 
 The stride-2 layers, the `256`-channel block 3 (W = 44 is not a multiple of the 8-wide tile), the two strided
 `ConvTranspose2d` and the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
-wraps a reference block so that its head runs on stock PyTorch and its stride-1 tail here.
+wraps a reference block so that its head runs on stock PyTorch and its stride-1 tail here, `HybridRPN` the whole RPN half
+of the reference's `MiddleConvNet`.
 """
 from __future__ import annotations
 
@@ -133,31 +134,107 @@ class DeConvMD2d(_Conv3x3BnRelu):
         return [self.deconv.weight, self.deconv.bias]
 
 
+def _stock_bf16(layer: nn.Module) -> nn.Module:
+    """A private bf16 channels-last copy of a stock layer (the caller's module is left as it is)."""
+    import copy
+
+    return copy.deepcopy(layer).to(dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
+
+
+def _as_bf16_nhwc(x: torch.Tensor) -> torch.Tensor:
+    if x.dtype != torch.bfloat16 or not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
+    return x
+
+
 class RPNBlockTail(nn.Module):
     """A reference RPN block (`nn.Sequential` of ConvMD(2, ...), model.py:212-251) with its stride-1 3x3 layers on the
-    tcgen05 kernel; layers the kernel does not cover (the stride-2 head) run as they are, in bf16 channels-last."""
+    tcgen05 kernel; layers the kernel does not cover (the stride-2 head, 256-channel inputs, widths that are not a
+    multiple of 8) run on a private bf16 channels-last copy of the stock layer."""
 
     def __init__(self, block: nn.Sequential):
         super().__init__()
-        layers = []
+        fast, stock = [], []
         for layer in block:
             try:
-                layers.append(ConvMD2d.from_reference(layer))
+                fast.append(ConvMD2d.from_reference(layer))
             except ValueError:
-                layers.append(layer.to(dtype=torch.bfloat16, memory_format=torch.channels_last))
-        self.layers = nn.ModuleList(layers)
+                fast.append(None)
+            stock.append(_stock_bf16(layer))
+        self.stock = nn.ModuleList(stock)
+        self.fast = nn.ModuleList([m if m is not None else nn.Identity() for m in fast])
+        self._ws = None
+
+    def on_tensor_cores(self, width: int) -> list:
+        """Which layers run on the tcgen05 kernel for an input of this width (after the block's own strides)."""
+        out, w = [], width
+        for f, s in zip(self.fast, self.stock):
+            w = w // int(s.conv.stride[1]) if hasattr(s, "conv") else w
+            out.append(isinstance(f, ConvMD2d) and w % 8 == 0)
+        return out
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
-        x = x.to(torch.bfloat16).contiguous(memory_format=torch.channels_last)
-        ws = None
-        for layer in self.layers:
-            if isinstance(layer, ConvMD2d):
-                B, _, H, W = x.shape
-                if W % 8 != 0:
-                    raise ValueError("ConvMD2d needs W % 8 == 0; got W=%d" % W)
-                if ws is None or ws[0] != (B, H, W):
-                    ws = ((B, H, W), torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device))
-                x = layer.forward_nhwc(x.permute(0, 2, 3, 1), workspace=ws[1]).permute(0, 3, 1, 2)
+        x = _as_bf16_nhwc(x)
+        for f, s in zip(self.fast, self.stock):
+            B, _, H, W = x.shape
+            if isinstance(f, ConvMD2d) and W % 8 == 0:
+                if self._ws is None or self._ws[0] != (B, H, W, x.device):
+                    self._ws = ((B, H, W, x.device), torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device))
+                x = f.forward_nhwc(x.permute(0, 2, 3, 1), workspace=self._ws[1]).permute(0, 3, 1, 2)
             else:
-                x = layer(x)
+                x = s(x)
         return x
+
+
+class HybridRPN(nn.Module):
+    """The RPN half of the reference's `MiddleConvNet` (model.py:212-254, forward :263-281) in bf16 channels-last, with the
+    layers the tcgen05 kernel covers running on it - the stride-1 3x3 layers of block1 / block2 and deconv1, 75 of the
+    ~110 GFLOP per Car frame - and everything else (stride-2 heads, block3, deconv2 / deconv3, the 1x1 heads, the
+    concatenation, the sigmoid) on private bf16 copies of the stock PyTorch layers.
+
+        rpn = HybridRPN(reference_model.middle_rpn)                 # eval mode; parameters are copied
+        fe = VoxelNetFrontEnd(fnet, mnet, 'Car', output_format="nhwc_bf16")
+        rpn.permute_input_channels(fe.reference_channel_of_output())
+        prob, reg = rpn(fe.forward_frames(frames))                  # (B,2,H/2,W/2), (B,14,H/2,W/2) float32
+
+    `middle_rpn` is anything with the reference's attribute names: block1..3 (Sequential of ConvMD(2,..)), deconv1..3
+    (DeConv2d), prob_conv, reg_conv."""
+
+    def __init__(self, middle_rpn: nn.Module):
+        super().__init__()
+        self.block1, self.block2, self.block3 = (RPNBlockTail(getattr(middle_rpn, n)) for n in ("block1", "block2", "block3"))
+        self.deconv_stock = nn.ModuleList([_stock_bf16(getattr(middle_rpn, n)) for n in ("deconv1", "deconv2", "deconv3")])
+        fast = []
+        for n in ("deconv1", "deconv2", "deconv3"):
+            try:
+                fast.append(DeConvMD2d.from_reference(getattr(middle_rpn, n)))
+            except ValueError:
+                fast.append(nn.Identity())
+        self.deconv_fast = nn.ModuleList(fast)
+        self.prob_conv, self.reg_conv = _stock_bf16(middle_rpn.prob_conv), _stock_bf16(middle_rpn.reg_conv)
+
+    def permute_input_channels(self, reference_channel_of_input: torch.Tensor) -> None:
+        """The input's channel k holds the reference's channel reference_channel_of_input[k] (VoxelNetFrontEnd
+        .reference_channel_of_output()): permute the input channels of block1's first layer once, so that the block sees
+        the same convolution."""
+        perm = reference_channel_of_input.to(self.block1.stock[0].conv.weight.device)
+        for m in (self.block1.stock[0], self.block1.fast[0]):
+            if hasattr(m, "conv"):
+                m.conv.weight.data = m.conv.weight.data[:, perm].contiguous()
+
+    def _deconv(self, i: int, x: torch.Tensor) -> torch.Tensor:
+        f = self.deconv_fast[i]
+        if isinstance(f, DeConvMD2d) and x.shape[3] % 8 == 0:
+            return f(x)
+        return self.deconv_stock[i](x)
+
+    def forward(self, x: torch.Tensor):
+        x = _as_bf16_nhwc(x)
+        x = self.block1(x)
+        d1 = self._deconv(0, x)
+        x = self.block2(x)
+        d2 = self._deconv(1, x)
+        x = self.block3(x)
+        d3 = self._deconv(2, x)
+        x = torch.cat([d3, d2, d1], dim=1)  # model.py:272-274
+        return torch.sigmoid(self.prob_conv(x).float()), self.reg_conv(x).float()
