@@ -134,11 +134,45 @@ class DeConvMD2d(_Conv3x3BnRelu):
         return [self.deconv.weight, self.deconv.bias]
 
 
-def _stock_bf16(layer: nn.Module) -> nn.Module:
-    """A private bf16 channels-last copy of a stock layer (the caller's module is left as it is)."""
-    import copy
+class _FoldedStock(nn.Module):
+    """A stock layer for inference: Conv2d / ConvTranspose2d with the eval-mode BatchNorm folded into its weights and bias
+    (one cuDNN call + an in-place ReLU instead of three passes over the activation), bf16 channels-last."""
 
-    return copy.deepcopy(layer).to(dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
+    def __init__(self, op: nn.Module, bn, relu: bool):
+        super().__init__()
+        import copy
+
+        op = copy.deepcopy(op).float()
+        if bn is not None:
+            scale, shift = _fold_bn(bn)
+            scale, shift = scale.to(op.weight.device), shift.to(op.weight.device)
+            shape = (1, -1, 1, 1) if isinstance(op, nn.ConvTranspose2d) else (-1, 1, 1, 1)
+            op.weight.data = op.weight.data * scale.view(shape)
+            op.bias.data = op.bias.data * scale + shift
+        self.op = op.to(dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
+        self.relu = relu
+        self.stride = tuple(op.stride)
+
+    @property
+    def conv(self):  # (the attribute RPNBlockTail / permute_input_channels look at)
+        return self.op
+
+    def forward(self, x):
+        y = self.op(x)
+        return torch.relu_(y) if self.relu else y
+
+
+def _stock_bf16(layer: nn.Module) -> nn.Module:
+    """A private bf16 channels-last inference copy of a reference ConvMD(2, ...) / DeConv2d (model.py:111-199); the
+    caller's module is left as it is."""
+    op = getattr(layer, "conv", None) or getattr(layer, "deconv", None)
+    if op is None:
+        import copy
+
+        return copy.deepcopy(layer).to(dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
+    bn = getattr(layer, "batch_norm", None) if getattr(layer, "bn", True) else None
+    relu = bool(getattr(layer, "activation", True))
+    return _FoldedStock(op, bn, relu)
 
 
 def _as_bf16_nhwc(x: torch.Tensor) -> torch.Tensor:
@@ -169,7 +203,7 @@ class RPNBlockTail(nn.Module):
         """Which layers run on the tcgen05 kernel for an input of this width (after the block's own strides)."""
         out, w = [], width
         for f, s in zip(self.fast, self.stock):
-            w = w // int(s.conv.stride[1]) if hasattr(s, "conv") else w
+            w = w // int(s.conv.stride[1])
             out.append(isinstance(f, ConvMD2d) and w % 8 == 0)
         return out
 
@@ -211,7 +245,15 @@ class HybridRPN(nn.Module):
             except ValueError:
                 fast.append(nn.Identity())
         self.deconv_fast = nn.ModuleList(fast)
-        self.prob_conv, self.reg_conv = _stock_bf16(middle_rpn.prob_conv), _stock_bf16(middle_rpn.reg_conv)
+        # the two 1x1 heads read the same 768-channel tensor: one convolution with their weights stacked (2 + 14 outputs)
+        import copy
+
+        pc, rc = middle_rpn.prob_conv.conv, middle_rpn.reg_conv.conv
+        head = nn.Conv2d(pc.in_channels, pc.out_channels + rc.out_channels, 1, 1, 0)
+        head.weight.data = torch.cat([pc.weight.data, rc.weight.data], 0).clone()
+        head.bias.data = torch.cat([pc.bias.data, rc.bias.data], 0).clone()
+        self.heads = head.to(device=pc.weight.device, dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
+        self.n_prob = pc.out_channels
 
     def permute_input_channels(self, reference_channel_of_input: torch.Tensor) -> None:
         """The input's channel k holds the reference's channel reference_channel_of_input[k] (VoxelNetFrontEnd
@@ -237,4 +279,5 @@ class HybridRPN(nn.Module):
         x = self.block3(x)
         d3 = self._deconv(2, x)
         x = torch.cat([d3, d2, d1], dim=1)  # model.py:272-274
-        return torch.sigmoid(self.prob_conv(x).float()), self.reg_conv(x).float()
+        y = self.heads(x).float()
+        return torch.sigmoid(y[:, : self.n_prob]).contiguous(), y[:, self.n_prob:].contiguous()
