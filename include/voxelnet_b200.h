@@ -274,23 +274,26 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
 /* ------------------------------------------------------------------------------------------
  * 2-D 3x3 convolution + BatchNorm2d(eval) + ReLU on the same tcgen05 kernel - the stride-1 ConvMD(2, 128, 128, 3, (1,1),
  * (1,1)) layers of the RPN blocks (voxelnet/model.py:212-251).  Channels-last bf16 in and out:
- *   x [B, H, W, cin] -> y [B, H, W, cout],  y = relu(conv(x, weight * scale) + shift),  cin in {64, 128}, cout in
- *   {64, 128, 192}, W % 8 == 0.  The groups of 64 output channels ride along the MMA's N dimension the way the depth
+ *   x [B, H, W, cin] -> y [B, H, W, cout],  y = relu(conv(x, weight * scale) + shift),  cin in {64, 128, 256}, cout in
+ *   {64, 128, 192} per launch, any W (the last 8-wide tile column may be ragged).  The groups of 64 output channels ride along the MMA's N dimension the way the depth
  *   taps of the 3-D layers do (one 128 x cout x 16 MMA per k-step).
  * vn_conv2d_pack_weights: weight [cout][cin][3][3] f32 (torch layout), scale [cout] = BatchNorm gamma / sqrt(var + eps) or
  *   NULL; packed: vn_conv2d_packed_weight_bytes(cin) bytes.  shift [cout] = beta + (bias - mean) * scale.
  * y has y_channels channels per position and the launch writes channels y_channel_offset .. + cout of it (a 256-channel
  *   layer is two launches of 128 into one tensor; ConvTranspose2d(k 3, stride 1, padding 1) = this convolution with the
  *   kernel flipped and its channel axes swapped: voxelnet/model.py:229 deconv1).
- * workspace: vn_conv3d_workspace_bytes(B, H, W).  Stride-2 layers, the strided deconvolutions and the 1x1 heads are not
+ * planned != 0: `workspace` still holds the work plan of an earlier launch with the same B, H, W and cout (the plan of a dense
+ *   2-D layer depends on nothing else) - it is reused instead of rebuilt.
+ * workspace: vn_conv2d_workspace_bytes(B, H, W).  Stride-2 layers, the strided deconvolutions and the 1x1 heads are not
  * covered. */
+size_t vn_conv2d_workspace_bytes(int32_t B, int32_t H, int32_t W);
 size_t vn_conv2d_packed_weight_bytes(int32_t cin);
 int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, void* packed,
                            vn_stream_t stream);
 int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout,
                           const void* packed_weight, const float* shift, void* y, int32_t y_channels,
-                          int32_t y_channel_offset, void* workspace, size_t workspace_bytes,
-                          vn_stream_t stream);
+                          int32_t y_channel_offset, int32_t planned, void* workspace,
+                          size_t workspace_bytes, vn_stream_t stream);
 
 /* Background folding for a layer whose INPUT is stored as a deviation from a background (what the previous
  * layer outputs wherever ITS input was all background; NULL = zero background).  The reference zero-pads, so

@@ -37,7 +37,8 @@ def _randomise(m, g):
     return m.eval()
 
 
-@pytest.mark.parametrize("cin,cout,B,H,W", [(128, 128, 2, 24, 16), (64, 64, 1, 16, 8), (128, 192, 1, 37, 24), (64, 128, 3, 100, 88)])
+@pytest.mark.parametrize("cin,cout,B,H,W", [(128, 128, 2, 24, 16), (64, 64, 1, 16, 8), (128, 192, 1, 37, 24), (64, 128, 3, 100, 88),
+                                              (256, 256, 2, 50, 44), (128, 64, 1, 9, 13)])
 def test_conv2d_bn_relu_matches_torch(cuda_device, cin, cout, B, H, W):
     import voxelnet_pytorch_b200 as vn
 
@@ -60,7 +61,8 @@ def test_conv2d_bn_relu_matches_torch(cuda_device, cin, cout, B, H, W):
     got64 = got.cpu().double()
     assert rel_max_err(got64, want) < 1e-2
     ulp = exact.abs().clamp_min(2.0 ** -100) * 2.0 ** -7  # one bf16 ulp is at most 2^-7 of the value
-    assert bool(((got64 - exact).abs() <= ulp + 1e-6).all()), float(((got64 - exact).abs() - ulp).max())
+    # (+ 2e-5: fp32 accumulation over up to 2,304 products before the rounding to bf16)
+    assert bool(((got64 - exact).abs() <= ulp + 2e-5).all()), float(((got64 - exact).abs() - ulp).max())
 
 
 @pytest.mark.parametrize("cin,cout,H,W", [(128, 256, 40, 32), (64, 192, 20, 16)])
@@ -103,6 +105,7 @@ def test_rpn_block_tail_matches_the_reference_block(cuda_device):
     with torch.no_grad():
         want = block.double()(x.double())
     tail = vn.RPNBlockTail(block.float().to(cuda_device))
+    tail.min_tiles = 0  # (a map this small would otherwise take the stock path)
     assert [type(m).__name__ for m in tail.fast] == ["Identity", "ConvMD2d", "ConvMD2d", "ConvMD2d"]
     assert tail.on_tensor_cores(96) == [False, True, True, True]
     assert block[0].conv.weight.dtype == torch.float32  # the caller's module is left alone
@@ -195,16 +198,19 @@ def test_hybrid_rpn_matches_the_fp32_rpn(cuda_device):
     with torch.no_grad():
         p_want, r_want = ref(x)
     rpn = vn.HybridRPN(ref.to(cuda_device))
+    rpn.set_min_tiles(0)  # (maps this small would otherwise take the stock path)
     assert rpn.block1.on_tensor_cores(96) == [False, True, True, True, True]
     assert rpn.block2.on_tensor_cores(48) == [False, True, True, True, True, True]
-    assert not any(rpn.block3.on_tensor_cores(24))
+    assert rpn.block3.on_tensor_cores(24) == [False, True, True, True, True, True]  # 256 channels, W = 12: ragged tile column
     assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and not isinstance(rpn.deconv_fast[1], vn.DeConvMD2d)
     with torch.no_grad():
         p_got, r_got = rpn(x.to(cuda_device))
         stock = ref.to(dtype=torch.bfloat16, memory_format=torch.channels_last)
         p_st, r_st = stock(x.to(cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
+        rpn.set_min_tiles(None)
+        p_auto, r_auto = rpn(x.to(cuda_device))  # default policy: these small maps run on the stock copies
     assert p_got.shape == (2, 2, 64, 48) and r_got.shape == (2, 14, 64, 48) and p_got.dtype == torch.float32
-    for name, got in (("hybrid", (p_got, r_got)), ("stock bf16", (p_st.float(), r_st.float()))):
+    for name, got in (("hybrid", (p_got, r_got)), ("hybrid, default tile policy", (p_auto, r_auto)), ("stock bf16", (p_st.float(), r_st.float()))):
         p, r = got[0].cpu(), got[1].cpu()
         assert float((p - p_want).abs().max()) < 2e-2, name
         assert float((r - r_want).norm() / r_want.norm()) < 2e-2, name

@@ -922,7 +922,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
 #pragma unroll
             for (int j = 0; j < 32; ++j) r[j] = 0u;
           }
-          if (inside && !no_store) {
+          if (inside && w < P.W && !no_store) {  // (w >= W: the 2-D layers allow a ragged last tile column)
             const float* shift_row = (variant == 0 || P.table_smem) ? ctl->table + (variant * P.Dout + dout) * 64 + half * 32
                                                                     : P.table + (variant * P.Dout + dout) * 64 + half * 32;
             const float* sub_row = (variant == 0 || P.sub_classes == 1) ? ctl->sub + dout * 64 + half * 32
@@ -1406,13 +1406,13 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                        vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr,
                        int32_t groups2d = 0, int32_t out_ctotal = 0, int32_t out_coff = 0) {
   VN_REQUIRE((x || gather) && packed_weight && scale && shift_table && y, "conv3d: null pointer");
-  VN_REQUIRE(cin == 64 || cin == 128, "conv3d: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(cin == 64 || cin == 128 || (groups2d > 0 && cin == 256), "conv3d: cin=%d (supported: 64, 128; 2-D layers also 256)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
   VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d: stride_d=%d pad_d=%d unsupported",
              stride_d, pad_d);
   VN_REQUIRE(out_mode == 0 || out_mode == 1 || out_mode == 2, "conv3d: out_mode=%d", out_mode);
-  VN_REQUIRE(W % kTileW == 0 && W / kTileW <= kMaxTilesW, "conv3d: W=%d must be a multiple of %d, at most %d", W, kTileW,
-             kTileW * kMaxTilesW);
+  VN_REQUIRE((W % kTileW == 0 || groups2d > 0) && (W + kTileW - 1) / kTileW <= kMaxTilesW,
+             "conv3d: W=%d must be a multiple of %d (3-D layers), at most %d", W, kTileW, kTileW * kMaxTilesW);
   VN_REQUIRE(Din <= kMaxPlanes, "conv3d: Din=%d exceeds %d", Din, kMaxPlanes);
   VN_REQUIRE(groups2d == 0 || (Din == 1 && groups2d >= 1 && groups2d <= 3), "conv2d: %d output channel groups (1..3), Din=%d", groups2d, Din);
   const int Dout = groups2d > 0 ? groups2d : (transposed_dout > 0 ? transposed_dout : out_depth(Din, stride_d, pad_d));
@@ -1427,7 +1427,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
              "conv3d: buffers must be 16-byte aligned");
   VN_REQUIRE(workspace != nullptr && (reinterpret_cast<uintptr_t>(workspace) & 15) == 0, "conv3d: workspace missing or misaligned");
 
-  const int tiles_h = (H + kTileH - 1) / kTileH, tiles_w = W / kTileW;
+  const int tiles_h = (H + kTileH - 1) / kTileH, tiles_w = (W + kTileW - 1) / kTileW;
   const int64_t n_tiles = (int64_t)B * tiles_h * tiles_w;
   VN_REQUIRE(n_tiles < (int64_t)0x7fffffff, "conv3d: too many tiles");
   const PlanLayout L = plan_layout(n_tiles);
@@ -1475,6 +1475,10 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                     : (transposed_dout > 0 ? plan_planes_transposed(Q, stride_d, pad_d) : plan_planes(Q, stride_d, pad_d))) != 0) {
     set_error("conv3d: unsupported depth schedule (Din=%d stride_d=%d pad_d=%d)", Din, stride_d, pad_d);
     return VN_ERR_UNSUPPORTED;
+  }
+  if ((flag_opts & VN_CONV_FLAGS_PLANNED) && groups2d > 0) {
+    // a dense 2-D plan depends on (B, H, W, groups) only: reuse it, rewind the work counter
+    VN_CUDA(cudaMemsetAsync(&hdr->next_group, 0, sizeof(int32_t), st));
   }
   if (!(flag_opts & VN_CONV_FLAGS_PLANNED)) {  // else: vn_conv3d_plan already built the plan in this workspace
     VN_CUDA(cudaMemsetAsync(hdr, 0, sizeof(PlanHeader), st));
@@ -1628,13 +1632,18 @@ int vn_conv3d_raw_stats_fwd(const void* x, int32_t B, int32_t Din, int32_t H, in
                      flag_opts, nullptr, workspace, workspace_bytes, stream, stats);
 }
 
+size_t vn_conv2d_workspace_bytes(int32_t B, int32_t H, int32_t W) {
+  if (B < 1 || H < 1 || W < 1) return 0;
+  return plan_layout((int64_t)B * ((H + kTileH - 1) / kTileH) * ((W + kTileW - 1) / kTileW)).total;
+}
+
 size_t vn_conv2d_packed_weight_bytes(int32_t cin) {
-  if (cin != 64 && cin != 128) return 0;
+  if (cin != 64 && cin != 128 && cin != 256) return 0;
   return (size_t)(cin / 64) * 3 * kBSlotBytes + 64 * sizeof(float);
 }
 
 int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, void* packed, vn_stream_t stream) {
-  VN_REQUIRE(cin == 64 || cin == 128, "conv2d_pack_weights: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d_pack_weights: cin=%d (supported: 64, 128, 256)", cin);
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d_pack_weights: cout=%d (supported: 64, 128, 192)", cout);
   VN_REQUIRE(weight != nullptr && packed != nullptr && (reinterpret_cast<uintptr_t>(packed) & 15) == 0,
              "conv2d_pack_weights: null or misaligned pointer");
@@ -1645,17 +1654,18 @@ int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin,
 }
 
 int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout, const void* packed_weight,
-                          const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset, void* workspace,
-                          size_t workspace_bytes, vn_stream_t stream) {
+                          const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset, int32_t planned,
+                          void* workspace, size_t workspace_bytes, vn_stream_t stream) {
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d: cout=%d (supported: 64, 128, 192)", cout);
-  VN_REQUIRE(cin == 64 || cin == 128, "conv2d: cin=%d (supported: 64, 128)", cin);
+  VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d: cin=%d (supported: 64, 128, 256)", cin);
   VN_REQUIRE(packed_weight != nullptr && shift != nullptr, "conv2d: null pointer");
   VN_REQUIRE(y_channels >= cout && y_channel_offset >= 0 && y_channel_offset + cout <= y_channels && y_channels % 16 == 0 &&
                  y_channel_offset % 16 == 0,
              "conv2d: channels %d..%d of %d (multiples of 16 inside y)", y_channel_offset, y_channel_offset + cout, y_channels);
   const float* ones = reinterpret_cast<const float*>(static_cast<const uint8_t*>(packed_weight) + (size_t)(cin / 64) * 3 * kBSlotBytes);
-  return conv_launch(x, B, 1, H, W, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr, 0, nullptr, workspace,
-                     workspace_bytes, stream, nullptr, 0, nullptr, cout / 64, y_channels, y_channel_offset);
+  return conv_launch(x, B, 1, H, W, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr,
+                     planned ? VN_CONV_FLAGS_PLANNED : 0, nullptr, workspace, workspace_bytes, stream, nullptr, 0, nullptr, cout / 64,
+                     y_channels, y_channel_offset);
 }
 
 }  // extern "C"

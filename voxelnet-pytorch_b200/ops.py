@@ -463,6 +463,10 @@ def conv3d_bn_relu_fwd_rows(grid, rows, voxel_offsets, n_points_total: int, vox_
 # ---------------------------------------------------------------------------------------------
 # 2-D 3x3 convolution (RPN blocks, model.py:212-251) on the same tcgen05 kernel
 # ---------------------------------------------------------------------------------------------
+def conv2d_workspace_bytes(B: int, H: int, W: int) -> int:
+    return int(_cabi.lib().vn_conv2d_workspace_bytes(B, H, W))
+
+
 def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
     """weight (cout,cin,3,3) f32 [* scale (cout,): BatchNorm folded in] -> the packed bf16 image of vn_conv2d_bn_relu_fwd."""
     _require_cuda(weight, scale)
@@ -472,7 +476,7 @@ def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
         raise RuntimeError("conv2d_pack_weights: 3x3 kernels only; got %s" % (tuple(w.shape),))
     nbytes = int(_cabi.lib().vn_conv2d_packed_weight_bytes(cin))
     if nbytes == 0:
-        raise RuntimeError("conv2d_pack_weights: cin=%d unsupported (64, 128)" % cin)
+        raise RuntimeError("conv2d_pack_weights: cin=%d unsupported (64, 128, 256)" % cin)
     packed = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
     with torch.cuda.device(w.device):
         check(_cabi.lib().vn_conv2d_pack_weights(_ptr(w), _ptr(None if scale is None else _contig(scale, torch.float32)), cin, cout,
@@ -480,10 +484,11 @@ def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
     return packed
 
 
-def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channel_offset: int = 0) -> torch.Tensor:
+def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channel_offset: int = 0, planned: bool = False) -> torch.Tensor:
     """x (B,H,W,cin) bf16 channels-last -> relu(conv3x3(x) + shift) as (B,H,W,cout) bf16 (stride 1, padding 1);
     shift (cout,) f32 carries the bias and the BatchNorm shift, the BatchNorm scale sits in the packed weights.
-    `out` may have more channels than cout: the launch writes channels channel_offset .. + cout of it."""
+    `out` may have more channels than cout: the launch writes channels channel_offset .. + cout of it.  planned: `workspace`
+    holds the plan of an earlier launch with the same B, H, W and cout - reuse it."""
     _require_cuda(x, packed_weight, shift, out, workspace)
     _contig(x, torch.bfloat16), _contig(shift, torch.float32)
     B, H, W, cin = x.shape
@@ -493,10 +498,10 @@ def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channe
     elif tuple(out.shape[:3]) != (B, H, W) or out.dtype != torch.bfloat16 or not out.is_contiguous():
         raise RuntimeError("out must be a contiguous (B,H,W,C) bf16 tensor")
     if workspace is None:
-        workspace = torch.empty(conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
+        workspace = torch.empty(conv2d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
         check(_cabi.lib().vn_conv2d_bn_relu_fwd(_ptr(x), B, H, W, cin, cout, _ptr(packed_weight), _ptr(shift), _ptr(out),
-                                                int(out.shape[3]), int(channel_offset), _ptr(workspace), workspace.numel(), _stream()),
+                                                int(out.shape[3]), int(channel_offset), 1 if planned else 0, _ptr(workspace), workspace.numel(), _stream()),
               "vn_conv2d_bn_relu_fwd")
     return out
 

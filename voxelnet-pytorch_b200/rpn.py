@@ -8,10 +8,11 @@ Conv2d layers and 61 of its ~110 GFLOP per frame.  `ConvMD2d` keeps the referenc
 `VoxelNetFrontEnd(output_format="nhwc_bf16")` hands over - so a block chains without a cast or layout pass.
 
 `DeConvMD2d` is the reference's `deconv1 = DeConv2d(128, 256, 3, (1,1), (1,1))` (model.py:229; 21 GFLOP per frame): a
-stride-1 transposed convolution is a convolution with the flipped kernel.  Together: 75 of the RPN's ~110 GFLOP.
+stride-1 transposed convolution is a convolution with the flipped kernel.  The five 256 -> 256 layers of block3 run as
+two launches of 128 output channels over four 64-channel input chunks (W = 44: the last tile column is ragged).
+Together 15 of the RPN's 22 layers, 88 of its ~110 GFLOP.
 
-The stride-2 layers, the `256`-channel block 3 (W = 44 is not a multiple of the 8-wide tile), the two strided
-`ConvTranspose2d` and the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
+The three stride-2 layers, the two strided `ConvTranspose2d` and the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
 wraps a reference block so that its head runs on stock PyTorch and its stride-1 tail here, `HybridRPN` the whole RPN half
 of the reference's `MiddleConvNet`.
 """
@@ -22,6 +23,29 @@ import torch.nn as nn
 
 from . import ops
 from .model import _fold_bn
+
+
+class _PlanCache:
+    """Workspaces of the dense 2-D launches by (B, H, W, output channels of a launch): the work plan of such a launch depends
+    on nothing else, so the second and later launches of that shape reuse it (`planned`)."""
+
+    def __init__(self):
+        self._ws = {}
+
+    def get(self, B, H, W, n, device):
+        key = (B, H, W, n, str(device))
+        hit = key in self._ws
+        if not hit:
+            self._ws[key] = torch.empty(ops.conv2d_workspace_bytes(B, H, W), dtype=torch.uint8, device=device)
+        return self._ws[key], hit
+
+
+def _enough_tiles(B: int, H: int, W: int, device, min_tiles=None) -> bool:
+    """The persistent conv kernel wants a few tiles per SM; tiny feature maps (block3 at batch 16: 384 tiles on 148 SMs)
+    are faster on the stock path.  min_tiles: threshold (default 4 per SM; 0 forces the tcgen05 path)."""
+    if min_tiles is None:
+        min_tiles = 4 * (torch.cuda.get_device_properties(device).multi_processor_count if torch.cuda.is_available() else 148)
+    return B * ((H + 15) // 16) * ((W + 7) // 8) >= min_tiles
 
 
 class _Conv3x3BnRelu(nn.Module):
@@ -54,17 +78,18 @@ class _Conv3x3BnRelu(nn.Module):
             self._packed, self._key = parts, key
         return self._packed
 
-    def forward_nhwc(self, x_nhwc: torch.Tensor, out=None, workspace=None) -> torch.Tensor:
-        """(B,H,W,cin) bf16 contiguous -> (B,H,W,cout) bf16."""
+    def forward_nhwc(self, x_nhwc: torch.Tensor, out=None, plans: "_PlanCache" = None, channel_offset: int = 0) -> torch.Tensor:
+        """(B,H,W,cin) bf16 contiguous -> (B,H,W,cout) bf16 (or channels channel_offset .. + cout of a wider `out`)."""
         if self.training:
             raise NotImplementedError("%s implements eval-mode BatchNorm (inference); train the RPN on stock PyTorch" % type(self).__name__)
         B, H, W, _ = x_nhwc.shape
         if out is None:
             out = torch.empty((B, H, W, self.cout), dtype=torch.bfloat16, device=x_nhwc.device)
-        if workspace is None:
-            workspace = torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x_nhwc.device)
+        if plans is None:
+            plans = self.__dict__.setdefault("_plans", _PlanCache())
         for o, packed, shift in self.folded():
-            ops.conv2d_bn_relu_fwd(x_nhwc, packed, shift, out=out, workspace=workspace, channel_offset=o)
+            ws, planned = plans.get(B, H, W, int(shift.numel()), x_nhwc.device)
+            ops.conv2d_bn_relu_fwd(x_nhwc, packed, shift, out=out, workspace=ws, channel_offset=channel_offset + o, planned=planned)
         return out
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -75,12 +100,12 @@ class _Conv3x3BnRelu(nn.Module):
 
 
 class ConvMD2d(_Conv3x3BnRelu):
-    """model.py:111-167, 2-D case, kernel 3, stride 1, padding 1, BatchNorm + ReLU; cin in {64,128}, cout a multiple of 64."""
+    """model.py:111-167, 2-D case, kernel 3, stride 1, padding 1, BatchNorm + ReLU; cin in {64,128,256}, cout a multiple of 64."""
 
     def __init__(self, cin: int, cout: int):
         super().__init__()
-        if cin not in (64, 128) or cout % 64 != 0 or cout < 64:
-            raise ValueError("ConvMD2d: cin=%d, cout=%d unsupported by the B200 kernel (cin 64/128, cout a multiple of 64)" % (cin, cout))
+        if cin not in (64, 128, 256) or cout % 64 != 0 or cout < 64:
+            raise ValueError("ConvMD2d: cin=%d, cout=%d unsupported by the B200 kernel (cin 64/128/256, cout a multiple of 64)" % (cin, cout))
         self.cin, self.cout = cin, cout
         self.conv = nn.Conv2d(cin, cout, 3, 1, 1)
         self.batch_norm = nn.BatchNorm2d(cout)
@@ -111,7 +136,7 @@ class DeConvMD2d(_Conv3x3BnRelu):
 
     def __init__(self, cin: int, cout: int):
         super().__init__()
-        if cin not in (64, 128) or cout % 64 != 0 or cout < 64:
+        if cin not in (64, 128, 256) or cout % 64 != 0 or cout < 64:
             raise ValueError("DeConvMD2d: cin=%d, cout=%d unsupported by the B200 kernel" % (cin, cout))
         self.cin, self.cout = cin, cout
         self.deconv = nn.ConvTranspose2d(cin, cout, 3, 1, 1)
@@ -183,8 +208,8 @@ def _as_bf16_nhwc(x: torch.Tensor) -> torch.Tensor:
 
 class RPNBlockTail(nn.Module):
     """A reference RPN block (`nn.Sequential` of ConvMD(2, ...), model.py:212-251) with its stride-1 3x3 layers on the
-    tcgen05 kernel; layers the kernel does not cover (the stride-2 head, 256-channel inputs, widths that are not a
-    multiple of 8) run on a private bf16 channels-last copy of the stock layer."""
+    tcgen05 kernel; layers the kernel does not cover (the stride-2 head) run on a private bf16 channels-last copy of the
+    stock layer."""
 
     def __init__(self, block: nn.Sequential):
         super().__init__()
@@ -197,24 +222,25 @@ class RPNBlockTail(nn.Module):
             stock.append(_stock_bf16(layer))
         self.stock = nn.ModuleList(stock)
         self.fast = nn.ModuleList([m if m is not None else nn.Identity() for m in fast])
-        self._ws = None
+        self._plans = _PlanCache()
+        self.min_tiles = None  # see _enough_tiles
 
     def on_tensor_cores(self, width: int) -> list:
         """Which layers run on the tcgen05 kernel for an input of this width (after the block's own strides)."""
         out, w = [], width
         for f, s in zip(self.fast, self.stock):
             w = w // int(s.conv.stride[1])
-            out.append(isinstance(f, ConvMD2d) and w % 8 == 0)
+            out.append(isinstance(f, ConvMD2d))
         return out
 
-    def forward(self, x: torch.Tensor) -> torch.Tensor:
+    def forward(self, x: torch.Tensor, plans: _PlanCache = None) -> torch.Tensor:
         x = _as_bf16_nhwc(x)
+        plans = self._plans if plans is None else plans
+        min_tiles = self.min_tiles
         for f, s in zip(self.fast, self.stock):
             B, _, H, W = x.shape
-            if isinstance(f, ConvMD2d) and W % 8 == 0:
-                if self._ws is None or self._ws[0] != (B, H, W, x.device):
-                    self._ws = ((B, H, W, x.device), torch.empty(ops.conv3d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device))
-                x = f.forward_nhwc(x.permute(0, 2, 3, 1), workspace=self._ws[1]).permute(0, 3, 1, 2)
+            if isinstance(f, ConvMD2d) and _enough_tiles(B, H, W, x.device, min_tiles):
+                x = f.forward_nhwc(x.permute(0, 2, 3, 1), plans=plans).permute(0, 3, 1, 2)
             else:
                 x = s(x)
         return x
@@ -255,6 +281,11 @@ class HybridRPN(nn.Module):
         self.heads = head.to(device=pc.weight.device, dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
         self.n_prob = pc.out_channels
 
+    def set_min_tiles(self, min_tiles) -> None:
+        """Feature maps with fewer 16x8 tiles than this run on the stock path (None: 4 per SM; 0: always tcgen05)."""
+        for b in (self.block1, self.block2, self.block3):
+            b.min_tiles = min_tiles
+
     def permute_input_channels(self, reference_channel_of_input: torch.Tensor) -> None:
         """The input's channel k holds the reference's channel reference_channel_of_input[k] (VoxelNetFrontEnd
         .reference_channel_of_output()): permute the input channels of block1's first layer once, so that the block sees
@@ -264,20 +295,23 @@ class HybridRPN(nn.Module):
             if hasattr(m, "conv"):
                 m.conv.weight.data = m.conv.weight.data[:, perm].contiguous()
 
-    def _deconv(self, i: int, x: torch.Tensor) -> torch.Tensor:
-        f = self.deconv_fast[i]
-        if isinstance(f, DeConvMD2d) and x.shape[3] % 8 == 0:
-            return f(x)
-        return self.deconv_stock[i](x)
-
     def forward(self, x: torch.Tensor):
+        plans = self.__dict__.setdefault("_plans", _PlanCache())
         x = _as_bf16_nhwc(x)
-        x = self.block1(x)
-        d1 = self._deconv(0, x)
-        x = self.block2(x)
-        d2 = self._deconv(1, x)
-        x = self.block3(x)
-        d3 = self._deconv(2, x)
-        x = torch.cat([d3, d2, d1], dim=1)  # model.py:272-274
+        x = self.block1(x, plans)
+        B, _, H, W = x.shape
+        # model.py:272-274: cat([deconv3, deconv2, deconv1], dim=1) - one channels-last buffer that every branch writes its slice of
+        c3, c2, c1 = (int(m.op.out_channels) for m in self.deconv_stock[::-1])
+        cat = torch.empty((B, H, W, c3 + c2 + c1), dtype=torch.bfloat16, device=x.device)
+        f1 = self.deconv_fast[0]
+        if isinstance(f1, DeConvMD2d) and _enough_tiles(B, H, W, x.device, self.block1.min_tiles):
+            f1.forward_nhwc(x.permute(0, 2, 3, 1), out=cat, plans=plans, channel_offset=c3 + c2)
+        else:
+            cat[..., c3 + c2:] = self.deconv_stock[0](x).permute(0, 2, 3, 1)
+        x = self.block2(x, plans)
+        cat[..., c3:c3 + c2] = self.deconv_stock[1](x).permute(0, 2, 3, 1)
+        x = self.block3(x, plans)
+        cat[..., :c3] = self.deconv_stock[2](x).permute(0, 2, 3, 1)
+        x = cat.permute(0, 3, 1, 2)
         y = self.heads(x).float()
         return torch.sigmoid(y[:, : self.n_prob]).contiguous(), y[:, self.n_prob:].contiguous()
