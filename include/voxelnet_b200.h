@@ -275,7 +275,8 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
  * 2-D 3x3 convolution + BatchNorm2d(eval) + ReLU on the same tcgen05 kernel - the stride-1 ConvMD(2, 128, 128, 3, (1,1),
  * (1,1)) layers of the RPN blocks (voxelnet/model.py:212-251).  Channels-last bf16 in and out:
  *   x [B, H, W, cin] -> y [B, H, W, cout],  y = relu(conv(x, weight * scale) + shift),  cin in {64, 128, 256}, cout in
- *   {64, 128, 192} per launch, any W (the last 8-wide tile column may be ragged).  The groups of 64 output channels ride along the MMA's N dimension the way the depth
+ *   {64, 128, 192} per launch, any W (the last 8-wide tile column may be ragged).  stride 1, or 2 (the heads of the
+ *   blocks, model.py:213,233,244): y is then [B, (H-1)/2+1, (W-1)/2+1, cout]; workspace and plan are those of the OUTPUT extent.  The groups of 64 output channels ride along the MMA's N dimension the way the depth
  *   taps of the 3-D layers do (one 128 x cout x 16 MMA per k-step).
  * vn_conv2d_pack_weights: weight [cout][cin][3][3] f32 (torch layout), scale [cout] = BatchNorm gamma / sqrt(var + eps) or
  *   NULL; packed: vn_conv2d_packed_weight_bytes(cin) bytes.  shift [cout] = beta + (bias - mean) * scale.
@@ -284,14 +285,13 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
  *   kernel flipped and its channel axes swapped: voxelnet/model.py:229 deconv1).
  * planned != 0: `workspace` still holds the work plan of an earlier launch with the same B, H, W and cout (the plan of a dense
  *   2-D layer depends on nothing else) - it is reused instead of rebuilt.
- * workspace: vn_conv2d_workspace_bytes(B, H, W).  Stride-2 layers, the strided deconvolutions and the 1x1 heads are not
- * covered. */
+ * workspace: vn_conv2d_workspace_bytes(B, output H, output W).  The strided deconvolutions and the 1x1 heads are not covered. */
 size_t vn_conv2d_workspace_bytes(int32_t B, int32_t H, int32_t W);
 size_t vn_conv2d_packed_weight_bytes(int32_t cin);
 int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, void* packed,
                            vn_stream_t stream);
 int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout,
-                          const void* packed_weight, const float* shift, void* y, int32_t y_channels,
+                          int32_t stride, const void* packed_weight, const float* shift, void* y, int32_t y_channels,
                           int32_t y_channel_offset, int32_t planned, void* workspace,
                           size_t workspace_bytes, vn_stream_t stream);
 

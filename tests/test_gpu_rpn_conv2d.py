@@ -65,6 +65,31 @@ def test_conv2d_bn_relu_matches_torch(cuda_device, cin, cout, B, H, W):
     assert bool(((got64 - exact).abs() <= ulp + 2e-5).all()), float(((got64 - exact).abs() - ulp).max())
 
 
+@pytest.mark.parametrize("cin,cout,B,H,W", [(128, 128, 2, 32, 16), (128, 128, 1, 50, 44), (64, 64, 1, 17, 9), (128, 256, 2, 40, 48)])
+def test_conv2d_stride2_matches_torch(cuda_device, cin, cout, B, H, W):
+    """The heads of the RPN blocks: ConvMD(2, 128, 128|256, 3, (2,2), (1,1)) (model.py:213,233,244).  Odd / even input rows
+    travel as two boxes; odd input extents give (H-1)/2+1 outputs like torch."""
+    import voxelnet_pytorch_b200 as vn
+
+    g = torch.Generator().manual_seed(cin + cout + H + 1)
+    ref = _randomise(RefConvMD2d(cin, cout, 3, 2, 1), g)
+    x = (torch.randn((B, cin, H, W), generator=g) * (torch.rand((B, cin, H, W), generator=g) < 0.6)).to(torch.bfloat16)
+    layer = vn.ConvMD2d.from_reference(ref.to(cuda_device))
+    got = layer(x.to(cuda_device).contiguous(memory_format=torch.channels_last))
+    with torch.no_grad():
+        want = ref.cpu().double()(x.double())
+        bn = ref.batch_norm
+        scale = (bn.weight.double() / torch.sqrt(bn.running_var.double() + bn.eps)).float()
+        w_q = (ref.conv.weight.float() * scale[:, None, None, None]).to(torch.bfloat16).double()
+        shift = (ref.conv.bias.double() * scale.double() + bn.bias.double() - bn.running_mean.double() * scale.double()).float().double()
+        exact = F.relu(F.conv2d(x.double(), w_q, None, 2, 1) + shift[None, :, None, None])
+    assert got.shape == want.shape and got.dtype == torch.bfloat16
+    got64 = got.cpu().double()
+    assert rel_max_err(got64, want) < 1e-2
+    ulp = exact.abs().clamp_min(2.0 ** -100) * 2.0 ** -7
+    assert bool(((got64 - exact).abs() <= ulp + 2e-5).all()), float(((got64 - exact).abs() - ulp).max())
+
+
 @pytest.mark.parametrize("cin,cout,H,W", [(128, 256, 40, 32), (64, 192, 20, 16)])
 def test_deconv_3x3_stride1_matches_torch(cuda_device, cin, cout, H, W):
     """The reference's deconv1 (DeConv2d(128, 256, 3, (1,1), (1,1)), model.py:229): ConvTranspose2d -> BN -> ReLU, 256
@@ -106,8 +131,8 @@ def test_rpn_block_tail_matches_the_reference_block(cuda_device):
         want = block.double()(x.double())
     tail = vn.RPNBlockTail(block.float().to(cuda_device))
     tail.min_tiles = 0  # (a map this small would otherwise take the stock path)
-    assert [type(m).__name__ for m in tail.fast] == ["Identity", "ConvMD2d", "ConvMD2d", "ConvMD2d"]
-    assert tail.on_tensor_cores(96) == [False, True, True, True]
+    assert [type(m).__name__ for m in tail.fast] == ["ConvMD2d", "ConvMD2d", "ConvMD2d", "ConvMD2d"]
+    assert tail.on_tensor_cores(96) == [True, True, True, True]
     assert block[0].conv.weight.dtype == torch.float32  # the caller's module is left alone
     with torch.no_grad():
         got = tail(x.to(cuda_device))
@@ -199,9 +224,8 @@ def test_hybrid_rpn_matches_the_fp32_rpn(cuda_device):
         p_want, r_want = ref(x)
     rpn = vn.HybridRPN(ref.to(cuda_device))
     rpn.set_min_tiles(0)  # (maps this small would otherwise take the stock path)
-    assert rpn.block1.on_tensor_cores(96) == [False, True, True, True, True]
-    assert rpn.block2.on_tensor_cores(48) == [False, True, True, True, True, True]
-    assert rpn.block3.on_tensor_cores(24) == [False, True, True, True, True, True]  # 256 channels, W = 12: ragged tile column
+    assert all(rpn.block1.on_tensor_cores(96)) and all(rpn.block2.on_tensor_cores(48))
+    assert all(rpn.block3.on_tensor_cores(24))  # 256 channels, W = 12: ragged tile column
     assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and not isinstance(rpn.deconv_fast[1], vn.DeConvMD2d)
     with torch.no_grad():
         p_got, r_got = rpn(x.to(cuda_device))

@@ -142,9 +142,8 @@ def test_hybrid_rpn_wraps_the_live_reference_rpn():
     ref = R.load_reference()
     net = ref.model.MiddleConvNet().eval()
     rpn = vn.HybridRPN(net)
-    assert rpn.block1.on_tensor_cores(352) == [False, True, True, True, True]
-    assert rpn.block2.on_tensor_cores(176) == [False, True, True, True, True, True]
-    assert rpn.block3.on_tensor_cores(88) == [False, True, True, True, True, True]
+    assert rpn.block1.on_tensor_cores(352) == [True] * 5 and rpn.block2.on_tensor_cores(176) == [True] * 6
+    assert rpn.block3.on_tensor_cores(88) == [True] * 6
     assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and not isinstance(rpn.deconv_fast[2], vn.DeConvMD2d)
     assert set(rpn.block1.fast[1].state_dict()) == set(net.block1[1].state_dict())
     assert net.block1[0].conv.weight.dtype == torch.float32

@@ -192,6 +192,8 @@ constexpr uint32_t kMsgSplit = 1u << 24;       // the taps of this box are in di
 constexpr uint32_t kMsgAccumulate = 1u << 25;  // no tap is fresh: the first MMA accumulates
 constexpr uint32_t kMsgCommitShift = 8;  // bits 8-15: TMEM slots that are complete after this message
 constexpr uint32_t kMsgWaitShift = 16;   // bits 16-23: TMEM slots the epilogue must have drained before the MMAs
+constexpr uint32_t kMsgKhSkipShift = 26;  // bits 26-27 (kS2): how many of the two extra kh rows of the box this message does NOT have
+constexpr uint32_t kABytesS2 = 17 * kTileW * 128;  // a stride-2 box: 17 sampled rows x 8 sampled columns x 64 channels
 // experiment switches of the kDebug instantiation (tools/prof_conv.py): what the kernel costs WITHOUT ...
 constexpr int kDbgNoALoad = 1;   // ... the TMA loads of the input boxes (the MMAs read stale shared memory)
 constexpr int kDbgNoBLoad = 2;   // ... the bulk loads of the weights
@@ -334,7 +336,10 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
 //                 wrote into the stage the last time, looks the 18 x 8 cells up in the voxelizer's occupancy bitmap,
 //                 copies the few occupied rows (64 channels = 128 B each) from the compact (K,128) row table into the
 //                 SWIZZLE_128B image the MMA expects, and arms the stage's full barrier.  tmap_x is unused.
-template <bool kTrain, bool kDebug, bool kGather>
+// kS2 = true (the stride-2 heads of the RPN blocks, 2-D only): the tensor map samples every second column and row of the
+//                 input; per (tile, chunk, kw) TWO boxes are loaded - 17 odd input rows 2 h0 - 1, + 1, ... serve kh = 0 (box rows
+//                 0..15) and kh = 2 (box rows 1..16), 16 even rows 2 h0, ... serve kh = 1 - and each is its own message.
+template <bool kTrain, bool kDebug, bool kGather, bool kS2 = false>
 __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     k_conv3d_bn_relu(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ ConvParams P) {
   extern __shared__ uint8_t smem_raw[];
@@ -507,7 +512,26 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
                   P.trace[(size_t)a_it * 4 + 3] = flags;
                 }
               }
-              if (elect_one()) {
+              if (kS2) {
+                // odd rows: kh = 0 and (one box row on, weights two kh rows on) kh = 2; the tile-complete bits go with the second box
+                const uint32_t commit_bits = flags & (0xffu << kMsgCommitShift);
+                if (elect_one()) {
+                  ctl->msg[sa] = make_uint4((flags & ~commit_bits) | (1u << kMsgKhSkipShift), tmem_base + slot_lo * 64, pi.woff >> 4,
+                                            (2 * pi.wstride) >> 4);
+                  mbar_arrive_expect_tx(&ctl->full_a[sa], kABytesS2);
+                  tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, 2 * w0 + kw - 1, 2 * h0 - 1, p, b);
+                }
+                __syncwarp();
+                ++a_it;
+                const uint32_t sa2 = a_it % kNA;
+                mbar_wait(&ctl->empty_a[sa2], ((a_it / kNA) & 1) ^ 1);
+                if (elect_one()) {  // even rows: kh = 1
+                  ctl->msg[sa2] = make_uint4((uint32_t)pi.nkd | kMsgAccumulate | commit_bits | (2u << kMsgKhSkipShift),
+                                             tmem_base + slot_lo * 64, (pi.woff + pi.wstride) >> 4, 0u);
+                  mbar_arrive_expect_tx(&ctl->full_a[sa2], kABytesS2);
+                  tma_load_5d(smem_a + sa2 * kABytes, &tmap_x, &ctl->full_a[sa2], c * 64, 2 * w0 + kw - 1, 2 * h0, p, b);
+                }
+              } else if (elect_one()) {
                 const uint4 msg = make_uint4(flags, tmem_base + slot_lo * 64, pi.woff >> 4, pi.wstride >> 4);
                 if (kGather) {
                   ctl_mail(ctl)->req[sf] = make_int4(w0 + kw - 1, h0 - 1, p | (c << 8) | (kReqBox << 16), b);
@@ -672,8 +696,10 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
           have_next = mbar_test_wait(&ctl->full_a[sn], pn);
           if (have_next) nxt = decode(lds_u4(&ctl->msg[sn]), a_it + 1);
           if (!no_mma) {  // kh = 1, 2
+            const int n_extra = kS2 ? 2 - (int)((f >> kMsgKhSkipShift) & 3u) : 2;
 #pragma unroll
             for (int kh = 1; kh < 3; ++kh) {
+              if (kS2 && kh > n_extra) break;
               const uint32_t a = a_lo + kh * ((kTileW * 128) >> 4);
               const uint32_t bq = b_lo + kh * cur.bw;
 #pragma unroll
@@ -1404,7 +1430,8 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                        int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
                        int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
                        vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr,
-                       int32_t groups2d = 0, int32_t out_ctotal = 0, int32_t out_coff = 0) {
+                       int32_t groups2d = 0, int32_t out_ctotal = 0, int32_t out_coff = 0, int32_t s2_hin = 0, int32_t s2_win = 0) {
+  // s2_hin > 0 (2-D layers only): stride 2 in H and W; x is [B, 1, s2_hin, s2_win, cin] and H, W are the OUTPUT extents
   VN_REQUIRE((x || gather) && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128 || (groups2d > 0 && cin == 256), "conv3d: cin=%d (supported: 64, 128; 2-D layers also 256)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
@@ -1449,11 +1476,15 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
     set_error("conv3d: cuTensorMapEncodeTiled not available from the driver");
     return VN_ERR_DRIVER;
   }
-  const cuuint64_t gdim[5] = {(cuuint64_t)cin, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)Din, (cuuint64_t)B};
-  const cuuint64_t gstr[4] = {(cuuint64_t)cin * 2, (cuuint64_t)W * cin * 2, (cuuint64_t)H * W * cin * 2,
-                              (cuuint64_t)Din * H * W * cin * 2};
-  const cuuint32_t box[5] = {64, (cuuint32_t)kTileW, (cuuint32_t)kHaloH, 1, 1};
-  const cuuint32_t estr[5] = {1, 1, 1, 1, 1};
+  const bool s2 = s2_hin > 0;
+  VN_REQUIRE(!s2 || (groups2d > 0 && gather == nullptr && stats == nullptr && (s2_hin - 1) / 2 + 1 == H && (s2_win - 1) / 2 + 1 == W),
+             "conv2d: stride-2 input %d x %d does not give a %d x %d output", s2_hin, s2_win, H, W);
+  const cuuint64_t Hx = s2 ? s2_hin : H, Wx = s2 ? s2_win : W;
+  const cuuint64_t gdim[5] = {(cuuint64_t)cin, Wx, Hx, (cuuint64_t)Din, (cuuint64_t)B};
+  const cuuint64_t gstr[4] = {(cuuint64_t)cin * 2, Wx * cin * 2, Hx * Wx * cin * 2, (cuuint64_t)Din * Hx * Wx * cin * 2};
+  // stride 2: the box spans 16 columns x 34 rows of the input and loads every second one (8 x 17 samples)
+  const cuuint32_t box[5] = {64, (cuuint32_t)(s2 ? 2 * kTileW : kTileW), (cuuint32_t)(s2 ? 2 * (kTileH + 1) : kHaloH), 1, 1};
+  const cuuint32_t estr[5] = {1, (cuuint32_t)(s2 ? 2 : 1), (cuuint32_t)(s2 ? 2 : 1), 1, 1};
   const CUresult cr = encode(&tmap, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(x), gdim, gstr, box, estr,
                              CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -1526,6 +1557,9 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
       VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
       k_conv3d_bn_relu<false, false, true><<<grid, kThreadsGather, kSmemBytes, st>>>(tmap, P);
     }
+  } else if (s2_hin > 0) {
+    VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    k_conv3d_bn_relu<false, false, false, true><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   } else if (stats != nullptr) {
     VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<true, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     k_conv3d_bn_relu<true, false, false><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
@@ -1653,19 +1687,21 @@ int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin,
   return VN_OK;
 }
 
-int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout, const void* packed_weight,
-                          const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset, int32_t planned,
-                          void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout, int32_t stride,
+                          const void* packed_weight, const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset,
+                          int32_t planned, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d: cout=%d (supported: 64, 128, 192)", cout);
   VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d: cin=%d (supported: 64, 128, 256)", cin);
-  VN_REQUIRE(packed_weight != nullptr && shift != nullptr, "conv2d: null pointer");
+  VN_REQUIRE(stride == 1 || stride == 2, "conv2d: stride=%d (supported: 1, 2)", stride);
+  VN_REQUIRE(packed_weight != nullptr && shift != nullptr && H >= 1 && W >= 1, "conv2d: null pointer or empty input");
   VN_REQUIRE(y_channels >= cout && y_channel_offset >= 0 && y_channel_offset + cout <= y_channels && y_channels % 16 == 0 &&
                  y_channel_offset % 16 == 0,
              "conv2d: channels %d..%d of %d (multiples of 16 inside y)", y_channel_offset, y_channel_offset + cout, y_channels);
   const float* ones = reinterpret_cast<const float*>(static_cast<const uint8_t*>(packed_weight) + (size_t)(cin / 64) * 3 * kBSlotBytes);
-  return conv_launch(x, B, 1, H, W, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr,
+  const int Ho = stride == 2 ? (H - 1) / 2 + 1 : H, Wo = stride == 2 ? (W - 1) / 2 + 1 : W;
+  return conv_launch(x, B, 1, Ho, Wo, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr,
                      planned ? VN_CONV_FLAGS_PLANNED : 0, nullptr, workspace, workspace_bytes, stream, nullptr, 0, nullptr, cout / 64,
-                     y_channels, y_channel_offset);
+                     y_channels, y_channel_offset, stride == 2 ? H : 0, stride == 2 ? W : 0);
 }
 
 }  // extern "C"

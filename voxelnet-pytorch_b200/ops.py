@@ -484,24 +484,27 @@ def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
     return packed
 
 
-def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channel_offset: int = 0, planned: bool = False) -> torch.Tensor:
-    """x (B,H,W,cin) bf16 channels-last -> relu(conv3x3(x) + shift) as (B,H,W,cout) bf16 (stride 1, padding 1);
+def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channel_offset: int = 0, planned: bool = False,
+                       stride: int = 1) -> torch.Tensor:
+    """x (B,H,W,cin) bf16 channels-last -> relu(conv3x3(x) + shift) as (B,Ho,Wo,cout) bf16 (padding 1; stride 1 or 2);
     shift (cout,) f32 carries the bias and the BatchNorm shift, the BatchNorm scale sits in the packed weights.
     `out` may have more channels than cout: the launch writes channels channel_offset .. + cout of it.  planned: `workspace`
-    holds the plan of an earlier launch with the same B, H, W and cout - reuse it."""
+    holds the plan of an earlier launch with the same B, Ho, Wo and cout - reuse it."""
     _require_cuda(x, packed_weight, shift, out, workspace)
     _contig(x, torch.bfloat16), _contig(shift, torch.float32)
     B, H, W, cin = x.shape
+    Ho, Wo = ((H - 1) // 2 + 1, (W - 1) // 2 + 1) if stride == 2 else (H, W)
     cout = int(shift.numel())
     if out is None:
-        out = torch.empty((B, H, W, cout), dtype=torch.bfloat16, device=x.device)
-    elif tuple(out.shape[:3]) != (B, H, W) or out.dtype != torch.bfloat16 or not out.is_contiguous():
-        raise RuntimeError("out must be a contiguous (B,H,W,C) bf16 tensor")
+        out = torch.empty((B, Ho, Wo, cout), dtype=torch.bfloat16, device=x.device)
+    elif tuple(out.shape[:3]) != (B, Ho, Wo) or out.dtype != torch.bfloat16 or not out.is_contiguous():
+        raise RuntimeError("out must be a contiguous (B,Ho,Wo,C) bf16 tensor")
     if workspace is None:
-        workspace = torch.empty(conv2d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
+        workspace = torch.empty(conv2d_workspace_bytes(B, Ho, Wo), dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
-        check(_cabi.lib().vn_conv2d_bn_relu_fwd(_ptr(x), B, H, W, cin, cout, _ptr(packed_weight), _ptr(shift), _ptr(out),
-                                                int(out.shape[3]), int(channel_offset), 1 if planned else 0, _ptr(workspace), workspace.numel(), _stream()),
+        check(_cabi.lib().vn_conv2d_bn_relu_fwd(_ptr(x), B, H, W, cin, cout, int(stride), _ptr(packed_weight), _ptr(shift), _ptr(out),
+                                                int(out.shape[3]), int(channel_offset), 1 if planned else 0, _ptr(workspace),
+                                                workspace.numel(), _stream()),
               "vn_conv2d_bn_relu_fwd")
     return out
 

@@ -1,4 +1,4 @@
-"""The stride-1 3x3 layers of the RPN blocks on the tcgen05 conv kernel (second half).
+"""The 3x3 layers of the RPN blocks (stride 1 and 2) and deconv1 on the tcgen05 conv kernel (second half).
 
 Reference: `ConvMD(2, 128, 128, 3, (1, 1), (1, 1))` = Conv2d -> BatchNorm2d -> ReLU (voxelnet/model.py:111-167), the four
 / five stride-1 layers that follow the stride-2 head of `block1` and `block2` (model.py:212-242): 9 of the RPN's 17
@@ -12,7 +12,8 @@ stride-1 transposed convolution is a convolution with the flipped kernel.  The f
 two launches of 128 output channels over four 64-channel input chunks (W = 44: the last tile column is ragged).
 Together 15 of the RPN's 22 layers, 88 of its ~110 GFLOP.
 
-The three stride-2 layers, the two strided `ConvTranspose2d` and the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
+The stride-2 heads of the blocks run on the kernel's stride-2 instantiation (odd / even input rows as two boxes).
+The two strided `ConvTranspose2d` and the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
 wraps a reference block so that its head runs on stock PyTorch and its stride-1 tail here, `HybridRPN` the whole RPN half
 of the reference's `MiddleConvNet`.
 """
@@ -83,13 +84,17 @@ class _Conv3x3BnRelu(nn.Module):
         if self.training:
             raise NotImplementedError("%s implements eval-mode BatchNorm (inference); train the RPN on stock PyTorch" % type(self).__name__)
         B, H, W, _ = x_nhwc.shape
+        stride = int(getattr(self, "stride", 1))
+        if stride == 2:
+            H, W = (H - 1) // 2 + 1, (W - 1) // 2 + 1
         if out is None:
             out = torch.empty((B, H, W, self.cout), dtype=torch.bfloat16, device=x_nhwc.device)
         if plans is None:
             plans = self.__dict__.setdefault("_plans", _PlanCache())
         for o, packed, shift in self.folded():
             ws, planned = plans.get(B, H, W, int(shift.numel()), x_nhwc.device)
-            ops.conv2d_bn_relu_fwd(x_nhwc, packed, shift, out=out, workspace=ws, channel_offset=channel_offset + o, planned=planned)
+            ops.conv2d_bn_relu_fwd(x_nhwc, packed, shift, out=out, workspace=ws, channel_offset=channel_offset + o, planned=planned,
+                                   stride=stride)
         return out
 
     def forward(self, x: torch.Tensor) -> torch.Tensor:
@@ -100,14 +105,15 @@ class _Conv3x3BnRelu(nn.Module):
 
 
 class ConvMD2d(_Conv3x3BnRelu):
-    """model.py:111-167, 2-D case, kernel 3, stride 1, padding 1, BatchNorm + ReLU; cin in {64,128,256}, cout a multiple of 64."""
+    """model.py:111-167, 2-D case, kernel 3, stride 1 or 2, padding 1, BatchNorm + ReLU; cin in {64,128,256}, cout a multiple of 64."""
 
-    def __init__(self, cin: int, cout: int):
+    def __init__(self, cin: int, cout: int, stride: int = 1):
         super().__init__()
-        if cin not in (64, 128, 256) or cout % 64 != 0 or cout < 64:
-            raise ValueError("ConvMD2d: cin=%d, cout=%d unsupported by the B200 kernel (cin 64/128/256, cout a multiple of 64)" % (cin, cout))
-        self.cin, self.cout = cin, cout
-        self.conv = nn.Conv2d(cin, cout, 3, 1, 1)
+        if cin not in (64, 128, 256) or cout % 64 != 0 or cout < 64 or stride not in (1, 2):
+            raise ValueError("ConvMD2d: cin=%d, cout=%d, stride=%d unsupported by the B200 kernel (cin 64/128/256, cout a multiple "
+                             "of 64, stride 1/2)" % (cin, cout, stride))
+        self.cin, self.cout, self.stride = cin, cout, stride
+        self.conv = nn.Conv2d(cin, cout, 3, stride, 1)
         self.batch_norm = nn.BatchNorm2d(cout)
 
     @classmethod
@@ -115,9 +121,10 @@ class ConvMD2d(_Conv3x3BnRelu):
         """A reference `ConvMD(2, ...)` (or anything with `.conv` Conv2d and `.batch_norm` BatchNorm2d) -> ConvMD2d sharing
         its parameter values."""
         conv = getattr(layer, "conv", None)
-        if not isinstance(conv, nn.Conv2d) or tuple(conv.kernel_size) != (3, 3) or tuple(conv.stride) != (1, 1) or tuple(conv.padding) != (1, 1):
-            raise ValueError("ConvMD2d covers 3x3 / stride 1 / padding 1 Conv2d layers only")
-        m = cls(conv.in_channels, conv.out_channels)
+        if not isinstance(conv, nn.Conv2d) or tuple(conv.kernel_size) != (3, 3) or tuple(conv.stride) not in ((1, 1), (2, 2)) \
+                or tuple(conv.padding) != (1, 1):
+            raise ValueError("ConvMD2d covers 3x3 / stride 1 or 2 / padding 1 Conv2d layers only")
+        m = cls(conv.in_channels, conv.out_channels, int(conv.stride[0]))
         m.load_state_dict(layer.state_dict())
         return m.to(conv.weight.device).eval()
 
@@ -239,7 +246,8 @@ class RPNBlockTail(nn.Module):
         min_tiles = self.min_tiles
         for f, s in zip(self.fast, self.stock):
             B, _, H, W = x.shape
-            if isinstance(f, ConvMD2d) and _enough_tiles(B, H, W, x.device, min_tiles):
+            st = int(s.conv.stride[0])
+            if isinstance(f, ConvMD2d) and _enough_tiles(B, (H - 1) // st + 1, (W - 1) // st + 1, x.device, min_tiles):
                 x = f.forward_nhwc(x.permute(0, 2, 3, 1), plans=plans).permute(0, 3, 1, 2)
             else:
                 x = s(x)
