@@ -288,12 +288,26 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
  * workspace: vn_conv2d_workspace_bytes(B, output H, output W).  The strided deconvolutions and the 1x1 heads are not covered. */
 size_t vn_conv2d_workspace_bytes(int32_t B, int32_t H, int32_t W);
 size_t vn_conv2d_packed_weight_bytes(int32_t cin);
-int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, void* packed,
+int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout,
+                           int32_t ksize /* 3, or 1 for vn_conv2d_pointwise_fwd */, void* packed,
                            vn_stream_t stream);
 int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout,
                           int32_t stride, const void* packed_weight, const float* shift, void* y, int32_t y_channels,
                           int32_t y_channel_offset, int32_t planned, void* workspace,
                           size_t workspace_bytes, vn_stream_t stream);
+
+/* 1x1 convolution (+ folded BatchNorm + ReLU) whose outputs are placed on an `up` times finer grid: position (h, w) of
+ * x [B, H, W, cin] is written to (h * up + oy, w * up + ox) of y [B, H * up, W * up, y_channels], channels y_channel_offset ..
+ * + cout.  A transposed convolution with kernel = stride = up and no padding (the reference's deconv2 / deconv3,
+ * voxelnet/model.py:242,253: DeConv2d(128, 256, 2, (2,2), (0,0)) and DeConv2d(256, 256, 4, (4,4), (0,0))) is up * up such launches
+ * per block of <= 192 output channels, launch (oy, ox) carrying the weights W[:, :, oy, ox] (packed with ksize 1: weight
+ * [cout][cin] f32) - each output is written once, straight into its slice of the concatenated tensor, BatchNorm and ReLU in
+ * the epilogue.  up = 1 is a plain 1x1 convolution.  workspace / planned as in vn_conv2d_bn_relu_fwd (plans of 3x3 and 1x1
+ * launches differ: do not share a planned workspace between them). */
+int vn_conv2d_pointwise_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout,
+                            const void* packed_weight, const float* shift, void* y, int32_t y_channels,
+                            int32_t y_channel_offset, int32_t up, int32_t oy, int32_t ox, int32_t planned,
+                            void* workspace, size_t workspace_bytes, vn_stream_t stream);
 
 /* Background folding for a layer whose INPUT is stored as a deviation from a background (what the previous
  * layer outputs wherever ITS input was all background; NULL = zero background).  The reference zero-pads, so

@@ -118,6 +118,40 @@ def test_deconv_3x3_stride1_matches_torch(cuda_device, cin, cout, H, W):
     assert float((got.cpu().double() - want).norm() / want.norm()) < 5e-3
 
 
+@pytest.mark.parametrize("cin,cout,k,H,W", [(128, 256, 2, 20, 24), (256, 256, 4, 13, 11), (64, 64, 3, 8, 8)])
+def test_deconv_kernel_equals_stride_matches_torch(cuda_device, cin, cout, k, H, W):
+    """deconv2 / deconv3 (DeConv2d(128, 256, 2, (2,2), (0,0)), DeConv2d(256, 256, 4, (4,4), (0,0)), model.py:242,253) as k*k
+    pointwise launches that write each output pixel once, into a channel slice of a wider tensor."""
+    import voxelnet_pytorch_b200 as vn
+
+    class RefDeConv(nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.deconv = nn.ConvTranspose2d(cin, cout, k, k, 0)
+            self.batch_norm = nn.BatchNorm2d(cout)
+
+        def forward(self, x):
+            return F.relu(self.batch_norm(self.deconv(x)))
+
+    g = torch.Generator().manual_seed(cout + k)
+    ref = _randomise(RefDeConv(), g)
+    x = torch.randn((2, cin, H, W), generator=g).relu().to(torch.bfloat16)
+    layer = vn.DeConvUpMD2d.from_reference(ref.to(cuda_device))
+    assert set(layer.state_dict()) == set(ref.state_dict())
+    xg = x.to(cuda_device).contiguous(memory_format=torch.channels_last)
+    got = layer(xg)
+    with torch.no_grad():
+        want = ref.cpu().double()(x.double())
+    assert got.shape == want.shape == (2, cout, H * k, W * k) and got.dtype == torch.bfloat16
+    assert rel_max_err(got.cpu().double(), want) < 1e-2
+    assert float((got.cpu().double() - want).norm() / want.norm()) < 5e-3
+    # into the middle of a wider tensor: the neighbouring channels stay untouched
+    wide = torch.full((2, H * k, W * k, cout + 128), 7.0, dtype=torch.bfloat16, device=cuda_device)
+    layer.forward_nhwc(xg.permute(0, 2, 3, 1), out=wide, channel_offset=64)
+    assert torch.equal(wide[..., 64:64 + cout], got.permute(0, 2, 3, 1))
+    assert bool((wide[..., :64] == 7).all()) and bool((wide[..., 64 + cout:] == 7).all())
+
+
 def test_rpn_block_tail_matches_the_reference_block(cuda_device):
     """A block shaped like the reference's block2 (stride-2 head + stride-1 layers, model.py:232-240), at reduced
     size: the head runs on stock PyTorch, the tail on the tcgen05 kernel, bf16 channels-last in between."""
@@ -226,7 +260,8 @@ def test_hybrid_rpn_matches_the_fp32_rpn(cuda_device):
     rpn.set_min_tiles(0)  # (maps this small would otherwise take the stock path)
     assert all(rpn.block1.on_tensor_cores(96)) and all(rpn.block2.on_tensor_cores(48))
     assert all(rpn.block3.on_tensor_cores(24))  # 256 channels, W = 12: ragged tile column
-    assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and not isinstance(rpn.deconv_fast[1], vn.DeConvMD2d)
+    assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and isinstance(rpn.deconv_fast[1], vn.DeConvUpMD2d) \
+        and isinstance(rpn.deconv_fast[2], vn.DeConvUpMD2d)
     with torch.no_grad():
         p_got, r_got = rpn(x.to(cuda_device))
         stock = ref.to(dtype=torch.bfloat16, memory_format=torch.channels_last)

@@ -144,6 +144,7 @@ def test_hybrid_rpn_wraps_the_live_reference_rpn():
     rpn = vn.HybridRPN(net)
     assert rpn.block1.on_tensor_cores(352) == [True] * 5 and rpn.block2.on_tensor_cores(176) == [True] * 6
     assert rpn.block3.on_tensor_cores(88) == [True] * 6
-    assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and not isinstance(rpn.deconv_fast[2], vn.DeConvMD2d)
+    assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and isinstance(rpn.deconv_fast[1], vn.DeConvUpMD2d) \
+        and isinstance(rpn.deconv_fast[2], vn.DeConvUpMD2d) and rpn.deconv_fast[2].k == 4
     assert set(rpn.block1.fast[1].state_dict()) == set(net.block1[1].state_dict())
     assert net.block1[0].conv.weight.dtype == torch.float32

@@ -89,7 +89,7 @@ with torch.no_grad():
     t_f = timed(lambda: ref_rpn(x32), 5)
 out["rpn_car16"] = {"ms_hybrid_tcgen05": t_h, "ms_stock_bf16_nhwc": t_s, "ms_stock_fp32": t_f,
                     "reg_rel_l2_vs_fp32": float((r1 - r0).norm() / r0.norm()), "prob_max_abs_err": float((p1 - p0).abs().max()),
-                    "layers_on_tcgen05": "block1 (5 layers incl. the stride-2 head), block2 (6), deconv1: 88 of ~110 GFLOP per frame; block3 too when the batch gives it >= 4 tiles per SM"}
+                    "layers_on_tcgen05": "block1 (5 layers incl. the stride-2 head), block2 (6), deconv1, deconv2, deconv3; block3 too when the batch gives it >= 4 tiles per SM; heads stock"}
 print("rpn_car16", out["rpn_car16"])
 
 # ---- points -> RPN maps: the fused front end (bf16 channels-last output) + the hybrid RPN, one step at a time ----------------

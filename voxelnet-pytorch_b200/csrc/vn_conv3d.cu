@@ -104,6 +104,9 @@ struct ConvParams {
   const float* table;   // [nvar][Dout][64] (or [64] when table_plain)
   int reverse;          // take the groups of the plan last to first (VN_CONV_FLAGS_REVERSE)
   int out_ctotal, out_coff;  // out_mode 2: channels per position of y and the first channel this launch writes
+  int out_up, out_oy, out_ox;  // out_mode 2: output position (h, w) is written at (h * out_up + out_oy, w * out_up + out_ox) of a
+                               // [B, H * out_up, W * out_up, out_ctotal] tensor (a transposed convolution with kernel = stride)
+  int pointwise;        // kS2 instantiation: 1x1 convolution - only the centre tap (kw = 1, kh = 1) exists, stride 1
   int table_plain;      // table is a plain [64] shift vector used for every row
   const float* sub;     // [Dout][64] subtracted after the ReLU, or nullptr
   void* out;
@@ -131,6 +134,7 @@ struct ConvParams {
 struct PlanParams {
   int B, Din, Dout, H, W, tiles_h, tiles_w;
   uint8_t* box_flags;  // [B][Din][tiles_h][tiles_w][3] or nullptr (every box live)
+  int only_kw1;        // 1x1 convolution: only the boxes of the centre column shift exist
   int consume;         // reset the flags that were read
   int force_ring;      // boxes containing an H/W border position are live (input deviates there)
   // [B][tiles_h][tiles_w] bytes kept by the caller next to the OUTPUT buffer, or nullptr.  Bit d set:
@@ -258,6 +262,7 @@ __global__ void __launch_bounds__(64) k_conv3d_plan(const __grid_constant__ Plan
       live = ~0u;
     }
     live &= valid;
+    if (Q.only_kw1) live &= kw_bits(1);
     const uint32_t touched = touched_accumulators(Q, live);
     uint32_t stale = all_out;
     if (Q.out_state != nullptr) {
@@ -512,7 +517,14 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
                   P.trace[(size_t)a_it * 4 + 3] = flags;
                 }
               }
-              if (kS2) {
+              if (kS2 && P.pointwise) {
+                // 1x1: the box starts at the tile's own first row, so box row 0 is kh = 1; the message has no other kh row
+                if (elect_one()) {
+                  ctl->msg[sa] = make_uint4(flags | (2u << kMsgKhSkipShift), tmem_base + slot_lo * 64, (pi.woff + pi.wstride) >> 4, 0u);
+                  mbar_arrive_expect_tx(&ctl->full_a[sa], kABytes);
+                  tma_load_5d(smem_a + sa * kABytes, &tmap_x, &ctl->full_a[sa], c * 64, w0 + kw - 1, h0, p, b);
+                }
+              } else if (kS2) {
                 // odd rows: kh = 0 and (one box row on, weights two kh rows on) kh = 2; the tile-complete bits go with the second box
                 const uint32_t commit_bits = flags & (0xffu << kMsgCommitShift);
                 if (elect_one()) {
@@ -969,7 +981,8 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
             if (P.out_mode != 1) {
               __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
                                    (P.out_mode == 0 ? ((((size_t)b * P.Dout + dout) * P.H + h) * P.W + w) * 64 + half * 32
-                                                    : (((size_t)b * P.H + h) * P.W + w) * P.out_ctotal + P.out_coff + dout * 64 + half * 32);
+                                                    : (((size_t)b * (P.H * P.out_up) + h * P.out_up + P.out_oy) * (P.W * P.out_up) + w * P.out_up + P.out_ox) * P.out_ctotal +
+                                                          P.out_coff + dout * 64 + half * 32);
 #pragma unroll
               for (int q = 0; q < 2; ++q) {  // 2 x 32 B: one full sector per lane per store
                 uint32_t pk[8];
@@ -1252,21 +1265,23 @@ int plan_planes_2d(Params& P, int groups) {
 // the kernel reads for the schedule above: per (chunk, kw) a 72 KB slot holding [kh][group][n = 64][k = 64] bf16 tiles
 // (rows 128B-swizzled); 64 floats of 1.0 behind the last slot serve as the epilogue's scale vector.
 __global__ void __launch_bounds__(256)
-    k_pack_weights2d(const float* __restrict__ w, const float* __restrict__ scale, int cin, int cout, uint8_t* __restrict__ packed) {
+    k_pack_weights2d(const float* __restrict__ w, const float* __restrict__ scale, int cin, int cout, int ksize,
+                     uint8_t* __restrict__ packed) {
   const int nchunk = cin / 64, groups = cout / 64;
-  const int total = 9 * cin * cout;
+  const int total = ksize * ksize * cin * cout;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
     int r = i;
     const int k = r % 64; r /= 64;
     const int n = r % 64; r /= 64;
     const int j = r % groups; r /= groups;
-    const int kh = r % 3; r /= 3;
-    const int kw = r % 3; r /= 3;
+    const int kh = r % ksize; r /= ksize;
+    const int kw = r % ksize; r /= ksize;
     const int c = r;
     const int co = j * 64 + n, ci = c * 64 + k;
-    float v = w[(((size_t)co * cin + ci) * 3 + kh) * 3 + kw];
+    float v = w[(((size_t)co * cin + ci) * ksize + kh) * ksize + kw];
     if (scale != nullptr) v *= scale[co];
-    const size_t tile = (size_t)(c * 3 + kw) * kBSlotBytes + (size_t)(kh * groups + j) * kBTapBytes;
+    const int kh3 = ksize == 1 ? 1 : kh, kw3 = ksize == 1 ? 1 : kw;  // a 1x1 kernel is the centre tap
+    const size_t tile = (size_t)(c * 3 + kw3) * kBSlotBytes + (size_t)(kh3 * groups + j) * kBTapBytes;
     const size_t off = tile + (size_t)n * 128 + ((((k >> 3) ^ (n & 7)) << 4) | ((k & 7) << 1));
     *reinterpret_cast<__nv_bfloat16*>(packed + off) = __float2bfloat16_rn(v);
   }
@@ -1430,7 +1445,8 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                        int32_t n_variants, const float* sub, int32_t out_mode, void* y, uint8_t* box_flags,
                        int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
                        vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr,
-                       int32_t groups2d = 0, int32_t out_ctotal = 0, int32_t out_coff = 0, int32_t s2_hin = 0, int32_t s2_win = 0) {
+                       int32_t groups2d = 0, int32_t out_ctotal = 0, int32_t out_coff = 0, int32_t s2_hin = 0, int32_t s2_win = 0,
+                       int32_t pointwise = 0, int32_t out_up = 1, int32_t out_oy = 0, int32_t out_ox = 0) {
   // s2_hin > 0 (2-D layers only): stride 2 in H and W; x is [B, 1, s2_hin, s2_win, cin] and H, W are the OUTPUT extents
   VN_REQUIRE((x || gather) && packed_weight && scale && shift_table && y, "conv3d: null pointer");
   VN_REQUIRE(cin == 64 || cin == 128 || (groups2d > 0 && cin == 256), "conv3d: cin=%d (supported: 64, 128; 2-D layers also 256)", cin);
@@ -1501,6 +1517,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   Q.consume = (flag_opts & VN_CONV_FLAGS_CONSUME) ? 1 : 0;
   Q.force_ring = (flag_opts & VN_CONV_FLAGS_BORDER_RING) ? 1 : 0;
   Q.out_state = out_state;
+  Q.only_kw1 = pointwise ? 1 : 0;
   Q.hdr = hdr; Q.groups = groups; Q.tiles = tiles; Q.gtiles = gtiles;
   if ((groups2d > 0 ? plan_planes_2d(Q, groups2d)
                     : (transposed_dout > 0 ? plan_planes_transposed(Q, stride_d, pad_d) : plan_planes(Q, stride_d, pad_d))) != 0) {
@@ -1532,6 +1549,8 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   P.reverse = (flag_opts & VN_CONV_FLAGS_REVERSE) ? 1 : 0;
   P.out_ctotal = out_ctotal > 0 ? out_ctotal : 64 * Dout;
   P.out_coff = out_coff;
+  P.out_up = out_up; P.out_oy = out_oy; P.out_ox = out_ox;
+  P.pointwise = pointwise;
   P.sub = sub;
   P.out = y;
   P.hdr = hdr; P.groups = groups; P.tiles = tiles; P.gtiles = gtiles;
@@ -1557,7 +1576,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
       VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
       k_conv3d_bn_relu<false, false, true><<<grid, kThreadsGather, kSmemBytes, st>>>(tmap, P);
     }
-  } else if (s2_hin > 0) {
+  } else if (s2_hin > 0 || pointwise) {
     VN_CUDA(cudaFuncSetAttribute(k_conv3d_bn_relu<false, false, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     k_conv3d_bn_relu<false, false, false, true><<<grid, kThreads, kSmemBytes, st>>>(tmap, P);
   } else if (stats != nullptr) {
@@ -1676,13 +1695,15 @@ size_t vn_conv2d_packed_weight_bytes(int32_t cin) {
   return (size_t)(cin / 64) * 3 * kBSlotBytes + 64 * sizeof(float);
 }
 
-int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, void* packed, vn_stream_t stream) {
+int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, int32_t ksize, void* packed,
+                           vn_stream_t stream) {
+  VN_REQUIRE(ksize == 3 || ksize == 1, "conv2d_pack_weights: ksize=%d (supported: 3, 1)", ksize);
   VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d_pack_weights: cin=%d (supported: 64, 128, 256)", cin);
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d_pack_weights: cout=%d (supported: 64, 128, 192)", cout);
   VN_REQUIRE(weight != nullptr && packed != nullptr && (reinterpret_cast<uintptr_t>(packed) & 15) == 0,
              "conv2d_pack_weights: null or misaligned pointer");
   VN_CUDA(cudaMemsetAsync(packed, 0, vn_conv2d_packed_weight_bytes(cin), as_stream(stream)));
-  k_pack_weights2d<<<sm_count() * 2, 256, 0, as_stream(stream)>>>(weight, scale, cin, cout, reinterpret_cast<uint8_t*>(packed));
+  k_pack_weights2d<<<sm_count() * 2, 256, 0, as_stream(stream)>>>(weight, scale, cin, cout, ksize, reinterpret_cast<uint8_t*>(packed));
   VN_LAUNCH_CHECK("k_pack_weights2d");
   return VN_OK;
 }
@@ -1702,6 +1723,22 @@ int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_
   return conv_launch(x, B, 1, Ho, Wo, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr,
                      planned ? VN_CONV_FLAGS_PLANNED : 0, nullptr, workspace, workspace_bytes, stream, nullptr, 0, nullptr, cout / 64,
                      y_channels, y_channel_offset, stride == 2 ? H : 0, stride == 2 ? W : 0);
+}
+
+int vn_conv2d_pointwise_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout, const void* packed_weight,
+                            const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset, int32_t up, int32_t oy,
+                            int32_t ox, int32_t planned, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+  VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d_pointwise: cout=%d (supported: 64, 128, 192)", cout);
+  VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d_pointwise: cin=%d (supported: 64, 128, 256)", cin);
+  VN_REQUIRE(packed_weight != nullptr && shift != nullptr && H >= 1 && W >= 1, "conv2d_pointwise: null pointer or empty input");
+  VN_REQUIRE(up >= 1 && up <= 8 && oy >= 0 && oy < up && ox >= 0 && ox < up, "conv2d_pointwise: up=%d offset (%d,%d)", up, oy, ox);
+  VN_REQUIRE(y_channels >= cout && y_channel_offset >= 0 && y_channel_offset + cout <= y_channels && y_channels % 16 == 0 &&
+                 y_channel_offset % 16 == 0,
+             "conv2d_pointwise: channels %d..%d of %d (multiples of 16 inside y)", y_channel_offset, y_channel_offset + cout, y_channels);
+  const float* ones = reinterpret_cast<const float*>(static_cast<const uint8_t*>(packed_weight) + (size_t)(cin / 64) * 3 * kBSlotBytes);
+  return conv_launch(x, B, 1, H, W, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr,
+                     planned ? VN_CONV_FLAGS_PLANNED : 0, nullptr, workspace, workspace_bytes, stream, nullptr, 0, nullptr, cout / 64,
+                     y_channels, y_channel_offset, 0, 0, 1, up, oy, ox);
 }
 
 }  // extern "C"

@@ -472,15 +472,16 @@ def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
     _require_cuda(weight, scale)
     w = _contig(weight.detach(), torch.float32)
     cout, cin = int(w.shape[0]), int(w.shape[1])
-    if tuple(w.shape[2:]) != (3, 3):
-        raise RuntimeError("conv2d_pack_weights: 3x3 kernels only; got %s" % (tuple(w.shape),))
+    if tuple(w.shape[2:]) not in ((3, 3), (1, 1)):
+        raise RuntimeError("conv2d_pack_weights: 3x3 or 1x1 kernels only; got %s" % (tuple(w.shape),))
+    ksize = int(w.shape[2])
     nbytes = int(_cabi.lib().vn_conv2d_packed_weight_bytes(cin))
     if nbytes == 0:
         raise RuntimeError("conv2d_pack_weights: cin=%d unsupported (64, 128, 256)" % cin)
     packed = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
     with torch.cuda.device(w.device):
         check(_cabi.lib().vn_conv2d_pack_weights(_ptr(w), _ptr(None if scale is None else _contig(scale, torch.float32)), cin, cout,
-                                                 _ptr(packed), _stream()), "vn_conv2d_pack_weights")
+                                                 ksize, _ptr(packed), _stream()), "vn_conv2d_pack_weights")
     return packed
 
 
@@ -506,6 +507,25 @@ def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channe
                                                 int(out.shape[3]), int(channel_offset), 1 if planned else 0, _ptr(workspace),
                                                 workspace.numel(), _stream()),
               "vn_conv2d_bn_relu_fwd")
+    return out
+
+
+def conv2d_pointwise_fwd(x, packed_weight, shift, out, channel_offset: int = 0, up: int = 1, oy: int = 0, ox: int = 0,
+                         workspace=None, planned: bool = False) -> torch.Tensor:
+    """1x1 convolution + shift + ReLU of x (B,H,W,cin) bf16 written to positions (h*up + oy, w*up + ox), channels
+    channel_offset .. + cout, of out (B,H*up,W*up,C) bf16 - one of the up*up launches of a transposed convolution with
+    kernel = stride = up (vn_conv2d_pointwise_fwd)."""
+    _require_cuda(x, packed_weight, shift, out, workspace)
+    _contig(x, torch.bfloat16), _contig(shift, torch.float32), _contig(out, torch.bfloat16)
+    B, H, W, cin = x.shape
+    if tuple(out.shape[:3]) != (B, H * up, W * up):
+        raise RuntimeError("out must be (B, H*up, W*up, C); got %s" % (tuple(out.shape),))
+    if workspace is None:
+        workspace = torch.empty(conv2d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
+    with torch.cuda.device(x.device):
+        check(_cabi.lib().vn_conv2d_pointwise_fwd(_ptr(x), B, H, W, cin, int(shift.numel()), _ptr(packed_weight), _ptr(shift), _ptr(out),
+                                                  int(out.shape[3]), int(channel_offset), int(up), int(oy), int(ox), 1 if planned else 0,
+                                                  _ptr(workspace), workspace.numel(), _stream()), "vn_conv2d_pointwise_fwd")
     return out
 
 

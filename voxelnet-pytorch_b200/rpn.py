@@ -13,7 +13,8 @@ two launches of 128 output channels over four 64-channel input chunks (W = 44: t
 Together 15 of the RPN's 22 layers, 88 of its ~110 GFLOP.
 
 The stride-2 heads of the blocks run on the kernel's stride-2 instantiation (odd / even input rows as two boxes).
-The two strided `ConvTranspose2d` and the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
+`DeConvUpMD2d` is deconv2 / deconv3 (kernel = stride 2 / 4): k*k 1x1 launches that write each output pixel once.
+Only the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
 wraps a reference block so that its head runs on stock PyTorch and its stride-1 tail here, `HybridRPN` the whole RPN half
 of the reference's `MiddleConvNet`.
 """
@@ -33,8 +34,8 @@ class _PlanCache:
     def __init__(self):
         self._ws = {}
 
-    def get(self, B, H, W, n, device):
-        key = (B, H, W, n, str(device))
+    def get(self, B, H, W, n, device, kind: str = "3x3"):
+        key = (B, H, W, n, str(device), kind)
         hit = key in self._ws
         if not hit:
             self._ws[key] = torch.empty(ops.conv2d_workspace_bytes(B, H, W), dtype=torch.uint8, device=device)
@@ -166,6 +167,71 @@ class DeConvMD2d(_Conv3x3BnRelu):
         return [self.deconv.weight, self.deconv.bias]
 
 
+class DeConvUpMD2d(nn.Module):
+    """model.py:170-199 for kernel = stride = k, padding 0 (`deconv2 = DeConv2d(128, 256, 2, (2,2), (0,0))`, `deconv3 =
+    DeConv2d(256, 256, 4, (4,4), (0,0))`, model.py:242,253): every output pixel (k y + i, k x + j) is a 1x1 convolution of
+    input pixel (y, x) with W[:, :, i, j] - k*k launches of `vn_conv2d_pointwise_fwd` per block of 128 output channels, each
+    writing its pixels once, BatchNorm + ReLU in the epilogue.  Parameter names as in the reference."""
+
+    def __init__(self, cin: int, cout: int, k: int):
+        super().__init__()
+        if cin not in (64, 128, 256) or cout % 64 != 0 or cout < 64 or not 1 <= k <= 8:
+            raise ValueError("DeConvUpMD2d: cin=%d, cout=%d, k=%d unsupported by the B200 kernel" % (cin, cout, k))
+        self.cin, self.cout, self.k = cin, cout, k
+        self.deconv = nn.ConvTranspose2d(cin, cout, k, k, 0)
+        self.batch_norm = nn.BatchNorm2d(cout)
+
+    @classmethod
+    def from_reference(cls, layer) -> "DeConvUpMD2d":
+        d = getattr(layer, "deconv", None)
+        if not isinstance(d, nn.ConvTranspose2d) or d.kernel_size[0] != d.kernel_size[1] or tuple(d.stride) != tuple(d.kernel_size) \
+                or tuple(d.padding) != (0, 0) or tuple(d.output_padding) != (0, 0):
+            raise ValueError("DeConvUpMD2d covers ConvTranspose2d with kernel = stride and no padding only")
+        m = cls(d.in_channels, d.out_channels, int(d.kernel_size[0]))
+        m.load_state_dict(layer.state_dict())
+        return m.to(d.weight.device).eval()
+
+    def folded(self):
+        """[(oy, ox, first output channel, packed 1x1 weights with the BatchNorm scale folded in, shift (n,) f32), ...]."""
+        ts = [self.deconv.weight, self.deconv.bias, self.batch_norm.weight, self.batch_norm.bias, self.batch_norm.running_mean,
+              self.batch_norm.running_var]
+        key = tuple((t.data_ptr(), t._version) for t in ts)
+        if getattr(self, "_packed", None) is None or self._key != key:
+            scale, bn_shift = _fold_bn(self.batch_norm)
+            shift = (self.deconv.bias.detach().double() * scale.double() + bn_shift.double()).float().contiguous()
+            w = self.deconv.weight.detach().float()  # (cin, cout, k, k)
+            parts = []
+            for oy in range(self.k):
+                for ox in range(self.k):
+                    w_ij = w[:, :, oy, ox].t().contiguous()[:, :, None, None]  # (cout, cin, 1, 1)
+                    o = 0
+                    while o < self.cout:
+                        n = min(128 if self.cout - o != 192 else 192, self.cout - o)
+                        parts.append((oy, ox, o, ops.conv2d_pack_weights(w_ij[o:o + n].contiguous(), scale[o:o + n].contiguous()),
+                                      shift[o:o + n].contiguous()))
+                        o += n
+            self._packed, self._key = parts, key
+        return self._packed
+
+    def forward_nhwc(self, x_nhwc: torch.Tensor, out=None, plans: "_PlanCache" = None, channel_offset: int = 0) -> torch.Tensor:
+        """(B,H,W,cin) bf16 contiguous -> (B,kH,kW,cout) bf16 (or channels channel_offset .. + cout of a wider `out`)."""
+        if self.training:
+            raise NotImplementedError("DeConvUpMD2d implements eval-mode BatchNorm (inference)")
+        B, H, W, _ = x_nhwc.shape
+        if out is None:
+            out = torch.empty((B, H * self.k, W * self.k, self.cout), dtype=torch.bfloat16, device=x_nhwc.device)
+        if plans is None:
+            plans = self.__dict__.setdefault("_plans", _PlanCache())
+        for oy, ox, o, packed, shift in self.folded():
+            ws, planned = plans.get(B, H, W, int(shift.numel()), x_nhwc.device, "1x1")
+            ops.conv2d_pointwise_fwd(x_nhwc, packed, shift, out, channel_offset=channel_offset + o, up=self.k, oy=oy, ox=ox,
+                                     workspace=ws, planned=planned)
+        return out
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        return self.forward_nhwc(_as_bf16_nhwc(x).permute(0, 2, 3, 1)).permute(0, 3, 1, 2)
+
+
 class _FoldedStock(nn.Module):
     """A stock layer for inference: Conv2d / ConvTranspose2d with the eval-mode BatchNorm folded into its weights and bias
     (one cuDNN call + an in-place ReLU instead of three passes over the activation), bf16 channels-last."""
@@ -274,10 +340,14 @@ class HybridRPN(nn.Module):
         self.deconv_stock = nn.ModuleList([_stock_bf16(getattr(middle_rpn, n)) for n in ("deconv1", "deconv2", "deconv3")])
         fast = []
         for n in ("deconv1", "deconv2", "deconv3"):
-            try:
-                fast.append(DeConvMD2d.from_reference(getattr(middle_rpn, n)))
-            except ValueError:
-                fast.append(nn.Identity())
+            m = nn.Identity()
+            for cls in (DeConvMD2d, DeConvUpMD2d):
+                try:
+                    m = cls.from_reference(getattr(middle_rpn, n))
+                    break
+                except ValueError:
+                    pass
+            fast.append(m)
         self.deconv_fast = nn.ModuleList(fast)
         # the two 1x1 heads read the same 768-channel tensor: one convolution with their weights stacked (2 + 14 outputs)
         import copy
@@ -288,11 +358,14 @@ class HybridRPN(nn.Module):
         head.bias.data = torch.cat([pc.bias.data, rc.bias.data], 0).clone()
         self.heads = head.to(device=pc.weight.device, dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
         self.n_prob = pc.out_channels
+        # the strided deconvolutions write every output once; even a map with few tiles beats the stock path's three passes
+        self.deconv_min_tiles = 0
 
     def set_min_tiles(self, min_tiles) -> None:
         """Feature maps with fewer 16x8 tiles than this run on the stock path (None: 4 per SM; 0: always tcgen05)."""
         for b in (self.block1, self.block2, self.block3):
             b.min_tiles = min_tiles
+        self.deconv_min_tiles = 0 if min_tiles is None else min_tiles
 
     def permute_input_channels(self, reference_channel_of_input: torch.Tensor) -> None:
         """The input's channel k holds the reference's channel reference_channel_of_input[k] (VoxelNetFrontEnd
@@ -302,6 +375,17 @@ class HybridRPN(nn.Module):
         for m in (self.block1.stock[0], self.block1.fast[0]):
             if hasattr(m, "conv"):
                 m.conv.weight.data = m.conv.weight.data[:, perm].contiguous()
+
+    def _deconv_up(self, i: int, x: torch.Tensor, cat: torch.Tensor, channel_offset: int, plans) -> None:
+        """deconv2 / deconv3 into their channel slice of the concatenated tensor: k*k pointwise launches on the tcgen05 kernel
+        when the map has enough tiles, else the stock copy + a slice copy."""
+        f = self.deconv_fast[i]
+        B, _, H, W = x.shape
+        if isinstance(f, DeConvUpMD2d) and _enough_tiles(B, H, W, x.device, self.deconv_min_tiles):
+            f.forward_nhwc(x.permute(0, 2, 3, 1), out=cat, plans=plans, channel_offset=channel_offset)
+        else:
+            y = self.deconv_stock[i](x)
+            cat[..., channel_offset:channel_offset + y.shape[1]] = y.permute(0, 2, 3, 1)
 
     def forward(self, x: torch.Tensor):
         plans = self.__dict__.setdefault("_plans", _PlanCache())
@@ -317,9 +401,9 @@ class HybridRPN(nn.Module):
         else:
             cat[..., c3 + c2:] = self.deconv_stock[0](x).permute(0, 2, 3, 1)
         x = self.block2(x, plans)
-        cat[..., c3:c3 + c2] = self.deconv_stock[1](x).permute(0, 2, 3, 1)
+        self._deconv_up(1, x, cat, c3, plans)
         x = self.block3(x, plans)
-        cat[..., :c3] = self.deconv_stock[2](x).permute(0, 2, 3, 1)
+        self._deconv_up(2, x, cat, 0, plans)
         x = cat.permute(0, 3, 1, 2)
         y = self.heads(x).float()
         return torch.sigmoid(y[:, : self.n_prob]).contiguous(), y[:, self.n_prob:].contiguous()
