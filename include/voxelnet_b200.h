@@ -274,7 +274,7 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
 /* ------------------------------------------------------------------------------------------
  * 2-D 3x3 convolution + BatchNorm2d(eval) + ReLU on the same tcgen05 kernel - the stride-1 ConvMD(2, 128, 128, 3, (1,1),
  * (1,1)) layers of the RPN blocks (voxelnet/model.py:212-251).  Channels-last bf16 in and out:
- *   x [B, H, W, cin] -> y [B, H, W, cout],  y = relu(conv(x, weight * scale) + shift),  cin in {64, 128, 256}, cout in
+ *   x [B, H, W, cin] -> y [B, H, W, cout],  y = relu(conv(x, weight * scale) + shift),  cin a multiple of 64 (<= 1024), cout in
  *   {64, 128, 192} per launch, any W (the last 8-wide tile column may be ragged).  stride 1, or 2 (the heads of the
  *   blocks, model.py:213,233,244): y is then [B, (H-1)/2+1, (W-1)/2+1, cout]; workspace and plan are those of the OUTPUT extent.  The groups of 64 output channels ride along the MMA's N dimension the way the depth
  *   taps of the 3-D layers do (one 128 x cout x 16 MMA per k-step).
@@ -302,11 +302,12 @@ int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_
  * voxelnet/model.py:242,253: DeConv2d(128, 256, 2, (2,2), (0,0)) and DeConv2d(256, 256, 4, (4,4), (0,0))) is up * up such launches
  * per block of <= 192 output channels, launch (oy, ox) carrying the weights W[:, :, oy, ox] (packed with ksize 1: weight
  * [cout][cin] f32) - each output is written once, straight into its slice of the concatenated tensor, BatchNorm and ReLU in
- * the epilogue.  up = 1 is a plain 1x1 convolution.  workspace / planned as in vn_conv2d_bn_relu_fwd (plans of 3x3 and 1x1
+ * the epilogue.  up = 1 is a plain 1x1 convolution; relu = 0 drops the activation (the RPN's prob_conv / reg_conv heads,
+ * model.py:253-254: 768 -> 2 + 14 channels, padded to 64 output channels by the caller).  cin: a multiple of 64 up to 1024.  workspace / planned as in vn_conv2d_bn_relu_fwd (plans of 3x3 and 1x1
  * launches differ: do not share a planned workspace between them). */
 int vn_conv2d_pointwise_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout,
-                            const void* packed_weight, const float* shift, void* y, int32_t y_channels,
-                            int32_t y_channel_offset, int32_t up, int32_t oy, int32_t ox, int32_t planned,
+                            const void* packed_weight, const float* shift, int32_t relu, void* y,
+                            int32_t y_channels, int32_t y_channel_offset, int32_t up, int32_t oy, int32_t ox, int32_t planned,
                             void* workspace, size_t workspace_bytes, vn_stream_t stream);
 
 /* Background folding for a layer whose INPUT is stored as a deviation from a background (what the previous

@@ -258,6 +258,7 @@ def test_hybrid_rpn_matches_the_fp32_rpn(cuda_device):
         p_want, r_want = ref(x)
     rpn = vn.HybridRPN(ref.to(cuda_device))
     rpn.set_min_tiles(0)  # (maps this small would otherwise take the stock path)
+    rpn.heads_on_tensor_cores = True  # (the 1x1 heads as a pointwise launch too: every layer of the RPN on the kernel)
     assert all(rpn.block1.on_tensor_cores(96)) and all(rpn.block2.on_tensor_cores(48))
     assert all(rpn.block3.on_tensor_cores(24))  # 256 channels, W = 12: ragged tile column
     assert isinstance(rpn.deconv_fast[0], vn.DeConvMD2d) and isinstance(rpn.deconv_fast[1], vn.DeConvUpMD2d) \
@@ -267,6 +268,7 @@ def test_hybrid_rpn_matches_the_fp32_rpn(cuda_device):
         stock = ref.to(dtype=torch.bfloat16, memory_format=torch.channels_last)
         p_st, r_st = stock(x.to(cuda_device).to(torch.bfloat16).contiguous(memory_format=torch.channels_last))
         rpn.set_min_tiles(None)
+        rpn.heads_on_tensor_cores = False
         p_auto, r_auto = rpn(x.to(cuda_device))  # default policy: these small maps run on the stock copies
     assert p_got.shape == (2, 2, 64, 48) and r_got.shape == (2, 14, 64, 48) and p_got.dtype == torch.float32
     for name, got in (("hybrid", (p_got, r_got)), ("hybrid, default tile policy", (p_auto, r_auto)), ("stock bf16", (p_st.float(), r_st.float()))):

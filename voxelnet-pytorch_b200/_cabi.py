@@ -70,7 +70,7 @@ PROTOTYPES = {
     "vn_conv2d_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "vn_conv2d_packed_weight_bytes": (_sz, [_i32]),
     "vn_conv2d_pack_weights": (C.c_int, [_p, _p, _i32, _i32, _i32, _p, _p]),
-    "vn_conv2d_pointwise_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p, _sz, _p]),
+    "vn_conv2d_pointwise_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _p, _p, _i32, _p, _i32, _i32, _i32, _i32, _i32, _i32, _p, _sz, _p]),
     "vn_conv2d_bn_relu_fwd": (C.c_int, [_p, _i32, _i32, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _i32, _i32, _p, _sz, _p]),
     "vn_conv3d_plan": (C.c_int, [_i32, _i32, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _sz, _p]),
     "vn_conv3d_fold_background": (C.c_int, [_p, _i32, _i32, _i32, _i32, _p, _p, _p, _i32, _p, _p, _p]),

@@ -106,6 +106,7 @@ struct ConvParams {
   int out_ctotal, out_coff;  // out_mode 2: channels per position of y and the first channel this launch writes
   int out_up, out_oy, out_ox;  // out_mode 2: output position (h, w) is written at (h * out_up + out_oy, w * out_up + out_ox) of a
                                // [B, H * out_up, W * out_up, out_ctotal] tensor (a transposed convolution with kernel = stride)
+  float relu_floor;     // y = max(conv * scale + shift, relu_floor) - sub: 0 = ReLU, -inf = no activation
   int pointwise;        // kS2 instantiation: 1x1 convolution - only the centre tap (kw = 1, kh = 1) exists, stride 1
   int table_plain;      // table is a plain [64] shift vector used for every row
   const float* sub;     // [Dout][64] subtracted after the ReLU, or nullptr
@@ -897,6 +898,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
     const uint32_t m = quad * 32 + lane;           // accumulator row = output position in the tile
     const int hl = m / kTileW, wl = m % kTileW;
     const float* scale_h = ctl->scale + half * 32;
+    const float relu_floor = P.relu_floor;  // 0 (ReLU), or -inf for a layer without activation (the 1x1 heads of the RPN)
     uint32_t s_it = 0, acc_phase = 0;
     float st_s[kTrain ? 32 : 1], st_q[kTrain ? 32 : 1];
 #pragma unroll
@@ -976,7 +978,7 @@ __global__ void __launch_bounds__(kGather ? kThreadsGather : kThreads, 1)
             } else {
 #pragma unroll
               for (int j = 0; j < 32; ++j)
-                v[j] = fmaxf(fmaf(__uint_as_float(r[j]), scale_h[j], shift_row[j]), 0.0f) - sub_row[j];
+                v[j] = fmaxf(fmaf(__uint_as_float(r[j]), scale_h[j], shift_row[j]), relu_floor) - sub_row[j];
             }
             if (P.out_mode != 1) {
               __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(P.out) +
@@ -1446,10 +1448,11 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
                        int32_t flag_opts, uint8_t* out_state, void* workspace, size_t workspace_bytes,
                        vn_stream_t stream, double* stats, int32_t transposed_dout = 0, const GatherSrc* gather = nullptr,
                        int32_t groups2d = 0, int32_t out_ctotal = 0, int32_t out_coff = 0, int32_t s2_hin = 0, int32_t s2_win = 0,
-                       int32_t pointwise = 0, int32_t out_up = 1, int32_t out_oy = 0, int32_t out_ox = 0) {
+                       int32_t pointwise = 0, int32_t out_up = 1, int32_t out_oy = 0, int32_t out_ox = 0, int32_t no_relu = 0) {
   // s2_hin > 0 (2-D layers only): stride 2 in H and W; x is [B, 1, s2_hin, s2_win, cin] and H, W are the OUTPUT extents
   VN_REQUIRE((x || gather) && packed_weight && scale && shift_table && y, "conv3d: null pointer");
-  VN_REQUIRE(cin == 64 || cin == 128 || (groups2d > 0 && cin == 256), "conv3d: cin=%d (supported: 64, 128; 2-D layers also 256)", cin);
+  VN_REQUIRE(cin == 64 || cin == 128 || (groups2d > 0 && cin % 64 == 0 && cin >= 64 && cin <= 1024),
+             "conv3d: cin=%d (supported: 64, 128; 2-D layers: multiples of 64 up to 1024)", cin);
   VN_REQUIRE(B >= 1 && Din >= 1 && H >= 1 && W >= 1, "conv3d: empty input");
   VN_REQUIRE((stride_d == 1 || stride_d == 2) && (pad_d == 0 || pad_d == 1), "conv3d: stride_d=%d pad_d=%d unsupported",
              stride_d, pad_d);
@@ -1551,6 +1554,7 @@ static int conv_launch(const void* x, int32_t B, int32_t Din, int32_t H, int32_t
   P.out_coff = out_coff;
   P.out_up = out_up; P.out_oy = out_oy; P.out_ox = out_ox;
   P.pointwise = pointwise;
+  P.relu_floor = no_relu ? -INFINITY : 0.0f;
   P.sub = sub;
   P.out = y;
   P.hdr = hdr; P.groups = groups; P.tiles = tiles; P.gtiles = gtiles;
@@ -1691,14 +1695,14 @@ size_t vn_conv2d_workspace_bytes(int32_t B, int32_t H, int32_t W) {
 }
 
 size_t vn_conv2d_packed_weight_bytes(int32_t cin) {
-  if (cin != 64 && cin != 128 && cin != 256) return 0;
+  if (cin < 64 || cin > 1024 || cin % 64 != 0) return 0;
   return (size_t)(cin / 64) * 3 * kBSlotBytes + 64 * sizeof(float);
 }
 
 int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout, int32_t ksize, void* packed,
                            vn_stream_t stream) {
   VN_REQUIRE(ksize == 3 || ksize == 1, "conv2d_pack_weights: ksize=%d (supported: 3, 1)", ksize);
-  VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d_pack_weights: cin=%d (supported: 64, 128, 256)", cin);
+  VN_REQUIRE(cin >= 64 && cin <= 1024 && cin % 64 == 0, "conv2d_pack_weights: cin=%d (multiples of 64 up to 1024)", cin);
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d_pack_weights: cout=%d (supported: 64, 128, 192)", cout);
   VN_REQUIRE(weight != nullptr && packed != nullptr && (reinterpret_cast<uintptr_t>(packed) & 15) == 0,
              "conv2d_pack_weights: null or misaligned pointer");
@@ -1712,7 +1716,7 @@ int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_
                           const void* packed_weight, const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset,
                           int32_t planned, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d: cout=%d (supported: 64, 128, 192)", cout);
-  VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d: cin=%d (supported: 64, 128, 256)", cin);
+  VN_REQUIRE(cin >= 64 && cin <= 1024 && cin % 64 == 0, "conv2d: cin=%d (multiples of 64 up to 1024)", cin);
   VN_REQUIRE(stride == 1 || stride == 2, "conv2d: stride=%d (supported: 1, 2)", stride);
   VN_REQUIRE(packed_weight != nullptr && shift != nullptr && H >= 1 && W >= 1, "conv2d: null pointer or empty input");
   VN_REQUIRE(y_channels >= cout && y_channel_offset >= 0 && y_channel_offset + cout <= y_channels && y_channels % 16 == 0 &&
@@ -1726,10 +1730,10 @@ int vn_conv2d_bn_relu_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_
 }
 
 int vn_conv2d_pointwise_fwd(const void* x, int32_t B, int32_t H, int32_t W, int32_t cin, int32_t cout, const void* packed_weight,
-                            const float* shift, void* y, int32_t y_channels, int32_t y_channel_offset, int32_t up, int32_t oy,
-                            int32_t ox, int32_t planned, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
+                            const float* shift, int32_t relu, void* y, int32_t y_channels, int32_t y_channel_offset, int32_t up,
+                            int32_t oy, int32_t ox, int32_t planned, void* workspace, size_t workspace_bytes, vn_stream_t stream) {
   VN_REQUIRE(cout == 64 || cout == 128 || cout == 192, "conv2d_pointwise: cout=%d (supported: 64, 128, 192)", cout);
-  VN_REQUIRE(cin == 64 || cin == 128 || cin == 256, "conv2d_pointwise: cin=%d (supported: 64, 128, 256)", cin);
+  VN_REQUIRE(cin >= 64 && cin <= 1024 && cin % 64 == 0, "conv2d_pointwise: cin=%d (multiples of 64 up to 1024)", cin);
   VN_REQUIRE(packed_weight != nullptr && shift != nullptr && H >= 1 && W >= 1, "conv2d_pointwise: null pointer or empty input");
   VN_REQUIRE(up >= 1 && up <= 8 && oy >= 0 && oy < up && ox >= 0 && ox < up, "conv2d_pointwise: up=%d offset (%d,%d)", up, oy, ox);
   VN_REQUIRE(y_channels >= cout && y_channel_offset >= 0 && y_channel_offset + cout <= y_channels && y_channels % 16 == 0 &&
@@ -1738,7 +1742,7 @@ int vn_conv2d_pointwise_fwd(const void* x, int32_t B, int32_t H, int32_t W, int3
   const float* ones = reinterpret_cast<const float*>(static_cast<const uint8_t*>(packed_weight) + (size_t)(cin / 64) * 3 * kBSlotBytes);
   return conv_launch(x, B, 1, H, W, cin, 1, 1, packed_weight, ones, shift, 1, nullptr, 2, y, nullptr,
                      planned ? VN_CONV_FLAGS_PLANNED : 0, nullptr, workspace, workspace_bytes, stream, nullptr, 0, nullptr, cout / 64,
-                     y_channels, y_channel_offset, 0, 0, 1, up, oy, ox);
+                     y_channels, y_channel_offset, 0, 0, 1, up, oy, ox, relu ? 0 : 1);
 }
 
 }  // extern "C"

@@ -477,7 +477,7 @@ def conv2d_pack_weights(weight, scale=None) -> torch.Tensor:
     ksize = int(w.shape[2])
     nbytes = int(_cabi.lib().vn_conv2d_packed_weight_bytes(cin))
     if nbytes == 0:
-        raise RuntimeError("conv2d_pack_weights: cin=%d unsupported (64, 128, 256)" % cin)
+        raise RuntimeError("conv2d_pack_weights: cin=%d unsupported (multiples of 64 up to 1024)" % cin)
     packed = torch.empty(nbytes, dtype=torch.uint8, device=w.device)
     with torch.cuda.device(w.device):
         check(_cabi.lib().vn_conv2d_pack_weights(_ptr(w), _ptr(None if scale is None else _contig(scale, torch.float32)), cin, cout,
@@ -511,7 +511,7 @@ def conv2d_bn_relu_fwd(x, packed_weight, shift, out=None, workspace=None, channe
 
 
 def conv2d_pointwise_fwd(x, packed_weight, shift, out, channel_offset: int = 0, up: int = 1, oy: int = 0, ox: int = 0,
-                         workspace=None, planned: bool = False) -> torch.Tensor:
+                         workspace=None, planned: bool = False, relu: bool = True) -> torch.Tensor:
     """1x1 convolution + shift + ReLU of x (B,H,W,cin) bf16 written to positions (h*up + oy, w*up + ox), channels
     channel_offset .. + cout, of out (B,H*up,W*up,C) bf16 - one of the up*up launches of a transposed convolution with
     kernel = stride = up (vn_conv2d_pointwise_fwd)."""
@@ -523,7 +523,7 @@ def conv2d_pointwise_fwd(x, packed_weight, shift, out, channel_offset: int = 0, 
     if workspace is None:
         workspace = torch.empty(conv2d_workspace_bytes(B, H, W), dtype=torch.uint8, device=x.device)
     with torch.cuda.device(x.device):
-        check(_cabi.lib().vn_conv2d_pointwise_fwd(_ptr(x), B, H, W, cin, int(shift.numel()), _ptr(packed_weight), _ptr(shift), _ptr(out),
+        check(_cabi.lib().vn_conv2d_pointwise_fwd(_ptr(x), B, H, W, cin, int(shift.numel()), _ptr(packed_weight), _ptr(shift), 1 if relu else 0, _ptr(out),
                                                   int(out.shape[3]), int(channel_offset), int(up), int(oy), int(ox), 1 if planned else 0,
                                                   _ptr(workspace), workspace.numel(), _stream()), "vn_conv2d_pointwise_fwd")
     return out

@@ -14,7 +14,8 @@ Together 15 of the RPN's 22 layers, 88 of its ~110 GFLOP.
 
 The stride-2 heads of the blocks run on the kernel's stride-2 instantiation (odd / even input rows as two boxes).
 `DeConvUpMD2d` is deconv2 / deconv3 (kernel = stride 2 / 4): k*k 1x1 launches that write each output pixel once.
-Only the two 1x1 heads stay stock PyTorch (`north_star` keeps the whole RPN there); `RPNBlockTail`
+The two 1x1 heads (no BatchNorm, no activation) can run as one pointwise launch padded to 64 output channels
+(`HybridRPN.heads_on_tensor_cores`; the fused stock 1x1 convolution is 2 % faster and is the default) (`north_star` keeps the whole RPN there); `RPNBlockTail`
 wraps a reference block so that its head runs on stock PyTorch and its stride-1 tail here, `HybridRPN` the whole RPN half
 of the reference's `MiddleConvNet`.
 """
@@ -320,6 +321,12 @@ class RPNBlockTail(nn.Module):
         return x
 
 
+def pc_in_ok(cat: torch.Tensor) -> bool:
+    """The 1x1 heads run on the tcgen05 kernel when the concatenated tensor's channel count is a multiple of 64 (<= 1024)."""
+    c = int(cat.shape[3])
+    return c % 64 == 0 and 64 <= c <= 1024
+
+
 class HybridRPN(nn.Module):
     """The RPN half of the reference's `MiddleConvNet` (model.py:212-254, forward :263-281) in bf16 channels-last, with the
     layers the tcgen05 kernel covers running on it - the stride-1 3x3 layers of block1 / block2 and deconv1, 75 of the
@@ -358,6 +365,17 @@ class HybridRPN(nn.Module):
         head.bias.data = torch.cat([pc.bias.data, rc.bias.data], 0).clone()
         self.heads = head.to(device=pc.weight.device, dtype=torch.bfloat16, memory_format=torch.channels_last).eval()
         self.n_prob = pc.out_channels
+        # ... and the same 1x1 convolution on the tcgen05 kernel: 16 outputs padded to one group of 64, no activation
+        n_out = pc.out_channels + rc.out_channels
+        w64 = torch.zeros((64, pc.in_channels, 1, 1), dtype=torch.float32, device=pc.weight.device)
+        b64 = torch.zeros(64, dtype=torch.float32, device=pc.weight.device)
+        w64[:n_out] = torch.cat([pc.weight.data, rc.weight.data], 0).float()
+        b64[:n_out] = torch.cat([pc.bias.data, rc.bias.data], 0).float()
+        self._head_w64, self._head_b64, self._head_packed = w64, b64, None
+        # measured at Car batch 16: 3.07 ms with the heads on the kernel (N = 64 MMAs over 12 channel chunks) vs 3.00 ms with the
+        # fused stock 1x1 convolution - off by default, parity-tested
+        self.heads_on_tensor_cores = False
+        self.n_out = n_out
         # the strided deconvolutions write every output once; even a map with few tiles beats the stock path's three passes
         self.deconv_min_tiles = 0
 
@@ -404,6 +422,14 @@ class HybridRPN(nn.Module):
         self._deconv_up(1, x, cat, c3, plans)
         x = self.block3(x, plans)
         self._deconv_up(2, x, cat, 0, plans)
+        if self.heads_on_tensor_cores and pc_in_ok(cat) and cat.is_cuda:
+            if self._head_packed is None:
+                self._head_packed = ops.conv2d_pack_weights(self._head_w64)
+            ws, planned = plans.get(B, H, W, 64, cat.device, "1x1")
+            y64 = torch.empty((B, H, W, 64), dtype=torch.bfloat16, device=cat.device)
+            ops.conv2d_pointwise_fwd(cat, self._head_packed, self._head_b64, y64, workspace=ws, planned=planned, relu=False)
+            y = y64[..., : self.n_out].permute(0, 3, 1, 2).float()
+            return torch.sigmoid(y[:, : self.n_prob]).contiguous(), y[:, self.n_prob:].contiguous()
         x = cat.permute(0, 3, 1, 2)
         y = self.heads(x).float()
         return torch.sigmoid(y[:, : self.n_prob]).contiguous(), y[:, self.n_prob:].contiguous()
