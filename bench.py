@@ -372,6 +372,7 @@ def main():
     ap.add_argument("--output", default="nchw_f32", choices=["nchw_f32", "nhwc_bf16"],
                     help="format of the returned tensor: the reference's float32 (B,128,H,W) (default), or bf16 channels-last for a bf16 RPN")
     ap.add_argument("--host-threads", type=int, default=None, help="threads of the host frame packer (default: cores / ranks, 2..8)")
+    ap.add_argument("--no-rpn", action="store_true", help="skip the points -> RPN maps figure (detection_pipeline, N=1 only)")
     ap.add_argument("--in-flight", type=int, default=None,
                     help="eval steps in flight per GPU (front ends on their own streams; 1 = strictly one step at a time); "
                          "default 3, or 1 for batches above 16 frames per GPU (each pipeline holds its own grid and outputs)")
@@ -671,6 +672,60 @@ def main():
                       "note": "bit-identical output (tests/test_gpu_bench_parity.py); compare with single_pipeline.ms_per_step and config.device_bytes_per_front_end"}
         del g_o, fe_o
 
+    # ---- SURVEY 8(f) "next" row: the RPN behind the path (N = 1 only; one step at a time, eager launches) ----------
+    # Not part of `value` / `e2e`: the front end hands its map over as bf16 channels-last and the RPN half of the reference's
+    # MiddleConvNet (model.py:212-281) runs on the tcgen05 kernel (HybridRPN) - beside the same layers on stock bf16 cuDNN.
+    detect = None
+    if world == 1 and batch <= 16 and not args.no_rpn:
+        try:
+            torch.manual_seed(2)
+            rpn_ref = vn.RPN(target).to(dev).eval()
+            for m in rpn_ref.modules():
+                if isinstance(m, torch.nn.BatchNorm2d):
+                    m.weight.data = 0.5 + torch.rand(m.weight.shape, generator=g).to(dev)
+                    m.bias.data = ((torch.rand(m.bias.shape, generator=g) - 0.5) * 0.6).to(dev)
+                    m.running_mean.data = ((torch.rand(m.running_mean.shape, generator=g) - 0.5) * 0.4).to(dev)
+                    m.running_var.data = (0.5 + torch.rand(m.running_var.shape, generator=g)).to(dev)
+            fe_d = vn.VoxelNetFrontEnd(fnet, mnet, target, output_format="nhwc_bf16")
+            n_rep = max(10, min(args.steps, 50))
+
+            def timed(fn):
+                for _ in range(3):
+                    fn()
+                barrier()
+                f0.record()
+                for i in range(n_rep):
+                    fn(i)
+                f1.record()
+                barrier()
+                return f0.elapsed_time(f1) / n_rep
+
+            with torch.no_grad():
+                hy = vn.HybridRPN(rpn_ref)
+                hy.permute_input_channels(fe_d.reference_channel_of_output())
+                x_d = fe_d.forward_points(batches[0].points, batches[0].offsets, batches[0].max_n)
+                ms_rpn = timed(lambda i=0: hy(x_d))
+                ms_both = timed(lambda i=0: hy(fe_d.forward_points(batches[i % 2].points, batches[i % 2].offsets, batches[i % 2].max_n)))
+                st = vn.HybridRPN(rpn_ref)
+                st.permute_input_channels(fe_d.reference_channel_of_output())
+                st.set_min_tiles(1 << 30)  # every layer on the private bf16 channels-last copies of the stock layers
+                ms_stock = timed(lambda i=0: st(x_d))
+                prob, reg = hy(x_d)
+                p2, r2 = st(x_d)
+                torch.cuda.synchronize()
+                dev_vs_stock = max(float((prob - p2).abs().max()), float((reg - r2).abs().max() / r2.abs().max().clamp_min(1e-6)))
+            detect = {
+                "rpn_ms_per_batch": ms_rpn, "rpn_stock_bf16_ms_per_batch": ms_stock,
+                "points_to_rpn_maps_ms_per_batch": ms_both, "points_to_rpn_maps_frames_per_s": batch / (ms_both * 1e-3),
+                "outputs": [list(prob.shape), list(reg.shape)], "max_dev_vs_stock_bf16": dev_vs_stock, "reps": n_rep,
+                "note": "voxelnet_pytorch_b200.HybridRPN(RPN(%r)) behind VoxelNetFrontEnd(output_format='nhwc_bf16'): one step at a time on one "
+                        "stream, eager launches, inputs resident; random-init weights.  Outside `value` and `e2e` (SURVEY 8(f) next row); "
+                        "parity against the fp32 reference layers: tests/test_gpu_rpn_conv2d.py" % target,
+            }
+            del hy, st, fe_d, x_d, rpn_ref
+        except Exception as e:  # the headline line must still be printed
+            detect = {"error": "%s: %s" % (type(e).__name__, e)}
+
     from voxelnet_pytorch_b200 import sharding
 
     per_rank_ms = sharding.gather_floats(ms_total / args.steps)
@@ -787,6 +842,7 @@ def main():
                 "value": frames_total / (ms_single / args.steps * 1e-3), "ms_per_step": ms_single / args.steps,
                 "note": "ONE step at a time (graph replays back to back on one stream): the latency of a step; `value` above is throughput with %d steps in flight" % P},
             "other_sparse_to_dense_form": other_form,
+            "detection_pipeline": detect,
             "gpu_launches": int(launches),
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
                          "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": traffic,

@@ -148,3 +148,37 @@ def test_hybrid_rpn_wraps_the_live_reference_rpn():
         and isinstance(rpn.deconv_fast[2], vn.DeConvUpMD2d) and rpn.deconv_fast[2].k == 4
     assert set(rpn.block1.fast[1].state_dict()) == set(net.block1[1].state_dict())
     assert net.block1[0].conv.weight.dtype == torch.float32
+
+
+def test_rpn_mirror_has_the_reference_parameter_names_and_output():
+    """vn.RPN is the RPN half of the reference's MiddleConvNet under the same parameter names: the reference's state dict
+    (minus middle_layer.*) loads strictly, and the two forwards agree bit for bit on a small map (stock fp32 layers on both
+    sides)."""
+    import voxelnet_pytorch_b200 as vn
+
+    ref = R.load_reference()
+    torch.manual_seed(3)
+    net = ref.model.MiddleConvNet().eval()
+    for m in net.modules():
+        if isinstance(m, torch.nn.BatchNorm2d):
+            m.running_mean.normal_(0, 0.1)
+            m.running_var.uniform_(0.5, 1.5)
+    mine = vn.RPN("Car").eval()
+    sd = {k: v for k, v in net.state_dict().items() if not k.startswith("middle_layer.")}
+    assert set(sd) == set(mine.state_dict())
+    mine.load_state_dict(sd, strict=True)
+    assert mine.output_shape == list(net.output_shape)
+
+    x = torch.randn(1, 128, 32, 16)
+    with torch.no_grad():
+        h = net.block1(x)
+        d1 = net.deconv1(h)
+        h = net.block2(h)
+        d2 = net.deconv2(h)
+        h = net.block3(h)
+        d3 = net.deconv3(h)
+        cat = torch.cat([d3, d2, d1], 1)
+        want = torch.sigmoid(net.prob_conv(cat)), net.reg_conv(cat)
+        got = mine(x)
+    assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+    assert vn.RPN("Pedestrian").block1[0].conv.stride == (1, 1)

@@ -25,6 +25,7 @@ import torch
 import torch.nn as nn
 
 from . import ops
+from .config import grid_config
 from .model import _fold_bn
 
 
@@ -433,3 +434,72 @@ class HybridRPN(nn.Module):
         x = cat.permute(0, 3, 1, 2)
         y = self.heads(x).float()
         return torch.sigmoid(y[:, : self.n_prob]).contiguous(), y[:, self.n_prob:].contiguous()
+
+
+class _StockConvMD2d(nn.Module):
+    """Parameter holder with the reference's ConvMD(2, ...) attribute names (`conv`, `batch_norm`, `bn`, `activation`;
+    model.py:111-167) on stock PyTorch layers - the fp32 form `RPN` trains and checkpoints in."""
+
+    def __init__(self, cin: int, cout: int, k: int, stride: int, pad: int, bn: bool = True, activation: bool = True):
+        super().__init__()
+        self.cin, self.cout, self.bn, self.activation = cin, cout, bn, activation
+        self.conv = nn.Conv2d(cin, cout, k, (stride, stride), (pad, pad))
+        if bn:
+            self.batch_norm = nn.BatchNorm2d(cout)
+
+    def forward(self, x):
+        x = self.conv(x)
+        if self.bn:
+            x = self.batch_norm(x)
+        return torch.relu(x) if self.activation else x
+
+
+class _StockDeConv2d(nn.Module):
+    """The reference's DeConv2d attribute names (`deconv`, `batch_norm`, `bn`; model.py:170-199) on stock layers."""
+
+    def __init__(self, cin: int, cout: int, k: int, stride: int, pad: int):
+        super().__init__()
+        self.cin, self.cout, self.bn = cin, cout, True
+        self.deconv = nn.ConvTranspose2d(cin, cout, k, (stride, stride), (pad, pad))
+        self.batch_norm = nn.BatchNorm2d(cout)
+
+    def forward(self, x):
+        return torch.relu(self.batch_norm(self.deconv(x)))
+
+
+class RPN(nn.Module):
+    """The region-proposal half of the reference's `MiddleConvNet` (model.py:212-254; forward :263-281) under the
+    reference's parameter names (block1..3, deconv1..3, prob_conv, reg_conv), so that the RPN entries of a reference
+    checkpoint load with a strict `load_state_dict` once the `middle_layer.*` keys are dropped.  This class is
+    the fp32 stock form (training, checkpoints, the parity reference); `HybridRPN(RPN(...))` is the inference form on the
+    tcgen05 kernel.  Car: block1 starts with a stride-2 layer; Pedestrian / Cyclist: stride 1 (model.py:220-236)."""
+
+    def __init__(self, cls_name: str = "Car"):
+        super().__init__()
+        s1 = 2 if cls_name == "Car" else 1
+
+        def block(cin, cout, n, stride):
+            return nn.Sequential(_StockConvMD2d(cin, cout, 3, stride, 1), *[_StockConvMD2d(cout, cout, 3, 1, 1) for _ in range(n - 1)])
+
+        self.block1 = block(128, 128, 5, s1)
+        self.deconv1 = _StockDeConv2d(128, 256, 3, 1, 1)
+        self.block2 = block(128, 128, 6, 2)
+        self.deconv2 = _StockDeConv2d(128, 256, 2, 2, 0)
+        self.block3 = block(128, 256, 6, 2)
+        self.deconv3 = _StockDeConv2d(256, 256, 4, 4, 0)
+        self.prob_conv = _StockConvMD2d(768, 2, 1, 1, 0, bn=False, activation=False)
+        self.reg_conv = _StockConvMD2d(768, 14, 1, 1, 0, bn=False, activation=False)
+        g = grid_config(cls_name)
+        ratio = 2 if cls_name == "Car" else 1  # config.py:51-53 / :74-76 (FEATURE_RATIO)
+        self.output_shape = [g.height // ratio, g.width // ratio]
+
+    def forward(self, x: torch.Tensor):
+        """x: (B, 128, H, W) float32 - the front end's map.  Returns (sigmoid(prob) (B,2,h,w), reg (B,14,h,w))."""
+        x = self.block1(x)
+        d1 = self.deconv1(x)
+        x = self.block2(x)
+        d2 = self.deconv2(x)
+        x = self.block3(x)
+        d3 = self.deconv3(x)
+        x = torch.cat([d3, d2, d1], dim=1)
+        return torch.sigmoid(self.prob_conv(x)), self.reg_conv(x)
