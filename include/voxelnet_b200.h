@@ -28,7 +28,7 @@
 extern "C" {
 #endif
 
-#define VN_ABI_VERSION 15
+#define VN_ABI_VERSION 16
 
 #define VN_OK 0
 #define VN_ERR_BAD_ARG (-1)
@@ -448,6 +448,26 @@ int vn_rpn_targets(const float* anchors_standup, const double* anchors, int32_t 
                    const double* gt_boxes, const int32_t* gt_offsets, int32_t n_frames, int32_t n_boxes_total,
                    float pos_iou, float neg_iou, double anchor_h, double* pos_equal_one, double* neg_equal_one,
                    double* targets, void* workspace, size_t workspace_bytes, vn_stream_t stream);
+
+/* vn_rpn_targets without a caller workspace and without any allocation.  This entry point has no counterpart in the
+ * reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  The scratch of the four kernels lives in a
+ * file-scope `static __device__` array of VN_RPN_TARGETS_STATIC_BYTES (16 MiB) inside the library; every GPU that loads
+ * the library holds it until the process exits.  Same arguments, outputs and results as vn_rpn_targets (bit-identical);
+ * the call enqueues the same four launches on `stream` and calls no cudaMalloc / cudaFree or allocating routine.
+ * Limit: vn_rpn_targets_workspace_bytes(n_frames, n_anchors, n_boxes_total) <= VN_RPN_TARGETS_STATIC_BYTES, i.e.
+ * about n_frames * n_anchors * 8 + n_boxes_total * 8 bytes - Car (70,400 anchors) up to 29 frames per call; beyond it
+ * the call returns VN_ERR_WORKSPACE with the sizes in vn_last_error() and launches nothing.
+ * Every call on a device shares the one array, which keeps the previous call's contents: the part that must start from
+ * a known value is re-initialised by the call's first kernel, but two calls that OVERLAP on the GPU (different streams,
+ * no ordering between them) race - serialise them, or use vn_rpn_targets with separate workspaces.
+ * vn_rpn_targets_static_capacity_bytes() returns VN_RPN_TARGETS_STATIC_BYTES as compiled into the library. */
+#define VN_RPN_TARGETS_STATIC_BYTES (16u << 20)
+size_t vn_rpn_targets_static_capacity_bytes(void);
+int vn_rpn_targets_static(const float* anchors_standup, const double* anchors, int32_t n_anchors, const float* gt_standup,
+                          const double* gt_boxes, const int32_t* gt_offsets, int32_t n_frames, int32_t n_boxes_total,
+                          float pos_iou, float neg_iou, double anchor_h, double* pos_equal_one, double* neg_equal_one,
+                          double* targets, vn_stream_t stream);
 
 /* ------------------------------------------------------------------------------------------
  * Host-side frame packer (HOST pointers only; no CUDA call) - the head of the input path that replaces the

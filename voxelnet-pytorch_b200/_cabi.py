@@ -14,7 +14,7 @@ import threading
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "lib", "libvoxelnet_b200.so")
 
-VN_ABI_VERSION = 15
+VN_ABI_VERSION = 16
 VN_CONV_FLAGS_CONSUME = 1
 VN_CONV_FLAGS_BORDER_RING = 2
 VN_CONV_FLAGS_PLANNED = 4
@@ -67,6 +67,8 @@ PROTOTYPES = {
     "vn_rpn_targets_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "vn_rpn_targets": (C.c_int, [_p, _p, _i32, _p, _p, _p, _i32, _i32, C.c_float, C.c_float, C.c_double, _p, _p, _p,
                                  _p, _sz, _p]),
+    "vn_rpn_targets_static_capacity_bytes": (_sz, []),
+    "vn_rpn_targets_static": (C.c_int, [_p, _p, _i32, _p, _p, _p, _i32, _i32, C.c_float, C.c_float, C.c_double, _p, _p, _p, _p]),
     "vn_conv2d_workspace_bytes": (_sz, [_i32, _i32, _i32]),
     "vn_conv2d_packed_weight_bytes": (_sz, [_i32]),
     "vn_conv2d_pack_weights": (C.c_int, [_p, _p, _i32, _i32, _i32, _p, _p]),

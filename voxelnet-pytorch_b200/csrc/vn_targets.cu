@@ -18,6 +18,13 @@
 // removed from the negatives (the reference's code for that is commented out, utils.py:453-460).
 #include "vn_common.cuh"
 
+#include <mutex>
+
+// Scratch of vn_rpn_targets_static: lives in every CUDA context that loads the library, from load until exit.
+// In host code `g_targets_scratch` is only a stand-in for the symbol - never a device address: the address comes from
+// cudaGetSymbolAddress, once per device, with that device current (static_scratch_for_current_device below).
+static __device__ __align__(256) unsigned char g_targets_scratch[VN_RPN_TARGETS_STATIC_BYTES];
+
 namespace vn {
 namespace {
 
@@ -151,6 +158,28 @@ __global__ void __launch_bounds__(256) k_targets_init(unsigned long long* best, 
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_best; i += stride) best[i] = 0ull;
 }
 
+constexpr size_t kStaticScratchBytes = VN_RPN_TARGETS_STATIC_BYTES;
+
+constexpr int kMaxDevices = 64;
+std::mutex g_scratch_mutex;
+void* g_scratch_addr[kMaxDevices] = {};
+
+// 0 and *out = the device address of g_targets_scratch on the current device, else a cudaError_t (> 0) / VN_ERR_*.
+int static_scratch_for_current_device(void** out) {
+  int dev = -1;
+  VN_CUDA(cudaGetDevice(&dev));
+  VN_REQUIRE(dev >= 0 && dev < kMaxDevices, "rpn_targets_static: device ordinal %d outside 0..%d", dev, kMaxDevices - 1);
+  std::lock_guard<std::mutex> lock(g_scratch_mutex);
+  if (g_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    VN_CUDA(cudaGetSymbolAddress(&p, g_targets_scratch));
+    VN_REQUIRE(p != nullptr && (reinterpret_cast<uintptr_t>(p) & 255) == 0, "rpn_targets_static: bad symbol address");
+    g_scratch_addr[dev] = p;
+  }
+  *out = g_scratch_addr[dev];
+  return VN_OK;
+}
+
 }  // namespace
 }  // namespace vn
 
@@ -212,6 +241,33 @@ int vn_rpn_targets(const float* anchors_standup, const double* anchors, int32_t 
                                         pos_equal_one, targets);
   VN_LAUNCH_CHECK("k_targets_write");
   return VN_OK;
+}
+
+size_t vn_rpn_targets_static_capacity_bytes(void) { return kStaticScratchBytes; }
+
+// vn_rpn_targets with its scratch in the library's own static device array: no allocation of any kind on this path
+// (no cudaMalloc / cudaFree, no allocating library routine) - only the four launches of vn_rpn_targets.  Every call on
+// a device uses the same array: k_targets_init re-arms the parts that must start from a known value, the rest is
+// written before it is read, so stale contents of the previous call are harmless; two calls that overlap on the GPU race.
+int vn_rpn_targets_static(const float* anchors_standup, const double* anchors, int32_t n_anchors, const float* gt_standup,
+                          const double* gt_boxes, const int32_t* gt_offsets, int32_t n_frames, int32_t n_boxes_total,
+                          float pos_iou, float neg_iou, double anchor_h, double* pos_equal_one, double* neg_equal_one,
+                          double* targets, vn_stream_t stream) {
+  VN_REQUIRE(n_frames >= 0 && n_anchors >= 0 && n_boxes_total >= 0, "rpn_targets_static: negative size");
+  if (n_frames == 0 || n_anchors == 0) return VN_OK;
+  const size_t need = vn_rpn_targets_workspace_bytes(n_frames, n_anchors, n_boxes_total);
+  if (need > kStaticScratchBytes) {
+    set_error("rpn_targets_static: %d frames x %d anchors with %d boxes need %zu bytes of scratch, the static array holds %zu "
+              "(VN_RPN_TARGETS_STATIC_BYTES) - use vn_rpn_targets with a caller workspace", n_frames, n_anchors,
+              n_boxes_total, need, kStaticScratchBytes);
+    return VN_ERR_WORKSPACE;
+  }
+  void* scratch = nullptr;
+  const int rc = static_scratch_for_current_device(&scratch);
+  if (rc != VN_OK) return rc;
+  return vn_rpn_targets(anchors_standup, anchors, n_anchors, gt_standup, gt_boxes, gt_offsets, n_frames, n_boxes_total,
+                        pos_iou, neg_iou, anchor_h, pos_equal_one, neg_equal_one, targets, scratch, kStaticScratchBytes,
+                        stream);
 }
 
 }  // extern "C"

@@ -844,3 +844,33 @@ def rpn_targets(anchors_standup, anchors, gt_standup, gt_boxes, gt_offsets, pos_
             "vn_rpn_targets",
         )
     return pos, neg, targets
+
+
+def rpn_targets_static_capacity_bytes() -> int:
+    return int(_cabi.lib().vn_rpn_targets_static_capacity_bytes())
+
+
+def rpn_targets_static(anchors_standup, anchors, gt_standup, gt_boxes, gt_offsets, pos_iou: float, neg_iou: float,
+                       anchor_h: float, pos, neg, targets):
+    """`rpn_targets` through vn_rpn_targets_static: the scratch is the library's static device array and the CALLER passes
+    the outputs (pos, neg (B,A) f64; targets (B,A,7) f64), so nothing is allocated on this path - neither by the library
+    nor here.  Raises when the batch needs more scratch than the array holds (header: VN_RPN_TARGETS_STATIC_BYTES).
+    Calls on one device share the array: do not let two of them overlap on the GPU."""
+    _require_cuda(anchors_standup, anchors, gt_standup, gt_boxes, gt_offsets, pos, neg, targets)
+    _contig(anchors_standup, torch.float32), _contig(anchors, torch.float64)
+    _contig(gt_standup, torch.float32), _contig(gt_boxes, torch.float64), _contig(gt_offsets, torch.int32)
+    _contig(pos, torch.float64), _contig(neg, torch.float64), _contig(targets, torch.float64)
+    A, B, G = anchors.shape[0], gt_offsets.numel() - 1, gt_boxes.shape[0]
+    if anchors_standup.shape != (A, 4) or anchors.shape != (A, 7) or gt_standup.shape != (G, 4) or gt_boxes.shape != (G, 7):
+        raise RuntimeError("rpn_targets_static: inconsistent shapes")
+    if pos.numel() != B * A or neg.numel() != B * A or targets.numel() != B * A * 7:
+        raise RuntimeError("rpn_targets_static: outputs must hold (B,A), (B,A) and (B,A,7) float64")
+    with torch.cuda.device(anchors.device):
+        check(
+            _cabi.lib().vn_rpn_targets_static(
+                _ptr(anchors_standup), _ptr(anchors), A, _ptr(gt_standup) if G else None, _ptr(gt_boxes) if G else None,
+                _ptr(gt_offsets), B, G, pos_iou, neg_iou, anchor_h, _ptr(pos), _ptr(neg), _ptr(targets), _stream(),
+            ),
+            "vn_rpn_targets_static",
+        )
+    return pos, neg, targets
