@@ -719,7 +719,7 @@ __global__ void __launch_bounds__(kPackWarps * 32, 3) k_vox_svfe_packed(
         const int f0 = W.first[k];
         const uint32_t bits = (on_bits >> f0) & (n >= 32 ? 0xffffffffu : ((1u << n) - 1u));
         float o[4];
-        vfe2_voxel_max(W.x[f0], W.agg[k], n, (uint64_t)bits, q, sh, lane, o);
+        vfe2_voxel_max<uint32_t>(W.x[f0], W.agg[k], n, bits, q, sh, lane, o);  // (a batch holds at most 32 rows)
         const int64_t vrow = rg * kPackRange + a + k;
         store_voxel_out(o, lane, voxelwise != nullptr ? voxelwise + vrow * 128 : nullptr,
                         dense != nullptr ? dense + (dense_rows ? vrow : cell_k) * 128 : nullptr);
