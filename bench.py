@@ -847,7 +847,9 @@ def main():
             "roofline": {"kernel": "k_conv3d_bn_relu (layer %d)" % (dom + 1), "bound": kind, "achieved": dk[kind]["achieved"],
                          "peak": dk[kind]["peak"], "unit": dk[kind]["unit"], "frac": dk[kind]["frac"], "traffic": traffic,
                          "traffic_source": traffic_tab.get("source") if traffic is not None else None,
-                         "peak_source": peaks["source"] + (" (bf16_tflops_sustained)" if kind == "tensor" else " (hbm_gbs)"),
+                         "peak_source": peaks["source"] + (" (bf16_tflops_sustained: cuBLAS back to back for seconds, power-limited; a kernel timed inside this step can exceed it - "
+                                                           "the burst figure is %.0f TFLOP/s, frac_of_burst below)" % peaks["tflops_burst"] if kind == "tensor" else " (hbm_gbs)"),
+                         "frac_of_burst": dk[kind]["achieved"] / peaks["tflops_burst"] if kind == "tensor" else None,
                          "counts": "executed work: MMAs issued / blocks moved, decoded from the device-built plan; "
                                    "dense-equivalent %.0f TFLOP/s" % dk["dense_equivalent_tflops"],
                          "other_bound": {k: dk[k] for k in ("tensor", "hbm") if k != kind}},
