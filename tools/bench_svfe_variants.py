@@ -1,5 +1,7 @@
-"""Stage times of the eval step for the build's VN_SVFE_VARIANT (read once per process by the library): prints the svfe stage
-and the single-pipeline step time.  Usage: VN_SVFE_VARIANT=2 python tools/bench_svfe_variants.py [reps]"""
+"""A/B harness for changes to the voxel -> SVFE kernel: prints the svfe / voxelize stage times (eager, CUDA events between the
+stages), the one-step-at-a-time graph-replay time and a checksum of the output (bit-identical variants print the same one).
+While variants were compared the library read VN_SVFE_VARIANT once per process (history); the shipped
+build has one variant and ignores it.  Usage: python tools/bench_svfe_variants.py [reps]"""
 import json
 import os
 import sys
