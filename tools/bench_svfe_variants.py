@@ -44,5 +44,6 @@ for i in range(reps * 2):
     graphs[i % 2].replay()
 e1.record()
 torch.cuda.synchronize()
-print(json.dumps({"variant": os.environ.get("VN_SVFE_VARIANT", "0"), "svfe_ms": t.summary()["svfe"][0], "voxelize_ms": t.summary()["voxelize"][0],
+print(json.dumps({"variant": os.environ.get("VN_SVFE_VARIANT", "0"), "f32_store": os.environ.get("VN_CONV_F32_STORE", "0"),
+                  "stages_ms": {k: round(v[0], 4) for k, v in t.summary().items()}, "svfe_ms": t.summary()["svfe"][0], "voxelize_ms": t.summary()["voxelize"][0],
                   "step_ms": e0.elapsed_time(e1) / (reps * 2), "checksum": check}))
