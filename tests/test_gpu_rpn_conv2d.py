@@ -275,3 +275,38 @@ def test_hybrid_rpn_matches_the_fp32_rpn(cuda_device):
         p, r = got[0].cpu(), got[1].cpu()
         assert float((p - p_want).abs().max()) < 2e-2, name
         assert float((r - r_want).norm() / r_want.norm()) < 2e-2, name
+
+
+def test_middle_rpn_drop_in_forward_and_fused_inference_pair(cuda_device):
+    """vn.MiddleRPN (the reference's whole MiddleConvNet under its names): forward(x (B,D,H,W,128)) = the tcgen05 3-D layers
+    followed by the stock fp32 RPN half - the same bits as vn.RPN(vn.MiddleConvNet(x)) with the same parameters - and the
+    inference pair `front_end()` (fused eval step, bf16 channels-last hand-over) + HybridRPN stays within the bf16 bar of
+    the float32 RPN fed by the float32 front end."""
+    import voxelnet_pytorch_b200 as vn
+    from voxelnet_pytorch_b200 import synth
+
+    g = torch.Generator().manual_seed(21)
+    net = _randomise(vn.MiddleRPN("Pedestrian"), g).to(cuda_device).eval()
+    mid, rpn32 = vn.MiddleConvNet().to(cuda_device).eval(), vn.RPN("Pedestrian").to(cuda_device).eval()
+    sd = net.state_dict()
+    mid.load_state_dict({k: v for k, v in sd.items() if k.startswith("middle_layer.")}, strict=True)
+    rpn32.load_state_dict({k: v for k, v in sd.items() if not k.startswith("middle_layer.")}, strict=True)
+    # the module forward on a small sparse grid
+    dense = torch.zeros((1, 10, 32, 48, 128))
+    cells = torch.randint(0, 10 * 32 * 48, (400,), generator=g)
+    dense.view(-1, 128)[cells] = torch.rand((400, 128), generator=g)
+    with torch.no_grad():
+        p_mod, r_mod = net(dense.to(cuda_device))
+        p_two, r_two = rpn32(mid(dense.to(cuda_device)))
+    assert p_mod.shape == (1, 2, 32, 48) and r_mod.shape == (1, 14, 32, 48)
+    assert torch.equal(p_mod, p_two) and torch.equal(r_mod, r_two)
+    # the inference pair against the float32 path, from points
+    fnet = vn.FeatureLearningNet("Pedestrian").to(cuda_device).eval()
+    frames = [f[::3].copy() for f in synth.lidar_batch(2, seed0=31)]
+    with torch.no_grad():
+        y = vn.VoxelNetFrontEnd(fnet, net, "Pedestrian").forward_frames(frames).clone()  # (B,128,H,W) float32
+        p_want, r_want = rpn32(y)
+        fe, hy = net.front_end(fnet)
+        p_got, r_got = hy(fe.forward_frames(frames))
+    assert p_got.shape == p_want.shape == (2, 2, 200, 240) and r_got.shape == (2, 14, 200, 240)
+    assert float((p_got - p_want).abs().max()) < 2e-2 and float((r_got - r_want).norm() / r_want.norm()) < 2e-2

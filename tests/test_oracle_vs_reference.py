@@ -182,3 +182,29 @@ def test_rpn_mirror_has_the_reference_parameter_names_and_output():
         got = mine(x)
     assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
     assert vn.RPN("Pedestrian").block1[0].conv.stride == (1, 1)
+
+
+def test_middle_rpn_is_a_strict_state_dict_match_of_the_reference_middle_conv_net():
+    """vn.MiddleRPN = the reference's whole MiddleConvNet under its names: same state-dict keys in the same order, strict
+    load, same output_shape, and the RPN half of its forward (stock fp32) agrees bit for bit on CPU."""
+    import voxelnet_pytorch_b200 as vn
+
+    ref = R.load_reference()
+    torch.manual_seed(4)
+    net = ref.model.MiddleConvNet().eval()
+    mine = vn.MiddleRPN("Car").eval()
+    assert list(mine.state_dict()) == list(net.state_dict())
+    mine.load_state_dict(net.state_dict(), strict=True)
+    assert mine.output_shape == list(net.output_shape)
+    x = torch.randn(1, 128, 16, 16)
+    with torch.no_grad():
+        got = vn.RPN.forward(mine, x)
+        h = net.block1(x)
+        d1 = net.deconv1(h)
+        h = net.block2(h)
+        d2 = net.deconv2(h)
+        h = net.block3(h)
+        cat = torch.cat([net.deconv3(h), d2, d1], 1)
+        want = torch.sigmoid(net.prob_conv(cat)), net.reg_conv(cat)
+    assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
+    assert isinstance(mine.hybrid(), vn.HybridRPN)

@@ -10,12 +10,12 @@ from .config import CAR, PED_CYC, GridConfig, grid_config  # noqa: F401
 from .dataset import PinnedFrameBatch, collate_fn, load_velodyne_bin, pinned_frame, prepare_voxel  # noqa: F401
 from .model import ConvMD, FeatureLearningNet, MiddleConvNet, VFELayer  # noqa: F401
 from .pipeline import HostFrameStream, VoxelNetFrontEnd  # noqa: F401
-from .rpn import ConvMD2d, DeConvMD2d, DeConvUpMD2d, HybridRPN, RPN, RPNBlockTail  # noqa: F401
+from .rpn import ConvMD2d, DeConvMD2d, DeConvUpMD2d, HybridRPN, MiddleRPN, RPN, RPNBlockTail  # noqa: F401
 from .targets import TargetAssigner, bbox_iou, generate_anchors, generate_targets, label_to_gt_box_3d  # noqa: F401
 from .utils import VoxelBatch, pack_frames, pcl_to_voxels, voxelize_batch  # noqa: F401
 
 __all__ = [
     "CAR", "PED_CYC", "GridConfig", "grid_config", "collate_fn", "prepare_voxel", "ConvMD", "FeatureLearningNet",
-    "MiddleConvNet", "VFELayer", "ConvMD2d", "DeConvMD2d", "DeConvUpMD2d", "HybridRPN", "RPN", "RPNBlockTail", "VoxelNetFrontEnd", "HostFrameStream", "PinnedFrameBatch", "load_velodyne_bin", "pinned_frame", "VoxelBatch", "pack_frames", "pcl_to_voxels", "voxelize_batch",
+    "MiddleConvNet", "VFELayer", "ConvMD2d", "DeConvMD2d", "DeConvUpMD2d", "HybridRPN", "MiddleRPN", "RPN", "RPNBlockTail", "VoxelNetFrontEnd", "HostFrameStream", "PinnedFrameBatch", "load_velodyne_bin", "pinned_frame", "VoxelBatch", "pack_frames", "pcl_to_voxels", "voxelize_batch",
     "TargetAssigner", "bbox_iou", "generate_anchors", "generate_targets", "label_to_gt_box_3d",
 ]

@@ -503,3 +503,46 @@ class RPN(nn.Module):
         d3 = self.deconv3(x)
         x = torch.cat([d3, d2, d1], dim=1)
         return torch.sigmoid(self.prob_conv(x)), self.reg_conv(x)
+
+
+class MiddleRPN(nn.Module):
+    """Drop-in for the reference's WHOLE `MiddleConvNet` (model.py:202-281): the three 3-D layers (`middle_layer`, on the
+    tcgen05 kernel like `MiddleConvNet` here) and the RPN half (`block1..3`, `deconv1..3`, `prob_conv`, `reg_conv`) under
+    the reference's attribute and parameter names, so `RPN3D.middle_rpn = MiddleRPN(cls_name)` keeps a reference checkpoint
+    loading with a strict `load_state_dict`.  forward(x (B,D,H,W,128)) -> (sigmoid(prob) (B,2,h,w), reg (B,14,h,w)) like
+    model.py:257-281; the RPN half of this forward is the stock fp32 path (training, parity).
+
+    Inference: `front_end(feature_net, cls_name)` + `hybrid()` give the fused eval step and the bf16 tcgen05 RPN that
+    belong together (channel permutation of block1's first layer applied)."""
+
+    _RPN_PARTS = ("block1", "deconv1", "block2", "deconv2", "block3", "deconv3", "prob_conv", "reg_conv")
+
+    def __init__(self, cls_name: str = "Car"):
+        super().__init__()
+        from .model import MiddleConvNet
+
+        self.cls_name = cls_name
+        self.middle_layer = MiddleConvNet().middle_layer
+        rpn = RPN(cls_name)
+        for name in self._RPN_PARTS:  # registration order = the reference's (state_dict order matches too)
+            setattr(self, name, getattr(rpn, name))
+        self.output_shape = rpn.output_shape
+
+    def forward(self, x: torch.Tensor):
+        from .model import MiddleConvNet
+
+        return RPN.forward(self, MiddleConvNet.forward(self, x))  # (both only read the sub-modules registered above)
+
+    def hybrid(self) -> "HybridRPN":
+        """The RPN half as `HybridRPN` (a snapshot of the current parameters; eval mode)."""
+        return HybridRPN(self)
+
+    def front_end(self, feature_net: nn.Module, **kw):
+        """(`VoxelNetFrontEnd` over feature_net + this module's 3-D layers with bf16 channels-last output, `HybridRPN` whose
+        first layer takes that tensor's channel order): `prob, reg = rpn(fe.forward_frames(frames))`."""
+        from .pipeline import VoxelNetFrontEnd
+
+        fe = VoxelNetFrontEnd(feature_net, self, self.cls_name, output_format="nhwc_bf16", **kw)
+        rpn = self.hybrid()
+        rpn.permute_input_channels(fe.reference_channel_of_output())
+        return fe, rpn
