@@ -205,3 +205,48 @@ def middle_layers_bf16_emulated(dense: torch.Tensor, sd: dict, prefix: str = "mi
             acts.append(x)
     out = x.reshape((B, -1, H, W))
     return (out, acts) if return_acts else out
+
+
+def fill_rpn_parameters(module, seed: int = 0) -> str:
+    """Deterministic, NAME-keyed values for every RPN parameter and buffer of `module` (the reference's `MiddleConvNet`,
+    or any mirror with the same names: block1..3, deconv1..3, prob_conv, reg_conv; voxelnet/model.py:212-254), so that the
+    reference in the container and a mirror on the GPU box hold the same numbers without shipping 18 MB of weights.
+    Weights: uniform with the He bound of their fan-in (activations keep their scale through the 20 layers); BatchNorm
+    scale 0.5..1.5, shift +-0.2, running mean +-0.15, running variance 0.5..1.5.  `middle_layer.*` is left alone.
+    Returns the sha256 of the filled values (the golden stores it)."""
+    import hashlib
+    import zlib
+
+    h = hashlib.sha256()
+    with torch.no_grad():
+        for name, t in module.state_dict().items():
+            if name.startswith("middle_layer.") or name.endswith("num_batches_tracked"):
+                continue
+            g = torch.Generator().manual_seed((zlib.crc32(name.encode()) ^ (seed * 2654435761)) & 0x7FFFFFFF)
+            u = torch.rand(t.shape, generator=g, dtype=torch.float32)
+            if name.endswith("running_var"):
+                v = 0.5 + u
+            elif name.endswith("running_mean"):
+                v = (u - 0.5) * 0.3
+            elif name.endswith("batch_norm.weight"):
+                v = 0.5 + u
+            elif name.endswith("batch_norm.bias"):
+                v = (u - 0.5) * 0.4
+            elif name.endswith("deconv.weight"):  # (cin, cout, k, k), kernel = stride except the 3x3 stride-1 deconv1
+                k = t.shape[2]
+                taps = 9 if k == 3 else 1
+                v = (u - 0.5) * 2.0 * (6.0 / (t.shape[0] * taps)) ** 0.5
+            elif name.endswith(".weight"):        # (cout, cin, k, k)
+                v = (u - 0.5) * 2.0 * (6.0 / (t.shape[1] * t.shape[2] * t.shape[3])) ** 0.5
+            else:                                  # conv / deconv bias
+                v = (u - 0.5) * 0.2
+            t.copy_(v.to(t.dtype))
+            h.update(name.encode())
+            h.update(v.contiguous().numpy().tobytes())
+    return h.hexdigest()
+
+
+def rpn_golden_input(seed: int = 0, shape=(1, 128, 64, 48)) -> torch.Tensor:
+    """The seeded non-negative map the RPN golden is computed on (what the ReLU of the last 3-D layer hands over)."""
+    g = torch.Generator().manual_seed(1000 + seed)
+    return torch.randn(shape, generator=g).relu()

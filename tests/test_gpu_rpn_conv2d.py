@@ -310,3 +310,36 @@ def test_middle_rpn_drop_in_forward_and_fused_inference_pair(cuda_device):
         p_got, r_got = hy(fe.forward_frames(frames))
     assert p_got.shape == p_want.shape == (2, 2, 200, 240) and r_got.shape == (2, 14, 200, 240)
     assert float((p_got - p_want).abs().max()) < 2e-2 and float((r_got - r_want).norm() / r_want.norm()) < 2e-2
+
+
+def test_hybrid_rpn_matches_the_reference_rpn_golden(cuda_device):
+    """HybridRPN against tests/golden/rpn_car.npz - outputs of the UNMODIFIED reference's RPN half (oracle/make_golden_rpn.py),
+    parameters re-created here by the same name-keyed seeded fill.  Bars as for the fp32 comparison above (20 bf16 layers):
+    regression map rel-L2 2e-2; probabilities 3e-2 absolute (the seeded He-scale weights give logits up to |8|, and at this small
+    map the default tile policy = the all-stock cuDNN bf16 path was observed at 2.1e-2); every layer on the tcgen05 kernel, the
+    heads too, and the default tile policy."""
+    import voxelnet_pytorch_b200 as vn
+    from oracle import model_torch as OM
+    from tests import golden_util as G
+
+    g = G.load("rpn_car.npz")
+    seed = int(g["seed"])
+    net = vn.RPN("Car").eval()
+    assert OM.fill_rpn_parameters(net, seed) == str(g["params_sha256"])
+    x = OM.rpn_golden_input(seed, tuple(int(v) for v in g["input_shape"])).to(cuda_device)
+    want_p, want_r = torch.from_numpy(g["prob"]), torch.from_numpy(g["reg"])
+    rpn = vn.HybridRPN(net.to(cuda_device))
+    with torch.no_grad():
+        rpn.set_min_tiles(0)
+        p0, r0 = rpn(x)
+        rpn.heads_on_tensor_cores = True
+        p1, r1 = rpn(x)
+        rpn.heads_on_tensor_cores = False
+        rpn.set_min_tiles(None)
+        p2, r2 = rpn(x)
+    for name, (p, r) in (("all 3x3 / deconv layers on tcgen05", (p0, r0)), ("+ heads on tcgen05", (p1, r1)), ("default tile policy", (p2, r2))):
+        assert p.shape == want_p.shape and r.shape == want_r.shape and p.dtype == torch.float32, name
+        ep, er = float((p.cpu() - want_p).abs().max()), float((r.cpu() - want_r).norm() / want_r.norm())
+        print("rpn golden: %s: prob max-abs err %.4f, reg rel-L2 %.5f" % (name, ep, er))
+        assert ep < 3e-2, name
+        assert er < 2e-2, name

@@ -153,3 +153,31 @@ def test_oracle_whole_chain_matches_reference_golden_on_a_full_kitti_frame():
     assert err < 1e-5, err
     sums = out.double().sum(dim=(0, 2, 3)).numpy()
     assert np.allclose(sums, g["out_channel_sums"], rtol=1e-6, atol=1e-3)
+
+
+def test_rpn_mirror_matches_the_reference_rpn_golden():
+    """tests/golden/rpn_car.npz = the RPN half of the unmodified reference's MiddleConvNet (oracle/make_golden_rpn.py) on a
+    seeded map with name-keyed seeded parameters.  The stock fp32 mirror `vn.RPN('Car')`, filled the same way, reproduces it
+    on the CPU (float32 convolutions on whatever host kernels: 1e-4 of the output range)."""
+    import hashlib
+
+    import voxelnet_pytorch_b200 as vn
+
+    g = G.load("rpn_car.npz")
+    seed = int(g["seed"])
+    net = vn.RPN("Car").eval()
+    assert OM.fill_rpn_parameters(net, seed) == str(g["params_sha256"])
+    x = OM.rpn_golden_input(seed, tuple(int(v) for v in g["input_shape"]))
+    assert hashlib.sha256(x.numpy().tobytes()).hexdigest() == str(g["input_sha256"])
+    with torch.no_grad():
+        prob, reg = net(x)
+    want_p, want_r = torch.from_numpy(g["prob"]), torch.from_numpy(g["reg"])
+    assert prob.shape == want_p.shape and reg.shape == want_r.shape
+    assert float((prob - want_p).abs().max()) <= 1e-4
+    assert float((reg - want_r).abs().max()) <= 1e-4 * float(want_r.abs().max())
+    # the whole-MiddleConvNet drop-in holds the same RPN under the same names
+    both = vn.MiddleRPN("Car").eval()
+    assert OM.fill_rpn_parameters(both, seed) == str(g["params_sha256"])
+    with torch.no_grad():
+        p2, r2 = vn.RPN.forward(both, x)
+    assert torch.equal(p2, prob) and torch.equal(r2, reg)

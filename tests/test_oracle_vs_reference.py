@@ -208,3 +208,26 @@ def test_middle_rpn_is_a_strict_state_dict_match_of_the_reference_middle_conv_ne
         want = torch.sigmoid(net.prob_conv(cat)), net.reg_conv(cat)
     assert torch.equal(got[0], want[0]) and torch.equal(got[1], want[1])
     assert isinstance(mine.hybrid(), vn.HybridRPN)
+
+
+def test_rpn_golden_is_what_the_live_reference_computes():
+    """tests/golden/rpn_car.npz regenerates bit for bit from the live reference (same torch build as the generator's)."""
+    import hashlib
+
+    from tests import golden_util as G
+
+    g = G.load("rpn_car.npz")
+    ref = R.load_reference()
+    net = ref.model.MiddleConvNet().eval()
+    assert OM.fill_rpn_parameters(net, int(g["seed"])) == str(g["params_sha256"])
+    x = OM.rpn_golden_input(int(g["seed"]), tuple(int(v) for v in g["input_shape"]))
+    assert hashlib.sha256(x.numpy().tobytes()).hexdigest() == str(g["input_sha256"])
+    with torch.no_grad():
+        h = net.block1(x)
+        d1 = net.deconv1(h)
+        h = net.block2(h)
+        d2 = net.deconv2(h)
+        h = net.block3(h)
+        cat = torch.cat([net.deconv3(h), d2, d1], 1)
+        prob, reg = torch.sigmoid(net.prob_conv(cat)), net.reg_conv(cat)
+    assert np.array_equal(prob.numpy(), g["prob"]) and np.array_equal(reg.numpy(), g["reg"])
