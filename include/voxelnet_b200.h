@@ -285,7 +285,8 @@ int vn_conv3d_bn_relu_fwd_rows(const vn_grid_t* grid, const void* rows_bf16, int
  *   kernel flipped and its channel axes swapped: voxelnet/model.py:229 deconv1).
  * planned != 0: `workspace` still holds the work plan of an earlier launch with the same B, H, W and cout (the plan of a dense
  *   2-D layer depends on nothing else) - it is reused instead of rebuilt.
- * workspace: vn_conv2d_workspace_bytes(B, output H, output W).  The strided deconvolutions and the 1x1 heads are not covered. */
+ * workspace: vn_conv2d_workspace_bytes(B, output H, output W).  The strided deconvolutions (kernel = stride) and the 1x1 heads go through
+ *   vn_conv2d_pointwise_fwd below. */
 size_t vn_conv2d_workspace_bytes(int32_t B, int32_t H, int32_t W);
 size_t vn_conv2d_packed_weight_bytes(int32_t cin);
 int vn_conv2d_pack_weights(const float* weight, const float* scale, int32_t cin, int32_t cout,
